@@ -1,0 +1,181 @@
+/*
+ * pdb200.h — C-ABI of the B200-native PHI hot path (libpdb200.so).
+ *
+ * One entry point per PHI kernel on the path named by BASELINE.json's north_star:
+ * the broadcast/elementwise and reduce machinery of
+ *   paddle/phi/kernels/funcs/broadcast_function.h, reduce_function.h
+ * and the ops built directly on it.  Each function is what a PHI kernel body
+ * (PD_REGISTER_KERNEL / PD_RegisterPhiKernel) forwards to after
+ * it has pulled raw pointers, dims and the stream out of DenseTensor / GPUContext.
+ *
+ * Conventions (identical for every entry point)
+ *   - plain pointers and sizes only; no C++/torch/Paddle types cross this boundary;
+ *   - every tensor pointer is DEVICE memory of the current CUDA device, contiguous
+ *     row-major (PHI's PrepareData guarantees this, paddle/phi/api/lib/data_transform.cc:394-428);
+ *   - outputs are caller-allocated with the shape/dtype Paddle's InferMeta produces
+ *     (the kernel's `dev_ctx.Alloc<T>(out)`, paddle/phi/core/device_context.h:156);
+ *   - `stream` is a cudaStream_t passed as void* (dev_ctx.stream(),
+ *     paddle/phi/backends/gpu/gpu_context.h:100); all work is enqueued on it and the
+ *     call never synchronises the host;
+ *   - scratch memory is caller-provided (`workspace`, `workspace_bytes`), sized by the
+ *     matching *_workspace_bytes() query — the PHI wrapper allocates it from Paddle's
+ *     stream-safe allocator the way reduce_function.h:287-295 does with phi::Empty;
+ *   - return value: PDB200_OK or an error code; pdb200_last_error() returns the
+ *     message of the last failure on the calling thread (the PHI wrapper turns it into
+ *     PADDLE_THROW(InvalidArgument(...)) — same checks as the reference, cited below);
+ *   - there is NO CPU fallback: without a CUDA device every compute call fails with
+ *     PDB200_CUDA_ERROR.
+ */
+#ifndef PDB200_H_
+#define PDB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define PDB200_API __attribute__((visibility("default")))
+#else
+#define PDB200_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* dtype codes (subset of phi::DataType, paddle/phi/common/data_type.h) */
+typedef enum {
+  PDB200_BOOL = 0,
+  PDB200_UINT8 = 1,
+  PDB200_INT8 = 2,
+  PDB200_INT16 = 3,
+  PDB200_INT32 = 4,
+  PDB200_INT64 = 5,
+  PDB200_FLOAT16 = 6,
+  PDB200_BFLOAT16 = 7,
+  PDB200_FLOAT32 = 8,
+  PDB200_FLOAT64 = 9
+} pdb200_dtype;
+
+typedef enum {
+  PDB200_OK = 0,
+  PDB200_INVALID_ARGUMENT = 1, /* shape/axis/dtype rule violated (PADDLE_ENFORCE_* in the reference) */
+  PDB200_UNSUPPORTED = 2,      /* dtype not registered for this op in the reference either */
+  PDB200_CUDA_ERROR = 3,       /* launch/runtime failure, or no CUDA device */
+  PDB200_WORKSPACE_TOO_SMALL = 4
+} pdb200_status;
+
+#define PDB200_MAX_RANK 9 /* common::DDim::kMaxRank, paddle/common/ddim.h */
+
+/* Message of the last error raised on this thread ("" if none). */
+PDB200_API const char* pdb200_last_error(void);
+/* Library version string and the SM architecture it was compiled for ("sm_100a"). */
+PDB200_API const char* pdb200_version(void);
+/* Number of kernels this library has launched in this process (all threads). */
+PDB200_API uint64_t pdb200_launch_count(void);
+
+/* ---------------------------------------------------------------------------
+ * Shape helpers (host only, no CUDA): what InferMeta computes for these ops.
+ * ------------------------------------------------------------------------- */
+
+/* NumPy right-aligned broadcast of two shapes.
+ * Replaces: funcs::GetBroadcastDimsArrays (paddle/phi/kernels/funcs/common_shape.h:35-93) as used by
+ * ElementwiseInferMeta (paddle/phi/infermeta/binary.cc:1652).  out_dims has room for PDB200_MAX_RANK. */
+PDB200_API int pdb200_broadcast_shape(const int64_t* x_dims, int x_rank, const int64_t* y_dims, int y_rank,
+                           int64_t* out_dims, int* out_rank);
+
+/* ---------------------------------------------------------------------------
+ * Elementwise with broadcasting.
+ * Replaces: phi::AddKernel / phi::MultiplyKernel<T, GPUContext>
+ *   (paddle/phi/kernels/kps/elementwise_kernel.cu:84-99, legacy/kps/elementwise_kernel.cu:25-33)
+ *   -> funcs::BroadcastKernel (paddle/phi/kernels/funcs/broadcast_function.h:759-824).
+ * out has the broadcast shape; x, y and out share `dtype`.  out may alias x or y when
+ * that operand already has the output shape (add_ / multiply_ in-place variants).
+ * dtypes: all of pdb200_dtype; multiply<bool> is logical AND (elementwise_functor.h:72-77).
+ * ------------------------------------------------------------------------- */
+PDB200_API int pdb200_add(const void* x, const int64_t* x_dims, int x_rank, const void* y,
+               const int64_t* y_dims, int y_rank, void* out, int dtype, void* stream);
+PDB200_API int pdb200_multiply(const void* x, const int64_t* x_dims, int x_rank, const void* y,
+                    const int64_t* y_dims, int y_rank, void* out, int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * Reductions.  `axes` may hold negative values; n_axes == 0 or reduce_all != 0 or a full axis
+ * set means "reduce everything" (phi::recompute_reduce_all, paddle/phi/core/kernel_utils.h:407-417).
+ * keep_dim only changes the output SHAPE (InferMeta), never the data, so it is not a parameter.
+ * x_dtype != out_dtype means "cast each element to out_dtype, then reduce in it"
+ * (paddle/phi/kernels/gpu/reduce.h:48-69); supported pairs: equal dtypes, any integer/bool -> INT64,
+ * FLOAT16/BFLOAT16 -> FLOAT32 (kps/reduce_kernel.cu:251-265), FLOAT32 -> FLOAT64.
+ * Accumulation type follows phi::dtype::MPTypeTrait (float for fp16/bf16, else out dtype;
+ * paddle/phi/common/amp_type_traits.h:24-54).  x must not be empty
+ * (reduce_function.h:1052-1055).  64-bit indexing throughout.
+ * ------------------------------------------------------------------------- */
+typedef enum {
+  PDB200_REDUCE_SUM = 0,
+  PDB200_REDUCE_MEAN = 1,
+  PDB200_REDUCE_MAX = 2,
+  PDB200_REDUCE_MIN = 3,
+  PDB200_REDUCE_PROD = 4
+} pdb200_reduce_op;
+
+/* Bytes of device scratch the call below needs for these arguments (0 when none). */
+PDB200_API size_t pdb200_reduce_workspace_bytes(int op, const int64_t* x_dims, int x_rank, const int64_t* axes,
+                                     int n_axes, int reduce_all, int x_dtype, int out_dtype);
+
+/* Replaces phi::SumRawKernel<T, GPUContext> (paddle/phi/kernels/kps/reduce_kernel.cu:184-271). */
+PDB200_API int pdb200_sum_raw(const void* x, const int64_t* x_dims, int x_rank, const int64_t* axes, int n_axes,
+                   int reduce_all, int x_dtype, int out_dtype, void* out, void* workspace,
+                   size_t workspace_bytes, void* stream);
+/* Replaces phi::MeanRawKernel (kps/reduce_kernel.cu:109-120). Integer mean truncates toward zero. */
+PDB200_API int pdb200_mean_raw(const void* x, const int64_t* x_dims, int x_rank, const int64_t* axes, int n_axes,
+                    int reduce_all, int x_dtype, int out_dtype, void* out, void* workspace,
+                    size_t workspace_bytes, void* stream);
+/* Replaces phi::MaxRawKernel (paddle/phi/kernels/legacy/kps/reduce_max_kernel.cu:21-32). */
+PDB200_API int pdb200_max_raw(const void* x, const int64_t* x_dims, int x_rank, const int64_t* axes, int n_axes,
+                   int reduce_all, int x_dtype, int out_dtype, void* out, void* workspace,
+                   size_t workspace_bytes, void* stream);
+/* Replaces phi::MinRawKernel (kps/reduce_kernel.cu:122-133). */
+PDB200_API int pdb200_min_raw(const void* x, const int64_t* x_dims, int x_rank, const int64_t* axes, int n_axes,
+                   int reduce_all, int x_dtype, int out_dtype, void* out, void* workspace,
+                   size_t workspace_bytes, void* stream);
+/* Replaces phi::ProdKernel (kps/reduce_kernel.cu:34-45). */
+PDB200_API int pdb200_prod(const void* x, const int64_t* x_dims, int x_rank, const int64_t* axes, int n_axes,
+                int reduce_all, int x_dtype, int out_dtype, void* out, void* workspace,
+                size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * argmax.  Replaces phi::ArgMaxKernel<T, GPUContext> (paddle/phi/kernels/gpu/arg_min_max_kernel.cu:59-204).
+ * Lowest index wins ties; out_dtype is PDB200_INT64 or PDB200_INT32; flatten != 0 reduces over the
+ * flattened tensor (axis ignored); 0-D input yields 0.  x must not be empty (:214-219).
+ * ------------------------------------------------------------------------- */
+PDB200_API size_t pdb200_argmax_workspace_bytes(const int64_t* x_dims, int x_rank, int64_t axis, int flatten,
+                                     int x_dtype);
+PDB200_API int pdb200_argmax(const void* x, const int64_t* x_dims, int x_rank, int64_t axis, int flatten,
+                  int x_dtype, int out_dtype, void* out, void* workspace, size_t workspace_bytes,
+                  void* stream);
+
+/* ---------------------------------------------------------------------------
+ * softmax forward along `axis`.  Replaces phi::SoftmaxGPUDNNKernel / SoftmaxKernel<T, GPUContext>
+ * (paddle/phi/kernels/gpudnn/softmax_kernel.cu:25-39 -> softmax_gpudnn.h:1239-1329).
+ * dtypes FLOAT32, FLOAT64, FLOAT16, BFLOAT16 (half types accumulate in float, one rounding at the end).
+ * numel == 0 is a no-op, 0-D yields 1.  x - max is clamped at -64 as the CPU kernel does
+ * (paddle/phi/kernels/funcs/softmax_impl.h:36-42).  out may alias x.
+ * ------------------------------------------------------------------------- */
+PDB200_API int pdb200_softmax(const void* x, const int64_t* dims, int rank, int axis, int dtype, void* out,
+                   void* stream);
+
+/* ---------------------------------------------------------------------------
+ * layer_norm forward.  Replaces phi::LayerNormKernel<T, GPUContext>
+ * (paddle/phi/kernels/gpu/layer_norm_kernel.cu:490-665).
+ * rows = prod(dims[:begin_norm_axis]), D = prod(dims[begin_norm_axis:]).  scale / bias may be NULL;
+ * param_dtype is `dtype` or PDB200_FLOAT32 and applies to both (:516-538).  y has x's dtype; mean and
+ * variance are FLOAT32 for fp16/bf16/fp32 inputs, FLOAT64 for FLOAT64 (LayerNormParamType,
+ * funcs/layer_norm_impl.cu.h:40-43) and hold `rows` values (biased variance, not rstd).
+ * mean / variance may be NULL when the caller does not need them.
+ * ------------------------------------------------------------------------- */
+PDB200_API int pdb200_layer_norm(const void* x, const int64_t* dims, int rank, const void* scale,
+                      const void* bias, int param_dtype, float epsilon, int begin_norm_axis,
+                      int dtype, void* y, void* mean, void* variance, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PDB200_H_ */

@@ -1,0 +1,363 @@
+// TEST INFRASTRUCTURE ONLY — never linked into, imported by, or called from the
+// product path (paddlepaddle_b200/).  Only tests/, __graft_entry__.smoke() and
+// bench.py's cpu_baseline / --impl reference legs may load the library built
+// from this file.
+//
+// This translation unit contains NO restated algorithm: it is a thin
+// `extern "C"` doorway onto the reference's *own* CPU PHI kernels, compiled in
+// place from the sources under /root/reference (never copied into this repo) by
+// oracle/build_ref.sh into oracle/_ref/libphi_cpu_ref.so.  What it reaches:
+//
+//   reduce      phi::funcs::ReduceKernelImpl   paddle/phi/kernels/funcs/reduce_function.h:1354-1402
+//               + Sum/Mean/Max/Min/ProdFunctor paddle/phi/kernels/funcs/reduce_functor.h:52-89
+//               (cast-before-reduce rule of     paddle/phi/kernels/cpu/reduce.h:56-65 is applied
+//                by the caller passing an already-cast buffer)
+//   argmax      phi::ArgMaxKernel<T,CPUContext> paddle/phi/kernels/cpu/arg_min_max_kernel.cc:150-196
+//   add/mul     phi::funcs::ElementwiseCompute  paddle/phi/kernels/funcs/elementwise_base.h:367-442
+//               + Add/MultiplyFunctor           paddle/phi/kernels/funcs/elementwise_functor.h:38-94
+//   softmax     phi::SoftmaxKernel<T,CPUContext> paddle/phi/kernels/impl/softmax_kernel_impl.h:25-53
+//               -> SoftmaxFunctor<CPUContext>   paddle/phi/kernels/funcs/softmax_impl.h:234-273
+//   layer_norm  CUDA-build branch of phi::LayerNormKernel<T,CPUContext>
+//               paddle/phi/kernels/cpu/layer_norm_kernel.cc:32-102 (the other branch needs the
+//               generated jit/kernels.h, absent from the tree)
+//   bf16 scalar phi::dtype::bfloat16            paddle/phi/common/bfloat16.h:61-88,264-276
+//
+// All of them run single-threaded on Eigen::DefaultDevice, exactly as Paddle
+// runs them (paddle/phi/backends/cpu/cpu_context.cc:40).
+
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "paddle/common/flags.h"
+#include "paddle/phi/backends/cpu/cpu_context.h"
+#include "paddle/phi/common/bfloat16.h"
+#include "paddle/phi/common/float16.h"
+#include "paddle/phi/common/scalar.h"
+#include "paddle/phi/core/dense_tensor.h"
+#include "paddle/phi/core/kernel_registry.h"
+
+// The reference kernel TUs end in PD_REGISTER_KERNEL(...) { body }.  We only want
+// the kernel templates, not a KernelFactory, so the registration becomes an
+// unused static function that swallows the body.
+#undef PD_REGISTER_KERNEL
+#define PD_REGISTER_KERNEL(name, backend, layout, fn, ...)                \
+  [[maybe_unused]] static void pdb200_unused_reg_##name##_##backend(      \
+      const ::phi::KernelKey& kernel_key, ::phi::Kernel* kernel)
+
+#include "paddle/phi/kernels/funcs/elementwise_base.h"
+#include "paddle/phi/kernels/funcs/elementwise_functor.h"
+#include "paddle/phi/kernels/funcs/layer_norm_util.h"
+#include "paddle/phi/kernels/funcs/math_function.h"
+#include "paddle/phi/kernels/funcs/reduce_function.h"
+#include "paddle/phi/kernels/funcs/reduce_functor.h"
+#include "paddle/phi/kernels/funcs/softmax.h"
+#include "paddle/phi/kernels/funcs/softmax_impl.h"
+#include "paddle/phi/kernels/impl/softmax_kernel_impl.h"
+
+#include "paddle/phi/kernels/cpu/arg_min_max_kernel.cc"  // NOLINT (kernel templates live in the .cc)
+
+// Defined in paddle/phi/core/kernel_factory.cc, which is deliberately not part of
+// this build (no KernelFactory needed); DenseTensor only reads it.
+PHI_DEFINE_EXPORTED_bool(use_stride_kernel, true, "oracle build: flag owned by kernel_factory.cc");
+
+namespace {
+
+class MallocAllocator : public phi::Allocator {
+ public:
+  static void Delete(phi::Allocation* a) {
+    std::free(a->ptr());
+    delete a;
+  }
+  AllocationPtr Allocate(size_t bytes) override {
+    void* p = nullptr;
+    if (posix_memalign(&p, 64, bytes ? bytes : 64) != 0) p = nullptr;
+    auto* a = new phi::Allocation(p, bytes, phi::CPUPlace());
+    return AllocationPtr(a, Delete);
+  }
+  bool IsAllocThreadSafe() const override { return true; }
+};
+
+struct Ctx {
+  MallocAllocator alloc;
+  phi::CPUContext ctx;
+  Ctx() {
+    ctx.SetAllocator(&alloc);
+    ctx.SetHostAllocator(&alloc);
+    ctx.SetZeroAllocator(&alloc);
+  }
+};
+
+Ctx& GetCtx() {
+  static Ctx c;
+  return c;
+}
+
+// dtype codes shared with include/pdb200.h
+enum DType {
+  kBool = 0, kUInt8 = 1, kInt8 = 2, kInt16 = 3, kInt32 = 4, kInt64 = 5,
+  kFloat16 = 6, kBFloat16 = 7, kFloat32 = 8, kFloat64 = 9
+};
+
+phi::DataType ToPhi(int dt) {
+  switch (dt) {
+    case kBool: return phi::DataType::BOOL;
+    case kUInt8: return phi::DataType::UINT8;
+    case kInt8: return phi::DataType::INT8;
+    case kInt16: return phi::DataType::INT16;
+    case kInt32: return phi::DataType::INT32;
+    case kInt64: return phi::DataType::INT64;
+    case kFloat16: return phi::DataType::FLOAT16;
+    case kBFloat16: return phi::DataType::BFLOAT16;
+    case kFloat32: return phi::DataType::FLOAT32;
+    case kFloat64: return phi::DataType::FLOAT64;
+  }
+  return phi::DataType::UNDEFINED;
+}
+
+// Borrow caller memory as a DenseTensor (no ownership).
+phi::DenseTensor Wrap(const void* data, const int64_t* dims, int rank, int dt) {
+  std::vector<int64_t> d(dims, dims + rank);
+  phi::DDim ddim = common::make_ddim(d);
+  phi::DenseTensorMeta meta(ToPhi(dt), ddim);
+  size_t bytes = static_cast<size_t>(common::product(ddim)) * phi::SizeOf(ToPhi(dt));
+  auto holder = std::make_shared<phi::Allocation>(const_cast<void*>(data), bytes, phi::CPUPlace());
+  return phi::DenseTensor(holder, meta);
+}
+
+thread_local std::string g_last_error;
+
+template <typename F>
+int Guard(F&& f) {
+  try {
+    f();
+    return 0;
+  } catch (const std::exception& e) {
+    g_last_error = e.what();
+    return 1;
+  } catch (...) {
+    g_last_error = "unknown exception";
+    return 1;
+  }
+}
+
+template <typename T, typename Functor>
+void ReduceT(const phi::DenseTensor& x, phi::DenseTensor* out, const std::vector<int64_t>& axes,
+             bool keep_dim, bool reduce_all) {
+  phi::funcs::ReduceKernelImpl<phi::CPUContext, T, T, Functor>(GetCtx().ctx, x, out, axes, keep_dim,
+                                                               reduce_all);
+}
+
+template <typename T>
+void ReduceOp(int op, const phi::DenseTensor& x, phi::DenseTensor* out,
+              const std::vector<int64_t>& axes, bool keep_dim, bool reduce_all) {
+  switch (op) {
+    case 0: ReduceT<T, phi::funcs::SumFunctor>(x, out, axes, keep_dim, reduce_all); break;
+    case 1: ReduceT<T, phi::funcs::MeanFunctor>(x, out, axes, keep_dim, reduce_all); break;
+    case 2: ReduceT<T, phi::funcs::MaxFunctor>(x, out, axes, keep_dim, reduce_all); break;
+    case 3: ReduceT<T, phi::funcs::MinFunctor>(x, out, axes, keep_dim, reduce_all); break;
+    case 4: ReduceT<T, phi::funcs::ProdFunctor>(x, out, axes, keep_dim, reduce_all); break;
+    default: throw std::runtime_error("bad reduce op");
+  }
+}
+
+template <typename T>
+void ElementwiseOp(int op, const phi::DenseTensor& x, const phi::DenseTensor& y,
+                   phi::DenseTensor* z) {
+  // Same routing as phi::AddKernel<T,CPUContext> minus the BLAS VADD shortcut
+  // (cpu/elementwise_add_kernel.cc:27-56, cpu/elementwise.h:30-69): the
+  // arithmetic is identical, and x.numel() < y.numel() uses the inverse functor.
+  auto xd = x.dims(), yd = y.dims();
+  bool x_larger = xd.size() >= yd.size();
+  if (op == 0) {
+    if (x_larger)
+      phi::funcs::ElementwiseCompute<phi::funcs::AddFunctor<T>, T>(GetCtx().ctx, x, y,
+                                                                   phi::funcs::AddFunctor<T>(), z, -1);
+    else
+      phi::funcs::ElementwiseCompute<phi::funcs::InverseAddFunctor<T>, T>(
+          GetCtx().ctx, x, y, phi::funcs::InverseAddFunctor<T>(), z, -1);
+  } else {
+    if (x_larger)
+      phi::funcs::ElementwiseCompute<phi::funcs::MultiplyFunctor<T>, T>(
+          GetCtx().ctx, x, y, phi::funcs::MultiplyFunctor<T>(), z, -1);
+    else
+      phi::funcs::ElementwiseCompute<phi::funcs::InverseMultiplyFunctor<T>, T>(
+          GetCtx().ctx, x, y, phi::funcs::InverseMultiplyFunctor<T>(), z, -1);
+  }
+}
+
+// CUDA-build branch of the CPU layer_norm kernel, cpu/layer_norm_kernel.cc:48-102,
+// called through the reference's own helpers (RowwiseMean2D, ElementwiseCompute,
+// SubAndSquareFunctor, DivAndSqrtFunctor).  Only the statement order is ours.
+template <typename T>
+void LayerNormT(const phi::DenseTensor& x, const phi::DenseTensor* scale,
+                const phi::DenseTensor* bias, float epsilon, int begin_norm_axis,
+                phi::DenseTensor* y, phi::DenseTensor* mean, phi::DenseTensor* var) {
+  auto& dev_ctx = GetCtx().ctx;
+  auto matrix_dim = common::flatten_to_2d(x.dims(), begin_norm_axis);
+  int left = static_cast<int>(matrix_dim[0]);
+  int right = static_cast<int>(matrix_dim[1]);
+  phi::DDim matrix_shape({left, right});
+  phi::DDim normalized_shape({left});
+  auto x_tmp = x;
+  x_tmp.Resize(matrix_shape);
+  phi::DenseTensor out;
+  out.ShareDataWith(*y);
+  out.Resize(matrix_shape);
+  phi::DenseTensor mean_tmp;
+  mean_tmp.ShareDataWith(*mean);
+  mean_tmp.Resize(normalized_shape);
+  phi::DenseTensor var_tmp;
+  var_tmp.ShareDataWith(*var);
+  var_tmp.Resize(normalized_shape);
+
+  phi::funcs::RowwiseMean2D<phi::CPUContext, T> row_mean(left, right, dev_ctx);
+  row_mean(dev_ctx, x_tmp, &mean_tmp);
+  phi::funcs::ElementwiseCompute<phi::funcs::SubAndSquareFunctor<T>, T>(
+      dev_ctx, x_tmp, mean_tmp, phi::funcs::SubAndSquareFunctor<T>(), &out, 0);
+  row_mean(dev_ctx, out, &var_tmp);
+  phi::funcs::ElementwiseCompute<phi::funcs::SubtractFunctor<T>, T>(
+      dev_ctx, x_tmp, mean_tmp, phi::funcs::SubtractFunctor<T>(), &out, 0);
+  phi::funcs::ElementwiseCompute<phi::funcs::DivAndSqrtFunctor<T>, T>(
+      dev_ctx, out, var_tmp, phi::funcs::DivAndSqrtFunctor<T>(static_cast<T>(epsilon)), &out, 0);
+  if (scale) {
+    phi::funcs::ElementwiseCompute<phi::funcs::MultiplyFunctor<T>, T>(
+        dev_ctx, out, *scale, phi::funcs::MultiplyFunctor<T>(), &out, 1);
+  }
+  if (bias) {
+    phi::funcs::ElementwiseCompute<phi::funcs::AddFunctor<T>, T>(
+        dev_ctx, out, *bias, phi::funcs::AddFunctor<T>(), &out, 1);
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* phi_ref_last_error() { return g_last_error.c_str(); }
+
+// op: 0 sum, 1 mean, 2 max, 3 min, 4 prod.  `out_dims` is the shape InferMeta
+// would have produced (keep_dim decides whether reduced dims stay as 1).
+int phi_ref_reduce(int op, int dtype, const void* x, const int64_t* dims, int rank,
+                   const int64_t* axes, int n_axes, int keep_dim, int reduce_all,
+                   const int64_t* out_dims, int out_rank, void* out) {
+  return Guard([&] {
+    auto xt = Wrap(x, dims, rank, dtype);
+    auto ot = Wrap(out, out_dims, out_rank, dtype);
+    std::vector<int64_t> ax(axes, axes + n_axes);
+    bool ra = phi::recompute_reduce_all(xt, ax, reduce_all != 0);
+    switch (dtype) {
+      case kFloat32: ReduceOp<float>(op, xt, &ot, ax, keep_dim, ra); break;
+      case kFloat64: ReduceOp<double>(op, xt, &ot, ax, keep_dim, ra); break;
+      case kInt32: ReduceOp<int32_t>(op, xt, &ot, ax, keep_dim, ra); break;
+      case kInt64: ReduceOp<int64_t>(op, xt, &ot, ax, keep_dim, ra); break;
+      default: throw std::runtime_error("phi_ref_reduce: dtype not registered on CPU");
+    }
+  });
+}
+
+int phi_ref_argmax(int dtype, const void* x, const int64_t* dims, int rank, int64_t axis,
+                   int keepdims, int flatten, int out_dtype, const int64_t* out_dims,
+                   int out_rank, void* out) {
+  return Guard([&] {
+    auto xt = Wrap(x, dims, rank, dtype);
+    auto ot = Wrap(out, out_dims, out_rank, out_dtype);
+    phi::Scalar ax(axis);
+    auto& ctx = GetCtx().ctx;
+    switch (dtype) {
+      case kFloat32: phi::ArgMaxKernel<float, phi::CPUContext>(ctx, xt, ax, keepdims, flatten, ToPhi(out_dtype), &ot); break;
+      case kFloat64: phi::ArgMaxKernel<double, phi::CPUContext>(ctx, xt, ax, keepdims, flatten, ToPhi(out_dtype), &ot); break;
+      case kInt32: phi::ArgMaxKernel<int32_t, phi::CPUContext>(ctx, xt, ax, keepdims, flatten, ToPhi(out_dtype), &ot); break;
+      case kInt64: phi::ArgMaxKernel<int64_t, phi::CPUContext>(ctx, xt, ax, keepdims, flatten, ToPhi(out_dtype), &ot); break;
+      case kInt16: phi::ArgMaxKernel<int16_t, phi::CPUContext>(ctx, xt, ax, keepdims, flatten, ToPhi(out_dtype), &ot); break;
+      case kUInt8: phi::ArgMaxKernel<uint8_t, phi::CPUContext>(ctx, xt, ax, keepdims, flatten, ToPhi(out_dtype), &ot); break;
+      default: throw std::runtime_error("phi_ref_argmax: dtype not registered on CPU");
+    }
+  });
+}
+
+// op: 0 add, 1 multiply.
+int phi_ref_elementwise(int op, int dtype, const void* x, const int64_t* xdims, int xrank,
+                        const void* y, const int64_t* ydims, int yrank, const int64_t* odims,
+                        int orank, void* out) {
+  return Guard([&] {
+    auto xt = Wrap(x, xdims, xrank, dtype);
+    auto yt = Wrap(y, ydims, yrank, dtype);
+    auto ot = Wrap(out, odims, orank, dtype);
+    switch (dtype) {
+      case kFloat32: ElementwiseOp<float>(op, xt, yt, &ot); break;
+      case kFloat64: ElementwiseOp<double>(op, xt, yt, &ot); break;
+      case kInt32: ElementwiseOp<int32_t>(op, xt, yt, &ot); break;
+      case kInt64: ElementwiseOp<int64_t>(op, xt, yt, &ot); break;
+      case kInt16: ElementwiseOp<int16_t>(op, xt, yt, &ot); break;
+      case kUInt8: ElementwiseOp<uint8_t>(op, xt, yt, &ot); break;
+      case kInt8: ElementwiseOp<int8_t>(op, xt, yt, &ot); break;
+      case kBool: ElementwiseOp<bool>(op, xt, yt, &ot); break;
+      case kBFloat16: ElementwiseOp<phi::dtype::bfloat16>(op, xt, yt, &ot); break;
+      case kFloat16: ElementwiseOp<phi::dtype::float16>(op, xt, yt, &ot); break;
+      default: throw std::runtime_error("phi_ref_elementwise: bad dtype");
+    }
+  });
+}
+
+int phi_ref_softmax(int dtype, const void* x, const int64_t* dims, int rank, int axis, void* out) {
+  return Guard([&] {
+    auto xt = Wrap(x, dims, rank, dtype);
+    auto ot = Wrap(out, dims, rank, dtype);
+    auto& ctx = GetCtx().ctx;
+    switch (dtype) {
+      case kFloat32: phi::SoftmaxKernel<float, phi::CPUContext>(ctx, xt, axis, &ot); break;
+      case kFloat64: phi::SoftmaxKernel<double, phi::CPUContext>(ctx, xt, axis, &ot); break;
+      default: throw std::runtime_error("phi_ref_softmax: dtype not registered on CPU");
+    }
+  });
+}
+
+int phi_ref_layer_norm(int dtype, const void* x, const int64_t* dims, int rank, const void* scale,
+                       const void* bias, float epsilon, int begin_norm_axis, void* y, void* mean,
+                       void* var) {
+  return Guard([&] {
+    auto xt = Wrap(x, dims, rank, dtype);
+    auto yt = Wrap(y, dims, rank, dtype);
+    int64_t left = 1, right = 1;
+    for (int i = 0; i < begin_norm_axis; ++i) left *= dims[i];
+    for (int i = begin_norm_axis; i < rank; ++i) right *= dims[i];
+    auto mt = Wrap(mean, &left, 1, dtype);
+    auto vt = Wrap(var, &left, 1, dtype);
+    phi::DenseTensor st, bt;
+    if (scale) st = Wrap(scale, &right, 1, dtype);
+    if (bias) bt = Wrap(bias, &right, 1, dtype);
+    switch (dtype) {
+      case kFloat32: LayerNormT<float>(xt, scale ? &st : nullptr, bias ? &bt : nullptr, epsilon, begin_norm_axis, &yt, &mt, &vt); break;
+      case kFloat64: LayerNormT<double>(xt, scale ? &st : nullptr, bias ? &bt : nullptr, epsilon, begin_norm_axis, &yt, &mt, &vt); break;
+      default: throw std::runtime_error("phi_ref_layer_norm: dtype not registered on CPU");
+    }
+  });
+}
+
+// Scalar bf16 rules (phi/common/bfloat16.h): float -> bf16 (RNE, NaN -> 0x7FFF) and back.
+void phi_ref_float_to_bf16(const float* in, uint16_t* out, int64_t n) {
+  for (int64_t i = 0; i < n; ++i) out[i] = phi::dtype::bfloat16(in[i]).x;
+}
+void phi_ref_bf16_to_float(const uint16_t* in, float* out, int64_t n) {
+  for (int64_t i = 0; i < n; ++i) {
+    phi::dtype::bfloat16 b;
+    b.x = in[i];
+    out[i] = static_cast<float>(b);
+  }
+}
+void phi_ref_float_to_fp16(const float* in, uint16_t* out, int64_t n) {
+  for (int64_t i = 0; i < n; ++i) out[i] = phi::dtype::float16(in[i]).x;
+}
+void phi_ref_fp16_to_float(const uint16_t* in, float* out, int64_t n) {
+  for (int64_t i = 0; i < n; ++i) {
+    phi::dtype::float16 h;
+    h.x = in[i];
+    out[i] = static_cast<float>(h);
+  }
+}
+
+}  // extern "C"

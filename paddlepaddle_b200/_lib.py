@@ -1,0 +1,84 @@
+"""ctypes binding of libpdb200.so (the C-ABI declared in include/pdb200.h).
+
+The library is the product: if it is missing or does not load, importing the ops fails
+loudly.  There is no Python, PyTorch or CPU fallback for any compute call.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpdb200.so")
+
+# dtype codes, include/pdb200.h
+BOOL, UINT8, INT8, INT16, INT32, INT64, FLOAT16, BFLOAT16, FLOAT32, FLOAT64 = range(10)
+OK, INVALID_ARGUMENT, UNSUPPORTED, CUDA_ERROR, WORKSPACE_TOO_SMALL = range(5)
+REDUCE_SUM, REDUCE_MEAN, REDUCE_MAX, REDUCE_MIN, REDUCE_PROD = range(5)
+MAX_RANK = 9
+
+_c_i64p = ctypes.POINTER(ctypes.c_int64)
+_vp = ctypes.c_void_p
+_int = ctypes.c_int
+_sz = ctypes.c_size_t
+
+# name -> (restype, argtypes); every symbol include/pdb200.h declares
+SIGNATURES = {
+    "pdb200_last_error": (ctypes.c_char_p, []),
+    "pdb200_version": (ctypes.c_char_p, []),
+    "pdb200_launch_count": (ctypes.c_uint64, []),
+    "pdb200_broadcast_shape": (_int, [_c_i64p, _int, _c_i64p, _int, _c_i64p, ctypes.POINTER(_int)]),
+    "pdb200_add": (_int, [_vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
+    "pdb200_multiply": (_int, [_vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
+    "pdb200_reduce_workspace_bytes": (_sz, [_int, _c_i64p, _int, _c_i64p, _int, _int, _int, _int]),
+    "pdb200_sum_raw": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _int, _vp, _vp, _sz, _vp]),
+    "pdb200_mean_raw": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _int, _vp, _vp, _sz, _vp]),
+    "pdb200_max_raw": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _int, _vp, _vp, _sz, _vp]),
+    "pdb200_min_raw": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _int, _vp, _vp, _sz, _vp]),
+    "pdb200_prod": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _int, _vp, _vp, _sz, _vp]),
+    "pdb200_argmax_workspace_bytes": (_sz, [_c_i64p, _int, ctypes.c_int64, _int, _int]),
+    "pdb200_argmax": (_int, [_vp, _c_i64p, _int, ctypes.c_int64, _int, _int, _int, _vp, _vp, _sz, _vp]),
+    "pdb200_softmax": (_int, [_vp, _c_i64p, _int, _int, _int, _vp, _vp]),
+    "pdb200_layer_norm": (_int, [_vp, _c_i64p, _int, _vp, _vp, _int, ctypes.c_float, _int, _int, _vp, _vp, _vp, _vp]),
+}
+
+_lib = None
+
+
+def load():
+    """Load libpdb200.so once; raise if it is not built (run `make` or __graft_entry__.build())."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} not found: the CUDA extension is not built. Run `make` at the repo root "
+                "(or `python -c 'import __graft_entry__ as g; g.build()'`). There is no fallback path.")
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def dims_array(dims):
+    n = len(dims)
+    arr = (ctypes.c_int64 * max(n, 1))(*[int(d) for d in dims])
+    return arr, n
+
+
+class PDB200Error(RuntimeError):
+    pass
+
+
+def check(rc, lib=None):
+    """Translate a C-ABI status into the exception Paddle's pybind would raise
+    (InvalidArgument -> ValueError, everything else -> RuntimeError)."""
+    if rc == OK:
+        return
+    lib = lib or load()
+    msg = lib.pdb200_last_error().decode("utf-8", "replace")
+    if rc == INVALID_ARGUMENT:
+        raise ValueError("(InvalidArgument) " + msg)
+    if rc == UNSUPPORTED:
+        raise NotImplementedError("(Unimplemented) " + msg)
+    raise PDB200Error(f"(External) pdb200 status {rc}: {msg}")

@@ -1,0 +1,187 @@
+// common.cuh — shared device/host helpers for the B200 (sm_100a) PHI hot path.
+//
+// Everything here is written for one target: compute_100a / sm_100a.  There is no
+// multi-arch dispatch and no CPU fallback.
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <string>
+
+#include "../../include/pdb200.h"
+
+namespace pdb200 {
+
+// ----------------------------------------------------------------------------
+// error plumbing (host)
+// ----------------------------------------------------------------------------
+void set_error(const std::string& msg);
+int fail(int code, const std::string& msg);
+extern std::atomic<uint64_t> g_launch_count;
+
+#define PDB_CHECK_ARG(cond, msg)                                          \
+  do {                                                                    \
+    if (!(cond)) return ::pdb200::fail(PDB200_INVALID_ARGUMENT, (msg));   \
+  } while (0)
+
+// Called after every <<<>>>: counts the launch and converts a launch error.
+inline int after_launch(const char* what) {
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    return fail(PDB200_CUDA_ERROR, std::string(what) + ": " + cudaGetErrorString(e));
+  }
+  return PDB200_OK;
+}
+
+inline int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+inline size_t dtype_size(int dt) {
+  switch (dt) {
+    case PDB200_BOOL: case PDB200_UINT8: case PDB200_INT8: return 1;
+    case PDB200_INT16: case PDB200_FLOAT16: case PDB200_BFLOAT16: return 2;
+    case PDB200_INT32: case PDB200_FLOAT32: return 4;
+    case PDB200_INT64: case PDB200_FLOAT64: return 8;
+  }
+  return 0;
+}
+
+inline bool is_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// ----------------------------------------------------------------------------
+// Accumulation type: phi::dtype::MPTypeTrait (amp_type_traits.h:24-54) —
+// float for fp16/bf16, the type itself otherwise.
+// ----------------------------------------------------------------------------
+template <typename T> struct AccType { using type = T; };
+template <> struct AccType<__half> { using type = float; };
+template <> struct AccType<__nv_bfloat16> { using type = float; };
+
+// Conversions.  float -> bf16/fp16 is round-to-nearest-even with canonical NaN
+// (0x7FFF for bf16), the same rule as phi/common/bfloat16.h:61-88.
+template <typename To, typename From>
+__device__ __forceinline__ To cvt(From v) { return static_cast<To>(v); }
+template <> __device__ __forceinline__ float cvt<float, __nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <> __device__ __forceinline__ float cvt<float, __half>(__half v) { return __half2float(v); }
+template <> __device__ __forceinline__ __nv_bfloat16 cvt<__nv_bfloat16, float>(float v) { return __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ __half cvt<__half, float>(float v) { return __float2half_rn(v); }
+template <> __device__ __forceinline__ __nv_bfloat16 cvt<__nv_bfloat16, __nv_bfloat16>(__nv_bfloat16 v) { return v; }
+template <> __device__ __forceinline__ __half cvt<__half, __half>(__half v) { return v; }
+template <> __device__ __forceinline__ double cvt<double, __nv_bfloat16>(__nv_bfloat16 v) { return (double)__bfloat162float(v); }
+template <> __device__ __forceinline__ double cvt<double, __half>(__half v) { return (double)__half2float(v); }
+template <> __device__ __forceinline__ int64_t cvt<int64_t, bool>(bool v) { return v ? 1 : 0; }
+
+// ----------------------------------------------------------------------------
+// 128-bit vectors.  Vec<T> is exactly 16 bytes: 8 x bf16/fp16/int16, 4 x fp32/int32,
+// 2 x fp64/int64, 16 x 8-bit.  (The reference caps vectors at 4 ELEMENTS, i.e. 8-byte
+// loads for bf16: funcs/aligned_vector.h:67-119.)
+// ----------------------------------------------------------------------------
+template <typename T>
+struct alignas(16) Vec {
+  static constexpr int N = 16 / sizeof(T);
+  T v[N];
+};
+
+// Streaming 16-byte load: read-only path, do not allocate in L1 (each byte is used once).
+template <typename T>
+__device__ __forceinline__ Vec<T> ld_stream(const T* p) {
+  Vec<T> r;
+  uint4 u;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
+               : "l"(p));
+  *reinterpret_cast<uint4*>(&r) = u;
+  return r;
+}
+// Cached 16-byte load (small operands that are re-read: broadcast rows, scale/bias).
+template <typename T>
+__device__ __forceinline__ Vec<T> ld_cached(const T* p) {
+  Vec<T> r;
+  *reinterpret_cast<uint4*>(&r) = __ldg(reinterpret_cast<const uint4*>(p));
+  return r;
+}
+// Plain (coherent) 16-byte load — used when out may alias the input (in-place ops).
+template <typename T>
+__device__ __forceinline__ Vec<T> ld_plain(const T* p) {
+  Vec<T> r;
+  *reinterpret_cast<uint4*>(&r) = *reinterpret_cast<const uint4*>(p);
+  return r;
+}
+// Streaming 16-byte store (evict-first in L1; written once, never re-read by this kernel).
+template <typename T>
+__device__ __forceinline__ void st_stream(T* p, const Vec<T>& r) {
+  const uint4 u = *reinterpret_cast<const uint4*>(&r);
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(u.x), "r"(u.y),
+               "r"(u.z), "r"(u.w)
+               : "memory");
+}
+
+// ----------------------------------------------------------------------------
+// warp / block reduction helpers
+// ----------------------------------------------------------------------------
+template <typename A>
+__device__ __forceinline__ A shfl_xor_any(A v, int mask) {
+  static_assert(sizeof(A) % 4 == 0, "shuffle payload must be a multiple of 4 bytes");
+  constexpr int W = sizeof(A) / 4;
+  union { A a; uint32_t w[W]; } in, out;
+  in.a = v;
+#pragma unroll
+  for (int i = 0; i < W; ++i) out.w[i] = __shfl_xor_sync(0xffffffffu, in.w[i], mask);
+  return out.a;
+}
+
+// Reduce across the G (power of two, <= 32) consecutive lanes that share a row.
+template <int G, typename A, typename Combine>
+__device__ __forceinline__ A group_reduce(A v, Combine comb) {
+#pragma unroll
+  for (int m = G / 2; m >= 1; m >>= 1) v = comb(v, shfl_xor_any(v, m));
+  return v;
+}
+
+// Whole-CTA reduction; result valid in every thread.  `smem` must hold >= 33 A's.
+template <typename A, typename Combine>
+__device__ __forceinline__ A block_reduce(A v, Combine comb, A identity, A* smem) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nwarps = (blockDim.x + 31) >> 5;
+  v = group_reduce<32>(v, comb);
+  if (lane == 0) smem[warp] = v;
+  __syncthreads();
+  if (warp == 0) {
+    A w = lane < nwarps ? smem[lane] : identity;
+    w = group_reduce<32>(w, comb);
+    if (lane == 0) smem[32] = w;
+  }
+  __syncthreads();
+  A r = smem[32];
+  __syncthreads();  // smem may be reused by the caller right away
+  return r;
+}
+
+// ----------------------------------------------------------------------------
+// dtype -> C++ type
+// ----------------------------------------------------------------------------
+template <int DT> struct CType;
+template <> struct CType<PDB200_BOOL> { using type = bool; };
+template <> struct CType<PDB200_UINT8> { using type = uint8_t; };
+template <> struct CType<PDB200_INT8> { using type = int8_t; };
+template <> struct CType<PDB200_INT16> { using type = int16_t; };
+template <> struct CType<PDB200_INT32> { using type = int32_t; };
+template <> struct CType<PDB200_INT64> { using type = int64_t; };
+template <> struct CType<PDB200_FLOAT16> { using type = __half; };
+template <> struct CType<PDB200_BFLOAT16> { using type = __nv_bfloat16; };
+template <> struct CType<PDB200_FLOAT32> { using type = float; };
+template <> struct CType<PDB200_FLOAT64> { using type = double; };
+
+}  // namespace pdb200

@@ -1,0 +1,357 @@
+// layer_norm.cu — layer_norm forward, hand-written for sm_100a.
+//
+// Replaces (fresh design): phi::LayerNormKernel<T, GPUContext> and its three forward kernels
+//   fast_ln_fwd_kernel, LayerNormFwdWithWelford, LayerNormForward<T,U,512>
+//   paddle/phi/kernels/gpu/layer_norm_kernel.cu:297-665,
+//   paddle/phi/kernels/funcs/layer_norm_impl.cu.h:178-508.
+// The reference's route for D = 8192 (config 3) is the generic kernel: one 512-thread CTA per
+// row, scalar 2-byte loads, x read twice, variance as E[x^2]-E[x]^2.  Here every route reads
+// x ONCE from HBM: the row lives in registers between the statistics and the normalisation.
+//
+// Numerics follow the CPU kernel the parity oracle is built from
+//   paddle/phi/kernels/cpu/layer_norm_kernel.cc:68-102 (two-pass: mean, then mean of
+//   (x-mean)^2, biased), computed in U = float (double for fp64 input);
+//   y = ((x-mean) * (1/sqrt(var+eps))) * scale + bias, product and sum rounded separately.
+//
+// Routes (x viewed as [rows][D]):
+//   rows_reg   : G lanes (<= 32) per row, C <= 8 16-byte chunks per lane     (D <= 256*V)
+//   block_reg  : one CTA (128..1024 threads) per row, C <= 4 chunks a thread (D <= 4096*V)
+//   block_strm : longer rows — three streaming sweeps
+#include "common.cuh"
+#include "shape.h"
+
+namespace pdb200 {
+
+template <typename U> __device__ __forceinline__ U rsqrt_exact(U v);
+template <> __device__ __forceinline__ float rsqrt_exact<float>(float v) { return 1.0f / sqrtf(v); }
+template <> __device__ __forceinline__ double rsqrt_exact<double>(double v) { return 1.0 / sqrt(v); }
+
+// sum * (1.0 / n) with the double-precision reciprocal the CPU RowwiseMean uses
+// (funcs/math_function_impl.h:180-189)
+template <typename U>
+__device__ __forceinline__ U mean_of(U sum, double inv_n) { return (U)((double)sum * inv_n); }
+
+template <typename U> struct AddU { __device__ __forceinline__ U operator()(U a, U b) const { return a + b; } };
+
+template <typename U> __device__ __forceinline__ U mul_rn(U a, U b);
+template <> __device__ __forceinline__ float mul_rn<float>(float a, float b) { return __fmul_rn(a, b); }
+template <> __device__ __forceinline__ double mul_rn<double>(double a, double b) { return __dmul_rn(a, b); }
+template <typename U> __device__ __forceinline__ U add_rn(U a, U b);
+template <> __device__ __forceinline__ float add_rn<float>(float a, float b) { return __fadd_rn(a, b); }
+template <> __device__ __forceinline__ double add_rn<double>(double a, double b) { return __dadd_rn(a, b); }
+
+// Normalise one chunk held in registers and store it.
+template <typename T, typename P, typename U, int V, bool VECTOR>
+__device__ __forceinline__ void ln_store_chunk(const U* e, U mean, U rstd, const P* __restrict__ scale,
+                                               const P* __restrict__ bias, T* dst, int64_t off) {
+  U o[V];
+#pragma unroll
+  for (int k = 0; k < V; ++k) o[k] = mul_rn<U>(e[k] - mean, rstd);
+  if (scale != nullptr) {
+    if constexpr (VECTOR && sizeof(P) == sizeof(T)) {
+      Vec<P> s = ld_cached(scale + off);
+#pragma unroll
+      for (int k = 0; k < V; ++k) o[k] = mul_rn<U>(o[k], cvt<U>(s.v[k]));
+    } else {
+#pragma unroll
+      for (int k = 0; k < V; ++k) o[k] = mul_rn<U>(o[k], cvt<U>(scale[off + k]));
+    }
+  }
+  if (bias != nullptr) {
+    if constexpr (VECTOR && sizeof(P) == sizeof(T)) {
+      Vec<P> b = ld_cached(bias + off);
+#pragma unroll
+      for (int k = 0; k < V; ++k) o[k] = add_rn<U>(o[k], cvt<U>(b.v[k]));
+    } else {
+#pragma unroll
+      for (int k = 0; k < V; ++k) o[k] = add_rn<U>(o[k], cvt<U>(bias[off + k]));
+    }
+  }
+  if constexpr (VECTOR) {
+    Vec<T> ov;
+#pragma unroll
+    for (int k = 0; k < V; ++k) ov.v[k] = cvt<T>(o[k]);
+    st_stream(dst + off, ov);
+  } else {
+    dst[off] = cvt<T>(o[0]);
+  }
+}
+
+// ---- rows_reg: G lanes per row ------------------------------------------------------------
+template <typename T, typename P, int C, bool VECTOR>
+__global__ void __launch_bounds__(256) ln_rows_reg_kernel(const T* __restrict__ x,
+                                                          const P* __restrict__ scale,
+                                                          const P* __restrict__ bias,
+                                                          T* __restrict__ y, typename AccType<T>::type* mean_out,
+                                                          typename AccType<T>::type* var_out, int64_t rows,
+                                                          int D, int G, typename AccType<T>::type eps,
+                                                          double inv_d) {
+  using U = typename AccType<T>::type;
+  constexpr int V = VECTOR ? Vec<T>::N : 1;
+  const int rows_per_cta = blockDim.x / G;
+  const int g = threadIdx.x / G, lane = threadIdx.x - g * G;
+  const int64_t row = (int64_t)blockIdx.x * rows_per_cta + g;
+  const bool valid = row < rows;
+  const T* src = x + row * D;
+  U e[C * V];
+  U sum = U(0);
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    const int off = (c * G + lane) * V;
+    if (valid && off < D) {
+      if constexpr (VECTOR) {
+        Vec<T> v = ld_stream(src + off);
+#pragma unroll
+        for (int k = 0; k < V; ++k) e[c * V + k] = cvt<U>(v.v[k]);
+      } else {
+        e[c] = cvt<U>(src[off]);
+      }
+#pragma unroll
+      for (int k = 0; k < V; ++k) sum += e[c * V + k];
+    } else {
+#pragma unroll
+      for (int k = 0; k < V; ++k) e[c * V + k] = U(0);
+    }
+  }
+  for (int s = G >> 1; s >= 1; s >>= 1) sum += shfl_xor_any(sum, s);
+  const U mean = mean_of<U>(sum, inv_d);
+  U sq = U(0);
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    const int off = (c * G + lane) * V;
+    if (off < D) {
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        const U d = e[c * V + k] - mean;
+        sq += d * d;
+      }
+    }
+  }
+  for (int s = G >> 1; s >= 1; s >>= 1) sq += shfl_xor_any(sq, s);
+  const U var = mean_of<U>(sq, inv_d);
+  const U rstd = rsqrt_exact<U>(var + eps);
+  if (valid && lane == 0) {
+    if (mean_out) mean_out[row] = mean;
+    if (var_out) var_out[row] = var;
+  }
+  if (!valid) return;
+  T* dst = y + row * D;
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    const int off = (c * G + lane) * V;
+    if (off < D) ln_store_chunk<T, P, U, V, VECTOR>(&e[c * V], mean, rstd, scale, bias, dst, off);
+  }
+}
+
+// ---- block_reg: one CTA per row -----------------------------------------------------------
+template <typename T, typename P, int C, bool VECTOR>
+__global__ void __launch_bounds__(1024) ln_block_reg_kernel(const T* __restrict__ x,
+                                                            const P* __restrict__ scale,
+                                                            const P* __restrict__ bias,
+                                                            T* __restrict__ y, typename AccType<T>::type* mean_out,
+                                                            typename AccType<T>::type* var_out, int D,
+                                                            typename AccType<T>::type eps, double inv_d) {
+  using U = typename AccType<T>::type;
+  constexpr int V = VECTOR ? Vec<T>::N : 1;
+  __shared__ U red[33];
+  const int64_t row = blockIdx.x;
+  const T* src = x + row * D;
+  const int nt = blockDim.x;
+  U e[C * V];
+  U sum = U(0);
+  // all loads first (C independent 16-byte requests per thread), then the arithmetic
+  if constexpr (VECTOR) {
+    Vec<T> raw[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + threadIdx.x) * V;
+      if (off < D) raw[c] = ld_stream(src + off);
+    }
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + threadIdx.x) * V;
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        e[c * V + k] = off < D ? cvt<U>(raw[c].v[k]) : U(0);
+        sum += e[c * V + k];
+      }
+    }
+  } else {
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = c * nt + threadIdx.x;
+      e[c] = off < D ? cvt<U>(src[off]) : U(0);
+      sum += e[c];
+    }
+  }
+  sum = block_reduce(sum, AddU<U>(), U(0), red);
+  const U mean = mean_of<U>(sum, inv_d);
+  U sq = U(0);
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    const int off = (c * nt + threadIdx.x) * V;
+    if (off < D) {
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        const U d = e[c * V + k] - mean;
+        sq += d * d;
+      }
+    }
+  }
+  sq = block_reduce(sq, AddU<U>(), U(0), red);
+  const U var = mean_of<U>(sq, inv_d);
+  const U rstd = rsqrt_exact<U>(var + eps);
+  if (threadIdx.x == 0) {
+    if (mean_out) mean_out[row] = mean;
+    if (var_out) var_out[row] = var;
+  }
+  T* dst = y + row * D;
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    const int off = (c * nt + threadIdx.x) * V;
+    if (off < D) ln_store_chunk<T, P, U, V, VECTOR>(&e[c * V], mean, rstd, scale, bias, dst, off);
+  }
+}
+
+// ---- block_strm: rows too long for registers ------------------------------------------------
+template <typename T, typename P>
+__global__ void __launch_bounds__(1024) ln_block_stream_kernel(const T* x, const P* __restrict__ scale,
+                                                               const P* __restrict__ bias, T* y,
+                                                               typename AccType<T>::type* mean_out,
+                                                               typename AccType<T>::type* var_out, int64_t D,
+                                                               typename AccType<T>::type eps, double inv_d) {
+  using U = typename AccType<T>::type;
+  __shared__ U red[33];
+  const int64_t row = blockIdx.x;
+  const T* src = x + row * D;
+  T* dst = y + row * D;
+  U sum = U(0);
+  for (int64_t i = threadIdx.x; i < D; i += blockDim.x) sum += cvt<U>(src[i]);
+  sum = block_reduce(sum, AddU<U>(), U(0), red);
+  const U mean = mean_of<U>(sum, inv_d);
+  U sq = U(0);
+  for (int64_t i = threadIdx.x; i < D; i += blockDim.x) {
+    const U d = cvt<U>(src[i]) - mean;
+    sq += d * d;
+  }
+  sq = block_reduce(sq, AddU<U>(), U(0), red);
+  const U var = mean_of<U>(sq, inv_d);
+  const U rstd = rsqrt_exact<U>(var + eps);
+  if (threadIdx.x == 0) {
+    if (mean_out) mean_out[row] = mean;
+    if (var_out) var_out[row] = var;
+  }
+  for (int64_t i = threadIdx.x; i < D; i += blockDim.x) {
+    U o = mul_rn<U>(cvt<U>(src[i]) - mean, rstd);
+    if (scale) o = mul_rn<U>(o, cvt<U>(scale[i]));
+    if (bias) o = add_rn<U>(o, cvt<U>(bias[i]));
+    dst[i] = cvt<T>(o);
+  }
+}
+
+// ---- host -------------------------------------------------------------------------------
+template <typename T, typename P>
+int layer_norm_typed(const T* x, const P* scale, const P* bias, T* y, void* mean, void* var,
+                     int64_t rows, int64_t D, float epsilon, cudaStream_t st) {
+  using U = typename AccType<T>::type;
+  constexpr int VN = Vec<T>::N;
+  U* m = static_cast<U*>(mean);
+  U* v = static_cast<U*>(var);
+  const U eps = static_cast<U>(epsilon);  // static_cast<T>(epsilon) on CPU (cpu/layer_norm_kernel.cc:88)
+  const double inv_d = 1.0 / (double)D;
+  bool vec = (D % VN == 0) && is_aligned16(x) && is_aligned16(y);
+  if (vec && sizeof(P) == sizeof(T)) vec = (!scale || is_aligned16(scale)) && (!bias || is_aligned16(bias));
+  const int V = vec ? VN : 1;
+  const int64_t nchunk = D / V;
+  if (rows > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "layer_norm: too many rows for one launch");
+#define PDB_LN_C(KERNEL, CC, ...)                                        \
+  case CC:                                                               \
+    if (vec) KERNEL<T, P, CC, true> __VA_ARGS__;                         \
+    else KERNEL<T, P, CC, false> __VA_ARGS__;                            \
+    break;
+  if (nchunk <= 32 * 8) {
+    int G = 1;
+    while (G < 32 && G < nchunk) G <<= 1;
+    int C = 1;
+    while ((int64_t)C * G < nchunk) C <<= 1;
+    const int rows_per_cta = 256 / G;
+    const int64_t blocks = (rows + rows_per_cta - 1) / rows_per_cta;
+    switch (C) {
+      PDB_LN_C(ln_rows_reg_kernel, 1, <<<(unsigned)blocks, 256, 0, st>>>(x, scale, bias, y, m, v, rows, (int)D, G, eps, inv_d))
+      PDB_LN_C(ln_rows_reg_kernel, 2, <<<(unsigned)blocks, 256, 0, st>>>(x, scale, bias, y, m, v, rows, (int)D, G, eps, inv_d))
+      PDB_LN_C(ln_rows_reg_kernel, 4, <<<(unsigned)blocks, 256, 0, st>>>(x, scale, bias, y, m, v, rows, (int)D, G, eps, inv_d))
+      PDB_LN_C(ln_rows_reg_kernel, 8, <<<(unsigned)blocks, 256, 0, st>>>(x, scale, bias, y, m, v, rows, (int)D, G, eps, inv_d))
+    }
+    return after_launch("ln_rows_reg");
+  }
+  if (nchunk <= 1024 * 4) {
+    // up to 4 chunks per thread (more would push a 1024-thread CTA past 64 registers a thread);
+    // widen the CTA first, deepen the chunks last
+    int threads = 128;
+    while (threads < 1024 && (int64_t)threads * 4 < nchunk) threads <<= 1;
+    int C = 1;
+    while ((int64_t)C * threads < nchunk) C <<= 1;
+    switch (C) {
+      PDB_LN_C(ln_block_reg_kernel, 1, <<<(unsigned)rows, threads, 0, st>>>(x, scale, bias, y, m, v, (int)D, eps, inv_d))
+      PDB_LN_C(ln_block_reg_kernel, 2, <<<(unsigned)rows, threads, 0, st>>>(x, scale, bias, y, m, v, (int)D, eps, inv_d))
+      PDB_LN_C(ln_block_reg_kernel, 4, <<<(unsigned)rows, threads, 0, st>>>(x, scale, bias, y, m, v, (int)D, eps, inv_d))
+    }
+    return after_launch("ln_block_reg");
+  }
+#undef PDB_LN_C
+  ln_block_stream_kernel<T, P><<<(unsigned)rows, 1024, 0, st>>>(x, scale, bias, y, m, v, D, eps, inv_d);
+  return after_launch("ln_block_stream");
+}
+
+}  // namespace pdb200
+
+extern "C" int pdb200_layer_norm(const void* x, const int64_t* dims, int rank, const void* scale,
+                                 const void* bias, int param_dtype, float epsilon, int begin_norm_axis,
+                                 int dtype, void* y, void* mean, void* variance, void* stream) {
+  using namespace pdb200;
+  PDB_CHECK_ARG(rank >= 1 && rank <= PDB200_MAX_RANK && dims != nullptr, "layer_norm: rank must be in [1, 9]");
+  // LayerNormInferMeta (infermeta/ternary.cc:1082): 0 < begin_norm_axis < rank (0 is tolerated by the kernels)
+  PDB_CHECK_ARG(begin_norm_axis >= 0 && begin_norm_axis <= rank,
+                "'begin_norm_axis' must be less than the dimensions of X, but received 'begin_norm_axis' is " +
+                    std::to_string(begin_norm_axis));
+  int64_t rows = 1, D = 1;
+  for (int i = 0; i < rank; ++i) {
+    PDB_CHECK_ARG(dims[i] >= 0, "layer_norm: negative dimension");
+    (i < begin_norm_axis ? rows : D) *= dims[i];
+  }
+  if (rows * D == 0) return PDB200_OK;
+  PDB_CHECK_ARG(x && y, "layer_norm: NULL tensor pointer");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const bool has_param = scale != nullptr || bias != nullptr;
+  // gpu/layer_norm_kernel.cu:516-538: scale/bias dtype == x dtype, or == float (U)
+  const bool same = !has_param || param_dtype == dtype;
+  if (has_param && !same && param_dtype != PDB200_FLOAT32)
+    return fail(PDB200_INVALID_ARGUMENT,
+                "Unsupported data type of Scale and Bias: the dtype must be the same as X's or float32");
+#define PDB_LN_CASE(DT)                                                                               \
+  case DT: {                                                                                          \
+    using T = typename CType<DT>::type;                                                               \
+    if (same)                                                                                         \
+      return layer_norm_typed<T, T>(static_cast<const T*>(x), static_cast<const T*>(scale),           \
+                                    static_cast<const T*>(bias), static_cast<T*>(y), mean, variance,  \
+                                    rows, D, epsilon, st);                                            \
+    return layer_norm_typed<T, float>(static_cast<const T*>(x), static_cast<const float*>(scale),     \
+                                      static_cast<const float*>(bias), static_cast<T*>(y), mean,      \
+                                      variance, rows, D, epsilon, st);                                \
+  }
+  switch (dtype) {
+    PDB_LN_CASE(PDB200_FLOAT32)
+    PDB_LN_CASE(PDB200_BFLOAT16)
+    PDB_LN_CASE(PDB200_FLOAT16)
+    case PDB200_FLOAT64: {
+      if (!same) return fail(PDB200_INVALID_ARGUMENT, "layer_norm: float64 input needs float64 scale/bias");
+      return layer_norm_typed<double, double>(static_cast<const double*>(x), static_cast<const double*>(scale),
+                                              static_cast<const double*>(bias), static_cast<double*>(y), mean,
+                                              variance, rows, D, epsilon, st);
+    }
+    default:
+      return fail(PDB200_UNSUPPORTED, "layer_norm: dtype must be float32/float64/float16/bfloat16, got code " +
+                                          std::to_string(dtype));
+  }
+#undef PDB_LN_CASE
+}

@@ -1,0 +1,310 @@
+// softmax.cu — softmax forward along one axis, hand-written for sm_100a.
+//
+// Replaces (fresh design): SoftmaxForwardCUDAKernelDriver and its four routes
+//   WarpSoftmaxForward (dim <= 512), cudnnSoftmaxForward (512 < dim < 100000),
+//   KeMatrixSoftmaxForward (dim >= 100000), NormalSoftmaxForward (axis != last)
+//   paddle/phi/kernels/gpudnn/softmax_gpudnn.h:442-611,870-912,1025-1069,1239-1329.
+// Numerics follow the CPU kernel the parity oracle is built from
+//   paddle/phi/kernels/funcs/softmax_impl.h:36-42,234-273:
+//   e = exp(max(x - rowmax, -64)); y = e * (1 / sum(e)); fp16/bf16 compute in float and
+//   round once at the end (softmax_gpudnn.h:257-269).
+//
+// Routes (x viewed as [outer][dim][inner]):
+//   inner == 1, row fits registers  -> rows_reg   : G lanes per row hold the whole row
+//        (C x 16-byte chunks per lane): ONE read + ONE write of HBM, max/sum by shuffles.
+//        Covers dim <= 32*16*V (2048 fp32, 4096 bf16) — the reference needs cuDNN there.
+//   inner == 1, row fits shared mem -> rows_smem  : one CTA per row, row staged once in
+//        shared memory as float (<= 50 K elements): still one read + one write.
+//   inner == 1, longer rows         -> rows_stream: three streaming sweeps (as the reference
+//        does from 100000 up).
+//   inner  > 1                      -> cols       : threads along `inner` (coalesced),
+//        sweeps over `dim`; later sweeps hit L2.
+#include "common.cuh"
+#include "shape.h"
+
+namespace pdb200 {
+
+template <typename A> __device__ __forceinline__ A exp_acc(A v);
+template <> __device__ __forceinline__ float exp_acc<float>(float v) { return expf(v); }
+template <> __device__ __forceinline__ double exp_acc<double>(double v) { return exp(v); }
+
+template <typename A>
+__device__ __forceinline__ A clipped_exp(A x, A m) {
+  A d = x - m;
+  d = d < A(-64) ? A(-64) : d;  // ValueClip, softmax_impl.h:36-42
+  return exp_acc<A>(d);
+}
+
+template <typename A> struct MaxF { __device__ __forceinline__ A operator()(A a, A b) const { return b > a ? b : a; } };
+template <typename A> struct AddF { __device__ __forceinline__ A operator()(A a, A b) const { return a + b; } };
+
+template <typename A>
+__device__ __forceinline__ A neg_inf() { return -std::numeric_limits<A>::infinity(); }
+
+// ---- rows_reg --------------------------------------------------------------------------
+// G lanes (power of two <= 32) per row, C chunks of V elements per lane; chunk c of lane l
+// covers elements (c*G + l)*V .. +V.  Out-of-row chunks hold -inf and are never stored.
+template <typename T, int C, bool VECTOR>
+__global__ void __launch_bounds__(256) softmax_rows_reg_kernel(const T* __restrict__ x,
+                                                               T* __restrict__ y, int64_t outer,
+                                                               int dim, int G) {
+  using A = typename AccType<T>::type;
+  constexpr int V = VECTOR ? Vec<T>::N : 1;
+  const int rows_per_cta = blockDim.x / G;
+  const int g = threadIdx.x / G, lane = threadIdx.x - g * G;
+  const int64_t row = (int64_t)blockIdx.x * rows_per_cta + g;
+  const bool valid = row < outer;  // shuffles below are full-mask: no early exit
+  const T* src = x + row * dim;
+  T* dst = y + row * dim;
+  A e[C * V];
+  A m = neg_inf<A>();
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    const int off = (c * G + lane) * V;
+    if (valid && off < dim) {
+      if constexpr (VECTOR) {
+        Vec<T> v = ld_stream(src + off);  // y may alias x (softmax_): each chunk is read and written by the same thread
+#pragma unroll
+        for (int k = 0; k < V; ++k) e[c * V + k] = cvt<A>(v.v[k]);
+      } else {
+        e[c] = cvt<A>(src[off]);
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < V; ++k) e[c * V + k] = neg_inf<A>();
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < C * V; ++i) m = e[i] > m ? e[i] : m;
+  for (int s = G >> 1; s >= 1; s >>= 1) {
+    A o = shfl_xor_any(m, s);
+    m = o > m ? o : m;
+  }
+  A sum = A(0);
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    const int off = (c * G + lane) * V;
+    if (off < dim) {
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        e[c * V + k] = clipped_exp<A>(e[c * V + k], m);
+        sum += e[c * V + k];
+      }
+    }
+  }
+  for (int s = G >> 1; s >= 1; s >>= 1) sum += shfl_xor_any(sum, s);
+  const A inv = A(1) / sum;
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    const int off = (c * G + lane) * V;
+    if (valid && off < dim) {
+      if constexpr (VECTOR) {
+        Vec<T> o;
+#pragma unroll
+        for (int k = 0; k < V; ++k) o.v[k] = cvt<T>(e[c * V + k] * inv);
+        st_stream(dst + off, o);
+      } else {
+        dst[off] = cvt<T>(e[c] * inv);
+      }
+    }
+  }
+}
+
+// ---- rows_smem -------------------------------------------------------------------------
+template <typename T, bool VECTOR>
+__global__ void __launch_bounds__(1024) softmax_rows_smem_kernel(const T* __restrict__ x,
+                                                                 T* __restrict__ y, int64_t dim) {
+  using A = typename AccType<T>::type;
+  constexpr int V = VECTOR ? Vec<T>::N : 1;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  A* row = reinterpret_cast<A*>(smem_raw);  // [dim]
+  __shared__ A red[33];
+  const T* src = x + (int64_t)blockIdx.x * dim;
+  T* dst = y + (int64_t)blockIdx.x * dim;
+  A m = neg_inf<A>();
+  for (int64_t i = (int64_t)threadIdx.x * V; i < dim; i += (int64_t)blockDim.x * V) {
+    if constexpr (VECTOR) {
+      Vec<T> v = ld_stream(src + i);
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        A a = cvt<A>(v.v[k]);
+        row[i + k] = a;
+        m = a > m ? a : m;
+      }
+    } else {
+      A a = cvt<A>(src[i]);
+      row[i] = a;
+      m = a > m ? a : m;
+    }
+  }
+  m = block_reduce(m, MaxF<A>(), neg_inf<A>(), red);  // also orders the smem writes
+  A sum = A(0);
+  for (int64_t i = threadIdx.x; i < dim; i += blockDim.x) {  // each thread revisits what any thread wrote: synced above
+    A ev = clipped_exp<A>(row[i], m);
+    row[i] = ev;
+    sum += ev;
+  }
+  sum = block_reduce(sum, AddF<A>(), A(0), red);
+  const A inv = A(1) / sum;
+  for (int64_t i = (int64_t)threadIdx.x * V; i < dim; i += (int64_t)blockDim.x * V) {
+    if constexpr (VECTOR) {
+      Vec<T> o;
+#pragma unroll
+      for (int k = 0; k < V; ++k) o.v[k] = cvt<T>(row[i + k] * inv);
+      st_stream(dst + i, o);
+    } else {
+      dst[i] = cvt<T>(row[i] * inv);
+    }
+  }
+}
+
+// ---- rows_stream -----------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(1024) softmax_rows_stream_kernel(const T* x, T* y, int64_t dim) {
+  using A = typename AccType<T>::type;
+  __shared__ A red[33];
+  const T* src = x + (int64_t)blockIdx.x * dim;
+  T* dst = y + (int64_t)blockIdx.x * dim;
+  A m = neg_inf<A>();
+  for (int64_t i = threadIdx.x; i < dim; i += blockDim.x) {
+    A a = cvt<A>(src[i]);
+    m = a > m ? a : m;
+  }
+  m = block_reduce(m, MaxF<A>(), neg_inf<A>(), red);
+  A sum = A(0);
+  for (int64_t i = threadIdx.x; i < dim; i += blockDim.x) sum += clipped_exp<A>(cvt<A>(src[i]), m);
+  sum = block_reduce(sum, AddF<A>(), A(0), red);
+  const A inv = A(1) / sum;
+  // in-place safe: each element is read and written by the same thread in this sweep
+  for (int64_t i = threadIdx.x; i < dim; i += blockDim.x) dst[i] = cvt<T>(clipped_exp<A>(cvt<A>(src[i]), m) * inv);
+}
+
+// ---- cols: softmax along the middle axis of [outer][dim][inner] ---------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) softmax_cols_kernel(const T* x, T* y, int64_t dim,
+                                                           int64_t inner, int64_t col_tiles) {
+  using A = typename AccType<T>::type;
+  const int64_t o = (int64_t)blockIdx.x / col_tiles;
+  const int64_t ct = (int64_t)blockIdx.x - o * col_tiles;
+  const int64_t col = ct * blockDim.x + threadIdx.x;
+  if (col >= inner) return;
+  const T* src = x + o * dim * inner + col;
+  T* dst = y + o * dim * inner + col;
+  A m = neg_inf<A>();
+  for (int64_t r = 0; r < dim; ++r) {
+    A a = cvt<A>(src[r * inner]);
+    m = a > m ? a : m;
+  }
+  A sum = A(0);
+  for (int64_t r = 0; r < dim; ++r) sum += clipped_exp<A>(cvt<A>(src[r * inner]), m);
+  const A inv = A(1) / sum;
+  for (int64_t r = 0; r < dim; ++r) dst[r * inner] = cvt<T>(clipped_exp<A>(cvt<A>(src[r * inner]), m) * inv);
+}
+
+template <typename T>
+__global__ void softmax_fill_one_kernel(T* y) { y[0] = cvt<T>(typename AccType<T>::type(1)); }
+
+// ---- host -------------------------------------------------------------------------------
+template <typename T, bool VECTOR>
+int launch_rows_reg(const T* x, T* y, int64_t outer, int dim, int G, int C, cudaStream_t st) {
+  const int rows_per_cta = 256 / G;
+  const int64_t blocks = (outer + rows_per_cta - 1) / rows_per_cta;
+  if (blocks > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "softmax: too many rows for one launch");
+#define PDB_SM_C(CC)                                                                                \
+  case CC:                                                                                          \
+    softmax_rows_reg_kernel<T, CC, VECTOR><<<(unsigned)blocks, 256, 0, st>>>(x, y, outer, dim, G); \
+    break;
+  switch (C) {
+    PDB_SM_C(1) PDB_SM_C(2) PDB_SM_C(4) PDB_SM_C(8) PDB_SM_C(16)
+    default: return fail(PDB200_UNSUPPORTED, "softmax: bad chunk count");
+  }
+#undef PDB_SM_C
+  return after_launch("softmax_rows_reg");
+}
+
+template <typename T>
+int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, cudaStream_t st) {
+  using A = typename AccType<T>::type;
+  constexpr int VN = Vec<T>::N;
+  if (inner == 1) {
+    const bool vec = (dim % VN == 0) && is_aligned16(x) && is_aligned16(y);
+    const int V = vec ? VN : 1;
+    const int64_t nchunk = dim / V;
+    if (nchunk <= 32 * 16) {
+      int G = 1;
+      while (G < 32 && G < nchunk) G <<= 1;
+      int C = 1;
+      while ((int64_t)C * G < nchunk) C <<= 1;
+      return vec ? launch_rows_reg<T, true>(x, y, outer, (int)dim, G, C, st)
+                 : launch_rows_reg<T, false>(x, y, outer, (int)dim, G, C, st);
+    }
+    if (outer > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "softmax: too many rows for one launch");
+    const size_t smem = (size_t)dim * sizeof(A);
+    if (smem <= 200 * 1024) {
+      int threads = 256;
+      while (threads < 1024 && (int64_t)threads * V * 8 < dim) threads <<= 1;
+      if (vec) {
+        cudaFuncSetAttribute(softmax_rows_smem_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        softmax_rows_smem_kernel<T, true><<<(unsigned)outer, threads, smem, st>>>(x, y, dim);
+      } else {
+        cudaFuncSetAttribute(softmax_rows_smem_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        softmax_rows_smem_kernel<T, false><<<(unsigned)outer, threads, smem, st>>>(x, y, dim);
+      }
+      return after_launch("softmax_rows_smem");
+    }
+    softmax_rows_stream_kernel<T><<<(unsigned)outer, 1024, 0, st>>>(x, y, dim);
+    return after_launch("softmax_rows_stream");
+  }
+  int threads = 32;
+  while (threads < 256 && threads < inner) threads <<= 1;
+  const int64_t col_tiles = (inner + threads - 1) / threads;
+  const int64_t blocks = col_tiles * outer;
+  if (blocks > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "softmax: too many tiles for one launch");
+  softmax_cols_kernel<T><<<(unsigned)blocks, threads, 0, st>>>(x, y, dim, inner, col_tiles);
+  return after_launch("softmax_cols");
+}
+
+}  // namespace pdb200
+
+extern "C" int pdb200_softmax(const void* x, const int64_t* dims, int rank, int axis, int dtype,
+                              void* out, void* stream) {
+  using namespace pdb200;
+  PDB_CHECK_ARG(rank >= 0 && rank <= PDB200_MAX_RANK, "softmax: rank must be in [0, 9]");
+  PDB_CHECK_ARG(rank == 0 || dims != nullptr, "softmax: dims is NULL");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  // CanonicalAxis (funcs/axis_utils.h): axis in [-rank, rank)
+  if (rank > 0) {
+    PDB_CHECK_ARG(axis >= -rank && axis < rank,
+                  "The axis is expected to be in range of [" + std::to_string(-rank) + ", " +
+                      std::to_string(rank) + "), but got " + std::to_string(axis));
+    if (axis < 0) axis += rank;
+  }
+  int64_t outer = 1, dim = 1, inner = 1;
+  for (int i = 0; i < rank; ++i) {
+    PDB_CHECK_ARG(dims[i] >= 0, "softmax: negative dimension");
+    if (i < axis) outer *= dims[i];
+    else if (i == axis) dim = dims[i];
+    else inner *= dims[i];
+  }
+  if (rank > 0 && outer * dim * inner == 0) return PDB200_OK;  // 0-size tensor: no-op
+  PDB_CHECK_ARG(x && out, "softmax: NULL tensor pointer");
+#define PDB_SM_CASE(DT)                                                                       \
+  case DT: {                                                                                  \
+    using T = typename CType<DT>::type;                                                       \
+    if (rank == 0) { /* 0-D tensor: 1.0 (impl/softmax_kernel_impl.h:41-44) */                 \
+      softmax_fill_one_kernel<T><<<1, 1, 0, st>>>(static_cast<T*>(out));                      \
+      return after_launch("softmax_fill_one");                                                \
+    }                                                                                         \
+    return softmax_typed<T>(static_cast<const T*>(x), static_cast<T*>(out), outer, dim, inner, st); \
+  }
+  switch (dtype) {
+    PDB_SM_CASE(PDB200_FLOAT32)
+    PDB_SM_CASE(PDB200_FLOAT64)
+    PDB_SM_CASE(PDB200_FLOAT16)
+    PDB_SM_CASE(PDB200_BFLOAT16)
+    default:
+      return fail(PDB200_UNSUPPORTED, "softmax: dtype must be float32/float64/float16/bfloat16, got code " +
+                                          std::to_string(dtype));
+  }
+#undef PDB_SM_CASE
+}

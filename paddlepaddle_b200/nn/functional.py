@@ -1,0 +1,88 @@
+"""paddle.nn.functional.softmax / layer_norm on the B200 kernels.
+
+Mirrors python/paddle/nn/functional/activation.py:1111 (softmax) and
+python/paddle/nn/functional/norm.py:320 (layer_norm); the C++ in between (SoftmaxInferMeta,
+LayerNormInferMeta, Alloc) is done here, then the call goes through the C-ABI.
+"""
+import ctypes
+import numbers
+
+import torch
+
+from .. import _lib as L
+from ..ops import _as_torch_dtype, _dtype_code, _ptr, _require_cuda, _stream
+
+
+def softmax(x, axis=-1, dtype=None, name=None):
+    """softmax along `axis`.  `dtype` casts the input first (activation.py:1245-1247); the cast itself
+    is not on the hot path and only the no-cast call is supported here."""
+    _require_cuda(x)
+    dt = _as_torch_dtype(dtype)
+    if dt is not None and dt != x.dtype:
+        raise NotImplementedError("softmax(dtype=...) needs phi::CastKernel, which is outside the hot path")
+    lib = L.load()
+    x = x.contiguous()
+    out = torch.empty_like(x)
+    d, r = L.dims_array(x.shape)
+    L.check(lib.pdb200_softmax(_ptr(x), d, r, int(axis), _dtype_code(x.dtype), _ptr(out), _stream()), lib)
+    return out
+
+
+def softmax_(x, axis=-1, dtype=None, name=None):
+    _require_cuda(x)
+    lib = L.load()
+    if not x.is_contiguous():
+        raise ValueError("softmax_ needs a contiguous tensor")
+    d, r = L.dims_array(x.shape)
+    L.check(lib.pdb200_softmax(_ptr(x), d, r, int(axis), _dtype_code(x.dtype), _ptr(x), _stream()), lib)
+    return x
+
+
+def layer_norm(x, normalized_shape, weight=None, bias=None, epsilon=1e-05, name=None, return_stats=False):
+    """layer_norm over the trailing `normalized_shape` dims (norm.py:320-396).
+    return_stats=True also returns the intermediate outputs `mean` and `variance`
+    (ops.yaml:2839-2851) that Paddle keeps for the backward pass."""
+    _require_cuda(x, weight, bias)
+    if isinstance(normalized_shape, numbers.Integral):
+        normalized_shape = [normalized_shape]
+    normalized_shape = list(normalized_shape)
+    ishape = list(x.shape)
+    n = len(normalized_shape)
+    if n == 0 or n > len(ishape) or ishape[len(ishape) - n:] != normalized_shape:
+        # norm.py:380-390
+        raise ValueError(
+            "Given normalized_shape is " + str(normalized_shape) + ", expected input with shape [*, " +
+            str(normalized_shape)[1:] + ", but got input shape " + str(ishape))
+    begin_norm_axis = len(ishape) - n
+    lib = L.load()
+    x = x.contiguous()
+    D = 1
+    for d in normalized_shape:
+        D *= d
+    rows = x.numel() // D if D else 0
+    pdt = None
+    for p, nm in ((weight, "Scale"), (bias, "Bias")):
+        if p is None:
+            continue
+        if p.numel() != D:
+            raise ValueError(f"(InvalidArgument) {nm} must have {D} elements, got {p.numel()}")
+        if pdt is None:
+            pdt = p.dtype
+        elif p.dtype != pdt:
+            raise ValueError("(InvalidArgument) Scale and Bias must share one dtype")
+    if pdt is not None and pdt != x.dtype and pdt != torch.float32:
+        raise ValueError("(InvalidArgument) Unsupported data type of Scale and Bias")
+    weight = weight.contiguous() if weight is not None else None
+    bias = bias.contiguous() if bias is not None else None
+    stat_dt = torch.float64 if x.dtype == torch.float64 else torch.float32
+    y = torch.empty_like(x)
+    mean = torch.empty((rows,), dtype=stat_dt, device=x.device)
+    var = torch.empty((rows,), dtype=stat_dt, device=x.device)
+    d, r = L.dims_array(x.shape)
+    pcode = _dtype_code(pdt) if pdt is not None else _dtype_code(x.dtype)
+    L.check(lib.pdb200_layer_norm(_ptr(x), d, r, _ptr(weight), _ptr(bias), pcode, ctypes.c_float(float(epsilon)),
+                                  begin_norm_axis, _dtype_code(x.dtype), _ptr(y), _ptr(mean), _ptr(var),
+                                  _stream()), lib)
+    if return_stats:
+        return y, mean, var
+    return y

@@ -1,0 +1,241 @@
+"""Host-side mirror of Paddle's Python operator API for the hot path.
+
+Same names, argument meaning and error behaviour as the reference front-end:
+  paddle.add / paddle.multiply        python/paddle/tensor/math.py:697, :1203 (multiply)
+  paddle.sum                          python/paddle/tensor/math.py:1494
+  paddle.max / min / prod             python/paddle/tensor/math.py:2906 / 3065 / 4830
+  paddle.mean                         python/paddle/tensor/stat.py:45
+  paddle.argmax                       python/paddle/tensor/search.py:175
+What Paddle does in C++ between `_C_ops.<op>` and the kernel (InferMeta: output shape and
+dtype; `dev_ctx.Alloc`; scratch through phi::Empty) is done here in Python, then the call goes
+through the C-ABI (include/pdb200.h) with raw device pointers.  torch is used ONLY as the
+owner of device memory and of the CUDA stream; no torch operator computes anything here.
+"""
+import ctypes
+
+import torch
+
+from . import _lib as L
+
+_TORCH2PDB = {
+    torch.bool: L.BOOL, torch.uint8: L.UINT8, torch.int8: L.INT8, torch.int16: L.INT16,
+    torch.int32: L.INT32, torch.int64: L.INT64, torch.float16: L.FLOAT16,
+    torch.bfloat16: L.BFLOAT16, torch.float32: L.FLOAT32, torch.float64: L.FLOAT64,
+}
+_STR2TORCH = {
+    "bool": torch.bool, "uint8": torch.uint8, "int8": torch.int8, "int16": torch.int16,
+    "int32": torch.int32, "int64": torch.int64, "float16": torch.float16,
+    "bfloat16": torch.bfloat16, "float32": torch.float32, "float64": torch.float64,
+}
+
+
+def _dtype_code(dt):
+    try:
+        return _TORCH2PDB[dt]
+    except KeyError:
+        raise TypeError(f"unsupported dtype {dt}") from None
+
+
+def _as_torch_dtype(dt):
+    if dt is None or isinstance(dt, torch.dtype):
+        return dt
+    s = str(dt)
+    s = s.split(".")[-1]
+    if s in _STR2TORCH:
+        return _STR2TORCH[s]
+    raise TypeError(f"unsupported dtype {dt!r}")
+
+
+def _require_cuda(*tensors):
+    for t in tensors:
+        if t is None:
+            continue
+        if not isinstance(t, torch.Tensor):
+            raise TypeError(f"expected a Tensor, got {type(t).__name__}")
+        if not t.is_cuda:
+            # The reference would dispatch to its CPU kernel; this build has none, on purpose.
+            raise RuntimeError("paddlepaddle_b200 has no CPU kernels: tensors must live on a CUDA device")
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+_workspaces = {}
+
+
+def _workspace(nbytes, device):
+    """Scratch from the caching allocator (stands in for phi::Empty on dev_ctx)."""
+    if nbytes == 0:
+        return None
+    key = (device.index, torch.cuda.current_stream().cuda_stream)
+    buf = _workspaces.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _workspaces[key] = buf
+    return buf
+
+
+# ---------------------------------------------------------------------------------------
+# elementwise
+# ---------------------------------------------------------------------------------------
+def _elementwise(fn_name, x, y, out=None):
+    _require_cuda(x, y)
+    if x.dtype != y.dtype:
+        raise TypeError(f"(InvalidType) the dtypes of X ({x.dtype}) and Y ({y.dtype}) must match "
+                        "(type promotion is done by the caller in Paddle's eager layer)")
+    lib = L.load()
+    x = x.contiguous()
+    y = y.contiguous()
+    xd, xr = L.dims_array(x.shape)
+    yd, yr = L.dims_array(y.shape)
+    od = (ctypes.c_int64 * L.MAX_RANK)()
+    orank = ctypes.c_int(0)
+    L.check(lib.pdb200_broadcast_shape(xd, xr, yd, yr, od, ctypes.byref(orank)), lib)
+    oshape = tuple(od[i] for i in range(orank.value))
+    if out is None:
+        out = torch.empty(oshape, dtype=x.dtype, device=x.device)
+    elif tuple(out.shape) != oshape:
+        # test_elementwise_add_op.py:695-720 (inplace broadcast errors)
+        raise ValueError(f"(InvalidArgument) The shape of tensor assigned value must be the same: {tuple(out.shape)} vs {oshape}")
+    L.check(getattr(lib, fn_name)(_ptr(x), xd, xr, _ptr(y), yd, yr, _ptr(out), _dtype_code(x.dtype), _stream()), lib)
+    return out
+
+
+def add(x, y, name=None):
+    """paddle.add(x, y): elementwise x + y with NumPy broadcasting."""
+    return _elementwise("pdb200_add", x, y)
+
+
+def add_(x, y, name=None):
+    """In-place add: x must already have the broadcast shape."""
+    return _elementwise("pdb200_add", x, y, out=x)
+
+
+def multiply(x, y, name=None):
+    """paddle.multiply(x, y): elementwise x * y with NumPy broadcasting (bool: logical AND)."""
+    return _elementwise("pdb200_multiply", x, y)
+
+
+def multiply_(x, y, name=None):
+    return _elementwise("pdb200_multiply", x, y, out=x)
+
+
+# ---------------------------------------------------------------------------------------
+# reductions
+# ---------------------------------------------------------------------------------------
+def _norm_axes(axis, rank):
+    if axis is None:
+        return []
+    if isinstance(axis, (list, tuple)):
+        axes = [int(a) for a in axis]
+    else:
+        axes = [int(axis)]
+    for a in axes:
+        if rank == 0:
+            if a not in (0, -1):
+                raise ValueError(f"(InvalidArgument) axis {a} out of range for a 0-D tensor")
+        elif a < -rank or a >= rank:
+            raise ValueError(f"(InvalidArgument) The reduce dim index should be in the range [-{rank}, {rank}), but received {a}")
+    return axes
+
+
+def _reduced_shape(shape, axes, keepdim):
+    """ReduceIntArrayAxisInferMeta / SumRawInferMeta shape rule (infermeta/unary.cc:3771, 4725-4753)."""
+    rank = len(shape)
+    if rank == 0:
+        return ()
+    red = set(a % rank for a in axes) if axes else set(range(rank))
+    if keepdim:
+        return tuple(1 if i in red else d for i, d in enumerate(shape))
+    return tuple(d for i, d in enumerate(shape) if i not in red)
+
+
+_REDUCE_FN = {
+    L.REDUCE_SUM: "pdb200_sum_raw", L.REDUCE_MEAN: "pdb200_mean_raw", L.REDUCE_MAX: "pdb200_max_raw",
+    L.REDUCE_MIN: "pdb200_min_raw", L.REDUCE_PROD: "pdb200_prod",
+}
+
+
+def _reduce(op, x, axis, keepdim, out_dtype):
+    _require_cuda(x)
+    lib = L.load()
+    x = x.contiguous()
+    axes = _norm_axes(axis, x.dim())
+    if x.numel() == 0:
+        raise ValueError("(InvalidArgument) Tensor need be reduced must not empty.")
+    oshape = _reduced_shape(tuple(x.shape), axes, keepdim)
+    out = torch.empty(oshape, dtype=out_dtype, device=x.device)
+    xd, xr = L.dims_array(x.shape)
+    ad, an = L.dims_array(axes)
+    reduce_all = 1 if not axes else 0
+    xc, oc = _dtype_code(x.dtype), _dtype_code(out_dtype)
+    nbytes = lib.pdb200_reduce_workspace_bytes(op, xd, xr, ad, an, reduce_all, xc, oc)
+    ws = _workspace(nbytes, x.device)
+    L.check(getattr(lib, _REDUCE_FN[op])(_ptr(x), xd, xr, ad, an, reduce_all, xc, oc, _ptr(out), _ptr(ws),
+                                         nbytes, _stream()), lib)
+    return out
+
+
+def sum(x, axis=None, dtype=None, keepdim=False, name=None):
+    """paddle.sum: bool/int32 inputs produce int64 unless `dtype` is given
+    (SumRawInferMeta, infermeta/unary.cc:4743-4747)."""
+    dt = _as_torch_dtype(dtype)
+    if dt is None:
+        dt = torch.int64 if x.dtype in (torch.bool, torch.int32) else x.dtype
+    return _reduce(L.REDUCE_SUM, x, axis, keepdim, dt)
+
+
+def mean(x, axis=None, keepdim=False, name=None):
+    return _reduce(L.REDUCE_MEAN, x, axis, keepdim, x.dtype)
+
+
+def max(x, axis=None, keepdim=False, name=None):
+    return _reduce(L.REDUCE_MAX, x, axis, keepdim, x.dtype)
+
+
+def min(x, axis=None, keepdim=False, name=None):
+    return _reduce(L.REDUCE_MIN, x, axis, keepdim, x.dtype)
+
+
+def prod(x, axis=None, keepdim=False, dtype=None, name=None):
+    dt = _as_torch_dtype(dtype)
+    if dt is not None and dt != x.dtype:
+        raise NotImplementedError("prod(dtype=...) casts first in Paddle (math.py:4830); cast the input yourself")
+    return _reduce(L.REDUCE_PROD, x, axis, keepdim, x.dtype)
+
+
+def argmax(x, axis=None, keepdim=False, dtype="int64", name=None):
+    """paddle.argmax: axis=None flattens; lowest index wins ties; dtype int64 or int32
+    (ArgMinMaxInferMeta, infermeta/unary.cc:257)."""
+    _require_cuda(x)
+    lib = L.load()
+    x = x.contiguous()
+    odt = _as_torch_dtype(dtype)
+    if odt not in (torch.int64, torch.int32):
+        raise ValueError("(InvalidArgument) The attribute of dtype in argmin/argmax must be [int32] or [int64]")
+    if x.numel() == 0:
+        raise ValueError("(InvalidArgument) argmin/argmax input numel must > 0")
+    rank = x.dim()
+    flatten = axis is None
+    ax = 0 if flatten else int(axis)
+    if not flatten and rank > 0 and (ax < -rank or ax >= rank):
+        raise ValueError(f"(InvalidArgument) 'axis'({ax}) must be in [-{rank}, {rank})")
+    if flatten or rank == 0:
+        oshape = tuple([1] * rank) if (keepdim and flatten) else ()
+    else:
+        a = ax % rank
+        oshape = tuple(1 if i == a else d for i, d in enumerate(x.shape)) if keepdim else \
+            tuple(d for i, d in enumerate(x.shape) if i != a)
+    out = torch.empty(oshape, dtype=odt, device=x.device)
+    xd, xr = L.dims_array(x.shape)
+    xc = _dtype_code(x.dtype)
+    nbytes = lib.pdb200_argmax_workspace_bytes(xd, xr, ax, int(flatten), xc)
+    ws = _workspace(nbytes, x.device)
+    L.check(lib.pdb200_argmax(_ptr(x), xd, xr, ax, int(flatten), xc, _dtype_code(odt), _ptr(out), _ptr(ws),
+                              nbytes, _stream()), lib)
+    return out

@@ -1,0 +1,184 @@
+"""Test-side access to the CPU oracles (TEST INFRASTRUCTURE — never imported by the product).
+
+  port : oracle/liboracle.so          plain-C restatement (oracle/phi_cpu_oracle.c), always available
+  ref  : oracle/_ref/libphi_cpu_ref.so the reference's own CPU PHI kernels compiled from
+         /root/reference (oracle/build_ref.sh); present in the build container and shipped
+         to the GPU box as a prebuilt .so
+
+Both expose the same numpy-level API through `Oracle`.  bf16/fp16 tensors travel as uint16 bit
+patterns (numpy has no bfloat16).
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PORT_SO = os.path.join(ROOT, "oracle", "liboracle.so")
+PORT_SRC = os.path.join(ROOT, "oracle", "phi_cpu_oracle.c")
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libphi_cpu_ref.so")
+
+BOOL, UINT8, INT8, INT16, INT32, INT64, FLOAT16, BFLOAT16, FLOAT32, FLOAT64 = range(10)
+NP2CODE = {np.dtype(np.bool_): BOOL, np.dtype(np.uint8): UINT8, np.dtype(np.int8): INT8,
+           np.dtype(np.int16): INT16, np.dtype(np.int32): INT32, np.dtype(np.int64): INT64,
+           np.dtype(np.float32): FLOAT32, np.dtype(np.float64): FLOAT64}
+OPS = {"sum": 0, "mean": 1, "max": 2, "min": 3, "prod": 4}
+
+_i64p = ctypes.POINTER(ctypes.c_int64)
+
+
+def build_port(force=False):
+    if force or not os.path.exists(PORT_SO) or os.path.getmtime(PORT_SO) < os.path.getmtime(PORT_SRC):
+        subprocess.check_call(["gcc", "-O2", "-fPIC", "-shared", "-std=gnu11", "-fno-fast-math",
+                               "-ffp-contract=off", "-o", PORT_SO, PORT_SRC, "-lm"])
+    return PORT_SO
+
+
+def _dims(shape):
+    n = len(shape)
+    return (ctypes.c_int64 * max(n, 1))(*[int(s) for s in shape]), n
+
+
+def _vp(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def reduced_shape(shape, axes, keepdim):
+    rank = len(shape)
+    if rank == 0:
+        return ()
+    red = set(a % rank for a in axes) if axes else set(range(rank))
+    if keepdim:
+        return tuple(1 if i in red else d for i, d in enumerate(shape))
+    return tuple(d for i, d in enumerate(shape) if i not in red)
+
+
+class Oracle:
+    """kind = 'port' (C restatement) or 'ref' (compiled reference)."""
+
+    def __init__(self, kind="port"):
+        self.kind = kind
+        if kind == "port":
+            self.lib = ctypes.CDLL(build_port())
+            self.p = "oracle_"
+        else:
+            if not os.path.exists(REF_SO):
+                raise FileNotFoundError(REF_SO)
+            self.lib = ctypes.CDLL(REF_SO)
+            self.p = "phi_ref_"
+
+    # ---- bf16 / fp16 -------------------------------------------------------------------
+    def _conv(self, name, src, dst_dtype):
+        src = np.ascontiguousarray(src)
+        dst = np.empty(src.shape, dst_dtype)
+        getattr(self.lib, self.p + name)(_vp(src), _vp(dst), ctypes.c_int64(src.size))
+        return dst
+
+    def f32_to_bf16(self, a):
+        return self._conv("float_to_bf16", np.asarray(a, np.float32), np.uint16)
+
+    def bf16_to_f32(self, a):
+        return self._conv("bf16_to_float", np.asarray(a, np.uint16), np.float32)
+
+    def f32_to_fp16(self, a):
+        return self._conv("float_to_fp16", np.asarray(a, np.float32), np.uint16)
+
+    def fp16_to_f32(self, a):
+        return self._conv("fp16_to_float", np.asarray(a, np.uint16), np.float32)
+
+    # ---- ops -----------------------------------------------------------------------------
+    def elementwise(self, op, x, y, code=None):
+        """op 'add'|'multiply'.  code overrides the dtype (BFLOAT16/FLOAT16 on uint16 arrays)."""
+        x = np.ascontiguousarray(x)
+        y = np.ascontiguousarray(y)
+        code = NP2CODE[x.dtype] if code is None else code
+        oshape = np.broadcast_shapes(x.shape, y.shape)
+        out = np.empty(oshape, x.dtype)
+        xd, xr = _dims(x.shape)
+        yd, yr = _dims(y.shape)
+        opc = 0 if op == "add" else 1
+        if self.kind == "port":
+            rc = self.lib.oracle_elementwise(opc, code, _vp(x), xd, xr, _vp(y), yd, yr, _vp(out))
+        else:
+            od, orank = _dims(oshape)
+            rc = self.lib.phi_ref_elementwise(opc, code, _vp(x), xd, xr, _vp(y), yd, yr, od, orank, _vp(out))
+        self._check(rc)
+        return out
+
+    def reduce(self, op, x, axis=None, keepdim=False):
+        x = np.ascontiguousarray(x)
+        axes = [] if axis is None else ([int(a) for a in axis] if isinstance(axis, (list, tuple)) else [int(axis)])
+        oshape = reduced_shape(x.shape, axes, keepdim)
+        out = np.empty(oshape, x.dtype)
+        xd, xr = _dims(x.shape)
+        ad, an = _dims(axes)
+        code = NP2CODE[x.dtype]
+        if self.kind == "port":
+            rc = self.lib.oracle_reduce(OPS[op], code, _vp(x), xd, xr, ad, an, int(not axes), _vp(out))
+        else:
+            od, orank = _dims(oshape)
+            rc = self.lib.phi_ref_reduce(OPS[op], code, _vp(x), xd, xr, ad, an, int(keepdim), int(not axes),
+                                         od, orank, _vp(out))
+        self._check(rc)
+        return out
+
+    def argmax(self, x, axis=None, keepdim=False, dtype=np.int64, code=None):
+        x = np.ascontiguousarray(x)
+        code = NP2CODE[x.dtype] if code is None else code
+        flatten = axis is None
+        rank = x.ndim
+        if flatten or rank == 0:
+            oshape = tuple([1] * rank) if (keepdim and flatten) else ()
+        else:
+            a = axis % rank
+            oshape = tuple(1 if i == a else d for i, d in enumerate(x.shape)) if keepdim else \
+                tuple(d for i, d in enumerate(x.shape) if i != a)
+        out = np.empty(oshape, dtype)
+        xd, xr = _dims(x.shape)
+        ocode = NP2CODE[np.dtype(dtype)]
+        ax = 0 if flatten else int(axis)
+        if self.kind == "port":
+            rc = self.lib.oracle_argmax(code, _vp(x), xd, xr, ctypes.c_int64(ax), int(flatten), ocode, _vp(out))
+        else:
+            od, orank = _dims(oshape)
+            rc = self.lib.phi_ref_argmax(code, _vp(x), xd, xr, ctypes.c_int64(ax), int(keepdim), int(flatten),
+                                         ocode, od, orank, _vp(out))
+        self._check(rc)
+        return out
+
+    def softmax(self, x, axis=-1):
+        x = np.ascontiguousarray(x)
+        out = np.empty_like(x)
+        xd, xr = _dims(x.shape)
+        rc = getattr(self.lib, self.p + "softmax")(NP2CODE[x.dtype], _vp(x), xd, xr, int(axis), _vp(out))
+        self._check(rc)
+        return out
+
+    def layer_norm(self, x, begin_norm_axis, scale=None, bias=None, epsilon=1e-5):
+        x = np.ascontiguousarray(x)
+        y = np.empty_like(x)
+        rows = int(np.prod(x.shape[:begin_norm_axis], dtype=np.int64))
+        mean = np.empty((rows,), x.dtype)
+        var = np.empty((rows,), x.dtype)
+        xd, xr = _dims(x.shape)
+        s = None if scale is None else np.ascontiguousarray(scale, x.dtype)
+        b = None if bias is None else np.ascontiguousarray(bias, x.dtype)
+        rc = getattr(self.lib, self.p + "layer_norm")(
+            NP2CODE[x.dtype], _vp(x), xd, xr, _vp(s) if s is not None else None,
+            _vp(b) if b is not None else None, ctypes.c_float(epsilon), int(begin_norm_axis), _vp(y), _vp(mean),
+            _vp(var))
+        self._check(rc)
+        return y, mean, var
+
+    def _check(self, rc):
+        if rc != 0:
+            msg = ""
+            if self.kind == "ref":
+                self.lib.phi_ref_last_error.restype = ctypes.c_char_p
+                msg = self.lib.phi_ref_last_error().decode("utf-8", "replace")[:400]
+            raise ValueError(f"oracle[{self.kind}] rc={rc} {msg}")
+
+
+def have_ref():
+    return os.path.exists(REF_SO)

@@ -1,0 +1,333 @@
+"""GPU parity: CUDA kernels (through the Python mirror -> C-ABI libpdb200.so) vs the CPU oracle.
+
+Bars (BASELINE.json north_star): bit-exact for integer sum/prod, max/min/argmax and all
+add/multiply; rtol 1e-5 for fp32 reductions / softmax / layer_norm accumulated in fp32;
+<= 1 ulp of the output type for bf16/fp16 outputs accumulated in fp32.
+Shape/axis matrices follow the reference's op tests (see tests/golden/make_golden.py).
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle_lib as O
+from gpu_util import assert_half_close, to_dev, to_np
+
+pytestmark = pytest.mark.gpu
+
+import paddlepaddle_b200 as paddle  # noqa: E402
+from golden.make_golden import BCAST_CASES, REDUCE_CASES  # noqa: E402
+
+F = paddle.nn.functional
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "phi_cpu_golden.npz")
+FP32_RTOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return dict(np.load(GOLDEN))
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _native_code_loaded():
+    from paddlepaddle_b200 import _lib
+    lib = _lib.load()
+    before = lib.pdb200_launch_count()
+    yield
+    assert lib.pdb200_launch_count() > before, "no pdb200 kernel was launched by this module"
+
+
+# ------------------------------------------------------------------------------------------
+# elementwise
+# ------------------------------------------------------------------------------------------
+def test_elementwise_golden(gold):
+    for name, xs, ys in BCAST_CASES:
+        for dt in ("float32", "int32", "int64", "float64", "int16", "uint8", "int8", "bool", "bfloat16"):
+            a, b = gold[f"ew_{name}_{dt}__in0"], gold[f"ew_{name}_{dt}__in1"]
+            half = "bf16" if dt == "bfloat16" else None
+            ta, tb = to_dev(a, half), to_dev(b, half)
+            for op, fn in (("add", paddle.add), ("multiply", paddle.multiply)):
+                got = to_np(fn(ta, tb))
+                want = gold[f"ew_{name}_{dt}_{op}__out"]
+                assert got.shape == want.shape, (name, dt, op)
+                assert np.array_equal(got.view(np.uint8), want.view(np.uint8)), (name, dt, op)
+
+
+@pytest.mark.parametrize("xs,ys", [
+    ((257, 4096), (4096,)), ((4096,), (257, 4096)), ((300, 1000), (1000,)), ((33, 1001), (1001,)),
+    ((512, 2048), (512, 1)), ((512, 1), (512, 2048)), ((1, 100000), (1,)), ((7, 130), (7, 1)),
+    ((1 << 20,), (1 << 20,)), ((1000003,), (1000003,)), ((2, 3, 4, 5, 6, 7), (3, 1, 5, 1, 7)),
+    ((64, 1, 32), (1, 48, 32)), ((16, 8), (16, 1)), ((5, 1, 8), (1, 6, 1)),
+])
+@pytest.mark.parametrize("dt", ["float32", "int32", "bfloat16", "float16", "int64"])
+def test_elementwise_routes(port, xs, ys, dt):
+    rng = np.random.default_rng(hash((xs, ys, dt)) & 0xffff)
+    if dt in ("bfloat16", "float16"):
+        conv = port.f32_to_bf16 if dt == "bfloat16" else port.f32_to_fp16
+        a, b = conv(rng.standard_normal(xs).astype(np.float32)), conv(rng.standard_normal(ys).astype(np.float32))
+        half, code = ("bf16", O.BFLOAT16) if dt == "bfloat16" else ("fp16", O.FLOAT16)
+    elif dt == "float32":
+        a, b = rng.standard_normal(xs).astype(np.float32), rng.standard_normal(ys).astype(np.float32)
+        half, code = None, None
+    else:
+        info = np.iinfo(dt)
+        a = rng.integers(info.min, info.max, xs, dtype=dt, endpoint=True)
+        b = rng.integers(info.min, info.max, ys, dtype=dt, endpoint=True)
+        half, code = None, None
+    ta, tb = to_dev(a, half), to_dev(b, half)
+    for op, fn in (("add", paddle.add), ("multiply", paddle.multiply)):
+        got = to_np(fn(ta, tb))
+        want = port.elementwise(op, a, b, code)
+        assert np.array_equal(got.view(np.uint8), want.view(np.uint8)), (op, xs, ys, dt)
+
+
+def test_elementwise_inplace_and_unaligned(port):
+    rng = np.random.default_rng(5)
+    a = rng.standard_normal((300, 1000)).astype(np.float32)
+    b = rng.standard_normal((1000,)).astype(np.float32)
+    ta = to_dev(a)
+    r = paddle.add_(ta, to_dev(b))
+    assert r.data_ptr() == ta.data_ptr()
+    assert np.array_equal(to_np(ta), port.elementwise("add", a, b))
+    with pytest.raises(ValueError):
+        paddle.add_(to_dev(b), to_dev(a))  # x is the smaller operand: inplace broadcast error
+    with pytest.raises(ValueError, match="Broadcast dimension mismatch"):
+        paddle.add(to_dev(a), to_dev(np.zeros((7,), np.float32)))
+    # unaligned base pointers (a view one element into a buffer) take the scalar routes
+    big = to_dev(rng.standard_normal(1000 * 300 + 1).astype(np.float32))
+    x = big[1:].view(300, 1000)
+    assert not x.data_ptr() % 16 == 0
+    got = to_np(paddle.multiply(x, to_dev(b)))
+    assert np.array_equal(got, port.elementwise("multiply", to_np(x), b))
+    assert paddle.add(torch.empty((0, 3), device="cuda"), torch.empty((3,), device="cuda")).shape == (0, 3)
+
+
+# ------------------------------------------------------------------------------------------
+# reductions
+# ------------------------------------------------------------------------------------------
+_RED = {"sum": paddle.sum, "mean": paddle.mean, "max": paddle.max, "min": paddle.min, "prod": paddle.prod}
+
+
+def _check_reduce(op, got, want, dt):
+    assert got.shape == want.shape
+    if dt.startswith("int") or op in ("max", "min"):
+        assert np.array_equal(got, want), (op, dt)
+    else:
+        np.testing.assert_allclose(got, want, rtol=FP32_RTOL if dt == "float32" else 1e-12)
+
+
+def test_reduce_golden(gold):
+    for name, shape, axis, keep in REDUCE_CASES:
+        for dt in ("float32", "float64", "int32", "int64"):
+            x = gold[f"red_{name}_{dt}__in0"]
+            tx = to_dev(x)
+            for op, fn in _RED.items():
+                want = gold[f"red_{name}_{dt}_{op}__out"]
+                if op == "sum" and dt == "int32":
+                    got = to_np(fn(tx, axis=axis, keepdim=keep, dtype="int32"))  # same-dtype kernel
+                    assert fn(tx, axis=axis).dtype == torch.int64                  # InferMeta default
+                else:
+                    got = to_np(fn(tx, axis=axis, keepdim=keep))
+                _check_reduce(op, got, want, dt)
+    x = gold["red_wrap_int64__in0"]
+    assert np.array_equal(to_np(paddle.prod(to_dev(x), axis=1)), gold["red_wrap_int64_prod__out"])
+    assert np.array_equal(to_np(paddle.sum(to_dev(x))), gold["red_wrap_int64_sum__out"])
+
+
+@pytest.mark.parametrize("shape,axis", [
+    ((4096, 4096), -1),                                   # config 1: rows_warp, G = 32
+    ((1000, 3), -1), ((1000, 20), -1), ((513, 100), -1),  # rows_warp, small G, scalar + vector
+    ((37, 5000), -1), ((3, 70000), -1),                   # rows_block, few rows -> splits
+    ((1 << 22,), None), ((1000003,), None),               # full reduce: partials + fold
+    ((4096, 512), 0), ((70000, 24), 0), ((129, 7, 33), 1),  # cols, with and without splits
+    ((8, 16, 32, 64), (0, 2)), ((6, 5, 4, 3, 2), (1, 3)),   # two reduce runs -> two passes
+    ((2, 3, 4), (0, 1, 2)), ((5, 1, 7), 1), ((), None),
+])
+@pytest.mark.parametrize("dt", ["float32", "int64", "int32", "float64"])
+def test_reduce_routes(port, shape, axis, dt):
+    rng = np.random.default_rng(hash((shape, str(axis), dt)) & 0xffff)
+    if dt.startswith("float"):
+        x = rng.uniform(-1, 1, shape).astype(dt)
+    else:
+        x = rng.integers(-2**30 if dt == "int32" else -2**40, 2**30 if dt == "int32" else 2**40, shape).astype(dt)
+    tx = to_dev(x)
+    for op, fn in _RED.items():
+        if op == "prod" and dt.startswith("float") and x.size > 100000:
+            continue  # underflows to 0 on both sides; nothing to compare
+        want = port.reduce(op, x, axis)
+        kw = {"dtype": "int32"} if (op == "sum" and dt == "int32") else {}
+        got = to_np(fn(tx, axis=axis, **kw))
+        if dt.startswith("float") and op in ("sum", "mean"):
+            # cancellation: judge against the magnitude of the terms, as rtol on |x| summed
+            scale = np.abs(x).sum(axis=axis if axis is None or isinstance(axis, int) else tuple(axis)) if x.ndim else abs(x)
+            if op == "mean":
+                scale = scale / max(1, x.size // max(1, want.size))
+            assert np.all(np.abs(got - want) <= (FP32_RTOL if dt == "float32" else 1e-12) * np.maximum(scale, 1e-30)), (op, shape)
+        else:
+            _check_reduce(op, got, want, dt)
+
+
+@pytest.mark.parametrize("half", ["bf16", "fp16"])
+def test_reduce_half_types(port, half):
+    """bf16/fp16 accumulate in float (MPTypeTrait); output rounded once: <= 1 ulp of the oracle
+    (oracle = upcast -> fp32 CPU kernel -> RNE)."""
+    rng = np.random.default_rng(11)
+    conv, back = (port.f32_to_bf16, port.bf16_to_f32) if half == "bf16" else (port.f32_to_fp16, port.fp16_to_f32)
+    for shape, axis in [((512, 1024), -1), ((64, 333), -1), ((300, 64), 0), ((20000,), None)]:
+        bits = conv(rng.uniform(-1, 1, shape).astype(np.float32))
+        xf = back(bits)
+        tx = to_dev(bits, half)
+        for op, fn in _RED.items():
+            if op == "prod" and xf.size > 1000:
+                continue
+            want_f = port.reduce(op, xf, axis)
+            got = to_np(fn(tx, axis=axis))
+            if op in ("max", "min"):
+                assert np.array_equal(got, conv(want_f))
+            else:
+                assert_half_close(got, conv(want_f), 1, f"{op} {shape}")
+        # sum with fp32 output keeps full precision (kps/reduce_kernel.cu:251-265)
+        got32 = to_np(paddle.sum(tx, axis=axis, dtype="float32"))
+        want32 = port.reduce("sum", xf, axis)
+        np.testing.assert_allclose(got32, want32, rtol=FP32_RTOL, atol=1e-4)
+
+
+def test_sum_bool_and_int32_promote(port):
+    rng = np.random.default_rng(12)
+    b = rng.random((100, 1000)) > 0.3
+    got = paddle.sum(to_dev(b), axis=1)
+    assert got.dtype == torch.int64 and np.array_equal(to_np(got), b.sum(1))
+    i = rng.integers(-2**31, 2**31 - 1, (50, 100000), dtype=np.int32)
+    got = paddle.sum(to_dev(i))
+    assert got.dtype == torch.int64 and to_np(got).item() == int(i.astype(np.int64).sum())
+    with pytest.raises(ValueError):
+        paddle.sum(to_dev(i), axis=2)
+    with pytest.raises(ValueError, match="must not empty"):
+        paddle.max(torch.empty((0, 4), device="cuda"), axis=1)
+
+
+# ------------------------------------------------------------------------------------------
+# argmax
+# ------------------------------------------------------------------------------------------
+def test_argmax_golden(gold):
+    table = {"a3_0": 0, "a3_1": 1, "a3_m1": -1, "a_flat": None, "a1": 0, "a2_wide": 1}
+    for name, axis in table.items():
+        for dt in ("float32", "float64", "int32", "int64", "int16", "uint8"):
+            x = gold[f"arg_{name}_{dt}__in0"]
+            tx = to_dev(x)
+            assert np.array_equal(to_np(paddle.argmax(tx, axis=axis)), gold[f"arg_{name}_{dt}_i64__out"])
+            got = paddle.argmax(tx, axis=axis, keepdim=True, dtype="int32")
+            want = gold[f"arg_{name}_{dt}_i32_keep__out"]
+            assert got.dtype == torch.int32 and tuple(got.shape) == want.shape
+            assert np.array_equal(to_np(got), want)
+
+
+@pytest.mark.parametrize("shape,axis", [((1 << 22,), None), ((2000, 4096), -1), ((3, 200000), 1), ((5000, 33), 0),
+                                        ((17, 300, 40), 1), ((7, 9), None), ((), None)])
+def test_argmax_routes_with_ties(port, shape, axis):
+    rng = np.random.default_rng(13)
+    x = rng.integers(0, 100, shape).astype(np.float32)  # ties everywhere: the lowest index must win
+    assert np.array_equal(to_np(paddle.argmax(to_dev(x), axis=axis)), port.argmax(x, axis))
+    xb = port.f32_to_bf16(x)
+    assert np.array_equal(to_np(paddle.argmax(to_dev(xb, "bf16"), axis=axis)), port.argmax(xb, axis, code=O.BFLOAT16))
+    xi = rng.integers(-2**62, 2**62, shape, dtype=np.int64)
+    assert np.array_equal(to_np(paddle.argmax(to_dev(xi), axis=axis)), port.argmax(xi, axis))
+
+
+# ------------------------------------------------------------------------------------------
+# softmax
+# ------------------------------------------------------------------------------------------
+def test_softmax_golden(gold):
+    table = {"s2": -1, "s4_m1": -1, "s4_0": 0, "s4_1": 1, "s4_2": 2, "s5": 3, "s_2048": -1, "s_odd": -1, "s_clip": -1}
+    for name, axis in table.items():
+        for dt in ("float32", "float64"):
+            x = gold[f"sm_{name}_{dt}__in0"]
+            got = to_np(F.softmax(to_dev(x), axis=axis))
+            np.testing.assert_allclose(got, gold[f"sm_{name}_{dt}__out"], rtol=FP32_RTOL if dt == "float32" else 1e-12)
+
+
+@pytest.mark.parametrize("shape,axis", [((64, 2048), -1), ((33, 1001), -1), ((1000, 7), -1), ((16, 4096), -1),
+                                        ((5, 20000), -1), ((3, 60001), -1), ((2, 300000), -1),
+                                        ((8, 100, 64), 1), ((4, 17, 5, 3), 1), ((50, 1), -1)])
+def test_softmax_routes(port, shape, axis):
+    rng = np.random.default_rng(14)
+    x = (rng.standard_normal(shape) * 2).astype(np.float32)
+    want = port.softmax(x, axis)
+    got = to_np(F.softmax(to_dev(x), axis=axis))
+    np.testing.assert_allclose(got, want, rtol=FP32_RTOL, atol=1e-30)
+    np.testing.assert_allclose(got.sum(axis), 1.0, rtol=1e-5)
+    for half, conv, back in (("bf16", port.f32_to_bf16, port.bf16_to_f32), ("fp16", port.f32_to_fp16, port.fp16_to_f32)):
+        bits = conv(x)
+        want_h = conv(port.softmax(back(bits), axis))
+        got_h = to_np(F.softmax(to_dev(bits, half), axis=axis))
+        assert_half_close(got_h, want_h, 1, f"softmax {half} {shape}")
+
+
+def test_softmax_edge_cases(port):
+    x = torch.randn(128, 2048, device="cuda")
+    ref_out = to_np(F.softmax(x, axis=-1))
+    y = F.softmax_(x, axis=-1)
+    assert y.data_ptr() == x.data_ptr() and np.array_equal(to_np(x), ref_out)
+    assert to_np(F.softmax(torch.tensor(3.0, device="cuda"), axis=-1)).item() == 1.0   # 0-D
+    assert F.softmax(torch.empty((0, 5), device="cuda")).shape == (0, 5)
+    with pytest.raises(ValueError):
+        F.softmax(torch.zeros(3, 4, device="cuda"), axis=2)
+
+
+# ------------------------------------------------------------------------------------------
+# layer_norm
+# ------------------------------------------------------------------------------------------
+def test_layer_norm_golden(gold):
+    table = {"l4": 1, "l4_3": 3, "l2_8192": 1, "l2_odd": 1, "l3": 2}
+    for name, bna in table.items():
+        for dt in ("float32", "float64"):
+            key = f"ln_{name}_{dt}"
+            x, w, b = gold[key + "__in0"], gold[key + "__in1"], gold[key + "__in2"]
+            shape = list(x.shape[bna:])
+            tw, tb = to_dev(w).view(shape), to_dev(b).view(shape)
+            y, m, v = F.layer_norm(to_dev(x), shape, tw, tb, 1e-5, return_stats=True)
+            tol = dict(rtol=FP32_RTOL, atol=1e-6) if dt == "float32" else dict(rtol=1e-12, atol=1e-13)
+            np.testing.assert_allclose(to_np(y), gold[key + "_wb__out0"], **tol)
+            np.testing.assert_allclose(to_np(m), gold[key + "_wb__out1"], **tol)
+            np.testing.assert_allclose(to_np(v), gold[key + "_wb__out2"], **tol)
+            y0 = F.layer_norm(to_dev(x), shape)
+            np.testing.assert_allclose(to_np(y0), gold[key + "_none__out0"], **tol)
+
+
+@pytest.mark.parametrize("rows,D", [(64, 8192), (33, 1001), (1000, 24), (7, 2048), (5, 4096), (3, 16384),
+                                    (2, 40000), (2, 100000), (16, 768), (9, 257)])
+def test_layer_norm_routes(port, rows, D):
+    rng = np.random.default_rng(15)
+    x = (rng.standard_normal((rows, D)) * (1 + np.arange(rows)[:, None] % 7) + np.arange(rows)[:, None] % 3).astype(np.float32)
+    w, b = rng.uniform(0.5, 1.5, D).astype(np.float32), rng.uniform(-0.5, 0.5, D).astype(np.float32)
+    wy, wm, wv = port.layer_norm(x, 1, w, b, 1e-5)
+    y, m, v = F.layer_norm(to_dev(x), [D], to_dev(w), to_dev(b), 1e-5, return_stats=True)
+    np.testing.assert_allclose(to_np(y), wy, rtol=FP32_RTOL, atol=2e-6)
+    np.testing.assert_allclose(to_np(m), wm, rtol=FP32_RTOL, atol=1e-6)
+    np.testing.assert_allclose(to_np(v), wv, rtol=FP32_RTOL)
+    # only scale / only bias
+    np.testing.assert_allclose(to_np(F.layer_norm(to_dev(x), [D], to_dev(w), None)), port.layer_norm(x, 1, w, None)[0], rtol=FP32_RTOL, atol=2e-6)
+    np.testing.assert_allclose(to_np(F.layer_norm(to_dev(x), [D], None, to_dev(b))), port.layer_norm(x, 1, None, b)[0], rtol=FP32_RTOL, atol=2e-6)
+    # bf16 / fp16 input, params in the same dtype and in float32: <= 1 ulp of the rounded fp32 oracle
+    for half, conv, back in (("bf16", port.f32_to_bf16, port.bf16_to_f32), ("fp16", port.f32_to_fp16, port.fp16_to_f32)):
+        xb, wb_, bb = conv(x), conv(w), conv(b)
+        oy, om, ov = port.layer_norm(back(xb), 1, back(wb_), back(bb), 1e-5)
+        gy, gm, gv = F.layer_norm(to_dev(xb, half), [D], to_dev(wb_, half), to_dev(bb, half), 1e-5, return_stats=True)
+        assert gm.dtype == torch.float32
+        assert_half_close(to_np(gy), conv(oy), 1, f"ln {half} same-dtype params {rows}x{D}")
+        np.testing.assert_allclose(to_np(gm), om, rtol=FP32_RTOL, atol=1e-6)
+        np.testing.assert_allclose(to_np(gv), ov, rtol=FP32_RTOL)
+        oy2, _, _ = port.layer_norm(back(xb), 1, w, b, 1e-5)
+        gy2 = F.layer_norm(to_dev(xb, half), [D], to_dev(w), to_dev(b), 1e-5)
+        assert_half_close(to_np(gy2), conv(oy2), 1, f"ln {half} fp32 params {rows}x{D}")
+
+
+def test_layer_norm_errors():
+    x = torch.zeros(4, 8, device="cuda")
+    with pytest.raises(ValueError, match="normalized_shape"):
+        F.layer_norm(x, [7])
+    with pytest.raises(ValueError):
+        F.layer_norm(x, [8], torch.zeros(8, device="cuda", dtype=torch.float64))
+    y = F.layer_norm(torch.zeros(2, 3, 4, device="cuda"), [3, 4])  # multi-dim normalized_shape
+    assert y.shape == (2, 3, 4) and float(y.abs().max()) == 0.0

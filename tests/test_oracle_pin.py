@@ -1,0 +1,165 @@
+"""Pins the C restatement (oracle/phi_cpu_oracle.c) to the reference.
+
+ - against tests/golden/phi_cpu_golden.npz (outputs of the reference's own CPU kernels, recorded by
+   tests/golden/make_golden.py) — always runs;
+ - against oracle/_ref/libphi_cpu_ref.so live, on fresh random inputs — when that library exists.
+Integer, max/min, argmax and elementwise results must be bit-identical; float sum/mean are
+bit-identical too (the Eigen accumulation order is restated); exp-based and prod results to 1e-6.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "phi_cpu_golden.npz")
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return dict(np.load(GOLDEN))
+
+
+def _cases(gold, prefix):
+    return sorted({k.split("__")[0] for k in gold if k.startswith(prefix) and "__in0" in k})
+
+
+def _axis_of(name, table):
+    for n, shape, axis, *rest in table:
+        if n == name:
+            return axis, (rest[0] if rest else False)
+    raise KeyError(name)
+
+
+from golden.make_golden import BCAST_CASES, REDUCE_CASES  # noqa: E402
+
+
+def test_doc_known_answers(port, gold):
+    # python/paddle/tensor/math.py:1530-1585
+    x = gold["doc_sum__in0"]
+    np.testing.assert_allclose(port.reduce("sum", x), 3.5, rtol=1e-6)
+    np.testing.assert_allclose(port.reduce("sum", x, 0), [0.3, 0.5, 1.1, 1.6], rtol=1e-6)
+    np.testing.assert_allclose(port.reduce("sum", x, -1), [1.9, 1.6], rtol=1e-6)
+    assert port.reduce("sum", x, -1, True).shape == (2, 1)
+    for k in ("doc_sum_all", "doc_sum_0", "doc_sum_m1", "doc_sum_m1_keep"):
+        ax = {"doc_sum_all": None, "doc_sum_0": 0}.get(k, -1)
+        assert np.array_equal(port.reduce("sum", x, ax, k.endswith("keep")), gold[k + "__out"])
+    # int32 sum -> int64 by InferMeta: the kernel sees an int64 tensor (cpu/reduce.h:56-65)
+    y = np.array([[1, 2], [3, 4]], np.int32).astype(np.int64)
+    assert port.reduce("sum", y).item() == 10
+
+
+def test_reduce_golden(port, gold):
+    n = 0
+    for name, shape, axis, keep in REDUCE_CASES:
+        for dt in ("float32", "float64", "int32", "int64"):
+            x = gold[f"red_{name}_{dt}__in0"]
+            for op in ("sum", "mean", "max", "min", "prod"):
+                want = gold[f"red_{name}_{dt}_{op}__out"]
+                got = port.reduce(op, x, axis, keep)
+                assert got.shape == want.shape
+                if dt.startswith("int") or op in ("max", "min", "sum", "mean"):
+                    assert np.array_equal(got, want), (name, dt, op)
+                else:
+                    np.testing.assert_allclose(got, want, rtol=1e-6)
+                n += 1
+    assert n == len(REDUCE_CASES) * 4 * 5
+    x = gold["red_wrap_int64__in0"]
+    assert np.array_equal(port.reduce("prod", x, 1), gold["red_wrap_int64_prod__out"])
+    assert np.array_equal(port.reduce("sum", x), gold["red_wrap_int64_sum__out"])
+
+
+def test_elementwise_golden(port, gold):
+    for name, xs, ys in BCAST_CASES:
+        for dt in ("float32", "int32", "int64", "float64", "int16", "uint8", "int8", "bool", "bfloat16"):
+            a, b = gold[f"ew_{name}_{dt}__in0"], gold[f"ew_{name}_{dt}__in1"]
+            code = O.BFLOAT16 if dt == "bfloat16" else None
+            for op in ("add", "multiply"):
+                got = port.elementwise(op, a, b, code)
+                want = gold[f"ew_{name}_{dt}_{op}__out"]
+                assert np.array_equal(got.view(np.uint8), want.view(np.uint8)), (name, dt, op)
+    assert np.array_equal(port.f32_to_bf16(gold["bf16_round__in0"]), gold["bf16_round__out"])
+
+
+def test_argmax_golden(port, gold):
+    table = {"a3_0": 0, "a3_1": 1, "a3_m1": -1, "a_flat": None, "a1": 0, "a2_wide": 1}
+    for name, axis in table.items():
+        for dt in ("float32", "float64", "int32", "int64", "int16", "uint8"):
+            x = gold[f"arg_{name}_{dt}__in0"]
+            assert np.array_equal(port.argmax(x, axis, False, np.int64), gold[f"arg_{name}_{dt}_i64__out"])
+            got = port.argmax(x, axis, True, np.int32)
+            want = gold[f"arg_{name}_{dt}_i32_keep__out"]
+            assert got.dtype == np.int32 and got.shape == want.shape and np.array_equal(got, want)
+
+
+def test_softmax_golden(port, gold):
+    table = {"s2": -1, "s4_m1": -1, "s4_0": 0, "s4_1": 1, "s4_2": 2, "s5": 3, "s_2048": -1, "s_odd": -1, "s_clip": -1}
+    for name, axis in table.items():
+        for dt in ("float32", "float64"):
+            x = gold[f"sm_{name}_{dt}__in0"]
+            got = port.softmax(x, axis)
+            np.testing.assert_allclose(got, gold[f"sm_{name}_{dt}__out"], rtol=2e-6 if dt == "float32" else 1e-14)
+    # the -64 clip is visible: exp(-64)/sum, not exp(-1e4)/sum == 0
+    y = port.softmax(gold["sm_s_clip_float32__in0"], -1)
+    assert y[0, 3] > 0
+
+
+def test_layer_norm_golden(port, gold):
+    table = {"l4": 1, "l4_3": 3, "l2_8192": 1, "l2_odd": 1, "l3": 2}
+    for name, bna in table.items():
+        for dt in ("float32", "float64"):
+            key = f"ln_{name}_{dt}"
+            x, w, b = gold[key + "__in0"], gold[key + "__in1"], gold[key + "__in2"]
+            y, m, v = port.layer_norm(x, bna, w, b, 1e-5)
+            assert np.array_equal(m, gold[key + "_wb__out1"])
+            assert np.array_equal(v, gold[key + "_wb__out2"])
+            np.testing.assert_allclose(y, gold[key + "_wb__out0"], rtol=1e-6, atol=1e-7)
+            y0, _, _ = port.layer_norm(x, bna, None, None, 1e-5)
+            np.testing.assert_allclose(y0, gold[key + "_none__out0"], rtol=1e-6, atol=1e-7)
+
+
+# ---- live comparison with the compiled reference ----------------------------------------------
+def test_live_reduce(port, ref):
+    rng = np.random.default_rng(7)
+    x = rng.random((4096, 4096), dtype=np.float32)  # BASELINE config 1
+    assert np.array_equal(port.reduce("sum", x, -1), ref.reduce("sum", x, -1))
+    assert np.array_equal(port.reduce("sum", x), ref.reduce("sum", x))
+    assert np.array_equal(port.reduce("mean", x, 0), ref.reduce("mean", x, 0))
+    for n in (1, 7, 8, 9, 1000, 8191, 8192, 8193, 100003):
+        v = rng.standard_normal(n).astype(np.float32)
+        for op in ("sum", "mean", "max", "min"):
+            assert np.array_equal(port.reduce(op, v), ref.reduce(op, v)), (n, op)
+    xi = rng.integers(-2**62, 2**62, (64, 1031), dtype=np.int64)
+    for op in ("sum", "max", "min", "prod", "mean"):
+        for ax in (0, 1, None):
+            assert np.array_equal(port.reduce(op, xi, ax), ref.reduce(op, xi, ax))
+
+
+def test_live_elementwise_and_halves(port, ref):
+    rng = np.random.default_rng(8)
+    f = rng.standard_normal(100000).astype(np.float32) * 100
+    assert np.array_equal(port.f32_to_bf16(f), ref.f32_to_bf16(f))
+    a, b = port.f32_to_bf16(f[:4096 * 4].reshape(4, 4096)), port.f32_to_bf16(f[4096 * 4:4096 * 5])
+    for op in ("add", "multiply"):
+        assert np.array_equal(port.elementwise(op, a, b, O.BFLOAT16), ref.elementwise(op, a, b, O.BFLOAT16))
+    # fp16: the port rounds to nearest even (== numpy, == the GPU's __float2half_rn, == an F16C
+    # build).  Paddle's default CPU build has no -mf16c and falls back to a TRUNCATING software
+    # routine (phi/common/float16.h:121-138), so the compiled reference may sit 1 ulp below.
+    h = port.f32_to_fp16(f)
+    assert np.array_equal(h, f.astype(np.float16).view(np.uint16))
+    hr = ref.f32_to_fp16(f)
+    assert np.max(np.abs(h.astype(np.int32) - hr.astype(np.int32))) <= 1
+
+
+def test_live_softmax_layernorm_argmax(port, ref):
+    rng = np.random.default_rng(9)
+    s = (rng.standard_normal((32, 2048)) * 2).astype(np.float32)
+    np.testing.assert_allclose(port.softmax(s), ref.softmax(s), rtol=2e-6)
+    x = (rng.standard_normal((16, 8192)) * 3 + 1).astype(np.float32)
+    w, b = rng.random(8192, dtype=np.float32), rng.random(8192, dtype=np.float32)
+    for p_, r_ in zip(port.layer_norm(x, 1, w, b), ref.layer_norm(x, 1, w, b)):
+        np.testing.assert_allclose(p_, r_, rtol=1e-6, atol=1e-7)
+    t = rng.integers(0, 9, (7, 300, 5)).astype(np.float32)
+    for ax in (0, 1, 2, None):
+        assert np.array_equal(port.argmax(t, ax), ref.argmax(t, ax))
