@@ -1,0 +1,413 @@
+#!/usr/bin/env python
+"""bench.py — throughput of the B200 PHI hot path on BASELINE.json's configurations.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--no-ops]
+
+Headline workload (config.workload): BASELINE.json configs[1], `paddle.add` bf16
+[64,2048,4096] + [4096].  One step = one pass of that op over one batch of synthetic input.
+  value   : whole-job GB/s of ALGORITHMIC bytes (x read once + y once + out written once;
+            SURVEY.md §8d: 2,147,491,840 B per pass), inputs resident in HBM, CUDA-event timed,
+            max over ranks.  N > 1: every rank runs its own [64,2048,4096] shard of a
+            [64N,2048,4096] tensor (weak scaling, no data-path collective).
+  e2e     : the same metric through the public API with HOST (pinned) buffers: H2D of x and y,
+            the kernel, D2H of out, all inside the timed region.
+  roofline: dominant kernel (ew_inner_kernel) — algorithmic bytes / mean launch duration
+            against MEASURED_PEAKS.json's hbm_gbs.
+  cpu_baseline: the reference's own CPU kernel (oracle/_ref, compiled from Paddle's sources) on a
+            bounded sample of the same workload, 1 thread (how Paddle runs it).
+  ops     : the other BASELINE configs (C1, C2 int32, C3, C4, C5 shard) timed the same way —
+            context for the metric "reduce/broadcast/layer_norm HBM GB/s", not the headline.
+`--impl reference` times the reference CPU implementation (all host threads, bounded sample).
+Inputs are far larger than the 126 MB L2 (>= 1 GiB per operand), so no L2 flush is needed.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+C2_SHAPE = (64, 2048, 4096)
+C2_ROWS = C2_SHAPE[0] * C2_SHAPE[1]
+C2_COLS = C2_SHAPE[2]
+C2_BYTES_BF16 = 2 * (C2_ROWS * C2_COLS * 2) + C2_COLS * 2  # 2,147,491,840
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi during the timed region)
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.lines = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [s.strip() for s in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------
+# reference / cpu-baseline arm (the ONLY place bench.py executes anything under oracle/)
+# ---------------------------------------------------------------------------------------------
+def _ref_lib():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O
+    if O.have_ref():
+        return O.Oracle("ref"), "reference"
+    return O.Oracle("port"), "port"
+
+
+def _cpu_add_sample(oracle, rows, threads):
+    """Time add bf16 [rows,4096] + [4096] on the host with `threads` threads (disjoint row slabs;
+    ctypes releases the GIL, each call is the reference's single-threaded kernel).  Returns seconds."""
+    import numpy as np
+    import oracle_lib as O
+    rng = np.random.default_rng(2)
+    x = oracle.f32_to_bf16(rng.standard_normal((rows, C2_COLS)).astype(np.float32))
+    y = oracle.f32_to_bf16(rng.standard_normal((C2_COLS,)).astype(np.float32))
+    slabs = np.array_split(np.arange(rows), threads)
+
+    def work(idx):
+        oracle.elementwise("add", x[idx[0]:idx[-1] + 1], y, O.BFLOAT16)
+
+    def run():
+        ts = [threading.Thread(target=work, args=(s,)) for s in slabs if len(s)]
+        t0 = time.perf_counter()
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        return time.perf_counter() - t0
+
+    return run
+
+
+def cpu_baseline_obj(budget_s=12.0):
+    """1-thread reference CPU kernel on a bounded sample of the headline workload."""
+    oracle, kind = _ref_lib()
+    rows = 8192  # 1/16 of the workload: 64 MiB in, 64 MiB out
+    run = _cpu_add_sample(oracle, rows, 1)
+    run()  # warm-up
+    best, t_used = None, 0.0
+    while t_used < budget_s and (best is None or t_used < 3 * best + 1):
+        dt = run()
+        t_used += dt
+        best = dt if best is None else min(best, dt)
+        if t_used > budget_s:
+            break
+    nbytes = 2 * rows * C2_COLS * 2 + C2_COLS * 2
+    return {"value": round(nbytes / best / 1e9, 3), "unit": "GB/s", "cores": 1, "kind": kind,
+            "sample": f"add bf16 [{rows},{C2_COLS}]+[{C2_COLS}] = 1/16 of the workload, best of repeats within "
+                      f"{budget_s:.0f} s, phi::funcs::ElementwiseCompute<AddFunctor<bfloat16>> on 1 thread"}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    oracle, kind = _ref_lib()
+    cores = os.cpu_count() or 1
+    rows = 1024 * cores if cores <= 32 else 32768  # bounded sample per step
+    rows = min(rows, C2_ROWS)
+    run = _cpu_add_sample(oracle, rows, cores)
+    for _ in range(args.warmup):
+        run()
+    t = 0.0
+    for _ in range(args.steps):
+        t += run()
+    ms = t / args.steps * 1e3
+    nbytes = 2 * rows * C2_COLS * 2 + C2_COLS * 2
+    val = round(nbytes / (ms / 1e3) / 1e9, 3)
+    line = {
+        "impl": "reference", "metric": "broadcast add HBM GB/s (algorithmic bytes / time)", "value": val, "unit": "GB/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 3),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "paddle.add bf16 [64,2048,4096] + [4096] (BASELINE configs[1])",
+                   "sample": f"each step = add bf16 [{rows},{C2_COLS}]+[{C2_COLS}] on the host"},
+        "cpu_baseline": {"value": val, "unit": "GB/s", "cores": cores, "kind": kind,
+                         "sample": f"[{rows},{C2_COLS}] rows split over {cores} threads, each running the reference's "
+                                   "single-threaded CPU kernel"},
+        "e2e": {"value": val, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------
+def time_op(torch, fn, steps, warmup):
+    """Mean ms per call, CUDA events on the current (launching) stream, sync on both sides."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(steps):
+        fn()
+    e.record()
+    torch.cuda.synchronize()
+    return s.elapsed_time(e) / steps
+
+
+def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
+    """BASELINE configs other than the headline, each: algorithmic bytes, ms, GB/s, fraction."""
+    F = paddle.nn.functional
+    out = []
+
+    def rec(name, nbytes, fn, elems):
+        ms = time_op(torch, fn, steps, warmup)
+        gbs = nbytes / (ms / 1e3) / 1e9
+        out.append({"op": name, "algorithmic_bytes": nbytes, "ms": round(ms, 4), "GB/s": round(gbs, 1),
+                    "elements/s": round(elems / (ms / 1e3), 1), "frac_of_measured_peak": round(gbs / peak, 4),
+                    "frac_of_8TBps": round(gbs / 8000.0, 4)})
+        torch.cuda.empty_cache()
+
+    g = torch.Generator(device="cuda")
+    g.manual_seed(100 + rank)
+    # C1 sum fp32 [4096,4096] axis=-1 (67 MB: fits L2 — reported, not a steady-state number)
+    x = torch.rand((4096, 4096), device="cuda", generator=g)
+    rec("C1 sum fp32 [4096,4096] axis=-1 (L2-resident size)", 4096 * 4096 * 4 + 4096 * 4, lambda: paddle.sum(x, axis=-1), 4096 * 4096)
+    del x
+    # C2 int32
+    xi = torch.randint(-2**30, 2**30, C2_SHAPE, device="cuda", dtype=torch.int32, generator=g)
+    yi = torch.randint(-2**30, 2**30, (C2_COLS,), device="cuda", dtype=torch.int32, generator=g)
+    oi = torch.empty_like(xi)
+    from paddlepaddle_b200.ops import _elementwise
+    rec("C2 add int32 [64,2048,4096]+[4096]", 2 * C2_ROWS * C2_COLS * 4 + C2_COLS * 4,
+        lambda: _elementwise("pdb200_add", xi, yi, out=oi), C2_ROWS * C2_COLS)
+    del xi, yi, oi
+    # C3 layer_norm bf16 [65536,8192] (per rank: 65536/world rows when sharded — here the full config per GPU)
+    rows, D = 65536, 8192
+    xl = torch.randn((rows, D), device="cuda", generator=g).to(torch.bfloat16)
+    w = (torch.rand(D, device="cuda", generator=g) + 0.5).to(torch.bfloat16)
+    b = (torch.rand(D, device="cuda", generator=g) - 0.5).to(torch.bfloat16)
+    rec("C3 layer_norm bf16 [65536,8192]", 2 * rows * D * 2 + 2 * rows * 4 + 2 * D * 2, lambda: F.layer_norm(xl, [D], w, b), rows * D)
+    del xl
+    # C4 softmax [32,32,2048,2048] last axis, bf16 and fp32
+    for dt, nm, eb in ((torch.bfloat16, "bf16", 2), (torch.float32, "fp32", 4)):
+        n = 32 * 32 * 2048 * 2048
+        xs = torch.empty((32, 32, 2048, 2048), device="cuda", dtype=dt)
+        xs.view(-1)[:] = 0
+        chunk = 1 << 28
+        for i in range(0, n, chunk):
+            xs.view(-1)[i:i + chunk] = (torch.randn(chunk, device="cuda", generator=g) * 2).to(dt)
+        rec(f"C4 softmax {nm} [32,32,2048,2048] axis=-1", 2 * n * eb, lambda: F.softmax(xs, axis=-1), n)
+        del xs
+    # C5: one rank's shard of the 2^34-element full reduce (2^31 elements), int64 and fp32, sum and max;
+    # with world > 1 the scalar partials are finished by an NCCL AllReduce timed separately.
+    n = 1 << 31
+    for dt, nm, eb in ((torch.int64, "int64", 8), (torch.float32, "fp32", 4)):
+        if dt == torch.int64:
+            xr = torch.randint(-2**40, 2**40, (n,), device="cuda", dtype=dt, generator=g)
+        else:
+            xr = torch.rand((n,), device="cuda", generator=g) * 2 - 1
+        for opn, fn in (("sum", paddle.sum), ("max", paddle.max)):
+            rec(f"C5 {opn} {nm} 2^31-element shard (1/8 of 2^34)", n * eb + eb, lambda: fn(xr), n)
+            if world > 1:
+                part = fn(xr)
+                op = dist.ReduceOp.SUM if opn == "sum" else dist.ReduceOp.MAX
+                ms = time_op(torch, lambda: dist.all_reduce(part, op=op), 20, 5)
+                out[-1]["allreduce_us"] = round(ms * 1e3, 2)
+        del xr
+    return out
+
+
+def run_gpu_arm(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        print(json.dumps({"error": "no CUDA device: paddlepaddle_b200 has no CPU path"}))
+        return 2
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import paddlepaddle_b200 as paddle
+    from paddlepaddle_b200 import _lib
+    from paddlepaddle_b200.ops import _elementwise
+    lib = _lib.load()  # raises if the CUDA extension is missing: no fallback
+    peak, peak_src = load_peaks()
+
+    g = torch.Generator(device="cuda")
+    g.manual_seed(2 + rank)
+    x = torch.randn(C2_SHAPE, device="cuda", generator=g).to(torch.bfloat16)
+    y = torch.randn((C2_COLS,), device="cuda", generator=g).to(torch.bfloat16)
+    out = torch.empty_like(x)
+    step = lambda: _elementwise("pdb200_add", x, y, out=out)  # noqa: E731  paddle.add into a preallocated out
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = lib.pdb200_launch_count()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(args.steps):
+        step()
+    e.record()
+    barrier()
+    launches = lib.pdb200_launch_count() - launches0
+    ms_total = torch.tensor([s.elapsed_time(e)], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
+    clocks = sampler.stop() if rank == 0 else None
+    ms_step = float(ms_total.item()) / args.steps
+    value = C2_BYTES_BF16 * world / (ms_step / 1e3) / 1e9
+
+    # dominant kernel, timed launch by launch (events on the launching stream)
+    per = []
+    for _ in range(min(args.steps, 20)):
+        a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        step()
+        b_.record()
+        b_.synchronize()
+        per.append(a.elapsed_time(b_))
+    kern_ms = sum(per) / len(per)
+    achieved = C2_BYTES_BF16 / (kern_ms / 1e3) / 1e9
+
+    # end to end through the public API with HOST buffers
+    hx = torch.empty(C2_SHAPE, dtype=torch.bfloat16, pin_memory=True)
+    hy = torch.empty((C2_COLS,), dtype=torch.bfloat16, pin_memory=True)
+    ho = torch.empty(C2_SHAPE, dtype=torch.bfloat16, pin_memory=True)
+    hx.copy_(x)
+    hy.copy_(y)
+    from paddlepaddle_b200 import host as phost
+
+    def e2e_step():
+        phost.add(hx, hy, out=ho)
+
+    e2e_steps = max(2, min(args.steps, 5))
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_ms = torch.tensor([(time.perf_counter() - t0) * 1e3 / e2e_steps], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+    e2e_val = C2_BYTES_BF16 * world / (float(e2e_ms.item()) / 1e3) / 1e9
+    del hx, ho
+
+    ops = None
+    if not args.no_ops:
+        del x, out
+        torch.cuda.empty_cache()
+        ops = other_configs(torch, paddle, peak, max(3, min(args.steps, 10)), 3, world, rank, dist)
+
+    if rank == 0:
+        cpu = cpu_baseline_obj() if world == 1 else None
+        line = {
+            "metric": "broadcast add HBM GB/s (algorithmic bytes / time)", "value": round(value, 1), "unit": "GB/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms_step, 4),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "paddle.add bf16 [64,2048,4096] + [4096] (BASELINE configs[1]); per-GPU shard of "
+                                   f"a [{64 * world},2048,4096] tensor", "parallelism": f"rows sharded over {world} GPU(s), no collective",
+                       "l2": "operands 1 GiB each >> 126 MB L2, no flush needed", "algorithmic_bytes_per_step_per_gpu": C2_BYTES_BF16,
+                       "elements_per_s": round(C2_ROWS * C2_COLS * world / (ms_step / 1e3), 1),
+                       "frac_of_8TBps_per_gpu": round(value / world / 8000.0, 4)},
+            "roofline": {"bound": "hbm", "kernel": "ew_inner_kernel<bf16,AddOp>", "achieved": round(achieved, 1), "peak": peak,
+                         "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                         "kernel_ms": round(kern_ms, 4)},
+            "e2e": {"value": round(e2e_val, 2), "unit": "GB/s", "h2d_bytes_per_step": C2_ROWS * C2_COLS * 2 + C2_COLS * 2,
+                    "d2h_bytes_per_step": C2_ROWS * C2_COLS * 2, "ms_per_step": round(float(e2e_ms.item()), 3),
+                    "path": "paddlepaddle_b200.host.add: pinned host -> H2D -> pdb200_add -> D2H, chunk-pipelined"},
+            "gpu_launches": int(launches), "clocks": clocks,
+        }
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        if ops is not None:
+            line["ops"] = ops
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-ops", action="store_true", help="skip the per-config table (ops)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -8,7 +8,7 @@ The compute lives in libpdb200.so (hand-written CUDA, C-ABI in include/pdb200.h)
 this package does not need a GPU; calling an op without the built library or without a CUDA
 device raises — there is no fallback.
 """
-from . import nn  # noqa: F401
+from . import distributed, nn  # noqa: F401
 from .ops import (add, add_, argmax, max, mean, min, multiply, multiply_, prod, sum)  # noqa: F401,A004
 
 __all__ = ["add", "add_", "multiply", "multiply_", "sum", "mean", "max", "min", "prod", "argmax", "nn"]

@@ -11,6 +11,7 @@ dtype; `dev_ctx.Alloc`; scratch through phi::Empty) is done here in Python, then
 through the C-ABI (include/pdb200.h) with raw device pointers.  torch is used ONLY as the
 owner of device memory and of the CUDA stream; no torch operator computes anything here.
 """
+import builtins
 import ctypes
 
 import torch
@@ -75,7 +76,7 @@ def _workspace(nbytes, device):
     key = (device.index, torch.cuda.current_stream().cuda_stream)
     buf = _workspaces.get(key)
     if buf is None or buf.numel() < nbytes:
-        buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        buf = torch.empty(builtins.max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
         _workspaces[key] = buf
     return buf
 

@@ -1,0 +1,54 @@
+"""Run ONE BASELINE configuration a few times — the short command ncu wraps (profiles/README.md).
+usage: python profiles/run_case.py <case> [iters]
+cases: add_bf16 add_int32 ln_bf16 softmax_fp32 softmax_bf16 sum_c1 sum_full_fp32 sum_full_int64 max_full_fp32
+Smaller-than-BASELINE tensors (still >> L2) keep ncu's ~40 replays per launch short."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+import paddlepaddle_b200 as paddle
+
+F = paddle.nn.functional
+case = sys.argv[1]
+iters = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+g = torch.Generator(device="cuda")
+g.manual_seed(0)
+if case == "add_bf16":
+    x = torch.randn((64, 2048, 4096), device="cuda", generator=g).to(torch.bfloat16)
+    y = torch.randn((4096,), device="cuda", generator=g).to(torch.bfloat16)
+    fn = lambda: paddle.add(x, y)
+elif case == "add_int32":
+    x = torch.randint(-2**30, 2**30, (64, 2048, 4096), device="cuda", dtype=torch.int32, generator=g)
+    y = torch.randint(-2**30, 2**30, (4096,), device="cuda", dtype=torch.int32, generator=g)
+    fn = lambda: paddle.add(x, y)
+elif case == "ln_bf16":
+    x = torch.randn((65536, 8192), device="cuda", generator=g).to(torch.bfloat16)
+    w = torch.rand(8192, device="cuda", generator=g).to(torch.bfloat16)
+    b = torch.rand(8192, device="cuda", generator=g).to(torch.bfloat16)
+    fn = lambda: F.layer_norm(x, [8192], w, b)
+elif case in ("softmax_fp32", "softmax_bf16"):
+    dt = torch.float32 if case.endswith("fp32") else torch.bfloat16
+    x = (torch.randn((8, 32, 2048, 2048), device="cuda", generator=g) * 2).to(dt)  # 1/4 of config 4
+    fn = lambda: F.softmax(x, axis=-1)
+elif case == "sum_c1":
+    x = torch.rand((4096, 4096), device="cuda", generator=g)
+    fn = lambda: paddle.sum(x, axis=-1)
+elif case in ("sum_full_fp32", "max_full_fp32"):
+    x = torch.rand((1 << 30,), device="cuda", generator=g)
+    fn = (lambda: paddle.sum(x)) if case.startswith("sum") else (lambda: paddle.max(x))
+elif case == "sum_full_int64":
+    x = torch.randint(-2**40, 2**40, (1 << 29,), device="cuda", dtype=torch.int64, generator=g)
+    fn = lambda: paddle.sum(x)
+else:
+    raise SystemExit(f"unknown case {case}")
+torch.cuda.synchronize()
+s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+fn()
+s.record()
+for _ in range(iters):
+    fn()
+e.record()
+torch.cuda.synchronize()
+print(f"{case}: {s.elapsed_time(e) / iters:.4f} ms/iter")

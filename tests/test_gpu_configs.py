@@ -73,9 +73,10 @@ def test_c3_layer_norm_bf16_full(port):
         wf = port.bf16_to_f32(to_np(wp)) if wp.dtype == torch.bfloat16 else to_np(wp)
         bf = port.bf16_to_f32(to_np(bp)) if bp.dtype == torch.bfloat16 else to_np(bp)
         oy, om, ov = port.layer_norm(xs, 1, wf, bf, 1e-5)
-        assert_half_close(to_np(y[idx]), port.f32_to_bf16(oy), 1, "config 3 sampled rows")
-        np.testing.assert_allclose(to_np(m[idx]), om, rtol=1e-5, atol=1e-6)
-        np.testing.assert_allclose(to_np(v[idx]), ov, rtol=1e-5)
+        # atol: see tests/test_gpu_parity.py::test_layer_norm_routes (the CPU kernel's sequential sums)
+        assert_half_close(to_np(y[idx]), port.f32_to_bf16(oy), 1, "config 3 sampled rows", atol=2e-5)
+        np.testing.assert_allclose(to_np(m[idx]), om, rtol=1e-5, atol=1e-5 * float(np.abs(xs).max()))
+        np.testing.assert_allclose(to_np(v[idx]), ov, rtol=2e-5)
     # property over all rows: without scale/bias each row has mean ~0 and variance ~1
     y0 = F.layer_norm(x, [D])
     mu = paddle.mean(y0, axis=-1)

@@ -22,6 +22,7 @@ from golden.make_golden import BCAST_CASES, REDUCE_CASES  # noqa: E402
 F = paddle.nn.functional
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "phi_cpu_golden.npz")
 FP32_RTOL = 1e-5
+LN_ATOL = 1e-5  # 1e-5 of the unit scale of a normalised row (see test_layer_norm_routes)
 
 
 @pytest.fixture(scope="module")
@@ -114,7 +115,9 @@ def _check_reduce(op, got, want, dt):
     if dt.startswith("int") or op in ("max", "min"):
         assert np.array_equal(got, want), (op, dt)
     else:
-        np.testing.assert_allclose(got, want, rtol=FP32_RTOL if dt == "float32" else 1e-12)
+        # atol: products that underflow into the denormal range lose bits in an order-dependent way
+        np.testing.assert_allclose(got, want, rtol=FP32_RTOL if dt == "float32" else 1e-12,
+                                   atol=1e-36 if dt == "float32" else 1e-300)
 
 
 def test_reduce_golden(gold):
@@ -184,9 +187,9 @@ def test_reduce_half_types(port, half):
             want_f = port.reduce(op, xf, axis)
             got = to_np(fn(tx, axis=axis))
             if op in ("max", "min"):
-                assert np.array_equal(got, conv(want_f))
+                assert np.array_equal(got.reshape(-1), conv(want_f).reshape(-1))
             else:
-                assert_half_close(got, conv(want_f), 1, f"{op} {shape}")
+                assert_half_close(got, conv(want_f), 1, f"{op} {shape}", kind=half)
         # sum with fp32 output keeps full precision (kps/reduce_kernel.cu:251-265)
         got32 = to_np(paddle.sum(tx, axis=axis, dtype="float32"))
         want32 = port.reduce("sum", xf, axis)
@@ -261,7 +264,7 @@ def test_softmax_routes(port, shape, axis):
         bits = conv(x)
         want_h = conv(port.softmax(back(bits), axis))
         got_h = to_np(F.softmax(to_dev(bits, half), axis=axis))
-        assert_half_close(got_h, want_h, 1, f"softmax {half} {shape}")
+        assert_half_close(got_h, want_h, 1, f"softmax {half} {shape}", kind=half)
 
 
 def test_softmax_edge_cases(port):
@@ -287,7 +290,7 @@ def test_layer_norm_golden(gold):
             shape = list(x.shape[bna:])
             tw, tb = to_dev(w).view(shape), to_dev(b).view(shape)
             y, m, v = F.layer_norm(to_dev(x), shape, tw, tb, 1e-5, return_stats=True)
-            tol = dict(rtol=FP32_RTOL, atol=1e-6) if dt == "float32" else dict(rtol=1e-12, atol=1e-13)
+            tol = dict(rtol=FP32_RTOL, atol=LN_ATOL) if dt == "float32" else dict(rtol=1e-12, atol=1e-13)
             np.testing.assert_allclose(to_np(y), gold[key + "_wb__out0"], **tol)
             np.testing.assert_allclose(to_np(m), gold[key + "_wb__out1"], **tol)
             np.testing.assert_allclose(to_np(v), gold[key + "_wb__out2"], **tol)
@@ -303,24 +306,32 @@ def test_layer_norm_routes(port, rows, D):
     w, b = rng.uniform(0.5, 1.5, D).astype(np.float32), rng.uniform(-0.5, 0.5, D).astype(np.float32)
     wy, wm, wv = port.layer_norm(x, 1, w, b, 1e-5)
     y, m, v = F.layer_norm(to_dev(x), [D], to_dev(w), to_dev(b), 1e-5, return_stats=True)
-    np.testing.assert_allclose(to_np(y), wy, rtol=FP32_RTOL, atol=2e-6)
-    np.testing.assert_allclose(to_np(m), wm, rtol=FP32_RTOL, atol=1e-6)
-    np.testing.assert_allclose(to_np(v), wv, rtol=FP32_RTOL)
+    # The CPU kernel sums each row sequentially in fp32 (RowwiseMean, math_function_impl.h:180-189):
+    # its own mean carries ~sqrt(D)*ulp(|running sum|) of noise, which the tree-summing GPU kernel does
+    # not reproduce.  So: 1e-5 relative, with the absolute floor set by the row scale (max|x| for
+    # mean, 1 for the normalised y), and the GPU must be at least as close to float64 as that.
+    xs = float(np.abs(x).max())
+    np.testing.assert_allclose(to_np(y), wy, rtol=FP32_RTOL, atol=LN_ATOL)
+    np.testing.assert_allclose(to_np(m), wm, rtol=FP32_RTOL, atol=FP32_RTOL * xs)
+    np.testing.assert_allclose(to_np(v), wv, rtol=2 * FP32_RTOL)
+    x64 = x.astype(np.float64)
+    np.testing.assert_allclose(to_np(m), x64.mean(1), rtol=FP32_RTOL, atol=1e-6 * xs)
+    np.testing.assert_allclose(to_np(v), x64.var(1), rtol=FP32_RTOL)
     # only scale / only bias
-    np.testing.assert_allclose(to_np(F.layer_norm(to_dev(x), [D], to_dev(w), None)), port.layer_norm(x, 1, w, None)[0], rtol=FP32_RTOL, atol=2e-6)
-    np.testing.assert_allclose(to_np(F.layer_norm(to_dev(x), [D], None, to_dev(b))), port.layer_norm(x, 1, None, b)[0], rtol=FP32_RTOL, atol=2e-6)
+    np.testing.assert_allclose(to_np(F.layer_norm(to_dev(x), [D], to_dev(w), None)), port.layer_norm(x, 1, w, None)[0], rtol=FP32_RTOL, atol=LN_ATOL)
+    np.testing.assert_allclose(to_np(F.layer_norm(to_dev(x), [D], None, to_dev(b))), port.layer_norm(x, 1, None, b)[0], rtol=FP32_RTOL, atol=LN_ATOL)
     # bf16 / fp16 input, params in the same dtype and in float32: <= 1 ulp of the rounded fp32 oracle
     for half, conv, back in (("bf16", port.f32_to_bf16, port.bf16_to_f32), ("fp16", port.f32_to_fp16, port.fp16_to_f32)):
         xb, wb_, bb = conv(x), conv(w), conv(b)
         oy, om, ov = port.layer_norm(back(xb), 1, back(wb_), back(bb), 1e-5)
         gy, gm, gv = F.layer_norm(to_dev(xb, half), [D], to_dev(wb_, half), to_dev(bb, half), 1e-5, return_stats=True)
         assert gm.dtype == torch.float32
-        assert_half_close(to_np(gy), conv(oy), 1, f"ln {half} same-dtype params {rows}x{D}")
-        np.testing.assert_allclose(to_np(gm), om, rtol=FP32_RTOL, atol=1e-6)
-        np.testing.assert_allclose(to_np(gv), ov, rtol=FP32_RTOL)
+        assert_half_close(to_np(gy), conv(oy), 1, f"ln {half} same-dtype params {rows}x{D}", kind=half, atol=2 * LN_ATOL)
+        np.testing.assert_allclose(to_np(gm), om, rtol=FP32_RTOL, atol=FP32_RTOL * xs)
+        np.testing.assert_allclose(to_np(gv), ov, rtol=2 * FP32_RTOL)
         oy2, _, _ = port.layer_norm(back(xb), 1, w, b, 1e-5)
         gy2 = F.layer_norm(to_dev(xb, half), [D], to_dev(w), to_dev(b), 1e-5)
-        assert_half_close(to_np(gy2), conv(oy2), 1, f"ln {half} fp32 params {rows}x{D}")
+        assert_half_close(to_np(gy2), conv(oy2), 1, f"ln {half} fp32 params {rows}x{D}", kind=half, atol=2 * LN_ATOL)
 
 
 def test_layer_norm_errors():
