@@ -17,7 +17,10 @@
 //   rows_reg   : G lanes (<= 32) per row, C <= 8 16-byte chunks per lane     (D <= 256*V)
 //   block_reg  : one CTA (128..1024 threads) per row, C <= 4 chunks a thread (D <= 4096*V)
 //   block_strm : longer rows — three streaming sweeps
+//   pipe       : the fast path for many rows (config 3): persistent CTAs fed by the TMA row
+//                pipeline of rowpipe.cuh; scale/bias stay in registers across rows
 #include "common.cuh"
+#include "rowpipe.cuh"
 #include "shape.h"
 
 namespace pdb200 {
@@ -213,6 +216,132 @@ __global__ void __launch_bounds__(1024) ln_block_reg_kernel(const T* __restrict_
   }
 }
 
+// ---- pipe: persistent CTAs, rows staged in shared memory by cp.async.bulk -------------------
+// blockDim.x threads per row, C chunks of V elements per thread (chunk c of thread t covers
+// elements (c*blockDim.x + t)*V ..), STAGES rows in flight per CTA.  x is read ONCE from HBM by the
+// copy engine; scale/bias (same dtype as x) are loaded once per CTA and kept packed in registers.
+template <typename T, typename P, int C>
+__global__ void __launch_bounds__(512) ln_pipe_kernel(const T* __restrict__ x, const P* __restrict__ scale,
+                                                      const P* __restrict__ bias, T* __restrict__ y,
+                                                      typename AccType<T>::type* mean_out,
+                                                      typename AccType<T>::type* var_out, int64_t rows, int D,
+                                                      int stages, typename AccType<T>::type eps, double inv_d) {
+  using U = typename AccType<T>::type;
+  constexpr int V = Vec<T>::N;
+  constexpr bool kParamsInRegs = sizeof(P) == sizeof(T);
+  extern __shared__ __align__(128) unsigned char ring_raw[];
+  T* ring = reinterpret_cast<T*>(ring_raw);
+  __shared__ uint64_t full[8];
+  __shared__ U red[33];
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const uint32_t row_bytes = (uint32_t)D * sizeof(T);
+  const int64_t row_step = gridDim.x;
+  if (tid == 0) {
+    for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  if (tid == 0) {
+    for (int s = 0; s < stages; ++s) {
+      const int64_t r = blockIdx.x + s * row_step;
+      if (r < rows) {
+        mbar_expect_tx(&full[s], row_bytes);
+        bulk_load_row(ring + (size_t)s * D, x + r * D, row_bytes, &full[s]);
+      }
+    }
+  }
+  // scale / bias for this thread's columns: constant across rows
+  Vec<P> wreg[kParamsInRegs ? C : 1], breg[kParamsInRegs ? C : 1];
+  if constexpr (kParamsInRegs) {
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + tid) * V;
+      if (off < D) {
+        if (scale) wreg[c] = ld_cached(scale + off);
+        if (bias) breg[c] = ld_cached(bias + off);
+      }
+    }
+  }
+  int s = 0;
+  uint32_t phase = 0;
+  for (int64_t row = blockIdx.x; row < rows; row += row_step) {
+    mbar_wait(&full[s], phase);
+    const T* st = ring + (size_t)s * D;
+    Vec<T> raw[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + tid) * V;
+      if (off < D) raw[c] = lds_vec(st + off);
+    }
+    U e[C * V];
+    U sum = U(0);
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + tid) * V;
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        e[c * V + k] = off < D ? cvt<U>(raw[c].v[k]) : U(0);
+        sum += e[c * V + k];
+      }
+    }
+    sum = block_reduce(sum, AddU<U>(), U(0), red);  // its barriers also mean: every thread has read stage s
+    if (tid == 0) {
+      const int64_t nrow = row + (int64_t)stages * row_step;
+      if (nrow < rows) {
+        fence_proxy_async_smem();
+        mbar_expect_tx(&full[s], row_bytes);
+        bulk_load_row(ring + (size_t)s * D, x + nrow * D, row_bytes, &full[s]);
+      }
+    }
+    const U mean = mean_of<U>(sum, inv_d);
+    U sq = U(0);
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + tid) * V;
+      if (off < D) {
+#pragma unroll
+        for (int k = 0; k < V; ++k) {
+          const U d = e[c * V + k] - mean;
+          e[c * V + k] = d;  // keep the centred value: the normalisation needs exactly this
+          sq += d * d;
+        }
+      }
+    }
+    sq = block_reduce(sq, AddU<U>(), U(0), red);
+    const U var = mean_of<U>(sq, inv_d);
+    const U rstd = rsqrt_exact<U>(var + eps);
+    if (tid == 0) {
+      if (mean_out) mean_out[row] = mean;
+      if (var_out) var_out[row] = var;
+    }
+    T* dst = y + row * D;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + tid) * V;
+      if (off < D) {
+        if constexpr (kParamsInRegs) {
+          Vec<T> ov;
+#pragma unroll
+          for (int k = 0; k < V; ++k) {
+            U o = mul_rn<U>(e[c * V + k], rstd);
+            if (scale) o = mul_rn<U>(o, cvt<U>(wreg[c].v[k]));
+            if (bias) o = add_rn<U>(o, cvt<U>(breg[c].v[k]));
+            ov.v[k] = cvt<T>(o);
+          }
+          st_stream(dst + off, ov);
+        } else {
+          // e[] already holds x - mean: hand ln_store_chunk a zero mean
+          ln_store_chunk<T, P, U, V, true>(&e[c * V], U(0), rstd, scale, bias, dst, off);
+        }
+      }
+    }
+    if (++s == stages) {
+      s = 0;
+      phase ^= 1;
+    }
+  }
+}
+
 // ---- block_strm: rows too long for registers ------------------------------------------------
 template <typename T, typename P>
 __global__ void __launch_bounds__(1024) ln_block_stream_kernel(const T* x, const P* __restrict__ scale,
@@ -269,6 +398,27 @@ int layer_norm_typed(const T* x, const P* scale, const P* bias, T* y, void* mean
     if (vec) KERNEL<T, P, CC, true> __VA_ARGS__;                         \
     else KERNEL<T, P, CC, false> __VA_ARGS__;                            \
     break;
+  // Fast path: many rows, 16-byte-multiple rows that fit <= 512 threads x 4 chunks -> TMA row pipeline.
+  if (vec && sizeof(T) <= 4 && nchunk >= 64 && nchunk <= 512 * 4 && rows >= 4 * (int64_t)sm_count()) {
+    int C = nchunk >= 512 ? 4 : (nchunk >= 256 ? 2 : 1);  // CTAs stay >= 128 threads wide
+    int threads = (int)((nchunk + C - 1) / C);
+    threads = (threads + 31) / 32 * 32;
+    const size_t row_bytes = (size_t)D * sizeof(T);
+    auto launch = [&](auto kern) -> int {
+      int per_sm = 0, stages = 0;
+      size_t smem = 0;
+      if (!pipe_geometry(kern, threads, row_bytes, &per_sm, &stages, &smem)) return -1;
+      int64_t grid = (int64_t)per_sm * sm_count();
+      if (grid > rows) grid = rows;
+      kern<<<(unsigned)grid, threads, smem, st>>>(x, scale, bias, y, m, v, rows, (int)D, stages, eps, inv_d);
+      return after_launch("ln_pipe");
+    };
+    int rc = -1;
+    if (C == 4) rc = launch(ln_pipe_kernel<T, P, 4>);
+    else if (C == 2) rc = launch(ln_pipe_kernel<T, P, 2>);
+    else rc = launch(ln_pipe_kernel<T, P, 1>);
+    if (rc >= 0) return rc;  // rc < 0: the pipeline does not fit this device; fall through
+  }
   if (nchunk <= 32 * 8) {
     int G = 1;
     while (G < 32 && G < nchunk) G <<= 1;

@@ -19,7 +19,11 @@
 //        does from 100000 up).
 //   inner  > 1                      -> cols       : threads along `inner` (coalesced),
 //        sweeps over `dim`; later sweeps hit L2.
+//   inner == 1, many rows (config 4) -> pipe      : persistent CTAs fed by the TMA row pipeline of
+//        rowpipe.cuh (one cp.async.bulk per row into a shared-memory ring), 16 values per thread,
+//        exp through ex2.approx on the pre-scaled difference.
 #include "common.cuh"
+#include "rowpipe.cuh"
 #include "shape.h"
 
 namespace pdb200 {
@@ -106,6 +110,111 @@ __global__ void __launch_bounds__(256) softmax_rows_reg_kernel(const T* __restri
       } else {
         dst[off] = cvt<T>(e[c] * inv);
       }
+    }
+  }
+}
+
+// exp(max(x - m, -64)) as 2^(x*log2e - m*log2e) with the clamp applied in the log2 domain.
+// One FFMA + FMNMX + MUFU.EX2.  The rounding of m*log2e is a common factor of the whole row and
+// cancels in the normalisation; per element the error is 0.5 ulp of the exponent argument plus
+// ex2.approx's 2^-22: <= ~2e-6 relative for |x - m| <= 64, inside the 1e-5 bar.
+__device__ __forceinline__ float fast_clipped_exp(float x, float neg_m_log2e) {
+  constexpr float kLog2e = 1.4426950408889634f;
+  float t = fmaf(x, kLog2e, neg_m_log2e);
+  t = fmaxf(t, -64.0f * kLog2e);
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(t));
+  return r;
+}
+
+// ---- pipe: persistent CTAs, rows staged in shared memory by cp.async.bulk -------------------
+// blockDim.x threads per row, C chunks of V elements per thread.  T is float, bf16 or fp16.
+template <typename T, int C>
+__global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__ x, T* __restrict__ y,
+                                                           int64_t rows, int dim, int stages) {
+  constexpr int V = Vec<T>::N;
+  extern __shared__ __align__(128) unsigned char ring_raw[];
+  T* ring = reinterpret_cast<T*>(ring_raw);
+  __shared__ uint64_t full[8];
+  __shared__ float red[33];
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const uint32_t row_bytes = (uint32_t)dim * sizeof(T);
+  const int64_t row_step = gridDim.x;
+  if (tid == 0) {
+    for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  if (tid == 0) {
+    for (int s = 0; s < stages; ++s) {
+      const int64_t r = blockIdx.x + s * row_step;
+      if (r < rows) {
+        mbar_expect_tx(&full[s], row_bytes);
+        bulk_load_row(ring + (size_t)s * dim, x + r * dim, row_bytes, &full[s]);
+      }
+    }
+  }
+  int s = 0;
+  uint32_t phase = 0;
+  for (int64_t row = blockIdx.x; row < rows; row += row_step) {
+    mbar_wait(&full[s], phase);
+    const T* st = ring + (size_t)s * dim;
+    Vec<T> raw[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + tid) * V;
+      if (off < dim) raw[c] = lds_vec(st + off);
+    }
+    float e[C * V];
+    float m = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + tid) * V;
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        e[c * V + k] = off < dim ? cvt<float>(raw[c].v[k]) : -INFINITY;
+        m = fmaxf(m, e[c * V + k]);
+      }
+    }
+    m = block_reduce(m, MaxF<float>(), -INFINITY, red);  // barriers inside: stage s fully read
+    if (tid == 0) {
+      const int64_t nrow = row + (int64_t)stages * row_step;
+      if (nrow < rows) {
+        fence_proxy_async_smem();
+        mbar_expect_tx(&full[s], row_bytes);
+        bulk_load_row(ring + (size_t)s * dim, x + nrow * dim, row_bytes, &full[s]);
+      }
+    }
+    const float nml = -m * 1.4426950408889634f;
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < C * V; ++i) {
+      e[i] = fast_clipped_exp(e[i], nml);  // padding lanes: exp(-inf) clamps to 2^-92, excluded below
+    }
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + tid) * V;
+      if (off < dim) {
+#pragma unroll
+        for (int k = 0; k < V; ++k) sum += e[c * V + k];
+      }
+    }
+    sum = block_reduce(sum, AddF<float>(), 0.f, red);
+    const float inv = 1.0f / sum;
+    T* dst = y + row * dim;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + tid) * V;
+      if (off < dim) {
+        Vec<T> o;
+#pragma unroll
+        for (int k = 0; k < V; ++k) o.v[k] = cvt<T>(e[c * V + k] * inv);
+        st_stream(dst + off, o);
+      }
+    }
+    if (++s == stages) {
+      s = 0;
+      phase ^= 1;
     }
   }
 }
@@ -222,6 +331,32 @@ int launch_rows_reg(const T* x, T* y, int64_t outer, int dim, int G, int C, cuda
   return after_launch("softmax_rows_reg");
 }
 
+// TMA row pipeline (float / bf16 / fp16 rows of 64..2048 16-byte chunks, many rows).
+template <typename T>
+int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, cudaStream_t st) {
+  constexpr int VN = Vec<T>::N;
+  const int64_t nchunk = dim / VN;
+  // keep CTAs >= 128 threads wide: 4 chunks a thread from 512 chunks up, 2 from 256
+  const int C = nchunk >= 512 ? 4 : (nchunk >= 256 ? 2 : 1);
+  int threads = (int)((nchunk + C - 1) / C);
+  threads = (threads + 31) / 32 * 32;
+  const size_t row_bytes = (size_t)dim * sizeof(T);
+  auto launch = [&](auto kern) -> int {
+    int per_sm = 0, stages = 0;
+    size_t smem = 0;
+    if (!pipe_geometry(kern, threads, row_bytes, &per_sm, &stages, &smem)) return -1;
+    int64_t grid = (int64_t)per_sm * sm_count();
+    if (grid > outer) grid = outer;
+    kern<<<(unsigned)grid, threads, smem, st>>>(x, y, outer, (int)dim, stages);
+    return after_launch("softmax_pipe");
+  };
+  if (C == 4) return launch(softmax_pipe_kernel<T, 4>);
+  if (C == 2) return launch(softmax_pipe_kernel<T, 2>);
+  return launch(softmax_pipe_kernel<T, 1>);
+}
+template <>
+int try_softmax_pipe<double>(const double*, double*, int64_t, int64_t, cudaStream_t) { return -1; }
+
 template <typename T>
 int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, cudaStream_t st) {
   using A = typename AccType<T>::type;
@@ -230,6 +365,10 @@ int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, c
     const bool vec = (dim % VN == 0) && is_aligned16(x) && is_aligned16(y);
     const int V = vec ? VN : 1;
     const int64_t nchunk = dim / V;
+    if (vec && nchunk >= 64 && nchunk <= 512 * 4 && outer >= 4 * (int64_t)sm_count()) {
+      const int rc = try_softmax_pipe<T>(x, y, outer, dim, st);
+      if (rc >= 0) return rc;  // < 0: the pipeline does not fit; use the register route
+    }
     if (nchunk <= 32 * 16) {
       int G = 1;
       while (G < 32 && G < nchunk) G <<= 1;

@@ -311,9 +311,11 @@ def test_layer_norm_routes(port, rows, D):
     # not reproduce.  So: 1e-5 relative, with the absolute floor set by the row scale (max|x| for
     # mean, 1 for the normalised y), and the GPU must be at least as close to float64 as that.
     xs = float(np.abs(x).max())
+    # relative noise of the CPU kernel's sequential fp32 row sums grows like sqrt(D) * 2^-24
+    stat_rtol = max(2 * FP32_RTOL, 8 * np.sqrt(D) * 2.0 ** -24)
     np.testing.assert_allclose(to_np(y), wy, rtol=FP32_RTOL, atol=LN_ATOL)
     np.testing.assert_allclose(to_np(m), wm, rtol=FP32_RTOL, atol=FP32_RTOL * xs)
-    np.testing.assert_allclose(to_np(v), wv, rtol=2 * FP32_RTOL)
+    np.testing.assert_allclose(to_np(v), wv, rtol=stat_rtol)
     x64 = x.astype(np.float64)
     np.testing.assert_allclose(to_np(m), x64.mean(1), rtol=FP32_RTOL, atol=1e-6 * xs)
     np.testing.assert_allclose(to_np(v), x64.var(1), rtol=FP32_RTOL)
@@ -328,7 +330,7 @@ def test_layer_norm_routes(port, rows, D):
         assert gm.dtype == torch.float32
         assert_half_close(to_np(gy), conv(oy), 1, f"ln {half} same-dtype params {rows}x{D}", kind=half, atol=2 * LN_ATOL)
         np.testing.assert_allclose(to_np(gm), om, rtol=FP32_RTOL, atol=FP32_RTOL * xs)
-        np.testing.assert_allclose(to_np(gv), ov, rtol=2 * FP32_RTOL)
+        np.testing.assert_allclose(to_np(gv), ov, rtol=stat_rtol)
         oy2, _, _ = port.layer_norm(back(xb), 1, w, b, 1e-5)
         gy2 = F.layer_norm(to_dev(xb, half), [D], to_dev(w), to_dev(b), 1e-5)
         assert_half_close(to_np(gy2), conv(oy2), 1, f"ln {half} fp32 params {rows}x{D}", kind=half, atol=2 * LN_ATOL)
