@@ -128,6 +128,53 @@ __device__ __forceinline__ void st_stream(T* p, const Vec<T>& r) {
                : "memory");
 }
 
+// Whole-vector conversion to float.  For bf16 the generic per-element path costs two
+// instructions on odd elements (PRMT + SHL); working on the 32-bit words gives one each:
+// low half = w << 16, high half = w & 0xffff0000.
+template <typename T>
+__device__ __forceinline__ void unpack_to_float(const Vec<T>& v, float* out) {
+#pragma unroll
+  for (int k = 0; k < Vec<T>::N; ++k) out[k] = cvt<float>(v.v[k]);
+}
+template <>
+__device__ __forceinline__ void unpack_to_float<__nv_bfloat16>(const Vec<__nv_bfloat16>& v, float* out) {
+  const uint4 u = *reinterpret_cast<const uint4*>(&v);
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    out[2 * i] = __uint_as_float(w[i] << 16);
+    out[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+template <>
+__device__ __forceinline__ void unpack_to_float<__half>(const Vec<__half>& v, float* out) {
+  const __half2* h = reinterpret_cast<const __half2*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = __half22float2(h[i]);
+    out[2 * i] = f.x;
+    out[2 * i + 1] = f.y;
+  }
+}
+// float -> T, two at a time (one F2FP.PACK for the 16-bit types)
+template <typename T>
+__device__ __forceinline__ void pack_from_float(const float* in, Vec<T>& v) {
+#pragma unroll
+  for (int k = 0; k < Vec<T>::N; ++k) v.v[k] = cvt<T>(in[k]);
+}
+template <>
+__device__ __forceinline__ void pack_from_float<__nv_bfloat16>(const float* in, Vec<__nv_bfloat16>& v) {
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(in[2 * i], in[2 * i + 1]);
+}
+template <>
+__device__ __forceinline__ void pack_from_float<__half>(const float* in, Vec<__half>& v) {
+  __half2* h = reinterpret_cast<__half2*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2half2_rn(in[2 * i], in[2 * i + 1]);
+}
+
 // ----------------------------------------------------------------------------
 // warp / block reduction helpers
 // ----------------------------------------------------------------------------
@@ -167,6 +214,24 @@ __device__ __forceinline__ A block_reduce(A v, Combine comb, A identity, A* smem
   A r = smem[32];
   __syncthreads();  // smem may be reused by the caller right away
   return r;
+}
+
+// One-barrier CTA reduction for persistent row kernels: every warp leaves its partial in
+// `buf[warp]`, one __syncthreads, then every warp folds the 32 slots with a shuffle tree.  `buf`
+// has 32 slots; slots >= nwarps must hold the identity (block_reduce_1sync_init, once per kernel).
+// The caller alternates between two `buf`s on consecutive calls, so the next write to a buffer is
+// always separated from these reads by the barrier of the call in between.
+template <typename A>
+__device__ __forceinline__ void block_reduce_1sync_init(A* buf, A identity) {
+  if (threadIdx.x < 32) buf[threadIdx.x] = identity;
+}
+template <typename A, typename Combine>
+__device__ __forceinline__ A block_reduce_1sync(A v, Combine comb, A* buf) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  v = group_reduce<32>(v, comb);
+  if (lane == 0) buf[warp] = v;
+  __syncthreads();
+  return group_reduce<32>(buf[lane], comb);
 }
 
 // ----------------------------------------------------------------------------

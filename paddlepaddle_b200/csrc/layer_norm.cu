@@ -218,21 +218,23 @@ __global__ void __launch_bounds__(1024) ln_block_reg_kernel(const T* __restrict_
 
 // ---- pipe: persistent CTAs, rows staged in shared memory by cp.async.bulk -------------------
 // blockDim.x threads per row, C chunks of V elements per thread (chunk c of thread t covers
-// elements (c*blockDim.x + t)*V ..), STAGES rows in flight per CTA.  x is read ONCE from HBM by the
-// copy engine; scale/bias (same dtype as x) are loaded once per CTA and kept packed in registers.
-template <typename T, typename P, int C>
-__global__ void __launch_bounds__(512) ln_pipe_kernel(const T* __restrict__ x, const P* __restrict__ scale,
-                                                      const P* __restrict__ bias, T* __restrict__ y,
-                                                      typename AccType<T>::type* mean_out,
-                                                      typename AccType<T>::type* var_out, int64_t rows, int D,
-                                                      int stages, typename AccType<T>::type eps, double inv_d) {
-  using U = typename AccType<T>::type;
+// elements (c*blockDim.x + t)*V ..), `stages` rows in flight per CTA.  x is read ONCE from HBM by
+// the copy engine.  T is float / bf16 / fp16 (U = float).  The first-round kernel was issue-bound
+// (profiles/r1_ln_bf16.txt: 26 instructions per element): here AFFINE (scale and bias present) and
+// EXACT (D == C*blockDim.x*V) are compile-time so no per-element predicates remain, bf16 unpacks
+// in one instruction per element, sums run in four independent chains, the affine step is one
+// FFMA, and each CTA reduction costs one barrier.
+template <typename T, typename P, int C, bool AFFINE, bool EXACT, int MAXT>
+__global__ void __launch_bounds__(MAXT, MAXT <= 256 ? 3 : 1)
+ln_pipe_kernel(const T* __restrict__ x, const P* __restrict__ scale, const P* __restrict__ bias,
+               T* __restrict__ y, float* mean_out, float* var_out, int64_t rows, int D, int stages, float eps,
+               double inv_d) {
   constexpr int V = Vec<T>::N;
-  constexpr bool kParamsInRegs = sizeof(P) == sizeof(T);
+  constexpr int PV = Vec<P>::N;  // params per 16-byte load (== V, or V/2 when P is float and T 16-bit)
   extern __shared__ __align__(128) unsigned char ring_raw[];
   T* ring = reinterpret_cast<T*>(ring_raw);
   __shared__ uint64_t full[8];
-  __shared__ U red[33];
+  __shared__ float red[2][32];
   const int tid = threadIdx.x, nt = blockDim.x;
   const uint32_t row_bytes = (uint32_t)D * sizeof(T);
   const int64_t row_step = gridDim.x;
@@ -240,6 +242,8 @@ __global__ void __launch_bounds__(512) ln_pipe_kernel(const T* __restrict__ x, c
     for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
     mbar_fence_init();
   }
+  block_reduce_1sync_init(red[0], 0.f);
+  block_reduce_1sync_init(red[1], 0.f);
   __syncthreads();
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) {
@@ -247,18 +251,6 @@ __global__ void __launch_bounds__(512) ln_pipe_kernel(const T* __restrict__ x, c
       if (r < rows) {
         mbar_expect_tx(&full[s], row_bytes);
         bulk_load_row(ring + (size_t)s * D, x + r * D, row_bytes, &full[s]);
-      }
-    }
-  }
-  // scale / bias for this thread's columns: constant across rows
-  Vec<P> wreg[kParamsInRegs ? C : 1], breg[kParamsInRegs ? C : 1];
-  if constexpr (kParamsInRegs) {
-#pragma unroll
-    for (int c = 0; c < C; ++c) {
-      const int off = (c * nt + tid) * V;
-      if (off < D) {
-        if (scale) wreg[c] = ld_cached(scale + off);
-        if (bias) breg[c] = ld_cached(bias + off);
       }
     }
   }
@@ -271,20 +263,24 @@ __global__ void __launch_bounds__(512) ln_pipe_kernel(const T* __restrict__ x, c
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       const int off = (c * nt + tid) * V;
-      if (off < D) raw[c] = lds_vec(st + off);
+      if (EXACT || off < D) raw[c] = lds_vec(st + off);
     }
-    U e[C * V];
-    U sum = U(0);
+    float e[C * V];
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       const int off = (c * nt + tid) * V;
+      if (EXACT || off < D) {
+        unpack_to_float<T>(raw[c], &e[c * V]);
+      } else {
 #pragma unroll
-      for (int k = 0; k < V; ++k) {
-        e[c * V + k] = off < D ? cvt<U>(raw[c].v[k]) : U(0);
-        sum += e[c * V + k];
+        for (int k = 0; k < V; ++k) e[c * V + k] = 0.f;
       }
+#pragma unroll
+      for (int k = 0; k < V; ++k) acc[k & 3] += e[c * V + k];
     }
-    sum = block_reduce(sum, AddU<U>(), U(0), red);  // its barriers also mean: every thread has read stage s
+    float sum = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+    sum = block_reduce_1sync(sum, AddU<float>(), red[0]);  // its barrier also means: stage s fully read
     if (tid == 0) {
       const int64_t nrow = row + (int64_t)stages * row_step;
       if (nrow < rows) {
@@ -293,23 +289,24 @@ __global__ void __launch_bounds__(512) ln_pipe_kernel(const T* __restrict__ x, c
         bulk_load_row(ring + (size_t)s * D, x + nrow * D, row_bytes, &full[s]);
       }
     }
-    const U mean = mean_of<U>(sum, inv_d);
-    U sq = U(0);
+    const float mean = mean_of<float>(sum, inv_d);
+    acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       const int off = (c * nt + tid) * V;
-      if (off < D) {
+      if (EXACT || off < D) {
 #pragma unroll
         for (int k = 0; k < V; ++k) {
-          const U d = e[c * V + k] - mean;
+          const float d = e[c * V + k] - mean;
           e[c * V + k] = d;  // keep the centred value: the normalisation needs exactly this
-          sq += d * d;
+          acc[k & 3] = fmaf(d, d, acc[k & 3]);
         }
       }
     }
-    sq = block_reduce(sq, AddU<U>(), U(0), red);
-    const U var = mean_of<U>(sq, inv_d);
-    const U rstd = rsqrt_exact<U>(var + eps);
+    float sq = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+    sq = block_reduce_1sync(sq, AddU<float>(), red[1]);
+    const float var = mean_of<float>(sq, inv_d);
+    const float rstd = rsqrt_exact<float>(var + eps);
     if (tid == 0) {
       if (mean_out) mean_out[row] = mean;
       if (var_out) var_out[row] = var;
@@ -318,20 +315,27 @@ __global__ void __launch_bounds__(512) ln_pipe_kernel(const T* __restrict__ x, c
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       const int off = (c * nt + tid) * V;
-      if (off < D) {
-        if constexpr (kParamsInRegs) {
-          Vec<T> ov;
+      if (EXACT || off < D) {
+        if constexpr (AFFINE) {
+          float w[V], b[V];
+#pragma unroll
+          for (int j = 0; j < V / PV; ++j) {
+            unpack_to_float<P>(ld_cached(scale + off + j * PV), &w[j * PV]);
+            unpack_to_float<P>(ld_cached(bias + off + j * PV), &b[j * PV]);
+          }
+          float o[V];
 #pragma unroll
           for (int k = 0; k < V; ++k) {
-            U o = mul_rn<U>(e[c * V + k], rstd);
-            if (scale) o = mul_rn<U>(o, cvt<U>(wreg[c].v[k]));
-            if (bias) o = add_rn<U>(o, cvt<U>(breg[c].v[k]));
-            ov.v[k] = cvt<T>(o);
+            // (d * rstd) * w + b with the product-sum fused: <= 0.5 ulp(fp32) from the CPU kernel's
+            // separately rounded multiply and add
+            o[k] = fmaf(__fmul_rn(e[c * V + k], rstd), w[k], b[k]);
           }
+          Vec<T> ov;
+          pack_from_float<T>(o, ov);
           st_stream(dst + off, ov);
         } else {
           // e[] already holds x - mean: hand ln_store_chunk a zero mean
-          ln_store_chunk<T, P, U, V, true>(&e[c * V], U(0), rstd, scale, bias, dst, off);
+          ln_store_chunk<T, P, float, V, true>(&e[c * V], 0.f, rstd, scale, bias, dst, off);
         }
       }
     }
@@ -413,10 +417,19 @@ int layer_norm_typed(const T* x, const P* scale, const P* bias, T* y, void* mean
       kern<<<(unsigned)grid, threads, smem, st>>>(x, scale, bias, y, m, v, rows, (int)D, stages, eps, inv_d);
       return after_launch("ln_pipe");
     };
+    const bool affine = scale != nullptr && bias != nullptr;
+    const bool exact = (int64_t)threads * C == nchunk;
     int rc = -1;
-    if (C == 4) rc = launch(ln_pipe_kernel<T, P, 4>);
-    else if (C == 2) rc = launch(ln_pipe_kernel<T, P, 2>);
-    else rc = launch(ln_pipe_kernel<T, P, 1>);
+#define PDB_LN_PIPE2(CC, MT)                                                             \
+  if (affine && exact) rc = launch(ln_pipe_kernel<T, P, CC, true, true, MT>);            \
+  else if (affine) rc = launch(ln_pipe_kernel<T, P, CC, true, false, MT>);               \
+  else rc = launch(ln_pipe_kernel<T, P, CC, false, false, MT>);
+#define PDB_LN_PIPE(CC) if (threads <= 256) { PDB_LN_PIPE2(CC, 256) } else { PDB_LN_PIPE2(CC, 512) }
+    if constexpr (!std::is_same<T, double>::value) {
+      if (C == 4) { PDB_LN_PIPE(4) } else if (C == 2) { PDB_LN_PIPE(2) } else { PDB_LN_PIPE(1) }
+    }
+#undef PDB_LN_PIPE
+#undef PDB_LN_PIPE2
     if (rc >= 0) return rc;  // rc < 0: the pipeline does not fit this device; fall through
   }
   if (nchunk <= 32 * 8) {

@@ -129,14 +129,14 @@ __device__ __forceinline__ float fast_clipped_exp(float x, float neg_m_log2e) {
 
 // ---- pipe: persistent CTAs, rows staged in shared memory by cp.async.bulk -------------------
 // blockDim.x threads per row, C chunks of V elements per thread.  T is float, bf16 or fp16.
-template <typename T, int C>
+template <typename T, int C, bool EXACT>
 __global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__ x, T* __restrict__ y,
                                                            int64_t rows, int dim, int stages) {
   constexpr int V = Vec<T>::N;
   extern __shared__ __align__(128) unsigned char ring_raw[];
   T* ring = reinterpret_cast<T*>(ring_raw);
   __shared__ uint64_t full[8];
-  __shared__ float red[33];
+  __shared__ float red[2][32];
   const int tid = threadIdx.x, nt = blockDim.x;
   const uint32_t row_bytes = (uint32_t)dim * sizeof(T);
   const int64_t row_step = gridDim.x;
@@ -144,6 +144,8 @@ __global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__
     for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
     mbar_fence_init();
   }
+  block_reduce_1sync_init(red[0], -INFINITY);
+  block_reduce_1sync_init(red[1], 0.f);
   __syncthreads();
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) {
@@ -163,20 +165,24 @@ __global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       const int off = (c * nt + tid) * V;
-      if (off < dim) raw[c] = lds_vec(st + off);
+      if (EXACT || off < dim) raw[c] = lds_vec(st + off);
     }
     float e[C * V];
-    float m = -INFINITY;
+    float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       const int off = (c * nt + tid) * V;
+      if (EXACT || off < dim) {
+        unpack_to_float<T>(raw[c], &e[c * V]);
+      } else {
 #pragma unroll
-      for (int k = 0; k < V; ++k) {
-        e[c * V + k] = off < dim ? cvt<float>(raw[c].v[k]) : -INFINITY;
-        m = fmaxf(m, e[c * V + k]);
+        for (int k = 0; k < V; ++k) e[c * V + k] = -INFINITY;
       }
+#pragma unroll
+      for (int k = 0; k < V; ++k) mx[k & 3] = fmaxf(mx[k & 3], e[c * V + k]);
     }
-    m = block_reduce(m, MaxF<float>(), -INFINITY, red);  // barriers inside: stage s fully read
+    float m = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+    m = block_reduce_1sync(m, MaxF<float>(), red[0]);  // its barrier also means: stage s fully read
     if (tid == 0) {
       const int64_t nrow = row + (int64_t)stages * row_step;
       if (nrow < rows) {
@@ -186,29 +192,29 @@ __global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__
       }
     }
     const float nml = -m * 1.4426950408889634f;
-    float sum = 0.f;
-#pragma unroll
-    for (int i = 0; i < C * V; ++i) {
-      e[i] = fast_clipped_exp(e[i], nml);  // padding lanes: exp(-inf) clamps to 2^-92, excluded below
-    }
+    float sm[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       const int off = (c * nt + tid) * V;
-      if (off < dim) {
 #pragma unroll
-        for (int k = 0; k < V; ++k) sum += e[c * V + k];
+      for (int k = 0; k < V; ++k) {
+        e[c * V + k] = fast_clipped_exp(e[c * V + k], nml);
+        if (EXACT || off < dim) sm[k & 3] += e[c * V + k];  // padding chunks are not part of the row
       }
     }
-    sum = block_reduce(sum, AddF<float>(), 0.f, red);
+    float sum = (sm[0] + sm[1]) + (sm[2] + sm[3]);
+    sum = block_reduce_1sync(sum, AddF<float>(), red[1]);
     const float inv = 1.0f / sum;
     T* dst = y + row * dim;
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       const int off = (c * nt + tid) * V;
-      if (off < dim) {
-        Vec<T> o;
+      if (EXACT || off < dim) {
+        float r[V];
 #pragma unroll
-        for (int k = 0; k < V; ++k) o.v[k] = cvt<T>(e[c * V + k] * inv);
+        for (int k = 0; k < V; ++k) r[k] = e[c * V + k] * inv;
+        Vec<T> o;
+        pack_from_float<T>(r, o);
         st_stream(dst + off, o);
       }
     }
@@ -350,9 +356,12 @@ int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, cudaStream_t 
     kern<<<(unsigned)grid, threads, smem, st>>>(x, y, outer, (int)dim, stages);
     return after_launch("softmax_pipe");
   };
-  if (C == 4) return launch(softmax_pipe_kernel<T, 4>);
-  if (C == 2) return launch(softmax_pipe_kernel<T, 2>);
-  return launch(softmax_pipe_kernel<T, 1>);
+  const bool exact = (int64_t)threads * C == nchunk;
+#define PDB_SM_PIPE(CC) return exact ? launch(softmax_pipe_kernel<T, CC, true>) : launch(softmax_pipe_kernel<T, CC, false>);
+  if (C == 4) { PDB_SM_PIPE(4) }
+  if (C == 2) { PDB_SM_PIPE(2) }
+  PDB_SM_PIPE(1)
+#undef PDB_SM_PIPE
 }
 template <>
 int try_softmax_pipe<double>(const double*, double*, int64_t, int64_t, cudaStream_t) { return -1; }
