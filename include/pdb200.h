@@ -141,6 +141,28 @@ PDB200_API int pdb200_prod(const void* x, const int64_t* x_dims, int x_rank, con
                 int reduce_all, int x_dtype, int out_dtype, void* out, void* workspace,
                 size_t workspace_bytes, void* stream);
 
+/* Column sums without any allocation: out[c] = sum over r of x[r][c] for a contiguous [rows, cols]
+ * matrix, the same result as pdb200_sum_raw(x, {rows, cols}, axes = {0}).
+ * No counterpart in the reference: every PHI kernel gets its scratch from the device context's
+ * allocator.  This variant is for callers that have no allocator to offer and may not call cudaMalloc
+ * themselves (memory planned and handed out at start-up, real-time loops, plugin hosts without an
+ * allocator): it takes no workspace argument and keeps its partial sums in a fixed array of
+ * PDB200_STATIC_SCRATCH_BYTES (3 MiB) inside the library's device image — present on every GPU that
+ * loads the library, for the life of the process.  Limits and rules:
+ *   - shapes whose partial sums need more than PDB200_STATIC_SCRATCH_BYTES are refused with
+ *     PDB200_WORKSPACE_TOO_SMALL (the message says how much was needed); shapes wide enough to need
+ *     no partials at all are unaffected by the limit;
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress, with
+ *     that device current); make that first call before starting any stream capture;
+ *   - the array is shared by all calls on a device and keeps the previous call's contents (nothing in
+ *     it needs to start at zero); calls that can overlap on the GPU — different streams without an
+ *     ordering between them — race on it, so keep them on one stream or order them with events;
+ *   - it calls no cudaMalloc / cudaFree and no allocating library routine.
+ * dtype pairs: FLOAT32->FLOAT32, BFLOAT16->BFLOAT16, BFLOAT16->FLOAT32, INT64->INT64. */
+#define PDB200_STATIC_SCRATCH_BYTES (3u << 20)
+PDB200_API int pdb200_sum_axis0_static(const void* x, int64_t rows, int64_t cols, int x_dtype, int out_dtype,
+                                       void* out, void* stream);
+
 /* ---------------------------------------------------------------------------
  * argmax.  Replaces phi::ArgMaxKernel<T, GPUContext> (paddle/phi/kernels/gpu/arg_min_max_kernel.cu:59-204).
  * Lowest index wins ties; out_dtype is PDB200_INT64 or PDB200_INT32; flatten != 0 reduces over the
