@@ -225,19 +225,26 @@ __global__ void __launch_bounds__(1024) ln_block_reg_kernel(const T* __restrict_
 // in one instruction per element, sums run in four independent chains, the affine step is one
 // FFMA, and each CTA reduction costs one barrier.
 template <typename T, typename P, int C, bool AFFINE, bool EXACT, int MAXT>
-__global__ void __launch_bounds__(MAXT, MAXT <= 256 ? 3 : 1)
+__global__ void __launch_bounds__(MAXT, MAXT <= 256 ? 2 : 1)
 ln_pipe_kernel(const T* __restrict__ x, const P* __restrict__ scale, const P* __restrict__ bias,
                T* __restrict__ y, float* mean_out, float* var_out, int64_t rows, int D, int stages, float eps,
-               double inv_d) {
+               double inv_d, int contiguous) {
   constexpr int V = Vec<T>::N;
   constexpr int PV = Vec<P>::N;  // params per 16-byte load (== V, or V/2 when P is float and T 16-bit)
   extern __shared__ __align__(128) unsigned char ring_raw[];
   T* ring = reinterpret_cast<T*>(ring_raw);
-  __shared__ uint64_t full[8];
+  __shared__ uint64_t full[kPipeMaxStages];
   __shared__ float red[2][32];
   const int tid = threadIdx.x, nt = blockDim.x;
   const uint32_t row_bytes = (uint32_t)D * sizeof(T);
-  const int64_t row_step = gridDim.x;
+  // Row -> CTA mapping: strided (row = cta + k*grid) or one contiguous slab per CTA.
+  int64_t row_first = blockIdx.x, row_step = gridDim.x, row_end = rows;
+  if (contiguous) {
+    const int64_t slab = (rows + gridDim.x - 1) / gridDim.x;
+    row_first = (int64_t)blockIdx.x * slab;
+    row_step = 1;
+    row_end = row_first + slab < rows ? row_first + slab : rows;
+  }
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
     mbar_fence_init();
@@ -247,16 +254,31 @@ ln_pipe_kernel(const T* __restrict__ x, const P* __restrict__ scale, const P* __
   __syncthreads();
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) {
-      const int64_t r = blockIdx.x + s * row_step;
-      if (r < rows) {
+      const int64_t r = row_first + s * row_step;
+      if (r < row_end) {
         mbar_expect_tx(&full[s], row_bytes);
         bulk_load_row(ring + (size_t)s * D, x + r * D, row_bytes, &full[s]);
       }
     }
   }
+  // scale / bias: re-read through L1 for every row (16-byte loads).  Keeping them packed in
+  // registers instead (kParamRegs) costs 32 registers and measured slower on B200; the L1 path
+  // needs the carve-out to leave L1 room for 2*D*sizeof(P) bytes, which pipe_geometry arranges.
+  constexpr bool kParamRegs = false;  // measured slower than the L1 path (0.368 vs 0.339 ms); kept for reference
+  Vec<P> wreg[kParamRegs ? C : 1], breg[kParamRegs ? C : 1];
+  if constexpr (kParamRegs) {
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + tid) * V;
+      if (EXACT || off < D) {
+        wreg[c] = ld_cached(scale + off);
+        breg[c] = ld_cached(bias + off);
+      }
+    }
+  }
   int s = 0;
   uint32_t phase = 0;
-  for (int64_t row = blockIdx.x; row < rows; row += row_step) {
+  for (int64_t row = row_first; row < row_end; row += row_step) {
     mbar_wait(&full[s], phase);
     const T* st = ring + (size_t)s * D;
     Vec<T> raw[C];
@@ -283,7 +305,7 @@ ln_pipe_kernel(const T* __restrict__ x, const P* __restrict__ scale, const P* __
     sum = block_reduce_1sync(sum, AddU<float>(), red[0]);  // its barrier also means: stage s fully read
     if (tid == 0) {
       const int64_t nrow = row + (int64_t)stages * row_step;
-      if (nrow < rows) {
+      if (nrow < row_end) {
         fence_proxy_async_smem();
         mbar_expect_tx(&full[s], row_bytes);
         bulk_load_row(ring + (size_t)s * D, x + nrow * D, row_bytes, &full[s]);
@@ -318,10 +340,15 @@ ln_pipe_kernel(const T* __restrict__ x, const P* __restrict__ scale, const P* __
       if (EXACT || off < D) {
         if constexpr (AFFINE) {
           float w[V], b[V];
+          if constexpr (kParamRegs) {
+            unpack_to_float<P>(wreg[c], w);
+            unpack_to_float<P>(breg[c], b);
+          } else {
 #pragma unroll
-          for (int j = 0; j < V / PV; ++j) {
-            unpack_to_float<P>(ld_cached(scale + off + j * PV), &w[j * PV]);
-            unpack_to_float<P>(ld_cached(bias + off + j * PV), &b[j * PV]);
+            for (int j = 0; j < V / PV; ++j) {
+              unpack_to_float<P>(ld_cached(scale + off + j * PV), &w[j * PV]);
+              unpack_to_float<P>(ld_cached(bias + off + j * PV), &b[j * PV]);
+            }
           }
           float o[V];
 #pragma unroll
@@ -405,16 +432,19 @@ int layer_norm_typed(const T* x, const P* scale, const P* bias, T* y, void* mean
   // Fast path: many rows, 16-byte-multiple rows that fit <= 512 threads x 4 chunks -> TMA row pipeline.
   if (vec && sizeof(T) <= 4 && nchunk >= 64 && nchunk <= 512 * 4 && rows >= 4 * (int64_t)sm_count()) {
     int C = nchunk >= 512 ? 4 : (nchunk >= 256 ? 2 : 1);  // CTAs stay >= 128 threads wide
+    if (const int o = pipe_c_override("PDB200_LN_PIPE_C")) C = o;
     int threads = (int)((nchunk + C - 1) / C);
     threads = (threads + 31) / 32 * 32;
     const size_t row_bytes = (size_t)D * sizeof(T);
     auto launch = [&](auto kern) -> int {
       int per_sm = 0, stages = 0;
       size_t smem = 0;
-      if (!pipe_geometry(kern, threads, row_bytes, &per_sm, &stages, &smem)) return -1;
+      int want = 512 / threads;  // ~512 threads per SM, 2..4 CTAs, 3 rows in flight each
+      want = want < 2 ? 2 : (want > 4 ? 4 : want);
+      if (!pipe_geometry(kern, threads, row_bytes, want, 3, &per_sm, &stages, &smem)) return -1;
       int64_t grid = (int64_t)per_sm * sm_count();
       if (grid > rows) grid = rows;
-      kern<<<(unsigned)grid, threads, smem, st>>>(x, scale, bias, y, m, v, rows, (int)D, stages, eps, inv_d);
+      kern<<<(unsigned)grid, threads, smem, st>>>(x, scale, bias, y, m, v, rows, (int)D, stages, eps, inv_d, pipe_contiguous());
       return after_launch("ln_pipe");
     };
     const bool affine = scale != nullptr && bias != nullptr;

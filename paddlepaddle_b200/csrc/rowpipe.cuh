@@ -18,6 +18,7 @@
 
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 namespace pdb200 {
 
@@ -72,45 +73,68 @@ __device__ __forceinline__ Vec<T> lds_vec(const T* p) {
   return r;
 }
 
-// Host: ring depth for rows of `row_bytes` when `ctas_per_sm` CTAs share an SM.  Leaves ~27 KB of
-// the 227 KB for static shared memory and the driver's reserve.
-inline int pipe_stages(size_t row_bytes, int ctas_per_sm) {
-  const size_t budget = 200 * 1024;
-  int st = static_cast<int>(budget / (static_cast<size_t>(ctas_per_sm) * row_bytes));
-  if (st > 8) st = 8;
-  return st;
+constexpr int kPipeMaxStages = 32;  // mbarriers per CTA
+
+// Tuning knob: row -> CTA mapping of the pipelined kernels (1 = contiguous slab per CTA).
+inline int pipe_contiguous() {
+  const char* v = getenv("PDB200_PIPE_CONTIG");
+  return v ? atoi(v) : 0;
 }
 
-// Launch helper shared by the pipelined kernels: find how many CTAs fit an SM (registers,
-// threads), give each an equal share of shared memory as ring stages, run a persistent grid.
+// Tuning knob: chunks per thread for the pipelined kernels (0 = use the built-in choice).
+inline int pipe_c_override(const char* name) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : 0;
+}
+
+// Launch helper shared by the pipelined kernels.  `want_ctas` CTAs per SM (capped by what registers
+// and threads allow) each get `want_stages` ring stages (capped by shared memory); the result is
+// VERIFIED with the occupancy calculator at the final shared-memory size — a persistent grid sized
+// for N CTAs per SM runs in two waves if only N-1 fit.  The shared-memory carve-out is set to what
+// the CTAs need and no more, so that the rest of the 256 KB stays L1 (layer_norm re-reads scale and
+// bias through L1 for every row; with the carve-out at its maximum that kernel ran 30% slower).
+// Geometry comes from sweeps on B200 (profiles/r1_sweep.txt): past ~512-768 threads and ~3 stages
+// per SM more concurrency does not help and often hurts.
 // Returns false when fewer than 2 stages fit (caller falls back to a non-pipelined route).
 template <typename Kern>
-inline bool pipe_geometry(Kern kern, int threads, size_t row_bytes, int* grid_per_sm, int* stages,
-                          size_t* smem_bytes) {
+inline bool pipe_geometry(Kern kern, int threads, size_t row_bytes, int want_ctas, int want_stages,
+                          int* grid_per_sm, int* stages, size_t* smem_bytes) {
+  auto ok = [](cudaError_t e) {
+    if (e != cudaSuccess) cudaGetLastError();
+    return e == cudaSuccess;
+  };
+  if (const char* v = getenv("PDB200_PIPE_MAX_CTAS")) {  // tuning knobs (profiles/sweep.py)
+    if (atoi(v) >= 1) want_ctas = atoi(v);
+  }
+  if (const char* v = getenv("PDB200_PIPE_MAX_STAGES")) {
+    if (atoi(v) >= 2) want_stages = atoi(v);
+  }
+  if (want_stages > kPipeMaxStages) want_stages = kPipeMaxStages;
+  if (!ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * (int)row_bytes))) return false;
   int occ = 0;
-  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * (int)row_bytes) != cudaSuccess) {
-    cudaGetLastError();
-    return false;
+  if (!ok(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, 2 * row_bytes)) || occ < 1) return false;
+  if (occ > want_ctas) occ = want_ctas;
+  const size_t sm_smem = 227 * 1024;
+  for (; occ >= 1; --occ) {
+    int st = static_cast<int>((sm_smem / occ - 2048) / row_bytes);  // 1 KB reserved + static barriers per CTA
+    if (st > want_stages) st = want_stages;
+    for (; st >= 2; --st) {
+      const size_t smem = (size_t)st * row_bytes;
+      int pct = static_cast<int>((occ * (smem + 2048) * 100 + sm_smem - 1) / sm_smem);
+      if (pct > 100) pct = 100;
+      if (!ok(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, pct))) continue;
+      if (!ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))) continue;
+      int real = 0;
+      if (!ok(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&real, kern, threads, smem))) continue;
+      if (real >= occ) {
+        *grid_per_sm = occ;
+        *stages = st;
+        *smem_bytes = smem;
+        return true;
+      }
+    }
   }
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, 2 * row_bytes) != cudaSuccess || occ < 1) {
-    cudaGetLastError();
-    return false;
-  }
-  if (occ > 16) occ = 16;
-  int st = pipe_stages(row_bytes, occ);
-  while (st < 3 && occ > 1) {  // prefer depth over CTA count
-    --occ;
-    st = pipe_stages(row_bytes, occ);
-  }
-  if (st < 2) return false;
-  *grid_per_sm = occ;
-  *stages = st;
-  *smem_bytes = (size_t)st * row_bytes;
-  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem_bytes) != cudaSuccess) {
-    cudaGetLastError();
-    return false;
-  }
-  return true;
+  return false;
 }
 
 }  // namespace pdb200

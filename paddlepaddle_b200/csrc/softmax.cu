@@ -131,15 +131,22 @@ __device__ __forceinline__ float fast_clipped_exp(float x, float neg_m_log2e) {
 // blockDim.x threads per row, C chunks of V elements per thread.  T is float, bf16 or fp16.
 template <typename T, int C, bool EXACT>
 __global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__ x, T* __restrict__ y,
-                                                           int64_t rows, int dim, int stages) {
+                                                           int64_t rows, int dim, int stages, int contiguous) {
   constexpr int V = Vec<T>::N;
   extern __shared__ __align__(128) unsigned char ring_raw[];
   T* ring = reinterpret_cast<T*>(ring_raw);
-  __shared__ uint64_t full[8];
+  __shared__ uint64_t full[kPipeMaxStages];
   __shared__ float red[2][32];
   const int tid = threadIdx.x, nt = blockDim.x;
   const uint32_t row_bytes = (uint32_t)dim * sizeof(T);
-  const int64_t row_step = gridDim.x;
+  // Row -> CTA mapping: strided (row = cta + k*grid) or one contiguous slab per CTA.
+  int64_t row_first = blockIdx.x, row_step = gridDim.x, row_end = rows;
+  if (contiguous) {
+    const int64_t slab = (rows + gridDim.x - 1) / gridDim.x;
+    row_first = (int64_t)blockIdx.x * slab;
+    row_step = 1;
+    row_end = row_first + slab < rows ? row_first + slab : rows;
+  }
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
     mbar_fence_init();
@@ -149,8 +156,8 @@ __global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__
   __syncthreads();
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) {
-      const int64_t r = blockIdx.x + s * row_step;
-      if (r < rows) {
+      const int64_t r = row_first + s * row_step;
+      if (r < row_end) {
         mbar_expect_tx(&full[s], row_bytes);
         bulk_load_row(ring + (size_t)s * dim, x + r * dim, row_bytes, &full[s]);
       }
@@ -158,7 +165,7 @@ __global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__
   }
   int s = 0;
   uint32_t phase = 0;
-  for (int64_t row = blockIdx.x; row < rows; row += row_step) {
+  for (int64_t row = row_first; row < row_end; row += row_step) {
     mbar_wait(&full[s], phase);
     const T* st = ring + (size_t)s * dim;
     Vec<T> raw[C];
@@ -185,7 +192,7 @@ __global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__
     m = block_reduce_1sync(m, MaxF<float>(), red[0]);  // its barrier also means: stage s fully read
     if (tid == 0) {
       const int64_t nrow = row + (int64_t)stages * row_step;
-      if (nrow < rows) {
+      if (nrow < row_end) {
         fence_proxy_async_smem();
         mbar_expect_tx(&full[s], row_bytes);
         bulk_load_row(ring + (size_t)s * dim, x + nrow * dim, row_bytes, &full[s]);
@@ -342,18 +349,22 @@ template <typename T>
 int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, cudaStream_t st) {
   constexpr int VN = Vec<T>::N;
   const int64_t nchunk = dim / VN;
-  // keep CTAs >= 128 threads wide: 4 chunks a thread from 512 chunks up, 2 from 256
-  const int C = nchunk >= 512 ? 4 : (nchunk >= 256 ? 2 : 1);
+  // chunks per thread: 16-bit rows do best with 4 (32 values a thread), fp32 rows with 2
+  // (8 values): profiles/r1_sweep.txt
+  int C = sizeof(T) == 2 ? (nchunk >= 256 ? 4 : (nchunk >= 128 ? 2 : 1)) : (nchunk >= 256 ? 2 : 1);
+  if (const int o = pipe_c_override("PDB200_SOFTMAX_PIPE_C")) C = o;
   int threads = (int)((nchunk + C - 1) / C);
   threads = (threads + 31) / 32 * 32;
   const size_t row_bytes = (size_t)dim * sizeof(T);
   auto launch = [&](auto kern) -> int {
     int per_sm = 0, stages = 0;
     size_t smem = 0;
-    if (!pipe_geometry(kern, threads, row_bytes, &per_sm, &stages, &smem)) return -1;
+    int want = 768 / threads;  // ~768 threads per SM, 2..6 CTAs, 3 rows in flight each
+    want = want < 2 ? 2 : (want > 6 ? 6 : want);
+    if (!pipe_geometry(kern, threads, row_bytes, want, 3, &per_sm, &stages, &smem)) return -1;
     int64_t grid = (int64_t)per_sm * sm_count();
     if (grid > outer) grid = outer;
-    kern<<<(unsigned)grid, threads, smem, st>>>(x, y, outer, (int)dim, stages);
+    kern<<<(unsigned)grid, threads, smem, st>>>(x, y, outer, (int)dim, stages, pipe_contiguous());
     return after_launch("softmax_pipe");
   };
   const bool exact = (int64_t)threads * C == nchunk;
