@@ -16,9 +16,13 @@
 // Routes (x viewed as [rows][D]):
 //   rows_reg   : G lanes (<= 32) per row, C <= 8 16-byte chunks per lane     (D <= 256*V)
 //   block_reg  : one CTA (128..1024 threads) per row, C <= 4 chunks a thread (D <= 4096*V)
-//   block_strm : longer rows — three streaming sweeps
+//   cluster    : long rows — one thread-block CLUSTER (2..8 CTAs) per row, each CTA keeps its slice
+//                in shared memory, the row sums are combined through distributed shared memory
+//   block_strm : longer still — three streaming sweeps
 //   pipe       : the fast path for many rows (config 3): persistent CTAs fed by the TMA row
 //                pipeline of rowpipe.cuh; scale/bias stay in registers across rows
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 #include "rowpipe.cuh"
 #include "shape.h"
@@ -373,6 +377,92 @@ ln_pipe_kernel(const T* __restrict__ x, const P* __restrict__ scale, const P* __
   }
 }
 
+// ---- cluster: one thread-block cluster per row, DSMEM combine -----------------------------------
+// CTA `rank` owns elements [rank*slice, +slice) of the row, staged once in shared memory in their
+// storage type (the only HBM read of x).  Sum and sum of squared deviations are produced per CTA,
+// published in shared memory and folded by every CTA, in rank order, through DSMEM after a cluster
+// barrier.  Vector path only (D % V == 0, 16-byte aligned bases).
+template <typename T, typename P>
+__global__ void __launch_bounds__(1024) ln_rows_cluster_kernel(const T* __restrict__ x, const P* __restrict__ scale,
+                                                               const P* __restrict__ bias, T* __restrict__ y,
+                                                               typename AccType<T>::type* mean_out,
+                                                               typename AccType<T>::type* var_out, int64_t D,
+                                                               int64_t slice, typename AccType<T>::type eps,
+                                                               double inv_d) {
+  namespace cg = cooperative_groups;
+  using U = typename AccType<T>::type;
+  constexpr int V = Vec<T>::N;
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned rank = cluster.block_rank(), cs = cluster.num_blocks();
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* srow = reinterpret_cast<T*>(smem_raw);
+  __shared__ U red[33];
+  __shared__ U xchg[2];
+  const int64_t row = (int64_t)blockIdx.x / cs;
+  const int64_t begin = (int64_t)rank * slice;
+  int64_t n = D - begin;
+  n = n < 0 ? 0 : (n > slice ? slice : n);
+  const T* src = x + row * D + begin;
+  T* dst = y + row * D + begin;
+  const int64_t step = (int64_t)blockDim.x * V;
+  // HBM -> shared with ONE bulk async copy for the whole slice, then the local sum from shared memory
+  __shared__ uint64_t bar;
+  if (threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  if (n > 0) {
+    if (threadIdx.x == 0) {
+      mbar_expect_tx(&bar, (uint32_t)(n * sizeof(T)));
+      bulk_load_row(srow, src, (uint32_t)(n * sizeof(T)), &bar);
+    }
+    mbar_wait(&bar, 0);
+  }
+  U sum = U(0);
+  for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
+    const Vec<T> v = lds_vec(srow + i);
+#pragma unroll
+    for (int k = 0; k < V; ++k) sum += cvt<U>(v.v[k]);
+  }
+  sum = block_reduce(sum, AddU<U>(), U(0), red);
+  if (threadIdx.x == 0) xchg[0] = sum;
+  cluster.sync();
+  U total = U(0);
+  for (unsigned r = 0; r < cs; ++r) total += *cluster.map_shared_rank(&xchg[0], r);
+  const U mean = mean_of<U>(total, inv_d);
+  U sq = U(0);
+  for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
+    const Vec<T> v = lds_vec(srow + i);
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+      const U d = cvt<U>(v.v[k]) - mean;
+      sq += d * d;
+    }
+  }
+  sq = block_reduce(sq, AddU<U>(), U(0), red);
+  if (threadIdx.x == 0) xchg[1] = sq;
+  cluster.sync();
+  U total_sq = U(0);
+  for (unsigned r = 0; r < cs; ++r) total_sq += *cluster.map_shared_rank(&xchg[1], r);
+  const U var = mean_of<U>(total_sq, inv_d);
+  const U rstd = rsqrt_exact<U>(var + eps);
+  if (rank == 0 && threadIdx.x == 0) {
+    if (mean_out) mean_out[row] = mean;
+    if (var_out) var_out[row] = var;
+  }
+  const P* sc = scale ? scale + begin : nullptr;
+  const P* bi = bias ? bias + begin : nullptr;
+  for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
+    const Vec<T> v = lds_vec(srow + i);
+    U e[V];
+#pragma unroll
+    for (int k = 0; k < V; ++k) e[k] = cvt<U>(v.v[k]);
+    ln_store_chunk<T, P, U, V, true>(e, mean, rstd, sc, bi, dst, i);
+  }
+  cluster.sync();  // nobody leaves while a peer may still be reading its xchg[]
+}
+
 // ---- block_strm: rows too long for registers ------------------------------------------------
 template <typename T, typename P>
 __global__ void __launch_bounds__(1024) ln_block_stream_kernel(const T* x, const P* __restrict__ scale,
@@ -492,6 +582,36 @@ int layer_norm_typed(const T* x, const P* scale, const P* bias, T* y, void* mean
     return after_launch("ln_block_reg");
   }
 #undef PDB_LN_C
+  // Long rows (beyond the register routes): thread-block cluster per row, slices in shared memory.
+  if (vec && nchunk > 1024 * 4) {
+    const size_t row_bytes = (size_t)D * sizeof(T);
+    const size_t kMaxSlice = 200 * 1024;
+    int cs = 1;
+    while (cs < 8 && (row_bytes / cs > 32 * 1024 || rows * cs < 2 * (int64_t)sm_count())) cs <<= 1;
+    int64_t slice = (D + cs - 1) / cs;
+    slice = (slice + VN - 1) / VN * VN;
+    auto kern = ln_rows_cluster_kernel<T, P>;
+    if ((size_t)slice * sizeof(T) <= kMaxSlice && rows * cs <= 0x7fffffffLL &&
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxSlice) == cudaSuccess) {
+      int threads = 256;
+      while (threads < 1024 && (int64_t)threads * VN * 16 < slice) threads <<= 1;
+      cudaLaunchConfig_t cfg{};
+      cfg.gridDim = dim3((unsigned)(rows * cs));
+      cfg.blockDim = dim3(threads);
+      cfg.dynamicSmemBytes = (size_t)slice * sizeof(T);
+      cfg.stream = st;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = cs;
+      attr[0].val.clusterDim.y = 1;
+      attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      if (cudaLaunchKernelEx(&cfg, kern, x, scale, bias, y, m, v, D, slice, eps, inv_d) == cudaSuccess)
+        return after_launch("ln_rows_cluster");
+    }
+    cudaGetLastError();  // could not be scheduled as a cluster: fall through to the streaming route
+  }
   ln_block_stream_kernel<T, P><<<(unsigned)rows, 1024, 0, st>>>(x, scale, bias, y, m, v, D, eps, inv_d);
   return after_launch("ln_block_stream");
 }

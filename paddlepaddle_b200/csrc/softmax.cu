@@ -15,13 +15,20 @@
 //        Covers dim <= 32*16*V (2048 fp32, 4096 bf16) — the reference needs cuDNN there.
 //   inner == 1, row fits shared mem -> rows_smem  : one CTA per row, row staged once in
 //        shared memory as float (<= 50 K elements): still one read + one write.
-//   inner == 1, longer rows         -> rows_stream: three streaming sweeps (as the reference
+//   inner == 1, long rows           -> rows_cluster: one thread-block CLUSTER (2..8 CTAs) per row;
+//        each CTA stages its slice of the row in shared memory, the per-CTA max and sum are
+//        combined through distributed shared memory (DSMEM) after a cluster barrier: one read +
+//        one write of HBM for rows up to 8 x 200 KB (vocabulary-sized rows), and 8x the CTAs when
+//        there are only a few rows.
+//   inner == 1, longer still        -> rows_stream: three streaming sweeps (as the reference
 //        does from 100000 up).
 //   inner  > 1                      -> cols       : threads along `inner` (coalesced),
 //        sweeps over `dim`; later sweeps hit L2.
 //   inner == 1, many rows (config 4) -> pipe      : persistent CTAs fed by the TMA row pipeline of
 //        rowpipe.cuh (one cp.async.bulk per row into a shared-memory ring), 16 values per thread,
 //        exp through ex2.approx on the pre-scaled difference.
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 #include "rowpipe.cuh"
 #include "shape.h"
@@ -125,6 +132,15 @@ __device__ __forceinline__ float fast_clipped_exp(float x, float neg_m_log2e) {
   float r;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(t));
   return r;
+}
+
+// float rows take the fast path, double rows the accurate one
+template <typename A> __device__ __forceinline__ A row_exp(A x, A m, A neg_m_log2e);
+template <> __device__ __forceinline__ float row_exp<float>(float x, float, float neg_m_log2e) {
+  return fast_clipped_exp(x, neg_m_log2e);
+}
+template <> __device__ __forceinline__ double row_exp<double>(double x, double m, double) {
+  return clipped_exp<double>(x, m);
 }
 
 // ---- pipe: persistent CTAs, rows staged in shared memory by cp.async.bulk -------------------
@@ -280,6 +296,88 @@ __global__ void __launch_bounds__(1024) softmax_rows_smem_kernel(const T* __rest
   }
 }
 
+// ---- rows_cluster: one thread-block cluster per row, DSMEM combine ------------------------------
+// CTA `rank` of the cluster owns elements [rank*slice, rank*slice + slice) of the row and keeps them in
+// shared memory in their storage type.  The two row-wide quantities (max, sum of exp) are produced
+// per CTA, published in that CTA's shared memory and read by every peer through DSMEM
+// (cluster.map_shared_rank) after a cluster barrier; all CTAs fold the partials in rank order, so
+// they agree bit for bit.  Requires dim % V == 0 and 16-byte aligned bases (vector path only).
+template <typename T>
+__global__ void __launch_bounds__(1024) softmax_rows_cluster_kernel(const T* __restrict__ x, T* __restrict__ y,
+                                                                    int64_t dim, int64_t slice) {
+  namespace cg = cooperative_groups;
+  using A = typename AccType<T>::type;
+  constexpr int V = Vec<T>::N;
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned rank = cluster.block_rank(), cs = cluster.num_blocks();
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* srow = reinterpret_cast<T*>(smem_raw);  // [slice]
+  __shared__ A red[33];
+  __shared__ A xchg[2];  // [0] this CTA's max, [1] this CTA's sum — read by peers through DSMEM
+  const int64_t row = (int64_t)blockIdx.x / cs;
+  const int64_t begin = (int64_t)rank * slice;
+  int64_t n = dim - begin;
+  n = n < 0 ? 0 : (n > slice ? slice : n);
+  const T* src = x + row * dim + begin;
+  T* dst = y + row * dim + begin;
+  const int64_t step = (int64_t)blockDim.x * V;
+  // sweep 1: HBM -> shared with ONE bulk async copy for the whole slice (the only read of x: all of
+  // its bytes are in flight at once, no registers involved), then the local max from shared memory
+  __shared__ uint64_t bar;
+  if (threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  if (n > 0) {
+    if (threadIdx.x == 0) {
+      mbar_expect_tx(&bar, (uint32_t)(n * sizeof(T)));
+      bulk_load_row(srow, src, (uint32_t)(n * sizeof(T)), &bar);
+    }
+    mbar_wait(&bar, 0);
+  }
+  A m = neg_inf<A>();
+  for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
+    const Vec<T> v = lds_vec(srow + i);
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+      const A a = cvt<A>(v.v[k]);
+      m = a > m ? a : m;
+    }
+  }
+  m = block_reduce(m, MaxF<A>(), neg_inf<A>(), red);
+  if (threadIdx.x == 0) xchg[0] = m;
+  cluster.sync();
+  A gm = neg_inf<A>();
+  for (unsigned r = 0; r < cs; ++r) {
+    const A o = *cluster.map_shared_rank(&xchg[0], r);
+    gm = o > gm ? o : gm;
+  }
+  // sweep 2 (shared memory): local sum of exp
+  const A nml = -gm * A(1.4426950408889634);
+  A sum = A(0);
+  for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
+    const Vec<T> v = lds_vec(srow + i);
+#pragma unroll
+    for (int k = 0; k < V; ++k) sum += row_exp<A>(cvt<A>(v.v[k]), gm, nml);
+  }
+  sum = block_reduce(sum, AddF<A>(), A(0), red);
+  if (threadIdx.x == 0) xchg[1] = sum;
+  cluster.sync();
+  A gs = A(0);
+  for (unsigned r = 0; r < cs; ++r) gs += *cluster.map_shared_rank(&xchg[1], r);
+  const A inv = A(1) / gs;
+  // sweep 3: normalise and store
+  for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
+    const Vec<T> v = lds_vec(srow + i);
+    Vec<T> o;
+#pragma unroll
+    for (int k = 0; k < V; ++k) o.v[k] = cvt<T>(row_exp<A>(cvt<A>(v.v[k]), gm, nml) * inv);
+    st_stream(dst + i, o);
+  }
+  cluster.sync();  // nobody leaves while a peer may still be reading its xchg[]
+}
+
 // ---- rows_stream -----------------------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(1024) softmax_rows_stream_kernel(const T* x, T* y, int64_t dim) {
@@ -369,6 +467,7 @@ int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, cudaStream_t 
   };
   const bool exact = (int64_t)threads * C == nchunk;
 #define PDB_SM_PIPE(CC) return exact ? launch(softmax_pipe_kernel<T, CC, true>) : launch(softmax_pipe_kernel<T, CC, false>);
+  if (C == 8) { PDB_SM_PIPE(8) }
   if (C == 4) { PDB_SM_PIPE(4) }
   if (C == 2) { PDB_SM_PIPE(2) }
   PDB_SM_PIPE(1)
@@ -376,6 +475,48 @@ int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, cudaStream_t 
 }
 template <>
 int try_softmax_pipe<double>(const double*, double*, int64_t, int64_t, cudaStream_t) { return -1; }
+
+// Cluster route: returns < 0 when the row does not fit 8 CTAs' shared memory.
+template <typename T>
+int try_softmax_cluster(const T* x, T* y, int64_t outer, int64_t dim, cudaStream_t st) {
+  constexpr int VN = Vec<T>::N;
+  const size_t row_bytes = (size_t)dim * sizeof(T);
+  const size_t kMaxSlice = 200 * 1024;
+  int cs = 1;
+  // split until a slice is <= 32 KB (several CTAs then share an SM and overlap their phases), and
+  // further while there are too few rows to fill the SMs
+  while (cs < 8 && (row_bytes / cs > 32 * 1024 || outer * cs < 2 * (int64_t)sm_count())) cs <<= 1;
+  int64_t slice = (dim + cs - 1) / cs;
+  slice = (slice + VN - 1) / VN * VN;
+  if ((size_t)slice * sizeof(T) > kMaxSlice) return -1;
+  if (outer * cs > 0x7fffffffLL) return -1;
+  int threads = 256;
+  while (threads < 1024 && (int64_t)threads * VN * 16 < slice) threads <<= 1;
+  const size_t smem = (size_t)slice * sizeof(T);
+  auto kern = softmax_rows_cluster_kernel<T>;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxSlice) != cudaSuccess) {
+    cudaGetLastError();
+    return -1;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)(outer * cs));
+  cfg.blockDim = dim3(threads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cs;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, x, y, dim, slice);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return -1;  // e.g. the cluster cannot be co-scheduled with this much shared memory: fall back
+  }
+  return after_launch("softmax_rows_cluster");
+}
 
 template <typename T>
 int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, cudaStream_t st) {
@@ -396,6 +537,10 @@ int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, c
       while ((int64_t)C * G < nchunk) C <<= 1;
       return vec ? launch_rows_reg<T, true>(x, y, outer, (int)dim, G, C, st)
                  : launch_rows_reg<T, false>(x, y, outer, (int)dim, G, C, st);
+    }
+    if (vec) {
+      const int rc = try_softmax_cluster<T>(x, y, outer, dim, st);
+      if (rc >= 0) return rc;
     }
     if (outer > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "softmax: too many rows for one launch");
     const size_t smem = (size_t)dim * sizeof(A);

@@ -32,6 +32,15 @@ elif case in ("softmax_fp32", "softmax_bf16"):
     dt = torch.float32 if case.endswith("fp32") else torch.bfloat16
     x = (torch.randn((8, 32, 2048, 2048), device="cuda", generator=g) * 2).to(dt)  # 1/4 of config 4
     fn = lambda: F.softmax(x, axis=-1)
+elif case in ("softmax_vocab_bf16", "softmax_vocab_fp32"):
+    dt = torch.float32 if case.endswith("fp32") else torch.bfloat16
+    x = (torch.randn((4096, 128256), device="cuda", generator=g) * 2).to(dt)  # LLM-vocabulary rows
+    fn = lambda: F.softmax(x, axis=-1)
+elif case == "ln_long_bf16":
+    x = torch.randn((8192, 65536), device="cuda", generator=g).to(torch.bfloat16)
+    w = torch.rand(65536, device="cuda", generator=g).to(torch.bfloat16)
+    b = torch.rand(65536, device="cuda", generator=g).to(torch.bfloat16)
+    fn = lambda: F.layer_norm(x, [65536], w, b)
 elif case == "sum_c1":
     x = torch.rand((4096, 4096), device="cuda", generator=g)
     fn = lambda: paddle.sum(x, axis=-1)
