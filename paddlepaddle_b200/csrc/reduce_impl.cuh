@@ -21,6 +21,7 @@
 #pragma once
 
 #include <limits>
+#include <type_traits>
 
 #include "common.cuh"
 #include "shape.h"
@@ -104,6 +105,24 @@ struct ArgMaxOp {
   }
 };
 
+// acc <- acc (+) element.  Every thread visits its elements in increasing index order, so argmax
+// can use the cheap "replace on strictly greater" rule here (first occurrence wins) and keep the
+// full index-aware combine() for merging accumulators.
+template <typename Op, typename T>
+__device__ __forceinline__ void accumulate(typename Op::Acc& a, T v, int64_t idx) {
+  a = Op::combine(a, Op::template lift<T>(v, idx));
+}
+template <typename V>
+struct ArgMaxOp;
+template <typename V, typename T>
+__device__ __forceinline__ void accumulate_argmax(KV<V>& a, T v, int64_t idx) {
+  const V x = cvt<V>(v);
+  if (x > a.val) {
+    a.val = x;
+    a.idx = idx;
+  }
+}
+
 // Finalisers: accumulator -> output element.
 template <typename A, typename O>
 struct CastFin {
@@ -116,8 +135,28 @@ struct MeanFin {  // sum / n at the very end (reduce_function.h:686-688); intege
 };
 template <typename V, typename O>
 struct IndexFin {
-  __device__ __forceinline__ O operator()(KV<V> a) const { return (O)a.idx; }
+  // idx is still the identity when no element ever compared greater than lowest() (a row of -inf,
+  // NaN or the type's minimum): Eigen's reducer starts at index 0 and never moves in that case.
+  __device__ __forceinline__ O operator()(KV<V> a) const {
+    return a.idx == std::numeric_limits<int64_t>::max() ? (O)0 : (O)a.idx;
+  }
 };
+
+template <typename V> struct IsArgMax { static constexpr bool value = false; };
+template <typename V> struct IsArgMax<ArgMaxOp<V>> { static constexpr bool value = true; };
+
+template <typename Op, typename T>
+__device__ __forceinline__ void acc_step(typename Op::Acc& a, T v, int64_t idx) {
+  if constexpr (IsArgMax<Op>::value) {
+    if constexpr (std::is_same<T, typename Op::Acc>::value) {
+      a = Op::combine(a, v);  // folding partial (value, index) pairs: indices are not ordered
+    } else {
+      accumulate_argmax(a, v, idx);
+    }
+  } else {
+    accumulate<Op, T>(a, v, idx);
+  }
+}
 
 constexpr int kRedUnroll = 4;
 
@@ -142,12 +181,12 @@ __device__ __forceinline__ typename Op::Acc fold_span(const T* __restrict__ row,
 #pragma unroll
       for (int u = 0; u < kRedUnroll; ++u)
 #pragma unroll
-        for (int k = 0; k < V; ++k) acc[u] = Op::combine(acc[u], Op::lift(v[u].v[k], i + u * step + k));
+        for (int k = 0; k < V; ++k) acc_step<Op, T>(acc[u], v[u].v[k], i + u * step + k);
     }
     for (; i < end; i += step) {
       Vec<T> v = ld_stream(row + i);
 #pragma unroll
-      for (int k = 0; k < V; ++k) acc[0] = Op::combine(acc[0], Op::lift(v.v[k], i + k));
+      for (int k = 0; k < V; ++k) acc_step<Op, T>(acc[0], v.v[k], i + k);
     }
   } else {
     for (; i + (kRedUnroll - 1) * step < end; i += kRedUnroll * step) {
@@ -155,9 +194,9 @@ __device__ __forceinline__ typename Op::Acc fold_span(const T* __restrict__ row,
 #pragma unroll
       for (int u = 0; u < kRedUnroll; ++u) v[u] = row[i + u * step];
 #pragma unroll
-      for (int u = 0; u < kRedUnroll; ++u) acc[u] = Op::combine(acc[u], Op::lift(v[u], i + u * step));
+      for (int u = 0; u < kRedUnroll; ++u) acc_step<Op, T>(acc[u], v[u], i + u * step);
     }
-    for (; i < end; i += step) acc[0] = Op::combine(acc[0], Op::lift(row[i], i));
+    for (; i < end; i += step) acc_step<Op, T>(acc[0], row[i], i);
   }
   // elements of acc[0..3] interleave in index order only loosely; combine() must be (and is)
   // insensitive to that: sums are re-associated, max/min/argmax are order-free by construction.
@@ -237,12 +276,12 @@ __global__ void __launch_bounds__(256) reduce_cols_kernel(const T* __restrict__ 
 #pragma unroll
         for (int u = 0; u < kRedUnroll; ++u)
 #pragma unroll
-          for (int k = 0; k < V; ++k) acc[k] = Op::combine(acc[k], Op::lift(v[u].v[k], r + u * TY));
+          for (int k = 0; k < V; ++k) acc_step<Op, T>(acc[k], v[u].v[k], r + u * TY);
       }
       for (; r < end; r += TY) {
         Vec<T> v = ld_stream(base + r * inner);
 #pragma unroll
-        for (int k = 0; k < V; ++k) acc[k] = Op::combine(acc[k], Op::lift(v.v[k], r));
+        for (int k = 0; k < V; ++k) acc_step<Op, T>(acc[k], v.v[k], r);
       }
     } else {
       for (; r + (kRedUnroll - 1) * TY < end; r += kRedUnroll * TY) {
@@ -250,9 +289,9 @@ __global__ void __launch_bounds__(256) reduce_cols_kernel(const T* __restrict__ 
 #pragma unroll
         for (int u = 0; u < kRedUnroll; ++u) v[u] = base[(r + u * TY) * inner];
 #pragma unroll
-        for (int u = 0; u < kRedUnroll; ++u) acc[0] = Op::combine(acc[0], Op::lift(v[u], r + u * TY));
+        for (int u = 0; u < kRedUnroll; ++u) acc_step<Op, T>(acc[0], v[u], r + u * TY);
       }
-      for (; r < end; r += TY) acc[0] = Op::combine(acc[0], Op::lift(base[r * inner], r));
+      for (; r < end; r += TY) acc_step<Op, T>(acc[0], base[r * inner], r);
     }
   }
   // fold the TY partials of each column through shared memory (tree over ty)

@@ -238,6 +238,14 @@ def test_argmax_routes_with_ties(port, shape, axis):
     assert np.array_equal(to_np(paddle.argmax(to_dev(xi), axis=axis)), port.argmax(xi, axis))
 
 
+def test_argmax_degenerate_rows(port):
+    x = np.array([[-np.inf, -np.inf, -np.inf], [-np.inf, 5.0, 5.0], [np.finfo(np.float32).min] * 3], np.float32)
+    assert np.array_equal(to_np(paddle.argmax(to_dev(x), axis=1)), port.argmax(x, 1))
+    xi = np.full((4, 7), np.iinfo(np.int32).min, np.int32)
+    xi[2, 5] = 3
+    assert np.array_equal(to_np(paddle.argmax(to_dev(xi), axis=1)), port.argmax(xi, 1))
+
+
 # ------------------------------------------------------------------------------------------
 # softmax
 # ------------------------------------------------------------------------------------------
