@@ -97,6 +97,24 @@ PDB200_API int pdb200_add(const void* x, const int64_t* x_dims, int x_rank, cons
 PDB200_API int pdb200_multiply(const void* x, const int64_t* x_dims, int x_rank, const void* y,
                     const int64_t* y_dims, int y_rank, void* out, int dtype, void* stream);
 
+/* The other binary ops on the same broadcast engine.
+ * Replace phi::SubtractKernel / DivideKernel / MaximumKernel / MinimumKernel<T, GPUContext>
+ *   (paddle/phi/kernels/kps/elementwise_kernel.cu:30-53,183-202,338-381) with the functors of
+ *   paddle/phi/kernels/funcs/elementwise_functor.h:80-120,471-511.
+ * dtypes: subtract {f32,f64,i16,i32,i64,f16,bf16}; divide {f32,f64,i8,u8,i16,i32,i64,f16,bf16};
+ * maximum / minimum {f32,f64,i32,i64,f16,bf16} (the GPU registrations; complex is out of scope).
+ * maximum is `a > b ? a : b` and minimum `a < b ? a : b` (a NaN operand returns b), not fmax/fmin.
+ * Integer divide truncates toward zero; a zero divisor yields 0 (the reference raises
+ * "Integer division by zero" through a device-side assert, which a C-ABI kernel cannot do). */
+PDB200_API int pdb200_subtract(const void* x, const int64_t* x_dims, int x_rank, const void* y,
+                    const int64_t* y_dims, int y_rank, void* out, int dtype, void* stream);
+PDB200_API int pdb200_divide(const void* x, const int64_t* x_dims, int x_rank, const void* y,
+                  const int64_t* y_dims, int y_rank, void* out, int dtype, void* stream);
+PDB200_API int pdb200_maximum(const void* x, const int64_t* x_dims, int x_rank, const void* y,
+                   const int64_t* y_dims, int y_rank, void* out, int dtype, void* stream);
+PDB200_API int pdb200_minimum(const void* x, const int64_t* x_dims, int x_rank, const void* y,
+                   const int64_t* y_dims, int y_rank, void* out, int dtype, void* stream);
+
 /* ---------------------------------------------------------------------------
  * Reductions.  `axes` may hold negative values; n_axes == 0 or reduce_all != 0 or a full axis
  * set means "reduce everything" (phi::recompute_reduce_all, paddle/phi/core/kernel_utils.h:407-417).

@@ -131,6 +131,54 @@ int oracle_elementwise(int op, int dtype, const void* x, const int64_t* xd, int 
     sx *= a; sy *= b;
     numel *= od[i];
   }
+  if (op >= 2) {
+    /* subtract / divide / maximum / minimum: funcs/elementwise_functor.h:70-76 (a - b), :102-121 (a / b;
+     * integer divide raises on b == 0 — here rc 3), :471-475 (a > b ? a : b), :507-511 (a < b ? a : b).
+     * When x has the lower rank the CPU kernels swap the operands: subtract/divide through the Inverse
+     * functors (same value), maximum/minimum by evaluating f(y, x) (same value unless NaN / signed zero). */
+#define EW_OP2(T, SUB, DIV)                                                        \
+  switch (op) {                                                                    \
+    case 2: EW_LOOP(T, SUB) break;                                                 \
+    case 3: EW_LOOP(T, DIV) break;                                                 \
+    case 4: EW_LOOP(T, a > b ? a : b) break;                                       \
+    case 5: EW_LOOP(T, a < b ? a : b) break;                                       \
+    default: return 2;                                                             \
+  }
+#define EW_INT_DIVZERO(T)                                                          \
+  if (op == 3) {                                                                   \
+    int64_t ny = 1; for (int i = 0; i < yr; ++i) ny *= yd[i];                      \
+    for (int64_t i = 0; i < ny; ++i) if (((const T*)y)[i] == 0) return 3;          \
+  }
+    switch (dtype) {
+      case DT_FLOAT32: EW_OP2(float, a - b, a / b) break;
+      case DT_FLOAT64: EW_OP2(double, a - b, a / b) break;
+      case DT_INT32: EW_INT_DIVZERO(int32_t) EW_OP2(int32_t, (int32_t)((uint32_t)a - (uint32_t)b), (b == -1 ? (int32_t)(0u - (uint32_t)a) : a / b)) break;
+      case DT_INT64: EW_INT_DIVZERO(int64_t) EW_OP2(int64_t, (int64_t)((uint64_t)a - (uint64_t)b), (b == -1 ? (int64_t)(0ull - (uint64_t)a) : a / b)) break;
+      case DT_INT16: EW_INT_DIVZERO(int16_t) EW_OP2(int16_t, (int16_t)(a - b), (int16_t)(a / b)) break;
+      case DT_INT8: EW_INT_DIVZERO(int8_t) EW_OP2(int8_t, (int8_t)(a - b), (int8_t)(a / b)) break;
+      case DT_UINT8: EW_INT_DIVZERO(uint8_t) EW_OP2(uint8_t, (uint8_t)(a - b), (uint8_t)(a / b)) break;
+      case DT_BFLOAT16:
+        switch (op) {
+          case 2: EW_LOOP(uint16_t, f2bf(bf2f(a) - bf2f(b))) break;
+          case 3: EW_LOOP(uint16_t, f2bf(bf2f(a) / bf2f(b))) break;
+          case 4: EW_LOOP(uint16_t, bf2f(a) > bf2f(b) ? a : b) break;
+          case 5: EW_LOOP(uint16_t, bf2f(a) < bf2f(b) ? a : b) break;
+          default: return 2;
+        }
+        break;
+      case DT_FLOAT16:
+        switch (op) {
+          case 2: EW_LOOP(uint16_t, f2h(h2f(a) - h2f(b))) break;
+          case 3: EW_LOOP(uint16_t, f2h(h2f(a) / h2f(b))) break;
+          case 4: EW_LOOP(uint16_t, h2f(a) > h2f(b) ? a : b) break;
+          case 5: EW_LOOP(uint16_t, h2f(a) < h2f(b) ? a : b) break;
+          default: return 2;
+        }
+        break;
+      default: return 2;
+    }
+    return 0;
+  }
   const int add = (op == 0);
   switch (dtype) {
     case DT_FLOAT32: EW_LOOP(float, add ? a + b : a * b) break;

@@ -189,6 +189,32 @@ void ElementwiseOp(int op, const phi::DenseTensor& x, const phi::DenseTensor& y,
   }
 }
 
+// subtract / divide / maximum / minimum: routing of phi::SubtractKernel / DivideKernel<T,CPUContext>
+// (cpu/elementwise_subtract_kernel.cc:26-46, cpu/elementwise_divide_kernel.cc: inverse functor when x has the
+// lower rank) and of Maximum/MinimumRawKernel (legacy/cpu/elementwise_kernel.cc:24-47: always the plain functor).
+template <typename T>
+void ElementwiseOp2(int op, const phi::DenseTensor& x, const phi::DenseTensor& y, phi::DenseTensor* z) {
+  auto& ctx = GetCtx().ctx;
+  const bool x_larger = x.dims().size() >= y.dims().size();
+  switch (op) {
+    case 2:
+      if (x_larger) phi::funcs::ElementwiseCompute<phi::funcs::SubtractFunctor<T>, T>(ctx, x, y, phi::funcs::SubtractFunctor<T>(), z, -1);
+      else phi::funcs::ElementwiseCompute<phi::funcs::InverseSubtractFunctor<T>, T>(ctx, x, y, phi::funcs::InverseSubtractFunctor<T>(), z, -1);
+      break;
+    case 3:
+      if (x_larger) phi::funcs::ElementwiseCompute<phi::funcs::DivideFunctor<T>, T>(ctx, x, y, phi::funcs::DivideFunctor<T>(), z, -1);
+      else phi::funcs::ElementwiseCompute<phi::funcs::InverseDivideFunctor<T>, T>(ctx, x, y, phi::funcs::InverseDivideFunctor<T>(), z, -1);
+      break;
+    case 4:
+      phi::funcs::ElementwiseCompute<phi::funcs::MaximumFunctor<T>, T>(ctx, x, y, phi::funcs::MaximumFunctor<T>(), z, -1);
+      break;
+    case 5:
+      phi::funcs::ElementwiseCompute<phi::funcs::MinimumFunctor<T>, T>(ctx, x, y, phi::funcs::MinimumFunctor<T>(), z, -1);
+      break;
+    default: throw std::runtime_error("bad elementwise op");
+  }
+}
+
 // CUDA-build branch of the CPU layer_norm kernel, cpu/layer_norm_kernel.cc:48-102,
 // called through the reference's own helpers (RowwiseMean2D, ElementwiseCompute,
 // SubAndSquareFunctor, DivAndSqrtFunctor).  Only the statement order is ours.
@@ -279,7 +305,7 @@ int phi_ref_argmax(int dtype, const void* x, const int64_t* dims, int rank, int6
   });
 }
 
-// op: 0 add, 1 multiply.
+// op: 0 add, 1 multiply, 2 subtract, 3 divide, 4 maximum, 5 minimum.
 int phi_ref_elementwise(int op, int dtype, const void* x, const int64_t* xdims, int xrank,
                         const void* y, const int64_t* ydims, int yrank, const int64_t* odims,
                         int orank, void* out) {
@@ -287,6 +313,21 @@ int phi_ref_elementwise(int op, int dtype, const void* x, const int64_t* xdims, 
     auto xt = Wrap(x, xdims, xrank, dtype);
     auto yt = Wrap(y, ydims, yrank, dtype);
     auto ot = Wrap(out, odims, orank, dtype);
+    if (op >= 2) {
+      switch (dtype) {
+        case kFloat32: ElementwiseOp2<float>(op, xt, yt, &ot); break;
+        case kFloat64: ElementwiseOp2<double>(op, xt, yt, &ot); break;
+        case kInt32: ElementwiseOp2<int32_t>(op, xt, yt, &ot); break;
+        case kInt64: ElementwiseOp2<int64_t>(op, xt, yt, &ot); break;
+        case kInt16: ElementwiseOp2<int16_t>(op, xt, yt, &ot); break;
+        case kUInt8: ElementwiseOp2<uint8_t>(op, xt, yt, &ot); break;
+        case kInt8: ElementwiseOp2<int8_t>(op, xt, yt, &ot); break;
+        case kBFloat16: ElementwiseOp2<phi::dtype::bfloat16>(op, xt, yt, &ot); break;
+        case kFloat16: ElementwiseOp2<phi::dtype::float16>(op, xt, yt, &ot); break;
+        default: throw std::runtime_error("phi_ref_elementwise: bad dtype");
+      }
+      return;
+    }
     switch (dtype) {
       case kFloat32: ElementwiseOp<float>(op, xt, yt, &ot); break;
       case kFloat64: ElementwiseOp<double>(op, xt, yt, &ot); break;

@@ -9,6 +9,8 @@ this package does not need a GPU; calling an op without the built library or wit
 device raises — there is no fallback.
 """
 from . import distributed, nn  # noqa: F401
-from .ops import (add, add_, argmax, max, mean, min, multiply, multiply_, prod, sum)  # noqa: F401,A004
+from .ops import (add, add_, argmax, divide, max, maximum, mean, min, minimum, multiply, multiply_, prod,  # noqa: F401,A004
+                  subtract, sum)
 
-__all__ = ["add", "add_", "multiply", "multiply_", "sum", "mean", "max", "min", "prod", "argmax", "nn"]
+__all__ = ["add", "add_", "multiply", "multiply_", "subtract", "divide", "maximum", "minimum", "sum", "mean", "max",
+           "min", "prod", "argmax", "nn"]

@@ -28,6 +28,10 @@ SIGNATURES = {
     "pdb200_broadcast_shape": (_int, [_c_i64p, _int, _c_i64p, _int, _c_i64p, ctypes.POINTER(_int)]),
     "pdb200_add": (_int, [_vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
     "pdb200_multiply": (_int, [_vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
+    "pdb200_subtract": (_int, [_vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
+    "pdb200_divide": (_int, [_vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
+    "pdb200_maximum": (_int, [_vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
+    "pdb200_minimum": (_int, [_vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
     "pdb200_reduce_workspace_bytes": (_sz, [_int, _c_i64p, _int, _c_i64p, _int, _int, _int, _int]),
     "pdb200_sum_raw": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _int, _vp, _vp, _sz, _vp]),
     "pdb200_mean_raw": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _int, _vp, _vp, _sz, _vp]),

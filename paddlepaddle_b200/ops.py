@@ -126,6 +126,26 @@ def multiply_(x, y, name=None):
     return _elementwise("pdb200_multiply", x, y, out=x)
 
 
+def subtract(x, y, name=None):
+    """paddle.subtract(x, y) (python/paddle/tensor/math.py): x - y with broadcasting."""
+    return _elementwise("pdb200_subtract", x, y)
+
+
+def divide(x, y, name=None):
+    """paddle.divide(x, y): true division for floats, truncating division for integers."""
+    return _elementwise("pdb200_divide", x, y)
+
+
+def maximum(x, y, name=None):
+    """paddle.maximum(x, y): elementwise `x > y ? x : y`."""
+    return _elementwise("pdb200_maximum", x, y)
+
+
+def minimum(x, y, name=None):
+    """paddle.minimum(x, y): elementwise `x < y ? x : y`."""
+    return _elementwise("pdb200_minimum", x, y)
+
+
 # ---------------------------------------------------------------------------------------
 # reductions
 # ---------------------------------------------------------------------------------------

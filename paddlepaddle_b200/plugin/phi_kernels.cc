@@ -87,6 +87,20 @@ void MultiplyKernel(const Context& ctx, const DenseTensor& x, const DenseTensor&
                         static_cast<int>(yd.size()), o, Code(x.dtype()), ctx.stream()));
 }
 
+#define PDB200_PHI_BINARY(Name, fn)                                                                      \
+  template <typename T, typename Context>                                                                \
+  void Name##Kernel(const Context& ctx, const DenseTensor& x, const DenseTensor& y, DenseTensor* out) {  \
+    T* o = ctx.template Alloc<T>(out);                                                                   \
+    auto xd = Dims(x), yd = Dims(y);                                                                     \
+    Check(fn(x.data<T>(), xd.data(), static_cast<int>(xd.size()), y.data<T>(), yd.data(),                \
+             static_cast<int>(yd.size()), o, Code(x.dtype()), ctx.stream()));                            \
+  }
+PDB200_PHI_BINARY(Subtract, pdb200_subtract)
+PDB200_PHI_BINARY(Divide, pdb200_divide)
+PDB200_PHI_BINARY(Maximum, pdb200_maximum)
+PDB200_PHI_BINARY(Minimum, pdb200_minimum)
+#undef PDB200_PHI_BINARY
+
 // ---- reductions --------------------------------------------------------------------------
 typedef int (*ReduceFn)(const void*, const int64_t*, int, const int64_t*, int, int, int, int, void*, void*,
                         size_t, void*);
@@ -199,6 +213,15 @@ PD_REGISTER_KERNEL(add, GPU, ALL_LAYOUT, pdb200_phi::AddKernel, float, double, i
                    int8_t, int64_t, phi::dtype::float16, phi::dtype::bfloat16) {}
 PD_REGISTER_KERNEL(multiply, GPU, ALL_LAYOUT, pdb200_phi::MultiplyKernel, float, double, int16_t, int, bool,
                    uint8_t, int8_t, int64_t, phi::dtype::float16, phi::dtype::bfloat16) {}
+// siblings on the same engine (kps/elementwise_kernel.cu:183-202,338-381; complex stays with the in-tree kernels)
+PD_REGISTER_KERNEL(subtract, GPU, ALL_LAYOUT, pdb200_phi::SubtractKernel, float, double, int16_t, int, int64_t,
+                   phi::dtype::float16, phi::dtype::bfloat16) {}
+PD_REGISTER_KERNEL(divide, GPU, ALL_LAYOUT, pdb200_phi::DivideKernel, float, double, int8_t, uint8_t, int16_t, int,
+                   int64_t, phi::dtype::float16, phi::dtype::bfloat16) {}
+PD_REGISTER_KERNEL(maximum, GPU, ALL_LAYOUT, pdb200_phi::MaximumKernel, float, double, int, int64_t,
+                   phi::dtype::float16, phi::dtype::bfloat16) {}
+PD_REGISTER_KERNEL(minimum, GPU, ALL_LAYOUT, pdb200_phi::MinimumKernel, float, double, int, int64_t,
+                   phi::dtype::float16, phi::dtype::bfloat16) {}
 PD_REGISTER_KERNEL(sum_raw, GPU, ALL_LAYOUT, pdb200_phi::SumRawKernel, bool, float, double, phi::dtype::float16,
                    phi::dtype::bfloat16, int, int64_t) {
   kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);  // reduce_sum_kernel.cc:75-77

@@ -37,6 +37,15 @@ BCAST_CASES = [  # from test_elementwise_add_op.py:318-615
 ]
 
 
+SIBLING_CASES = [("same", (13, 17), (13, 17)), ("vec_last", (2, 10, 12), (12,)), ("four", (10, 3, 1, 4), (10, 1, 12, 1)),
+                 ("x_small", (10, 12), (2, 2, 10, 12)), ("col", (64, 33), (64, 1)), ("scalar0d", (3, 4), ())]
+SIBLING_OPS = {  # GPU registrations, kps/elementwise_kernel.cu:183-202,338-381
+    "float32": ("subtract", "divide", "maximum", "minimum"), "float64": ("subtract", "divide", "maximum", "minimum"),
+    "int32": ("subtract", "divide", "maximum", "minimum"), "int64": ("subtract", "divide", "maximum", "minimum"),
+    "int16": ("subtract", "divide"), "bfloat16": ("subtract", "divide", "maximum", "minimum"),
+}
+
+
 def main():
     ref = O.Oracle("ref")
     rng = np.random.default_rng(20261106)
@@ -123,6 +132,26 @@ def main():
             g[key + "_wb__out0"], g[key + "_wb__out1"], g[key + "_wb__out2"] = y, m, v
             y, m, v = ref.layer_norm(xin, bna, None, None, 1e-5)
             g[key + "_none__out0"] = y
+    # --- subtract / divide / maximum / minimum, appended last so that every array above
+    #     keeps the value it had before these were added ---
+    for name, xs, ys in SIBLING_CASES:
+        for dt in ("float32", "float64", "int32", "int64", "int16", "bfloat16"):
+            if dt == "bfloat16":
+                a = ref.f32_to_bf16(rng.standard_normal(xs).astype(np.float32))
+                b = ref.f32_to_bf16((rng.standard_normal(ys) + 3).astype(np.float32))
+                code = O.BFLOAT16
+            elif dt.startswith("float"):
+                a, b, code = rng.standard_normal(xs).astype(dt), (rng.standard_normal(ys) + 3).astype(dt), None
+            else:
+                info = np.iinfo(dt)
+                a = rng.integers(info.min, info.max, xs, dtype=dt, endpoint=True)
+                b = rng.integers(info.min, info.max, ys, dtype=dt, endpoint=True)
+                b[b == 0] = 1
+                code = None
+            key = f"ew2_{name}_{dt}"
+            g[key + "__in0"], g[key + "__in1"] = a, b
+            for op in SIBLING_OPS[dt]:
+                g[f"{key}_{op}__out"] = ref.elementwise(op, a, b, code)
     path = os.path.join(HERE, "phi_cpu_golden.npz")
     np.savez_compressed(path, **g)
     print(f"wrote {path}: {len(g)} arrays, {os.path.getsize(path) / 1e6:.2f} MB")

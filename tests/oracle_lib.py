@@ -89,7 +89,8 @@ class Oracle:
 
     # ---- ops -----------------------------------------------------------------------------
     def elementwise(self, op, x, y, code=None):
-        """op 'add'|'multiply'.  code overrides the dtype (BFLOAT16/FLOAT16 on uint16 arrays)."""
+        """op 'add'|'multiply'|'subtract'|'divide'|'maximum'|'minimum'.  code overrides the dtype
+        (BFLOAT16/FLOAT16 on uint16 arrays)."""
         x = np.ascontiguousarray(x)
         y = np.ascontiguousarray(y)
         code = NP2CODE[x.dtype] if code is None else code
@@ -97,7 +98,7 @@ class Oracle:
         out = np.empty(oshape, x.dtype)
         xd, xr = _dims(x.shape)
         yd, yr = _dims(y.shape)
-        opc = 0 if op == "add" else 1
+        opc = {"add": 0, "multiply": 1, "subtract": 2, "divide": 3, "maximum": 4, "minimum": 5}[op]
         if self.kind == "port":
             rc = self.lib.oracle_elementwise(opc, code, _vp(x), xd, xr, _vp(y), yd, yr, _vp(out))
         else:

@@ -17,7 +17,7 @@ from gpu_util import assert_half_close, to_dev, to_np
 pytestmark = pytest.mark.gpu
 
 import paddlepaddle_b200 as paddle  # noqa: E402
-from golden.make_golden import BCAST_CASES, REDUCE_CASES  # noqa: E402
+from golden.make_golden import BCAST_CASES, REDUCE_CASES, SIBLING_CASES, SIBLING_OPS  # noqa: E402
 
 F = paddle.nn.functional
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "phi_cpu_golden.npz")
@@ -81,6 +81,60 @@ def test_elementwise_routes(port, xs, ys, dt):
         got = to_np(fn(ta, tb))
         want = port.elementwise(op, a, b, code)
         assert np.array_equal(got.view(np.uint8), want.view(np.uint8)), (op, xs, ys, dt)
+
+
+_SIB = {"subtract": paddle.subtract, "divide": paddle.divide, "maximum": paddle.maximum, "minimum": paddle.minimum}
+
+
+def test_sibling_elementwise_golden(gold):
+    """subtract / divide / maximum / minimum: bit-exact against the reference CPU kernels."""
+    for name, xs, ys in SIBLING_CASES:
+        for dt, ops in SIBLING_OPS.items():
+            a, b = gold[f"ew2_{name}_{dt}__in0"], gold[f"ew2_{name}_{dt}__in1"]
+            half = "bf16" if dt == "bfloat16" else None
+            ta, tb = to_dev(a, half), to_dev(b, half)
+            for op in ops:
+                got = to_np(_SIB[op](ta, tb))
+                want = gold[f"ew2_{name}_{dt}_{op}__out"]
+                assert got.shape == want.shape and np.array_equal(got.view(np.uint8), want.view(np.uint8)), (name, dt, op)
+
+
+@pytest.mark.parametrize("xs,ys", [((257, 4096), (4096,)), ((4096,), (257, 4096)), ((512, 2048), (512, 1)),
+                                   ((512, 1), (512, 2048)), ((1000003,), (1000003,)), ((64, 1, 32), (1, 48, 32)),
+                                   ((1, 100000), (1,)), ((33, 1001), (1001,))])
+@pytest.mark.parametrize("dt", ["float32", "bfloat16", "float16", "int32", "int64"])
+def test_sibling_elementwise_routes(port, xs, ys, dt):
+    """Non-commutative ops through every broadcast route, with the small operand on either side."""
+    rng = np.random.default_rng(hash((xs, ys, dt, "sib")) & 0xffff)
+    half, code = None, None
+    if dt in ("bfloat16", "float16"):
+        conv = port.f32_to_bf16 if dt == "bfloat16" else port.f32_to_fp16
+        a = conv(rng.standard_normal(xs).astype(np.float32))
+        b = conv((rng.standard_normal(ys) + 3).astype(np.float32))
+        half, code = ("bf16", O.BFLOAT16) if dt == "bfloat16" else ("fp16", O.FLOAT16)
+    elif dt == "float32":
+        a, b = rng.standard_normal(xs).astype(np.float32), (rng.standard_normal(ys) + 3).astype(np.float32)
+    else:
+        info = np.iinfo(dt)
+        a = rng.integers(info.min, info.max, xs, dtype=dt, endpoint=True)
+        b = rng.integers(info.min, info.max, ys, dtype=dt, endpoint=True)
+        b[b == 0] = 1
+    ta, tb = to_dev(a, half), to_dev(b, half)
+    for op, fn in _SIB.items():
+        got = to_np(fn(ta, tb))
+        want = port.elementwise(op, a, b, code)
+        assert np.array_equal(got.view(np.uint8), want.view(np.uint8)), (op, xs, ys, dt)
+
+
+def test_sibling_dtype_gates_and_integer_divide_by_zero():
+    with pytest.raises(NotImplementedError):
+        paddle.maximum(torch.zeros(4, dtype=torch.int8, device="cuda"), torch.zeros(4, dtype=torch.int8, device="cuda"))
+    with pytest.raises(NotImplementedError):
+        paddle.subtract(torch.zeros(4, dtype=torch.bool, device="cuda"), torch.zeros(4, dtype=torch.bool, device="cuda"))
+    # documented deviation: the reference raises through a device-side assert; a zero divisor yields 0 here
+    x = torch.tensor([7, -7, 0, -2**31], dtype=torch.int32, device="cuda")
+    y = torch.tensor([0, 2, 0, -1], dtype=torch.int32, device="cuda")
+    assert to_np(paddle.divide(x, y)).tolist() == [0, -3, 0, -2**31]
 
 
 def test_elementwise_inplace_and_unaligned(port):

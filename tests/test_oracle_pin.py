@@ -32,7 +32,7 @@ def _axis_of(name, table):
     raise KeyError(name)
 
 
-from golden.make_golden import BCAST_CASES, REDUCE_CASES  # noqa: E402
+from golden.make_golden import BCAST_CASES, REDUCE_CASES, SIBLING_CASES, SIBLING_OPS  # noqa: E402
 
 
 def test_doc_known_answers(port, gold):
@@ -80,6 +80,22 @@ def test_elementwise_golden(port, gold):
                 want = gold[f"ew_{name}_{dt}_{op}__out"]
                 assert np.array_equal(got.view(np.uint8), want.view(np.uint8)), (name, dt, op)
     assert np.array_equal(port.f32_to_bf16(gold["bf16_round__in0"]), gold["bf16_round__out"])
+
+
+def test_sibling_elementwise_golden(port, gold):
+    n = 0
+    for name, xs, ys in SIBLING_CASES:
+        for dt, ops in SIBLING_OPS.items():
+            a, b = gold[f"ew2_{name}_{dt}__in0"], gold[f"ew2_{name}_{dt}__in1"]
+            code = O.BFLOAT16 if dt == "bfloat16" else None
+            for op in ops:
+                got = port.elementwise(op, a, b, code)
+                want = gold[f"ew2_{name}_{dt}_{op}__out"]
+                assert np.array_equal(got.view(np.uint8), want.view(np.uint8)), (name, dt, op)
+                n += 1
+    assert n == len(SIBLING_CASES) * 22
+    with pytest.raises(ValueError):  # integer division by zero is an error on the CPU (elementwise_functor.h:98-115)
+        port.elementwise("divide", np.ones(3, np.int32), np.zeros(3, np.int32))
 
 
 def test_argmax_golden(port, gold):
