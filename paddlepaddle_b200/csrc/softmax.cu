@@ -451,7 +451,9 @@ int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, cudaStream_t 
   // (8 values): profiles/r1_sweep.txt
   int C = sizeof(T) == 2 ? (nchunk >= 256 ? 4 : (nchunk >= 128 ? 2 : 1)) : (nchunk >= 256 ? 2 : 1);
   if (const int o = pipe_c_override("PDB200_SOFTMAX_PIPE_C")) C = o;
+  while (C < 8 && (nchunk + C - 1) / C > 512) C <<= 1;  // the kernel is built for <= 512 threads
   int threads = (int)((nchunk + C - 1) / C);
+  if (threads > 512) return -1;
   threads = (threads + 31) / 32 * 32;
   const size_t row_bytes = (size_t)dim * sizeof(T);
   auto launch = [&](auto kern) -> int {

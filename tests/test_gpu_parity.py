@@ -314,6 +314,8 @@ def test_softmax_golden(gold):
 
 @pytest.mark.parametrize("shape,axis", [((64, 2048), -1), ((33, 1001), -1), ((1000, 7), -1), ((16, 4096), -1),
                                         ((5, 20000), -1), ((3, 60001), -1), ((2, 300000), -1), ((600, 32768), -1), ((40, 128256), -1),
+                                        # >= 4 rows per SM: the TMA row-pipeline route (exact and ragged chunk counts)
+                                        ((700, 2048), -1), ((600, 8192), -1), ((1300, 512), -1), ((650, 1000), -1), ((600, 4104), -1),
                                         ((8, 100, 64), 1), ((4, 17, 5, 3), 1), ((50, 1), -1)])
 def test_softmax_routes(port, shape, axis):
     rng = np.random.default_rng(14)
@@ -361,7 +363,9 @@ def test_layer_norm_golden(gold):
 
 
 @pytest.mark.parametrize("rows,D", [(64, 8192), (33, 1001), (1000, 24), (7, 2048), (5, 4096), (3, 16384),
-                                    (2, 40000), (2, 100000), (16, 768), (9, 257), (300, 20000), (40, 131072)])
+                                    (2, 40000), (2, 100000), (16, 768), (9, 257), (300, 20000), (40, 131072),
+                                    # >= 4 rows per SM: the TMA row-pipeline route
+                                    (700, 8192), (650, 1024), (600, 4096), (620, 2000), (600, 16384), (1200, 520)])
 def test_layer_norm_routes(port, rows, D):
     rng = np.random.default_rng(15)
     x = (rng.standard_normal((rows, D)) * (1 + np.arange(rows)[:, None] % 7) + np.arange(rows)[:, None] % 3).astype(np.float32)
