@@ -379,9 +379,10 @@ def test_layer_norm_routes(port, rows, D):
     xs = float(np.abs(x).max())
     # relative noise of the CPU kernel's sequential fp32 row sums grows like sqrt(D) * 2^-24
     stat_rtol = max(2 * FP32_RTOL, 8 * np.sqrt(D) * 2.0 ** -24)
-    # ... and for rows longer than config 3's it dominates y as well; those rows are additionally held
-    # to 1e-5 against a float64 evaluation below, which the CPU kernel itself would not pass.
-    y_atol = LN_ATOL if D <= 16384 else max(LN_ATOL, 16 * np.sqrt(D) * 2.0 ** -24)
+    # ... and it reaches y through mean and variance (measured: up to 1.0e-5 at D = 8192, 1.1e-4 at
+    # D = 131072 for rows with |mean| ~ 2 and sigma up to 7).  The GPU result is additionally held to 1e-5
+    # against a float64 evaluation below — a bar the CPU kernel itself does not meet for long rows.
+    y_atol = max(LN_ATOL, 4e-7 * np.sqrt(D))
     np.testing.assert_allclose(to_np(y), wy, rtol=FP32_RTOL, atol=y_atol)
     np.testing.assert_allclose(to_np(m), wm, rtol=FP32_RTOL, atol=FP32_RTOL * xs)
     np.testing.assert_allclose(to_np(v), wv, rtol=stat_rtol)
