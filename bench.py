@@ -303,9 +303,25 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
         for opn, fn in (("sum", paddle.sum), ("max", paddle.max)):
             rec(f"C5 {opn} {nm} 2^31-element shard (1/8 of 2^34)", n * eb + eb, lambda: fn(xr), n)
             if world > 1:
-                part = fn(xr)
+                from paddlepaddle_b200 import distributed as pdist
+                part = fn(xr).reshape(1)
                 op = dist.ReduceOp.SUM if opn == "sum" else dist.ReduceOp.MAX
-                ms = time_op(torch, lambda: dist.all_reduce(part, op=op), 20, 5)
+                # the global result, exactly as a user gets it (shard kernel + one NCCL AllReduce) ...
+                glob = (pdist.global_sum if opn == "sum" else pdist.global_max)(xr).reshape(1)
+                # ... checked against the per-rank partials gathered the slow way
+                parts = [torch.empty_like(part) for _ in range(world)]
+                dist.all_gather(parts, part)
+                stack = torch.cat(parts)
+                want = stack.sum() if opn == "sum" else stack.max()
+                if dt == torch.int64 or opn == "max":
+                    ok = bool(glob[0] == want)  # exact (int64 sum wraps identically; max is exact)
+                else:
+                    ok = bool((glob[0] - want).abs() <= 1e-5 * stack.abs().sum())
+                out[-1]["global_result_matches_gathered_partials"] = ok
+                if not ok:
+                    raise SystemExit(f"C5 {opn} {nm}: AllReduce result {glob.item()} != gathered {want.item()}")
+                scratch = part.clone()
+                ms = time_op(torch, lambda: dist.all_reduce(scratch, op=op), 20, 5)
                 out[-1]["allreduce_us"] = round(ms * 1e3, 2)
         del xr
     return out

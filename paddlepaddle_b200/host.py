@@ -10,14 +10,17 @@ import torch
 
 from . import ops
 
-_SLAB_BYTES = 64 << 20
+import os
+
+_SLAB_BYTES = int(os.environ.get("PDB200_HOST_SLAB_MB", "64")) << 20
+_NSTREAMS = int(os.environ.get("PDB200_HOST_STREAMS", "2"))
 _state = {}
 
 
 def _streams(device):
     st = _state.get(device)
     if st is None:
-        st = {"streams": [torch.cuda.Stream(device=device) for _ in range(2)], "bufs": {}}
+        st = {"streams": [torch.cuda.Stream(device=device) for _ in range(_NSTREAMS)], "bufs": {}}
         _state[device] = st
     return st
 
@@ -65,10 +68,10 @@ def _binary(fn_name, x, y, out=None, device=None):
     ready.record(cur)
     for k, r0 in enumerate(range(0, oshape[0], rows_per)):
         r1 = min(oshape[0], r0 + rows_per)
-        slot = k % 2
+        slot = k % _NSTREAMS
         s = st["streams"][slot]
         with torch.cuda.stream(s):
-            if k < 2:
+            if k < _NSTREAMS:
                 s.wait_event(ready)
             shp = (r1 - r0,) + tuple(oshape[1:])
             d_big = _staging(st, slot, "big", shp, x.dtype, device)
