@@ -215,6 +215,27 @@ PDB200_API int pdb200_layer_norm(const void* x, const int64_t* dims, int rank, c
                       const void* bias, int param_dtype, float epsilon, int begin_norm_axis,
                       int dtype, void* y, void* mean, void* variance, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * Backward kernels.
+ * softmax_grad: x_grad = (out_grad - sum(out * out_grad, axis)) * out.  Replaces phi::SoftmaxGradGPUDNNKernel /
+ *   SoftmaxGradKernel<T, GPUContext> (paddle/phi/kernels/gpudnn/softmax_grad_kernel.cu ->
+ *   softmax_gpudnn.h:1331-1407); numerics of paddle/phi/kernels/funcs/softmax_impl.h:275-308,406-445.
+ *   dtypes FLOAT32/FLOAT64/FLOAT16/BFLOAT16; 0-D yields 0; numel == 0 is a no-op; x_grad may alias out_grad.
+ * layer_norm_grad: Replaces phi::LayerNormGradKernel<T, GPUContext> (paddle/phi/kernels/gpu/layer_norm_grad_kernel.cu);
+ *   formulas of paddle/phi/kernels/cpu/layer_norm_grad_kernel.cc:28-155.  mean / variance are the forward
+ *   kernel's outputs (FLOAT32, or FLOAT64 for FLOAT64 x).  scale may be NULL; x_grad, scale_grad, bias_grad
+ *   may each be NULL (at least one is required); scale_grad / bias_grad have param_dtype (= dtype or FLOAT32).
+ *   Unlike the CPU kernel, scale is applied whenever it is given, not only when scale_grad is requested.
+ *   Scratch: pdb200_layer_norm_grad_workspace_bytes() bytes when scale_grad or bias_grad is requested.
+ * ------------------------------------------------------------------------- */
+PDB200_API int pdb200_softmax_grad(const void* out, const void* out_grad, const int64_t* dims, int rank, int axis,
+                        int dtype, void* x_grad, void* stream);
+PDB200_API size_t pdb200_layer_norm_grad_workspace_bytes(const int64_t* dims, int rank, int begin_norm_axis, int dtype);
+PDB200_API int pdb200_layer_norm_grad(const void* x, const int64_t* dims, int rank, const void* scale, int param_dtype,
+                           const void* mean, const void* variance, const void* out_grad, float epsilon,
+                           int begin_norm_axis, int dtype, void* x_grad, void* scale_grad, void* bias_grad,
+                           void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -17,7 +17,7 @@ if [ ! -d "$R/paddle/phi" ]; then
   echo "build_registry.sh: reference tree not found at $R - keeping prebuilt libraries" >&2
   exit 0
 fi
-mkdir -p "$OBJ"
+mkdir -p "$OBJ" "$OUT/plugin"
 CUDA_INC="${CUDA_HOME:-/usr/local/cuda}/include"
 CUDA_LIB="${CUDA_HOME:-/usr/local/cuda}/lib64"
 FLAGS="-std=c++17 -O1 -DNDEBUG -fPIC -w -DPADDLE_WITH_CUDA -DPADDLE_USE_REFERENCE_CBLAS -I$ROOT/include -I$HERE/stub -I$R -I$R/third_party/eigen3 -I$CUDA_INC"
@@ -42,9 +42,9 @@ for f in $TUS; do
 done
 build_one "$HERE/phi_registry_shim.cc" "$OBJ/shim.o" "" &
 # the binding itself is an out-of-tree build: PADDLE_WITH_CUSTOM_KERNEL as paddle.utils.cpp_extension passes it
-build_one "$ROOT/paddlepaddle_b200/plugin/phi_kernels.cc" "$OUT/plugin_phi_kernels.o" "-DPADDLE_WITH_CUSTOM_KERNEL" &
+build_one "$ROOT/paddlepaddle_b200/plugin/phi_kernels.cc" "$OUT/plugin/phi_kernels.o" "-DPADDLE_WITH_CUSTOM_KERNEL" &
 wait
 g++ -shared -o "$OUT/libphi_registry_min.so" "$OBJ"/*.o -Wl,--no-undefined -L"$CUDA_LIB" -lcudart -lpthread -ldl
-g++ -shared -o "$OUT/libpdb200_phi.so" "$OUT/plugin_phi_kernels.o" -L"$ROOT/paddlepaddle_b200" -lpdb200 \
+g++ -shared -o "$OUT/libpdb200_phi.so" "$OUT/plugin/phi_kernels.o" -L"$ROOT/paddlepaddle_b200" -lpdb200 \
     -Wl,-rpath,'$ORIGIN/../../paddlepaddle_b200'
 echo "built $OUT/libphi_registry_min.so and $OUT/libpdb200_phi.so"

@@ -522,3 +522,110 @@ int oracle_layer_norm(int dtype, const void* x, const int64_t* dims, int rank, c
   (void)dt_size;
   return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * softmax_grad.  phi::SoftmaxGradKernel<T,CPUContext>
+ *   (paddle/phi/kernels/impl/softmax_grad_kernel_impl.h:25-59): 0-D -> 0; 0-size -> no-op; else
+ *   SoftmaxGradFunctor<CPUContext> (paddle/phi/kernels/funcs/softmax_impl.h:406-445):
+ *   last axis + AVX: per row dot = vec_mul_reduce(dy, y) (float: 8 AVX lanes, then
+ *   ((l0+l1)+(l4+l5)) + ((l2+l3)+(l6+l7)), then the tail, funcs/cpu_vec.h:229-263; double: sequential);
+ *   dx = y * (dy + (-dot)).  Other axes: SoftmaxGradEigen (:275-308): dot = sum over the axis
+ *   (sequential), dx = (dy - dot) * y.
+ * ---------------------------------------------------------------------------------------- */
+static float vec_mul_reduce_avx_f32(const float* x, const float* y, int64_t n) {
+  if (n < 8) { float z = x[0] * y[0]; for (int64_t i = 1; i < n; ++i) z += x[i] * y[i]; return z; }
+  const int64_t end = n & ~(int64_t)7;
+  float l[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (int64_t i = 0; i < end; i += 8) for (int k = 0; k < 8; ++k) l[k] = l[k] + x[i + k] * y[i + k];
+  float z = ((l[0] + l[1]) + (l[4] + l[5])) + ((l[2] + l[3]) + (l[6] + l[7]));
+  for (int64_t i = end; i < n; ++i) z += x[i] * y[i];
+  return z;
+}
+
+int oracle_softmax_grad(int dtype, const void* out, const void* out_grad, const int64_t* dims, int rank, int axis,
+                        void* x_grad) {
+  if (dtype != DT_FLOAT32 && dtype != DT_FLOAT64) return 2;
+  int64_t numel = 1;
+  for (int i = 0; i < rank; ++i) numel *= dims[i];
+  if (rank == 0) { if (dtype == DT_FLOAT32) *(float*)x_grad = 0.f; else *(double*)x_grad = 0.0; return 0; }
+  if (numel == 0) return 0;
+  if (axis < -rank || axis >= rank) return 1;
+  if (axis < 0) axis += rank;
+  int64_t outer = 1, dim = dims[axis], inner = 1;
+  for (int i = 0; i < axis; ++i) outer *= dims[i];
+  for (int i = axis + 1; i < rank; ++i) inner *= dims[i];
+#define SMG_BODY(T, LAST_DOT)                                                              \
+  {                                                                                        \
+    const T* Y = (const T*)out; const T* G = (const T*)out_grad; T* DX = (T*)x_grad;       \
+    for (int64_t o = 0; o < outer; ++o)                                                    \
+      for (int64_t q = 0; q < inner; ++q) {                                                \
+        const T* y = Y + o * dim * inner + q; const T* g = G + o * dim * inner + q;        \
+        T* dx = DX + o * dim * inner + q;                                                  \
+        if (inner == 1) {                                                                  \
+          T dot = LAST_DOT;                                                                \
+          dot = dot * (T)-1;                                                               \
+          for (int64_t k = 0; k < dim; ++k) dx[k] = y[k] * (g[k] + dot);                   \
+        } else {                                                                           \
+          T dot = 0;                                                                       \
+          for (int64_t k = 0; k < dim; ++k) dot += y[k * inner] * g[k * inner];            \
+          for (int64_t k = 0; k < dim; ++k) dx[k * inner] = (g[k * inner] - dot) * y[k * inner]; \
+        }                                                                                  \
+      }                                                                                    \
+  }
+  if (dtype == DT_FLOAT32) SMG_BODY(float, vec_mul_reduce_avx_f32(g, y, dim))
+  else {
+#define SEQ_DOT_F64 ({ double z_ = g[0] * y[0]; for (int64_t i_ = 1; i_ < dim; ++i_) z_ += g[i_] * y[i_]; z_; })
+    SMG_BODY(double, SEQ_DOT_F64)
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * layer_norm_grad.  phi::LayerNormGradKernel<T,CPUContext> (paddle/phi/kernels/cpu/layer_norm_grad_kernel.cc:28-155):
+ *   xhat = (x - mean) / sqrt(var + eps)                 (SubtractFunctor, DivAndSqrtFunctor)
+ *   d_bias[j]  = sum over rows of dy[r][j]               (ColwiseSum: sequential over rows, math_function_impl.h)
+ *   d_scale[j] = sum over rows of xhat[r][j] * dy[r][j]
+ *   g = dy * scale  (when scale is given)                else g = dy
+ *   dx = ((g - rowmean(g)) - xhat * rowmean(g * xhat)) / sqrt(var + eps)
+ *   rowmean = sequential T sum times double 1/right (RowwiseMean).  Every step is a separate pass over
+ *   memory, hence separately rounded.  T = float or double.
+ *   (The CPU kernel multiplies by *scale exactly when d_scale is requested, :110-125; callers of this
+ *   oracle request d_scale whenever scale is given, which is also what the GPU kernel's contract is.)
+ * ---------------------------------------------------------------------------------------- */
+int oracle_layer_norm_grad(int dtype, const void* x, const int64_t* dims, int rank, const void* scale,
+                           const void* mean, const void* variance, const void* out_grad, float epsilon,
+                           int begin_norm_axis, void* x_grad, void* scale_grad, void* bias_grad) {
+  if (dtype != DT_FLOAT32 && dtype != DT_FLOAT64) return 2;
+  if (begin_norm_axis < 0 || begin_norm_axis > rank) return 1;
+  int64_t left = 1, right = 1;
+  for (int i = 0; i < rank; ++i) { if (i < begin_norm_axis) left *= dims[i]; else right *= dims[i]; }
+#define LNG_BODY(T, SQRT)                                                                          \
+  {                                                                                                \
+    const T* X = (const T*)x; const T* S = (const T*)scale; const T* M = (const T*)mean;           \
+    const T* V = (const T*)variance; const T* G = (const T*)out_grad;                              \
+    T* DX = (T*)x_grad; T* DS = (T*)scale_grad; T* DB = (T*)bias_grad;                             \
+    const double inv = 1.0 / (double)right; const T eps = (T)epsilon;                              \
+    T* xh = (T*)malloc(sizeof(T) * (size_t)(left * right)); T* tmp = (T*)malloc(sizeof(T) * (size_t)right); \
+    for (int64_t r = 0; r < left; ++r) {                                                           \
+      const T den = SQRT(V[r] + eps);                                                              \
+      for (int64_t j = 0; j < right; ++j) { T d = X[r * right + j] - M[r]; xh[r * right + j] = d / den; } \
+    }                                                                                              \
+    if (DB) for (int64_t j = 0; j < right; ++j) { T s = 0; for (int64_t r = 0; r < left; ++r) s += G[r * right + j]; DB[j] = s; } \
+    if (DS) for (int64_t j = 0; j < right; ++j) { T s = 0; for (int64_t r = 0; r < left; ++r) { T p = xh[r * right + j] * G[r * right + j]; s += p; } DS[j] = s; } \
+    if (DX) for (int64_t r = 0; r < left; ++r) {                                                   \
+      const T* g = G + r * right; const T* h = xh + r * right; T* dx = DX + r * right;             \
+      T sum = 0;                                                                                   \
+      for (int64_t j = 0; j < right; ++j) { tmp[j] = S ? (T)(g[j] * S[j]) : g[j]; sum += tmp[j]; } \
+      const T m1 = (T)(sum * inv);                                                                 \
+      sum = 0;                                                                                     \
+      for (int64_t j = 0; j < right; ++j) { dx[j] = tmp[j] - m1; T p = tmp[j] * h[j]; tmp[j] = p; sum += p; } \
+      const T m2 = (T)(sum * inv);                                                                 \
+      const T den = SQRT(V[r] + eps);                                                              \
+      for (int64_t j = 0; j < right; ++j) { T t = h[j] * m2; t = dx[j] - t; dx[j] = t / den; }     \
+    }                                                                                              \
+    free(xh); free(tmp);                                                                           \
+  }
+  if (dtype == DT_FLOAT32) LNG_BODY(float, sqrtf)
+  else LNG_BODY(double, sqrt)
+  return 0;
+}

@@ -20,6 +20,9 @@
 //   layer_norm  CUDA-build branch of phi::LayerNormKernel<T,CPUContext>
 //               paddle/phi/kernels/cpu/layer_norm_kernel.cc:32-102 (the other branch needs the
 //               generated jit/kernels.h, absent from the tree)
+//   softmax_grad    phi::SoftmaxGradKernel<T,CPUContext> paddle/phi/kernels/impl/softmax_grad_kernel_impl.h:25-59
+//               -> SoftmaxGradFunctor<CPUContext>  paddle/phi/kernels/funcs/softmax_impl.h:406-445
+//   layer_norm_grad phi::LayerNormGradKernel<T,CPUContext> paddle/phi/kernels/cpu/layer_norm_grad_kernel.cc:28-155
 //   bf16 scalar phi::dtype::bfloat16            paddle/phi/common/bfloat16.h:61-88,264-276
 //
 // All of them run single-threaded on Eigen::DefaultDevice, exactly as Paddle
@@ -57,8 +60,23 @@
 #include "paddle/phi/kernels/funcs/softmax.h"
 #include "paddle/phi/kernels/funcs/softmax_impl.h"
 #include "paddle/phi/kernels/impl/softmax_kernel_impl.h"
+#include "paddle/phi/kernels/impl/softmax_grad_kernel_impl.h"
+#include "paddle/phi/core/tensor_utils.h"
 
 #include "paddle/phi/kernels/cpu/arg_min_max_kernel.cc"  // NOLINT (kernel templates live in the .cc)
+#include "paddle/phi/kernels/cpu/layer_norm_grad_kernel.cc"  // NOLINT
+
+// phi::Copy lives in paddle/phi/core/tensor_utils.cc, whose CPU path goes through Paddle's memcpy
+// registry (fluid).  Host-to-host it is a memcpy; this is plumbing, not part of any algorithm under test.
+namespace phi {
+template <typename Context>
+void Copy(const Context& dev_ctx, const DenseTensor& src, Place, bool, DenseTensor* dst) {
+  dst->Resize(src.dims());
+  void* d = dev_ctx.Alloc(dst, src.dtype());
+  std::memcpy(d, src.data(), static_cast<size_t>(src.numel()) * phi::SizeOf(src.dtype()));
+}
+template void Copy<CPUContext>(const CPUContext&, const DenseTensor&, Place, bool, DenseTensor*);
+}  // namespace phi
 
 // Defined in paddle/phi/core/kernel_factory.cc, which is deliberately not part of
 // this build (no KernelFactory needed); DenseTensor only reads it.
@@ -375,6 +393,55 @@ int phi_ref_layer_norm(int dtype, const void* x, const int64_t* dims, int rank, 
       case kFloat32: LayerNormT<float>(xt, scale ? &st : nullptr, bias ? &bt : nullptr, epsilon, begin_norm_axis, &yt, &mt, &vt); break;
       case kFloat64: LayerNormT<double>(xt, scale ? &st : nullptr, bias ? &bt : nullptr, epsilon, begin_norm_axis, &yt, &mt, &vt); break;
       default: throw std::runtime_error("phi_ref_layer_norm: dtype not registered on CPU");
+    }
+  });
+}
+
+int phi_ref_softmax_grad(int dtype, const void* out, const void* out_grad, const int64_t* dims, int rank, int axis,
+                         void* x_grad) {
+  return Guard([&] {
+    auto yt = Wrap(out, dims, rank, dtype);
+    auto gt = Wrap(out_grad, dims, rank, dtype);
+    auto xt = Wrap(x_grad, dims, rank, dtype);
+    auto& ctx = GetCtx().ctx;
+    switch (dtype) {
+      case kFloat32: phi::SoftmaxGradKernel<float, phi::CPUContext>(ctx, yt, gt, axis, &xt); break;
+      case kFloat64: phi::SoftmaxGradKernel<double, phi::CPUContext>(ctx, yt, gt, axis, &xt); break;
+      default: throw std::runtime_error("phi_ref_softmax_grad: dtype not registered on CPU");
+    }
+  });
+}
+
+// scale may be NULL (then d_scale must be NULL too: the CPU kernel multiplies by *scale exactly when d_scale is
+// requested, cpu/layer_norm_grad_kernel.cc:110-125).  d_scale / d_bias may be NULL.
+int phi_ref_layer_norm_grad(int dtype, const void* x, const int64_t* dims, int rank, const void* scale,
+                            const void* mean, const void* variance, const void* out_grad, float epsilon,
+                            int begin_norm_axis, void* x_grad, void* scale_grad, void* bias_grad) {
+  return Guard([&] {
+    int64_t left = 1, right = 1;
+    for (int i = 0; i < begin_norm_axis; ++i) left *= dims[i];
+    for (int i = begin_norm_axis; i < rank; ++i) right *= dims[i];
+    auto xt = Wrap(x, dims, rank, dtype);
+    auto gt = Wrap(out_grad, dims, rank, dtype);
+    auto dxt = Wrap(x_grad, dims, rank, dtype);
+    auto mt = Wrap(mean, &left, 1, dtype);
+    auto vt = Wrap(variance, &left, 1, dtype);
+    paddle::optional<phi::DenseTensor> so, bo;
+    if (scale) so = Wrap(scale, &right, 1, dtype);
+    phi::DenseTensor ds, db;
+    if (scale_grad) ds = Wrap(scale_grad, &right, 1, dtype);
+    if (bias_grad) db = Wrap(bias_grad, &right, 1, dtype);
+    auto& ctx = GetCtx().ctx;
+    switch (dtype) {
+      case kFloat32:
+        phi::LayerNormGradKernel<float, phi::CPUContext>(ctx, xt, so, bo, mt, vt, gt, epsilon, begin_norm_axis, &dxt,
+                                                         scale_grad ? &ds : nullptr, bias_grad ? &db : nullptr);
+        break;
+      case kFloat64:
+        phi::LayerNormGradKernel<double, phi::CPUContext>(ctx, xt, so, bo, mt, vt, gt, epsilon, begin_norm_axis, &dxt,
+                                                          scale_grad ? &ds : nullptr, bias_grad ? &db : nullptr);
+        break;
+      default: throw std::runtime_error("phi_ref_layer_norm_grad: dtype not registered on CPU");
     }
   });
 }

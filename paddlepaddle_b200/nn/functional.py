@@ -10,7 +10,7 @@ import numbers
 import torch
 
 from .. import _lib as L
-from ..ops import _as_torch_dtype, _dtype_code, _ptr, _require_cuda, _stream
+from ..ops import _as_torch_dtype, _dtype_code, _ptr, _require_cuda, _stream, _workspace
 
 
 def softmax(x, axis=-1, dtype=None, name=None):
@@ -86,3 +86,52 @@ def layer_norm(x, normalized_shape, weight=None, bias=None, epsilon=1e-05, name=
     if return_stats:
         return y, mean, var
     return y
+
+
+# ---------------------------------------------------------------------------------------------------
+# backward kernels (what Paddle's autograd nodes call: _C_ops.softmax_grad / layer_norm_grad,
+# paddle/phi/ops/yaml/backward.yaml)
+# ---------------------------------------------------------------------------------------------------
+def softmax_grad(out, out_grad, axis=-1):
+    """x_grad of softmax given its output and the output's gradient."""
+    _require_cuda(out, out_grad)
+    if out.shape != out_grad.shape or out.dtype != out_grad.dtype:
+        raise ValueError("(InvalidArgument) out and out_grad must have the same shape and dtype")
+    lib = L.load()
+    out, out_grad = out.contiguous(), out_grad.contiguous()
+    x_grad = torch.empty_like(out)
+    d, r = L.dims_array(out.shape)
+    L.check(lib.pdb200_softmax_grad(_ptr(out), _ptr(out_grad), d, r, int(axis), _dtype_code(out.dtype), _ptr(x_grad),
+                                    _stream()), lib)
+    return x_grad
+
+
+def layer_norm_grad(x, normalized_shape, weight, mean, variance, out_grad, epsilon=1e-05, need_weight_grad=None,
+                    need_bias_grad=True):
+    """(x_grad, weight_grad or None, bias_grad or None) of layer_norm.  mean / variance are the forward
+    outputs (layer_norm(..., return_stats=True)).  weight_grad is produced when weight is given."""
+    _require_cuda(x, weight, mean, variance, out_grad)
+    if isinstance(normalized_shape, numbers.Integral):
+        normalized_shape = [normalized_shape]
+    n = len(list(normalized_shape))
+    begin_norm_axis = x.dim() - n
+    lib = L.load()
+    x, out_grad = x.contiguous(), out_grad.contiguous()
+    D = 1
+    for dd in normalized_shape:
+        D *= dd
+    pdt = weight.dtype if weight is not None else x.dtype
+    if need_weight_grad is None:
+        need_weight_grad = weight is not None
+    x_grad = torch.empty_like(x)
+    wg = torch.empty((D,), dtype=pdt, device=x.device) if need_weight_grad else None
+    bg = torch.empty((D,), dtype=pdt, device=x.device) if need_bias_grad else None
+    d, r = L.dims_array(x.shape)
+    nbytes = lib.pdb200_layer_norm_grad_workspace_bytes(d, r, begin_norm_axis, _dtype_code(x.dtype)) if (wg is not None or bg is not None) else 0
+    ws = _workspace(nbytes, x.device)
+    L.check(lib.pdb200_layer_norm_grad(_ptr(x), d, r, _ptr(weight.contiguous() if weight is not None else None),
+                                       _dtype_code(pdt), _ptr(mean.contiguous()), _ptr(variance.contiguous()),
+                                       _ptr(out_grad), ctypes.c_float(float(epsilon)), begin_norm_axis,
+                                       _dtype_code(x.dtype), _ptr(x_grad), _ptr(wg), _ptr(bg), _ptr(ws), nbytes,
+                                       _stream()), lib)
+    return x_grad, wg, bg

@@ -206,6 +206,43 @@ void LayerNormKernel(const Context& ctx, const DenseTensor& x, const paddle::opt
                           yo, mo, vo, ctx.stream()));
 }
 
+// ---- backward: softmax_grad_kernel.h:22-27, layer_norm_grad_kernel.h:22-35 ----
+template <typename T, typename Context>
+void SoftmaxGradKernel(const Context& ctx, const DenseTensor& out, const DenseTensor& out_grad, int axis,
+                       DenseTensor* x_grad) {
+  T* dx = ctx.template Alloc<T>(x_grad);
+  auto d = Dims(out);
+  Check(pdb200_softmax_grad(out.data<T>(), out_grad.data<T>(), d.data(), static_cast<int>(d.size()), axis,
+                            Code(out.dtype()), dx, ctx.stream()));
+}
+template <typename T, typename Context>
+void SoftmaxGradGPUDNNKernel(const Context& ctx, const DenseTensor& out, const DenseTensor& out_grad, int axis,
+                             DenseTensor* x_grad) {
+  SoftmaxGradKernel<T, Context>(ctx, out, out_grad, axis, x_grad);
+}
+
+template <typename T, typename Context>
+void LayerNormGradKernel(const Context& ctx, const DenseTensor& x, const paddle::optional<DenseTensor>& scale_opt,
+                         const paddle::optional<DenseTensor>& bias_opt, const DenseTensor& mean,
+                         const DenseTensor& variance, const DenseTensor& out_grad, float epsilon, int begin_norm_axis,
+                         DenseTensor* x_grad, DenseTensor* scale_grad, DenseTensor* bias_grad) {
+  auto* scale = scale_opt.get_ptr();
+  auto* bias = bias_opt.get_ptr();
+  DataType pdt = scale ? scale->dtype() : (bias ? bias->dtype() : x.dtype());
+  void* dx = x_grad ? ctx.Alloc(x_grad, x.dtype()) : nullptr;
+  void* ds = scale_grad ? ctx.Alloc(scale_grad, pdt) : nullptr;
+  void* db = bias_grad ? ctx.Alloc(bias_grad, pdt) : nullptr;
+  auto d = Dims(x);
+  const size_t bytes = (ds || db) ? pdb200_layer_norm_grad_workspace_bytes(d.data(), static_cast<int>(d.size()),
+                                                                           begin_norm_axis, Code(x.dtype()))
+                                  : 0;
+  DenseTensor holder;
+  void* ws = Scratch(ctx, bytes, &holder);
+  Check(pdb200_layer_norm_grad(x.data(), d.data(), static_cast<int>(d.size()), scale ? scale->data() : nullptr,
+                               Code(pdt), mean.data(), variance.data(), out_grad.data(), epsilon, begin_norm_axis,
+                               Code(x.dtype()), dx, ds, db, ws, bytes, ctx.stream()));
+}
+
 }  // namespace pdb200_phi
 
 // dtype lists = the in-tree GPU registrations this library covers.
@@ -257,4 +294,16 @@ PD_REGISTER_KERNEL(layer_norm, GPU, ALL_LAYOUT, pdb200_phi::LayerNormKernel, flo
                    phi::dtype::bfloat16) {
   kernel->OutputAt(1).SetDataType(phi::DataType::UNDEFINED);  // gpu/layer_norm_kernel.cu:688-690
   kernel->OutputAt(2).SetDataType(phi::DataType::UNDEFINED);
+}
+// backward kernels (gpudnn/softmax_grad_kernel.cu, gpu/softmax_grad_kernel.cu, gpu/layer_norm_grad_kernel.cu)
+PD_REGISTER_KERNEL(softmax_grad, GPUDNN, ALL_LAYOUT, pdb200_phi::SoftmaxGradGPUDNNKernel, float, double,
+                   phi::dtype::float16, phi::dtype::bfloat16) {}
+PD_REGISTER_KERNEL(softmax_grad, GPU, ALL_LAYOUT, pdb200_phi::SoftmaxGradKernel, float, double, phi::dtype::float16,
+                   phi::dtype::bfloat16) {}
+PD_REGISTER_KERNEL(layer_norm_grad, GPU, ALL_LAYOUT, pdb200_phi::LayerNormGradKernel, float, double,
+                   phi::dtype::float16, phi::dtype::bfloat16) {
+  if (kernel_key.dtype() == phi::DataType::FLOAT16 || kernel_key.dtype() == phi::DataType::BFLOAT16) {
+    kernel->OutputAt(1).SetDataType(phi::DataType::UNDEFINED);  // follows the scale dtype (x's or float32)
+    kernel->OutputAt(2).SetDataType(phi::DataType::UNDEFINED);
+  }
 }

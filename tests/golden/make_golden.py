@@ -46,6 +46,12 @@ SIBLING_OPS = {  # GPU registrations, kps/elementwise_kernel.cu:183-202,338-381
 }
 
 
+GRAD_SOFTMAX_CASES = [("g2", (10, 10), -1), ("g4_m1", (2, 3, 4, 5), -1), ("g4_1", (2, 3, 4, 5), 1), ("g4_0", (2, 3, 4, 5), 0),
+                      ("g_2048", (6, 2048), -1), ("g_odd", (3, 1001), -1)]
+GRAD_LN_CASES = [("g4", (2, 6, 6, 3), 1), ("g4_3", (2, 6, 6, 3), 3), ("g2_8192", (2, 8192), 1), ("g2_odd", (3, 1001), 1),
+                 ("g3", (2, 5, 768), 2)]
+
+
 def main():
     ref = O.Oracle("ref")
     rng = np.random.default_rng(20261106)
@@ -152,6 +158,27 @@ def main():
             g[key + "__in0"], g[key + "__in1"] = a, b
             for op in SIBLING_OPS[dt]:
                 g[f"{key}_{op}__out"] = ref.elementwise(op, a, b, code)
+    # --- backward kernels, appended after everything above ---
+    for name, shape, axis in GRAD_SOFTMAX_CASES:
+        for dt in (np.float32, np.float64):
+            y = ref.softmax((rng.standard_normal(shape) * 2).astype(dt), axis)
+            dy = rng.standard_normal(shape).astype(dt)
+            key = f"smg_{name}_{np.dtype(dt).name}"
+            g[key + "__in0"], g[key + "__in1"] = y, dy
+            g[key + "__out"] = ref.softmax_grad(y, dy, axis)
+    for name, shape, bna in GRAD_LN_CASES:
+        for dt in (np.float32, np.float64):
+            xin = (rng.standard_normal(shape) * 3 + 1).astype(dt)
+            D = int(np.prod(shape[bna:]))
+            w = rng.uniform(0.5, 1.5, D).astype(dt)
+            _, m, v = ref.layer_norm(xin, bna, w, None, 1e-5)
+            dy = rng.standard_normal(shape).astype(dt)
+            key = f"lng_{name}_{np.dtype(dt).name}"
+            g[key + "__in0"], g[key + "__in1"], g[key + "__in2"], g[key + "__in3"], g[key + "__in4"] = xin, w, m, v, dy
+            dx, ds, db = ref.layer_norm_grad(xin, bna, w, m, v, dy, 1e-5)
+            g[key + "_w__out0"], g[key + "_w__out1"], g[key + "_w__out2"] = dx, ds, db
+            dx, _, db = ref.layer_norm_grad(xin, bna, None, m, v, dy, 1e-5)
+            g[key + "_now__out0"], g[key + "_now__out2"] = dx, db
     path = os.path.join(HERE, "phi_cpu_golden.npz")
     np.savez_compressed(path, **g)
     print(f"wrote {path}: {len(g)} arrays, {os.path.getsize(path) / 1e6:.2f} MB")

@@ -172,6 +172,34 @@ class Oracle:
         self._check(rc)
         return y, mean, var
 
+    def softmax_grad(self, out, out_grad, axis=-1):
+        out = np.ascontiguousarray(out)
+        out_grad = np.ascontiguousarray(out_grad, out.dtype)
+        dx = np.empty_like(out)
+        d, r = _dims(out.shape)
+        rc = getattr(self.lib, self.p + "softmax_grad")(NP2CODE[out.dtype], _vp(out), _vp(out_grad), d, r, int(axis), _vp(dx))
+        self._check(rc)
+        return dx
+
+    def layer_norm_grad(self, x, begin_norm_axis, scale, mean, var, out_grad, epsilon=1e-5, want_bias_grad=True):
+        """Returns (dx, dscale or None, dbias or None).  dscale is produced exactly when scale is given."""
+        x = np.ascontiguousarray(x)
+        g = np.ascontiguousarray(out_grad, x.dtype)
+        D = int(np.prod(x.shape[begin_norm_axis:], dtype=np.int64))
+        dx = np.empty_like(x)
+        s = None if scale is None else np.ascontiguousarray(scale, x.dtype)
+        ds = None if scale is None else np.empty((D,), x.dtype)
+        db = np.empty((D,), x.dtype) if want_bias_grad else None
+        m = np.ascontiguousarray(mean, x.dtype)
+        v = np.ascontiguousarray(var, x.dtype)
+        d, r = _dims(x.shape)
+        rc = getattr(self.lib, self.p + "layer_norm_grad")(
+            NP2CODE[x.dtype], _vp(x), d, r, _vp(s) if s is not None else None, _vp(m), _vp(v), _vp(g),
+            ctypes.c_float(epsilon), int(begin_norm_axis), _vp(dx), _vp(ds) if ds is not None else None,
+            _vp(db) if db is not None else None)
+        self._check(rc)
+        return dx, ds, db
+
     def _check(self, rc):
         if rc != 0:
             msg = ""

@@ -17,7 +17,8 @@ from gpu_util import assert_half_close, to_dev, to_np
 pytestmark = pytest.mark.gpu
 
 import paddlepaddle_b200 as paddle  # noqa: E402
-from golden.make_golden import BCAST_CASES, REDUCE_CASES, SIBLING_CASES, SIBLING_OPS  # noqa: E402
+from golden.make_golden import (BCAST_CASES, GRAD_LN_CASES, GRAD_SOFTMAX_CASES, REDUCE_CASES,  # noqa: E402
+                                SIBLING_CASES, SIBLING_OPS)
 
 F = paddle.nn.functional
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "phi_cpu_golden.npz")
@@ -416,3 +417,91 @@ def test_layer_norm_errors():
         F.layer_norm(x, [8], torch.zeros(8, device="cuda", dtype=torch.float64))
     y = F.layer_norm(torch.zeros(2, 3, 4, device="cuda"), [3, 4])  # multi-dim normalized_shape
     assert y.shape == (2, 3, 4) and float(y.abs().max()) == 0.0
+
+
+# ------------------------------------------------------------------------------------------
+# backward kernels
+# ------------------------------------------------------------------------------------------
+def test_grad_kernels_golden(gold):
+    for name, shape, axis in GRAD_SOFTMAX_CASES:
+        for dt in ("float32", "float64"):
+            key = f"smg_{name}_{dt}"
+            got = to_np(F.softmax_grad(to_dev(gold[key + "__in0"]), to_dev(gold[key + "__in1"]), axis=axis))
+            np.testing.assert_allclose(got, gold[key + "__out"], rtol=FP32_RTOL if dt == "float32" else 1e-12,
+                                       atol=1e-7 if dt == "float32" else 1e-15)
+    for name, shape, bna in GRAD_LN_CASES:
+        for dt in ("float32", "float64"):
+            key = f"lng_{name}_{dt}"
+            x, w, m, v, dy = (gold[key + f"__in{i}"] for i in range(5))
+            ns = list(x.shape[bna:])
+            tol = dict(rtol=FP32_RTOL, atol=2e-5) if dt == "float32" else dict(rtol=1e-11, atol=1e-12)
+            dx, ds, db = F.layer_norm_grad(to_dev(x), ns, to_dev(w), to_dev(m), to_dev(v), to_dev(dy), 1e-5)
+            np.testing.assert_allclose(to_np(dx), gold[key + "_w__out0"], **tol)
+            np.testing.assert_allclose(to_np(ds), gold[key + "_w__out1"], **tol)
+            np.testing.assert_allclose(to_np(db), gold[key + "_w__out2"], **tol)
+            dx, ds, db = F.layer_norm_grad(to_dev(x), ns, None, to_dev(m), to_dev(v), to_dev(dy), 1e-5)
+            assert ds is None
+            np.testing.assert_allclose(to_np(dx), gold[key + "_now__out0"], **tol)
+            np.testing.assert_allclose(to_np(db), gold[key + "_now__out2"], **tol)
+
+
+@pytest.mark.parametrize("shape,axis", [((64, 2048), -1), ((700, 2048), -1), ((600, 8192), -1), ((650, 1000), -1), ((33, 1001), -1),
+                                        ((5, 20000), -1), ((8, 100, 64), 1), ((1300, 512), -1)])
+def test_softmax_grad_routes(port, shape, axis):
+    rng = np.random.default_rng(21)
+    y = port.softmax((rng.standard_normal(shape) * 2).astype(np.float32), axis)
+    dy = rng.standard_normal(shape).astype(np.float32)
+    want = port.softmax_grad(y, dy, axis)
+    got = to_np(F.softmax_grad(to_dev(y), to_dev(dy), axis=axis))
+    # |dx| <= |y| * (|dy| + |dot|): judge against that scale (dot is a cancelling sum)
+    scale = np.abs(y) * (np.abs(dy) + np.abs((y * dy).sum(axis, keepdims=True))) + 1e-30
+    assert np.all(np.abs(got - want) <= FP32_RTOL * scale + 1e-9)
+    for half, conv, back in (("bf16", port.f32_to_bf16, port.bf16_to_f32), ("fp16", port.f32_to_fp16, port.fp16_to_f32)):
+        yb, gb = conv(y), conv(dy)
+        want_h = conv(port.softmax_grad(back(yb), back(gb), axis))
+        got_h = to_np(F.softmax_grad(to_dev(yb, half), to_dev(gb, half), axis=axis))
+        assert_half_close(got_h, want_h, 1, f"softmax_grad {half} {shape}", kind=half, atol=1e-6)
+
+
+@pytest.mark.parametrize("rows,D", [(64, 8192), (700, 8192), (650, 1024), (620, 2000), (33, 1001), (1000, 24), (3, 16384), (2, 40000),
+                                    (1200, 520), (600, 4096)])
+def test_layer_norm_grad_routes(port, rows, D):
+    rng = np.random.default_rng(22)
+    x = (rng.standard_normal((rows, D)) * 2 + 0.5).astype(np.float32)
+    w = rng.uniform(0.5, 1.5, D).astype(np.float32)
+    dy = rng.standard_normal((rows, D)).astype(np.float32)
+    _, m, v = port.layer_norm(x, 1, w, None, 1e-5)
+    wdx, wds, wdb = port.layer_norm_grad(x, 1, w, m, v, dy, 1e-5)
+    dx, ds, db = F.layer_norm_grad(to_dev(x), [D], to_dev(w), to_dev(m), to_dev(v), to_dev(dy), 1e-5)
+    # column sums run over `rows` terms of size ~1: judge them against sum |terms|; the CPU kernel sums
+    # sequentially in fp32, so its own noise grows like sqrt(rows) * 2^-24 of that
+    col_scale = np.abs(dy).sum(0)
+    col_tol = max(FP32_RTOL, 4 * np.sqrt(rows) * 2.0 ** -24)
+    assert np.all(np.abs(to_np(db) - wdb) <= col_tol * col_scale + 1e-6)
+    xh = (x - m[:, None]) / np.sqrt(v[:, None] + 1e-5)
+    assert np.all(np.abs(to_np(ds) - wds) <= col_tol * np.abs(dy * xh).sum(0) + 1e-6)
+    np.testing.assert_allclose(to_np(dx), wdx, rtol=FP32_RTOL, atol=max(1e-5, 4e-7 * np.sqrt(D)))
+    # float64 truth
+    x64, dy64 = x.astype(np.float64), dy.astype(np.float64)
+    mu, var = x64.mean(1, keepdims=True), x64.var(1, keepdims=True)
+    xh64 = (x64 - mu) / np.sqrt(var + 1e-5)
+    g64 = dy64 * w
+    dx64 = (g64 - g64.mean(1, keepdims=True) - xh64 * (g64 * xh64).mean(1, keepdims=True)) / np.sqrt(var + 1e-5)
+    dxg = F.layer_norm_grad(to_dev(x), [D], to_dev(w), to_dev(x64.mean(1).astype(np.float32)),
+                            to_dev(x64.var(1).astype(np.float32)), to_dev(dy), 1e-5)[0]
+    np.testing.assert_allclose(to_np(dxg), dx64, rtol=FP32_RTOL, atol=5e-6)
+    # no scale, dx only
+    dx2, ds2, db2 = F.layer_norm_grad(to_dev(x), [D], None, to_dev(m), to_dev(v), to_dev(dy), 1e-5, need_bias_grad=False)
+    assert ds2 is None and db2 is None
+    np.testing.assert_allclose(to_np(dx2), port.layer_norm_grad(x, 1, None, m, v, dy, 1e-5)[0], rtol=FP32_RTOL,
+                               atol=max(1e-5, 4e-7 * np.sqrt(D)))
+    # bf16 tensors with bf16 scale: dx within 1 ulp (or 2e-5), parameter grads in bf16 within 1 ulp of the fp32 oracle
+    xb, wb, gb = port.f32_to_bf16(x), port.f32_to_bf16(w), port.f32_to_bf16(dy)
+    xf, wf, gf = port.bf16_to_f32(xb), port.bf16_to_f32(wb), port.bf16_to_f32(gb)
+    _, mb, vb = port.layer_norm(xf, 1, wf, None, 1e-5)
+    odx, ods, odb = port.layer_norm_grad(xf, 1, wf, mb, vb, gf, 1e-5)
+    gdx, gds, gdb = F.layer_norm_grad(to_dev(xb, "bf16"), [D], to_dev(wb, "bf16"), to_dev(mb), to_dev(vb), to_dev(gb, "bf16"), 1e-5)
+    assert gds.dtype == torch.bfloat16
+    assert_half_close(to_np(gdx), port.f32_to_bf16(odx), 1, f"ln_grad dx bf16 {rows}x{D}", atol=3e-5)
+    assert_half_close(to_np(gds), port.f32_to_bf16(ods), 1, f"ln_grad dscale bf16 {rows}x{D}", atol=float(col_tol * np.abs(gf * xh).sum(0).max()) + 1e-3)
+    assert_half_close(to_np(gdb), port.f32_to_bf16(odb), 1, f"ln_grad dbias bf16 {rows}x{D}", atol=float(col_tol * np.abs(gf).sum(0).max()) + 1e-3)

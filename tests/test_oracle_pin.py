@@ -32,7 +32,8 @@ def _axis_of(name, table):
     raise KeyError(name)
 
 
-from golden.make_golden import BCAST_CASES, REDUCE_CASES, SIBLING_CASES, SIBLING_OPS  # noqa: E402
+from golden.make_golden import (BCAST_CASES, GRAD_LN_CASES, GRAD_SOFTMAX_CASES, REDUCE_CASES,  # noqa: E402
+                                SIBLING_CASES, SIBLING_OPS)
 
 
 def test_doc_known_answers(port, gold):
@@ -133,6 +134,23 @@ def test_layer_norm_golden(port, gold):
             np.testing.assert_allclose(y, gold[key + "_wb__out0"], rtol=1e-6, atol=1e-7)
             y0, _, _ = port.layer_norm(x, bna, None, None, 1e-5)
             np.testing.assert_allclose(y0, gold[key + "_none__out0"], rtol=1e-6, atol=1e-7)
+
+
+def test_grad_kernels_golden(port, gold):
+    for name, shape, axis in GRAD_SOFTMAX_CASES:
+        for dt in ("float32", "float64"):
+            key = f"smg_{name}_{dt}"
+            got = port.softmax_grad(gold[key + "__in0"], gold[key + "__in1"], axis)
+            np.testing.assert_allclose(got, gold[key + "__out"], rtol=1e-6 if dt == "float32" else 1e-13, atol=1e-30)
+    for name, shape, bna in GRAD_LN_CASES:
+        for dt in ("float32", "float64"):
+            key = f"lng_{name}_{dt}"
+            x, w, m, v, dy = (gold[key + f"__in{i}"] for i in range(5))
+            dx, ds, db = port.layer_norm_grad(x, bna, w, m, v, dy, 1e-5)
+            assert np.array_equal(dx, gold[key + "_w__out0"]) and np.array_equal(ds, gold[key + "_w__out1"])
+            assert np.array_equal(db, gold[key + "_w__out2"])
+            dx, _, db = port.layer_norm_grad(x, bna, None, m, v, dy, 1e-5)
+            assert np.array_equal(dx, gold[key + "_now__out0"]) and np.array_equal(db, gold[key + "_now__out2"])
 
 
 # ---- live comparison with the compiled reference ----------------------------------------------

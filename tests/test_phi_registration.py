@@ -35,7 +35,8 @@ keys = json.loads(sys.argv[3])
 out["has"] = {f"{n}/{b}/{d}": reg.phi_min_has_kernel(n.encode(), b.encode(), d) for n, b, d in keys}
 ar = {}
 a, b_, c = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
-for n in ["add", "divide", "sum", "sum_raw", "mean", "max_raw", "prod", "argmax", "softmax", "layer_norm"]:
+for n in ["add", "divide", "sum", "sum_raw", "mean", "max_raw", "prod", "argmax", "softmax", "layer_norm", "softmax_grad",
+          "layer_norm_grad"]:
     reg.phi_min_arity(n.encode(), b"GPU", 10, ctypes.byref(a), ctypes.byref(b_), ctypes.byref(c))
     ar[n] = [a.value, b_.value, c.value]
 out["arity"] = ar
@@ -58,6 +59,7 @@ EXPECT = {  # the registrations of plugin/phi_kernels.cc
     "prod": "float32 float64 int32 int64 float16 bfloat16",
     "argmax": "float16 bfloat16 float32 float64 int32 int64 int16 uint8",
     "softmax": "float32 float64 float16 bfloat16", "layer_norm": "float32 float64 float16 bfloat16",
+    "softmax_grad": "float32 float64 float16 bfloat16", "layer_norm_grad": "float32 float64 float16 bfloat16",
 }
 
 
@@ -66,6 +68,7 @@ EXPECT = {  # the registrations of plugin/phi_kernels.cc
 def test_pd_register_kernel_overwrites_paddles_keys():
     keys = [(n, "GPU", DT[d]) for n, ds in EXPECT.items() for d in ds.split()]
     keys += [("softmax", "GPUDNN", DT[d]) for d in EXPECT["softmax"].split()]
+    keys += [("softmax_grad", "GPUDNN", DT[d]) for d in EXPECT["softmax_grad"].split()]
     r = subprocess.run([sys.executable, "-c", CHILD, REG, PLUG, json.dumps(keys)], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stderr[-2000:]
     out = json.loads(r.stdout.strip().splitlines()[-1])
@@ -78,6 +81,6 @@ def test_pd_register_kernel_overwrites_paddles_keys():
     # what the registrar parsed out of our C++ signatures == the in-tree signatures (inputs, attributes, outputs)
     assert out["arity"] == {"add": [2, 0, 1], "divide": [2, 0, 1], "sum": [1, 3, 1], "sum_raw": [1, 4, 1], "mean": [1, 2, 1],
                             "max_raw": [1, 3, 1], "prod": [1, 3, 1], "argmax": [1, 4, 1], "softmax": [1, 1, 1],
-                            "layer_norm": [3, 2, 3]}
+                            "layer_norm": [3, 2, 3], "softmax_grad": [2, 1, 1], "layer_norm_grad": [6, 2, 3]}
     # output dtypes left UNDEFINED where the in-tree registration bodies do so
     assert out["ln_out_dtypes"] == [DT["bfloat16"], 0, 0] and out["sum_out_dtype"] == 0 and out["argmax_out_dtype"] == 0
