@@ -76,23 +76,16 @@ ln_grad_pipe_kernel(const T* __restrict__ x, const T* __restrict__ dy, const P* 
     mbar_wait(&full[s], phase);
     const T* sx = ring + (size_t)s * 2 * D;
     const T* sg = sx + D;
-    Vec<T> rx[C], rg[C];
-#pragma unroll
-    for (int c = 0; c < C; ++c) {
-      const int off = (c * nt + tid) * V;
-      if (EXACT || off < D) {
-        rx[c] = lds_vec(sx + off);
-        rg[c] = lds_vec(sg + off);
-      }
-    }
+    // The row is read from shared memory twice (sums, then dx) instead of being parked in 32 registers:
+    // with the dscale/dbias accumulators that keeps the kernel under 128 registers without spills.
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       const int off = (c * nt + tid) * V;
       if (EXACT || off < D) {
         float xf[V], gf[V], w[V];
-        unpack_to_float<T>(rx[c], xf);
-        unpack_to_float<T>(rg[c], gf);
+        unpack_to_float<T>(lds_vec(sx + off), xf);
+        unpack_to_float<T>(lds_vec(sg + off), gf);
         if constexpr (HAS_SCALE) {
 #pragma unroll
           for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(scale + off + j * PV), &w[j * PV]);
@@ -117,17 +110,10 @@ ln_grad_pipe_kernel(const T* __restrict__ x, const T* __restrict__ dy, const P* 
       red[flip][0][warp] = s1;
       red[flip][1][warp] = s2;
     }
-    __syncthreads();  // also: every thread has read stage s
+    __syncthreads();
     s1 = group_reduce<32>(red[flip][0][lane], AddU2());
     s2 = group_reduce<32>(red[flip][1][lane], AddU2());
     flip ^= 1;
-    if (tid == 0) {
-      const int64_t nrow = row + (int64_t)stages * row_step;
-      if (nrow < rows) {
-        fence_proxy_async_smem();
-        fill(s, nrow);
-      }
-    }
     const float m1 = s1 * inv_d, m2 = s2 * inv_d;
     T* dst = dx + row * D;
 #pragma unroll
@@ -135,8 +121,8 @@ ln_grad_pipe_kernel(const T* __restrict__ x, const T* __restrict__ dy, const P* 
       const int off = (c * nt + tid) * V;
       if (EXACT || off < D) {
         float xf[V], gf[V], w[V], o[V];
-        unpack_to_float<T>(rx[c], xf);
-        unpack_to_float<T>(rg[c], gf);
+        unpack_to_float<T>(lds_vec(sx + off), xf);
+        unpack_to_float<T>(lds_vec(sg + off), gf);
         if constexpr (HAS_SCALE) {
 #pragma unroll
           for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(scale + off + j * PV), &w[j * PV]);
@@ -150,6 +136,14 @@ ln_grad_pipe_kernel(const T* __restrict__ x, const T* __restrict__ dy, const P* 
         Vec<T> ov;
         pack_from_float<T>(o, ov);
         st_stream(dst + off, ov);
+      }
+    }
+    __syncthreads();  // every thread has finished with stage s: hand it back to the copy engine
+    if (tid == 0) {
+      const int64_t nrow = row + (int64_t)stages * row_step;
+      if (nrow < rows) {
+        fence_proxy_async_smem();
+        fill(s, nrow);
       }
     }
     if (++s == stages) {

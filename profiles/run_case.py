@@ -41,6 +41,21 @@ elif case == "ln_long_bf16":
     w = torch.rand(65536, device="cuda", generator=g).to(torch.bfloat16)
     b = torch.rand(65536, device="cuda", generator=g).to(torch.bfloat16)
     fn = lambda: F.layer_norm(x, [65536], w, b)
+elif case in ("softmax_grad_fp32", "softmax_grad_bf16"):
+    dt = torch.float32 if case.endswith("fp32") else torch.bfloat16
+    y = torch.rand((8, 32, 2048, 2048), device="cuda", generator=g).to(dt)
+    dy = torch.randn((8, 32, 2048, 2048), device="cuda", generator=g).to(dt)
+    fn = lambda: F.softmax_grad(y, dy, axis=-1)
+elif case in ("ln_grad_bf16", "ln_grad_bf16_dx"):
+    x = torch.randn((65536, 8192), device="cuda", generator=g).to(torch.bfloat16)
+    dy = torch.randn((65536, 8192), device="cuda", generator=g).to(torch.bfloat16)
+    w = torch.rand(8192, device="cuda", generator=g).to(torch.bfloat16)
+    m = torch.zeros(65536, device="cuda")
+    v = torch.ones(65536, device="cuda")
+    if case.endswith("_dx"):
+        fn = lambda: F.layer_norm_grad(x, [8192], w, m, v, dy, need_weight_grad=False, need_bias_grad=False)
+    else:
+        fn = lambda: F.layer_norm_grad(x, [8192], w, m, v, dy)
 elif case == "sum_c1":
     x = torch.rand((4096, 4096), device="cuda", generator=g)
     fn = lambda: paddle.sum(x, axis=-1)
