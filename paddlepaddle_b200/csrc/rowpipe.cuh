@@ -20,6 +20,10 @@
 #include <stdint.h>
 #include <stdlib.h>
 
+#include <map>
+#include <mutex>
+#include <tuple>
+
 namespace pdb200 {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -110,6 +114,34 @@ inline bool pipe_geometry(Kern kern, int threads, size_t row_bytes, int want_cta
     if (atoi(v) >= 2) want_stages = atoi(v);
   }
   if (want_stages > kPipeMaxStages) want_stages = kPipeMaxStages;
+  // The answer depends only on (kernel, device, threads, row size, wishes): remember it, so that a launch
+  // costs one map lookup instead of a dozen attribute / occupancy calls.  The attributes set below are
+  // per-function state in the driver; every cached entry of one kernel re-applies its own pair on use.
+  struct Geo { int per_sm, stages; size_t smem; int pct; bool ok; };
+  static std::mutex mu;
+  static std::map<std::tuple<const void*, int, int, size_t, int, int>, Geo> cache;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const auto key = std::make_tuple(reinterpret_cast<const void*>(kern), dev, threads, row_bytes, want_ctas, want_stages);
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) {
+      const Geo& g = it->second;
+      if (!g.ok) return false;
+      // another shape of the same kernel may have changed the function attributes since
+      if (!ok(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, g.pct))) return false;
+      if (!ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem))) return false;
+      *grid_per_sm = g.per_sm;
+      *stages = g.stages;
+      *smem_bytes = g.smem;
+      return true;
+    }
+  }
+  auto remember = [&](const Geo& g) {
+    std::lock_guard<std::mutex> lock(mu);
+    cache[key] = g;
+  };
   if (!ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * (int)row_bytes))) return false;
   int occ = 0;
   if (!ok(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, 2 * row_bytes)) || occ < 1) return false;
@@ -130,10 +162,12 @@ inline bool pipe_geometry(Kern kern, int threads, size_t row_bytes, int want_cta
         *grid_per_sm = occ;
         *stages = st;
         *smem_bytes = smem;
+        remember(Geo{occ, st, smem, pct, true});
         return true;
       }
     }
   }
+  remember(Geo{0, 0, 0, 0, false});
   return false;
 }
 
