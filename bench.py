@@ -80,7 +80,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE,
+                                          "-lms", "20", "-i", str(self.gpu)], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._pump, daemon=True)
             self.t.start()
@@ -292,6 +292,27 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
             xs.view(-1)[i:i + chunk] = (torch.randn(chunk, device="cuda", generator=g) * 2).to(dt)
         rec(f"C4 softmax {nm} [32,32,2048,2048] axis=-1", 2 * n * eb, lambda: F.softmax(xs, axis=-1), n)
         del xs
+    # Widened rows, at the shapes of the configs they sit next to
+    xa = torch.randn(C2_SHAPE, device="cuda", generator=g).to(torch.bfloat16)
+    ya = torch.randn((C2_COLS,), device="cuda", generator=g).to(torch.bfloat16)
+    oa = torch.empty_like(xa)
+    for nm_, fn_ in (("subtract", "pdb200_subtract"), ("divide", "pdb200_divide"), ("maximum", "pdb200_maximum")):
+        rec(f"next: {nm_} bf16 [64,2048,4096]+[4096]", C2_BYTES_BF16, lambda f=fn_: _elementwise(f, xa, ya, out=oa), C2_ROWS * C2_COLS)
+    del xa, ya, oa
+    n = 8 * 32 * 2048 * 2048
+    yy = torch.rand((8, 32, 2048, 2048), device="cuda", generator=g).to(torch.bfloat16)
+    dyy = torch.randn((8, 32, 2048, 2048), device="cuda", generator=g).to(torch.bfloat16)
+    rec("next: softmax_grad bf16 [8,32,2048,2048] axis=-1", 3 * n * 2, lambda: F.softmax_grad(yy, dyy, axis=-1), n)
+    del yy, dyy
+    rows, D = 65536, 8192
+    xl = torch.randn((rows, D), device="cuda", generator=g).to(torch.bfloat16)
+    dl = torch.randn((rows, D), device="cuda", generator=g).to(torch.bfloat16)
+    w = (torch.rand(D, device="cuda", generator=g) + 0.5).to(torch.bfloat16)
+    m_ = torch.zeros(rows, device="cuda")
+    v_ = torch.ones(rows, device="cuda")
+    rec("next: layer_norm_grad bf16 [65536,8192] (dx, dscale, dbias)", 3 * rows * D * 2 + 2 * rows * 4 + 3 * D * 2,
+        lambda: F.layer_norm_grad(xl, [D], w, m_, v_, dl), rows * D)
+    del xl, dl
     # C5: one rank's shard of the 2^34-element full reduce (2^31 elements), int64 and fp32, sum and max;
     # with world > 1 the scalar partials are finished by an NCCL AllReduce timed separately.
     n = 1 << 31
