@@ -20,6 +20,8 @@
 // in flight per thread, 64-bit indexing (the reference's `int` dims overflow at 2^31).
 #pragma once
 
+#include <stdlib.h>
+
 #include <limits>
 #include <type_traits>
 
@@ -159,6 +161,10 @@ __device__ __forceinline__ void acc_step(typename Op::Acc& a, T v, int64_t idx) 
 }
 
 constexpr int kRedUnroll = 4;
+
+}  // namespace pdb200
+#include "reduce_cols_tma.cuh"  // needs acc_step / Vec; adds reduce_cols_tma_kernel
+namespace pdb200 {
 
 // Per-thread streaming fold of elements [begin, end) of one row, this thread touching
 // chunks begin + (lane + k*nlanes)*V.  VECTOR: 16-byte loads (caller guarantees alignment
@@ -319,7 +325,7 @@ __global__ void __launch_bounds__(256) reduce_cols_kernel(const T* __restrict__ 
 // Host side: launch geometry for one pass.
 // ---------------------------------------------------------------------------------------
 struct PassGeom {
-  int kind;        // 0 rows_warp, 1 rows_block, 2 cols
+  int kind;        // 0 rows_warp, 1 rows_block, 2 cols, 3 cols staged by TMA tensor-map boxes
   int G;           // rows_warp: lanes per row
   int threads;     // rows_block
   int splits;      // rows_block / cols: cuts of the reduced axis (1 = single pass)
@@ -370,9 +376,20 @@ inline PassGeom plan_pass(const ReducePass& ps, size_t elem_bytes, int V) {
   }
   g.kind = 2;
   const int64_t vec_cols = (ps.inner + V - 1) / V;
-  g.TX = pow2_ceil(vec_cols, 64);
-  if (g.TX < 1) g.TX = 1;
-  g.TY = 256 / g.TX;
+  // Wide enough, long enough, and an element size the tensor map knows: stage [32 rows][512 B] boxes with TMA.
+  // The tile (32 vectors x 8 row-groups) is also a valid geometry for the plain kernel, which launch_pass
+  // falls back to if the tensor map cannot be encoded.
+  const bool tma = V > 1 && (elem_bytes == 2 || elem_bytes == 4 || elem_bytes == 8) && vec_cols >= 32 &&
+                   ps.red >= 64 && getenv("PDB200_NO_TMA_COLS") == nullptr;
+  if (tma) {
+    g.kind = 3;
+    g.TX = 32;
+    g.TY = 8;
+  } else {
+    g.TX = pow2_ceil(vec_cols, 64);
+    if (g.TX < 1) g.TX = 1;
+    g.TY = 256 / g.TX;
+  }
   g.col_tiles = (vec_cols + g.TX - 1) / g.TX;
   const int64_t ctas = g.col_tiles * ps.outer;
   int64_t splits = 1;
@@ -413,6 +430,24 @@ int launch_pass(const ReducePass& ps, const PassGeom& g, bool vec, const T* x, O
   }
   const int64_t blocks = g.col_tiles * g.splits * ps.outer;
   if (blocks > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "reduce: too many tiles for one launch");
+  if constexpr (sizeof(T) == 2 || sizeof(T) == 4 || sizeof(T) == 8) {
+    if (g.kind == 3 && vec) {
+      CUtensorMap map;
+      if (make_cols_tensor_map(&map, x, ps.outer * ps.red, ps.inner, sizeof(T))) {
+        using A = typename Op::Acc;
+        constexpr int TI = 32 * Vec<T>::N;
+        const size_t smem_tma = (size_t)kTmaStages * kTmaTileRows * TI * sizeof(T) + (size_t)8 * TI * sizeof(A);
+        auto kern = reduce_cols_tma_kernel<T, O, Op, Fin>;
+        static bool attr_set = false;  // per instantiation
+        if (!attr_set) {
+          cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tma);
+          attr_set = true;
+        }
+        kern<<<(unsigned)blocks, kTmaThreads, smem_tma, st>>>(map, out, ps.red, ps.inner, g.seg, g.splits, g.col_tiles, fin);
+        return after_launch("reduce_cols_tma");
+      }
+    }
+  }
   dim3 block(g.TX, g.TY);
   const int V = vec ? Vec<T>::N : 1;
   const size_t smem = sizeof(typename Op::Acc) * (size_t)g.TX * g.TY * V;
