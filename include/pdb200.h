@@ -165,7 +165,7 @@ PDB200_API int pdb200_prod(const void* x, const int64_t* x_dims, int x_rank, con
  * allocator.  This variant is for callers that have no allocator to offer and may not call cudaMalloc
  * themselves (memory planned and handed out at start-up, real-time loops, plugin hosts without an
  * allocator): it takes no workspace argument and keeps its partial sums in a fixed array of
- * PDB200_STATIC_SCRATCH_BYTES (3 MiB) inside the library's device image — present on every GPU that
+ * PDB200_STATIC_SCRATCH_BYTES (1.5 MiB) inside the library's device image — present on every GPU that
  * loads the library, for the life of the process.  Limits and rules:
  *   - shapes whose partial sums need more than PDB200_STATIC_SCRATCH_BYTES are refused with
  *     PDB200_WORKSPACE_TOO_SMALL (the message says how much was needed); shapes wide enough to need
@@ -177,7 +177,7 @@ PDB200_API int pdb200_prod(const void* x, const int64_t* x_dims, int x_rank, con
  *     ordering between them — race on it, so keep them on one stream or order them with events;
  *   - it calls no cudaMalloc / cudaFree and no allocating library routine.
  * dtype pairs: FLOAT32->FLOAT32, BFLOAT16->BFLOAT16, BFLOAT16->FLOAT32, INT64->INT64. */
-#define PDB200_STATIC_SCRATCH_BYTES (3u << 20)
+#define PDB200_STATIC_SCRATCH_BYTES (3u << 19)
 PDB200_API int pdb200_sum_axis0_static(const void* x, int64_t rows, int64_t cols, int x_dtype, int out_dtype,
                                        void* out, void* stream);
 

@@ -6,9 +6,10 @@
 // that must not take the allocator's lock or risk its implicit synchronisation, or a plugin host
 // that gives a kernel library no allocator at all.  The regular entry point (pdb200_sum_raw) asks such a caller for a workspace buffer; a
 // caller that has nowhere to get one from can use this variant instead, which brings its own
-// scratch: a fixed 3 MiB array that lives in the library's device image.  (On a 148-SM B200 the
-// split heuristic never asks for more than ~1.8 MB for float32/int64 input and ~3.6 MB for
-// bfloat16 input accumulated in float; only the widest of the bfloat16 split shapes are refused.)
+// scratch: a fixed 1.5 MiB array that lives in the library's device image.  (On a 148-SM B200 the
+// split heuristic never asks for more than ~0.9 MB for float32/int64 input and ~1.8 MB for
+// bfloat16 input accumulated in float; only the widest of the bfloat16 split shapes - roughly
+// 131072 to 151552 columns - are refused.)
 //
 // Trade-offs the caller accepts:
 //   * the array exists on every GPU that loads libpdb200.so, from load until the process exits;
@@ -25,7 +26,7 @@
 
 namespace pdb200 {
 
-constexpr size_t kStaticScratchBytes = size_t(3) << 20;  // 3 MiB per device, stated in pdb200.h
+constexpr size_t kStaticScratchBytes = size_t(3) << 19;  // 1.5 MiB per device, stated in pdb200.h
 
 // File-scope device array.  In HOST code this name is only a handle for the runtime (passing it to
 // a kernel would hand the kernel a host address); the device address comes from

@@ -3,7 +3,7 @@
 Some users of this library cannot allocate device memory at call time: their memory was planned and
 handed out when the process started, or they sit in a latency-critical loop that must stay away from
 cudaMalloc, or their host framework simply passes no allocator down.  For them the library carries a
-fixed 3 MiB scratch array of its own.  This test drives that entry point through the C-ABI and checks
+fixed 1.5 MiB scratch array of its own.  This test drives that entry point through the C-ABI and checks
 it against pdb200_sum_raw (which is given a caller-allocated workspace), twice in a row with different
 shapes so that a result depending on what the previous call left in the shared scratch would show.
 
@@ -103,17 +103,17 @@ def test_static_scratch_limit_and_no_allocation():
     rc, got = _sum_axis0_static(lib, x, torch.float32, xc, oc)
     L.check(rc, lib)
     assert torch.equal(got, want)
-    # a shape whose partial sums exceed the 3 MiB built-in scratch is refused with a clear message:
-    # bf16 [4096, 286720] is cut into 3 row-slabs of 286720 float partials = 3.44 MB
-    rows, cols = 4096, 286720
+    # a shape whose partial sums exceed the 1.5 MiB built-in scratch is refused with a clear message:
+    # bf16 [4096, 140032] is cut into 3 row-slabs of 140032 float partials = 1.68 MB
+    rows, cols = 4096, 140032
     big = torch.zeros((rows, cols), dtype=torch.bfloat16, device="cuda")
     rc, _ = _sum_axis0_static(lib, big, torch.float32, L.BFLOAT16, L.FLOAT32)
     assert rc == L.WORKSPACE_TOO_SMALL
     msg = lib.pdb200_last_error().decode()
-    assert "built-in scratch holds 3145728" in msg and "pdb200_sum_raw" in msg
+    assert "built-in scratch holds 1572864" in msg and "pdb200_sum_raw" in msg
     # ... while the regular entry point, given a workspace, handles the same shape
     want, nbytes, _, _ = _sum_axis0_regular(lib, big, torch.float32)
-    assert nbytes > (3 << 20) and float(want.abs().max()) == 0.0
+    assert nbytes > (3 << 19) and float(want.abs().max()) == 0.0
     del big, want
     # device memory in use does not move across calls (after the first call's one-time address lookup)
     x = _make((70000, 1000), torch.float32, 8)
