@@ -370,7 +370,9 @@ int oracle_reduce(int op, int dtype, const void* x, const int64_t* dims, int ran
  *   paddle/phi/kernels/cpu/arg_min_max_kernel.cc:35-66,150-196.
  * Eigen's ArgMaxTupleReducer keeps the accumulator unless t.second > accum.second (strict), so the
  *   FIRST maximal index wins (TensorFunctors.h:370-381).  flatten -> index into the flat tensor.
- * Output int64 (default) or int32.  Values are compared in T (bf16/fp16 as their float values).
+ * Output int64 (default) or int32.  Values are compared in T.  The CPU kernel is not registered for
+ *   bf16/fp16 (arg_min_max_kernel.cc:212-224); for those the same rule is applied to their float values
+ *   with float's lowest() as the start — an extension by analogy, not pinned by the reference.
  * ---------------------------------------------------------------------------------------- */
 static double load_as_double(const void* x, int dtype, int64_t i) {
   switch (dtype) {
@@ -404,8 +406,10 @@ int oracle_argmax(int dtype, const void* x, const int64_t* dims, int rank, int64
         int64_t bv = X[p * n * post + q];
         for (int64_t k = 1; k < n; ++k) { int64_t v = X[(p * n + k) * post + q]; if (v > bv) { bv = v; best = k; } }
       } else {
-        double bv = load_as_double(x, dtype, p * n * post + q);
-        for (int64_t k = 1; k < n; ++k) { double v = load_as_double(x, dtype, (p * n + k) * post + q); if (v > bv) { bv = v; best = k; } }
+        /* the accumulator starts as (index 0, lowest()) — NOT as element 0 — so a NaN in front is skipped
+         * like any other NaN, and a row that never beats lowest() (all -inf / NaN) answers 0 */
+        double bv = dtype == DT_FLOAT64 ? -1.7976931348623157e308 : (dtype == DT_INT32 ? -2147483648.0 : (dtype == DT_INT16 ? -32768.0 : (dtype == DT_UINT8 ? 0.0 : -(double)3.40282346638528859812e38f)));
+        for (int64_t k = 0; k < n; ++k) { double v = load_as_double(x, dtype, (p * n + k) * post + q); if (v > bv) { bv = v; best = k; } }
       }
       if (out_dtype == DT_INT32) ((int32_t*)out)[p * post + q] = (int32_t)best;
       else ((int64_t*)out)[p * post + q] = best;

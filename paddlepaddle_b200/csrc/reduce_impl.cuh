@@ -76,6 +76,11 @@ struct MaxOp {
   static __device__ __forceinline__ A lift(T v, int64_t) { return cvt<A>(v); }
   static __device__ __forceinline__ A combine(A a, A b) { return (b > a) ? b : a; }  // functor_primitives.h:146-149
 };
+// The accumulator starts at lowest() and "(b > a) ? b : a" never lets a NaN in, so for floating point
+// this is exactly fmax (which returns the non-NaN operand): one FMNMX instead of compare + select.
+// (Only the sign of a zero result can differ, and that already depends on visiting order in the reference.)
+template <> __device__ __forceinline__ float MaxOp<float>::combine(float a, float b) { return fmaxf(a, b); }
+template <> __device__ __forceinline__ double MaxOp<double>::combine(double a, double b) { return fmax(a, b); }
 template <typename A>
 struct MinOp {
   using Acc = A;
@@ -84,6 +89,9 @@ struct MinOp {
   static __device__ __forceinline__ A lift(T v, int64_t) { return cvt<A>(v); }
   static __device__ __forceinline__ A combine(A a, A b) { return (b < a) ? b : a; }
 };
+
+template <> __device__ __forceinline__ float MinOp<float>::combine(float a, float b) { return fminf(a, b); }
+template <> __device__ __forceinline__ double MinOp<double>::combine(double a, double b) { return fmin(a, b); }
 
 // (value, index) pair for argmax.  16 bytes for every value type we instantiate.
 template <typename V>
@@ -166,6 +174,70 @@ constexpr int kRedUnroll = 4;
 #include "reduce_cols_tma.cuh"  // needs acc_step / Vec; adds reduce_cols_tma_kernel
 namespace pdb200 {
 
+// ---- argmax over 16-bit values: track the best 16-BYTE VECTOR, not the best element ---------------
+// Element-wise "replace on strictly greater" costs ~5 instructions per 2-byte element (unpack, compare,
+// three selects) — more than the issue slots a 7 TB/s stream of bf16 leaves.  Instead: the maximum of a
+// vector's 8 values takes 4 packed max instructions; only when it beats the running maximum (rare: the
+// maximum of n random values rises ~ln n times) the vector and its position are remembered.  The element is
+// picked from the remembered vector at the very end.  Result is the same as the element-wise rule: the
+// first vector (in increasing index order) whose maximum equals the overall maximum, then the first equal
+// element inside it; NaNs never win (packed max returns the other operand; '>' is false for NaN).
+template <typename T> struct Pair16;
+template <> struct Pair16<__nv_bfloat16> { using type = __nv_bfloat162; };
+template <> struct Pair16<__half> { using type = __half2; };
+
+template <typename T, typename Op>
+__device__ __forceinline__ typename Op::Acc fold_span_argmax16(const T* __restrict__ row, int64_t begin, int64_t end,
+                                                               int lane, int nlanes) {
+  using A = typename Op::Acc;  // KV<float>
+  using T2 = typename Pair16<T>::type;
+  constexpr int V = Vec<T>::N;  // 8
+  static_assert(V == 8, "16-bit vectors hold 8 values");
+  float run[kRedUnroll];
+  Vec<T> best[kRedUnroll];
+  int64_t at[kRedUnroll];
+#pragma unroll
+  for (int u = 0; u < kRedUnroll; ++u) {
+    run[u] = Op::identity().val;
+    at[u] = Op::identity().idx;
+    *reinterpret_cast<uint4*>(&best[u]) = make_uint4(0, 0, 0, 0);
+  }
+  auto visit = [&](int u, const Vec<T>& v, int64_t i) {
+    const T2* p = reinterpret_cast<const T2*>(&v);
+    const T2 m = __hmax2(__hmax2(p[0], p[1]), __hmax2(p[2], p[3]));
+    const float f = fmaxf(cvt<float>(m.x), cvt<float>(m.y));
+    if (f > run[u]) {
+      run[u] = f;
+      best[u] = v;
+      at[u] = i;
+    }
+  };
+  const int64_t step = (int64_t)nlanes * V;
+  int64_t i = begin + (int64_t)lane * V;
+  for (; i + (kRedUnroll - 1) * step < end; i += kRedUnroll * step) {
+    Vec<T> v[kRedUnroll];
+#pragma unroll
+    for (int u = 0; u < kRedUnroll; ++u) v[u] = ld_stream(row + i + u * step);
+#pragma unroll
+    for (int u = 0; u < kRedUnroll; ++u) visit(u, v[u], i + u * step);
+  }
+  for (; i < end; i += step) visit(0, ld_stream(row + i), i);
+  // pick the element inside each remembered vector (last to first, so the first equal one sticks)
+  A acc[kRedUnroll];
+#pragma unroll
+  for (int u = 0; u < kRedUnroll; ++u) {
+    acc[u] = Op::identity();
+    if (at[u] != Op::identity().idx) {
+      int k_first = 0;
+#pragma unroll
+      for (int k = V - 1; k >= 0; --k)
+        if (cvt<float>(best[u].v[k]) == run[u]) k_first = k;
+      acc[u] = A{run[u], at[u] + k_first};
+    }
+  }
+  return Op::combine(Op::combine(acc[0], acc[1]), Op::combine(acc[2], acc[3]));
+}
+
 // Per-thread streaming fold of elements [begin, end) of one row, this thread touching
 // chunks begin + (lane + k*nlanes)*V.  VECTOR: 16-byte loads (caller guarantees alignment
 // and that begin, end are multiples of V).
@@ -173,6 +245,10 @@ template <typename T, typename Op, bool VECTOR>
 __device__ __forceinline__ typename Op::Acc fold_span(const T* __restrict__ row, int64_t begin,
                                                       int64_t end, int lane, int nlanes) {
   using A = typename Op::Acc;
+  if constexpr (VECTOR && IsArgMax<Op>::value && sizeof(T) == 2 &&
+                (std::is_same<T, __nv_bfloat16>::value || std::is_same<T, __half>::value)) {
+    return fold_span_argmax16<T, Op>(row, begin, end, lane, nlanes);
+  }
   constexpr int V = VECTOR ? Vec<T>::N : 1;
   A acc[kRedUnroll];
 #pragma unroll

@@ -301,6 +301,25 @@ def test_argmax_degenerate_rows(port):
     assert np.array_equal(to_np(paddle.argmax(to_dev(xi), axis=1)), port.argmax(xi, 1))
 
 
+@pytest.mark.parametrize("half,code", [("bf16", O.BFLOAT16), ("fp16", O.FLOAT16)])
+@pytest.mark.parametrize("shape,axis", [((64, 4096), -1), ((5, 100000), 1), ((300, 264), 1), ((1 << 20,), None)])
+def test_argmax_16bit_special_values(port, half, code, shape, axis):
+    """The 16-bit route remembers the best 16-byte vector and picks the element at the end: ties, signed
+    zeros, infinities and NaNs must still resolve like the element-by-element CPU kernel."""
+    rng = np.random.default_rng(99)
+    conv = port.f32_to_bf16 if half == "bf16" else port.f32_to_fp16
+    base = rng.choice(np.array([-np.inf, -3.0, -0.0, 0.0, 0.5, 2.0, np.nan], np.float32), size=shape)
+    cases = [base, np.where(np.isnan(base), np.float32(-1.0), base), -np.abs(np.nan_to_num(base, nan=1.0, neginf=-7.0)),
+             np.full(shape, -np.inf, np.float32), np.where(rng.random(shape) < 0.001, np.float32(0.0), np.float32(-0.0))]
+    if len(shape) == 2:
+        peak = rng.standard_normal(shape).astype(np.float32)
+        peak[np.arange(shape[0]), rng.integers(0, shape[1], shape[0])] = np.inf
+        cases.append(peak)
+    for x in cases:
+        xb = conv(np.ascontiguousarray(x, np.float32))
+        assert np.array_equal(to_np(paddle.argmax(to_dev(xb, half), axis=axis)), port.argmax(xb, axis, code=code))
+
+
 # ------------------------------------------------------------------------------------------
 # softmax
 # ------------------------------------------------------------------------------------------

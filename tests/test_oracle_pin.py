@@ -197,3 +197,17 @@ def test_live_softmax_layernorm_argmax(port, ref):
     t = rng.integers(0, 9, (7, 300, 5)).astype(np.float32)
     for ax in (0, 1, 2, None):
         assert np.array_equal(port.argmax(t, ax), ref.argmax(t, ax))
+
+
+def test_live_argmax_nan_and_infinities(port, ref):
+    """Eigen's accumulator starts as (0, lowest()): NaNs never win wherever they stand, and a row that never
+    beats lowest() (all -inf / NaN / lowest) answers 0."""
+    rng = np.random.default_rng(10)
+    for dt in (np.float32, np.float64):
+        x = rng.choice(np.array([-np.inf, -3.0, -0.0, 0.0, 0.5, 2.0, np.nan], dt), size=(40, 37))
+        x[3] = np.nan
+        x[4] = -np.inf
+        x[5] = np.finfo(dt).min
+        x[6, 0] = np.nan
+        for ax in (0, 1, None):
+            assert np.array_equal(port.argmax(x, ax), ref.argmax(x, ax))
