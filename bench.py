@@ -298,7 +298,15 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
     oa = torch.empty_like(xa)
     for nm_, fn_ in (("subtract", "pdb200_subtract"), ("divide", "pdb200_divide"), ("maximum", "pdb200_maximum")):
         rec(f"next: {nm_} bf16 [64,2048,4096]+[4096]", C2_BYTES_BF16, lambda f=fn_: _elementwise(f, xa, ya, out=oa), C2_ROWS * C2_COLS)
-    del xa, ya, oa
+    # compare writes one bool per element; where reads a bool + two operands; cast bf16 -> fp32; scale in place
+    ob = torch.empty(C2_SHAPE, device="cuda", dtype=torch.bool)
+    n2 = C2_ROWS * C2_COLS
+    rec("next: less_than bf16 [64,2048,4096] vs [4096] -> bool", n2 * 2 + n2 + C2_COLS * 2,
+        lambda: _elementwise("pdb200_compare", xa, ya, out=ob, op=0, out_dtype=torch.bool), n2)
+    rec("next: scale bf16 [64,2048,4096] (2.5*x + 1)", 2 * n2 * 2, lambda: paddle.scale(xa, 2.5, 1.0), n2)
+    rec("next: cast bf16 -> fp32 [64,2048,4096]", n2 * 2 + n2 * 4, lambda: paddle.cast(xa, "float32"), n2)
+    rec("next: where bf16 [64,2048,4096] (bool, x, y)", n2 + 3 * n2 * 2, lambda: paddle.where(ob, xa, oa), n2)
+    del xa, ya, oa, ob
     n = 8 * 32 * 2048 * 2048
     yy = torch.rand((8, 32, 2048, 2048), device="cuda", generator=g).to(torch.bfloat16)
     dyy = torch.randn((8, 32, 2048, 2048), device="cuda", generator=g).to(torch.bfloat16)

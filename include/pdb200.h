@@ -116,6 +116,57 @@ PDB200_API int pdb200_minimum(const void* x, const int64_t* x_dims, int x_rank, 
                    const int64_t* y_dims, int y_rank, void* out, int dtype, void* stream);
 
 /* ---------------------------------------------------------------------------
+ * Compare / logical / bitwise with broadcasting — the remaining binary callers of
+ * funcs::BroadcastKernel.  Shapes broadcast exactly as for pdb200_add; `dtype` is the dtype of x and y.
+ *
+ * pdb200_compare replaces LessThan/LessEqual/GreaterThan/GreaterEqual/Equal/NotEqual Kernel
+ *   paddle/phi/kernels/kps/compare_kernel.cu:49-66,143-173 (functors funcs/compare_functors.h:21-62).
+ *   out is BOOL (one byte per element).  All ten dtypes.  equal / not_equal on the floating types (bf16
+ *   and fp16 included) follow the reference's EqualFunctor: |a - b| < 1e-8 counts as equal (a - b taken in
+ *   the tensor's type), infinities compare exactly, NaN equals nothing; integers and bool use ==.
+ * pdb200_logical replaces LogicalAnd/Or/Xor Kernel, kps/logical_kernel.cu:60-69,112-134: out (BOOL) =
+ *   bool(x) op bool(y); every dtype except uint8.
+ * pdb200_bitwise replaces BitwiseAnd/Or/Xor Kernel, kps/bitwise_kernel.cu:55-67,94-125: out has the input
+ *   dtype; bool and the integer dtypes (bool uses &&, ||, !=). */
+enum pdb200_compare_op {
+  PDB200_LESS_THAN = 0, PDB200_LESS_EQUAL = 1, PDB200_GREATER_THAN = 2, PDB200_GREATER_EQUAL = 3,
+  PDB200_EQUAL = 4, PDB200_NOT_EQUAL = 5
+};
+enum pdb200_logical_op { PDB200_LOGICAL_AND = 0, PDB200_LOGICAL_OR = 1, PDB200_LOGICAL_XOR = 2 };
+enum pdb200_bitwise_op { PDB200_BITWISE_AND = 0, PDB200_BITWISE_OR = 1, PDB200_BITWISE_XOR = 2 };
+PDB200_API int pdb200_compare(int op, const void* x, const int64_t* x_dims, int x_rank, const void* y,
+                   const int64_t* y_dims, int y_rank, void* out, int dtype, void* stream);
+PDB200_API int pdb200_logical(int op, const void* x, const int64_t* x_dims, int x_rank, const void* y,
+                   const int64_t* y_dims, int y_rank, void* out, int dtype, void* stream);
+PDB200_API int pdb200_bitwise(int op, const void* x, const int64_t* x_dims, int x_rank, const void* y,
+                   const int64_t* y_dims, int y_rank, void* out, int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * One-input maps and `where` — the callers of funcs::ElementwiseKernel.
+ * `numel` elements, contiguous.  out may be x itself when both have the same element size.
+ *
+ * pdb200_logical_not  LogicalNotKernel, kps/logical_kernel.cu:71-91: out (BOOL) = !bool(x); no uint8.
+ * pdb200_bitwise_not  BitwiseNotKernel, kps/bitwise_kernel.cu:69-80: ~x (bool: !x); bool and integers.
+ * pdb200_scale        ScaleKernel, gpu/scale_kernel.cu:24-65: out = scale*x + bias (bias_after_scale != 0)
+ *                     or scale*(x + bias); computed in float for bf16/fp16 and in the tensor's own type
+ *                     otherwise, scale and bias converted to that type first (Scalar::to<>).
+ *                     Integer overflow wraps.  All ten dtypes.
+ * pdb200_cast         CastKernel, gpu/cast_kernel.cu + gpu/cast_impl.h: static_cast per element between any
+ *                     two of the ten dtypes (bf16/fp16 through float; to bool = "!= 0"; float -> integer
+ *                     truncates toward zero; out-of-range float -> integer is undefined in the reference
+ *                     and is not reproduced).
+ * pdb200_where        WhereKernel, gpu/where_kernel.cu:24-51: out = condition ? x : y, three same-shape
+ *                     tensors (broadcasting is done by the Python layer in the reference); condition is
+ *                     BOOL; any of the ten dtypes (a bit select, built per element size). */
+PDB200_API int pdb200_logical_not(const void* x, int64_t numel, int dtype, void* out, void* stream);
+PDB200_API int pdb200_bitwise_not(const void* x, int64_t numel, int dtype, void* out, void* stream);
+PDB200_API int pdb200_scale(const void* x, int64_t numel, int dtype, double scale, double bias,
+                 int bias_after_scale, void* out, void* stream);
+PDB200_API int pdb200_cast(const void* x, int64_t numel, int x_dtype, int out_dtype, void* out, void* stream);
+PDB200_API int pdb200_where(const void* condition, const void* x, const void* y, int64_t numel, int dtype,
+                 void* out, void* stream);
+
+/* ---------------------------------------------------------------------------
  * Reductions.  `axes` may hold negative values; n_axes == 0 or reduce_all != 0 or a full axis
  * set means "reduce everything" (phi::recompute_reduce_all, paddle/phi/core/kernel_utils.h:407-417).
  * keep_dim only changes the output SHAPE (InferMeta), never the data, so it is not a parameter.

@@ -38,11 +38,12 @@ paddle/phi/core/enforce.cc
 paddle/phi/backends/cpu/cpu_context.cc
 paddle/phi/backends/cpu/cpu_info.cc
 paddle/phi/kernels/funcs/math_function.cc
+paddle/phi/kernels/funcs/eigen/scale.cc
 "
 pids=()
 build_one() {  # $1 = source path, $2 = object
   if [ ! -f "$2" ] || [ "$1" -nt "$2" ]; then
-    g++ $FLAGS -c "$1" -o "$2"
+    g++ $FLAGS -c "$1" -o "$2" || { rm -f "$2"; return 1; }  # no stale object left for the link step
   fi
 }
 JOBS="${JOBS:-$(nproc)}"
@@ -54,6 +55,7 @@ for f in $TUS; do
   if [ "$running" -ge "$JOBS" ]; then wait -n; running=$((running - 1)); fi
 done
 build_one "$HERE/ref_shim.cc" "$OUT/ref_shim.o" &
+build_one "$HERE/ref_shim_family.cc" "$OUT/ref_shim_family.o" &
 wait
 g++ -shared -o "$OUT/libphi_cpu_ref.so" "$OUT"/*.o -Wl,--no-undefined -lpthread -ldl
 echo "built $OUT/libphi_cpu_ref.so"

@@ -31,7 +31,8 @@ paddle/phi/core/compat/op_utils.cc paddle/phi/core/compat/convert_utils.cc
 paddle/phi/core/extended_tensor.cc paddle/phi/core/sparse_coo_tensor.cc paddle/phi/core/sparse_csr_tensor.cc
 paddle/phi/core/string_tensor.cc paddle/phi/core/tensor_array.cc paddle/phi/backends/cpu/cpu_context.cc
 "
-build_one() { if [ ! -f "$2" ] || [ "$1" -nt "$2" ]; then g++ $FLAGS $3 -c "$1" -o "$2"; fi; }
+# a failed compile removes its (stale) object, so the link below fails instead of silently reusing it
+build_one() { if [ ! -f "$2" ] || [ "$1" -nt "$2" ]; then g++ $FLAGS $3 -c "$1" -o "$2" || { rm -f "$2"; return 1; }; fi; }
 JOBS="${JOBS:-$(nproc)}"
 running=0
 for f in $TUS; do

@@ -1,0 +1,355 @@
+/*
+ * phi_cpu_oracle_family.c — TEST INFRASTRUCTURE ONLY (see phi_cpu_oracle.c for the rules: only tests/,
+ * __graft_entry__.smoke() and bench.py's CPU legs may load the library this is compiled into).
+ *
+ * Plain-C restatement of the rest of the elementwise family of PaddlePaddle's CPU PHI kernels
+ * (SURVEY.md §8f rank 1): compare, logical, bitwise, logical_not / bitwise_not, scale, cast, where.
+ *
+ * Parity status: PINNED — tests/test_oracle_pin.py checks every function against
+ * oracle/_ref/libphi_cpu_ref.so (the reference's own CPU kernels, reached through oracle/ref_shim_family.cc)
+ * and against tests/golden/phi_family_golden.npz recorded from it.  Where the CPU build registers no kernel
+ * for a dtype the GPU build has (bf16 / fp16 logical ops; where on 1- and 2-byte types) the same functor is
+ * applied to that dtype — an extension by analogy that the reference CPU cannot pin; it is marked below.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <string.h>
+
+enum { DT_BOOL = 0, DT_UINT8, DT_INT8, DT_INT16, DT_INT32, DT_INT64, DT_FLOAT16, DT_BFLOAT16, DT_FLOAT32, DT_FLOAT64 };
+#define MAXR 9
+
+int oracle_broadcast_shape(const int64_t* xd, int xr, const int64_t* yd, int yr, int64_t* od, int* orank);
+
+static float bf2f(uint16_t b) { uint32_t u = (uint32_t)b << 16; float f; memcpy(&f, &u, 4); return f; }
+static float h2f(uint16_t b) { _Float16 h; memcpy(&h, &b, 2); return (float)h; }
+/* float -> bf16, paddle/phi/common/bfloat16.h:61-88: NaN -> 0x7FFF, else round to nearest even */
+static uint16_t f2bf(float f) {
+  uint32_t u; memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return 0x7FFF;
+  u += 0x7FFFu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+/* float -> fp16: round to nearest even (the GPU build's __float2half; the non-F16C CPU routine of
+ * phi/common/float16.h:121-138 truncates instead — tests allow one unit in the last place for fp16 outputs) */
+static uint16_t f2h(float f) { _Float16 h = (_Float16)f; uint16_t b; memcpy(&b, &h, 2); return b; }
+
+/* ---- the broadcast walk of CommonForwardBroadcastCPU (funcs/elementwise_base.h:274-307) ------------------------ */
+typedef struct { int R; int64_t od[MAXR], xs[MAXR], ys[MAXR], numel; } Walk;
+static int walk_init(Walk* w, const int64_t* xd, int xr, const int64_t* yd, int yr) {
+  if (oracle_broadcast_shape(xd, xr, yd, yr, w->od, &w->R)) return 1;
+  int64_t sx = 1, sy = 1;
+  w->numel = 1;
+  for (int i = w->R - 1; i >= 0; --i) {
+    int xi = i - (w->R - xr), yi = i - (w->R - yr);
+    int64_t a = xi >= 0 ? xd[xi] : 1, b = yi >= 0 ? yd[yi] : 1;
+    w->xs[i] = a == 1 ? 0 : sx;
+    w->ys[i] = b == 1 ? 0 : sy;
+    sx *= a; sy *= b;
+    w->numel *= w->od[i];
+  }
+  return 0;
+}
+#define WALK(BODY)                                                                       \
+  {                                                                                      \
+    int64_t idx[MAXR] = {0};                                                             \
+    for (int64_t i = 0; i < w.numel; ++i) {                                              \
+      int64_t xo = 0, yo = 0;                                                            \
+      for (int d = 0; d < w.R; ++d) { xo += idx[d] * w.xs[d]; yo += idx[d] * w.ys[d]; }  \
+      BODY;                                                                              \
+      for (int d = w.R - 1; d >= 0; --d) { if (++idx[d] < w.od[d]) break; idx[d] = 0; }  \
+    }                                                                                    \
+  }
+
+/* ------------------------------------------------------------------------------------------
+ * compare.  funcs/compare_functors.h:21-62; cpu/compare_kernel.cc:26-44 (when x has the lower rank the
+ * inverse functor is applied to swapped operands — the value is the same).
+ * op: 0 <, 1 <=, 2 >, 3 >=, 4 equal, 5 not_equal.  Equal on float/double: infinities exact, NaN never,
+ * else fabs((double)(a - b)) < 1e-8 with a - b evaluated in T; isinf / isnan are tested on the value cast to
+ * float, so a finite double beyond float range is treated as infinite.  bf16 / fp16 take the same route
+ * (std::is_floating_point is specialised for them, bfloat16.h:373-379, float16.h:1019): a - b is one float
+ * subtraction rounded back to the 16-bit type.
+ * ---------------------------------------------------------------------------------------- */
+static int eq_f32(float a, float b) {
+  if (isinf(a) || isinf(b)) return a == b;
+  if (isnan(a) || isnan(b)) return 0;
+  volatile float d = a - b;
+  return fabs((double)d) < 1e-8;
+}
+static int eq_f64(double a, double b) {
+  float fa = (float)a, fb = (float)b;
+  if (isinf(fa) || isinf(fb)) return a == b;
+  if (isnan(fa) || isnan(fb)) return 0;
+  return fabs(a - b) < 1e-8;
+}
+static int eq_bf16(float a, float b) {
+  if (isinf(a) || isinf(b)) return a == b;
+  if (isnan(a) || isnan(b)) return 0;
+  return fabs((double)bf2f(f2bf(a - b))) < 1e-8;
+}
+static int eq_fp16(float a, float b) {
+  if (isinf(a) || isinf(b)) return a == b;
+  if (isnan(a) || isnan(b)) return 0;
+  /* fp16 cannot hold a non-zero magnitude below 1e-8 (smallest subnormal 6e-8): equal iff the rounded difference is 0,
+   * whichever way the conversion rounds (the truncating CPU routine flushes what it cannot represent to zero too) */
+  return fabs((double)h2f(f2h(a - b))) < 1e-8;
+}
+#define CMP_CASES(T, LOAD, EQ)                                                         \
+  {                                                                                    \
+    const T* X = (const T*)x; const T* Y = (const T*)y;                                \
+    switch (op) {                                                                      \
+      case 0: WALK(O[i] = LOAD(X[xo]) < LOAD(Y[yo])) break;                            \
+      case 1: WALK(O[i] = LOAD(X[xo]) <= LOAD(Y[yo])) break;                           \
+      case 2: WALK(O[i] = LOAD(X[xo]) > LOAD(Y[yo])) break;                            \
+      case 3: WALK(O[i] = LOAD(X[xo]) >= LOAD(Y[yo])) break;                           \
+      case 4: WALK(O[i] = EQ(LOAD(X[xo]), LOAD(Y[yo])) ? 1 : 0) break;                 \
+      case 5: WALK(O[i] = EQ(LOAD(X[xo]), LOAD(Y[yo])) ? 0 : 1) break;                 \
+      default: return 2;                                                               \
+    }                                                                                  \
+  }
+#define ID(v) (v)
+#define EQ_PLAIN(a, b) ((a) == (b))
+int oracle_compare(int op, int dtype, const void* x, const int64_t* xd, int xr, const void* y, const int64_t* yd,
+                   int yr, uint8_t* O) {
+  Walk w;
+  if (walk_init(&w, xd, xr, yd, yr)) return 1;
+  switch (dtype) {
+    case DT_BOOL: case DT_UINT8: CMP_CASES(uint8_t, ID, EQ_PLAIN) break;
+    case DT_INT8: CMP_CASES(int8_t, ID, EQ_PLAIN) break;
+    case DT_INT16: CMP_CASES(int16_t, ID, EQ_PLAIN) break;
+    case DT_INT32: CMP_CASES(int32_t, ID, EQ_PLAIN) break;
+    case DT_INT64: CMP_CASES(int64_t, ID, EQ_PLAIN) break;
+    case DT_FLOAT16: CMP_CASES(uint16_t, h2f, eq_fp16) break;
+    case DT_BFLOAT16: CMP_CASES(uint16_t, bf2f, eq_bf16) break;
+    case DT_FLOAT32: CMP_CASES(float, ID, eq_f32) break;
+    case DT_FLOAT64: CMP_CASES(double, ID, eq_f64) break;
+    default: return 2;
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * logical and / or / xor: static_cast<bool>(a) op static_cast<bool>(b), funcs/logical_functor.h:20-32.
+ * CPU registers float, double, bool, int64, int, int8, int16 (cpu/logical_kernel.cc:93-111); fp16 / bf16
+ * (GPU only, kps/logical_kernel.cu:117-119) follow by analogy: bool(v) = (float(v) != 0).
+ * ---------------------------------------------------------------------------------------- */
+#define LOG_CASES(T, TRUTH)                                                            \
+  {                                                                                    \
+    const T* X = (const T*)x; const T* Y = (const T*)y;                                \
+    switch (op) {                                                                      \
+      case 0: WALK(O[i] = (TRUTH(X[xo]) && TRUTH(Y[yo])) ? 1 : 0) break;               \
+      case 1: WALK(O[i] = (TRUTH(X[xo]) || TRUTH(Y[yo])) ? 1 : 0) break;               \
+      case 2: WALK(O[i] = (TRUTH(X[xo]) != TRUTH(Y[yo])) ? 1 : 0) break;               \
+      default: return 2;                                                               \
+    }                                                                                  \
+  }
+#define T_PLAIN(v) ((v) != 0)
+#define T_BF(v) (bf2f(v) != 0.0f)
+#define T_H(v) (h2f(v) != 0.0f)
+int oracle_logical(int op, int dtype, const void* x, const int64_t* xd, int xr, const void* y, const int64_t* yd,
+                   int yr, uint8_t* O) {
+  Walk w;
+  if (walk_init(&w, xd, xr, yd, yr)) return 1;
+  switch (dtype) {
+    case DT_BOOL: LOG_CASES(uint8_t, T_PLAIN) break;
+    case DT_INT8: LOG_CASES(int8_t, T_PLAIN) break;
+    case DT_INT16: LOG_CASES(int16_t, T_PLAIN) break;
+    case DT_INT32: LOG_CASES(int32_t, T_PLAIN) break;
+    case DT_INT64: LOG_CASES(int64_t, T_PLAIN) break;
+    case DT_FLOAT16: LOG_CASES(uint16_t, T_H) break;
+    case DT_BFLOAT16: LOG_CASES(uint16_t, T_BF) break;
+    case DT_FLOAT32: LOG_CASES(float, T_PLAIN) break;
+    case DT_FLOAT64: LOG_CASES(double, T_PLAIN) break;
+    default: return 2;
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * bitwise and / or / xor: a & b, a | b, a ^ b; bool: &&, ||, != (funcs/bitwise_functors.h:20-35).
+ * ---------------------------------------------------------------------------------------- */
+#define BIT_CASES(T)                                                                   \
+  {                                                                                    \
+    const T* X = (const T*)x; const T* Y = (const T*)y; T* Q = (T*)out;                \
+    switch (op) {                                                                      \
+      case 0: WALK(Q[i] = (T)(X[xo] & Y[yo])) break;                                   \
+      case 1: WALK(Q[i] = (T)(X[xo] | Y[yo])) break;                                   \
+      case 2: WALK(Q[i] = (T)(X[xo] ^ Y[yo])) break;                                   \
+      default: return 2;                                                               \
+    }                                                                                  \
+  }
+int oracle_bitwise(int op, int dtype, const void* x, const int64_t* xd, int xr, const void* y, const int64_t* yd,
+                   int yr, void* out) {
+  Walk w;
+  if (walk_init(&w, xd, xr, yd, yr)) return 1;
+  switch (dtype) {
+    case DT_BOOL: {
+      const uint8_t* X = (const uint8_t*)x; const uint8_t* Y = (const uint8_t*)y; uint8_t* Q = (uint8_t*)out;
+      switch (op) {
+        case 0: WALK(Q[i] = (X[xo] && Y[yo]) ? 1 : 0) break;
+        case 1: WALK(Q[i] = (X[xo] || Y[yo]) ? 1 : 0) break;
+        case 2: WALK(Q[i] = ((X[xo] != 0) != (Y[yo] != 0)) ? 1 : 0) break;
+        default: return 2;
+      }
+      break;
+    }
+    case DT_UINT8: BIT_CASES(uint8_t) break;
+    case DT_INT8: BIT_CASES(int8_t) break;
+    case DT_INT16: BIT_CASES(int16_t) break;
+    case DT_INT32: BIT_CASES(int32_t) break;
+    case DT_INT64: BIT_CASES(int64_t) break;
+    default: return 2;
+  }
+  return 0;
+}
+
+/* logical_not: !a (funcs/logical_functor.h:34-38) -> bool; bitwise_not: ~a, bool: !a (bitwise_functors.h:38-49).
+ * which: 0 logical_not, 1 bitwise_not. */
+int oracle_not(int which, int dtype, const void* x, int64_t n, void* out) {
+  uint8_t* O = (uint8_t*)out;
+#define LNOT(T, TRUTH) { const T* X = (const T*)x; for (int64_t i = 0; i < n; ++i) O[i] = TRUTH(X[i]) ? 0 : 1; }
+#define BNOT(T) { const T* X = (const T*)x; T* Q = (T*)out; for (int64_t i = 0; i < n; ++i) Q[i] = (T)~X[i]; }
+  if (which == 0) {
+    switch (dtype) {
+      case DT_BOOL: LNOT(uint8_t, T_PLAIN) break;
+      case DT_INT8: LNOT(int8_t, T_PLAIN) break;
+      case DT_INT16: LNOT(int16_t, T_PLAIN) break;
+      case DT_INT32: LNOT(int32_t, T_PLAIN) break;
+      case DT_INT64: LNOT(int64_t, T_PLAIN) break;
+      case DT_FLOAT16: LNOT(uint16_t, T_H) break;
+      case DT_BFLOAT16: LNOT(uint16_t, T_BF) break;
+      case DT_FLOAT32: LNOT(float, T_PLAIN) break;
+      case DT_FLOAT64: LNOT(double, T_PLAIN) break;
+      default: return 2;
+    }
+  } else {
+    switch (dtype) {
+      case DT_BOOL: LNOT(uint8_t, T_PLAIN) break;
+      case DT_UINT8: BNOT(uint8_t) break;
+      case DT_INT8: BNOT(int8_t) break;
+      case DT_INT16: BNOT(int16_t) break;
+      case DT_INT32: BNOT(int32_t) break;
+      case DT_INT64: BNOT(int64_t) break;
+      default: return 2;
+    }
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * scale.  phi::ScaleKernel<T,CPUContext> (cpu/scale_kernel.cc:27-48) -> EigenScale (funcs/eigen/scale.cc:22-40):
+ *   out = scale * x + bias  or  scale * (x + bias), every operation in T, with scale.to<T>() / bias.to<T>()
+ *   (= static_cast<T> of the Python float, which arrives as a double).
+ *   bf16 / fp16: T arithmetic = float operation + rounding per operation (bfloat16.h:264-292).
+ *   Integers wrap.  bool: (s && x) || b, resp. s && (x || b).
+ *   float / double: whether the multiply-add is fused is the host compiler's choice in the reference build
+ *   (-mfma, GNU C++ contracts by default); this restatement does not fuse — tests compare to one unit in
+ *   the last place.
+ * ---------------------------------------------------------------------------------------- */
+int oracle_scale(int dtype, const void* x, int64_t n, double scale, double bias, int after, void* out) {
+#define SC_INT(T, U) { const T* X = (const T*)x; T* Q = (T*)out; const U s = (U)(T)scale, b = (U)(T)bias;           \
+    for (int64_t i = 0; i < n; ++i) Q[i] = after ? (T)(U)(s * (U)X[i] + b) : (T)(U)(s * (U)((U)X[i] + b)); }
+  switch (dtype) {
+    case DT_BOOL: {
+      const uint8_t* X = (const uint8_t*)x; uint8_t* Q = (uint8_t*)out;
+      const int s = scale != 0.0, b = bias != 0.0;
+      for (int64_t i = 0; i < n; ++i) Q[i] = after ? ((s && X[i]) || b) : (s && (X[i] || b));
+      break;
+    }
+    case DT_UINT8: SC_INT(uint8_t, uint8_t) break;
+    case DT_INT8: SC_INT(int8_t, uint8_t) break;
+    case DT_INT16: SC_INT(int16_t, uint16_t) break;
+    case DT_INT32: SC_INT(int32_t, uint32_t) break;
+    case DT_INT64: SC_INT(int64_t, uint64_t) break;
+    case DT_BFLOAT16: {
+      const uint16_t* X = (const uint16_t*)x; uint16_t* Q = (uint16_t*)out;
+      const float s = bf2f(f2bf((float)scale)), b = bf2f(f2bf((float)bias));
+      for (int64_t i = 0; i < n; ++i)
+        Q[i] = after ? f2bf(bf2f(f2bf(s * bf2f(X[i]))) + b) : f2bf(s * bf2f(f2bf(bf2f(X[i]) + b)));
+      break;
+    }
+    case DT_FLOAT16: {
+      const uint16_t* X = (const uint16_t*)x; uint16_t* Q = (uint16_t*)out;
+      const float s = h2f(f2h((float)scale)), b = h2f(f2h((float)bias));
+      for (int64_t i = 0; i < n; ++i)
+        Q[i] = after ? f2h(h2f(f2h(s * h2f(X[i]))) + b) : f2h(s * h2f(f2h(h2f(X[i]) + b)));
+      break;
+    }
+    case DT_FLOAT32: {
+      const float* X = (const float*)x; float* Q = (float*)out;
+      const float s = (float)scale, b = (float)bias;
+      for (int64_t i = 0; i < n; ++i) Q[i] = after ? s * X[i] + b : s * (X[i] + b);
+      break;
+    }
+    case DT_FLOAT64: {
+      const double* X = (const double*)x; double* Q = (double*)out;
+      for (int64_t i = 0; i < n; ++i) Q[i] = after ? scale * X[i] + bias : scale * (X[i] + bias);
+      break;
+    }
+    default: return 2;
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * cast.  phi::CastKernel -> CastKernelImpl -> CastOpTransformFunctor: static_cast<OutT>(in) per element
+ * (cpu/cast_impl.h:22-40).  bf16 / fp16 sources convert through float, every source reaches bf16 / fp16
+ * through float (the constructors of phi::dtype::bfloat16 / float16).  To bool: != 0.
+ * Float -> integer truncates toward zero; a value outside the target range is undefined behaviour in the
+ * reference and is kept out of the test inputs.  Narrow integer targets keep the low bits.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct { int is_float; double f; int64_t i; uint64_t u; int is_unsigned; } Num;
+static Num load_num(const void* x, int dt, int64_t k) {
+  Num v = {0, 0.0, 0, 0, 0};
+  switch (dt) {
+    case DT_BOOL: v.i = ((const uint8_t*)x)[k] != 0; break;
+    case DT_UINT8: v.i = ((const uint8_t*)x)[k]; break;
+    case DT_INT8: v.i = ((const int8_t*)x)[k]; break;
+    case DT_INT16: v.i = ((const int16_t*)x)[k]; break;
+    case DT_INT32: v.i = ((const int32_t*)x)[k]; break;
+    case DT_INT64: v.i = ((const int64_t*)x)[k]; break;
+    case DT_FLOAT16: v.is_float = 1; v.f = h2f(((const uint16_t*)x)[k]); break;
+    case DT_BFLOAT16: v.is_float = 1; v.f = bf2f(((const uint16_t*)x)[k]); break;
+    case DT_FLOAT32: v.is_float = 1; v.f = ((const float*)x)[k]; break;
+    case DT_FLOAT64: v.is_float = 2; v.f = ((const double*)x)[k]; break;
+  }
+  return v;
+}
+int oracle_cast(int x_dtype, int out_dtype, const void* x, int64_t n, void* out) {
+  if (x_dtype < 0 || x_dtype > DT_FLOAT64 || out_dtype < 0 || out_dtype > DT_FLOAT64) return 2;
+  for (int64_t k = 0; k < n; ++k) {
+    const Num v = load_num(x, x_dtype, k);
+    /* the value as the source type would convert it */
+    const float as_f = v.is_float ? (float)v.f : (float)v.i;     /* int64 -> float: round to nearest */
+    const double as_d = v.is_float ? v.f : (double)v.i;
+    const int64_t as_i = v.is_float ? (int64_t)v.f : v.i;         /* truncation toward zero */
+    switch (out_dtype) {
+      case DT_BOOL: ((uint8_t*)out)[k] = v.is_float ? (v.f != 0.0) : (v.i != 0); break;
+      case DT_UINT8: ((uint8_t*)out)[k] = (uint8_t)(v.is_float ? (int64_t)(int32_t)v.f : as_i); break;
+      case DT_INT8: ((int8_t*)out)[k] = (int8_t)(v.is_float ? (int64_t)(int32_t)v.f : as_i); break;
+      case DT_INT16: ((int16_t*)out)[k] = (int16_t)(v.is_float ? (int64_t)(int32_t)v.f : as_i); break;
+      case DT_INT32: ((int32_t*)out)[k] = v.is_float ? (int32_t)v.f : (int32_t)as_i; break;
+      case DT_INT64: ((int64_t*)out)[k] = as_i; break;
+      case DT_FLOAT16: ((uint16_t*)out)[k] = x_dtype == DT_FLOAT16 ? ((const uint16_t*)x)[k] : f2h(as_f); break;
+      case DT_BFLOAT16: ((uint16_t*)out)[k] = x_dtype == DT_BFLOAT16 ? ((const uint16_t*)x)[k] : f2bf(as_f); break;
+      case DT_FLOAT32: ((float*)out)[k] = as_f; break;
+      case DT_FLOAT64: ((double*)out)[k] = as_d; break;
+    }
+  }
+  return 0;
+}
+
+/* where: out[i] = cond[i] ? x[i] : y[i] (cpu/where_kernel.cc:20-36).  CPU registers float, double, int, int64;
+ * the select copies bits, so the other element sizes follow without any arithmetic. */
+int oracle_where(int dtype, const uint8_t* cond, const void* x, const void* y, int64_t n, void* out) {
+  size_t es;
+  switch (dtype) {
+    case DT_BOOL: case DT_UINT8: case DT_INT8: es = 1; break;
+    case DT_INT16: case DT_FLOAT16: case DT_BFLOAT16: es = 2; break;
+    case DT_INT32: case DT_FLOAT32: es = 4; break;
+    case DT_INT64: case DT_FLOAT64: es = 8; break;
+    default: return 2;
+  }
+  for (int64_t i = 0; i < n; ++i)
+    memcpy((char*)out + i * es, (cond[i] ? (const char*)x : (const char*)y) + i * es, es);
+  return 0;
+}

@@ -1,0 +1,236 @@
+// TEST INFRASTRUCTURE ONLY — never linked into, imported by, or called from the product path.
+//
+// Second `extern "C"` doorway onto the reference's own CPU PHI kernels (see ref_shim.cc for the first):
+// the rest of the elementwise family.  No restated algorithm here; every call lands in a
+// kernel template compiled from /root/reference:
+//   compare      phi::LessThan/LessEqual/GreaterThan/GreaterEqual/Equal/NotEqualKernel<T,CPUContext>
+//                paddle/phi/kernels/impl/compare_kernel_impl.h:44-76, cpu/compare_kernel.cc:26-44
+//   logical      phi::LogicalAnd/Or/Xor/NotKernel<T,CPUContext>  paddle/phi/kernels/cpu/logical_kernel.cc:27-91
+//   bitwise      phi::BitwiseAnd/Or/Xor/NotKernel<T,CPUContext>  paddle/phi/kernels/cpu/bitwise_kernel.cc:27-92
+//   scale        phi::ScaleKernel<T,CPUContext>                  paddle/phi/kernels/cpu/scale_kernel.cc:27-48
+//   cast         phi::CastKernel<T,CPUContext>                   paddle/phi/kernels/cpu/cast_kernel.cc, cast_impl.h
+//   where        phi::WhereKernel<T,CPUContext>                  paddle/phi/kernels/cpu/where_kernel.cc:20-36
+#include "paddle/common/flags.h"
+#include "paddle/phi/common/bfloat16.h"
+#include "paddle/phi/common/float16.h"
+#include "paddle/phi/common/scalar.h"
+#include "paddle/phi/core/kernel_registry.h"
+
+// registrations at the end of the kernel TUs become unused functions (see ref_shim.cc)
+#undef PD_REGISTER_KERNEL
+#define PD_REGISTER_KERNEL(name, backend, layout, fn, ...)                \
+  [[maybe_unused]] static void pdb200_unused_reg_##name##_##backend(      \
+      const ::phi::KernelKey& kernel_key, ::phi::Kernel* kernel)
+
+#include "paddle/phi/kernels/cpu/bitwise_kernel.cc"  // NOLINT (kernel templates live in the .cc)
+#include "paddle/phi/kernels/cpu/cast_kernel.cc"     // NOLINT
+#include "paddle/phi/kernels/cpu/compare_kernel.cc"  // NOLINT
+#include "paddle/phi/kernels/cpu/logical_kernel.cc"  // NOLINT
+#include "paddle/phi/kernels/cpu/scale_kernel.cc"    // NOLINT
+#include "paddle/phi/kernels/cpu/where_kernel.cc"    // NOLINT
+
+#include "ref_shim_common.h"
+
+namespace {
+
+using phi::CPUContext;
+using phi::DenseTensor;
+using bf16 = phi::dtype::bfloat16;
+using fp16 = phi::dtype::float16;
+
+template <typename T>
+void CompareT(int op, const DenseTensor& x, const DenseTensor& y, DenseTensor* out) {
+  auto& ctx = GetCtx().ctx;
+  switch (op) {
+    case 0: phi::LessThanKernel<T, CPUContext>(ctx, x, y, out); break;
+    case 1: phi::LessEqualKernel<T, CPUContext>(ctx, x, y, out); break;
+    case 2: phi::GreaterThanKernel<T, CPUContext>(ctx, x, y, out); break;
+    case 3: phi::GreaterEqualKernel<T, CPUContext>(ctx, x, y, out); break;
+    case 4: phi::EqualKernel<T, CPUContext>(ctx, x, y, out); break;
+    case 5: phi::NotEqualKernel<T, CPUContext>(ctx, x, y, out); break;
+    default: throw std::runtime_error("bad compare op");
+  }
+}
+template <typename T>
+void LogicalT(int op, const DenseTensor& x, const DenseTensor& y, DenseTensor* out) {
+  auto& ctx = GetCtx().ctx;
+  switch (op) {
+    case 0: phi::LogicalAndKernel<T, CPUContext>(ctx, x, y, out); break;
+    case 1: phi::LogicalOrKernel<T, CPUContext>(ctx, x, y, out); break;
+    case 2: phi::LogicalXorKernel<T, CPUContext>(ctx, x, y, out); break;
+    default: throw std::runtime_error("bad logical op");
+  }
+}
+template <typename T>
+void BitwiseT(int op, const DenseTensor& x, const DenseTensor& y, DenseTensor* out) {
+  auto& ctx = GetCtx().ctx;
+  switch (op) {
+    case 0: phi::BitwiseAndKernel<T, CPUContext>(ctx, x, y, out); break;
+    case 1: phi::BitwiseOrKernel<T, CPUContext>(ctx, x, y, out); break;
+    case 2: phi::BitwiseXorKernel<T, CPUContext>(ctx, x, y, out); break;
+    default: throw std::runtime_error("bad bitwise op");
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+// op: 0 less_than, 1 less_equal, 2 greater_than, 3 greater_equal, 4 equal, 5 not_equal.  out: bool.
+int phi_ref_compare(int op, int dtype, const void* x, const int64_t* xdims, int xrank, const void* y,
+                    const int64_t* ydims, int yrank, const int64_t* odims, int orank, void* out) {
+  return Guard([&] {
+    auto xt = Wrap(x, xdims, xrank, dtype);
+    auto yt = Wrap(y, ydims, yrank, dtype);
+    auto ot = Wrap(out, odims, orank, kBool);
+    switch (dtype) {  // cpu/compare_kernel.cc:121-141
+      case kBool: CompareT<bool>(op, xt, yt, &ot); break;
+      case kUInt8: CompareT<uint8_t>(op, xt, yt, &ot); break;
+      case kInt8: CompareT<int8_t>(op, xt, yt, &ot); break;
+      case kInt16: CompareT<int16_t>(op, xt, yt, &ot); break;
+      case kInt32: CompareT<int32_t>(op, xt, yt, &ot); break;
+      case kInt64: CompareT<int64_t>(op, xt, yt, &ot); break;
+      case kFloat16: CompareT<fp16>(op, xt, yt, &ot); break;
+      case kBFloat16: CompareT<bf16>(op, xt, yt, &ot); break;
+      case kFloat32: CompareT<float>(op, xt, yt, &ot); break;
+      case kFloat64: CompareT<double>(op, xt, yt, &ot); break;
+      default: throw std::runtime_error("phi_ref_compare: bad dtype");
+    }
+  });
+}
+
+// op: 0 and, 1 or, 2 xor.  out: bool.
+int phi_ref_logical(int op, int dtype, const void* x, const int64_t* xdims, int xrank, const void* y,
+                    const int64_t* ydims, int yrank, const int64_t* odims, int orank, void* out) {
+  return Guard([&] {
+    auto xt = Wrap(x, xdims, xrank, dtype);
+    auto yt = Wrap(y, ydims, yrank, dtype);
+    auto ot = Wrap(out, odims, orank, kBool);
+    switch (dtype) {  // cpu/logical_kernel.cc:93-111 (no fp16 / bf16 / uint8 on CPU)
+      case kBool: LogicalT<bool>(op, xt, yt, &ot); break;
+      case kInt8: LogicalT<int8_t>(op, xt, yt, &ot); break;
+      case kInt16: LogicalT<int16_t>(op, xt, yt, &ot); break;
+      case kInt32: LogicalT<int32_t>(op, xt, yt, &ot); break;
+      case kInt64: LogicalT<int64_t>(op, xt, yt, &ot); break;
+      case kFloat32: LogicalT<float>(op, xt, yt, &ot); break;
+      case kFloat64: LogicalT<double>(op, xt, yt, &ot); break;
+      default: throw std::runtime_error("phi_ref_logical: dtype not registered on CPU");
+    }
+  });
+}
+
+// op: 0 and, 1 or, 2 xor.  out has the input dtype.
+int phi_ref_bitwise(int op, int dtype, const void* x, const int64_t* xdims, int xrank, const void* y,
+                    const int64_t* ydims, int yrank, const int64_t* odims, int orank, void* out) {
+  return Guard([&] {
+    auto xt = Wrap(x, xdims, xrank, dtype);
+    auto yt = Wrap(y, ydims, yrank, dtype);
+    auto ot = Wrap(out, odims, orank, dtype);
+    switch (dtype) {
+      case kBool: BitwiseT<bool>(op, xt, yt, &ot); break;
+      case kUInt8: BitwiseT<uint8_t>(op, xt, yt, &ot); break;
+      case kInt8: BitwiseT<int8_t>(op, xt, yt, &ot); break;
+      case kInt16: BitwiseT<int16_t>(op, xt, yt, &ot); break;
+      case kInt32: BitwiseT<int32_t>(op, xt, yt, &ot); break;
+      case kInt64: BitwiseT<int64_t>(op, xt, yt, &ot); break;
+      default: throw std::runtime_error("phi_ref_bitwise: dtype not registered on CPU");
+    }
+  });
+}
+
+// which: 0 logical_not (out bool), 1 bitwise_not (out dtype)
+int phi_ref_not(int which, int dtype, const void* x, int64_t numel, void* out) {
+  return Guard([&] {
+    auto& ctx = GetCtx().ctx;
+    auto xt = Wrap(x, &numel, 1, dtype);
+    auto ot = Wrap(out, &numel, 1, which == 0 ? kBool : dtype);
+    if (which == 0) {
+      switch (dtype) {
+        case kBool: phi::LogicalNotKernel<bool, CPUContext>(ctx, xt, &ot); break;
+        case kInt8: phi::LogicalNotKernel<int8_t, CPUContext>(ctx, xt, &ot); break;
+        case kInt16: phi::LogicalNotKernel<int16_t, CPUContext>(ctx, xt, &ot); break;
+        case kInt32: phi::LogicalNotKernel<int32_t, CPUContext>(ctx, xt, &ot); break;
+        case kInt64: phi::LogicalNotKernel<int64_t, CPUContext>(ctx, xt, &ot); break;
+        case kFloat32: phi::LogicalNotKernel<float, CPUContext>(ctx, xt, &ot); break;
+        case kFloat64: phi::LogicalNotKernel<double, CPUContext>(ctx, xt, &ot); break;
+        default: throw std::runtime_error("phi_ref_not: dtype not registered on CPU");
+      }
+    } else {
+      switch (dtype) {
+        case kBool: phi::BitwiseNotKernel<bool, CPUContext>(ctx, xt, &ot); break;
+        case kUInt8: phi::BitwiseNotKernel<uint8_t, CPUContext>(ctx, xt, &ot); break;
+        case kInt8: phi::BitwiseNotKernel<int8_t, CPUContext>(ctx, xt, &ot); break;
+        case kInt16: phi::BitwiseNotKernel<int16_t, CPUContext>(ctx, xt, &ot); break;
+        case kInt32: phi::BitwiseNotKernel<int32_t, CPUContext>(ctx, xt, &ot); break;
+        case kInt64: phi::BitwiseNotKernel<int64_t, CPUContext>(ctx, xt, &ot); break;
+        default: throw std::runtime_error("phi_ref_not: dtype not registered on CPU");
+      }
+    }
+  });
+}
+
+int phi_ref_scale(int dtype, const void* x, int64_t numel, double scale, double bias, int bias_after_scale, void* out) {
+  return Guard([&] {
+    auto& ctx = GetCtx().ctx;
+    auto xt = Wrap(x, &numel, 1, dtype);
+    auto ot = Wrap(out, &numel, 1, dtype);
+    // paddle.scale's attributes are Python floats, which pybind turns into Scalar(double)
+    // (paddle/fluid/pybind/eager_utils.cc:2297-2299); the kernel then takes scale.to<T>()
+    phi::Scalar s(scale), b(bias);
+    const bool after = bias_after_scale != 0;
+    switch (dtype) {  // cpu/scale_kernel.cc:52-66
+      case kBool: phi::ScaleKernel<bool, CPUContext>(ctx, xt, s, b, after, &ot); break;
+      case kUInt8: phi::ScaleKernel<uint8_t, CPUContext>(ctx, xt, s, b, after, &ot); break;
+      case kInt8: phi::ScaleKernel<int8_t, CPUContext>(ctx, xt, s, b, after, &ot); break;
+      case kInt16: phi::ScaleKernel<int16_t, CPUContext>(ctx, xt, s, b, after, &ot); break;
+      case kInt32: phi::ScaleKernel<int32_t, CPUContext>(ctx, xt, s, b, after, &ot); break;
+      case kInt64: phi::ScaleKernel<int64_t, CPUContext>(ctx, xt, s, b, after, &ot); break;
+      case kFloat16: phi::ScaleKernel<fp16, CPUContext>(ctx, xt, s, b, after, &ot); break;
+      case kBFloat16: phi::ScaleKernel<bf16, CPUContext>(ctx, xt, s, b, after, &ot); break;
+      case kFloat32: phi::ScaleKernel<float, CPUContext>(ctx, xt, s, b, after, &ot); break;
+      case kFloat64: phi::ScaleKernel<double, CPUContext>(ctx, xt, s, b, after, &ot); break;
+      default: throw std::runtime_error("phi_ref_scale: bad dtype");
+    }
+  });
+}
+
+int phi_ref_cast(int x_dtype, int out_dtype, const void* x, int64_t numel, void* out) {
+  return Guard([&] {
+    auto& ctx = GetCtx().ctx;
+    auto xt = Wrap(x, &numel, 1, x_dtype);
+    auto ot = Wrap(out, &numel, 1, out_dtype);
+    const auto od = ToPhi(out_dtype);
+    switch (x_dtype) {  // cpu/cast_kernel.cc registration list
+      case kBool: phi::CastKernel<bool, CPUContext>(ctx, xt, od, &ot); break;
+      case kUInt8: phi::CastKernel<uint8_t, CPUContext>(ctx, xt, od, &ot); break;
+      case kInt8: phi::CastKernel<int8_t, CPUContext>(ctx, xt, od, &ot); break;
+      case kInt16: phi::CastKernel<int16_t, CPUContext>(ctx, xt, od, &ot); break;
+      case kInt32: phi::CastKernel<int32_t, CPUContext>(ctx, xt, od, &ot); break;
+      case kInt64: phi::CastKernel<int64_t, CPUContext>(ctx, xt, od, &ot); break;
+      case kFloat16: phi::CastKernel<fp16, CPUContext>(ctx, xt, od, &ot); break;
+      case kBFloat16: phi::CastKernel<bf16, CPUContext>(ctx, xt, od, &ot); break;
+      case kFloat32: phi::CastKernel<float, CPUContext>(ctx, xt, od, &ot); break;
+      case kFloat64: phi::CastKernel<double, CPUContext>(ctx, xt, od, &ot); break;
+      default: throw std::runtime_error("phi_ref_cast: bad dtype");
+    }
+  });
+}
+
+int phi_ref_where(int dtype, const void* cond, const void* x, const void* y, int64_t numel, void* out) {
+  return Guard([&] {
+    auto& ctx = GetCtx().ctx;
+    auto ct = Wrap(cond, &numel, 1, kBool);
+    auto xt = Wrap(x, &numel, 1, dtype);
+    auto yt = Wrap(y, &numel, 1, dtype);
+    auto ot = Wrap(out, &numel, 1, dtype);
+    switch (dtype) {  // cpu/where_kernel.cc:40-41
+      case kInt32: phi::WhereKernel<int32_t, CPUContext>(ctx, ct, xt, yt, &ot); break;
+      case kInt64: phi::WhereKernel<int64_t, CPUContext>(ctx, ct, xt, yt, &ot); break;
+      case kFloat32: phi::WhereKernel<float, CPUContext>(ctx, ct, xt, yt, &ot); break;
+      case kFloat64: phi::WhereKernel<double, CPUContext>(ctx, ct, xt, yt, &ot); break;
+      default: throw std::runtime_error("phi_ref_where: dtype not registered on CPU");
+    }
+  });
+}
+
+}  // extern "C"

@@ -13,6 +13,9 @@ LIB_PATH = os.path.join(_HERE, "libpdb200.so")
 BOOL, UINT8, INT8, INT16, INT32, INT64, FLOAT16, BFLOAT16, FLOAT32, FLOAT64 = range(10)
 OK, INVALID_ARGUMENT, UNSUPPORTED, CUDA_ERROR, WORKSPACE_TOO_SMALL = range(5)
 REDUCE_SUM, REDUCE_MEAN, REDUCE_MAX, REDUCE_MIN, REDUCE_PROD = range(5)
+LESS_THAN, LESS_EQUAL, GREATER_THAN, GREATER_EQUAL, EQUAL, NOT_EQUAL = range(6)
+LOGICAL_AND, LOGICAL_OR, LOGICAL_XOR = range(3)
+BITWISE_AND, BITWISE_OR, BITWISE_XOR = range(3)
 MAX_RANK = 9
 
 _c_i64p = ctypes.POINTER(ctypes.c_int64)
@@ -32,6 +35,14 @@ SIGNATURES = {
     "pdb200_divide": (_int, [_vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
     "pdb200_maximum": (_int, [_vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
     "pdb200_minimum": (_int, [_vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
+    "pdb200_compare": (_int, [_int, _vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
+    "pdb200_logical": (_int, [_int, _vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
+    "pdb200_bitwise": (_int, [_int, _vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
+    "pdb200_logical_not": (_int, [_vp, ctypes.c_int64, _int, _vp, _vp]),
+    "pdb200_bitwise_not": (_int, [_vp, ctypes.c_int64, _int, _vp, _vp]),
+    "pdb200_scale": (_int, [_vp, ctypes.c_int64, _int, ctypes.c_double, ctypes.c_double, _int, _vp, _vp]),
+    "pdb200_cast": (_int, [_vp, ctypes.c_int64, _int, _int, _vp, _vp]),
+    "pdb200_where": (_int, [_vp, _vp, _vp, ctypes.c_int64, _int, _vp, _vp]),
     "pdb200_reduce_workspace_bytes": (_sz, [_int, _c_i64p, _int, _c_i64p, _int, _int, _int, _int]),
     "pdb200_sum_raw": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _int, _vp, _vp, _sz, _vp]),
     "pdb200_mean_raw": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _int, _vp, _vp, _sz, _vp]),

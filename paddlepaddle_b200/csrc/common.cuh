@@ -128,6 +128,48 @@ __device__ __forceinline__ void st_stream(T* p, const Vec<T>& r) {
                : "memory");
 }
 
+// N elements of T moved as one 2/4/8/16-byte access (N * sizeof(T) is a power of two <= 16): the output side
+// of kernels whose result type is narrower than their input (compare/logical: bool out), and both sides of
+// the unary kernels (cast).
+template <typename T, int N>
+struct alignas(sizeof(T) * N) Pack {
+  T v[N];
+};
+template <typename T, int N>
+__device__ __forceinline__ void st_stream(T* p, const Pack<T, N>& r) {
+  constexpr int B = (int)sizeof(T) * N;
+  static_assert(B == 2 || B == 4 || B == 8 || B == 16, "pack must be 2, 4, 8 or 16 bytes");
+  if constexpr (B == 16) {
+    const uint4 u = *reinterpret_cast<const uint4*>(&r);
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(u.x), "r"(u.y), "r"(u.z),
+                 "r"(u.w)
+                 : "memory");
+  } else if constexpr (B == 8) {
+    const uint2 u = *reinterpret_cast<const uint2*>(&r);
+    asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(u.x), "r"(u.y) : "memory");
+  } else if constexpr (B == 4) {
+    const uint32_t u = *reinterpret_cast<const uint32_t*>(&r);
+    asm volatile("st.global.L1::no_allocate.u32 [%0], %1;" ::"l"(p), "r"(u) : "memory");
+  } else {
+    const uint16_t u = *reinterpret_cast<const uint16_t*>(&r);
+    asm volatile("st.global.L1::no_allocate.u16 [%0], %1;" ::"l"(p), "h"(u) : "memory");
+  }
+}
+// Streaming load of a pack (coherent path: callers may run in place).
+template <typename T, int N>
+__device__ __forceinline__ Pack<T, N> ld_pack(const T* p) {
+  constexpr int B = (int)sizeof(T) * N;
+  static_assert(B == 1 || B == 2 || B == 4 || B == 8 || B == 16, "pack must be 1..16 bytes");
+  Pack<T, N> r;
+  if constexpr (B == 16) *reinterpret_cast<uint4*>(&r) = __ldcs(reinterpret_cast<const uint4*>(p));
+  else if constexpr (B == 8) *reinterpret_cast<uint2*>(&r) = __ldcs(reinterpret_cast<const uint2*>(p));
+  else if constexpr (B == 4) *reinterpret_cast<uint32_t*>(&r) = __ldcs(reinterpret_cast<const uint32_t*>(p));
+  else if constexpr (B == 2) *reinterpret_cast<uint16_t*>(&r) = __ldcs(reinterpret_cast<const uint16_t*>(p));
+  else *reinterpret_cast<uint8_t*>(&r) = __ldcs(reinterpret_cast<const uint8_t*>(p));
+  return r;
+}
+inline bool is_aligned_to(const void* p, size_t bytes) { return (reinterpret_cast<uintptr_t>(p) % bytes) == 0; }
+
 // Whole-vector conversion to float.  For bf16 the generic per-element path costs two
 // instructions on odd elements (PRMT + SHL); working on the 32-bit words gives one each:
 // low half = w << 16, high half = w & 0xffff0000.

@@ -137,9 +137,14 @@ template <> struct DivOp<bool> {
   static __device__ __forceinline__ bool apply(bool a, bool b) { return a && b; }
 };
 
+// Result type of an operator on T: T itself for arithmetic, bool for compare / logical.
 template <typename T, typename Op>
-__device__ __forceinline__ Vec<T> apply_vec(const Vec<T>& a, const Vec<T>& b) {
-  Vec<T> r;
+struct OpOut {
+  using type = decltype(Op::apply(T(), T()));
+};
+template <typename T, typename Op>
+__device__ __forceinline__ Pack<typename OpOut<T, Op>::type, Vec<T>::N> apply_vec(const Vec<T>& a, const Vec<T>& b) {
+  Pack<typename OpOut<T, Op>::type, Vec<T>::N> r;
 #pragma unroll
   for (int i = 0; i < Vec<T>::N; ++i) r.v[i] = Op::apply(a.v[i], b.v[i]);
   return r;
@@ -153,8 +158,8 @@ constexpr int kUnroll = 4;
 template <typename T, typename Op>
 __global__ void __launch_bounds__(kThreads) ew_same_kernel(const T* __restrict__ x,
                                                            const T* __restrict__ y,
-                                                           T* __restrict__ out, int64_t nvec,
-                                                           int64_t numel) {
+                                                           typename OpOut<T, Op>::type* __restrict__ out,
+                                                           int64_t nvec, int64_t numel) {
   constexpr int V = Vec<T>::N;
   const int64_t base = (int64_t)blockIdx.x * (kThreads * kUnroll) + threadIdx.x;
   if (base + (kUnroll - 1) * kThreads < nvec) {  // full tile: all loads first, then math+stores
@@ -181,8 +186,8 @@ __global__ void __launch_bounds__(kThreads) ew_same_kernel(const T* __restrict__
 
 // Unaligned / in-place-safe scalar fallback for Same.
 template <typename T, typename Op>
-__global__ void __launch_bounds__(kThreads) ew_same_scalar_kernel(const T* x, const T* y, T* out,
-                                                                  int64_t numel) {
+__global__ void __launch_bounds__(kThreads) ew_same_scalar_kernel(const T* x, const T* y,
+                                                                  typename OpOut<T, Op>::type* out, int64_t numel) {
   int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
   const int64_t stride = (int64_t)gridDim.x * kThreads;
   for (; i < numel; i += stride) out[i] = Op::apply(x[i], y[i]);
@@ -196,8 +201,8 @@ __global__ void __launch_bounds__(kThreads) ew_same_scalar_kernel(const T* x, co
 template <typename T, typename Op, bool SWAP>
 __global__ void __launch_bounds__(kThreads) ew_inner_kernel(const T* __restrict__ big,
                                                             const T* __restrict__ row,
-                                                            T* __restrict__ out, int64_t nvec,
-                                                            uint32_t P, uint32_t step_mod) {
+                                                            typename OpOut<T, Op>::type* __restrict__ out,
+                                                            int64_t nvec, uint32_t P, uint32_t step_mod) {
   constexpr int V = Vec<T>::N;
   const int64_t tile0 = (int64_t)blockIdx.x * (kThreads * kUnroll);
   const int64_t base = tile0 + threadIdx.x;
@@ -228,15 +233,15 @@ __global__ void __launch_bounds__(kThreads) ew_inner_kernel(const T* __restrict_
 template <typename T, typename Op, bool SWAP, bool VECTOR>
 __global__ void __launch_bounds__(kThreads) ew_outer_kernel(const T* __restrict__ big,
                                                             const T* __restrict__ colv,
-                                                            T* __restrict__ out, int64_t rows,
-                                                            int64_t cols, int64_t tiles_per_row) {
+                                                            typename OpOut<T, Op>::type* __restrict__ out,
+                                                            int64_t rows, int64_t cols, int64_t tiles_per_row) {
   constexpr int V = VECTOR ? Vec<T>::N : 1;
   const int64_t row = (int64_t)blockIdx.x / tiles_per_row;
   const int64_t tile = (int64_t)blockIdx.x - row * tiles_per_row;
   const T s = colv[row];
   const int64_t n = cols / V;  // vectors (or elements) in this row
   const T* src = big + row * cols;
-  T* dst = out + row * cols;
+  typename OpOut<T, Op>::type* dst = out + row * cols;
   const int64_t base = tile * (kThreads * kUnroll) + threadIdx.x;
   if constexpr (VECTOR) {
     Vec<T> sv;
@@ -276,8 +281,8 @@ struct GeneralParams {
 template <typename T, typename Op, bool VECTOR>
 __global__ void __launch_bounds__(kThreads) ew_general_kernel(const T* __restrict__ x,
                                                               const T* __restrict__ y,
-                                                              T* __restrict__ out, int64_t nruns,
-                                                              GeneralParams p) {
+                                                              typename OpOut<T, Op>::type* __restrict__ out,
+                                                              int64_t nruns, GeneralParams p) {
   constexpr int V = VECTOR ? Vec<T>::N : 1;
   const int64_t inner_runs = p.dims[0] / V;
   int64_t run = (int64_t)blockIdx.x * kThreads + threadIdx.x;
@@ -320,14 +325,16 @@ __global__ void __launch_bounds__(kThreads) ew_general_kernel(const T* __restric
 
 // ---- host launcher ----------------------------------------------------------------------
 template <typename T, typename Op>
-int launch_elementwise(const BroadcastPlan& p, const T* x, const T* y, T* out, cudaStream_t st) {
+int launch_elementwise(const BroadcastPlan& p, const T* x, const T* y, typename OpOut<T, Op>::type* out,
+                       cudaStream_t st) {
+  using O = typename OpOut<T, Op>::type;
   constexpr int V = Vec<T>::N;
-  const bool aliased = (out == x) || (out == y);
+  constexpr size_t kOutAlign = sizeof(O) * V;  // one output pack per input vector
   switch (p.kind) {
     case kBcastEmpty:
       return PDB200_OK;
     case kBcastSame: {
-      const bool vec_ok = is_aligned16(x) && is_aligned16(y) && is_aligned16(out);
+      const bool vec_ok = is_aligned16(x) && is_aligned16(y) && is_aligned_to(out, kOutAlign);
       if (vec_ok) {
         // In-place (out == x or y) is safe on the .nc path: each 16-byte chunk is read and
         // written by the same thread and never re-read.
@@ -344,7 +351,7 @@ int launch_elementwise(const BroadcastPlan& p, const T* x, const T* y, T* out, c
       const T* big = p.small_is_x ? y : x;
       const T* row = p.small_is_x ? x : y;
       const bool vec_ok = (p.cols % V == 0) && is_aligned16(big) && is_aligned16(row) &&
-                          is_aligned16(out) && (p.cols / V) <= 0x7fffffffLL;
+                          is_aligned_to(out, kOutAlign) && (p.cols / V) <= 0x7fffffffLL;
       if (!vec_ok) break;  // -> general
       const int64_t nvec = p.numel / V;
       const uint32_t P = (uint32_t)(p.cols / V);
@@ -359,7 +366,7 @@ int launch_elementwise(const BroadcastPlan& p, const T* x, const T* y, T* out, c
     case kBcastOuter: {
       const T* big = p.small_is_x ? y : x;
       const T* colv = p.small_is_x ? x : y;
-      const bool vec_ok = (p.cols % V == 0) && is_aligned16(big) && is_aligned16(out);
+      const bool vec_ok = (p.cols % V == 0) && is_aligned16(big) && is_aligned_to(out, kOutAlign);
       // rows shorter than one warp of vectors waste most of a CTA: use the general walk
       if (p.rows > 1 && p.cols < 32 * V) break;
       const int64_t n = vec_ok ? p.cols / V : p.cols;
@@ -377,7 +384,6 @@ int launch_elementwise(const BroadcastPlan& p, const T* x, const T* y, T* out, c
       break;
   }
   // General walk (also the fallback for unaligned Inner/Outer shapes).
-  (void)aliased;
   GeneralParams gp;
   gp.rank = p.rank;
   for (int i = 0; i < PDB200_MAX_RANK; ++i) {
@@ -388,7 +394,7 @@ int launch_elementwise(const BroadcastPlan& p, const T* x, const T* y, T* out, c
   // vector runs need: inner dim a multiple of V; every outer stride of a contiguous operand
   // is then a multiple of V automatically (strides are products of inner dims) as long as
   // that operand's innermost stride is 1; bases aligned.
-  const bool vec_ok = (gp.dims[0] % V == 0) && is_aligned16(x) && is_aligned16(y) && is_aligned16(out);
+  const bool vec_ok = (gp.dims[0] % V == 0) && is_aligned16(x) && is_aligned16(y) && is_aligned_to(out, kOutAlign);
   const int64_t nruns = vec_ok ? p.numel / V : p.numel;
   const int64_t blocks = std::min<int64_t>((nruns + kThreads - 1) / kThreads, (int64_t)sm_count() * 64);
   if (vec_ok)
@@ -419,7 +425,7 @@ int elementwise_entry(const char* name, const void* x, const int64_t* xd, int xr
     using T = typename CType<DT>::type;                                                            \
     if constexpr (((kMask >> DT) & 1u) != 0)                                                       \
       return launch_elementwise<T, OpT<T>>(p, static_cast<const T*>(x), static_cast<const T*>(y),  \
-                                           static_cast<T*>(out), st);                              \
+                                           static_cast<typename OpOut<T, OpT<T>>::type*>(out), st); \
     break;                                                                                         \
   }
   switch (dtype) {

@@ -1,0 +1,170 @@
+// elementwise_pred.cu — compare / logical / bitwise binary ops on the broadcast engine.
+//
+// Replaces (fresh design): the KPS compare / logical / bitwise kernels, which are thin callers of
+// funcs::BroadcastKernel —
+//   paddle/phi/kernels/kps/compare_kernel.cu:49-66,143-173   (functors: funcs/compare_functors.h:21-62)
+//   paddle/phi/kernels/kps/logical_kernel.cu:112-134          (functors: funcs/logical_functor.h:20-40)
+//   paddle/phi/kernels/kps/bitwise_kernel.cu:94-136           (functors: funcs/bitwise_functors.h:20-49)
+// Same launcher and kernels as add/multiply (elementwise_impl.cuh); compare and logical write one bool per
+// element, so a thread that loads 16 bytes of each operand stores a 2/4/8/16-byte pack of bools and a warp's
+// store is still one contiguous run.
+#include "elementwise_impl.cuh"
+
+namespace pdb200 {
+
+// ---- compare ------------------------------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ float as_float(T v) { return static_cast<float>(v); }
+template <> __device__ __forceinline__ float as_float<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <> __device__ __forceinline__ float as_float<__half>(__half v) { return __half2float(v); }
+
+template <typename T> struct LessThanOp {
+  static __device__ __forceinline__ bool apply(T a, T b) { return a < b; }
+};
+template <typename T> struct LessEqualOp {
+  static __device__ __forceinline__ bool apply(T a, T b) { return a <= b; }
+};
+// EqualFunctor (compare_functors.h:37-51): float and double are "equal" when |a - b| < 1e-8 (difference taken
+// in T, compared in double), infinities compare exactly, NaN equals nothing.  bf16 / fp16 take the same
+// route (std::is_floating_point is specialised for them): the difference is one float subtraction rounded
+// back to the 16-bit type.  Integers and bool use plain ==.
+template <typename T> struct EqualOp {
+  static __device__ __forceinline__ bool apply(T a, T b) { return a == b; }
+};
+template <> struct EqualOp<float> {
+  static __device__ __forceinline__ bool apply(float a, float b) {
+    if (isinf(a) || isinf(b)) return a == b;
+    if (isnan(a) || isnan(b)) return false;
+    return fabs(static_cast<double>(__fsub_rn(a, b))) < 1e-8;
+  }
+};
+template <> struct EqualOp<double> {
+  static __device__ __forceinline__ bool apply(double a, double b) {
+    // the reference tests isinf / isnan on the value cast to float: a finite double beyond float range counts as inf
+    const float fa = static_cast<float>(a), fb = static_cast<float>(b);
+    if (isinf(fa) || isinf(fb)) return a == b;
+    if (isnan(fa) || isnan(fb)) return false;
+    return fabs(__dsub_rn(a, b)) < 1e-8;
+  }
+};
+template <typename T> struct NotEqualOp {
+  static __device__ __forceinline__ bool apply(T a, T b) { return !EqualOp<T>::apply(a, b); }
+};
+#define PDB_HALF_CMP(T)                                                                                  \
+  template <> struct LessThanOp<T> {                                                                     \
+    static __device__ __forceinline__ bool apply(T a, T b) { return as_float(a) < as_float(b); }         \
+  };                                                                                                     \
+  template <> struct LessEqualOp<T> {                                                                    \
+    static __device__ __forceinline__ bool apply(T a, T b) { return as_float(a) <= as_float(b); }        \
+  };                                                                                                     \
+  template <> struct EqualOp<T> {                                                                        \
+    static __device__ __forceinline__ bool apply(T a, T b) {                                             \
+      const float fa = as_float(a), fb = as_float(b);                                                    \
+      if (isinf(fa) || isinf(fb)) return fa == fb;                                                       \
+      if (isnan(fa) || isnan(fb)) return false;                                                          \
+      return fabs(static_cast<double>(as_float(cvt<T>(__fsub_rn(fa, fb))))) < 1e-8;                      \
+    }                                                                                                    \
+  };
+PDB_HALF_CMP(__nv_bfloat16)
+PDB_HALF_CMP(__half)
+#undef PDB_HALF_CMP
+
+// ---- logical: static_cast<bool>(a) op static_cast<bool>(b) ------------------------------------------------
+template <typename T> __device__ __forceinline__ bool truthy(T v) { return static_cast<bool>(v); }
+template <> __device__ __forceinline__ bool truthy<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v) != 0.0f; }
+template <> __device__ __forceinline__ bool truthy<__half>(__half v) { return __half2float(v) != 0.0f; }
+template <typename T> struct LogicalAndOp {
+  static __device__ __forceinline__ bool apply(T a, T b) { return truthy(a) && truthy(b); }
+};
+template <typename T> struct LogicalOrOp {
+  static __device__ __forceinline__ bool apply(T a, T b) { return truthy(a) || truthy(b); }
+};
+template <typename T> struct LogicalXorOp {
+  static __device__ __forceinline__ bool apply(T a, T b) { return truthy(a) != truthy(b); }
+};
+
+// ---- bitwise: a & b, a | b, a ^ b; bool uses &&, ||, != -----------------------------------------------------
+template <typename T> struct BitAndOp {
+  static __device__ __forceinline__ T apply(T a, T b) { return static_cast<T>(a & b); }
+};
+template <typename T> struct BitOrOp {
+  static __device__ __forceinline__ T apply(T a, T b) { return static_cast<T>(a | b); }
+};
+template <typename T> struct BitXorOp {
+  static __device__ __forceinline__ T apply(T a, T b) { return static_cast<T>(a ^ b); }
+};
+template <> struct BitAndOp<bool> {
+  static __device__ __forceinline__ bool apply(bool a, bool b) { return a && b; }
+};
+template <> struct BitOrOp<bool> {
+  static __device__ __forceinline__ bool apply(bool a, bool b) { return a || b; }
+};
+template <> struct BitXorOp<bool> {
+  static __device__ __forceinline__ bool apply(bool a, bool b) { return a != b; }
+};
+
+#define B(dt) (1u << (dt))
+constexpr uint32_t kAllTypes = (1u << (PDB200_FLOAT64 + 1)) - 1;                      // compare_kernel.cu:157-173
+constexpr uint32_t kLogicalTypes = kAllTypes & ~B(PDB200_UINT8);                      // logical_kernel.cu:112-129
+constexpr uint32_t kBitwiseTypes = B(PDB200_BOOL) | B(PDB200_UINT8) | B(PDB200_INT8) | B(PDB200_INT16) |
+                                   B(PDB200_INT32) | B(PDB200_INT64);                 // bitwise_kernel.cu:94-136
+#undef B
+
+}  // namespace pdb200
+
+extern "C" {
+
+int pdb200_compare(int op, const void* x, const int64_t* x_dims, int x_rank, const void* y, const int64_t* y_dims,
+                   int y_rank, void* out, int dtype, void* stream) {
+  using namespace pdb200;
+  switch (op) {
+    case PDB200_LESS_THAN:
+      return elementwise_entry<LessThanOp, kAllTypes>("less_than", x, x_dims, x_rank, y, y_dims, y_rank, out, dtype, stream);
+    case PDB200_LESS_EQUAL:
+      return elementwise_entry<LessEqualOp, kAllTypes>("less_equal", x, x_dims, x_rank, y, y_dims, y_rank, out, dtype, stream);
+    // a > b is b < a: the operands trade places on the host, the kernels are shared
+    case PDB200_GREATER_THAN:
+      return elementwise_entry<LessThanOp, kAllTypes>("greater_than", y, y_dims, y_rank, x, x_dims, x_rank, out, dtype, stream);
+    case PDB200_GREATER_EQUAL:
+      return elementwise_entry<LessEqualOp, kAllTypes>("greater_equal", y, y_dims, y_rank, x, x_dims, x_rank, out, dtype, stream);
+    case PDB200_EQUAL:
+      return elementwise_entry<EqualOp, kAllTypes>("equal", x, x_dims, x_rank, y, y_dims, y_rank, out, dtype, stream);
+    case PDB200_NOT_EQUAL:
+      return elementwise_entry<NotEqualOp, kAllTypes>("not_equal", x, x_dims, x_rank, y, y_dims, y_rank, out, dtype, stream);
+    default:
+      return fail(PDB200_INVALID_ARGUMENT, "compare: unknown op code " + std::to_string(op));
+  }
+}
+
+int pdb200_logical(int op, const void* x, const int64_t* x_dims, int x_rank, const void* y, const int64_t* y_dims,
+                   int y_rank, void* out, int dtype, void* stream) {
+  using namespace pdb200;
+  switch (op) {
+    case PDB200_LOGICAL_AND:
+      return elementwise_entry<LogicalAndOp, kLogicalTypes>("logical_and", x, x_dims, x_rank, y, y_dims, y_rank, out, dtype, stream);
+    case PDB200_LOGICAL_OR:
+      return elementwise_entry<LogicalOrOp, kLogicalTypes>("logical_or", x, x_dims, x_rank, y, y_dims, y_rank, out, dtype, stream);
+    case PDB200_LOGICAL_XOR:
+      return elementwise_entry<LogicalXorOp, kLogicalTypes>("logical_xor", x, x_dims, x_rank, y, y_dims, y_rank, out, dtype, stream);
+    default:
+      return fail(PDB200_INVALID_ARGUMENT, "logical: unknown op code " + std::to_string(op) +
+                                               " (logical_not is unary: pdb200_logical_not)");
+  }
+}
+
+int pdb200_bitwise(int op, const void* x, const int64_t* x_dims, int x_rank, const void* y, const int64_t* y_dims,
+                   int y_rank, void* out, int dtype, void* stream) {
+  using namespace pdb200;
+  switch (op) {
+    case PDB200_BITWISE_AND:
+      return elementwise_entry<BitAndOp, kBitwiseTypes>("bitwise_and", x, x_dims, x_rank, y, y_dims, y_rank, out, dtype, stream);
+    case PDB200_BITWISE_OR:
+      return elementwise_entry<BitOrOp, kBitwiseTypes>("bitwise_or", x, x_dims, x_rank, y, y_dims, y_rank, out, dtype, stream);
+    case PDB200_BITWISE_XOR:
+      return elementwise_entry<BitXorOp, kBitwiseTypes>("bitwise_xor", x, x_dims, x_rank, y, y_dims, y_rank, out, dtype, stream);
+    default:
+      return fail(PDB200_INVALID_ARGUMENT, "bitwise: unknown op code " + std::to_string(op) +
+                                               " (bitwise_not is unary: pdb200_bitwise_not)");
+  }
+}
+
+}  // extern "C"

@@ -84,7 +84,9 @@ def _workspace(nbytes, device):
 # ---------------------------------------------------------------------------------------
 # elementwise
 # ---------------------------------------------------------------------------------------
-def _elementwise(fn_name, x, y, out=None):
+def _elementwise(fn_name, x, y, out=None, op=None, out_dtype=None):
+    """One binary broadcast call.  `op`: leading op-code argument of the coded entry points (compare /
+    logical / bitwise); `out_dtype`: dtype of the result when it is not x's (bool for compare / logical)."""
     _require_cuda(x, y)
     if x.dtype != y.dtype:
         raise TypeError(f"(InvalidType) the dtypes of X ({x.dtype}) and Y ({y.dtype}) must match "
@@ -99,11 +101,13 @@ def _elementwise(fn_name, x, y, out=None):
     L.check(lib.pdb200_broadcast_shape(xd, xr, yd, yr, od, ctypes.byref(orank)), lib)
     oshape = tuple(od[i] for i in range(orank.value))
     if out is None:
-        out = torch.empty(oshape, dtype=x.dtype, device=x.device)
+        out = torch.empty(oshape, dtype=out_dtype or x.dtype, device=x.device)
     elif tuple(out.shape) != oshape:
         # test_elementwise_add_op.py:695-720 (inplace broadcast errors)
         raise ValueError(f"(InvalidArgument) The shape of tensor assigned value must be the same: {tuple(out.shape)} vs {oshape}")
-    L.check(getattr(lib, fn_name)(_ptr(x), xd, xr, _ptr(y), yd, yr, _ptr(out), _dtype_code(x.dtype), _stream()), lib)
+    lead = () if op is None else (op,)
+    L.check(getattr(lib, fn_name)(*lead, _ptr(x), xd, xr, _ptr(y), yd, yr, _ptr(out), _dtype_code(x.dtype), _stream()),
+            lib)
     return out
 
 
@@ -144,6 +148,114 @@ def maximum(x, y, name=None):
 def minimum(x, y, name=None):
     """paddle.minimum(x, y): elementwise `x < y ? x : y`."""
     return _elementwise("pdb200_minimum", x, y)
+
+
+# compare / logical / bitwise: python/paddle/tensor/logic.py (equal :476, less_than :884, logical_and :132,
+# bitwise_and :1263, ...).  Compare and logical results are bool tensors.
+def less_than(x, y, name=None):
+    return _elementwise("pdb200_compare", x, y, op=L.LESS_THAN, out_dtype=torch.bool)
+
+
+def less_equal(x, y, name=None):
+    return _elementwise("pdb200_compare", x, y, op=L.LESS_EQUAL, out_dtype=torch.bool)
+
+
+def greater_than(x, y, name=None):
+    return _elementwise("pdb200_compare", x, y, op=L.GREATER_THAN, out_dtype=torch.bool)
+
+
+def greater_equal(x, y, name=None):
+    return _elementwise("pdb200_compare", x, y, op=L.GREATER_EQUAL, out_dtype=torch.bool)
+
+
+def equal(x, y, name=None):
+    """paddle.equal: for float32/float64 "equal" means |x - y| < 1e-8 (the reference's EqualFunctor)."""
+    return _elementwise("pdb200_compare", x, y, op=L.EQUAL, out_dtype=torch.bool)
+
+
+def not_equal(x, y, name=None):
+    return _elementwise("pdb200_compare", x, y, op=L.NOT_EQUAL, out_dtype=torch.bool)
+
+
+def logical_and(x, y, out=None, name=None):
+    return _elementwise("pdb200_logical", x, y, out=out, op=L.LOGICAL_AND, out_dtype=torch.bool)
+
+
+def logical_or(x, y, out=None, name=None):
+    return _elementwise("pdb200_logical", x, y, out=out, op=L.LOGICAL_OR, out_dtype=torch.bool)
+
+
+def logical_xor(x, y, out=None, name=None):
+    return _elementwise("pdb200_logical", x, y, out=out, op=L.LOGICAL_XOR, out_dtype=torch.bool)
+
+
+def bitwise_and(x, y, out=None, name=None):
+    return _elementwise("pdb200_bitwise", x, y, out=out, op=L.BITWISE_AND)
+
+
+def bitwise_or(x, y, out=None, name=None):
+    return _elementwise("pdb200_bitwise", x, y, out=out, op=L.BITWISE_OR)
+
+
+def bitwise_xor(x, y, out=None, name=None):
+    return _elementwise("pdb200_bitwise", x, y, out=out, op=L.BITWISE_XOR)
+
+
+# ---------------------------------------------------------------------------------------
+# one-input maps and where
+# ---------------------------------------------------------------------------------------
+def _unary(fn_name, x, out_dtype, *mid):
+    _require_cuda(x)
+    lib = L.load()
+    x = x.contiguous()
+    out = torch.empty(x.shape, dtype=out_dtype, device=x.device)
+    L.check(getattr(lib, fn_name)(_ptr(x), x.numel(), _dtype_code(x.dtype), *mid, _ptr(out), _stream()), lib)
+    return out
+
+
+def logical_not(x, out=None, name=None):
+    """paddle.logical_not (python/paddle/tensor/logic.py:331): bool tensor, true where x == 0."""
+    return _unary("pdb200_logical_not", x, torch.bool)
+
+
+def bitwise_not(x, out=None, name=None):
+    """paddle.bitwise_not (logic.py:1500): ~x for integers, !x for bool."""
+    return _unary("pdb200_bitwise_not", x, x.dtype)
+
+
+def scale(x, scale=1.0, bias=0.0, bias_after_scale=True, act=None, name=None):
+    """paddle.scale (python/paddle/tensor/math.py:243): scale*x + bias, or scale*(x + bias)."""
+    if act is not None:
+        raise NotImplementedError("(Unimplemented) scale(act=...) is a static-graph legacy option outside this path")
+    if isinstance(scale, torch.Tensor):
+        scale = scale.item()  # ScaleKernel takes a Scalar; a tensor scale is read on the host in the reference too
+    return _unary("pdb200_scale", x, x.dtype, float(scale), float(bias), int(bool(bias_after_scale)))
+
+
+def cast(x, dtype):
+    """paddle.cast (python/paddle/tensor/manipulation.py:200): static_cast per element; same dtype returns a copy."""
+    dt = _as_torch_dtype(dtype)
+    return _unary("pdb200_cast", x, dt, _dtype_code(dt))
+
+
+def where(condition, x, y, name=None):
+    """paddle.where(condition, x, y) (python/paddle/tensor/search.py:704).  WhereKernel takes three tensors of ONE
+    shape; the reference's Python layer first materialises differently-shaped operands with its `expand` op
+    (search.py:776-797), which is outside this path — so here the three shapes must already agree."""
+    _require_cuda(condition, x, y)
+    if condition.dtype != torch.bool:
+        raise TypeError("(InvalidType) the dtype of condition must be bool")
+    if x.dtype != y.dtype:
+        raise TypeError(f"(InvalidType) the dtypes of X ({x.dtype}) and Y ({y.dtype}) must match")
+    if not (tuple(condition.shape) == tuple(x.shape) == tuple(y.shape)):
+        raise ValueError("(InvalidArgument) where: condition, x and y must have the same shape "
+                         f"(got {tuple(condition.shape)}, {tuple(x.shape)}, {tuple(y.shape)}); expand them first")
+    condition, x, y = condition.contiguous(), x.contiguous(), y.contiguous()
+    lib = L.load()
+    out = torch.empty(x.shape, dtype=x.dtype, device=x.device)
+    L.check(lib.pdb200_where(_ptr(condition), _ptr(x), _ptr(y), out.numel(), _dtype_code(x.dtype), _ptr(out), _stream()),
+            lib)
+    return out
 
 
 # ---------------------------------------------------------------------------------------

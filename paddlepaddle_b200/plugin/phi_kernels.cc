@@ -101,6 +101,62 @@ PDB200_PHI_BINARY(Maximum, pdb200_maximum)
 PDB200_PHI_BINARY(Minimum, pdb200_minimum)
 #undef PDB200_PHI_BINARY
 
+// ---- compare / logical / bitwise (kps/compare_kernel.cu:49-66, kps/logical_kernel.cu:60-91, kps/bitwise_kernel.cu:55-80)
+#define PDB200_PHI_CODED(Name, OutT, fn, OP)                                                             \
+  template <typename T, typename Context>                                                                \
+  void Name##Kernel(const Context& ctx, const DenseTensor& x, const DenseTensor& y, DenseTensor* out) {  \
+    OutT* o = ctx.template Alloc<OutT>(out);                                                             \
+    auto xd = Dims(x), yd = Dims(y);                                                                     \
+    Check(fn(OP, x.data<T>(), xd.data(), static_cast<int>(xd.size()), y.data<T>(), yd.data(),            \
+             static_cast<int>(yd.size()), o, Code(x.dtype()), ctx.stream()));                            \
+  }
+PDB200_PHI_CODED(LessThan, bool, pdb200_compare, PDB200_LESS_THAN)
+PDB200_PHI_CODED(LessEqual, bool, pdb200_compare, PDB200_LESS_EQUAL)
+PDB200_PHI_CODED(GreaterThan, bool, pdb200_compare, PDB200_GREATER_THAN)
+PDB200_PHI_CODED(GreaterEqual, bool, pdb200_compare, PDB200_GREATER_EQUAL)
+PDB200_PHI_CODED(Equal, bool, pdb200_compare, PDB200_EQUAL)
+PDB200_PHI_CODED(NotEqual, bool, pdb200_compare, PDB200_NOT_EQUAL)
+PDB200_PHI_CODED(LogicalAnd, bool, pdb200_logical, PDB200_LOGICAL_AND)
+PDB200_PHI_CODED(LogicalOr, bool, pdb200_logical, PDB200_LOGICAL_OR)
+PDB200_PHI_CODED(LogicalXor, bool, pdb200_logical, PDB200_LOGICAL_XOR)
+PDB200_PHI_CODED(BitwiseAnd, T, pdb200_bitwise, PDB200_BITWISE_AND)
+PDB200_PHI_CODED(BitwiseOr, T, pdb200_bitwise, PDB200_BITWISE_OR)
+PDB200_PHI_CODED(BitwiseXor, T, pdb200_bitwise, PDB200_BITWISE_XOR)
+#undef PDB200_PHI_CODED
+
+// ---- one-input maps and where (kps/logical_kernel.cu:71-91, kps/bitwise_kernel.cu:69-80, gpu/scale_kernel.cu:45-65,
+//      gpu/cast_kernel.cu:25-41, gpu/where_kernel.cu:32-46)
+template <typename T, typename Context>
+void LogicalNotKernel(const Context& ctx, const DenseTensor& x, DenseTensor* out) {
+  bool* o = ctx.template Alloc<bool>(out);
+  Check(pdb200_logical_not(x.data<T>(), x.numel(), Code(x.dtype()), o, ctx.stream()));
+}
+template <typename T, typename Context>
+void BitwiseNotKernel(const Context& ctx, const DenseTensor& x, DenseTensor* out) {
+  T* o = ctx.template Alloc<T>(out);
+  Check(pdb200_bitwise_not(x.data<T>(), x.numel(), Code(x.dtype()), o, ctx.stream()));
+}
+template <typename T, typename Context>
+void ScaleKernel(const Context& ctx, const DenseTensor& x, const phi::Scalar& scale, const phi::Scalar& bias,
+                 bool bias_after_scale, DenseTensor* out) {
+  T* o = ctx.template Alloc<T>(out);
+  if (x.numel() <= 0 || !x.initialized()) return;
+  Check(pdb200_scale(x.data<T>(), x.numel(), Code(x.dtype()), scale.to<double>(), bias.to<double>(),
+                     bias_after_scale ? 1 : 0, o, ctx.stream()));
+}
+template <typename T, typename Context>
+void CastKernel(const Context& ctx, const DenseTensor& x, DataType out_dtype, DenseTensor* out) {
+  if (out->IsSharedWith(x) && out_dtype == x.dtype()) return;  // same dtype in place: nothing to do
+  void* o = ctx.Alloc(out, out_dtype);
+  Check(pdb200_cast(x.data<T>(), x.numel(), Code(x.dtype()), Code(out_dtype), o, ctx.stream()));
+}
+template <typename T, typename Context>
+void WhereKernel(const Context& ctx, const DenseTensor& condition, const DenseTensor& x, const DenseTensor& y,
+                 DenseTensor* out) {
+  T* o = ctx.template Alloc<T>(out);
+  Check(pdb200_where(condition.data<bool>(), x.data<T>(), y.data<T>(), x.numel(), Code(x.dtype()), o, ctx.stream()));
+}
+
 // ---- reductions --------------------------------------------------------------------------
 typedef int (*ReduceFn)(const void*, const int64_t*, int, const int64_t*, int, int, int, int, void*, void*,
                         size_t, void*);
@@ -259,6 +315,44 @@ PD_REGISTER_KERNEL(maximum, GPU, ALL_LAYOUT, pdb200_phi::MaximumKernel, float, d
                    phi::dtype::float16, phi::dtype::bfloat16) {}
 PD_REGISTER_KERNEL(minimum, GPU, ALL_LAYOUT, pdb200_phi::MinimumKernel, float, double, int, int64_t,
                    phi::dtype::float16, phi::dtype::bfloat16) {}
+// compare / logical write BOOL whatever the input dtype (kps/compare_kernel.cu:156-173, kps/logical_kernel.cu:112-134)
+#define PDB200_REGISTER_COMPARE(name, Fn)                                                                           \
+  PD_REGISTER_KERNEL(name, GPU, ALL_LAYOUT, pdb200_phi::Fn##Kernel, bool, int, uint8_t, int8_t, int16_t, int64_t,   \
+                     float, double, phi::dtype::float16, phi::dtype::bfloat16) {                                    \
+    kernel->OutputAt(0).SetDataType(phi::DataType::BOOL);                                                           \
+  }
+PDB200_REGISTER_COMPARE(less_than, LessThan)
+PDB200_REGISTER_COMPARE(less_equal, LessEqual)
+PDB200_REGISTER_COMPARE(greater_than, GreaterThan)
+PDB200_REGISTER_COMPARE(greater_equal, GreaterEqual)
+PDB200_REGISTER_COMPARE(equal, Equal)
+PDB200_REGISTER_COMPARE(not_equal, NotEqual)
+#define PDB200_REGISTER_LOGICAL(name, Fn)                                                                           \
+  PD_REGISTER_KERNEL(name, GPU, ALL_LAYOUT, pdb200_phi::Fn##Kernel, float, phi::dtype::float16,                     \
+                     phi::dtype::bfloat16, double, bool, int64_t, int, int8_t, int16_t) {                           \
+    kernel->OutputAt(0).SetDataType(phi::DataType::BOOL);                                                           \
+  }
+PDB200_REGISTER_LOGICAL(logical_and, LogicalAnd)
+PDB200_REGISTER_LOGICAL(logical_or, LogicalOr)
+PDB200_REGISTER_LOGICAL(logical_xor, LogicalXor)
+PDB200_REGISTER_LOGICAL(logical_not, LogicalNot)
+PD_REGISTER_KERNEL(bitwise_and, GPU, ALL_LAYOUT, pdb200_phi::BitwiseAndKernel, bool, uint8_t, int8_t, int16_t, int,
+                   int64_t) {}
+PD_REGISTER_KERNEL(bitwise_or, GPU, ALL_LAYOUT, pdb200_phi::BitwiseOrKernel, bool, uint8_t, int8_t, int16_t, int,
+                   int64_t) {}
+PD_REGISTER_KERNEL(bitwise_xor, GPU, ALL_LAYOUT, pdb200_phi::BitwiseXorKernel, bool, uint8_t, int8_t, int16_t, int,
+                   int64_t) {}
+PD_REGISTER_KERNEL(bitwise_not, GPU, ALL_LAYOUT, pdb200_phi::BitwiseNotKernel, bool, uint8_t, int8_t, int16_t, int,
+                   int64_t) {}
+// gpu/scale_kernel.cu:67-83, gpu/cast_kernel.cu:43-66, gpu/where_kernel.cu:48-57 (complex and float8 stay in-tree)
+PD_REGISTER_KERNEL(scale, GPU, ALL_LAYOUT, pdb200_phi::ScaleKernel, bool, float, double, phi::dtype::float16,
+                   phi::dtype::bfloat16, uint8_t, int8_t, int16_t, int, int64_t) {}
+PD_REGISTER_KERNEL(cast, GPU, ALL_LAYOUT, pdb200_phi::CastKernel, float, double, int, int64_t, int16_t, bool, int8_t,
+                   uint8_t, phi::dtype::float16, phi::dtype::bfloat16) {
+  kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);
+}
+PD_REGISTER_KERNEL(where, GPU, ALL_LAYOUT, pdb200_phi::WhereKernel, float, double, int, int64_t, phi::dtype::float16,
+                   phi::dtype::bfloat16) {}
 PD_REGISTER_KERNEL(sum_raw, GPU, ALL_LAYOUT, pdb200_phi::SumRawKernel, bool, float, double, phi::dtype::float16,
                    phi::dtype::bfloat16, int, int64_t) {
   kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);  // reduce_sum_kernel.cc:75-77

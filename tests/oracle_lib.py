@@ -17,21 +17,24 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PORT_SO = os.path.join(ROOT, "oracle", "liboracle.so")
 PORT_SRC = os.path.join(ROOT, "oracle", "phi_cpu_oracle.c")
+PORT_SRCS = [PORT_SRC, os.path.join(ROOT, "oracle", "phi_cpu_oracle_family.c")]
 REF_SO = os.path.join(ROOT, "oracle", "_ref", "libphi_cpu_ref.so")
 
 BOOL, UINT8, INT8, INT16, INT32, INT64, FLOAT16, BFLOAT16, FLOAT32, FLOAT64 = range(10)
 NP2CODE = {np.dtype(np.bool_): BOOL, np.dtype(np.uint8): UINT8, np.dtype(np.int8): INT8,
            np.dtype(np.int16): INT16, np.dtype(np.int32): INT32, np.dtype(np.int64): INT64,
            np.dtype(np.float32): FLOAT32, np.dtype(np.float64): FLOAT64}
+CODE2NP = {BOOL: np.bool_, UINT8: np.uint8, INT8: np.int8, INT16: np.int16, INT32: np.int32, INT64: np.int64,
+           FLOAT16: np.uint16, BFLOAT16: np.uint16, FLOAT32: np.float32, FLOAT64: np.float64}
 OPS = {"sum": 0, "mean": 1, "max": 2, "min": 3, "prod": 4}
 
 _i64p = ctypes.POINTER(ctypes.c_int64)
 
 
 def build_port(force=False):
-    if force or not os.path.exists(PORT_SO) or os.path.getmtime(PORT_SO) < os.path.getmtime(PORT_SRC):
+    if force or not os.path.exists(PORT_SO) or os.path.getmtime(PORT_SO) < max(os.path.getmtime(p) for p in PORT_SRCS):
         subprocess.check_call(["gcc", "-O2", "-fPIC", "-shared", "-std=gnu11", "-fno-fast-math",
-                               "-ffp-contract=off", "-o", PORT_SO, PORT_SRC, "-lm"])
+                               "-ffp-contract=off", "-o", PORT_SO, *PORT_SRCS, "-lm"])
     return PORT_SO
 
 
@@ -199,6 +202,72 @@ class Oracle:
             _vp(db) if db is not None else None)
         self._check(rc)
         return dx, ds, db
+
+    # ---- the rest of the elementwise family (oracle/phi_cpu_oracle_family.c, oracle/ref_shim_family.cc) ----
+    def _binary_coded(self, fam, opc, x, y, code, out_dtype):
+        x = np.ascontiguousarray(x)
+        y = np.ascontiguousarray(y)
+        code = NP2CODE[x.dtype] if code is None else code
+        oshape = np.broadcast_shapes(x.shape, y.shape)
+        out = np.empty(oshape, out_dtype or x.dtype)
+        xd, xr = _dims(x.shape)
+        yd, yr = _dims(y.shape)
+        if self.kind == "port":
+            rc = getattr(self.lib, "oracle_" + fam)(opc, code, _vp(x), xd, xr, _vp(y), yd, yr, _vp(out))
+        else:
+            od, orank = _dims(oshape)
+            rc = getattr(self.lib, "phi_ref_" + fam)(opc, code, _vp(x), xd, xr, _vp(y), yd, yr, od, orank, _vp(out))
+        self._check(rc)
+        return out
+
+    def compare(self, op, x, y, code=None):
+        """op 'less_than'|'less_equal'|'greater_than'|'greater_equal'|'equal'|'not_equal' -> bool array."""
+        opc = ["less_than", "less_equal", "greater_than", "greater_equal", "equal", "not_equal"].index(op)
+        return self._binary_coded("compare", opc, x, y, code, np.bool_)
+
+    def logical(self, op, x, y, code=None):
+        return self._binary_coded("logical", ["and", "or", "xor"].index(op), x, y, code, np.bool_)
+
+    def bitwise(self, op, x, y):
+        return self._binary_coded("bitwise", ["and", "or", "xor"].index(op), x, y, None, None)
+
+    def logical_not(self, x, code=None):
+        x = np.ascontiguousarray(x)
+        code = NP2CODE[x.dtype] if code is None else code
+        out = np.empty(x.shape, np.bool_)
+        self._check(getattr(self.lib, self.p + "not")(0, code, _vp(x), ctypes.c_int64(x.size), _vp(out)))
+        return out
+
+    def bitwise_not(self, x):
+        x = np.ascontiguousarray(x)
+        out = np.empty(x.shape, x.dtype)
+        self._check(getattr(self.lib, self.p + "not")(1, NP2CODE[x.dtype], _vp(x), ctypes.c_int64(x.size), _vp(out)))
+        return out
+
+    def scale(self, x, scale=1.0, bias=0.0, bias_after_scale=True, code=None):
+        x = np.ascontiguousarray(x)
+        code = NP2CODE[x.dtype] if code is None else code
+        out = np.empty(x.shape, x.dtype)
+        self._check(getattr(self.lib, self.p + "scale")(code, _vp(x), ctypes.c_int64(x.size), ctypes.c_double(scale),
+                                                        ctypes.c_double(bias), int(bool(bias_after_scale)), _vp(out)))
+        return out
+
+    def cast(self, x, out_code, code=None):
+        """out_code: dtype code of the result; bf16/fp16 results come back as uint16 bit patterns."""
+        x = np.ascontiguousarray(x)
+        code = NP2CODE[x.dtype] if code is None else code
+        out = np.empty(x.shape, CODE2NP[out_code])
+        self._check(getattr(self.lib, self.p + "cast")(code, out_code, _vp(x), ctypes.c_int64(x.size), _vp(out)))
+        return out
+
+    def where(self, cond, x, y, code=None):
+        cond = np.ascontiguousarray(cond, np.bool_)
+        x = np.ascontiguousarray(x)
+        y = np.ascontiguousarray(y)
+        code = NP2CODE[x.dtype] if code is None else code
+        out = np.empty(x.shape, x.dtype)
+        self._check(getattr(self.lib, self.p + "where")(code, _vp(cond), _vp(x), _vp(y), ctypes.c_int64(x.size), _vp(out)))
+        return out
 
     def _check(self, rc):
         if rc != 0:

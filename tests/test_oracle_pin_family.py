@@ -1,0 +1,109 @@
+"""Pins oracle/phi_cpu_oracle_family.c (compare / logical / bitwise / not / scale / cast / where) to the reference:
+against tests/golden/phi_family_golden.npz (outputs of the reference's own CPU kernels, recorded by
+tests/golden/make_golden_family.py) — always; and live against oracle/_ref/libphi_cpu_ref.so when it exists.
+Everything is bit-identical except float32/float64 scale (the reference build may or may not fuse the
+multiply-add: one unit in the last place)."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from golden.make_golden_family import BCAST, COMPARE_OPS, INT_TYPES, SCALE_ARGS, cast_input, draw
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "phi_family_golden.npz")
+HALVES = {"bfloat16": O.BFLOAT16, "float16": O.FLOAT16}
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return dict(np.load(GOLDEN))
+
+
+def test_compare_logical_bitwise_golden(port, gold):
+    n = 0
+    for name, _, _ in BCAST:
+        for dt in INT_TYPES + ["float32", "float64", "bfloat16", "float16"]:
+            x, y = gold[f"fam_{name}_{dt}__in0"], gold[f"fam_{name}_{dt}__in1"]
+            code = HALVES.get(dt)
+            for op in COMPARE_OPS:
+                assert np.array_equal(port.compare(op, x, y, code=code), gold[f"cmp_{op}_{name}_{dt}__out"]), (op, name, dt)
+                n += 1
+            if dt in HALVES:
+                continue
+            if dt != "uint8":
+                for op in ("and", "or", "xor"):
+                    assert np.array_equal(port.logical(op, x, y), gold[f"log_{op}_{name}_{dt}__out"]), (op, name, dt)
+            if dt in INT_TYPES:
+                for op in ("and", "or", "xor"):
+                    assert np.array_equal(port.bitwise(op, x, y), gold[f"bit_{op}_{name}_{dt}__out"]), (op, name, dt)
+    assert n == len(BCAST) * 10 * 6
+
+
+def test_unary_golden(port, gold):
+    for dt in INT_TYPES + ["float32", "float64"]:
+        x = gold[f"un_{dt}__in0"]
+        if dt != "uint8":
+            assert np.array_equal(port.logical_not(x), gold[f"lnot_{dt}__out"])
+        if dt in INT_TYPES:
+            assert np.array_equal(port.bitwise_not(x), gold[f"bnot_{dt}__out"])
+
+
+def test_scale_golden(port, gold):
+    for dt in ["uint8", "int8", "int16", "int32", "int64", "float32", "float64", "bool", "bfloat16"]:
+        x = gold[f"scale_{dt}__in0"]
+        for k, (s, b, after) in enumerate(SCALE_ARGS):
+            got, want = port.scale(x, s, b, after, code=HALVES.get(dt)), gold[f"scale_{dt}_{k}__out"]
+            if dt in ("float32", "float64"):
+                np.testing.assert_allclose(got, want, rtol=2 * np.finfo(dt).eps, atol=np.finfo(dt).eps)
+            else:
+                assert np.array_equal(got, want), (dt, k)
+
+
+def test_cast_golden(port, gold):
+    for sc in range(10):
+        x = gold[f"cast_{sc}__in0"]
+        for dc in range(10):
+            if dc == O.FLOAT16 and sc != O.FLOAT16:
+                continue
+            assert np.array_equal(port.cast(x, dc, code=sc), gold[f"cast_{sc}_{dc}__out"]), (sc, dc)
+
+
+def test_where_golden(port, gold):
+    for dt in ("int32", "int64", "float32", "float64"):
+        c, x, y = gold[f"where_{dt}__in0"], gold[f"where_{dt}__in1"], gold[f"where_{dt}__in2"]
+        assert np.array_equal(port.where(c, x, y), gold[f"where_{dt}__out"])
+    # other element sizes: a bit select
+    rng = np.random.default_rng(3)
+    for dt in (np.uint8, np.int16):
+        c, x, y = rng.random(100) < 0.5, rng.integers(0, 99, 100).astype(dt), rng.integers(0, 99, 100).astype(dt)
+        assert np.array_equal(port.where(c, x, y), np.where(c, x, y))
+
+
+def test_live_family(port, ref):
+    rng = np.random.default_rng(77)
+    for dt in INT_TYPES + ["float32", "float64"]:
+        for xs, ys in (((33, 1, 65), (7, 65)), ((1000,), (1000,)), ((5, 6), ())):
+            x, y = draw(rng, dt, xs), draw(rng, dt, ys)
+            for op in COMPARE_OPS:
+                assert np.array_equal(port.compare(op, x, y), ref.compare(op, x, y))
+                assert np.array_equal(port.compare(op, y, x), ref.compare(op, y, x))
+            if dt != "uint8":
+                for op in ("and", "or", "xor"):
+                    assert np.array_equal(port.logical(op, x, y), ref.logical(op, x, y))
+                assert np.array_equal(port.logical_not(x), ref.logical_not(x))
+            if dt in INT_TYPES:
+                for op in ("and", "or", "xor"):
+                    assert np.array_equal(port.bitwise(op, x, y), ref.bitwise(op, x, y))
+                assert np.array_equal(port.bitwise_not(x), ref.bitwise_not(x))
+    for sc in range(10):
+        x = cast_input(rng, port, sc)
+        for dc in range(10):
+            if dc == O.FLOAT16 and sc != O.FLOAT16:
+                continue
+            assert np.array_equal(port.cast(x, dc, code=sc), ref.cast(x, dc, code=sc)), (sc, dc)
+    xb = port.f32_to_bf16(rng.standard_normal(4096).astype(np.float32))
+    for s, b, after in SCALE_ARGS:
+        assert np.array_equal(port.scale(xb, s, b, after, code=O.BFLOAT16), ref.scale(xb, s, b, after, code=O.BFLOAT16))
+        xi = rng.integers(-2**40, 2**40, 999)
+        assert np.array_equal(port.scale(xi, s, b, after), ref.scale(xi, s, b, after))

@@ -36,13 +36,14 @@ out["has"] = {f"{n}/{b}/{d}": reg.phi_min_has_kernel(n.encode(), b.encode(), d) 
 ar = {}
 a, b_, c = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
 for n in ["add", "divide", "sum", "sum_raw", "mean", "max_raw", "prod", "argmax", "softmax", "layer_norm", "softmax_grad",
-          "layer_norm_grad"]:
+          "layer_norm_grad", "less_than", "logical_not", "logical_xor", "scale", "cast", "where"]:
     reg.phi_min_arity(n.encode(), b"GPU", 10, ctypes.byref(a), ctypes.byref(b_), ctypes.byref(c))
     ar[n] = [a.value, b_.value, c.value]
 out["arity"] = ar
 out["ln_out_dtypes"] = [reg.phi_min_output_dtype(b"layer_norm", b"GPU", 16, i) for i in range(3)]
 out["sum_out_dtype"] = reg.phi_min_output_dtype(b"sum", b"GPU", 7, 0)
 out["argmax_out_dtype"] = reg.phi_min_output_dtype(b"argmax", b"GPU", 10, 0)
+out["family_out_dtypes"] = [reg.phi_min_output_dtype(n, b"GPU", 10, 0) for n in (b"equal", b"logical_or", b"cast", b"scale")]
 print(json.dumps(out))
 '''
 
@@ -60,6 +61,14 @@ EXPECT = {  # the registrations of plugin/phi_kernels.cc
     "argmax": "float16 bfloat16 float32 float64 int32 int64 int16 uint8",
     "softmax": "float32 float64 float16 bfloat16", "layer_norm": "float32 float64 float16 bfloat16",
     "softmax_grad": "float32 float64 float16 bfloat16", "layer_norm_grad": "float32 float64 float16 bfloat16",
+    **{n: "bool int32 uint8 int8 int16 int64 float32 float64 float16 bfloat16"
+       for n in ("less_than", "less_equal", "greater_than", "greater_equal", "equal", "not_equal")},
+    **{n: "float32 float16 bfloat16 float64 bool int64 int32 int8 int16"
+       for n in ("logical_and", "logical_or", "logical_xor", "logical_not")},
+    **{n: "bool uint8 int8 int16 int32 int64" for n in ("bitwise_and", "bitwise_or", "bitwise_xor", "bitwise_not")},
+    "scale": "bool float32 float64 float16 bfloat16 uint8 int8 int16 int32 int64",
+    "cast": "float32 float64 int32 int64 int16 bool int8 uint8 float16 bfloat16",
+    "where": "float32 float64 int32 int64 float16 bfloat16",
 }
 
 
@@ -81,6 +90,10 @@ def test_pd_register_kernel_overwrites_paddles_keys():
     # what the registrar parsed out of our C++ signatures == the in-tree signatures (inputs, attributes, outputs)
     assert out["arity"] == {"add": [2, 0, 1], "divide": [2, 0, 1], "sum": [1, 3, 1], "sum_raw": [1, 4, 1], "mean": [1, 2, 1],
                             "max_raw": [1, 3, 1], "prod": [1, 3, 1], "argmax": [1, 4, 1], "softmax": [1, 1, 1],
-                            "layer_norm": [3, 2, 3], "softmax_grad": [2, 1, 1], "layer_norm_grad": [6, 2, 3]}
+                            "layer_norm": [3, 2, 3], "softmax_grad": [2, 1, 1], "layer_norm_grad": [6, 2, 3],
+                            "less_than": [2, 0, 1], "logical_not": [1, 0, 1], "logical_xor": [2, 0, 1], "scale": [1, 3, 1],
+                            "cast": [1, 1, 1], "where": [3, 0, 1]}
     # output dtypes left UNDEFINED where the in-tree registration bodies do so
     assert out["ln_out_dtypes"] == [DT["bfloat16"], 0, 0] and out["sum_out_dtype"] == 0 and out["argmax_out_dtype"] == 0
+    # compare / logical outputs are BOOL, cast's is left to InferMeta, scale keeps the input dtype
+    assert out["family_out_dtypes"] == [DT["bool"], DT["bool"], 0, DT["float32"]]
