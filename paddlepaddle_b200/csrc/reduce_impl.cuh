@@ -307,7 +307,12 @@ __global__ void __launch_bounds__(256) reduce_rows_warp_kernel(const T* __restri
 
 // ---- rows_block: one CTA per (row, split) -----------------------------------------------
 // out[row * splits + split]; with splits > 1 O is the accumulator type and Fin the identity.
-template <typename T, typename O, typename Op, typename Fin, bool VECTOR>
+// INTERLEAVE (vector path, splits > 1): the row is cut into tiles of blockDim * V * kRedUnroll elements and split s
+// folds tiles s, s + splits, s + 2*splits, ...  All CTAs then sweep the row together, so at any moment the
+// machine reads one ~20 MB window instead of ~600 far-apart streams: with contiguous segments a 17 GB row
+// ran 8% slower than a 4 GB one (TLB reach / DRAM page locality; profiles/r1e_notes.txt).  The partial of a
+// split is still a fixed, run-to-run identical sum.  The ragged end of the row goes to one split, after its tiles.
+template <typename T, typename O, typename Op, typename Fin, bool VECTOR, bool INTERLEAVE>
 __global__ void __launch_bounds__(512) reduce_rows_block_kernel(const T* __restrict__ x,
                                                                 O* __restrict__ out, int64_t red,
                                                                 int64_t seg, int splits, Fin fin) {
@@ -315,9 +320,40 @@ __global__ void __launch_bounds__(512) reduce_rows_block_kernel(const T* __restr
   __shared__ A smem[33];
   const int64_t row = (int64_t)blockIdx.x / splits;
   const int split = (int)((int64_t)blockIdx.x - row * splits);
-  const int64_t begin = (int64_t)split * seg;
-  const int64_t end = begin + seg < red ? begin + seg : red;
-  A a = fold_span<T, Op, VECTOR>(x + row * red, begin, end, threadIdx.x, blockDim.x);
+  A a;
+  if constexpr (VECTOR && INTERLEAVE) {
+    constexpr int V = Vec<T>::N;
+    const int64_t tile = (int64_t)blockDim.x * V * kRedUnroll;
+    const int64_t full_tiles = red / tile;
+    const T* base = x + row * red + (int64_t)threadIdx.x * V;
+    const int64_t step = (int64_t)blockDim.x * V;
+    A acc[kRedUnroll];
+#pragma unroll
+    for (int u = 0; u < kRedUnroll; ++u) acc[u] = Op::identity();
+    if constexpr (IsArgMax<Op>::value && sizeof(T) == 2) {
+      // 16-bit argmax keeps its vector-granular bookkeeping inside fold_span: go tile by tile through it
+      for (int64_t t = split; t < full_tiles; t += splits)
+        acc[0] = Op::combine(acc[0], fold_span<T, Op, true>(x + row * red, t * tile, (t + 1) * tile, threadIdx.x, blockDim.x));
+    } else {
+      for (int64_t t = split; t < full_tiles; t += splits) {
+        const int64_t i0 = t * tile;
+        Vec<T> v[kRedUnroll];
+#pragma unroll
+        for (int u = 0; u < kRedUnroll; ++u) v[u] = ld_stream(base + i0 + u * step);
+#pragma unroll
+        for (int u = 0; u < kRedUnroll; ++u)
+#pragma unroll
+          for (int k = 0; k < V; ++k) acc_step<Op, T>(acc[u], v[u].v[k], i0 + (int64_t)threadIdx.x * V + u * step + k);
+      }
+    }
+    a = Op::combine(Op::combine(acc[0], acc[1]), Op::combine(acc[2], acc[3]));
+    if (split == (int)(full_tiles % splits) && full_tiles * tile < red)
+      a = Op::combine(a, fold_span<T, Op, true>(x + row * red, full_tiles * tile, red, threadIdx.x, blockDim.x));
+  } else {
+    const int64_t begin = (int64_t)split * seg;
+    const int64_t end = begin + seg < red ? begin + seg : red;
+    a = fold_span<T, Op, VECTOR>(x + row * red, begin, end, threadIdx.x, blockDim.x);
+  }
   a = block_reduce(a, [](A p, A q) { return Op::combine(p, q); }, Op::identity(), smem);
   if (threadIdx.x == 0) out[blockIdx.x] = fin(a);
 }
@@ -498,10 +534,13 @@ int launch_pass(const ReducePass& ps, const PassGeom& g, bool vec, const T* x, O
   if (g.kind == 1) {
     const int64_t blocks = ps.outer * g.splits;
     if (blocks > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "reduce: too many rows for one launch");
-    if (vec)
-      reduce_rows_block_kernel<T, O, Op, Fin, true><<<(unsigned)blocks, g.threads, 0, st>>>(x, out, ps.red, g.seg, g.splits, fin);
+    static const bool no_interleave = getenv("PDB200_NO_INTERLEAVE") != nullptr;  // tuning knob
+    if (vec && g.splits > 1 && !no_interleave)
+      reduce_rows_block_kernel<T, O, Op, Fin, true, true><<<(unsigned)blocks, g.threads, 0, st>>>(x, out, ps.red, g.seg, g.splits, fin);
+    else if (vec)
+      reduce_rows_block_kernel<T, O, Op, Fin, true, false><<<(unsigned)blocks, g.threads, 0, st>>>(x, out, ps.red, g.seg, g.splits, fin);
     else
-      reduce_rows_block_kernel<T, O, Op, Fin, false><<<(unsigned)blocks, g.threads, 0, st>>>(x, out, ps.red, g.seg, g.splits, fin);
+      reduce_rows_block_kernel<T, O, Op, Fin, false, false><<<(unsigned)blocks, g.threads, 0, st>>>(x, out, ps.red, g.seg, g.splits, fin);
     return after_launch("reduce_rows_block");
   }
   const int64_t blocks = g.col_tiles * g.splits * ps.outer;

@@ -16,6 +16,8 @@ g.manual_seed(0)
 def rnd(shape, dt):
     if dt in (torch.int64, torch.int32):
         return torch.randint(-2**20, 2**20, shape, device="cuda", dtype=dt, generator=g)
+    if dt == torch.float32:
+        return torch.randn(shape, device="cuda", generator=g)
     return torch.randn(shape, device="cuda", generator=g).to(dt)
 
 
@@ -40,6 +42,14 @@ CASES = [
     ("argmax fp32 2^30 flat", (1 << 30,), torch.float32, lambda x: paddle.argmax(x)),
     ("argmax bf16 [524288,4096] axis=-1", (524288, 4096), torch.bfloat16, lambda x: paddle.argmax(x, axis=-1)),
 ]
+if os.environ.get("BIG"):  # the C5 shard sizes (17 GB / 8.6 GB inputs)
+    CASES += [
+        ("sum  int64 2^31 all (C5 shard)", (1 << 31,), torch.int64, lambda x: paddle.sum(x)),
+        ("max  int64 2^31 all (C5 shard)", (1 << 31,), torch.int64, lambda x: paddle.max(x)),
+        ("sum  fp32 2^31 all (C5 shard)", (1 << 31,), torch.float32, lambda x: paddle.sum(x)),
+        ("max  fp32 2^31 all (C5 shard)", (1 << 31,), torch.float32, lambda x: paddle.max(x)),
+        ("argmax fp32 2^31 flat", (1 << 31,), torch.float32, lambda x: paddle.argmax(x)),
+    ]
 only = os.environ.get("ONLY")
 for name, shape, dt, fn in CASES:
     if only and not any(o in name for o in only.split(";")):
