@@ -306,6 +306,12 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
     rec("next: scale bf16 [64,2048,4096] (2.5*x + 1)", 2 * n2 * 2, lambda: paddle.scale(xa, 2.5, 1.0), n2)
     rec("next: cast bf16 -> fp32 [64,2048,4096]", n2 * 2 + n2 * 4, lambda: paddle.cast(xa, "float32"), n2)
     rec("next: where bf16 [64,2048,4096] (bool, x, y)", n2 + 3 * n2 * 2, lambda: paddle.where(ob, xa, oa), n2)
+    # backward of config 2: multiply_grad reads dout and x once, writes dx and the 4096 column sums (one pass);
+    # add_grad = column sums of dout only (dx aliases dout in the reference's in-place pass, so it is not asked for)
+    rec("next: multiply_grad bf16 [64,2048,4096]*[4096] (dx, dy)", 3 * n2 * 2 + 2 * C2_COLS * 2,
+        lambda: paddle.multiply_grad(xa, ya, oa), n2)
+    rec("next: add_grad bf16 [64,2048,4096]+[4096] (dy only)", n2 * 2 + C2_COLS * 2,
+        lambda: paddle.add_grad(xa, ya, oa, want_x_grad=False), n2)
     del xa, ya, oa, ob
     n = 8 * 32 * 2048 * 2048
     yy = torch.rand((8, 32, 2048, 2048), device="cuda", generator=g).to(torch.bfloat16)

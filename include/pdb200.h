@@ -167,6 +167,30 @@ PDB200_API int pdb200_where(const void* condition, const void* x, const void* y,
                  void* out, void* stream);
 
 /* ---------------------------------------------------------------------------
+ * Backward of add / multiply with broadcasting: the gradient of an operand that was
+ * broadcast is dout summed over the broadcast dimensions (funcs::GetReduceDim, axis = -1).
+ * Replaces phi::AddGradKernel / MultiplyGradKernel on GPU:
+ *   paddle/phi/kernels/gpu/elementwise_grad_kernel.cu:361-372,431-443 (registrations)
+ *   paddle/phi/kernels/gpu/elementwise_grad.h:148-232 (add), :57-107,371-399 (multiply)
+ * dout has the broadcast shape of x_dims and y_dims; dx has x's shape, dy has y's; either may be NULL (not
+ * wanted).  dx or dy may be the dout buffer itself when their shapes agree (the in-place case: nothing is
+ * copied).  add_grad: dx = sum(dout), dy = sum(dout).  multiply_grad: dx = sum(dout * y), dy = sum(dout * x),
+ * each product rounded to the tensor dtype first (as the reference's temporaries are), sums in float for
+ * bf16/fp16 (double for float64, wrapping integers) and rounded once.
+ * dtypes: float32, float64, int32, int64, float16, bfloat16 (complex, and bool multiply_grad, are out of scope).
+ * Workspace: ask pdb200_elementwise_grad_workspace_bytes (op = PDB200_GRAD_ADD / PDB200_GRAD_MULTIPLY); 0 when
+ * nothing is reduced; 16-byte aligned; PDB200_WORKSPACE_TOO_SMALL if the buffer is smaller. */
+enum pdb200_grad_op { PDB200_GRAD_ADD = 0, PDB200_GRAD_MULTIPLY = 1 };
+PDB200_API size_t pdb200_elementwise_grad_workspace_bytes(int op, const int64_t* x_dims, int x_rank,
+                                               const int64_t* y_dims, int y_rank, int dtype, int want_dx,
+                                               int want_dy);
+PDB200_API int pdb200_add_grad(const int64_t* x_dims, int x_rank, const int64_t* y_dims, int y_rank, const void* dout,
+                    int dtype, void* dx, void* dy, void* workspace, size_t workspace_bytes, void* stream);
+PDB200_API int pdb200_multiply_grad(const void* x, const int64_t* x_dims, int x_rank, const void* y,
+                         const int64_t* y_dims, int y_rank, const void* dout, int dtype, void* dx, void* dy,
+                         void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------
  * Reductions.  `axes` may hold negative values; n_axes == 0 or reduce_all != 0 or a full axis
  * set means "reduce everything" (phi::recompute_reduce_all, paddle/phi/core/kernel_utils.h:407-417).
  * keep_dim only changes the output SHAPE (InferMeta), never the data, so it is not a parameter.

@@ -353,3 +353,87 @@ int oracle_where(int dtype, const uint8_t* cond, const void* x, const void* y, i
     memcpy((char*)out + i * es, (cond[i] ? (const char*)x : (const char*)y) + i * es, es);
   return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * add_grad / multiply_grad with broadcasting.
+ * phi::AddGradKernel / MultiplyGradKernel<T,CPUContext> (cpu/elementwise_add_grad_kernel.cc:25-62,
+ * cpu/elementwise_multiply_grad_kernel.cc:26-39) -> ElemwiseGradCompute / ElemwiseExplicitGradCompute
+ * (funcs/elementwise_grad_base.h:1802-1821).  add: dx_op = dy_op = dout (IdentityGrad); multiply:
+ * dx_op = dout * y, dy_op = dout * x (MulGradDX / MulGradDY, cpu/elementwise_grad.h), each a T-typed product.
+ * Route (elementwise_grad_base.h:266-355, funcs/elementwise_utils.h:40-75 GetMidDims):
+ *   - the lower-rank operand, trailing 1s trimmed, equals a contiguous run of the other's dims starting at
+ *     axis = |rank_x - rank_y|  ->  (pre, n, post) loops (:103-211): the full operand's gradient is the plain
+ *     product, the broadcast operand's is accumulated per element in MPType (float for bf16) over increasing
+ *     dout index and rounded once;
+ *   - anything else -> CommonGradBroadcastCPU (:52-98): both gradients start at 0 and take "+=" in T, in
+ *     increasing dout index (bf16: rounded after every addition).
+ * float / double: the reference build (-O3 -mfma, GNU contraction default) fuses "sum += a * b" into one fma in
+ *   every loop except the (pre, n, post > 1) loop compiled for "full operand's gradient not wanted", which GCC
+ *   vectorises as multiply-then-ordered-add.  This restatement always fuses: bit-identical to oracle/_ref
+ *   everywhere else, within a few units in the last place there (tests/test_oracle_pin_family.py states both).
+ * acc_mode 1 (not a CPU route): the GPU kernels' arithmetic for every shape — products rounded to T, sums in
+ *   MPType, rounded once (gpu/elementwise_grad.h:57-107 + ReduceKernel).  It differs from acc_mode 0 only for
+ *   16-bit types on the common route.  fp16 exists only in this mode (no CPU registration).
+ * dx / dy may be NULL.  op: 0 add_grad, 1 multiply_grad.
+ * ---------------------------------------------------------------------------------------- */
+#include <stdlib.h>
+static int grad_common_route(const int64_t* xd, int xr, const int64_t* yd, int yr) {
+  const int x_larger = xr >= yr;
+  const int64_t* bd = x_larger ? xd : yd; const int br = x_larger ? xr : yr;
+  const int64_t* sd = x_larger ? yd : xd; int sr = x_larger ? yr : xr;
+  const int axis0 = br - sr;
+  while (sr > 0 && sd[sr - 1] == 1) --sr;            /* TrimTrailingSingularDims */
+  const int axis = sr == 0 ? br : axis0;
+  for (int i = 0; i < sr; ++i) if (bd[i + axis] != sd[i]) return 1;
+  return 0;
+}
+int oracle_elementwise_grad(int op, int dtype, int acc_mode, const void* x, const int64_t* xd, int xr, const void* y,
+                            const int64_t* yd, int yr, const void* dout, void* dx, void* dy) {
+  Walk w;
+  if (walk_init(&w, xd, xr, yd, yr)) return 1;
+  int64_t xn = 1, yn = 1;
+  for (int i = 0; i < xr; ++i) xn *= xd[i];
+  for (int i = 0; i < yr; ++i) yn *= yd[i];
+#define GRAD_NATIVE(T, ACC_ADD, ACC_MULADD)                                                    \
+  {                                                                                            \
+    const T* X = (const T*)x; const T* Y = (const T*)y; const T* G = (const T*)dout;           \
+    T* DX = (T*)dx; T* DY = (T*)dy;                                                            \
+    if (DX) memset(DX, 0, (size_t)xn * sizeof(T));                                             \
+    if (DY) memset(DY, 0, (size_t)yn * sizeof(T));                                             \
+    WALK({                                                                                     \
+      if (DX) DX[xo] = op == 0 ? ACC_ADD(DX[xo], G[i]) : ACC_MULADD(G[i], Y[yo], DX[xo]);      \
+      if (DY) DY[yo] = op == 0 ? ACC_ADD(DY[yo], G[i]) : ACC_MULADD(G[i], X[xo], DY[yo]);      \
+    })                                                                                         \
+  }
+#define F_ADD(a, b) ((a) + (b))
+#define I32_ADD(a, b) ((int32_t)((uint32_t)(a) + (uint32_t)(b)))
+#define I32_MULADD(a, b, c) ((int32_t)((uint32_t)(a) * (uint32_t)(b) + (uint32_t)(c)))
+#define I64_ADD(a, b) ((int64_t)((uint64_t)(a) + (uint64_t)(b)))
+#define I64_MULADD(a, b, c) ((int64_t)((uint64_t)(a) * (uint64_t)(b) + (uint64_t)(c)))
+  switch (dtype) {
+    case DT_FLOAT32: GRAD_NATIVE(float, F_ADD, fmaf) break;
+    case DT_FLOAT64: GRAD_NATIVE(double, F_ADD, fma) break;
+    case DT_INT32: GRAD_NATIVE(int32_t, I32_ADD, I32_MULADD) break;
+    case DT_INT64: GRAD_NATIVE(int64_t, I64_ADD, I64_MULADD) break;
+    case DT_BFLOAT16: case DT_FLOAT16: {
+      const int bf = dtype == DT_BFLOAT16;
+      if (!bf && !acc_mode) return 2;
+      const int per_add = !acc_mode && grad_common_route(xd, xr, yd, yr);
+      const uint16_t* X = (const uint16_t*)x; const uint16_t* Y = (const uint16_t*)y; const uint16_t* G = (const uint16_t*)dout;
+      uint16_t* DX = (uint16_t*)dx; uint16_t* DY = (uint16_t*)dy;
+      float* ax = DX ? (float*)calloc((size_t)xn, sizeof(float)) : NULL;
+      float* ay = DY ? (float*)calloc((size_t)yn, sizeof(float)) : NULL;
+#define H2F(v) (bf ? bf2f(v) : h2f(v))
+#define F2H(v) (bf ? f2bf(v) : f2h(v))
+      WALK({
+        if (DX) { float v = op == 0 ? H2F(G[i]) : H2F(F2H(H2F(G[i]) * H2F(Y[yo]))); ax[xo] = per_add ? H2F(F2H(ax[xo] + v)) : ax[xo] + v; }
+        if (DY) { float v = op == 0 ? H2F(G[i]) : H2F(F2H(H2F(G[i]) * H2F(X[xo]))); ay[yo] = per_add ? H2F(F2H(ay[yo] + v)) : ay[yo] + v; }
+      })
+      if (DX) { for (int64_t k = 0; k < xn; ++k) DX[k] = F2H(ax[k]); free(ax); }
+      if (DY) { for (int64_t k = 0; k < yn; ++k) DY[k] = F2H(ay[k]); free(ay); }
+      break;
+    }
+    default: return 2;
+  }
+  return 0;
+}

@@ -10,6 +10,8 @@
 //   scale        phi::ScaleKernel<T,CPUContext>                  paddle/phi/kernels/cpu/scale_kernel.cc:27-48
 //   cast         phi::CastKernel<T,CPUContext>                   paddle/phi/kernels/cpu/cast_kernel.cc, cast_impl.h
 //   where        phi::WhereKernel<T,CPUContext>                  paddle/phi/kernels/cpu/where_kernel.cc:20-36
+//   add_grad     phi::AddGradKernel<T,CPUContext>                paddle/phi/kernels/cpu/elementwise_add_grad_kernel.cc:25-62
+//   multiply_grad phi::MultiplyGradKernel<T,CPUContext>          paddle/phi/kernels/cpu/elementwise_multiply_grad_kernel.cc:26-39
 #include "paddle/common/flags.h"
 #include "paddle/phi/common/bfloat16.h"
 #include "paddle/phi/common/float16.h"
@@ -25,6 +27,8 @@
 #include "paddle/phi/kernels/cpu/bitwise_kernel.cc"  // NOLINT (kernel templates live in the .cc)
 #include "paddle/phi/kernels/cpu/cast_kernel.cc"     // NOLINT
 #include "paddle/phi/kernels/cpu/compare_kernel.cc"  // NOLINT
+#include "paddle/phi/kernels/cpu/elementwise_add_grad_kernel.cc"       // NOLINT
+#include "paddle/phi/kernels/cpu/elementwise_multiply_grad_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/logical_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/scale_kernel.cc"    // NOLINT
 #include "paddle/phi/kernels/cpu/where_kernel.cc"    // NOLINT
@@ -230,6 +234,40 @@ int phi_ref_where(int dtype, const void* cond, const void* x, const void* y, int
       case kFloat64: phi::WhereKernel<double, CPUContext>(ctx, ct, xt, yt, &ot); break;
       default: throw std::runtime_error("phi_ref_where: dtype not registered on CPU");
     }
+  });
+}
+
+// op: 0 add_grad, 1 multiply_grad.  dx / dy may be NULL (gradient not wanted).  x / y are read by multiply_grad only,
+// but must be valid buffers of their shapes for both (the kernels take the tensors for their dims).
+int phi_ref_elementwise_grad(int op, int dtype, const void* x, const int64_t* xdims, int xrank, const void* y,
+                             const int64_t* ydims, int yrank, const void* dout, const int64_t* odims, int orank,
+                             void* dx, void* dy) {
+  return Guard([&] {
+    auto& ctx = GetCtx().ctx;
+    auto xt = Wrap(x, xdims, xrank, dtype);
+    auto yt = Wrap(y, ydims, yrank, dtype);
+    auto gt = Wrap(dout, odims, orank, dtype);
+    DenseTensor dxt, dyt;
+    if (dx) dxt = Wrap(dx, xdims, xrank, dtype);
+    if (dy) dyt = Wrap(dy, ydims, yrank, dtype);
+    DenseTensor* pdx = dx ? &dxt : nullptr;
+    DenseTensor* pdy = dy ? &dyt : nullptr;
+#define GRAD_CASE(T)                                                                             \
+  if (op == 0) phi::AddGradKernel<T, CPUContext>(ctx, xt, yt, gt, -1, pdx, pdy);                 \
+  else phi::MultiplyGradKernel<T, CPUContext>(ctx, xt, yt, gt, -1, pdx, pdy);                    \
+  break;
+    switch (dtype) {
+      case kFloat32: GRAD_CASE(float)
+      case kFloat64: GRAD_CASE(double)
+      case kInt32: GRAD_CASE(int32_t)
+      case kInt64: GRAD_CASE(int64_t)
+      case kBFloat16: GRAD_CASE(bf16)
+      default: throw std::runtime_error("phi_ref_elementwise_grad: dtype not registered on CPU");
+    }
+#undef GRAD_CASE
+    // the kernels may have re-allocated an output (Alloc on a borrowed buffer keeps it when the size fits)
+    if (dx && dxt.data() != dx) std::memcpy(dx, dxt.data(), static_cast<size_t>(dxt.numel()) * phi::SizeOf(dxt.dtype()));
+    if (dy && dyt.data() != dy) std::memcpy(dy, dyt.data(), static_cast<size_t>(dyt.numel()) * phi::SizeOf(dyt.dtype()));
   });
 }
 

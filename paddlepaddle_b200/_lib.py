@@ -16,6 +16,7 @@ REDUCE_SUM, REDUCE_MEAN, REDUCE_MAX, REDUCE_MIN, REDUCE_PROD = range(5)
 LESS_THAN, LESS_EQUAL, GREATER_THAN, GREATER_EQUAL, EQUAL, NOT_EQUAL = range(6)
 LOGICAL_AND, LOGICAL_OR, LOGICAL_XOR = range(3)
 BITWISE_AND, BITWISE_OR, BITWISE_XOR = range(3)
+GRAD_ADD, GRAD_MULTIPLY = range(2)
 MAX_RANK = 9
 
 _c_i64p = ctypes.POINTER(ctypes.c_int64)
@@ -43,6 +44,9 @@ SIGNATURES = {
     "pdb200_scale": (_int, [_vp, ctypes.c_int64, _int, ctypes.c_double, ctypes.c_double, _int, _vp, _vp]),
     "pdb200_cast": (_int, [_vp, ctypes.c_int64, _int, _int, _vp, _vp]),
     "pdb200_where": (_int, [_vp, _vp, _vp, ctypes.c_int64, _int, _vp, _vp]),
+    "pdb200_elementwise_grad_workspace_bytes": (_sz, [_int, _c_i64p, _int, _c_i64p, _int, _int, _int, _int]),
+    "pdb200_add_grad": (_int, [_c_i64p, _int, _c_i64p, _int, _vp, _int, _vp, _vp, _vp, _sz, _vp]),
+    "pdb200_multiply_grad": (_int, [_vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp, _vp, _vp, _sz, _vp]),
     "pdb200_reduce_workspace_bytes": (_sz, [_int, _c_i64p, _int, _c_i64p, _int, _int, _int, _int]),
     "pdb200_sum_raw": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _int, _vp, _vp, _sz, _vp]),
     "pdb200_mean_raw": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _int, _vp, _vp, _sz, _vp]),

@@ -202,6 +202,50 @@ def bitwise_xor(x, y, out=None, name=None):
 
 
 # ---------------------------------------------------------------------------------------
+# backward of add / multiply (what `_C_ops.add_grad` / `_C_ops.multiply_grad` run under autograd;
+# paddle/phi/ops/yaml/backward.yaml: add_grad(x, y, out_grad, axis=-1) -> (x_grad, y_grad))
+# ---------------------------------------------------------------------------------------
+def _binary_grad(op, x, y, out_grad, axis, want_x, want_y):
+    _require_cuda(x, y, out_grad)
+    if axis != -1:
+        raise NotImplementedError("(Unimplemented) only axis=-1 (NumPy right-aligned broadcasting) is on this path")
+    if not (x.dtype == y.dtype == out_grad.dtype):
+        raise TypeError("(InvalidType) x, y and out_grad must share one dtype")
+    lib = L.load()
+    x, y, out_grad = x.contiguous(), y.contiguous(), out_grad.contiguous()
+    xd, xr = L.dims_array(x.shape)
+    yd, yr = L.dims_array(y.shape)
+    od = (ctypes.c_int64 * L.MAX_RANK)()
+    orank = ctypes.c_int(0)
+    L.check(lib.pdb200_broadcast_shape(xd, xr, yd, yr, od, ctypes.byref(orank)), lib)
+    oshape = tuple(od[i] for i in range(orank.value))
+    if tuple(out_grad.shape) != oshape:
+        raise ValueError(f"(InvalidArgument) out_grad has shape {tuple(out_grad.shape)}, the forward output has {oshape}")
+    dx = torch.empty_like(x) if want_x else None
+    dy = torch.empty_like(y) if want_y else None
+    code = _dtype_code(x.dtype)
+    nbytes = lib.pdb200_elementwise_grad_workspace_bytes(op, xd, xr, yd, yr, code, int(want_x), int(want_y))
+    ws = _workspace(nbytes, x.device)
+    if op == L.GRAD_ADD:
+        rc = lib.pdb200_add_grad(xd, xr, yd, yr, _ptr(out_grad), code, _ptr(dx), _ptr(dy), _ptr(ws), nbytes, _stream())
+    else:
+        rc = lib.pdb200_multiply_grad(_ptr(x), xd, xr, _ptr(y), yd, yr, _ptr(out_grad), code, _ptr(dx), _ptr(dy), _ptr(ws),
+                                      nbytes, _stream())
+    L.check(rc, lib)
+    return dx, dy
+
+
+def add_grad(x, y, out_grad, axis=-1, want_x_grad=True, want_y_grad=True):
+    """(x_grad, y_grad) of out = x + y: out_grad summed over the dimensions each operand was broadcast along."""
+    return _binary_grad(L.GRAD_ADD, x, y, out_grad, axis, want_x_grad, want_y_grad)
+
+
+def multiply_grad(x, y, out_grad, axis=-1, want_x_grad=True, want_y_grad=True):
+    """(x_grad, y_grad) of out = x * y: sum(out_grad * y) and sum(out_grad * x) over the broadcast dimensions."""
+    return _binary_grad(L.GRAD_MULTIPLY, x, y, out_grad, axis, want_x_grad, want_y_grad)
+
+
+# ---------------------------------------------------------------------------------------
 # one-input maps and where
 # ---------------------------------------------------------------------------------------
 def _unary(fn_name, x, out_dtype, *mid):

@@ -157,6 +157,41 @@ void WhereKernel(const Context& ctx, const DenseTensor& condition, const DenseTe
   Check(pdb200_where(condition.data<bool>(), x.data<T>(), y.data<T>(), x.numel(), Code(x.dtype()), o, ctx.stream()));
 }
 
+// ---- add_grad / multiply_grad (gpu/elementwise_grad_kernel.cu:361-372,431-443) -------------------------------
+// dx / dy are NULL when autograd does not need them; a gradient that keeps dout's shape may share dout's buffer
+// (the reference's in-place pass), in which case nothing is copied.
+template <typename T, typename Context>
+void BinaryGrad(const Context& ctx, int op, const DenseTensor& x, const DenseTensor& y, const DenseTensor& dout, int axis,
+                DenseTensor* dx, DenseTensor* dy) {
+  if (axis != -1 && axis != std::abs(x.dims().size() - y.dims().size()))
+    PADDLE_THROW(common::errors::Unimplemented("pdb200: elementwise grad supports axis = -1 only"));
+  T* px = dx ? ctx.template Alloc<T>(dx) : nullptr;
+  T* py = dy ? ctx.template Alloc<T>(dy) : nullptr;
+  auto xd = Dims(x), yd = Dims(y);
+  const int code = Code(x.dtype());
+  const size_t bytes = pdb200_elementwise_grad_workspace_bytes(op, xd.data(), static_cast<int>(xd.size()), yd.data(),
+                                                               static_cast<int>(yd.size()), code, dx != nullptr,
+                                                               dy != nullptr);
+  DenseTensor holder;
+  void* ws = Scratch(ctx, bytes, &holder);
+  if (op == PDB200_GRAD_ADD)
+    Check(pdb200_add_grad(xd.data(), static_cast<int>(xd.size()), yd.data(), static_cast<int>(yd.size()), dout.data<T>(),
+                          code, px, py, ws, bytes, ctx.stream()));
+  else
+    Check(pdb200_multiply_grad(x.data<T>(), xd.data(), static_cast<int>(xd.size()), y.data<T>(), yd.data(),
+                               static_cast<int>(yd.size()), dout.data<T>(), code, px, py, ws, bytes, ctx.stream()));
+}
+template <typename T, typename Context>
+void AddGradKernel(const Context& ctx, const DenseTensor& x, const DenseTensor& y, const DenseTensor& dout, int axis,
+                   DenseTensor* dx, DenseTensor* dy) {
+  BinaryGrad<T>(ctx, PDB200_GRAD_ADD, x, y, dout, axis, dx, dy);
+}
+template <typename T, typename Context>
+void MultiplyGradKernel(const Context& ctx, const DenseTensor& x, const DenseTensor& y, const DenseTensor& dout, int axis,
+                        DenseTensor* dx, DenseTensor* dy) {
+  BinaryGrad<T>(ctx, PDB200_GRAD_MULTIPLY, x, y, dout, axis, dx, dy);
+}
+
 // ---- reductions --------------------------------------------------------------------------
 typedef int (*ReduceFn)(const void*, const int64_t*, int, const int64_t*, int, int, int, int, void*, void*,
                         size_t, void*);
@@ -353,6 +388,11 @@ PD_REGISTER_KERNEL(cast, GPU, ALL_LAYOUT, pdb200_phi::CastKernel, float, double,
 }
 PD_REGISTER_KERNEL(where, GPU, ALL_LAYOUT, pdb200_phi::WhereKernel, float, double, int, int64_t, phi::dtype::float16,
                    phi::dtype::bfloat16) {}
+// complex (both) and bool (multiply_grad) stay with the in-tree kernels
+PD_REGISTER_KERNEL(add_grad, GPU, ALL_LAYOUT, pdb200_phi::AddGradKernel, float, double, int, int64_t,
+                   phi::dtype::float16, phi::dtype::bfloat16) {}
+PD_REGISTER_KERNEL(multiply_grad, GPU, ALL_LAYOUT, pdb200_phi::MultiplyGradKernel, float, phi::dtype::float16, double,
+                   int, int64_t, phi::dtype::bfloat16) {}
 PD_REGISTER_KERNEL(sum_raw, GPU, ALL_LAYOUT, pdb200_phi::SumRawKernel, bool, float, double, phi::dtype::float16,
                    phi::dtype::bfloat16, int, int64_t) {
   kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);  // reduce_sum_kernel.cc:75-77

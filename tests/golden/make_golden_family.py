@@ -98,11 +98,31 @@ def main():
         y = (rng.standard_normal((6, 5, 20)) * 9).astype(dt)
         g[f"where_{dt}__in0"], g[f"where_{dt}__in1"], g[f"where_{dt}__in2"] = c, x, y
         g[f"where_{dt}__out"] = ref.where(c, x, y)
+    # add_grad / multiply_grad: the broadcast matrix of test_elementwise_add_op.py / test_elementwise_mul_op.py
+    for name, xs, ys in GRAD_CASES:
+        os_ = np.broadcast_shapes(xs, ys)
+        for dt in ("float32", "float64", "int32", "int64"):
+            if dt.startswith("int"):
+                x, y, d = (rng.integers(-9, 9, s_).astype(dt) for s_ in (xs, ys, os_))
+            else:
+                x, y, d = (rng.standard_normal(s_).astype(dt) for s_ in (xs, ys, os_))
+            g[f"grad_{name}_{dt}__in0"], g[f"grad_{name}_{dt}__in1"], g[f"grad_{name}_{dt}__in2"] = x, y, d
+            for op in ("add", "multiply"):
+                dx, dy = ref.elementwise_grad(op, x, y, d)
+                g[f"grad_{op}_{name}_{dt}__out0"], g[f"grad_{op}_{name}_{dt}__out1"] = dx, dy
+        x, y, d = (ref.f32_to_bf16(rng.standard_normal(s_).astype(np.float32)) for s_ in (xs, ys, os_))
+        g[f"grad_{name}_bfloat16__in0"], g[f"grad_{name}_bfloat16__in1"], g[f"grad_{name}_bfloat16__in2"] = x, y, d
+        dx, dy = ref.elementwise_grad("multiply", x, y, d, code=O.BFLOAT16)  # add_grad has no bf16 kernel on CPU
+        g[f"grad_multiply_{name}_bfloat16__out0"], g[f"grad_multiply_{name}_bfloat16__out1"] = dx, dy
     out = os.path.join(HERE, "phi_family_golden.npz")
     np.savez_compressed(out, **g)
     print(f"wrote {out}: {len(g)} arrays, {os.path.getsize(out)} bytes")
 
 
+GRAD_CASES = [("same", (13, 17), (13, 17)), ("vec_last", (2, 10, 12), (12,)), ("b_10_12", (2, 10, 12), (10, 12)),
+              ("mid", (2, 3, 100), (3, 1)), ("lead", (100, 2, 3), (100, 1, 1)), ("four", (10, 3, 1, 4), (10, 1, 12, 1)),
+              ("x_small", (10, 12), (2, 2, 10, 12)), ("scalar0d", (3, 4), ()), ("both0d", (), ()), ("col", (64, 33), (64, 1)),
+              ("outer_x", (1, 33), (64, 33)), ("rows", (300, 256), (256,))]
 SCALE_ARGS = [(-2.3, 0.0, True), (-2.3, 2.3, True), (-2.3, 2.3, False), (3.0, -1.0, True), (0.0, 0.5, False)]
 
 

@@ -269,6 +269,28 @@ class Oracle:
         self._check(getattr(self.lib, self.p + "where")(code, _vp(cond), _vp(x), _vp(y), ctypes.c_int64(x.size), _vp(out)))
         return out
 
+    def elementwise_grad(self, op, x, y, dout, want_dx=True, want_dy=True, code=None, gpu_arithmetic=False):
+        """op 'add'|'multiply' -> (dx, dy) (None where not wanted).  gpu_arithmetic (port only): sums of 16-bit types
+        in float, rounded once, as the reference's GPU kernels do (the CPU kernels round after every addition)."""
+        x, y, dout = (np.ascontiguousarray(a) for a in (x, y, dout))
+        code = NP2CODE[x.dtype] if code is None else code
+        dx = np.empty(x.shape, x.dtype) if want_dx else None
+        dy = np.empty(y.shape, y.dtype) if want_dy else None
+        xd, xr = _dims(x.shape)
+        yd, yr = _dims(y.shape)
+        opc = {"add": 0, "multiply": 1}[op]
+        pdx = _vp(dx) if dx is not None else None
+        pdy = _vp(dy) if dy is not None else None
+        if self.kind == "port":
+            rc = self.lib.oracle_elementwise_grad(opc, code, int(gpu_arithmetic), _vp(x), xd, xr, _vp(y), yd, yr,
+                                                  _vp(dout), pdx, pdy)
+        else:
+            od, orank = _dims(dout.shape)
+            rc = self.lib.phi_ref_elementwise_grad(opc, code, _vp(x), xd, xr, _vp(y), yd, yr, _vp(dout), od, orank,
+                                                   pdx, pdy)
+        self._check(rc)
+        return dx, dy
+
     def _check(self, rc):
         if rc != 0:
             msg = ""

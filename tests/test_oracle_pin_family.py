@@ -107,3 +107,40 @@ def test_live_family(port, ref):
         assert np.array_equal(port.scale(xb, s, b, after, code=O.BFLOAT16), ref.scale(xb, s, b, after, code=O.BFLOAT16))
         xi = rng.integers(-2**40, 2**40, 999)
         assert np.array_equal(port.scale(xi, s, b, after), ref.scale(xi, s, b, after))
+
+
+def test_elementwise_grad_golden_and_live(port, gold):
+    from golden.make_golden_family import GRAD_CASES
+    for name, _, _ in GRAD_CASES:
+        for dt in ("float32", "float64", "int32", "int64", "bfloat16"):
+            x, y, d = (gold[f"grad_{name}_{dt}__in{i}"] for i in range(3))
+            for op in ("add", "multiply"):
+                if dt == "bfloat16" and op == "add":
+                    continue  # no bf16 add_grad kernel on CPU
+                dx, dy = port.elementwise_grad(op, x, y, d, code=HALVES.get(dt))
+                # every case bit-for-bit (both gradients wanted: the fused multiply-add loops, see the oracle's header)
+                assert np.array_equal(dx, gold[f"grad_{op}_{name}_{dt}__out0"]), (op, name, dt)
+                assert np.array_equal(dy, gold[f"grad_{op}_{name}_{dt}__out1"]), (op, name, dt)
+
+
+def test_elementwise_grad_live_single_outputs(port, ref):
+    """Only one gradient wanted: the reference build compiles one loop unfused (a few ulp), the rest bit-exact."""
+    from golden.make_golden_family import GRAD_CASES
+    rng = np.random.default_rng(12)
+    for _, xs, ys in GRAD_CASES:
+        os_ = np.broadcast_shapes(xs, ys)
+        for dt in (np.float32, np.float64, np.int64):
+            if dt == np.int64:
+                x, y, d = (rng.integers(-2**31, 2**31, s_) for s_ in (xs, ys, os_))
+            else:
+                x, y, d = (rng.standard_normal(s_).astype(dt) for s_ in (xs, ys, os_))
+            for op in ("add", "multiply"):
+                for wx, wy in ((True, False), (False, True)):
+                    got, want = port.elementwise_grad(op, x, y, d, wx, wy), ref.elementwise_grad(op, x, y, d, wx, wy)
+                    for a, b in zip(got, want):
+                        if a is None:
+                            assert b is None
+                        elif dt == np.int64 or op == "add":
+                            assert np.array_equal(a, b)
+                        else:
+                            np.testing.assert_allclose(a, b, rtol=64 * np.finfo(dt).eps, atol=64 * np.finfo(dt).eps)
