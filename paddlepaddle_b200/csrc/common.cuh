@@ -218,6 +218,49 @@ __device__ __forceinline__ void pack_from_float<__half>(const float* in, Vec<__h
 }
 
 // ----------------------------------------------------------------------------
+// Packed fp32 pairs.  sm_100 has FFMA2 / FADD2 / FMUL2: one instruction performs two independent IEEE
+// round-to-nearest fp32 operations on a 64-bit register pair — the same results as two scalar instructions at
+// the same FLOP rate (profiles/micro/f32x2.cu: 72 vs 74 TFLOP/s), for HALF the issue slots.  The row kernels
+// are issue-bound, not pipe-bound, so their per-element arithmetic is written on pairs.
+// ----------------------------------------------------------------------------
+struct F2 {
+  unsigned long long v;
+};
+__device__ __forceinline__ F2 f2_make(float lo, float hi) {
+  F2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ F2 f2_splat(float x) { return f2_make(x, x); }
+__device__ __forceinline__ float f2_lo(F2 a) {
+  float lo, hi;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.v));
+  (void)hi;
+  return lo;
+}
+__device__ __forceinline__ float f2_hi(F2 a) {
+  float lo, hi;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.v));
+  (void)lo;
+  return hi;
+}
+__device__ __forceinline__ F2 f2_fma(F2 a, F2 b, F2 c) {
+  F2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v));
+  return r;
+}
+__device__ __forceinline__ F2 f2_add(F2 a, F2 b) {
+  F2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
+  return r;
+}
+__device__ __forceinline__ F2 f2_mul(F2 a, F2 b) {
+  F2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
+  return r;
+}
+
+// ----------------------------------------------------------------------------
 // warp / block reduction helpers
 // ----------------------------------------------------------------------------
 template <typename A>

@@ -63,22 +63,25 @@ ln_grad_pipe_kernel(const T* __restrict__ x, const T* __restrict__ dy, const P* 
       if (r < rows) fill(s, r);
     }
   }
-  float ds[PARAMS ? C * V : 1], db[PARAMS ? C * V : 1];
+  // per-element arithmetic on fp32 pairs (FFMA2 / FADD2 / FMUL2, common.cuh): same results, half the issue slots
+  constexpr int H = V / 2;
+  F2 ds[PARAMS ? C * H : 1], db[PARAMS ? C * H : 1];
   if constexpr (PARAMS) {
 #pragma unroll
-    for (int i = 0; i < C * V; ++i) ds[i] = db[i] = 0.f;
+    for (int i = 0; i < C * H; ++i) ds[i] = db[i] = f2_splat(0.f);
   }
   int s = 0, flip = 0;
   uint32_t phase = 0;
   for (int64_t row = blockIdx.x; row < rows; row += row_step) {
     const float mu = mean[row];
     const float rstd = lng_rstd<float>(var[row] + eps);
+    const F2 rstd2 = f2_splat(rstd), nmr2 = f2_splat(-mu * rstd);
     mbar_wait(&full[s], phase);
     const T* sx = ring + (size_t)s * 2 * D;
     const T* sg = sx + D;
     // The row is read from shared memory twice (sums, then dx) instead of being parked in 32 registers:
     // with the dscale/dbias accumulators that keeps the kernel under 128 registers without spills.
-    float s1 = 0.f, s2 = 0.f;
+    F2 s1p = f2_splat(0.f), s2p = f2_splat(0.f);
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       const int off = (c * nt + tid) * V;
@@ -91,18 +94,20 @@ ln_grad_pipe_kernel(const T* __restrict__ x, const T* __restrict__ dy, const P* 
           for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(scale + off + j * PV), &w[j * PV]);
         }
 #pragma unroll
-        for (int k = 0; k < V; ++k) {
-          const float xh = (xf[k] - mu) * rstd;
-          const float gw = HAS_SCALE ? gf[k] * w[k] : gf[k];
-          s1 += gw;
-          s2 = fmaf(gw, xh, s2);
+        for (int h = 0; h < H; ++h) {
+          const F2 g2 = f2_make(gf[2 * h], gf[2 * h + 1]);
+          const F2 xh = f2_fma(f2_make(xf[2 * h], xf[2 * h + 1]), rstd2, nmr2);
+          const F2 gw = HAS_SCALE ? f2_mul(g2, f2_make(w[2 * h], w[2 * h + 1])) : g2;
+          s1p = f2_add(s1p, gw);
+          s2p = f2_fma(gw, xh, s2p);
           if constexpr (PARAMS) {
-            db[c * V + k] += gf[k];
-            ds[c * V + k] = fmaf(gf[k], xh, ds[c * V + k]);
+            db[c * H + h] = f2_add(db[c * H + h], g2);
+            ds[c * H + h] = f2_fma(g2, xh, ds[c * H + h]);
           }
         }
       }
     }
+    float s1 = f2_lo(s1p) + f2_hi(s1p), s2 = f2_lo(s2p) + f2_hi(s2p);
     // both row sums through ONE barrier
     s1 = group_reduce<32>(s1, AddU2());
     s2 = group_reduce<32>(s2, AddU2());
@@ -118,9 +123,8 @@ ln_grad_pipe_kernel(const T* __restrict__ x, const T* __restrict__ dy, const P* 
     // dx = rstd * (gw - m1 - xhat * m2) with xhat = (x - mu) * rstd, regrouped as a*gw + (b*x + c): two FMAs per
     // element instead of five operations (b*x + c cancels to -rstd*(m1 + xhat*m2); its rounding error is
     // ~ulp(|mu| * rstd^2 * |m2|), far below the 1e-5 bar since m2 is a mean of zero-mean products)
-    const float ca = rstd;
     const float cb = -rstd * rstd * m2;
-    const float cc = -rstd * m1 - mu * cb;
+    const F2 ca2 = rstd2, cb2 = f2_splat(cb), cc2 = f2_splat(-rstd * m1 - mu * cb);
     T* dst = dx + row * D;
 #pragma unroll
     for (int c = 0; c < C; ++c) {
@@ -134,9 +138,12 @@ ln_grad_pipe_kernel(const T* __restrict__ x, const T* __restrict__ dy, const P* 
           for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(scale + off + j * PV), &w[j * PV]);
         }
 #pragma unroll
-        for (int k = 0; k < V; ++k) {
-          const float gw = HAS_SCALE ? gf[k] * w[k] : gf[k];
-          o[k] = fmaf(ca, gw, fmaf(cb, xf[k], cc));
+        for (int h = 0; h < H; ++h) {
+          const F2 g2 = f2_make(gf[2 * h], gf[2 * h + 1]);
+          const F2 gw = HAS_SCALE ? f2_mul(g2, f2_make(w[2 * h], w[2 * h + 1])) : g2;
+          const F2 r = f2_fma(ca2, gw, f2_fma(cb2, f2_make(xf[2 * h], xf[2 * h + 1]), cc2));
+          o[2 * h] = f2_lo(r);
+          o[2 * h + 1] = f2_hi(r);
         }
         Vec<T> ov;
         pack_from_float<T>(o, ov);
@@ -164,9 +171,11 @@ ln_grad_pipe_kernel(const T* __restrict__ x, const T* __restrict__ dy, const P* 
       const int off = (c * nt + tid) * V;
       if (EXACT || off < D) {
 #pragma unroll
-        for (int k = 0; k < V; ++k) {
-          pds[off + k] = ds[c * V + k];
-          pdb[off + k] = db[c * V + k];
+        for (int h = 0; h < H; ++h) {
+          pds[off + 2 * h] = f2_lo(ds[c * H + h]);
+          pds[off + 2 * h + 1] = f2_hi(ds[c * H + h]);
+          pdb[off + 2 * h] = f2_lo(db[c * H + h]);
+          pdb[off + 2 * h + 1] = f2_hi(db[c * H + h]);
         }
       }
     }
