@@ -312,6 +312,9 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
         lambda: paddle.multiply_grad(xa, ya, oa), n2)
     rec("next: add_grad bf16 [64,2048,4096]+[4096] (dy only)", n2 * 2 + C2_COLS * 2,
         lambda: paddle.add_grad(xa, ya, oa, want_x_grad=False), n2)
+    # mean_grad: a write-only stream (out_grad is one row)
+    rec("next: mean_grad bf16 -> [64,2048,4096] (axis 0,1)", n2 * 2 + C2_COLS * 2,
+        lambda: paddle.mean_grad(xa, ya, axis=[0, 1]), n2)
     del xa, ya, oa, ob
     n = 8 * 32 * 2048 * 2048
     yy = torch.rand((8, 32, 2048, 2048), device="cuda", generator=g).to(torch.bfloat16)

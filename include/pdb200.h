@@ -257,6 +257,19 @@ PDB200_API int pdb200_sum_axis0_static(const void* x, int64_t rows, int64_t cols
                                        void* out, void* stream);
 
 /* ---------------------------------------------------------------------------
+ * Backward of sum / mean: x_grad = out_grad broadcast back over the reduced dimensions
+ * (mean: divided by n = the number of reduced elements, in float for bf16/fp16 — the CPU kernel's g / n; the
+ * GPU kernel's g * (1.0 / n) differs by at most half an fp32 ulp, and for integers by being zero).
+ * Replaces phi::ReduceSumGradKernel / ReduceMeanGradKernel, paddle/phi/kernels/gpu/reduce_kernel.cu:40-76,122-155.
+ * x_dims is the shape of the forward INPUT (= of x_grad); out_grad holds one element per kept position (its own
+ * rank — keep_dim or not — does not matter: the data layout is the same); axes / reduce_all as for the forward.
+ * dtypes: float32, float64, float16, bfloat16, int32, int64.  No workspace. */
+PDB200_API int pdb200_sum_grad(const void* out_grad, const int64_t* x_dims, int x_rank, const int64_t* axes, int n_axes,
+                    int reduce_all, int dtype, void* x_grad, void* stream);
+PDB200_API int pdb200_mean_grad(const void* out_grad, const int64_t* x_dims, int x_rank, const int64_t* axes, int n_axes,
+                     int reduce_all, int dtype, void* x_grad, void* stream);
+
+/* ---------------------------------------------------------------------------
  * argmax.  Replaces phi::ArgMaxKernel<T, GPUContext> (paddle/phi/kernels/gpu/arg_min_max_kernel.cu:59-204).
  * Lowest index wins ties; out_dtype is PDB200_INT64 or PDB200_INT32; flatten != 0 reduces over the
  * flattened tensor (axis ignored); 0-D input yields 0.  x must not be empty (:214-219).

@@ -437,3 +437,36 @@ int oracle_elementwise_grad(int op, int dtype, int acc_mode, const void* x, cons
   }
   return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * sum_grad / mean_grad.  phi::ReduceSumGradKernel / ReduceMeanGradKernel<T,CPUContext>
+ * (cpu/reduce_sum_grad_kernel.cc:26-43, cpu/reduce_mean_grad_kernel.cc) -> ReduceGradKernel (impl/reduce_grad.h) ->
+ * funcs::SumGradFunctor / MeanGradFunctor (funcs/reduce_functor.h:91-123):
+ *     dx = dy.broadcast(dim)                 dx = dy.broadcast(dim) / dx.constant(size)
+ * i.e. every x_grad element is its out_grad element (mean: divided by the number of reduced elements, in T;
+ * integers divide truncating).  bf16 / fp16 mean_grad (no CPU kernel): float division, one rounding.
+ * red[i] != 0 marks a reduced dimension of x.  op: 0 sum_grad, 1 mean_grad.
+ * ---------------------------------------------------------------------------------------- */
+int oracle_reduce_grad(int op, int dtype, const int64_t* xd, int xr, const int* red, const void* out_grad, void* x_grad) {
+  int64_t gs[MAXR], idx[MAXR] = {0}, numel = 1, n = 1, s = 1;
+  for (int i = xr - 1; i >= 0; --i) {
+    gs[i] = red[i] ? 0 : s;
+    if (!red[i]) s *= xd[i]; else n *= xd[i];
+    numel *= xd[i];
+  }
+  for (int64_t i = 0; i < numel; ++i) {
+    int64_t go = 0;
+    for (int d = 0; d < xr; ++d) go += idx[d] * gs[d];
+    switch (dtype) {
+      case DT_FLOAT32: { float v = ((const float*)out_grad)[go]; ((float*)x_grad)[i] = op ? v / (float)n : v; break; }
+      case DT_FLOAT64: { double v = ((const double*)out_grad)[go]; ((double*)x_grad)[i] = op ? v / (double)n : v; break; }
+      case DT_INT32: { int32_t v = ((const int32_t*)out_grad)[go]; ((int32_t*)x_grad)[i] = op ? (int32_t)(v / (int32_t)n) : v; break; }
+      case DT_INT64: { int64_t v = ((const int64_t*)out_grad)[go]; ((int64_t*)x_grad)[i] = op ? v / n : v; break; }
+      case DT_BFLOAT16: { uint16_t v = ((const uint16_t*)out_grad)[go]; ((uint16_t*)x_grad)[i] = op ? f2bf(bf2f(v) / (float)n) : v; break; }
+      case DT_FLOAT16: { uint16_t v = ((const uint16_t*)out_grad)[go]; ((uint16_t*)x_grad)[i] = op ? f2h(h2f(v) / (float)n) : v; break; }
+      default: return 2;
+    }
+    for (int d = xr - 1; d >= 0; --d) { if (++idx[d] < xd[d]) break; idx[d] = 0; }
+  }
+  return 0;
+}

@@ -11,6 +11,8 @@
 //   cast         phi::CastKernel<T,CPUContext>                   paddle/phi/kernels/cpu/cast_kernel.cc, cast_impl.h
 //   where        phi::WhereKernel<T,CPUContext>                  paddle/phi/kernels/cpu/where_kernel.cc:20-36
 //   add_grad     phi::AddGradKernel<T,CPUContext>                paddle/phi/kernels/cpu/elementwise_add_grad_kernel.cc:25-62
+//   sum_grad / mean_grad  phi::ReduceSumGradKernel / ReduceMeanGradKernel<T,CPUContext>
+//                paddle/phi/kernels/cpu/reduce_sum_grad_kernel.cc:26-43, cpu/reduce_mean_grad_kernel.cc
 //   multiply_grad phi::MultiplyGradKernel<T,CPUContext>          paddle/phi/kernels/cpu/elementwise_multiply_grad_kernel.cc:26-39
 #include "paddle/common/flags.h"
 #include "paddle/phi/common/bfloat16.h"
@@ -30,6 +32,8 @@
 #include "paddle/phi/kernels/cpu/elementwise_add_grad_kernel.cc"       // NOLINT
 #include "paddle/phi/kernels/cpu/elementwise_multiply_grad_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/logical_kernel.cc"  // NOLINT
+#include "paddle/phi/kernels/cpu/reduce_mean_grad_kernel.cc"  // NOLINT
+#include "paddle/phi/kernels/cpu/reduce_sum_grad_kernel.cc"   // NOLINT
 #include "paddle/phi/kernels/cpu/scale_kernel.cc"    // NOLINT
 #include "paddle/phi/kernels/cpu/where_kernel.cc"    // NOLINT
 
@@ -268,6 +272,38 @@ int phi_ref_elementwise_grad(int op, int dtype, const void* x, const int64_t* xd
     // the kernels may have re-allocated an output (Alloc on a borrowed buffer keeps it when the size fits)
     if (dx && dxt.data() != dx) std::memcpy(dx, dxt.data(), static_cast<size_t>(dxt.numel()) * phi::SizeOf(dxt.dtype()));
     if (dy && dyt.data() != dy) std::memcpy(dy, dyt.data(), static_cast<size_t>(dyt.numel()) * phi::SizeOf(dyt.dtype()));
+  });
+}
+
+// op: 0 sum_grad, 1 mean_grad.  out_grad is passed with the kept-dim (or dropped-dim) shape the forward produced.
+int phi_ref_reduce_grad(int op, int dtype, const void* x, const int64_t* xdims, int xrank, const void* out_grad,
+                        const int64_t* gdims, int grank, const int64_t* axes, int n_axes, int keep_dim, int reduce_all,
+                        void* x_grad) {
+  return Guard([&] {
+    auto& ctx = GetCtx().ctx;
+    auto xt = Wrap(x, xdims, xrank, dtype);
+    auto gt = Wrap(out_grad, gdims, grank, dtype);
+    auto dxt = Wrap(x_grad, xdims, xrank, dtype);
+    phi::IntArray ax(std::vector<int64_t>(axes, axes + n_axes));
+#define RG_SUM(T) phi::ReduceSumGradKernel<T, CPUContext>(ctx, xt, gt, ax, keep_dim != 0, reduce_all != 0, &dxt); break;
+#define RG_BOTH(T)                                                                                              \
+  if (op == 0) phi::ReduceSumGradKernel<T, CPUContext>(ctx, xt, gt, ax, keep_dim != 0, reduce_all != 0, &dxt);   \
+  else phi::ReduceMeanGradKernel<T, CPUContext>(ctx, xt, gt, ax, keep_dim != 0, reduce_all != 0, &dxt);          \
+  break;
+    if (op != 0 && (dtype == kBFloat16 || dtype == kFloat16))
+      throw std::runtime_error("phi_ref_reduce_grad: mean_grad has no 16-bit kernel on CPU");
+    switch (dtype) {
+      case kFloat32: RG_BOTH(float)
+      case kFloat64: RG_BOTH(double)
+      case kInt32: RG_BOTH(int32_t)
+      case kInt64: RG_BOTH(int64_t)
+      case kBFloat16: RG_SUM(bf16)
+      case kFloat16: RG_SUM(fp16)
+      default: throw std::runtime_error("phi_ref_reduce_grad: dtype not registered on CPU");
+    }
+#undef RG_SUM
+#undef RG_BOTH
+    if (dxt.data() != x_grad) std::memcpy(x_grad, dxt.data(), static_cast<size_t>(dxt.numel()) * phi::SizeOf(dxt.dtype()));
   });
 }
 

@@ -47,6 +47,8 @@ SIGNATURES = {
     "pdb200_elementwise_grad_workspace_bytes": (_sz, [_int, _c_i64p, _int, _c_i64p, _int, _int, _int, _int]),
     "pdb200_add_grad": (_int, [_c_i64p, _int, _c_i64p, _int, _vp, _int, _vp, _vp, _vp, _sz, _vp]),
     "pdb200_multiply_grad": (_int, [_vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp, _vp, _vp, _sz, _vp]),
+    "pdb200_sum_grad": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _vp, _vp]),
+    "pdb200_mean_grad": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _vp, _vp]),
     "pdb200_reduce_workspace_bytes": (_sz, [_int, _c_i64p, _int, _c_i64p, _int, _int, _int, _int]),
     "pdb200_sum_raw": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _int, _vp, _vp, _sz, _vp]),
     "pdb200_mean_raw": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _int, _vp, _vp, _sz, _vp]),

@@ -233,15 +233,13 @@ __device__ __forceinline__ F2 f2_make(float lo, float hi) {
 }
 __device__ __forceinline__ F2 f2_splat(float x) { return f2_make(x, x); }
 __device__ __forceinline__ float f2_lo(F2 a) {
-  float lo, hi;
-  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.v));
-  (void)hi;
+  float lo;
+  asm("{ .reg .b32 hi; mov.b64 {%0, hi}, %1; }" : "=f"(lo) : "l"(a.v));
   return lo;
 }
 __device__ __forceinline__ float f2_hi(F2 a) {
-  float lo, hi;
-  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.v));
-  (void)lo;
+  float hi;
+  asm("{ .reg .b32 lo; mov.b64 {lo, %0}, %1; }" : "=f"(hi) : "l"(a.v));
   return hi;
 }
 __device__ __forceinline__ F2 f2_fma(F2 a, F2 b, F2 c) {

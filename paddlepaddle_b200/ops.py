@@ -367,6 +367,35 @@ def sum(x, axis=None, dtype=None, keepdim=False, name=None):
     return _reduce(L.REDUCE_SUM, x, axis, keepdim, dt)
 
 
+def _reduce_grad(fn_name, x, out_grad, axis, keepdim, reduce_all):
+    """sum_grad / mean_grad(x, out_grad, axis, keepdim, reduce_all) -> x_grad (paddle/phi/ops/yaml/backward.yaml)."""
+    _require_cuda(x, out_grad)
+    if x.dtype != out_grad.dtype:
+        raise TypeError("(InvalidType) x and out_grad must share one dtype")
+    axes = _norm_axes(axis, x.dim())
+    want = _reduced_shape(tuple(x.shape), [] if reduce_all else axes, keepdim)
+    if tuple(out_grad.shape) != tuple(want):
+        raise ValueError(f"(InvalidArgument) out_grad has shape {tuple(out_grad.shape)}, the forward output has {tuple(want)}")
+    lib = L.load()
+    out_grad = out_grad.contiguous()
+    x_grad = torch.empty(x.shape, dtype=x.dtype, device=x.device)
+    xd, xr = L.dims_array(x.shape)
+    ad, an = L.dims_array(axes)
+    L.check(getattr(lib, fn_name)(_ptr(out_grad), xd, xr, ad, an, int(bool(reduce_all) or not axes), _dtype_code(x.dtype),
+                                  _ptr(x_grad), _stream()), lib)
+    return x_grad
+
+
+def sum_grad(x, out_grad, axis=None, keepdim=False, reduce_all=False):
+    """Backward of paddle.sum: out_grad repeated along the reduced axes (only x's shape and dtype are used)."""
+    return _reduce_grad("pdb200_sum_grad", x, out_grad, axis, keepdim, reduce_all)
+
+
+def mean_grad(x, out_grad, axis=None, keepdim=False, reduce_all=False):
+    """Backward of paddle.mean: out_grad / n repeated along the reduced axes."""
+    return _reduce_grad("pdb200_mean_grad", x, out_grad, axis, keepdim, reduce_all)
+
+
 def mean(x, axis=None, keepdim=False, name=None):
     return _reduce(L.REDUCE_MEAN, x, axis, keepdim, x.dtype)
 

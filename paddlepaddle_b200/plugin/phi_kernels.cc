@@ -192,6 +192,26 @@ void MultiplyGradKernel(const Context& ctx, const DenseTensor& x, const DenseTen
   BinaryGrad<T>(ctx, PDB200_GRAD_MULTIPLY, x, y, dout, axis, dx, dy);
 }
 
+// ---- sum_grad / mean_grad (gpu/reduce_kernel.cu:40-76,122-155) ---------------------------------------------------
+template <typename T, typename Context>
+void ReduceSumGradKernel(const Context& ctx, const DenseTensor& x, const DenseTensor& out_grad, const phi::IntArray& dims,
+                         bool keep_dim, bool reduce_all, DenseTensor* x_grad) {
+  void* o = ctx.Alloc(x_grad, x.dtype());
+  auto xd = Dims(x);
+  const auto& ax = dims.GetData();
+  Check(pdb200_sum_grad(out_grad.data(), xd.data(), static_cast<int>(xd.size()), ax.data(), static_cast<int>(ax.size()),
+                        reduce_all, Code(x.dtype()), o, ctx.stream()));
+}
+template <typename T, typename Context>
+void ReduceMeanGradKernel(const Context& ctx, const DenseTensor& x, const DenseTensor& out_grad, const phi::IntArray& dims,
+                          bool keep_dim, bool reduce_all, DenseTensor* x_grad) {
+  void* o = ctx.Alloc(x_grad, x.dtype());
+  auto xd = Dims(x);
+  const auto& ax = dims.GetData();
+  Check(pdb200_mean_grad(out_grad.data(), xd.data(), static_cast<int>(xd.size()), ax.data(), static_cast<int>(ax.size()),
+                         reduce_all, Code(x.dtype()), o, ctx.stream()));
+}
+
 // ---- reductions --------------------------------------------------------------------------
 typedef int (*ReduceFn)(const void*, const int64_t*, int, const int64_t*, int, int, int, int, void*, void*,
                         size_t, void*);
@@ -393,6 +413,13 @@ PD_REGISTER_KERNEL(add_grad, GPU, ALL_LAYOUT, pdb200_phi::AddGradKernel, float, 
                    phi::dtype::float16, phi::dtype::bfloat16) {}
 PD_REGISTER_KERNEL(multiply_grad, GPU, ALL_LAYOUT, pdb200_phi::MultiplyGradKernel, float, phi::dtype::float16, double,
                    int, int64_t, phi::dtype::bfloat16) {}
+// gpu/reduce_kernel.cu:346-358,371-388 (bool, the 8/16-bit integers and complex stay with the in-tree kernels)
+PD_REGISTER_KERNEL(sum_grad, GPU, ALL_LAYOUT, pdb200_phi::ReduceSumGradKernel, float, double, phi::dtype::float16,
+                   phi::dtype::bfloat16, int, int64_t) {
+  kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);
+}
+PD_REGISTER_KERNEL(mean_grad, GPU, ALL_LAYOUT, pdb200_phi::ReduceMeanGradKernel, float, double, phi::dtype::float16,
+                   phi::dtype::bfloat16, int, int64_t) {}
 PD_REGISTER_KERNEL(sum_raw, GPU, ALL_LAYOUT, pdb200_phi::SumRawKernel, bool, float, double, phi::dtype::float16,
                    phi::dtype::bfloat16, int, int64_t) {
   kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);  // reduce_sum_kernel.cc:75-77

@@ -114,6 +114,15 @@ def main():
         g[f"grad_{name}_bfloat16__in0"], g[f"grad_{name}_bfloat16__in1"], g[f"grad_{name}_bfloat16__in2"] = x, y, d
         dx, dy = ref.elementwise_grad("multiply", x, y, d, code=O.BFLOAT16)  # add_grad has no bf16 kernel on CPU
         g[f"grad_multiply_{name}_bfloat16__out0"], g[f"grad_multiply_{name}_bfloat16__out1"] = dx, dy
+    # sum_grad / mean_grad: the axis matrix of test_reduce_op.py
+    for name, shape, axis, keep in REDUCE_GRAD_CASES:
+        axes = [] if axis is None else ([axis] if isinstance(axis, int) else list(axis))
+        gshape = O.reduced_shape(shape, axes, keep)
+        for dt in ("float32", "float64", "int32", "int64"):
+            d = (rng.standard_normal(gshape) * 100).astype(dt)
+            g[f"rgrad_{name}_{dt}__in0"] = d
+            for op in ("sum", "mean"):
+                g[f"rgrad_{op}_{name}_{dt}__out"] = ref.reduce_grad(op, shape, d, axis, keep)
     out = os.path.join(HERE, "phi_family_golden.npz")
     np.savez_compressed(out, **g)
     print(f"wrote {out}: {len(g)} arrays, {os.path.getsize(out)} bytes")
@@ -123,6 +132,10 @@ GRAD_CASES = [("same", (13, 17), (13, 17)), ("vec_last", (2, 10, 12), (12,)), ("
               ("mid", (2, 3, 100), (3, 1)), ("lead", (100, 2, 3), (100, 1, 1)), ("four", (10, 3, 1, 4), (10, 1, 12, 1)),
               ("x_small", (10, 12), (2, 2, 10, 12)), ("scalar0d", (3, 4), ()), ("both0d", (), ()), ("col", (64, 33), (64, 1)),
               ("outer_x", (1, 33), (64, 33)), ("rows", (300, 256), (256,))]
+REDUCE_GRAD_CASES = [("r2_last", (5, 6), -1, False), ("r2_first_keep", (5, 6), 0, True), ("r2_all", (5, 6), None, False),
+                     ("r3_mid_keep", (5, 6, 10), 1, True), ("r3_02", (5, 6, 10), (0, 2), False), ("r4_12", (2, 5, 3, 2), (1, 2), False),
+                     ("r1", (120,), 0, False), ("r3_one", (3, 1, 4), 1, False), ("r0", (), None, False),
+                     ("r5", (1, 2, 5, 6, 10), 2, False), ("r2_wide", (3, 901), -1, False)]
 SCALE_ARGS = [(-2.3, 0.0, True), (-2.3, 2.3, True), (-2.3, 2.3, False), (3.0, -1.0, True), (0.0, 0.5, False)]
 
 

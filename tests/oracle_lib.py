@@ -291,6 +291,27 @@ class Oracle:
         self._check(rc)
         return dx, dy
 
+    def reduce_grad(self, op, x_shape, out_grad, axis=None, keepdim=False, code=None):
+        """op 'sum'|'mean' -> x_grad of shape x_shape; out_grad has the forward output's shape."""
+        out_grad = np.ascontiguousarray(out_grad)
+        code = NP2CODE[out_grad.dtype] if code is None else code
+        rank = len(x_shape)
+        axes = [] if axis is None else ([int(a) for a in axis] if isinstance(axis, (list, tuple)) else [int(axis)])
+        x_grad = np.empty(x_shape, out_grad.dtype)
+        xd, xr = _dims(x_shape)
+        opc = {"sum": 0, "mean": 1}[op]
+        if self.kind == "port":
+            red = [1] * rank if not axes else [int(i in {a % rank for a in axes}) for i in range(rank)]
+            rc = self.lib.oracle_reduce_grad(opc, code, xd, xr, (ctypes.c_int * max(rank, 1))(*red), _vp(out_grad), _vp(x_grad))
+        else:
+            x = np.zeros(x_shape, out_grad.dtype)
+            gd, gr = _dims(out_grad.shape if out_grad.shape == reduced_shape(x_shape, axes, keepdim) else reduced_shape(x_shape, axes, keepdim))
+            ad, an = _dims(axes)
+            rc = self.lib.phi_ref_reduce_grad(opc, code, _vp(x), xd, xr, _vp(out_grad), gd, gr, ad, an, int(keepdim),
+                                              int(not axes), _vp(x_grad))
+        self._check(rc)
+        return x_grad
+
     def _check(self, rc):
         if rc != 0:
             msg = ""

@@ -144,3 +144,12 @@ def test_elementwise_grad_live_single_outputs(port, ref):
                             assert np.array_equal(a, b)
                         else:
                             np.testing.assert_allclose(a, b, rtol=64 * np.finfo(dt).eps, atol=64 * np.finfo(dt).eps)
+
+
+def test_reduce_grad_golden_and_live(port, gold):
+    from golden.make_golden_family import REDUCE_GRAD_CASES
+    for name, shape, axis, keep in REDUCE_GRAD_CASES:
+        for dt in ("float32", "float64", "int32", "int64"):
+            d = gold[f"rgrad_{name}_{dt}__in0"]
+            for op in ("sum", "mean"):
+                assert np.array_equal(port.reduce_grad(op, shape, d, axis, keep), gold[f"rgrad_{op}_{name}_{dt}__out"]), (op, name, dt)
