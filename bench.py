@@ -319,6 +319,7 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
     n = 8 * 32 * 2048 * 2048
     yy = torch.rand((8, 32, 2048, 2048), device="cuda", generator=g).to(torch.bfloat16)
     dyy = torch.randn((8, 32, 2048, 2048), device="cuda", generator=g).to(torch.bfloat16)
+    rec("next: log_softmax bf16 [8,32,2048,2048] axis=-1", 2 * n * 2, lambda: F.log_softmax(yy, axis=-1), n)
     rec("next: softmax_grad bf16 [8,32,2048,2048] axis=-1", 3 * n * 2, lambda: F.softmax_grad(yy, dyy, axis=-1), n)
     del yy, dyy
     rows, D = 65536, 8192

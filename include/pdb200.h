@@ -290,6 +290,13 @@ PDB200_API int pdb200_argmax(const void* x, const int64_t* x_dims, int x_rank, i
 PDB200_API int pdb200_softmax(const void* x, const int64_t* dims, int rank, int axis, int dtype, void* out,
                    void* stream);
 
+/* log_softmax forward along `axis`.  Replaces phi::LogSoftmaxKernel<T, GPUContext>
+ * (paddle/phi/kernels/gpu/log_softmax_kernel.cu; numerics of the CPU kernel,
+ * paddle/phi/kernels/cpu/log_softmax_kernel.cc:40-127): y = d - log(sum(exp(d))) with d = max(x - max, -64).
+ * Same routes, dtypes and edge cases as pdb200_softmax (0-D yields 0). */
+PDB200_API int pdb200_log_softmax(const void* x, const int64_t* dims, int rank, int axis, int dtype, void* out,
+                       void* stream);
+
 /* ---------------------------------------------------------------------------
  * layer_norm forward.  Replaces phi::LayerNormKernel<T, GPUContext>
  * (paddle/phi/kernels/gpu/layer_norm_kernel.cu:490-665).

@@ -470,3 +470,57 @@ int oracle_reduce_grad(int op, int dtype, const int64_t* xd, int xr, const int* 
   }
   return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * log_softmax.  phi::LogSoftmaxKernel<T,CPUContext> -> LogSoftmaxFunctor
+ * (cpu/log_softmax_kernel.cc:40-127): x viewed as [n][axis_dim][remain];
+ *     d = max(x - max_along_axis, -64)   (ValueClip :32-38)
+ *     y = d - log(sum_along_axis(exp(d)))
+ * 0-D -> 0; 0-size -> no-op.  Sums run along the axis in increasing index (Eigen's reducer order only moves the
+ * last bits: tests compare to 1e-6).  T = float or double on the CPU; bf16 / fp16 (GPU registration) follow by
+ * computing in float and rounding once.
+ * ---------------------------------------------------------------------------------------- */
+int oracle_log_softmax(int dtype, const void* x, const int64_t* dims, int rank, int axis, void* out) {
+  if (rank == 0) {
+    switch (dtype) {
+      case DT_FLOAT32: *(float*)out = 0.f; break;
+      case DT_FLOAT64: *(double*)out = 0.0; break;
+      case DT_BFLOAT16: case DT_FLOAT16: *(uint16_t*)out = 0; break;
+      default: return 2;
+    }
+    return 0;
+  }
+  if (axis < -rank || axis >= rank) return 1;
+  if (axis < 0) axis += rank;
+  int64_t n = 1, ad = dims[axis], rem = 1;
+  for (int i = 0; i < axis; ++i) n *= dims[i];
+  for (int i = axis + 1; i < rank; ++i) rem *= dims[i];
+  if (n * ad * rem == 0) return 0;
+  for (int64_t b = 0; b < n; ++b)
+    for (int64_t r = 0; r < rem; ++r) {
+      const int64_t base = b * ad * rem + r;
+#define LSM_AT(k) (base + (k) * rem)
+      if (dtype == DT_FLOAT64) {
+        const double* X = (const double*)x; double* Y = (double*)out;
+        double m = X[LSM_AT(0)], s = 0.0;
+        for (int64_t k = 1; k < ad; ++k) if (X[LSM_AT(k)] > m) m = X[LSM_AT(k)];
+        for (int64_t k = 0; k < ad; ++k) { double d = X[LSM_AT(k)] - m; if (d < -64.0) d = -64.0; Y[LSM_AT(k)] = d; s += exp(d); }
+        const double l = log(s);
+        for (int64_t k = 0; k < ad; ++k) Y[LSM_AT(k)] -= l;
+      } else {
+        float m = -INFINITY, s = 0.f;
+#define LSM_LOAD(k) (dtype == DT_FLOAT32 ? ((const float*)x)[LSM_AT(k)] : dtype == DT_BFLOAT16 ? bf2f(((const uint16_t*)x)[LSM_AT(k)]) : h2f(((const uint16_t*)x)[LSM_AT(k)]))
+        if (dtype != DT_FLOAT32 && dtype != DT_BFLOAT16 && dtype != DT_FLOAT16) return 2;
+        for (int64_t k = 0; k < ad; ++k) { const float v = LSM_LOAD(k); if (v > m) m = v; }
+        for (int64_t k = 0; k < ad; ++k) { float d = LSM_LOAD(k) - m; if (d < -64.f) d = -64.f; s += expf(d); }
+        const float l = logf(s);
+        for (int64_t k = 0; k < ad; ++k) {
+          float d = LSM_LOAD(k) - m; if (d < -64.f) d = -64.f;
+          const float y = d - l;
+          if (dtype == DT_FLOAT32) ((float*)out)[LSM_AT(k)] = y;
+          else ((uint16_t*)out)[LSM_AT(k)] = dtype == DT_BFLOAT16 ? f2bf(y) : f2h(y);
+        }
+      }
+    }
+  return 0;
+}

@@ -11,6 +11,7 @@
 //   cast         phi::CastKernel<T,CPUContext>                   paddle/phi/kernels/cpu/cast_kernel.cc, cast_impl.h
 //   where        phi::WhereKernel<T,CPUContext>                  paddle/phi/kernels/cpu/where_kernel.cc:20-36
 //   add_grad     phi::AddGradKernel<T,CPUContext>                paddle/phi/kernels/cpu/elementwise_add_grad_kernel.cc:25-62
+//   log_softmax  phi::LogSoftmaxKernel<T,CPUContext>             paddle/phi/kernels/cpu/log_softmax_kernel.cc:40-127
 //   sum_grad / mean_grad  phi::ReduceSumGradKernel / ReduceMeanGradKernel<T,CPUContext>
 //                paddle/phi/kernels/cpu/reduce_sum_grad_kernel.cc:26-43, cpu/reduce_mean_grad_kernel.cc
 //   multiply_grad phi::MultiplyGradKernel<T,CPUContext>          paddle/phi/kernels/cpu/elementwise_multiply_grad_kernel.cc:26-39
@@ -31,6 +32,7 @@
 #include "paddle/phi/kernels/cpu/compare_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/elementwise_add_grad_kernel.cc"       // NOLINT
 #include "paddle/phi/kernels/cpu/elementwise_multiply_grad_kernel.cc"  // NOLINT
+#include "paddle/phi/kernels/cpu/log_softmax_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/logical_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/reduce_mean_grad_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/reduce_sum_grad_kernel.cc"   // NOLINT
@@ -272,6 +274,19 @@ int phi_ref_elementwise_grad(int op, int dtype, const void* x, const int64_t* xd
     // the kernels may have re-allocated an output (Alloc on a borrowed buffer keeps it when the size fits)
     if (dx && dxt.data() != dx) std::memcpy(dx, dxt.data(), static_cast<size_t>(dxt.numel()) * phi::SizeOf(dxt.dtype()));
     if (dy && dyt.data() != dy) std::memcpy(dy, dyt.data(), static_cast<size_t>(dyt.numel()) * phi::SizeOf(dyt.dtype()));
+  });
+}
+
+int phi_ref_log_softmax(int dtype, const void* x, const int64_t* dims, int rank, int axis, void* out) {
+  return Guard([&] {
+    auto& ctx = GetCtx().ctx;
+    auto xt = Wrap(x, dims, rank, dtype);
+    auto ot = Wrap(out, dims, rank, dtype);
+    switch (dtype) {
+      case kFloat32: phi::LogSoftmaxKernel<float, CPUContext>(ctx, xt, axis, &ot); break;
+      case kFloat64: phi::LogSoftmaxKernel<double, CPUContext>(ctx, xt, axis, &ot); break;
+      default: throw std::runtime_error("phi_ref_log_softmax: dtype not registered on CPU");
+    }
   });
 }
 

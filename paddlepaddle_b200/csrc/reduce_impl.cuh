@@ -553,10 +553,13 @@ int launch_pass(const ReducePass& ps, const PassGeom& g, bool vec, const T* x, O
         constexpr int TI = 32 * Vec<T>::N;
         const size_t smem_tma = (size_t)kTmaStages * kTmaTileRows * TI * sizeof(T) + (size_t)8 * TI * sizeof(A);
         auto kern = reduce_cols_tma_kernel<T, O, Op, Fin>;
-        static bool attr_set = false;  // per instantiation
-        if (!attr_set) {
+        // the attribute is per (kernel, device): remember it per device, one flag array per instantiation
+        static bool attr_set[64] = {false};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev < 0 || dev >= 64 || !attr_set[dev]) {
           cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tma);
-          attr_set = true;
+          if (dev >= 0 && dev < 64) attr_set[dev] = true;
         }
         kern<<<(unsigned)blocks, kTmaThreads, smem_tma, st>>>(map, out, ps.red, ps.inner, g.seg, g.splits, g.col_tiles, fin);
         return after_launch("reduce_cols_tma");

@@ -46,6 +46,23 @@ __device__ __forceinline__ A clipped_exp(A x, A m) {
   return exp_acc<A>(d);
 }
 
+template <typename A> __device__ __forceinline__ A log_acc(A v);
+template <> __device__ __forceinline__ float log_acc<float>(float v) { return logf(v); }
+template <> __device__ __forceinline__ double log_acc<double>(double v) { return log(v); }
+// max(x - m, -64): the shifted, clipped logit both softmax and log_softmax are built from
+template <typename A>
+__device__ __forceinline__ A clipped_diff(A x, A m) {
+  const A d = x - m;
+  return d < A(-64) ? A(-64) : d;
+}
+// LOG = false: softmax,      y = e * (1 / sum)          with e = exp(clipped_diff)
+// LOG = true : log_softmax,  y = d - log(sum)           with d = clipped_diff
+//   (phi::LogSoftmaxFunctor, paddle/phi/kernels/cpu/log_softmax_kernel.cc:40-100; GPU: gpu/log_softmax_kernel.cu)
+template <bool LOG, typename A>
+__device__ __forceinline__ A row_constant(A sum) { return LOG ? log_acc<A>(sum) : A(1) / sum; }
+template <bool LOG, typename A>
+__device__ __forceinline__ A finish(A e_or_d, A k) { return LOG ? e_or_d - k : e_or_d * k; }
+
 template <typename A> struct MaxF { __device__ __forceinline__ A operator()(A a, A b) const { return b > a ? b : a; } };
 template <typename A> struct AddF { __device__ __forceinline__ A operator()(A a, A b) const { return a + b; } };
 
@@ -55,7 +72,7 @@ __device__ __forceinline__ A neg_inf() { return -std::numeric_limits<A>::infinit
 // ---- rows_reg --------------------------------------------------------------------------
 // G lanes (power of two <= 32) per row, C chunks of V elements per lane; chunk c of lane l
 // covers elements (c*G + l)*V .. +V.  Out-of-row chunks hold -inf and are never stored.
-template <typename T, int C, bool VECTOR>
+template <typename T, int C, bool VECTOR, bool LOG>
 __global__ void __launch_bounds__(256) softmax_rows_reg_kernel(const T* __restrict__ x,
                                                                T* __restrict__ y, int64_t outer,
                                                                int dim, int G) {
@@ -98,13 +115,18 @@ __global__ void __launch_bounds__(256) softmax_rows_reg_kernel(const T* __restri
     if (off < dim) {
 #pragma unroll
       for (int k = 0; k < V; ++k) {
-        e[c * V + k] = clipped_exp<A>(e[c * V + k], m);
-        sum += e[c * V + k];
+        if constexpr (LOG) {
+          e[c * V + k] = clipped_diff<A>(e[c * V + k], m);
+          sum += exp_acc<A>(e[c * V + k]);
+        } else {
+          e[c * V + k] = clipped_exp<A>(e[c * V + k], m);
+          sum += e[c * V + k];
+        }
       }
     }
   }
   for (int s = G >> 1; s >= 1; s >>= 1) sum += shfl_xor_any(sum, s);
-  const A inv = A(1) / sum;
+  const A inv = row_constant<LOG, A>(sum);
 #pragma unroll
   for (int c = 0; c < C; ++c) {
     const int off = (c * G + lane) * V;
@@ -112,10 +134,10 @@ __global__ void __launch_bounds__(256) softmax_rows_reg_kernel(const T* __restri
       if constexpr (VECTOR) {
         Vec<T> o;
 #pragma unroll
-        for (int k = 0; k < V; ++k) o.v[k] = cvt<T>(e[c * V + k] * inv);
+        for (int k = 0; k < V; ++k) o.v[k] = cvt<T>(finish<LOG, A>(e[c * V + k], inv));
         st_stream(dst + off, o);
       } else {
-        dst[off] = cvt<T>(e[c] * inv);
+        dst[off] = cvt<T>(finish<LOG, A>(e[c], inv));
       }
     }
   }
@@ -145,7 +167,7 @@ template <> __device__ __forceinline__ double row_exp<double>(double x, double m
 
 // ---- pipe: persistent CTAs, rows staged in shared memory by cp.async.bulk -------------------
 // blockDim.x threads per row, C chunks of V elements per thread.  T is float, bf16 or fp16.
-template <typename T, int C, bool EXACT>
+template <typename T, int C, bool EXACT, bool LOG>
 __global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__ x, T* __restrict__ y,
                                                            int64_t rows, int dim, int stages, int contiguous) {
   constexpr int V = Vec<T>::N;
@@ -221,13 +243,20 @@ __global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__
       const int off = (c * nt + tid) * V;
 #pragma unroll
       for (int k = 0; k < V; ++k) {
-        e[c * V + k] = fast_clipped_exp(e[c * V + k], nml);
-        if (EXACT || off < dim) sm[k & 3] += e[c * V + k];  // padding chunks are not part of the row
+        float p;
+        if constexpr (LOG) {
+          const float d = fmaxf(e[c * V + k] - m, -64.0f);  // the exact clipped difference is the output term
+          e[c * V + k] = d;
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p) : "f"(d * 1.4426950408889634f));
+        } else {
+          p = e[c * V + k] = fast_clipped_exp(e[c * V + k], nml);
+        }
+        if (EXACT || off < dim) sm[k & 3] += p;  // padding chunks are not part of the row
       }
     }
     float sum = (sm[0] + sm[1]) + (sm[2] + sm[3]);
     sum = block_reduce_1sync(sum, AddF<float>(), red[1]);
-    const float inv = 1.0f / sum;
+    const float inv = row_constant<LOG, float>(sum);
     T* dst = y + row * dim;
 #pragma unroll
     for (int c = 0; c < C; ++c) {
@@ -235,7 +264,7 @@ __global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__
       if (EXACT || off < dim) {
         float r[V];
 #pragma unroll
-        for (int k = 0; k < V; ++k) r[k] = e[c * V + k] * inv;
+        for (int k = 0; k < V; ++k) r[k] = finish<LOG, float>(e[c * V + k], inv);
         Vec<T> o;
         pack_from_float<T>(r, o);
         st_stream(dst + off, o);
@@ -249,7 +278,7 @@ __global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__
 }
 
 // ---- rows_smem -------------------------------------------------------------------------
-template <typename T, bool VECTOR>
+template <typename T, bool VECTOR, bool LOG>
 __global__ void __launch_bounds__(1024) softmax_rows_smem_kernel(const T* __restrict__ x,
                                                                  T* __restrict__ y, int64_t dim) {
   using A = typename AccType<T>::type;
@@ -278,20 +307,26 @@ __global__ void __launch_bounds__(1024) softmax_rows_smem_kernel(const T* __rest
   m = block_reduce(m, MaxF<A>(), neg_inf<A>(), red);  // also orders the smem writes
   A sum = A(0);
   for (int64_t i = threadIdx.x; i < dim; i += blockDim.x) {  // each thread revisits what any thread wrote: synced above
-    A ev = clipped_exp<A>(row[i], m);
-    row[i] = ev;
-    sum += ev;
+    if constexpr (LOG) {
+      const A d = clipped_diff<A>(row[i], m);
+      row[i] = d;
+      sum += exp_acc<A>(d);
+    } else {
+      A ev = clipped_exp<A>(row[i], m);
+      row[i] = ev;
+      sum += ev;
+    }
   }
   sum = block_reduce(sum, AddF<A>(), A(0), red);
-  const A inv = A(1) / sum;
+  const A inv = row_constant<LOG, A>(sum);
   for (int64_t i = (int64_t)threadIdx.x * V; i < dim; i += (int64_t)blockDim.x * V) {
     if constexpr (VECTOR) {
       Vec<T> o;
 #pragma unroll
-      for (int k = 0; k < V; ++k) o.v[k] = cvt<T>(row[i + k] * inv);
+      for (int k = 0; k < V; ++k) o.v[k] = cvt<T>(finish<LOG, A>(row[i + k], inv));
       st_stream(dst + i, o);
     } else {
-      dst[i] = cvt<T>(row[i] * inv);
+      dst[i] = cvt<T>(finish<LOG, A>(row[i], inv));
     }
   }
 }
@@ -302,7 +337,7 @@ __global__ void __launch_bounds__(1024) softmax_rows_smem_kernel(const T* __rest
 // per CTA, published in that CTA's shared memory and read by every peer through DSMEM
 // (cluster.map_shared_rank) after a cluster barrier; all CTAs fold the partials in rank order, so
 // they agree bit for bit.  Requires dim % V == 0 and 16-byte aligned bases (vector path only).
-template <typename T>
+template <typename T, bool LOG>
 __global__ void __launch_bounds__(1024) softmax_rows_cluster_kernel(const T* __restrict__ x, T* __restrict__ y,
                                                                     int64_t dim, int64_t slice) {
   namespace cg = cooperative_groups;
@@ -366,20 +401,21 @@ __global__ void __launch_bounds__(1024) softmax_rows_cluster_kernel(const T* __r
   cluster.sync();
   A gs = A(0);
   for (unsigned r = 0; r < cs; ++r) gs += *cluster.map_shared_rank(&xchg[1], r);
-  const A inv = A(1) / gs;
+  const A inv = row_constant<LOG, A>(gs);
   // sweep 3: normalise and store
   for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
     const Vec<T> v = lds_vec(srow + i);
     Vec<T> o;
 #pragma unroll
-    for (int k = 0; k < V; ++k) o.v[k] = cvt<T>(row_exp<A>(cvt<A>(v.v[k]), gm, nml) * inv);
+    for (int k = 0; k < V; ++k)
+      o.v[k] = cvt<T>(LOG ? clipped_diff<A>(cvt<A>(v.v[k]), gm) - inv : row_exp<A>(cvt<A>(v.v[k]), gm, nml) * inv);
     st_stream(dst + i, o);
   }
   cluster.sync();  // nobody leaves while a peer may still be reading its xchg[]
 }
 
 // ---- rows_stream -----------------------------------------------------------------------
-template <typename T>
+template <typename T, bool LOG>
 __global__ void __launch_bounds__(1024) softmax_rows_stream_kernel(const T* x, T* y, int64_t dim) {
   using A = typename AccType<T>::type;
   __shared__ A red[33];
@@ -394,13 +430,14 @@ __global__ void __launch_bounds__(1024) softmax_rows_stream_kernel(const T* x, T
   A sum = A(0);
   for (int64_t i = threadIdx.x; i < dim; i += blockDim.x) sum += clipped_exp<A>(cvt<A>(src[i]), m);
   sum = block_reduce(sum, AddF<A>(), A(0), red);
-  const A inv = A(1) / sum;
+  const A inv = row_constant<LOG, A>(sum);
   // in-place safe: each element is read and written by the same thread in this sweep
-  for (int64_t i = threadIdx.x; i < dim; i += blockDim.x) dst[i] = cvt<T>(clipped_exp<A>(cvt<A>(src[i]), m) * inv);
+  for (int64_t i = threadIdx.x; i < dim; i += blockDim.x)
+    dst[i] = cvt<T>(LOG ? clipped_diff<A>(cvt<A>(src[i]), m) - inv : clipped_exp<A>(cvt<A>(src[i]), m) * inv);
 }
 
 // ---- cols: softmax along the middle axis of [outer][dim][inner] ---------------------------
-template <typename T>
+template <typename T, bool LOG>
 __global__ void __launch_bounds__(256) softmax_cols_kernel(const T* x, T* y, int64_t dim,
                                                            int64_t inner, int64_t col_tiles) {
   using A = typename AccType<T>::type;
@@ -417,22 +454,23 @@ __global__ void __launch_bounds__(256) softmax_cols_kernel(const T* x, T* y, int
   }
   A sum = A(0);
   for (int64_t r = 0; r < dim; ++r) sum += clipped_exp<A>(cvt<A>(src[r * inner]), m);
-  const A inv = A(1) / sum;
-  for (int64_t r = 0; r < dim; ++r) dst[r * inner] = cvt<T>(clipped_exp<A>(cvt<A>(src[r * inner]), m) * inv);
+  const A inv = row_constant<LOG, A>(sum);
+  for (int64_t r = 0; r < dim; ++r)
+    dst[r * inner] = cvt<T>(LOG ? clipped_diff<A>(cvt<A>(src[r * inner]), m) - inv : clipped_exp<A>(cvt<A>(src[r * inner]), m) * inv);
 }
 
 template <typename T>
-__global__ void softmax_fill_one_kernel(T* y) { y[0] = cvt<T>(typename AccType<T>::type(1)); }
+__global__ void softmax_fill_one_kernel(T* y, float v) { y[0] = cvt<T>(typename AccType<T>::type(v)); }
 
 // ---- host -------------------------------------------------------------------------------
-template <typename T, bool VECTOR>
+template <typename T, bool VECTOR, bool LOG>
 int launch_rows_reg(const T* x, T* y, int64_t outer, int dim, int G, int C, cudaStream_t st) {
   const int rows_per_cta = 256 / G;
   const int64_t blocks = (outer + rows_per_cta - 1) / rows_per_cta;
   if (blocks > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "softmax: too many rows for one launch");
 #define PDB_SM_C(CC)                                                                                \
   case CC:                                                                                          \
-    softmax_rows_reg_kernel<T, CC, VECTOR><<<(unsigned)blocks, 256, 0, st>>>(x, y, outer, dim, G); \
+    softmax_rows_reg_kernel<T, CC, VECTOR, LOG><<<(unsigned)blocks, 256, 0, st>>>(x, y, outer, dim, G); \
     break;
   switch (C) {
     PDB_SM_C(1) PDB_SM_C(2) PDB_SM_C(4) PDB_SM_C(8) PDB_SM_C(16)
@@ -443,8 +481,11 @@ int launch_rows_reg(const T* x, T* y, int64_t outer, int dim, int G, int C, cuda
 }
 
 // TMA row pipeline (float / bf16 / fp16 rows of 64..2048 16-byte chunks, many rows).
-template <typename T>
+template <typename T, bool LOG>
 int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, cudaStream_t st) {
+  if constexpr (std::is_same<T, double>::value) {
+    return -1;  // the pipeline computes in float
+  } else {
   constexpr int VN = Vec<T>::N;
   const int64_t nchunk = dim / VN;
   // chunks per thread: 16-bit rows do best with 4 (32 values a thread), fp32 rows with 2
@@ -468,18 +509,18 @@ int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, cudaStream_t 
     return after_launch("softmax_pipe");
   };
   const bool exact = (int64_t)threads * C == nchunk;
-#define PDB_SM_PIPE(CC) return exact ? launch(softmax_pipe_kernel<T, CC, true>) : launch(softmax_pipe_kernel<T, CC, false>);
+#define PDB_SM_PIPE(CC) \
+  return exact ? launch(softmax_pipe_kernel<T, CC, true, LOG>) : launch(softmax_pipe_kernel<T, CC, false, LOG>);
   if (C == 8) { PDB_SM_PIPE(8) }
   if (C == 4) { PDB_SM_PIPE(4) }
   if (C == 2) { PDB_SM_PIPE(2) }
   PDB_SM_PIPE(1)
 #undef PDB_SM_PIPE
+  }
 }
-template <>
-int try_softmax_pipe<double>(const double*, double*, int64_t, int64_t, cudaStream_t) { return -1; }
 
 // Cluster route: returns < 0 when the row does not fit 8 CTAs' shared memory.
-template <typename T>
+template <typename T, bool LOG>
 int try_softmax_cluster(const T* x, T* y, int64_t outer, int64_t dim, cudaStream_t st) {
   constexpr int VN = Vec<T>::N;
   const size_t row_bytes = (size_t)dim * sizeof(T);
@@ -495,7 +536,7 @@ int try_softmax_cluster(const T* x, T* y, int64_t outer, int64_t dim, cudaStream
   int threads = 256;
   while (threads < 1024 && (int64_t)threads * VN * 16 < slice) threads <<= 1;
   const size_t smem = (size_t)slice * sizeof(T);
-  auto kern = softmax_rows_cluster_kernel<T>;
+  auto kern = softmax_rows_cluster_kernel<T, LOG>;
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxSlice) != cudaSuccess) {
     cudaGetLastError();
     return -1;
@@ -520,7 +561,7 @@ int try_softmax_cluster(const T* x, T* y, int64_t outer, int64_t dim, cudaStream
   return after_launch("softmax_rows_cluster");
 }
 
-template <typename T>
+template <typename T, bool LOG>
 int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, cudaStream_t st) {
   using A = typename AccType<T>::type;
   constexpr int VN = Vec<T>::N;
@@ -529,7 +570,7 @@ int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, c
     const int V = vec ? VN : 1;
     const int64_t nchunk = dim / V;
     if (vec && nchunk >= 64 && nchunk <= 512 * 4 && outer >= 4 * (int64_t)sm_count()) {
-      const int rc = try_softmax_pipe<T>(x, y, outer, dim, st);
+      const int rc = try_softmax_pipe<T, LOG>(x, y, outer, dim, st);
       if (rc >= 0) return rc;  // < 0: the pipeline does not fit; use the register route
     }
     if (nchunk <= 32 * 16) {
@@ -537,11 +578,11 @@ int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, c
       while (G < 32 && G < nchunk) G <<= 1;
       int C = 1;
       while ((int64_t)C * G < nchunk) C <<= 1;
-      return vec ? launch_rows_reg<T, true>(x, y, outer, (int)dim, G, C, st)
-                 : launch_rows_reg<T, false>(x, y, outer, (int)dim, G, C, st);
+      return vec ? launch_rows_reg<T, true, LOG>(x, y, outer, (int)dim, G, C, st)
+                 : launch_rows_reg<T, false, LOG>(x, y, outer, (int)dim, G, C, st);
     }
     if (vec) {
-      const int rc = try_softmax_cluster<T>(x, y, outer, dim, st);
+      const int rc = try_softmax_cluster<T, LOG>(x, y, outer, dim, st);
       if (rc >= 0) return rc;
     }
     if (outer > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "softmax: too many rows for one launch");
@@ -550,15 +591,15 @@ int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, c
       int threads = 256;
       while (threads < 1024 && (int64_t)threads * V * 8 < dim) threads <<= 1;
       if (vec) {
-        cudaFuncSetAttribute(softmax_rows_smem_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        softmax_rows_smem_kernel<T, true><<<(unsigned)outer, threads, smem, st>>>(x, y, dim);
+        cudaFuncSetAttribute(softmax_rows_smem_kernel<T, true, LOG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        softmax_rows_smem_kernel<T, true, LOG><<<(unsigned)outer, threads, smem, st>>>(x, y, dim);
       } else {
-        cudaFuncSetAttribute(softmax_rows_smem_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        softmax_rows_smem_kernel<T, false><<<(unsigned)outer, threads, smem, st>>>(x, y, dim);
+        cudaFuncSetAttribute(softmax_rows_smem_kernel<T, false, LOG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        softmax_rows_smem_kernel<T, false, LOG><<<(unsigned)outer, threads, smem, st>>>(x, y, dim);
       }
       return after_launch("softmax_rows_smem");
     }
-    softmax_rows_stream_kernel<T><<<(unsigned)outer, 1024, 0, st>>>(x, y, dim);
+    softmax_rows_stream_kernel<T, LOG><<<(unsigned)outer, 1024, 0, st>>>(x, y, dim);
     return after_launch("softmax_rows_stream");
   }
   int threads = 32;
@@ -566,15 +607,12 @@ int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, c
   const int64_t col_tiles = (inner + threads - 1) / threads;
   const int64_t blocks = col_tiles * outer;
   if (blocks > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "softmax: too many tiles for one launch");
-  softmax_cols_kernel<T><<<(unsigned)blocks, threads, 0, st>>>(x, y, dim, inner, col_tiles);
+  softmax_cols_kernel<T, LOG><<<(unsigned)blocks, threads, 0, st>>>(x, y, dim, inner, col_tiles);
   return after_launch("softmax_cols");
 }
 
-}  // namespace pdb200
-
-extern "C" int pdb200_softmax(const void* x, const int64_t* dims, int rank, int axis, int dtype,
-                              void* out, void* stream) {
-  using namespace pdb200;
+template <bool LOG>
+int softmax_entry(const void* x, const int64_t* dims, int rank, int axis, int dtype, void* out, void* stream) {
   PDB_CHECK_ARG(rank >= 0 && rank <= PDB200_MAX_RANK, "softmax: rank must be in [0, 9]");
   PDB_CHECK_ARG(rank == 0 || dims != nullptr, "softmax: dims is NULL");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
@@ -597,11 +635,11 @@ extern "C" int pdb200_softmax(const void* x, const int64_t* dims, int rank, int 
 #define PDB_SM_CASE(DT)                                                                       \
   case DT: {                                                                                  \
     using T = typename CType<DT>::type;                                                       \
-    if (rank == 0) { /* 0-D tensor: 1.0 (impl/softmax_kernel_impl.h:41-44) */                 \
-      softmax_fill_one_kernel<T><<<1, 1, 0, st>>>(static_cast<T*>(out));                      \
+    if (rank == 0) { /* 0-D tensor: softmax 1.0 (impl/softmax_kernel_impl.h:41-44), log_softmax 0.0 */ \
+      softmax_fill_one_kernel<T><<<1, 1, 0, st>>>(static_cast<T*>(out), LOG ? 0.f : 1.f);     \
       return after_launch("softmax_fill_one");                                                \
     }                                                                                         \
-    return softmax_typed<T>(static_cast<const T*>(x), static_cast<T*>(out), outer, dim, inner, st); \
+    return softmax_typed<T, LOG>(static_cast<const T*>(x), static_cast<T*>(out), outer, dim, inner, st); \
   }
   switch (dtype) {
     PDB_SM_CASE(PDB200_FLOAT32)
@@ -613,4 +651,14 @@ extern "C" int pdb200_softmax(const void* x, const int64_t* dims, int rank, int 
                                           std::to_string(dtype));
   }
 #undef PDB_SM_CASE
+}
+}  // namespace pdb200
+
+extern "C" int pdb200_softmax(const void* x, const int64_t* dims, int rank, int axis, int dtype, void* out,
+                              void* stream) {
+  return pdb200::softmax_entry<false>(x, dims, rank, axis, dtype, out, stream);
+}
+extern "C" int pdb200_log_softmax(const void* x, const int64_t* dims, int rank, int axis, int dtype, void* out,
+                                  void* stream) {
+  return pdb200::softmax_entry<true>(x, dims, rank, axis, dtype, out, stream);
 }

@@ -28,6 +28,21 @@ def softmax(x, axis=-1, dtype=None, name=None):
     return out
 
 
+def log_softmax(x, axis=-1, dtype=None, name=None):
+    """log(softmax(x)) along `axis` (python/paddle/nn/functional/activation.py: log_softmax), computed in one pass as
+    (x - max) - log(sum(exp(x - max)))."""
+    _require_cuda(x)
+    dt = _as_torch_dtype(dtype)
+    if dt is not None and dt != x.dtype:
+        raise NotImplementedError("log_softmax(dtype=...): cast first with paddle.cast")
+    lib = L.load()
+    x = x.contiguous()
+    out = torch.empty_like(x)
+    d, r = L.dims_array(x.shape)
+    L.check(lib.pdb200_log_softmax(_ptr(x), d, r, int(axis), _dtype_code(x.dtype), _ptr(out), _stream()), lib)
+    return out
+
+
 def softmax_(x, axis=-1, dtype=None, name=None):
     _require_cuda(x)
     lib = L.load()

@@ -281,6 +281,12 @@ void ArgMaxKernel(const Context& ctx, const DenseTensor& x, const phi::Scalar& a
 
 // ---- softmax -----------------------------------------------------------------------------
 template <typename T, typename Context>
+void LogSoftmaxKernel(const Context& ctx, const DenseTensor& x, int axis, DenseTensor* out) {
+  T* o = ctx.template Alloc<T>(out);
+  auto d = Dims(x);
+  Check(pdb200_log_softmax(x.data<T>(), d.data(), static_cast<int>(d.size()), axis, Code(x.dtype()), o, ctx.stream()));
+}
+template <typename T, typename Context>
 void SoftmaxKernel(const Context& ctx, const DenseTensor& x, int axis, DenseTensor* out) {
   T* o = ctx.template Alloc<T>(out);
   auto xd = Dims(x);
@@ -420,6 +426,8 @@ PD_REGISTER_KERNEL(sum_grad, GPU, ALL_LAYOUT, pdb200_phi::ReduceSumGradKernel, f
 }
 PD_REGISTER_KERNEL(mean_grad, GPU, ALL_LAYOUT, pdb200_phi::ReduceMeanGradKernel, float, double, phi::dtype::float16,
                    phi::dtype::bfloat16, int, int64_t) {}
+PD_REGISTER_KERNEL(log_softmax, GPU, ALL_LAYOUT, pdb200_phi::LogSoftmaxKernel, float, double, phi::dtype::float16,
+                   phi::dtype::bfloat16) {}  // gpu/log_softmax_kernel.cu registration
 PD_REGISTER_KERNEL(sum_raw, GPU, ALL_LAYOUT, pdb200_phi::SumRawKernel, bool, float, double, phi::dtype::float16,
                    phi::dtype::bfloat16, int, int64_t) {
   kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);  // reduce_sum_kernel.cc:75-77

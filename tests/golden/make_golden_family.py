@@ -123,6 +123,14 @@ def main():
             g[f"rgrad_{name}_{dt}__in0"] = d
             for op in ("sum", "mean"):
                 g[f"rgrad_{op}_{name}_{dt}__out"] = ref.reduce_grad(op, shape, d, axis, keep)
+    # log_softmax: test_log_softmax_op.py shapes + the softmax matrix of make_golden.py
+    for name, shape, axis in LOG_SOFTMAX_CASES:
+        for dt in ("float32", "float64"):
+            x = (rng.standard_normal(shape) * 3).astype(dt)
+            if name == "ls_clip":
+                x[..., 0] = 200.0  # everything else sits below max - 64: the clip is active
+            g[f"lsm_{name}_{dt}__in0"] = x
+            g[f"lsm_{name}_{dt}__out"] = ref.log_softmax(x, axis)
     out = os.path.join(HERE, "phi_family_golden.npz")
     np.savez_compressed(out, **g)
     print(f"wrote {out}: {len(g)} arrays, {os.path.getsize(out)} bytes")
@@ -136,6 +144,8 @@ REDUCE_GRAD_CASES = [("r2_last", (5, 6), -1, False), ("r2_first_keep", (5, 6), 0
                      ("r3_mid_keep", (5, 6, 10), 1, True), ("r3_02", (5, 6, 10), (0, 2), False), ("r4_12", (2, 5, 3, 2), (1, 2), False),
                      ("r1", (120,), 0, False), ("r3_one", (3, 1, 4), 1, False), ("r0", (), None, False),
                      ("r5", (1, 2, 5, 6, 10), 2, False), ("r2_wide", (3, 901), -1, False)]
+LOG_SOFTMAX_CASES = [("ls2", (2, 3), -1), ("ls4_m1", (2, 3, 4, 5), -1), ("ls4_0", (2, 3, 4, 5), 0), ("ls4_1", (2, 3, 4, 5), 1),
+                     ("ls4_2", (2, 3, 4, 5), 2), ("ls_2048", (6, 2048), -1), ("ls_odd", (3, 1001), -1), ("ls_clip", (4, 50), -1)]
 SCALE_ARGS = [(-2.3, 0.0, True), (-2.3, 2.3, True), (-2.3, 2.3, False), (3.0, -1.0, True), (0.0, 0.5, False)]
 
 

@@ -312,6 +312,14 @@ class Oracle:
         self._check(rc)
         return x_grad
 
+    def log_softmax(self, x, axis=-1, code=None):
+        x = np.ascontiguousarray(x)
+        code = NP2CODE[x.dtype] if code is None else code
+        out = np.empty(x.shape, x.dtype)
+        d, r = _dims(x.shape)
+        self._check(getattr(self.lib, self.p + "log_softmax")(code, _vp(x), d, r, int(axis), _vp(out)))
+        return out
+
     def _check(self, rc):
         if rc != 0:
             msg = ""

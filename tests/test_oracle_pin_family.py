@@ -153,3 +153,13 @@ def test_reduce_grad_golden_and_live(port, gold):
             d = gold[f"rgrad_{name}_{dt}__in0"]
             for op in ("sum", "mean"):
                 assert np.array_equal(port.reduce_grad(op, shape, d, axis, keep), gold[f"rgrad_{op}_{name}_{dt}__out"]), (op, name, dt)
+
+
+def test_log_softmax_golden(port, gold):
+    from golden.make_golden_family import LOG_SOFTMAX_CASES
+    for name, _, axis in LOG_SOFTMAX_CASES:
+        for dt in ("float32", "float64"):
+            x = gold[f"lsm_{name}_{dt}__in0"]
+            np.testing.assert_allclose(port.log_softmax(x, axis), gold[f"lsm_{name}_{dt}__out"],
+                                       rtol=2e-6 if dt == "float32" else 1e-12, atol=2e-6 if dt == "float32" else 1e-12)
+    assert port.log_softmax(np.array(3.0, np.float32)).item() == 0.0
