@@ -320,6 +320,11 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
     yy = torch.rand((8, 32, 2048, 2048), device="cuda", generator=g).to(torch.bfloat16)
     dyy = torch.randn((8, 32, 2048, 2048), device="cuda", generator=g).to(torch.bfloat16)
     rec("next: log_softmax bf16 [8,32,2048,2048] axis=-1", 2 * n * 2, lambda: F.log_softmax(yy, axis=-1), n)
+    xl32 = torch.randn((65536, 8192), device="cuda", generator=g)
+    lbl = torch.randint(0, 8192, (65536, 1), device="cuda", generator=g)
+    rec("next: softmax_with_cross_entropy fp32 [65536,8192] hard labels (softmax + loss)", 2 * 65536 * 8192 * 4 + 65536 * 12,
+        lambda: F.softmax_with_cross_entropy(xl32, lbl, return_softmax=True), 65536 * 8192)
+    del xl32, lbl
     rec("next: softmax_grad bf16 [8,32,2048,2048] axis=-1", 3 * n * 2, lambda: F.softmax_grad(yy, dyy, axis=-1), n)
     del yy, dyy
     rows, D = 65536, 8192

@@ -297,6 +297,22 @@ PDB200_API int pdb200_softmax(const void* x, const int64_t* dims, int rank, int 
 PDB200_API int pdb200_log_softmax(const void* x, const int64_t* dims, int rank, int axis, int dtype, void* out,
                        void* stream);
 
+/* cross_entropy_with_softmax forward.  Replaces phi::CrossEntropyWithSoftmaxKernel<T, GPUContext>
+ * (paddle/phi/kernels/gpu/cross_entropy_kernel.cu:1452-1476) with the numerics of the CPU kernel
+ * (paddle/phi/kernels/cpu/cross_entropy_kernel.cc:27-104, funcs/cross_entropy.cc:29-134).
+ * logits dims/rank, softmax along `axis` -> `softmax` (same shape; may be the logits buffer, as the op is declared
+ * in-place) and `loss` (the logits shape with the axis dimension set to 1).
+ *   soft_label == 0: label holds one class index per position (label_dtype INT64 or INT32, the logits shape with the
+ *     axis dimension 1); loss = -log(softmax[label]), 0 where label == ignore_index, NaN for an index out of range
+ *     (the reference raises there).
+ *   soft_label != 0: label has the logits shape and dtype; loss = -sum(label * log(softmax)) along the axis.
+ *   use_softmax == 0: the input already is a softmax: it is copied to `softmax` and only the loss is computed.
+ * log results of +-inf become +-1e20 (TolerableValue).  dtypes FLOAT32, FLOAT64 (the reference's float16
+ * registration stays with the in-tree kernel for now). */
+PDB200_API int pdb200_cross_entropy_with_softmax(const void* logits, const int64_t* dims, int rank, const void* label,
+                                      int label_dtype, int soft_label, int use_softmax, int ignore_index, int axis,
+                                      int dtype, void* softmax, void* loss, void* stream);
+
 /* ---------------------------------------------------------------------------
  * layer_norm forward.  Replaces phi::LayerNormKernel<T, GPUContext>
  * (paddle/phi/kernels/gpu/layer_norm_kernel.cu:490-665).

@@ -39,6 +39,7 @@ paddle/phi/backends/cpu/cpu_context.cc
 paddle/phi/backends/cpu/cpu_info.cc
 paddle/phi/kernels/funcs/math_function.cc
 paddle/phi/kernels/funcs/eigen/scale.cc
+paddle/phi/kernels/funcs/cross_entropy.cc
 "
 pids=()
 build_one() {  # $1 = source path, $2 = object

@@ -524,3 +524,52 @@ int oracle_log_softmax(int dtype, const void* x, const int64_t* dims, int rank, 
     }
   return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * cross_entropy_with_softmax.  phi::CrossEntropyWithSoftmaxKernel<T,CPUContext>
+ * (cpu/cross_entropy_kernel.cc:73-104): softmax = SoftmaxKernel(logits, axis) (oracle_softmax in phi_cpu_oracle.c), or
+ * the input itself when use_softmax is false; then CrossEntropyFunctor (funcs/cross_entropy.cc:29-134) on
+ * [n][axis_dim][remain]:
+ *   hard: loss[i][j] = label == ignore_index ? 0 : -TolerableValue(log(prob[i][label][j]))   (label: int64 here)
+ *   soft: loss[i][j] = -sum_k label[i][k][j] * TolerableValue(log(prob[i][k][j]))   (summed along k in increasing order)
+ * TolerableValue: +-inf -> +-1e20 (funcs/cross_entropy.h:28-38).  A label outside [0, axis_dim) raises in the
+ * reference: rc 3 here.  T = float or double.
+ * ---------------------------------------------------------------------------------------- */
+int oracle_softmax(int dtype, const void* x, const int64_t* dims, int rank, int axis, void* out);
+static double tol_d(double v) { return v == INFINITY ? 1e20 : (v == -INFINITY ? -1e20 : v); }
+static float tol_f(float v) { return v == INFINITY ? 1e20f : (v == -INFINITY ? -1e20f : v); }
+int oracle_cross_entropy_with_softmax(int dtype, const void* logits, const int64_t* dims, int rank, const void* label,
+                                      int soft_label, int use_softmax, int ignore_index, int axis, void* softmax,
+                                      void* loss) {
+  if (rank < 1 || axis < -rank || axis >= rank) return 1;
+  if (axis < 0) axis += rank;
+  int64_t n = 1, ad = dims[axis], rem = 1;
+  for (int i = 0; i < axis; ++i) n *= dims[i];
+  for (int i = axis + 1; i < rank; ++i) rem *= dims[i];
+  if (ad <= 0 || n <= 0) return 1;
+  const size_t es = dtype == DT_FLOAT64 ? 8 : 4;
+  if (dtype != DT_FLOAT32 && dtype != DT_FLOAT64) return 2;
+  if (use_softmax) { int rc = oracle_softmax(dtype, logits, dims, rank, axis, softmax); if (rc) return rc; }
+  else if (softmax != logits) memcpy(softmax, logits, (size_t)(n * ad * rem) * es);
+  for (int64_t i = 0; i < n; ++i)
+    for (int64_t j = 0; j < rem; ++j) {
+      const int64_t pos = i * rem + j;
+      if (soft_label) {
+        if (dtype == DT_FLOAT64) {
+          double s = 0.0;
+          for (int64_t k = 0; k < ad; ++k) s += ((const double*)label)[(i * ad + k) * rem + j] * tol_d(log(((const double*)softmax)[(i * ad + k) * rem + j]));
+          ((double*)loss)[pos] = -s;
+        } else {
+          float s = 0.f;
+          for (int64_t k = 0; k < ad; ++k) s += ((const float*)label)[(i * ad + k) * rem + j] * tol_f(logf(((const float*)softmax)[(i * ad + k) * rem + j]));
+          ((float*)loss)[pos] = -s;
+        }
+      } else {
+        const int64_t lbl = ((const int64_t*)label)[pos];
+        if (lbl != ignore_index && (lbl < 0 || lbl >= ad)) return 3;
+        if (dtype == DT_FLOAT64) ((double*)loss)[pos] = lbl == ignore_index ? 0.0 : -tol_d(log(((const double*)softmax)[(i * ad + lbl) * rem + j]));
+        else ((float*)loss)[pos] = lbl == ignore_index ? 0.f : -tol_f(logf(((const float*)softmax)[(i * ad + lbl) * rem + j]));
+      }
+    }
+  return 0;
+}

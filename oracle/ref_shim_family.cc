@@ -11,6 +11,8 @@
 //   cast         phi::CastKernel<T,CPUContext>                   paddle/phi/kernels/cpu/cast_kernel.cc, cast_impl.h
 //   where        phi::WhereKernel<T,CPUContext>                  paddle/phi/kernels/cpu/where_kernel.cc:20-36
 //   add_grad     phi::AddGradKernel<T,CPUContext>                paddle/phi/kernels/cpu/elementwise_add_grad_kernel.cc:25-62
+//   cross_entropy_with_softmax  phi::CrossEntropyWithSoftmaxKernel<T,CPUContext>
+//                paddle/phi/kernels/cpu/cross_entropy_kernel.cc:73-104 (+ funcs/cross_entropy.cc, compiled as its own TU)
 //   log_softmax  phi::LogSoftmaxKernel<T,CPUContext>             paddle/phi/kernels/cpu/log_softmax_kernel.cc:40-127
 //   sum_grad / mean_grad  phi::ReduceSumGradKernel / ReduceMeanGradKernel<T,CPUContext>
 //                paddle/phi/kernels/cpu/reduce_sum_grad_kernel.cc:26-43, cpu/reduce_mean_grad_kernel.cc
@@ -30,6 +32,7 @@
 #include "paddle/phi/kernels/cpu/bitwise_kernel.cc"  // NOLINT (kernel templates live in the .cc)
 #include "paddle/phi/kernels/cpu/cast_kernel.cc"     // NOLINT
 #include "paddle/phi/kernels/cpu/compare_kernel.cc"  // NOLINT
+#include "paddle/phi/kernels/cpu/cross_entropy_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/elementwise_add_grad_kernel.cc"       // NOLINT
 #include "paddle/phi/kernels/cpu/elementwise_multiply_grad_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/log_softmax_kernel.cc"  // NOLINT
@@ -274,6 +277,32 @@ int phi_ref_elementwise_grad(int op, int dtype, const void* x, const int64_t* xd
     // the kernels may have re-allocated an output (Alloc on a borrowed buffer keeps it when the size fits)
     if (dx && dxt.data() != dx) std::memcpy(dx, dxt.data(), static_cast<size_t>(dxt.numel()) * phi::SizeOf(dxt.dtype()));
     if (dy && dyt.data() != dy) std::memcpy(dy, dyt.data(), static_cast<size_t>(dyt.numel()) * phi::SizeOf(dyt.dtype()));
+  });
+}
+
+// label: int64 class indices (the logits shape with 1 along axis) or, with soft_label, distributions of the logits dtype
+int phi_ref_cross_entropy_with_softmax(int dtype, const void* logits, const int64_t* dims, int rank, const void* label,
+                                       const int64_t* ldims, int soft_label, int use_softmax, int ignore_index, int axis,
+                                       void* softmax, void* loss) {
+  return Guard([&] {
+    auto& ctx = GetCtx().ctx;
+    auto xt = Wrap(logits, dims, rank, dtype);
+    auto lt = Wrap(label, ldims, rank, soft_label ? dtype : kInt64);
+    auto st = Wrap(softmax, dims, rank, dtype);
+    std::vector<int64_t> od(dims, dims + rank);
+    od[axis < 0 ? axis + rank : axis] = 1;
+    auto ot = Wrap(loss, od.data(), rank, dtype);
+    switch (dtype) {
+      case kFloat32:
+        phi::CrossEntropyWithSoftmaxKernel<float, CPUContext>(ctx, xt, lt, soft_label != 0, use_softmax != 0, true, ignore_index, axis, &st, &ot);
+        break;
+      case kFloat64:
+        phi::CrossEntropyWithSoftmaxKernel<double, CPUContext>(ctx, xt, lt, soft_label != 0, use_softmax != 0, true, ignore_index, axis, &st, &ot);
+        break;
+      default: throw std::runtime_error("phi_ref_cross_entropy_with_softmax: dtype not registered on CPU");
+    }
+    if (st.data() != softmax) std::memcpy(softmax, st.data(), static_cast<size_t>(st.numel()) * phi::SizeOf(st.dtype()));
+    if (ot.data() != loss) std::memcpy(loss, ot.data(), static_cast<size_t>(ot.numel()) * phi::SizeOf(ot.dtype()));
   });
 }
 

@@ -1,0 +1,159 @@
+// cross_entropy.cu — cross_entropy_with_softmax forward: softmax along `axis` plus the
+// per-position loss, hard (index) or soft (distribution) labels.
+//
+// Replaces (fresh design): phi::CrossEntropyWithSoftmaxKernel<T, GPUContext>
+//   paddle/phi/kernels/gpu/cross_entropy_kernel.cu (registration :1452-1476)
+// with the numerics of the CPU kernel the parity oracle is built from
+//   paddle/phi/kernels/cpu/cross_entropy_kernel.cc:27-104 -> funcs/cross_entropy.cc:29-134:
+//     softmax = SoftmaxKernel(logits)                  (or a copy of the input when use_softmax is false)
+//     hard:  loss[i, j] = label == ignore_index ? 0 : -TolerableValue(log(softmax[i, label, j]))
+//     soft:  loss[i, j] = -sum_k label[i, k, j] * TolerableValue(log(softmax[i, k, j]))
+//   with x viewed as [n][axis_dim][remain] and TolerableValue mapping +-inf to +-1e20 (funcs/cross_entropy.h:28-38).
+// The softmax is this library's own kernel (every route of softmax.cu, one read + one write of the logits); a hard-label
+// loss then costs one gathered element per position, a soft-label loss one more pass over softmax and label.
+// A label outside [0, axis_dim) that is not ignore_index makes the reference raise (a device-side assert on GPU); a
+// C-ABI kernel cannot, so the loss at that position is NaN.
+#include <string>
+
+#include "common.cuh"
+#include "shape.h"
+
+namespace pdb200 {
+
+template <typename A> __device__ __forceinline__ A ce_log(A v);
+template <> __device__ __forceinline__ float ce_log<float>(float v) { return logf(v); }
+template <> __device__ __forceinline__ double ce_log<double>(double v) { return log(v); }
+template <typename A>
+__device__ __forceinline__ A tolerable(A x) {
+  if (x == std::numeric_limits<A>::infinity()) return A(1e20);
+  if (x == -std::numeric_limits<A>::infinity()) return A(-1e20);
+  return x;
+}
+
+// one thread per (i, j)
+template <typename T, typename L>
+__global__ void __launch_bounds__(256) ce_hard_kernel(const T* __restrict__ prob, const L* __restrict__ label,
+                                                      T* __restrict__ loss, int64_t n_pos, int64_t axis_dim,
+                                                      int64_t remain, int64_t ignore_index) {
+  using A = typename AccType<T>::type;
+  const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_pos) return;
+  const int64_t i = p / remain, j = p - i * remain;
+  const int64_t lbl = static_cast<int64_t>(label[p]);
+  A v;
+  if (lbl == ignore_index) v = A(0);
+  else if (lbl < 0 || lbl >= axis_dim) v = std::numeric_limits<A>::quiet_NaN();
+  else v = -tolerable<A>(ce_log<A>(cvt<A>(prob[(i * axis_dim + lbl) * remain + j])));
+  loss[p] = cvt<T>(v);
+}
+
+// remain == 1: one CTA per row, threads stride over the classes (coalesced), one block reduction
+template <typename T>
+__global__ void __launch_bounds__(256) ce_soft_rows_kernel(const T* __restrict__ prob, const T* __restrict__ label,
+                                                           T* __restrict__ loss, int64_t axis_dim) {
+  using A = typename AccType<T>::type;
+  __shared__ A red[33];
+  const T* p = prob + (int64_t)blockIdx.x * axis_dim;
+  const T* l = label + (int64_t)blockIdx.x * axis_dim;
+  A acc[2] = {A(0), A(0)};
+  int64_t k = threadIdx.x;
+  for (; k + blockDim.x < axis_dim; k += 2 * blockDim.x) {
+    acc[0] += cvt<A>(l[k]) * tolerable<A>(ce_log<A>(cvt<A>(p[k])));
+    acc[1] += cvt<A>(l[k + blockDim.x]) * tolerable<A>(ce_log<A>(cvt<A>(p[k + blockDim.x])));
+  }
+  if (k < axis_dim) acc[0] += cvt<A>(l[k]) * tolerable<A>(ce_log<A>(cvt<A>(p[k])));
+  A s = block_reduce(acc[0] + acc[1], [](A a, A b) { return a + b; }, A(0), red);
+  if (threadIdx.x == 0) loss[blockIdx.x] = cvt<T>(-s);
+}
+// remain > 1: one thread per (i, j), walking the axis with stride `remain` (neighbouring threads stay coalesced)
+template <typename T>
+__global__ void __launch_bounds__(256) ce_soft_cols_kernel(const T* __restrict__ prob, const T* __restrict__ label,
+                                                           T* __restrict__ loss, int64_t n_pos, int64_t axis_dim,
+                                                           int64_t remain) {
+  using A = typename AccType<T>::type;
+  const int64_t pos = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pos >= n_pos) return;
+  const int64_t i = pos / remain, j = pos - i * remain;
+  const int64_t base = i * axis_dim * remain + j;
+  A s = A(0);
+  for (int64_t k = 0; k < axis_dim; ++k)
+    s += cvt<A>(label[base + k * remain]) * tolerable<A>(ce_log<A>(cvt<A>(prob[base + k * remain])));
+  loss[pos] = cvt<T>(-s);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) ce_copy_kernel(const T* src, T* dst, int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) dst[i] = src[i];
+}
+
+template <typename T>
+int ce_loss(const T* prob, const void* label, int label_dtype, bool soft, int64_t n, int64_t axis_dim, int64_t remain,
+            int64_t ignore_index, T* loss, cudaStream_t st) {
+  const int64_t n_pos = n * remain;
+  const int64_t blocks = (n_pos + 255) / 256;
+  if (blocks > 0x7fffffffLL || n > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "cross_entropy: too many positions for one launch");
+  if (soft) {
+    if (remain == 1) ce_soft_rows_kernel<T><<<(unsigned)n, 256, 0, st>>>(prob, static_cast<const T*>(label), loss, axis_dim);
+    else ce_soft_cols_kernel<T><<<(unsigned)blocks, 256, 0, st>>>(prob, static_cast<const T*>(label), loss, n_pos, axis_dim, remain);
+    return after_launch("ce_soft");
+  }
+  if (label_dtype == PDB200_INT64)
+    ce_hard_kernel<T, int64_t><<<(unsigned)blocks, 256, 0, st>>>(prob, static_cast<const int64_t*>(label), loss, n_pos, axis_dim, remain, ignore_index);
+  else if (label_dtype == PDB200_INT32)
+    ce_hard_kernel<T, int32_t><<<(unsigned)blocks, 256, 0, st>>>(prob, static_cast<const int32_t*>(label), loss, n_pos, axis_dim, remain, ignore_index);
+  else
+    return fail(PDB200_UNSUPPORTED, "cross_entropy: hard labels must be int64 or int32, got dtype code " + std::to_string(label_dtype));
+  return after_launch("ce_hard");
+}
+
+}  // namespace pdb200
+
+extern "C" int pdb200_cross_entropy_with_softmax(const void* logits, const int64_t* dims, int rank, const void* label,
+                                                 int label_dtype, int soft_label, int use_softmax, int ignore_index,
+                                                 int axis, int dtype, void* softmax, void* loss, void* stream) {
+  using namespace pdb200;
+  PDB_CHECK_ARG(rank >= 1 && rank <= PDB200_MAX_RANK, "cross_entropy_with_softmax: rank must be in [1, 9]");
+  PDB_CHECK_ARG(dims != nullptr, "cross_entropy_with_softmax: dims is NULL");
+  PDB_CHECK_ARG(axis >= -rank && axis < rank, "The axis is expected to be in range of [" + std::to_string(-rank) + ", " +
+                                                  std::to_string(rank) + "), but got " + std::to_string(axis));
+  if (axis < 0) axis += rank;
+  int64_t n = 1, axis_dim = dims[axis], remain = 1;
+  for (int i = 0; i < rank; ++i) {
+    PDB_CHECK_ARG(dims[i] >= 0, "cross_entropy_with_softmax: negative dimension");
+    if (i < axis) n *= dims[i];
+    else if (i > axis) remain *= dims[i];
+  }
+  PDB_CHECK_ARG(axis_dim > 0, "The axis dimension should be larger than 0, but received axis dimension is " + std::to_string(axis_dim) + ".");
+  PDB_CHECK_ARG(n > 0, "The size of axis should be larger than 0, but received SizeToAxis of softmax is " + std::to_string(n) + ".");
+  if (remain == 0) return PDB200_OK;
+  PDB_CHECK_ARG(logits && label && softmax && loss, "cross_entropy_with_softmax: NULL tensor pointer");
+  if (soft_label && label_dtype != dtype)
+    return fail(PDB200_INVALID_ARGUMENT, "cross_entropy_with_softmax: soft labels must have the dtype of the logits");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (use_softmax) {
+    const int rc = pdb200_softmax(logits, dims, rank, axis, dtype, softmax, stream);
+    if (rc != PDB200_OK) return rc;
+  }
+  switch (dtype) {
+#define M(DT)                                                                                                       \
+  case DT: {                                                                                                        \
+    using T = typename CType<DT>::type;                                                                             \
+    if (!use_softmax && softmax != logits) { /* the input already is a softmax: hand it on (cross_entropy_kernel.cc:83-88) */ \
+      const int64_t total = n * axis_dim * remain;                                                                  \
+      const int64_t blocks = std::min<int64_t>((total + 255) / 256, (int64_t)sm_count() * 32);                      \
+      ce_copy_kernel<T><<<(unsigned)blocks, 256, 0, st>>>(static_cast<const T*>(logits), static_cast<T*>(softmax), total); \
+      const int rc = after_launch("ce_copy");                                                                       \
+      if (rc != PDB200_OK) return rc;                                                                               \
+    }                                                                                                               \
+    return ce_loss<T>(static_cast<const T*>(softmax), label, label_dtype, soft_label != 0, n, axis_dim, remain,     \
+                      ignore_index, static_cast<T*>(loss), st);                                                     \
+  }
+    // float16 (registered on GPU in the reference) is left with the in-tree kernel: -log of a probability rounded to 11
+    // bits is not a usable loss; it needs the row statistics (max, log-sum) handed from the softmax kernel to the loss.
+    M(PDB200_FLOAT32) M(PDB200_FLOAT64)
+#undef M
+  }
+  return fail(PDB200_UNSUPPORTED, "cross_entropy_with_softmax: dtype must be float32/float64, got code " + std::to_string(dtype));
+}

@@ -43,6 +43,42 @@ def log_softmax(x, axis=-1, dtype=None, name=None):
     return out
 
 
+def softmax_with_cross_entropy(logits, label, soft_label=False, ignore_index=-100, numeric_stable_mode=True,
+                               return_softmax=False, axis=-1):
+    """paddle.nn.functional.softmax_with_cross_entropy (python/paddle/nn/functional/loss.py): loss, or (loss, softmax).
+    Hard labels: integer class indices with the logits' shape except a 1 along `axis`; soft labels: distributions with
+    the logits' shape and dtype."""
+    return _cross_entropy(logits, label, soft_label, True, ignore_index, axis, return_softmax)
+
+
+def _cross_entropy(logits, label, soft_label, use_softmax, ignore_index, axis, return_softmax):
+    _require_cuda(logits, label)
+    rank = logits.dim()
+    if rank == 0:
+        raise ValueError("(InvalidArgument) cross_entropy needs at least one dimension")
+    if not -rank <= axis < rank:
+        raise ValueError(f"(InvalidArgument) The axis is expected to be in range of [{-rank}, {rank}), but got {axis}")
+    ax = axis % rank
+    lshape = tuple(1 if i == ax else d for i, d in enumerate(logits.shape))
+    if soft_label:
+        if tuple(label.shape) != tuple(logits.shape) or label.dtype != logits.dtype:
+            raise ValueError("(InvalidArgument) soft labels must have the shape and dtype of the logits")
+    else:
+        if label.dtype not in (torch.int64, torch.int32):
+            raise TypeError("(InvalidType) hard labels must be int64 or int32")
+        if tuple(label.shape) != lshape:
+            raise ValueError(f"(InvalidArgument) label has shape {tuple(label.shape)}, expected {lshape}")
+    lib = L.load()
+    logits, label = logits.contiguous(), label.contiguous()
+    sm = torch.empty_like(logits)
+    loss = torch.empty(lshape, dtype=logits.dtype, device=logits.device)
+    d, r = L.dims_array(logits.shape)
+    L.check(lib.pdb200_cross_entropy_with_softmax(_ptr(logits), d, r, _ptr(label), _dtype_code(label.dtype), int(bool(soft_label)),
+                                                  int(bool(use_softmax)), int(ignore_index), int(axis),
+                                                  _dtype_code(logits.dtype), _ptr(sm), _ptr(loss), _stream()), lib)
+    return (loss, sm) if return_softmax else loss
+
+
 def softmax_(x, axis=-1, dtype=None, name=None):
     _require_cuda(x)
     lib = L.load()

@@ -281,6 +281,17 @@ void ArgMaxKernel(const Context& ctx, const DenseTensor& x, const phi::Scalar& a
 
 // ---- softmax -----------------------------------------------------------------------------
 template <typename T, typename Context>
+void CrossEntropyWithSoftmaxKernel(const Context& ctx, const DenseTensor& logits, const DenseTensor& label, bool soft_label,
+                                   bool use_softmax, bool numeric_stable_mode, int ignore_index, int axis,
+                                   DenseTensor* softmax, DenseTensor* loss) {
+  T* sm = ctx.template Alloc<T>(softmax);
+  T* lo = ctx.template Alloc<T>(loss);
+  auto d = Dims(logits);
+  Check(pdb200_cross_entropy_with_softmax(logits.data<T>(), d.data(), static_cast<int>(d.size()), label.data(),
+                                          Code(label.dtype()), soft_label, use_softmax, ignore_index, axis,
+                                          Code(logits.dtype()), sm, lo, ctx.stream()));
+}
+template <typename T, typename Context>
 void LogSoftmaxKernel(const Context& ctx, const DenseTensor& x, int axis, DenseTensor* out) {
   T* o = ctx.template Alloc<T>(out);
   auto d = Dims(x);
@@ -426,6 +437,8 @@ PD_REGISTER_KERNEL(sum_grad, GPU, ALL_LAYOUT, pdb200_phi::ReduceSumGradKernel, f
 }
 PD_REGISTER_KERNEL(mean_grad, GPU, ALL_LAYOUT, pdb200_phi::ReduceMeanGradKernel, float, double, phi::dtype::float16,
                    phi::dtype::bfloat16, int, int64_t) {}
+// gpu/cross_entropy_kernel.cu:1460-1466 (float16 stays with the in-tree kernel)
+PD_REGISTER_KERNEL(cross_entropy_with_softmax, GPU, ALL_LAYOUT, pdb200_phi::CrossEntropyWithSoftmaxKernel, float, double) {}
 PD_REGISTER_KERNEL(log_softmax, GPU, ALL_LAYOUT, pdb200_phi::LogSoftmaxKernel, float, double, phi::dtype::float16,
                    phi::dtype::bfloat16) {}  // gpu/log_softmax_kernel.cu registration
 PD_REGISTER_KERNEL(sum_raw, GPU, ALL_LAYOUT, pdb200_phi::SumRawKernel, bool, float, double, phi::dtype::float16,

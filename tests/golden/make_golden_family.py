@@ -131,6 +131,19 @@ def main():
                 x[..., 0] = 200.0  # everything else sits below max - 64: the clip is active
             g[f"lsm_{name}_{dt}__in0"] = x
             g[f"lsm_{name}_{dt}__out"] = ref.log_softmax(x, axis)
+    # cross_entropy_with_softmax: test_softmax_with_cross_entropy_op.py (hard / soft labels, axis, ignore_index)
+    for name, shape, axis in CE_CASES:
+        ax = axis % len(shape)
+        lshape = tuple(1 if i == ax else d for i, d in enumerate(shape))
+        for dt in ("float32", "float64"):
+            x = (rng.standard_normal(shape) * 3).astype(dt)
+            hard = rng.integers(0, shape[ax], lshape)
+            hard.flat[0] = -100
+            soft = rng.random(shape).astype(dt)
+            soft /= soft.sum(axis=ax, keepdims=True)
+            g[f"ce_{name}_{dt}__in0"], g[f"ce_{name}_{dt}__in1"], g[f"ce_{name}_{dt}__in2"] = x, hard, soft
+            g[f"ce_hard_{name}_{dt}__out0"], g[f"ce_hard_{name}_{dt}__out1"] = ref.cross_entropy_with_softmax(x, hard, False, True, -100, axis)
+            g[f"ce_soft_{name}_{dt}__out0"], g[f"ce_soft_{name}_{dt}__out1"] = ref.cross_entropy_with_softmax(x, soft, True, True, -100, axis)
     out = os.path.join(HERE, "phi_family_golden.npz")
     np.savez_compressed(out, **g)
     print(f"wrote {out}: {len(g)} arrays, {os.path.getsize(out)} bytes")
@@ -146,6 +159,8 @@ REDUCE_GRAD_CASES = [("r2_last", (5, 6), -1, False), ("r2_first_keep", (5, 6), 0
                      ("r5", (1, 2, 5, 6, 10), 2, False), ("r2_wide", (3, 901), -1, False)]
 LOG_SOFTMAX_CASES = [("ls2", (2, 3), -1), ("ls4_m1", (2, 3, 4, 5), -1), ("ls4_0", (2, 3, 4, 5), 0), ("ls4_1", (2, 3, 4, 5), 1),
                      ("ls4_2", (2, 3, 4, 5), 2), ("ls_2048", (6, 2048), -1), ("ls_odd", (3, 1001), -1), ("ls_clip", (4, 50), -1)]
+CE_CASES = [("c2", (5, 7), -1), ("c3_1", (4, 6, 9), 1), ("c4_2", (3, 4, 5, 6), 2), ("c_2048", (8, 2048), -1), ("c3_0", (2, 3, 4), 0),
+            ("c4_m1", (2, 3, 4, 41), -1)]
 SCALE_ARGS = [(-2.3, 0.0, True), (-2.3, 2.3, True), (-2.3, 2.3, False), (3.0, -1.0, True), (0.0, 0.5, False)]
 
 

@@ -320,6 +320,26 @@ class Oracle:
         self._check(getattr(self.lib, self.p + "log_softmax")(code, _vp(x), d, r, int(axis), _vp(out)))
         return out
 
+    def cross_entropy_with_softmax(self, logits, label, soft_label=False, use_softmax=True, ignore_index=-100, axis=-1):
+        """-> (softmax, loss); hard labels are int64 with a 1 along `axis`."""
+        logits = np.ascontiguousarray(logits)
+        label = np.ascontiguousarray(label if soft_label else np.asarray(label, np.int64))
+        code = NP2CODE[logits.dtype]
+        ax = axis % logits.ndim
+        lshape = tuple(1 if i == ax else d for i, d in enumerate(logits.shape))
+        sm = np.empty(logits.shape, logits.dtype)
+        loss = np.empty(lshape, logits.dtype)
+        d, r = _dims(logits.shape)
+        if self.kind == "port":
+            rc = self.lib.oracle_cross_entropy_with_softmax(code, _vp(logits), d, r, _vp(label), int(soft_label), int(use_softmax),
+                                                            int(ignore_index), int(axis), _vp(sm), _vp(loss))
+        else:
+            ld, _ = _dims(label.shape)
+            rc = self.lib.phi_ref_cross_entropy_with_softmax(code, _vp(logits), d, r, _vp(label), ld, int(soft_label),
+                                                             int(use_softmax), int(ignore_index), int(axis), _vp(sm), _vp(loss))
+        self._check(rc)
+        return sm, loss
+
     def _check(self, rc):
         if rc != 0:
             msg = ""

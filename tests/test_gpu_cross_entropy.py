@@ -1,0 +1,83 @@
+"""GPU parity for cross_entropy_with_softmax through the C-ABI, against the reference CPU kernel's
+recorded outputs and the CPU oracle: softmax to the softmax bars (1e-5 float32, 1e-12 float64), loss to 1e-5 / 1e-12
+(relative, plus the same absolute term for losses near zero)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle_lib as O
+from gpu_util import to_dev, to_np
+
+pytestmark = pytest.mark.gpu
+
+import paddlepaddle_b200 as paddle  # noqa: E402
+from golden.make_golden_family import CE_CASES  # noqa: E402
+
+F = paddle.nn.functional
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "phi_family_golden.npz")
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return dict(np.load(GOLDEN))
+
+
+def test_cross_entropy_golden(gold):
+    for name, shape, axis in CE_CASES:
+        for dt in ("float32", "float64"):
+            x, hard, soft = (gold[f"ce_{name}_{dt}__in{i}"] for i in range(3))
+            tol = dict(rtol=1e-5, atol=1e-5) if dt == "float32" else dict(rtol=1e-12, atol=1e-12)
+            for kind, lbl in (("hard", hard), ("soft", soft)):
+                loss, sm = F.softmax_with_cross_entropy(to_dev(x), to_dev(lbl).reshape(lbl.shape), soft_label=kind == "soft",
+                                                        axis=axis, return_softmax=True)
+                np.testing.assert_allclose(to_np(sm), gold[f"ce_{kind}_{name}_{dt}__out0"], **tol)
+                np.testing.assert_allclose(to_np(loss), gold[f"ce_{kind}_{name}_{dt}__out1"], **tol)
+
+
+@pytest.mark.parametrize("shape,axis", [((4096, 512), -1), ((300, 32000), -1), ((64, 7, 1000), 1), ((2, 128256), -1), ((33, 5, 17), 0),
+                                        ((1000, 1), -1)])
+def test_cross_entropy_routes(port, shape, axis):
+    rng = np.random.default_rng(31)
+    ax = axis % len(shape)
+    lshape = tuple(1 if i == ax else d for i, d in enumerate(shape))
+    x = (rng.standard_normal(shape) * 3).astype(np.float32)
+    hard = rng.integers(0, shape[ax], lshape)
+    hard.flat[::7] = -1  # ignored positions
+    soft = rng.random(shape).astype(np.float32)
+    soft /= soft.sum(axis=ax, keepdims=True)
+    # yardstick: the float64 restatement (long float32 sums carry more error than the bar)
+    sm64, lh64 = port.cross_entropy_with_softmax(x.astype(np.float64), hard, False, True, -1, axis)
+    _, ls64 = port.cross_entropy_with_softmax(x.astype(np.float64), soft.astype(np.float64), True, True, -1, axis)
+    for lbl_t in (torch.int64, torch.int32):
+        loss, sm = F.softmax_with_cross_entropy(to_dev(x), to_dev(hard).reshape(lshape).to(lbl_t), ignore_index=-1, axis=axis,
+                                                return_softmax=True)
+        np.testing.assert_allclose(to_np(sm), sm64, rtol=1e-5, atol=1e-9)
+        np.testing.assert_allclose(to_np(loss), lh64, rtol=1e-5, atol=1e-5)
+    loss = F.softmax_with_cross_entropy(to_dev(x), to_dev(soft), soft_label=True, axis=axis)
+    np.testing.assert_allclose(to_np(loss), ls64, rtol=1e-5, atol=1e-5)
+    xd = x.astype(np.float64)
+    loss = F.softmax_with_cross_entropy(to_dev(xd), to_dev(hard).reshape(lshape), ignore_index=-1, axis=axis)
+    np.testing.assert_allclose(to_np(loss), lh64, rtol=1e-12, atol=1e-12)
+
+
+def test_cross_entropy_input_is_softmax_and_errors(port):
+    rng = np.random.default_rng(32)
+    x = (rng.standard_normal((50, 33)) * 2).astype(np.float32)
+    prob = port.softmax(x, -1)
+    hard = rng.integers(0, 33, (50, 1))
+    lib_loss, lib_sm = F._cross_entropy(to_dev(prob), to_dev(hard).reshape(50, 1), False, False, -100, -1, True)
+    want_sm, want_loss = port.cross_entropy_with_softmax(prob, hard, False, False, -100, -1)
+    assert np.array_equal(to_np(lib_sm), want_sm)
+    np.testing.assert_allclose(to_np(lib_loss), want_loss, rtol=1e-6, atol=1e-6)
+    bad = hard.copy()
+    bad[3, 0] = 33  # out of range: the reference raises; here the position is NaN and the rest is unaffected
+    loss = to_np(F.softmax_with_cross_entropy(to_dev(x), to_dev(bad).reshape(50, 1)))
+    assert np.isnan(loss[3, 0]) and not np.isnan(np.delete(loss, 3, 0)).any()
+    with pytest.raises(ValueError, match="label has shape"):
+        F.softmax_with_cross_entropy(to_dev(x), to_dev(hard).reshape(50))
+    with pytest.raises(TypeError):
+        F.softmax_with_cross_entropy(to_dev(x), to_dev(hard.astype(np.float32)).reshape(50, 1))
+    with pytest.raises(NotImplementedError):
+        F.softmax_with_cross_entropy(to_dev(x).to(torch.float16), to_dev(hard).reshape(50, 1))

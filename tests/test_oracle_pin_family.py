@@ -163,3 +163,17 @@ def test_log_softmax_golden(port, gold):
             np.testing.assert_allclose(port.log_softmax(x, axis), gold[f"lsm_{name}_{dt}__out"],
                                        rtol=2e-6 if dt == "float32" else 1e-12, atol=2e-6 if dt == "float32" else 1e-12)
     assert port.log_softmax(np.array(3.0, np.float32)).item() == 0.0
+
+
+def test_cross_entropy_golden(port, gold):
+    from golden.make_golden_family import CE_CASES
+    for name, _, axis in CE_CASES:
+        for dt in ("float32", "float64"):
+            x, hard, soft = (gold[f"ce_{name}_{dt}__in{i}"] for i in range(3))
+            tol = dict(rtol=2e-6, atol=2e-6) if dt == "float32" else dict(rtol=1e-12, atol=1e-12)
+            for kind, lbl in (("hard", hard), ("soft", soft)):
+                sm, loss = port.cross_entropy_with_softmax(x, lbl, kind == "soft", True, -100, axis)
+                np.testing.assert_allclose(sm, gold[f"ce_{kind}_{name}_{dt}__out0"], **tol)
+                np.testing.assert_allclose(loss, gold[f"ce_{kind}_{name}_{dt}__out1"], **tol)
+                assert loss.shape == gold[f"ce_{kind}_{name}_{dt}__out1"].shape
+            assert port.cross_entropy_with_softmax(x, hard, False, True, -100, axis)[1].flat[0] == 0  # ignore_index
