@@ -262,6 +262,7 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
 
     g = torch.Generator(device="cuda")
     g.manual_seed(100 + rank)
+    peer = None  # NVLink peer-memory exchange group, created on first use when world > 1
     # C1 sum fp32 [4096,4096] axis=-1 (67 MB: fits L2 — reported, not a steady-state number)
     x = torch.rand((4096, 4096), device="cuda", generator=g)
     rec("C1 sum fp32 [4096,4096] axis=-1 (67 MB: L2-resident between launches; 20 launches per CUDA graph replay)",
@@ -367,7 +368,34 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
                 scratch = part.clone()
                 ms = time_op(torch, lambda: dist.all_reduce(scratch, op=op), 20, 5)
                 out[-1]["allreduce_us"] = round(ms * 1e3, 2)
+                # the same exchange without NCCL: the reduction writes into this rank's NVLink-visible slot and one
+                # kernel combines all ranks' slots (csrc/peer.cu); must give the same global result
+                if peer is None:
+                    peer = pdist.PeerGroup(slot_bytes=1 << 20)
+                glob_p = (pdist.global_sum if opn == "sum" else pdist.global_max)(xr, peer=peer).reshape(1)
+                same = bool(glob_p[0] == glob[0]) if (dt == torch.int64 or opn == "max") else \
+                    bool((glob_p[0] - glob[0]).abs() <= 1e-6 * stack.abs().sum())
+                out[-1]["peer_exchange_matches_nccl"] = same
+                if not same or peer.error() != 0:
+                    raise SystemExit(f"C5 {opn} {nm}: peer exchange {glob_p.item()} != NCCL {glob.item()} (error word {peer.error()})")
+                ms = time_op(torch, lambda: peer.all_reduce(1, part.dtype, opn), 20, 5)
+                out[-1]["peer_exchange_us"] = round(ms * 1e3, 2)
         del xr
+    if world > 1:
+        # row-sharded sum(axis=0): local column sums + exchange of the [8192] vector (SURVEY §8e last row, §8f rank 4)
+        from paddlepaddle_b200 import distributed as pdist
+        xm = torch.randn((65536, 8192), device="cuda", generator=g).to(torch.bfloat16)
+        a = pdist.global_sum_axis0(xm)
+        b = pdist.global_sum_axis0(xm, peer=peer)
+        ms_n = time_op(torch, lambda: pdist.global_sum_axis0(xm), steps, warmup)
+        ms_p = time_op(torch, lambda: pdist.global_sum_axis0(xm, peer=peer), steps, warmup)
+        out.append({"op": f"next: sum(axis=0) of a row-sharded bf16 [{world}x65536, 8192] (local column sums + exchange)",
+                    "algorithmic_bytes": 65536 * 8192 * 2, "ms_with_nccl_allreduce": round(ms_n, 4),
+                    "ms_with_peer_exchange": round(ms_p, 4), "GB/s_per_gpu_with_peer_exchange": round(65536 * 8192 * 2 / ms_p / 1e6, 1),
+                    "max_abs_diff_peer_vs_nccl": float((a.float() - b.float()).abs().max())})
+        del xm
+        if peer is not None:
+            peer.close()
     return out
 
 

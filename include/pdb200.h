@@ -347,6 +347,29 @@ PDB200_API int pdb200_layer_norm_grad(const void* x, const int64_t* dims, int ra
                            int begin_norm_axis, int dtype, void* x_grad, void* scale_grad, void* bias_grad,
                            void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * The exchange step of sharded reductions over NVLink peer memory — one process per GPU.
+ * Replaces paddle.distributed.all_reduce -> ProcessGroupNCCL::AllReduce -> ncclAllReduce
+ * (paddle/fluid/distributed/collective/process_group_nccl.cc:267-297) for the small results this path exchanges.
+ * Each rank creates a window (device memory: flags + two slots of `slot_bytes`), sends its 64-byte IPC handle to the
+ * other ranks (any transport; the Python layer uses torch.distributed.all_gather once, at set-up) and opens theirs.
+ * Per call: write the local partial result into pdb200_peer_slot(window, slot_bytes, epoch) — e.g. pass it as the `out`
+ * of a reduction — then pdb200_peer_all_reduce with the same epoch on every rank (1, 2, 3, ... per window).  One kernel
+ * publishes the epoch to all peers, waits for theirs and combines all slots in rank order (bit-identical on every rank);
+ * op codes: 0 sum, 1 max, 2 min, 3 prod; accumulation in float for bf16/fp16.  The wait is bounded (~1 s): a peer that
+ * never arrives sets the error word (pdb200_peer_error != 0) instead of hanging the GPU.
+ * windows[r] = this process's mapping of rank r's window (its own window for r == rank).
+ * These entry points allocate (window_create) and synchronise (window_create, peer_error): set-up and checks only. */
+PDB200_API size_t pdb200_peer_window_bytes(size_t slot_bytes);
+PDB200_API int pdb200_peer_window_create(size_t slot_bytes, void** window, void* ipc_handle_64);
+PDB200_API int pdb200_peer_window_open(const void* ipc_handle_64, void** mapped);
+PDB200_API int pdb200_peer_window_close(void* mapped);
+PDB200_API int pdb200_peer_window_destroy(void* window);
+PDB200_API void* pdb200_peer_slot(void* window, size_t slot_bytes, unsigned long long epoch);
+PDB200_API int pdb200_peer_error(void* window);
+PDB200_API int pdb200_peer_all_reduce(int op, void* const* windows, int world, int rank, size_t slot_bytes,
+                           unsigned long long epoch, int64_t n, int dtype, void* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -10,11 +10,13 @@ Only two things on the hot path ever cross GPUs:
   * one scalar (or one (value, index) pair) per rank for full-tensor reductions: `global_*` reduce
     the local shard with the CUDA kernels and finish with a single AllReduce on the native dtype.
 """
+import ctypes
 import os
 
 import torch
 import torch.distributed as dist
 
+from . import _lib as L
 from . import ops
 
 
@@ -56,6 +58,86 @@ def all_reduce(tensor, op=ReduceOp.SUM, group=None, sync_op=True):
     return work
 
 
+class PeerGroup:
+    """All-reduce of small results over NVLink peer memory, without NCCL (csrc/peer.cu, include/pdb200.h).
+
+    Every rank owns a window of device memory (flags + two slots) that all other ranks of the node map through CUDA
+    IPC.  `slot(dtype, shape)` hands out the current slot as a tensor — pass it as the output of the local reduction —
+    and `all_reduce(n, op)` runs the one exchange kernel: publish this rank's epoch to all peers, wait for theirs,
+    combine all slots in rank order.  No host synchronisation, no staging copy; results are bit-identical on all ranks.
+    Set-up (the constructor) is collective: it exchanges the 64-byte IPC handles with one all_gather."""
+
+    _OPS = {"sum": 0, "max": 1, "min": 2, "prod": 3}
+
+    def __init__(self, slot_bytes=1 << 20):
+        if not dist.is_initialized():
+            raise RuntimeError("PeerGroup needs an initialised process group (init_parallel_env)")
+        self.lib = L.load()
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        self.slot_bytes = int(slot_bytes)
+        self.epoch = 0
+        self._window = ctypes.c_void_p()
+        handle = (ctypes.c_ubyte * 64)()
+        L.check(self.lib.pdb200_peer_window_create(self.slot_bytes, ctypes.byref(self._window), handle), self.lib)
+        mine = torch.tensor(list(handle), dtype=torch.uint8, device="cuda")
+        handles = [torch.empty_like(mine) for _ in range(self.world)]
+        dist.all_gather(handles, mine)
+        self._mapped = (ctypes.c_void_p * self.world)()
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                self._mapped[r] = self._window.value
+                continue
+            raw = (ctypes.c_ubyte * 64)(*h.cpu().tolist())
+            ptr = ctypes.c_void_p()
+            L.check(self.lib.pdb200_peer_window_open(raw, ctypes.byref(ptr)), self.lib)
+            self._mapped[r] = ptr.value
+        dist.barrier()  # every rank has mapped every window before the first exchange
+
+    def slot(self, dtype, numel):
+        """The slot of the NEXT all_reduce as a flat tensor of `numel` elements (write the local partial result here)."""
+        esize = torch.empty((), dtype=dtype).element_size()
+        if numel * esize > self.slot_bytes:
+            raise ValueError(f"(InvalidArgument) {numel} x {dtype} does not fit the {self.slot_bytes}-byte slot")
+        ptr = self.lib.pdb200_peer_slot(self._window, self.slot_bytes, self.epoch + 1)
+        return _tensor_from_ptr(ptr, numel, dtype)
+
+    def all_reduce(self, numel, dtype, op="sum", out=None):
+        """Combine the `numel` elements every rank wrote into its slot; returns a new tensor (or fills `out`)."""
+        self.epoch += 1
+        if out is None:
+            out = torch.empty(numel, dtype=dtype, device="cuda")
+        L.check(self.lib.pdb200_peer_all_reduce(self._OPS[op], self._mapped, self.world, self.rank, self.slot_bytes, self.epoch,
+                                                numel, ops._dtype_code(dtype), ctypes.c_void_p(out.data_ptr()),
+                                                ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)), self.lib)
+        return out
+
+    def error(self):
+        """Non-zero if an exchange timed out waiting for a peer (synchronises the device)."""
+        return self.lib.pdb200_peer_error(self._window)
+
+    def close(self):
+        torch.cuda.synchronize()
+        dist.barrier()
+        for r in range(self.world):
+            if r != self.rank and self._mapped[r]:
+                self.lib.pdb200_peer_window_close(ctypes.c_void_p(self._mapped[r]))
+        dist.barrier()
+        self.lib.pdb200_peer_window_destroy(self._window)
+        self._window = ctypes.c_void_p()
+
+
+class _ForeignMemory:
+    """__cuda_array_interface__ view of device memory owned by libpdb200.so (a peer window slot)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+
+
+def _tensor_from_ptr(ptr, numel, dtype):
+    esize = torch.empty((), dtype=dtype).element_size()
+    return torch.as_tensor(_ForeignMemory(ptr, numel * esize), device="cuda").view(dtype)
+
+
 def shard_rows(n_rows, rank=None, world=None):
     """Contiguous block [begin, end) of rows owned by `rank`; the first n_rows % world ranks get one extra."""
     rank = get_rank() if rank is None else rank
@@ -77,29 +159,48 @@ def combine_argmax(local_val, local_idx, shard_begin):
     return gval, cand
 
 
-def global_sum(x_shard, dtype=None):
+_LOCAL = {"sum": (L.REDUCE_SUM, ReduceOp.SUM), "max": (L.REDUCE_MAX, ReduceOp.MAX), "min": (L.REDUCE_MIN, ReduceOp.MIN),
+          "prod": (L.REDUCE_PROD, ReduceOp.PROD)}
+
+
+def _global(op_name, x_shard, peer, axis=None, out_dtype=None):
+    """Local reduction, then the exchange: through `peer` (a PeerGroup — the reduction kernel writes its result straight
+    into this rank's peer-visible slot and ONE kernel combines all ranks' slots over NVLink) or, without one, an NCCL
+    AllReduce on the native dtype."""
+    code, nccl_op = _LOCAL[op_name]
+    dt = out_dtype or x_shard.dtype
+    if op_name == "sum" and out_dtype is None and x_shard.dtype in (torch.bool, torch.int32):
+        dt = torch.int64  # SumRawInferMeta
+    if peer is not None and get_world_size() > 1:
+        n = 1 if axis is None else x_shard.shape[-1]
+        ops._reduce(code, x_shard, axis, False, dt, out=peer.slot(dt, n))
+        return peer.all_reduce(n, dt, op_name)
+    part = ops._reduce(code, x_shard, axis, False, dt).reshape(-1)
+    all_reduce(part, nccl_op)
+    return part
+
+
+def global_sum(x_shard, dtype=None, peer=None):
     """sum over a tensor whose flat elements are sharded across ranks."""
-    part = ops.sum(x_shard, dtype=dtype).reshape(1)
-    all_reduce(part, ReduceOp.SUM)
-    return part.reshape(())
+    return _global("sum", x_shard, peer, out_dtype=ops._as_torch_dtype(dtype)).reshape(())
 
 
-def global_max(x_shard):
-    part = ops.max(x_shard).reshape(1)
-    all_reduce(part, ReduceOp.MAX)
-    return part.reshape(())
+def global_max(x_shard, peer=None):
+    return _global("max", x_shard, peer).reshape(())
 
 
-def global_min(x_shard):
-    part = ops.min(x_shard).reshape(1)
-    all_reduce(part, ReduceOp.MIN)
-    return part.reshape(())
+def global_min(x_shard, peer=None):
+    return _global("min", x_shard, peer).reshape(())
 
 
-def global_prod(x_shard):
-    part = ops.prod(x_shard).reshape(1)
-    all_reduce(part, ReduceOp.PROD)
-    return part.reshape(())
+def global_prod(x_shard, peer=None):
+    return _global("prod", x_shard, peer).reshape(())
+
+
+def global_sum_axis0(x_shard, peer=None):
+    """sum(axis=0) of a matrix whose ROWS are sharded across ranks: local column sums, then the exchange of the
+    [cols] vector (SURVEY.md §8e last row / §8f rank 4)."""
+    return _global("sum", x_shard.reshape(-1, x_shard.shape[-1]), peer, axis=0)
 
 
 def global_mean(x_shard, total_numel):

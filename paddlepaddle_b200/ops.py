@@ -338,7 +338,9 @@ _REDUCE_FN = {
 }
 
 
-def _reduce(op, x, axis, keepdim, out_dtype):
+def _reduce(op, x, axis, keepdim, out_dtype, out=None):
+    """`out`: write the result into this buffer (right element count and dtype) instead of a new tensor — used by the
+    distributed layer to let the kernel write straight into a peer-visible slot."""
     _require_cuda(x)
     lib = L.load()
     x = x.contiguous()
@@ -346,7 +348,14 @@ def _reduce(op, x, axis, keepdim, out_dtype):
     if x.numel() == 0:
         raise ValueError("(InvalidArgument) Tensor need be reduced must not empty.")
     oshape = _reduced_shape(tuple(x.shape), axes, keepdim)
-    out = torch.empty(oshape, dtype=out_dtype, device=x.device)
+    if out is None:
+        out = torch.empty(oshape, dtype=out_dtype, device=x.device)
+    else:
+        n_out = 1
+        for d_ in oshape:
+            n_out *= d_
+        if out.numel() != n_out or out.dtype != out_dtype or not out.is_contiguous():
+            raise ValueError("(InvalidArgument) out must be a contiguous tensor of the result's element count and dtype")
     xd, xr = L.dims_array(x.shape)
     ad, an = L.dims_array(axes)
     reduce_all = 1 if not axes else 0
