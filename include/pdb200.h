@@ -140,6 +140,12 @@ PDB200_API int pdb200_logical(int op, const void* x, const int64_t* x_dims, int 
                    const int64_t* y_dims, int y_rank, void* out, int dtype, void* stream);
 PDB200_API int pdb200_bitwise(int op, const void* x, const int64_t* x_dims, int x_rank, const void* y,
                    const int64_t* y_dims, int y_rank, void* out, int dtype, void* stream);
+/* bitwise_left_shift / bitwise_right_shift (kps/bitwise_kernel.cu:138-156, funcs/bitwise_functors.h:51-200): out =
+ * x << y or x >> y elementwise with broadcasting; right != 0 selects the right shift, is_arithmetic != 0 the
+ * sign-filling one (a logical right shift of a signed value shifts its unsigned representation).  A count outside
+ * [0, bits) gives 0, or the sign fill for an arithmetic right shift.  dtypes: uint8, int8, int16, int32, int64. */
+PDB200_API int pdb200_bitwise_shift(int right, int is_arithmetic, const void* x, const int64_t* x_dims, int x_rank,
+                         const void* y, const int64_t* y_dims, int y_rank, void* out, int dtype, void* stream);
 
 /* ---------------------------------------------------------------------------
  * One-input maps and `where` — the callers of funcs::ElementwiseKernel.

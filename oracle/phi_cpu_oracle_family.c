@@ -573,3 +573,37 @@ int oracle_cross_entropy_with_softmax(int dtype, const void* logits, const int64
     }
   return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * bitwise_left_shift / bitwise_right_shift (funcs/bitwise_functors.h:51-200; cpu/bitwise_kernel.cc:40-78 applies the
+ * inverse functor to swapped operands when x has the lower rank — the value is x shifted by y either way).
+ *   left (arithmetic and logic alike): count outside [0, bits) -> 0, else x << y
+ *   right arithmetic: count outside -> the sign fill (-1 for negative x, 0 otherwise; uint8: 0), else x >> y
+ *   right logic: count outside -> 0, else the unsigned representation shifted (logic_shift_func for signed types)
+ * ---------------------------------------------------------------------------------------- */
+#define SHIFT_CASES(T, U, SIGNED)                                                                          \
+  {                                                                                                        \
+    const T* X = (const T*)x; const T* Y = (const T*)y; T* Q = (T*)out;                                    \
+    const int bits = (int)sizeof(T) * 8;                                                                   \
+    WALK({                                                                                                 \
+      const T a = X[xo]; const T b = Y[yo];                                                                \
+      const int bad = (SIGNED && b < 0) || (int64_t)b >= bits;                                             \
+      if (!right) Q[i] = bad ? (T)0 : (T)(U)((U)a << b);                                                   \
+      else if (is_arithmetic) Q[i] = bad ? (T)((SIGNED && a < 0) ? -1 : 0) : (T)(a >> b);                  \
+      else Q[i] = bad ? (T)0 : (T)(U)((U)a >> b);                                                          \
+    })                                                                                                     \
+  }
+int oracle_bitwise_shift(int right, int is_arithmetic, int dtype, const void* x, const int64_t* xd, int xr, const void* y,
+                         const int64_t* yd, int yr, void* out) {
+  Walk w;
+  if (walk_init(&w, xd, xr, yd, yr)) return 1;
+  switch (dtype) {
+    case DT_UINT8: SHIFT_CASES(uint8_t, uint8_t, 0) break;
+    case DT_INT8: SHIFT_CASES(int8_t, uint8_t, 1) break;
+    case DT_INT16: SHIFT_CASES(int16_t, uint16_t, 1) break;
+    case DT_INT32: SHIFT_CASES(int32_t, uint32_t, 1) break;
+    case DT_INT64: SHIFT_CASES(int64_t, uint64_t, 1) break;
+    default: return 2;
+  }
+  return 0;
+}

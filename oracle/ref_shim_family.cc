@@ -151,6 +151,30 @@ int phi_ref_bitwise(int op, int dtype, const void* x, const int64_t* xdims, int 
   });
 }
 
+// right: 0 bitwise_left_shift, 1 bitwise_right_shift (cpu/bitwise_kernel.cc:40-78)
+int phi_ref_bitwise_shift(int right, int is_arithmetic, int dtype, const void* x, const int64_t* xdims, int xrank,
+                          const void* y, const int64_t* ydims, int yrank, const int64_t* odims, int orank, void* out) {
+  return Guard([&] {
+    auto& ctx = GetCtx().ctx;
+    auto xt = Wrap(x, xdims, xrank, dtype);
+    auto yt = Wrap(y, ydims, yrank, dtype);
+    auto ot = Wrap(out, odims, orank, dtype);
+#define SH_CASE(T)                                                                                      \
+  if (right) phi::BitwiseRightShiftKernel<T, CPUContext>(ctx, xt, yt, is_arithmetic != 0, &ot);          \
+  else phi::BitwiseLeftShiftKernel<T, CPUContext>(ctx, xt, yt, is_arithmetic != 0, &ot);                 \
+  break;
+    switch (dtype) {
+      case kUInt8: SH_CASE(uint8_t)
+      case kInt8: SH_CASE(int8_t)
+      case kInt16: SH_CASE(int16_t)
+      case kInt32: SH_CASE(int32_t)
+      case kInt64: SH_CASE(int64_t)
+      default: throw std::runtime_error("phi_ref_bitwise_shift: dtype not registered on CPU");
+    }
+#undef SH_CASE
+  });
+}
+
 // which: 0 logical_not (out bool), 1 bitwise_not (out dtype)
 int phi_ref_not(int which, int dtype, const void* x, int64_t numel, void* out) {
   return Guard([&] {

@@ -39,6 +39,7 @@ SIGNATURES = {
     "pdb200_compare": (_int, [_int, _vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
     "pdb200_logical": (_int, [_int, _vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
     "pdb200_bitwise": (_int, [_int, _vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
+    "pdb200_bitwise_shift": (_int, [_int, _int, _vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp]),
     "pdb200_logical_not": (_int, [_vp, ctypes.c_int64, _int, _vp, _vp]),
     "pdb200_bitwise_not": (_int, [_vp, ctypes.c_int64, _int, _vp, _vp]),
     "pdb200_scale": (_int, [_vp, ctypes.c_int64, _int, ctypes.c_double, ctypes.c_double, _int, _vp, _vp]),

@@ -8,6 +8,8 @@
 // Same launcher and kernels as add/multiply (elementwise_impl.cuh); compare and logical write one bool per
 // element, so a thread that loads 16 bytes of each operand stores a 2/4/8/16-byte pack of bools and a warp's
 // store is still one contiguous run.
+#include <type_traits>
+
 #include "elementwise_impl.cuh"
 
 namespace pdb200 {
@@ -102,7 +104,42 @@ template <> struct BitXorOp<bool> {
   static __device__ __forceinline__ bool apply(bool a, bool b) { return a != b; }
 };
 
+// ---- shifts (funcs/bitwise_functors.h:51-200): a shift count outside [0, bits) gives 0 — or, for an arithmetic right
+// shift of a signed value, the sign fill; a logical right shift of a signed value shifts its unsigned representation
+template <typename T>
+__device__ __forceinline__ bool bad_count(T b) {
+  if constexpr (std::is_signed<T>::value) return b < T(0) || b >= T(sizeof(T) * 8);
+  else return b >= T(sizeof(T) * 8);
+}
+template <typename T>
+__device__ __forceinline__ bool is_negative(T a) {
+  if constexpr (std::is_signed<T>::value) return a < T(0);
+  else return false;
+}
+template <typename T> struct ShlOp {
+  static __device__ __forceinline__ T apply(T a, T b) {
+    using U = typename std::make_unsigned<T>::type;
+    if (bad_count(b)) return T(0);
+    return static_cast<T>(static_cast<U>(static_cast<U>(a) << b));
+  }
+};
+template <typename T> struct ShrArithOp {
+  static __device__ __forceinline__ T apply(T a, T b) {
+    if (bad_count(b)) return is_negative(a) ? T(-1) : T(0);
+    return static_cast<T>(a >> b);
+  }
+};
+template <typename T> struct ShrLogicOp {
+  static __device__ __forceinline__ T apply(T a, T b) {
+    using U = typename std::make_unsigned<T>::type;
+    if (bad_count(b)) return T(0);
+    return static_cast<T>(static_cast<U>(static_cast<U>(a) >> b));
+  }
+};
+
 #define B(dt) (1u << (dt))
+constexpr uint32_t kShiftTypes = B(PDB200_UINT8) | B(PDB200_INT8) | B(PDB200_INT16) | B(PDB200_INT32) |
+                                 B(PDB200_INT64);  // bitwise_kernel.cu:138-156
 constexpr uint32_t kAllTypes = (1u << (PDB200_FLOAT64 + 1)) - 1;                      // compare_kernel.cu:157-173
 constexpr uint32_t kLogicalTypes = kAllTypes & ~B(PDB200_UINT8);                      // logical_kernel.cu:112-129
 constexpr uint32_t kBitwiseTypes = B(PDB200_BOOL) | B(PDB200_UINT8) | B(PDB200_INT8) | B(PDB200_INT16) |
@@ -165,6 +202,16 @@ int pdb200_bitwise(int op, const void* x, const int64_t* x_dims, int x_rank, con
       return fail(PDB200_INVALID_ARGUMENT, "bitwise: unknown op code " + std::to_string(op) +
                                                " (bitwise_not is unary: pdb200_bitwise_not)");
   }
+}
+
+int pdb200_bitwise_shift(int right, int is_arithmetic, const void* x, const int64_t* x_dims, int x_rank, const void* y,
+                         const int64_t* y_dims, int y_rank, void* out, int dtype, void* stream) {
+  using namespace pdb200;
+  if (!right)  // the arithmetic and the logical left shift are the same function
+    return elementwise_entry<ShlOp, kShiftTypes>("bitwise_left_shift", x, x_dims, x_rank, y, y_dims, y_rank, out, dtype, stream);
+  if (is_arithmetic)
+    return elementwise_entry<ShrArithOp, kShiftTypes>("bitwise_right_shift", x, x_dims, x_rank, y, y_dims, y_rank, out, dtype, stream);
+  return elementwise_entry<ShrLogicOp, kShiftTypes>("bitwise_right_shift", x, x_dims, x_rank, y, y_dims, y_rank, out, dtype, stream);
 }
 
 }  // extern "C"

@@ -105,7 +105,7 @@ def _elementwise(fn_name, x, y, out=None, op=None, out_dtype=None):
     elif tuple(out.shape) != oshape:
         # test_elementwise_add_op.py:695-720 (inplace broadcast errors)
         raise ValueError(f"(InvalidArgument) The shape of tensor assigned value must be the same: {tuple(out.shape)} vs {oshape}")
-    lead = () if op is None else (op,)
+    lead = () if op is None else (tuple(op) if isinstance(op, tuple) else (op,))
     L.check(getattr(lib, fn_name)(*lead, _ptr(x), xd, xr, _ptr(y), yd, yr, _ptr(out), _dtype_code(x.dtype), _stream()),
             lib)
     return out
@@ -199,6 +199,16 @@ def bitwise_or(x, y, out=None, name=None):
 
 def bitwise_xor(x, y, out=None, name=None):
     return _elementwise("pdb200_bitwise", x, y, out=out, op=L.BITWISE_XOR)
+
+
+def bitwise_left_shift(x, y, is_arithmetic=True, out=None, name=None):
+    """paddle.bitwise_left_shift (python/paddle/tensor/math.py): x << y; counts outside [0, bits) give 0."""
+    return _elementwise("pdb200_bitwise_shift", x, y, out=out, op=(0, int(bool(is_arithmetic))))
+
+
+def bitwise_right_shift(x, y, is_arithmetic=True, out=None, name=None):
+    """paddle.bitwise_right_shift: sign-filling when is_arithmetic, else a shift of the unsigned representation."""
+    return _elementwise("pdb200_bitwise_shift", x, y, out=out, op=(1, int(bool(is_arithmetic))))
 
 
 # ---------------------------------------------------------------------------------------

@@ -124,6 +124,24 @@ PDB200_PHI_CODED(BitwiseOr, T, pdb200_bitwise, PDB200_BITWISE_OR)
 PDB200_PHI_CODED(BitwiseXor, T, pdb200_bitwise, PDB200_BITWISE_XOR)
 #undef PDB200_PHI_CODED
 
+// shifts (kps/bitwise_kernel.cu:55-67 with the functors of funcs/bitwise_functors.h:51-200)
+template <typename T, typename Context>
+void BitwiseLeftShiftKernel(const Context& ctx, const DenseTensor& x, const DenseTensor& y, bool is_arithmetic,
+                            DenseTensor* out) {
+  T* o = ctx.template Alloc<T>(out);
+  auto xd = Dims(x), yd = Dims(y);
+  Check(pdb200_bitwise_shift(0, is_arithmetic, x.data<T>(), xd.data(), static_cast<int>(xd.size()), y.data<T>(), yd.data(),
+                             static_cast<int>(yd.size()), o, Code(x.dtype()), ctx.stream()));
+}
+template <typename T, typename Context>
+void BitwiseRightShiftKernel(const Context& ctx, const DenseTensor& x, const DenseTensor& y, bool is_arithmetic,
+                             DenseTensor* out) {
+  T* o = ctx.template Alloc<T>(out);
+  auto xd = Dims(x), yd = Dims(y);
+  Check(pdb200_bitwise_shift(1, is_arithmetic, x.data<T>(), xd.data(), static_cast<int>(xd.size()), y.data<T>(), yd.data(),
+                             static_cast<int>(yd.size()), o, Code(x.dtype()), ctx.stream()));
+}
+
 // ---- one-input maps and where (kps/logical_kernel.cu:71-91, kps/bitwise_kernel.cu:69-80, gpu/scale_kernel.cu:45-65,
 //      gpu/cast_kernel.cu:25-41, gpu/where_kernel.cu:32-46)
 template <typename T, typename Context>
@@ -416,6 +434,10 @@ PD_REGISTER_KERNEL(bitwise_xor, GPU, ALL_LAYOUT, pdb200_phi::BitwiseXorKernel, b
                    int64_t) {}
 PD_REGISTER_KERNEL(bitwise_not, GPU, ALL_LAYOUT, pdb200_phi::BitwiseNotKernel, bool, uint8_t, int8_t, int16_t, int,
                    int64_t) {}
+PD_REGISTER_KERNEL(bitwise_left_shift, GPU, ALL_LAYOUT, pdb200_phi::BitwiseLeftShiftKernel, uint8_t, int8_t, int16_t, int,
+                   int64_t) {}
+PD_REGISTER_KERNEL(bitwise_right_shift, GPU, ALL_LAYOUT, pdb200_phi::BitwiseRightShiftKernel, uint8_t, int8_t, int16_t,
+                   int, int64_t) {}
 // gpu/scale_kernel.cu:67-83, gpu/cast_kernel.cu:43-66, gpu/where_kernel.cu:48-57 (complex and float8 stay in-tree)
 PD_REGISTER_KERNEL(scale, GPU, ALL_LAYOUT, pdb200_phi::ScaleKernel, bool, float, double, phi::dtype::float16,
                    phi::dtype::bfloat16, uint8_t, int8_t, int16_t, int, int64_t) {}

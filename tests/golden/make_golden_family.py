@@ -144,6 +144,16 @@ def main():
             g[f"ce_{name}_{dt}__in0"], g[f"ce_{name}_{dt}__in1"], g[f"ce_{name}_{dt}__in2"] = x, hard, soft
             g[f"ce_hard_{name}_{dt}__out0"], g[f"ce_hard_{name}_{dt}__out1"] = ref.cross_entropy_with_softmax(x, hard, False, True, -100, axis)
             g[f"ce_soft_{name}_{dt}__out0"], g[f"ce_soft_{name}_{dt}__out1"] = ref.cross_entropy_with_softmax(x, soft, True, True, -100, axis)
+    # shifts: test_bitwise_op.py (TestBitwiseLeftShift / RightShift, arithmetic and logic), counts in and out of range
+    for name, xs, ys in SHIFT_CASES:
+        for dt in ("uint8", "int8", "int16", "int32", "int64"):
+            info = np.iinfo(dt)
+            x = rng.integers(info.min, info.max, xs, dtype=dt, endpoint=True)
+            y = rng.integers(0 if dt == "uint8" else -3, info.bits + 3, ys).astype(dt)
+            g[f"sh_{name}_{dt}__in0"], g[f"sh_{name}_{dt}__in1"] = x, y
+            for right in (0, 1):
+                for ar in (0, 1):
+                    g[f"sh_{name}_{dt}_{right}{ar}__out"] = ref.bitwise_shift(right, x, y, bool(ar))
     out = os.path.join(HERE, "phi_family_golden.npz")
     np.savez_compressed(out, **g)
     print(f"wrote {out}: {len(g)} arrays, {os.path.getsize(out)} bytes")
@@ -161,6 +171,8 @@ LOG_SOFTMAX_CASES = [("ls2", (2, 3), -1), ("ls4_m1", (2, 3, 4, 5), -1), ("ls4_0"
                      ("ls4_2", (2, 3, 4, 5), 2), ("ls_2048", (6, 2048), -1), ("ls_odd", (3, 1001), -1), ("ls_clip", (4, 50), -1)]
 CE_CASES = [("c2", (5, 7), -1), ("c3_1", (4, 6, 9), 1), ("c4_2", (3, 4, 5, 6), 2), ("c_2048", (8, 2048), -1), ("c3_0", (2, 3, 4), 0),
             ("c4_m1", (2, 3, 4, 41), -1)]
+SHIFT_CASES = [("same", (13, 17), (13, 17)), ("vec_last", (2, 10, 12), (12,)), ("x_small", (10, 12), (2, 2, 10, 12)),
+               ("four", (10, 3, 1, 4), (10, 1, 12, 1)), ("scalar0d", (3, 4), ())]
 SCALE_ARGS = [(-2.3, 0.0, True), (-2.3, 2.3, True), (-2.3, 2.3, False), (3.0, -1.0, True), (0.0, 0.5, False)]
 
 

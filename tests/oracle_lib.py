@@ -231,6 +231,22 @@ class Oracle:
     def bitwise(self, op, x, y):
         return self._binary_coded("bitwise", ["and", "or", "xor"].index(op), x, y, None, None)
 
+    def bitwise_shift(self, right, x, y, is_arithmetic=True):
+        x = np.ascontiguousarray(x)
+        y = np.ascontiguousarray(y)
+        oshape = np.broadcast_shapes(x.shape, y.shape)
+        out = np.empty(oshape, x.dtype)
+        xd, xr = _dims(x.shape)
+        yd, yr = _dims(y.shape)
+        if self.kind == "port":
+            rc = self.lib.oracle_bitwise_shift(int(right), int(is_arithmetic), NP2CODE[x.dtype], _vp(x), xd, xr, _vp(y), yd, yr, _vp(out))
+        else:
+            od, orank = _dims(oshape)
+            rc = self.lib.phi_ref_bitwise_shift(int(right), int(is_arithmetic), NP2CODE[x.dtype], _vp(x), xd, xr, _vp(y), yd, yr,
+                                                od, orank, _vp(out))
+        self._check(rc)
+        return out
+
     def logical_not(self, x, code=None):
         x = np.ascontiguousarray(x)
         code = NP2CODE[x.dtype] if code is None else code

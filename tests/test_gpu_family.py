@@ -192,6 +192,26 @@ def test_where_all_sizes(port):
     assert np.array_equal(to_np(paddle.where(to_dev(c), to_dev(xb, "bf16"), to_dev(yb, "bf16"))), np.where(c, xb, yb))
 
 
+def test_bitwise_shift_golden_and_routes(port, gold):
+    from golden.make_golden_family import SHIFT_CASES
+    fns = {0: paddle.bitwise_left_shift, 1: paddle.bitwise_right_shift}
+    for name, _, _ in SHIFT_CASES:
+        for dt in ("uint8", "int8", "int16", "int32", "int64"):
+            x, y = to_dev(gold[f"sh_{name}_{dt}__in0"]), to_dev(gold[f"sh_{name}_{dt}__in1"])
+            for right in (0, 1):
+                for ar in (0, 1):
+                    assert np.array_equal(to_np(fns[right](x, y, is_arithmetic=bool(ar))), gold[f"sh_{name}_{dt}_{right}{ar}__out"])
+    rng = np.random.default_rng(9)
+    for xs, ys in ROUTES[:8]:
+        for dt in (np.int32, np.int64, np.uint8):
+            info = np.iinfo(dt)
+            x = rng.integers(info.min, info.max, xs, dtype=dt, endpoint=True)
+            y = rng.integers(0 if dt == np.uint8 else -2, info.bits + 2, ys).astype(dt)
+            for right in (0, 1):
+                for ar in (True, False):
+                    assert np.array_equal(to_np(fns[right](to_dev(x), to_dev(y), is_arithmetic=ar)), port.bitwise_shift(right, x, y, ar))
+
+
 def test_family_errors():
     x = torch.zeros(4, 5, device="cuda")
     with pytest.raises(ValueError, match="Broadcast dimension mismatch|broadcast"):

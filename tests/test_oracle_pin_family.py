@@ -177,3 +177,13 @@ def test_cross_entropy_golden(port, gold):
                 np.testing.assert_allclose(loss, gold[f"ce_{kind}_{name}_{dt}__out1"], **tol)
                 assert loss.shape == gold[f"ce_{kind}_{name}_{dt}__out1"].shape
             assert port.cross_entropy_with_softmax(x, hard, False, True, -100, axis)[1].flat[0] == 0  # ignore_index
+
+
+def test_bitwise_shift_golden(port, gold):
+    from golden.make_golden_family import SHIFT_CASES
+    for name, _, _ in SHIFT_CASES:
+        for dt in ("uint8", "int8", "int16", "int32", "int64"):
+            x, y = gold[f"sh_{name}_{dt}__in0"], gold[f"sh_{name}_{dt}__in1"]
+            for right in (0, 1):
+                for ar in (0, 1):
+                    assert np.array_equal(port.bitwise_shift(right, x, y, bool(ar)), gold[f"sh_{name}_{dt}_{right}{ar}__out"]), (name, dt, right, ar)

@@ -67,6 +67,7 @@ EXPECT = {  # the registrations of plugin/phi_kernels.cc
     **{n: "float32 float16 bfloat16 float64 bool int64 int32 int8 int16"
        for n in ("logical_and", "logical_or", "logical_xor", "logical_not")},
     **{n: "bool uint8 int8 int16 int32 int64" for n in ("bitwise_and", "bitwise_or", "bitwise_xor", "bitwise_not")},
+    "bitwise_left_shift": "uint8 int8 int16 int32 int64", "bitwise_right_shift": "uint8 int8 int16 int32 int64",
     "scale": "bool float32 float64 float16 bfloat16 uint8 int8 int16 int32 int64",
     "cast": "float32 float64 int32 int64 int16 bool int8 uint8 float16 bfloat16",
     "where": "float32 float64 int32 int64 float16 bfloat16",
