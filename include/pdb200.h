@@ -313,11 +313,16 @@ PDB200_API int pdb200_log_softmax(const void* x, const int64_t* dims, int rank, 
  *     (the reference raises there).
  *   soft_label != 0: label has the logits shape and dtype; loss = -sum(label * log(softmax)) along the axis.
  *   use_softmax == 0: the input already is a softmax: it is copied to `softmax` and only the loss is computed.
- * log results of +-inf become +-1e20 (TolerableValue).  dtypes FLOAT32, FLOAT64 (the reference's float16
- * registration stays with the in-tree kernel for now). */
+ * The loss is computed in float (double for FLOAT64) from the logits and the two statistics of each row (max, log of the
+ * sum) that the softmax kernel hands over through `workspace` (pdb200_cross_entropy_workspace_bytes; 16-byte aligned):
+ * log softmax[k] = max(x[k] - max, -64) - log(sum).  Without use_softmax, or when `softmax` is the logits buffer, the
+ * loss is -log of the stored probability (+-inf become +-1e20, TolerableValue) and no workspace is needed.
+ * dtypes FLOAT32, FLOAT64, FLOAT16 (the reference's GPU registrations) and BFLOAT16. */
+PDB200_API size_t pdb200_cross_entropy_workspace_bytes(const int64_t* dims, int rank, int axis, int dtype);
 PDB200_API int pdb200_cross_entropy_with_softmax(const void* logits, const int64_t* dims, int rank, const void* label,
                                       int label_dtype, int soft_label, int use_softmax, int ignore_index, int axis,
-                                      int dtype, void* softmax, void* loss, void* stream);
+                                      int dtype, void* softmax, void* loss, void* workspace, size_t workspace_bytes,
+                                      void* stream);
 
 /* ---------------------------------------------------------------------------
  * layer_norm forward.  Replaces phi::LayerNormKernel<T, GPUContext>

@@ -9,8 +9,13 @@
 //     hard:  loss[i, j] = label == ignore_index ? 0 : -TolerableValue(log(softmax[i, label, j]))
 //     soft:  loss[i, j] = -sum_k label[i, k, j] * TolerableValue(log(softmax[i, k, j]))
 //   with x viewed as [n][axis_dim][remain] and TolerableValue mapping +-inf to +-1e20 (funcs/cross_entropy.h:28-38).
-// The softmax is this library's own kernel (every route of softmax.cu, one read + one write of the logits); a hard-label
-// loss then costs one gathered element per position, a soft-label loss one more pass over softmax and label.
+// The softmax is this library's own kernel (every route of softmax.cu, one read + one write of the logits), which also
+// hands out the two statistics of every row, max and log(sum) (softmax_with_stats).  The loss is built from those and
+// the LOGITS in the accumulator type:  log(softmax[k]) = max(x[k] - max, -64) - log(sum)  — the same quantity the CPU
+// kernel gets by taking the log of its stored probability, without the detour through a probability rounded to the
+// tensor dtype (which makes a float16 loss useless: 11 bits, subnormal probabilities).  A hard-label loss costs one
+// gathered logit per position, a soft-label loss one pass over logits and labels.  When `softmax` is the logits
+// buffer itself (the op is declared in-place) the logits are gone by then and the loss falls back to log(softmax).
 // A label outside [0, axis_dim) that is not ignore_index makes the reference raise (a device-side assert on GPU); a
 // C-ABI kernel cannot, so the loss at that position is NaN.
 #include <string>
@@ -30,11 +35,26 @@ __device__ __forceinline__ A tolerable(A x) {
   return x;
 }
 
+// log(softmax[k]) for one element: from the logits and the row statistics (FROM_LOGITS), or from the stored probability
+template <typename T, bool FROM_LOGITS>
+__device__ __forceinline__ typename AccType<T>::type log_prob(const T* __restrict__ src, int64_t idx,
+                                                              const typename AccType<T>::type* __restrict__ stats,
+                                                              int64_t pos) {
+  using A = typename AccType<T>::type;
+  if constexpr (FROM_LOGITS) {
+    A d = cvt<A>(src[idx]) - stats[2 * pos];
+    d = d < A(-64) ? A(-64) : d;  // ValueClip of the softmax (funcs/softmax_impl.h:36-42)
+    return d - stats[2 * pos + 1];
+  } else {
+    return tolerable<A>(ce_log<A>(cvt<A>(src[idx])));
+  }
+}
+
 // one thread per (i, j)
-template <typename T, typename L>
-__global__ void __launch_bounds__(256) ce_hard_kernel(const T* __restrict__ prob, const L* __restrict__ label,
-                                                      T* __restrict__ loss, int64_t n_pos, int64_t axis_dim,
-                                                      int64_t remain, int64_t ignore_index) {
+template <typename T, typename L, bool FROM_LOGITS>
+__global__ void __launch_bounds__(256) ce_hard_kernel(const T* __restrict__ src, const typename AccType<T>::type* __restrict__ stats,
+                                                      const L* __restrict__ label, T* __restrict__ loss, int64_t n_pos,
+                                                      int64_t axis_dim, int64_t remain, int64_t ignore_index) {
   using A = typename AccType<T>::type;
   const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= n_pos) return;
@@ -43,33 +63,32 @@ __global__ void __launch_bounds__(256) ce_hard_kernel(const T* __restrict__ prob
   A v;
   if (lbl == ignore_index) v = A(0);
   else if (lbl < 0 || lbl >= axis_dim) v = std::numeric_limits<A>::quiet_NaN();
-  else v = -tolerable<A>(ce_log<A>(cvt<A>(prob[(i * axis_dim + lbl) * remain + j])));
+  else v = -log_prob<T, FROM_LOGITS>(src, (i * axis_dim + lbl) * remain + j, stats, p);
   loss[p] = cvt<T>(v);
 }
 
 // remain == 1: one CTA per row, threads stride over the classes (coalesced), one block reduction
-template <typename T>
-__global__ void __launch_bounds__(256) ce_soft_rows_kernel(const T* __restrict__ prob, const T* __restrict__ label,
-                                                           T* __restrict__ loss, int64_t axis_dim) {
+template <typename T, bool FROM_LOGITS>
+__global__ void __launch_bounds__(256) ce_soft_rows_kernel(const T* __restrict__ src, const typename AccType<T>::type* __restrict__ stats,
+                                                           const T* __restrict__ label, T* __restrict__ loss, int64_t axis_dim) {
   using A = typename AccType<T>::type;
   __shared__ A red[33];
-  const T* p = prob + (int64_t)blockIdx.x * axis_dim;
-  const T* l = label + (int64_t)blockIdx.x * axis_dim;
+  const int64_t row = blockIdx.x, base = row * axis_dim;
   A acc[2] = {A(0), A(0)};
   int64_t k = threadIdx.x;
   for (; k + blockDim.x < axis_dim; k += 2 * blockDim.x) {
-    acc[0] += cvt<A>(l[k]) * tolerable<A>(ce_log<A>(cvt<A>(p[k])));
-    acc[1] += cvt<A>(l[k + blockDim.x]) * tolerable<A>(ce_log<A>(cvt<A>(p[k + blockDim.x])));
+    acc[0] += cvt<A>(label[base + k]) * log_prob<T, FROM_LOGITS>(src, base + k, stats, row);
+    acc[1] += cvt<A>(label[base + k + blockDim.x]) * log_prob<T, FROM_LOGITS>(src, base + k + blockDim.x, stats, row);
   }
-  if (k < axis_dim) acc[0] += cvt<A>(l[k]) * tolerable<A>(ce_log<A>(cvt<A>(p[k])));
+  if (k < axis_dim) acc[0] += cvt<A>(label[base + k]) * log_prob<T, FROM_LOGITS>(src, base + k, stats, row);
   A s = block_reduce(acc[0] + acc[1], [](A a, A b) { return a + b; }, A(0), red);
-  if (threadIdx.x == 0) loss[blockIdx.x] = cvt<T>(-s);
+  if (threadIdx.x == 0) loss[row] = cvt<T>(-s);
 }
 // remain > 1: one thread per (i, j), walking the axis with stride `remain` (neighbouring threads stay coalesced)
-template <typename T>
-__global__ void __launch_bounds__(256) ce_soft_cols_kernel(const T* __restrict__ prob, const T* __restrict__ label,
-                                                           T* __restrict__ loss, int64_t n_pos, int64_t axis_dim,
-                                                           int64_t remain) {
+template <typename T, bool FROM_LOGITS>
+__global__ void __launch_bounds__(256) ce_soft_cols_kernel(const T* __restrict__ src, const typename AccType<T>::type* __restrict__ stats,
+                                                           const T* __restrict__ label, T* __restrict__ loss, int64_t n_pos,
+                                                           int64_t axis_dim, int64_t remain) {
   using A = typename AccType<T>::type;
   const int64_t pos = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (pos >= n_pos) return;
@@ -77,7 +96,7 @@ __global__ void __launch_bounds__(256) ce_soft_cols_kernel(const T* __restrict__
   const int64_t base = i * axis_dim * remain + j;
   A s = A(0);
   for (int64_t k = 0; k < axis_dim; ++k)
-    s += cvt<A>(label[base + k * remain]) * tolerable<A>(ce_log<A>(cvt<A>(prob[base + k * remain])));
+    s += cvt<A>(label[base + k * remain]) * log_prob<T, FROM_LOGITS>(src, base + k * remain, stats, pos);
   loss[pos] = cvt<T>(-s);
 }
 
@@ -88,31 +107,48 @@ __global__ void __launch_bounds__(256) ce_copy_kernel(const T* src, T* dst, int6
   for (; i < n; i += stride) dst[i] = src[i];
 }
 
-template <typename T>
-int ce_loss(const T* prob, const void* label, int label_dtype, bool soft, int64_t n, int64_t axis_dim, int64_t remain,
-            int64_t ignore_index, T* loss, cudaStream_t st) {
+template <typename T, bool FROM_LOGITS>
+int ce_loss(const T* src, const typename AccType<T>::type* stats, const void* label, int label_dtype, bool soft, int64_t n,
+            int64_t axis_dim, int64_t remain, int64_t ignore_index, T* loss, cudaStream_t st) {
   const int64_t n_pos = n * remain;
   const int64_t blocks = (n_pos + 255) / 256;
   if (blocks > 0x7fffffffLL || n > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "cross_entropy: too many positions for one launch");
   if (soft) {
-    if (remain == 1) ce_soft_rows_kernel<T><<<(unsigned)n, 256, 0, st>>>(prob, static_cast<const T*>(label), loss, axis_dim);
-    else ce_soft_cols_kernel<T><<<(unsigned)blocks, 256, 0, st>>>(prob, static_cast<const T*>(label), loss, n_pos, axis_dim, remain);
+    const T* l = static_cast<const T*>(label);
+    if (remain == 1) ce_soft_rows_kernel<T, FROM_LOGITS><<<(unsigned)n, 256, 0, st>>>(src, stats, l, loss, axis_dim);
+    else ce_soft_cols_kernel<T, FROM_LOGITS><<<(unsigned)blocks, 256, 0, st>>>(src, stats, l, loss, n_pos, axis_dim, remain);
     return after_launch("ce_soft");
   }
   if (label_dtype == PDB200_INT64)
-    ce_hard_kernel<T, int64_t><<<(unsigned)blocks, 256, 0, st>>>(prob, static_cast<const int64_t*>(label), loss, n_pos, axis_dim, remain, ignore_index);
+    ce_hard_kernel<T, int64_t, FROM_LOGITS><<<(unsigned)blocks, 256, 0, st>>>(src, stats, static_cast<const int64_t*>(label), loss, n_pos, axis_dim, remain, ignore_index);
   else if (label_dtype == PDB200_INT32)
-    ce_hard_kernel<T, int32_t><<<(unsigned)blocks, 256, 0, st>>>(prob, static_cast<const int32_t*>(label), loss, n_pos, axis_dim, remain, ignore_index);
+    ce_hard_kernel<T, int32_t, FROM_LOGITS><<<(unsigned)blocks, 256, 0, st>>>(src, stats, static_cast<const int32_t*>(label), loss, n_pos, axis_dim, remain, ignore_index);
   else
     return fail(PDB200_UNSUPPORTED, "cross_entropy: hard labels must be int64 or int32, got dtype code " + std::to_string(label_dtype));
   return after_launch("ce_hard");
 }
 
+int softmax_with_stats(const void* x, const int64_t* dims, int rank, int axis, int dtype, void* out, void* stats, void* stream);
+
+inline size_t ce_stats_bytes(int64_t n_pos, int dtype) {
+  return (size_t)n_pos * 2 * (dtype == PDB200_FLOAT64 ? sizeof(double) : sizeof(float));
+}
+
 }  // namespace pdb200
+
+extern "C" size_t pdb200_cross_entropy_workspace_bytes(const int64_t* dims, int rank, int axis, int dtype) {
+  if (rank < 1 || rank > PDB200_MAX_RANK || dims == nullptr || axis < -rank || axis >= rank) return 0;
+  if (axis < 0) axis += rank;
+  int64_t n_pos = 1;
+  for (int i = 0; i < rank; ++i)
+    if (i != axis) n_pos *= dims[i] < 0 ? 0 : dims[i];
+  return (pdb200::ce_stats_bytes(n_pos, dtype) + 255) / 256 * 256;
+}
 
 extern "C" int pdb200_cross_entropy_with_softmax(const void* logits, const int64_t* dims, int rank, const void* label,
                                                  int label_dtype, int soft_label, int use_softmax, int ignore_index,
-                                                 int axis, int dtype, void* softmax, void* loss, void* stream) {
+                                                 int axis, int dtype, void* softmax, void* loss, void* workspace,
+                                                 size_t workspace_bytes, void* stream) {
   using namespace pdb200;
   PDB_CHECK_ARG(rank >= 1 && rank <= PDB200_MAX_RANK, "cross_entropy_with_softmax: rank must be in [1, 9]");
   PDB_CHECK_ARG(dims != nullptr, "cross_entropy_with_softmax: dims is NULL");
@@ -131,15 +167,25 @@ extern "C" int pdb200_cross_entropy_with_softmax(const void* logits, const int64
   PDB_CHECK_ARG(logits && label && softmax && loss, "cross_entropy_with_softmax: NULL tensor pointer");
   if (soft_label && label_dtype != dtype)
     return fail(PDB200_INVALID_ARGUMENT, "cross_entropy_with_softmax: soft labels must have the dtype of the logits");
+  if (!(dtype == PDB200_FLOAT32 || dtype == PDB200_FLOAT64 || dtype == PDB200_FLOAT16 || dtype == PDB200_BFLOAT16))
+    return fail(PDB200_UNSUPPORTED, "cross_entropy_with_softmax: dtype must be float32/float64/float16/bfloat16, got code " + std::to_string(dtype));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  // the loss is built from logits + row statistics unless the logits are overwritten (in place) or are probabilities already
+  const bool from_logits = use_softmax && softmax != logits;
   if (use_softmax) {
-    const int rc = pdb200_softmax(logits, dims, rank, axis, dtype, softmax, stream);
+    const size_t need = pdb200_cross_entropy_workspace_bytes(dims, rank, axis, dtype);
+    if (from_logits && (workspace == nullptr || workspace_bytes < need))
+      return fail(PDB200_WORKSPACE_TOO_SMALL, "cross_entropy_with_softmax: workspace has " + std::to_string(workspace_bytes) +
+                                                  " bytes, this call needs " + std::to_string(need) +
+                                                  " (ask pdb200_cross_entropy_workspace_bytes)");
+    const int rc = softmax_with_stats(logits, dims, rank, axis, dtype, softmax, from_logits ? workspace : nullptr, stream);
     if (rc != PDB200_OK) return rc;
   }
   switch (dtype) {
 #define M(DT)                                                                                                       \
   case DT: {                                                                                                        \
     using T = typename CType<DT>::type;                                                                             \
+    using A = typename AccType<T>::type;                                                                            \
     if (!use_softmax && softmax != logits) { /* the input already is a softmax: hand it on (cross_entropy_kernel.cc:83-88) */ \
       const int64_t total = n * axis_dim * remain;                                                                  \
       const int64_t blocks = std::min<int64_t>((total + 255) / 256, (int64_t)sm_count() * 32);                      \
@@ -147,13 +193,14 @@ extern "C" int pdb200_cross_entropy_with_softmax(const void* logits, const int64
       const int rc = after_launch("ce_copy");                                                                       \
       if (rc != PDB200_OK) return rc;                                                                               \
     }                                                                                                               \
-    return ce_loss<T>(static_cast<const T*>(softmax), label, label_dtype, soft_label != 0, n, axis_dim, remain,     \
-                      ignore_index, static_cast<T*>(loss), st);                                                     \
+    if (from_logits)                                                                                                \
+      return ce_loss<T, true>(static_cast<const T*>(logits), static_cast<const A*>(workspace), label, label_dtype,  \
+                              soft_label != 0, n, axis_dim, remain, ignore_index, static_cast<T*>(loss), st);       \
+    return ce_loss<T, false>(static_cast<const T*>(softmax), nullptr, label, label_dtype, soft_label != 0, n,       \
+                             axis_dim, remain, ignore_index, static_cast<T*>(loss), st);                            \
   }
-    // float16 (registered on GPU in the reference) is left with the in-tree kernel: -log of a probability rounded to 11
-    // bits is not a usable loss; it needs the row statistics (max, log-sum) handed from the softmax kernel to the loss.
-    M(PDB200_FLOAT32) M(PDB200_FLOAT64)
+    M(PDB200_FLOAT32) M(PDB200_FLOAT64) M(PDB200_FLOAT16) M(PDB200_BFLOAT16)
 #undef M
   }
-  return fail(PDB200_UNSUPPORTED, "cross_entropy_with_softmax: dtype must be float32/float64, got code " + std::to_string(dtype));
+  return fail(PDB200_UNSUPPORTED, "cross_entropy_with_softmax: dtype not built");
 }

@@ -58,6 +58,9 @@ __device__ __forceinline__ A clipped_diff(A x, A m) {
 // LOG = false: softmax,      y = e * (1 / sum)          with e = exp(clipped_diff)
 // LOG = true : log_softmax,  y = d - log(sum)           with d = clipped_diff
 //   (phi::LogSoftmaxFunctor, paddle/phi/kernels/cpu/log_softmax_kernel.cc:40-100; GPU: gpu/log_softmax_kernel.cu)
+// Every kernel can also hand out the two row statistics, stats[2*pos] = max and stats[2*pos + 1] = log(sum), in the
+// accumulator type (pos = row, or outer*inner + col for a non-last axis): cross_entropy_with_softmax builds its loss from
+// them and the logits, in float, instead of taking the log of an already rounded probability.
 template <bool LOG, typename A>
 __device__ __forceinline__ A row_constant(A sum) { return LOG ? log_acc<A>(sum) : A(1) / sum; }
 template <bool LOG, typename A>
@@ -75,7 +78,7 @@ __device__ __forceinline__ A neg_inf() { return -std::numeric_limits<A>::infinit
 template <typename T, int C, bool VECTOR, bool LOG>
 __global__ void __launch_bounds__(256) softmax_rows_reg_kernel(const T* __restrict__ x,
                                                                T* __restrict__ y, int64_t outer,
-                                                               int dim, int G) {
+                                                               int dim, int G, typename AccType<T>::type* __restrict__ stats) {
   using A = typename AccType<T>::type;
   constexpr int V = VECTOR ? Vec<T>::N : 1;
   const int rows_per_cta = blockDim.x / G;
@@ -127,6 +130,7 @@ __global__ void __launch_bounds__(256) softmax_rows_reg_kernel(const T* __restri
   }
   for (int s = G >> 1; s >= 1; s >>= 1) sum += shfl_xor_any(sum, s);
   const A inv = row_constant<LOG, A>(sum);
+  if (stats != nullptr && lane == 0 && valid) { stats[2 * row] = m; stats[2 * row + 1] = log_acc<A>(sum); }
 #pragma unroll
   for (int c = 0; c < C; ++c) {
     const int off = (c * G + lane) * V;
@@ -169,7 +173,8 @@ template <> __device__ __forceinline__ double row_exp<double>(double x, double m
 // blockDim.x threads per row, C chunks of V elements per thread.  T is float, bf16 or fp16.
 template <typename T, int C, bool EXACT, bool LOG>
 __global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__ x, T* __restrict__ y,
-                                                           int64_t rows, int dim, int stages, int contiguous) {
+                                                           int64_t rows, int dim, int stages, int contiguous,
+                                                           float* __restrict__ stats) {
   constexpr int V = Vec<T>::N;
   extern __shared__ __align__(128) unsigned char ring_raw[];
   T* ring = reinterpret_cast<T*>(ring_raw);
@@ -257,6 +262,7 @@ __global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__
     float sum = (sm[0] + sm[1]) + (sm[2] + sm[3]);
     sum = block_reduce_1sync(sum, AddF<float>(), red[1]);
     const float inv = row_constant<LOG, float>(sum);
+    if (stats != nullptr && tid == 0) { stats[2 * row] = m; stats[2 * row + 1] = logf(sum); }
     T* dst = y + row * dim;
 #pragma unroll
     for (int c = 0; c < C; ++c) {
@@ -280,7 +286,8 @@ __global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__
 // ---- rows_smem -------------------------------------------------------------------------
 template <typename T, bool VECTOR, bool LOG>
 __global__ void __launch_bounds__(1024) softmax_rows_smem_kernel(const T* __restrict__ x,
-                                                                 T* __restrict__ y, int64_t dim) {
+                                                                 T* __restrict__ y, int64_t dim,
+                                                                 typename AccType<T>::type* __restrict__ stats) {
   using A = typename AccType<T>::type;
   constexpr int V = VECTOR ? Vec<T>::N : 1;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -319,6 +326,7 @@ __global__ void __launch_bounds__(1024) softmax_rows_smem_kernel(const T* __rest
   }
   sum = block_reduce(sum, AddF<A>(), A(0), red);
   const A inv = row_constant<LOG, A>(sum);
+  if (stats != nullptr && threadIdx.x == 0) { stats[2 * (int64_t)blockIdx.x] = m; stats[2 * (int64_t)blockIdx.x + 1] = log_acc<A>(sum); }
   for (int64_t i = (int64_t)threadIdx.x * V; i < dim; i += (int64_t)blockDim.x * V) {
     if constexpr (VECTOR) {
       Vec<T> o;
@@ -339,7 +347,8 @@ __global__ void __launch_bounds__(1024) softmax_rows_smem_kernel(const T* __rest
 // they agree bit for bit.  Requires dim % V == 0 and 16-byte aligned bases (vector path only).
 template <typename T, bool LOG>
 __global__ void __launch_bounds__(1024) softmax_rows_cluster_kernel(const T* __restrict__ x, T* __restrict__ y,
-                                                                    int64_t dim, int64_t slice) {
+                                                                    int64_t dim, int64_t slice,
+                                                                    typename AccType<T>::type* __restrict__ stats) {
   namespace cg = cooperative_groups;
   using A = typename AccType<T>::type;
   constexpr int V = Vec<T>::N;
@@ -402,6 +411,7 @@ __global__ void __launch_bounds__(1024) softmax_rows_cluster_kernel(const T* __r
   A gs = A(0);
   for (unsigned r = 0; r < cs; ++r) gs += *cluster.map_shared_rank(&xchg[1], r);
   const A inv = row_constant<LOG, A>(gs);
+  if (stats != nullptr && rank == 0 && threadIdx.x == 0) { stats[2 * row] = gm; stats[2 * row + 1] = log_acc<A>(gs); }
   // sweep 3: normalise and store
   for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
     const Vec<T> v = lds_vec(srow + i);
@@ -416,7 +426,8 @@ __global__ void __launch_bounds__(1024) softmax_rows_cluster_kernel(const T* __r
 
 // ---- rows_stream -----------------------------------------------------------------------
 template <typename T, bool LOG>
-__global__ void __launch_bounds__(1024) softmax_rows_stream_kernel(const T* x, T* y, int64_t dim) {
+__global__ void __launch_bounds__(1024) softmax_rows_stream_kernel(const T* x, T* y, int64_t dim,
+                                                                   typename AccType<T>::type* stats) {
   using A = typename AccType<T>::type;
   __shared__ A red[33];
   const T* src = x + (int64_t)blockIdx.x * dim;
@@ -431,6 +442,7 @@ __global__ void __launch_bounds__(1024) softmax_rows_stream_kernel(const T* x, T
   for (int64_t i = threadIdx.x; i < dim; i += blockDim.x) sum += clipped_exp<A>(cvt<A>(src[i]), m);
   sum = block_reduce(sum, AddF<A>(), A(0), red);
   const A inv = row_constant<LOG, A>(sum);
+  if (stats != nullptr && threadIdx.x == 0) { stats[2 * (int64_t)blockIdx.x] = m; stats[2 * (int64_t)blockIdx.x + 1] = log_acc<A>(sum); }
   // in-place safe: each element is read and written by the same thread in this sweep
   for (int64_t i = threadIdx.x; i < dim; i += blockDim.x)
     dst[i] = cvt<T>(LOG ? clipped_diff<A>(cvt<A>(src[i]), m) - inv : clipped_exp<A>(cvt<A>(src[i]), m) * inv);
@@ -439,7 +451,8 @@ __global__ void __launch_bounds__(1024) softmax_rows_stream_kernel(const T* x, T
 // ---- cols: softmax along the middle axis of [outer][dim][inner] ---------------------------
 template <typename T, bool LOG>
 __global__ void __launch_bounds__(256) softmax_cols_kernel(const T* x, T* y, int64_t dim,
-                                                           int64_t inner, int64_t col_tiles) {
+                                                           int64_t inner, int64_t col_tiles,
+                                                           typename AccType<T>::type* stats) {
   using A = typename AccType<T>::type;
   const int64_t o = (int64_t)blockIdx.x / col_tiles;
   const int64_t ct = (int64_t)blockIdx.x - o * col_tiles;
@@ -455,6 +468,7 @@ __global__ void __launch_bounds__(256) softmax_cols_kernel(const T* x, T* y, int
   A sum = A(0);
   for (int64_t r = 0; r < dim; ++r) sum += clipped_exp<A>(cvt<A>(src[r * inner]), m);
   const A inv = row_constant<LOG, A>(sum);
+  if (stats != nullptr) { stats[2 * (o * inner + col)] = m; stats[2 * (o * inner + col) + 1] = log_acc<A>(sum); }
   for (int64_t r = 0; r < dim; ++r)
     dst[r * inner] = cvt<T>(LOG ? clipped_diff<A>(cvt<A>(src[r * inner]), m) - inv : clipped_exp<A>(cvt<A>(src[r * inner]), m) * inv);
 }
@@ -464,13 +478,13 @@ __global__ void softmax_fill_one_kernel(T* y, float v) { y[0] = cvt<T>(typename 
 
 // ---- host -------------------------------------------------------------------------------
 template <typename T, bool VECTOR, bool LOG>
-int launch_rows_reg(const T* x, T* y, int64_t outer, int dim, int G, int C, cudaStream_t st) {
+int launch_rows_reg(const T* x, T* y, int64_t outer, int dim, int G, int C, typename AccType<T>::type* stats, cudaStream_t st) {
   const int rows_per_cta = 256 / G;
   const int64_t blocks = (outer + rows_per_cta - 1) / rows_per_cta;
   if (blocks > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "softmax: too many rows for one launch");
 #define PDB_SM_C(CC)                                                                                \
   case CC:                                                                                          \
-    softmax_rows_reg_kernel<T, CC, VECTOR, LOG><<<(unsigned)blocks, 256, 0, st>>>(x, y, outer, dim, G); \
+    softmax_rows_reg_kernel<T, CC, VECTOR, LOG><<<(unsigned)blocks, 256, 0, st>>>(x, y, outer, dim, G, stats); \
     break;
   switch (C) {
     PDB_SM_C(1) PDB_SM_C(2) PDB_SM_C(4) PDB_SM_C(8) PDB_SM_C(16)
@@ -482,7 +496,7 @@ int launch_rows_reg(const T* x, T* y, int64_t outer, int dim, int G, int C, cuda
 
 // TMA row pipeline (float / bf16 / fp16 rows of 64..2048 16-byte chunks, many rows).
 template <typename T, bool LOG>
-int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, cudaStream_t st) {
+int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, typename AccType<T>::type* stats, cudaStream_t st) {
   if constexpr (std::is_same<T, double>::value) {
     return -1;  // the pipeline computes in float
   } else {
@@ -505,7 +519,7 @@ int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, cudaStream_t 
     if (!pipe_geometry(kern, threads, row_bytes, want, 3, &per_sm, &stages, &smem)) return -1;
     int64_t grid = (int64_t)per_sm * sm_count();
     if (grid > outer) grid = outer;
-    kern<<<(unsigned)grid, threads, smem, st>>>(x, y, outer, (int)dim, stages, pipe_contiguous());
+    kern<<<(unsigned)grid, threads, smem, st>>>(x, y, outer, (int)dim, stages, pipe_contiguous(), stats);
     return after_launch("softmax_pipe");
   };
   const bool exact = (int64_t)threads * C == nchunk;
@@ -521,7 +535,7 @@ int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, cudaStream_t 
 
 // Cluster route: returns < 0 when the row does not fit 8 CTAs' shared memory.
 template <typename T, bool LOG>
-int try_softmax_cluster(const T* x, T* y, int64_t outer, int64_t dim, cudaStream_t st) {
+int try_softmax_cluster(const T* x, T* y, int64_t outer, int64_t dim, typename AccType<T>::type* stats, cudaStream_t st) {
   constexpr int VN = Vec<T>::N;
   const size_t row_bytes = (size_t)dim * sizeof(T);
   const size_t kMaxSlice = 200 * 1024;
@@ -553,7 +567,7 @@ int try_softmax_cluster(const T* x, T* y, int64_t outer, int64_t dim, cudaStream
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, x, y, dim, slice);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, x, y, dim, slice, stats);
   if (e != cudaSuccess) {
     cudaGetLastError();
     return -1;  // e.g. the cluster cannot be co-scheduled with this much shared memory: fall back
@@ -562,7 +576,8 @@ int try_softmax_cluster(const T* x, T* y, int64_t outer, int64_t dim, cudaStream
 }
 
 template <typename T, bool LOG>
-int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, cudaStream_t st) {
+int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, typename AccType<T>::type* stats,
+                  cudaStream_t st) {
   using A = typename AccType<T>::type;
   constexpr int VN = Vec<T>::N;
   if (inner == 1) {
@@ -570,7 +585,7 @@ int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, c
     const int V = vec ? VN : 1;
     const int64_t nchunk = dim / V;
     if (vec && nchunk >= 64 && nchunk <= 512 * 4 && outer >= 4 * (int64_t)sm_count()) {
-      const int rc = try_softmax_pipe<T, LOG>(x, y, outer, dim, st);
+      const int rc = try_softmax_pipe<T, LOG>(x, y, outer, dim, stats, st);
       if (rc >= 0) return rc;  // < 0: the pipeline does not fit; use the register route
     }
     if (nchunk <= 32 * 16) {
@@ -578,11 +593,11 @@ int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, c
       while (G < 32 && G < nchunk) G <<= 1;
       int C = 1;
       while ((int64_t)C * G < nchunk) C <<= 1;
-      return vec ? launch_rows_reg<T, true, LOG>(x, y, outer, (int)dim, G, C, st)
-                 : launch_rows_reg<T, false, LOG>(x, y, outer, (int)dim, G, C, st);
+      return vec ? launch_rows_reg<T, true, LOG>(x, y, outer, (int)dim, G, C, stats, st)
+                 : launch_rows_reg<T, false, LOG>(x, y, outer, (int)dim, G, C, stats, st);
     }
     if (vec) {
-      const int rc = try_softmax_cluster<T, LOG>(x, y, outer, dim, st);
+      const int rc = try_softmax_cluster<T, LOG>(x, y, outer, dim, stats, st);
       if (rc >= 0) return rc;
     }
     if (outer > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "softmax: too many rows for one launch");
@@ -592,14 +607,14 @@ int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, c
       while (threads < 1024 && (int64_t)threads * V * 8 < dim) threads <<= 1;
       if (vec) {
         cudaFuncSetAttribute(softmax_rows_smem_kernel<T, true, LOG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        softmax_rows_smem_kernel<T, true, LOG><<<(unsigned)outer, threads, smem, st>>>(x, y, dim);
+        softmax_rows_smem_kernel<T, true, LOG><<<(unsigned)outer, threads, smem, st>>>(x, y, dim, stats);
       } else {
         cudaFuncSetAttribute(softmax_rows_smem_kernel<T, false, LOG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        softmax_rows_smem_kernel<T, false, LOG><<<(unsigned)outer, threads, smem, st>>>(x, y, dim);
+        softmax_rows_smem_kernel<T, false, LOG><<<(unsigned)outer, threads, smem, st>>>(x, y, dim, stats);
       }
       return after_launch("softmax_rows_smem");
     }
-    softmax_rows_stream_kernel<T, LOG><<<(unsigned)outer, 1024, 0, st>>>(x, y, dim);
+    softmax_rows_stream_kernel<T, LOG><<<(unsigned)outer, 1024, 0, st>>>(x, y, dim, stats);
     return after_launch("softmax_rows_stream");
   }
   int threads = 32;
@@ -607,12 +622,12 @@ int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, c
   const int64_t col_tiles = (inner + threads - 1) / threads;
   const int64_t blocks = col_tiles * outer;
   if (blocks > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "softmax: too many tiles for one launch");
-  softmax_cols_kernel<T, LOG><<<(unsigned)blocks, threads, 0, st>>>(x, y, dim, inner, col_tiles);
+  softmax_cols_kernel<T, LOG><<<(unsigned)blocks, threads, 0, st>>>(x, y, dim, inner, col_tiles, stats);
   return after_launch("softmax_cols");
 }
 
 template <bool LOG>
-int softmax_entry(const void* x, const int64_t* dims, int rank, int axis, int dtype, void* out, void* stream) {
+int softmax_entry(const void* x, const int64_t* dims, int rank, int axis, int dtype, void* out, void* stats, void* stream) {
   PDB_CHECK_ARG(rank >= 0 && rank <= PDB200_MAX_RANK, "softmax: rank must be in [0, 9]");
   PDB_CHECK_ARG(rank == 0 || dims != nullptr, "softmax: dims is NULL");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
@@ -639,7 +654,8 @@ int softmax_entry(const void* x, const int64_t* dims, int rank, int axis, int dt
       softmax_fill_one_kernel<T><<<1, 1, 0, st>>>(static_cast<T*>(out), LOG ? 0.f : 1.f);     \
       return after_launch("softmax_fill_one");                                                \
     }                                                                                         \
-    return softmax_typed<T, LOG>(static_cast<const T*>(x), static_cast<T*>(out), outer, dim, inner, st); \
+    return softmax_typed<T, LOG>(static_cast<const T*>(x), static_cast<T*>(out), outer, dim, inner,          \
+                                 static_cast<typename AccType<T>::type*>(stats), st);                       \
   }
   switch (dtype) {
     PDB_SM_CASE(PDB200_FLOAT32)
@@ -654,11 +670,19 @@ int softmax_entry(const void* x, const int64_t* dims, int rank, int axis, int dt
 }
 }  // namespace pdb200
 
+namespace pdb200 {
+// softmax + row statistics for cross_entropy.cu (same library, not part of the C-ABI): stats = [positions][2] of the
+// accumulator type (float, or double for float64 input)
+int softmax_with_stats(const void* x, const int64_t* dims, int rank, int axis, int dtype, void* out, void* stats, void* stream) {
+  return softmax_entry<false>(x, dims, rank, axis, dtype, out, stats, stream);
+}
+}  // namespace pdb200
+
 extern "C" int pdb200_softmax(const void* x, const int64_t* dims, int rank, int axis, int dtype, void* out,
                               void* stream) {
-  return pdb200::softmax_entry<false>(x, dims, rank, axis, dtype, out, stream);
+  return pdb200::softmax_entry<false>(x, dims, rank, axis, dtype, out, nullptr, stream);
 }
 extern "C" int pdb200_log_softmax(const void* x, const int64_t* dims, int rank, int axis, int dtype, void* out,
                                   void* stream) {
-  return pdb200::softmax_entry<true>(x, dims, rank, axis, dtype, out, stream);
+  return pdb200::softmax_entry<true>(x, dims, rank, axis, dtype, out, nullptr, stream);
 }

@@ -73,9 +73,12 @@ def _cross_entropy(logits, label, soft_label, use_softmax, ignore_index, axis, r
     sm = torch.empty_like(logits)
     loss = torch.empty(lshape, dtype=logits.dtype, device=logits.device)
     d, r = L.dims_array(logits.shape)
+    nbytes = lib.pdb200_cross_entropy_workspace_bytes(d, r, int(axis), _dtype_code(logits.dtype)) if use_softmax else 0
+    ws = _workspace(nbytes, logits.device)
     L.check(lib.pdb200_cross_entropy_with_softmax(_ptr(logits), d, r, _ptr(label), _dtype_code(label.dtype), int(bool(soft_label)),
                                                   int(bool(use_softmax)), int(ignore_index), int(axis),
-                                                  _dtype_code(logits.dtype), _ptr(sm), _ptr(loss), _stream()), lib)
+                                                  _dtype_code(logits.dtype), _ptr(sm), _ptr(loss), _ptr(ws), nbytes, _stream()),
+            lib)
     return (loss, sm) if return_softmax else loss
 
 

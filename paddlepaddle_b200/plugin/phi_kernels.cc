@@ -305,9 +305,14 @@ void CrossEntropyWithSoftmaxKernel(const Context& ctx, const DenseTensor& logits
   T* sm = ctx.template Alloc<T>(softmax);
   T* lo = ctx.template Alloc<T>(loss);
   auto d = Dims(logits);
+  const size_t bytes = use_softmax ? pdb200_cross_entropy_workspace_bytes(d.data(), static_cast<int>(d.size()), axis,
+                                                                          Code(logits.dtype()))
+                                   : 0;
+  DenseTensor holder;
+  void* ws = Scratch(ctx, bytes, &holder);
   Check(pdb200_cross_entropy_with_softmax(logits.data<T>(), d.data(), static_cast<int>(d.size()), label.data(),
                                           Code(label.dtype()), soft_label, use_softmax, ignore_index, axis,
-                                          Code(logits.dtype()), sm, lo, ctx.stream()));
+                                          Code(logits.dtype()), sm, lo, ws, bytes, ctx.stream()));
 }
 template <typename T, typename Context>
 void LogSoftmaxKernel(const Context& ctx, const DenseTensor& x, int axis, DenseTensor* out) {
@@ -459,8 +464,9 @@ PD_REGISTER_KERNEL(sum_grad, GPU, ALL_LAYOUT, pdb200_phi::ReduceSumGradKernel, f
 }
 PD_REGISTER_KERNEL(mean_grad, GPU, ALL_LAYOUT, pdb200_phi::ReduceMeanGradKernel, float, double, phi::dtype::float16,
                    phi::dtype::bfloat16, int, int64_t) {}
-// gpu/cross_entropy_kernel.cu:1460-1466 (float16 stays with the in-tree kernel)
-PD_REGISTER_KERNEL(cross_entropy_with_softmax, GPU, ALL_LAYOUT, pdb200_phi::CrossEntropyWithSoftmaxKernel, float, double) {}
+// gpu/cross_entropy_kernel.cu:1460-1466
+PD_REGISTER_KERNEL(cross_entropy_with_softmax, GPU, ALL_LAYOUT, pdb200_phi::CrossEntropyWithSoftmaxKernel, float, double,
+                   phi::dtype::float16) {}
 PD_REGISTER_KERNEL(log_softmax, GPU, ALL_LAYOUT, pdb200_phi::LogSoftmaxKernel, float, double, phi::dtype::float16,
                    phi::dtype::bfloat16) {}  // gpu/log_softmax_kernel.cu registration
 PD_REGISTER_KERNEL(sum_raw, GPU, ALL_LAYOUT, pdb200_phi::SumRawKernel, bool, float, double, phi::dtype::float16,

@@ -1,6 +1,7 @@
 """GPU parity for cross_entropy_with_softmax through the C-ABI, against the reference CPU kernel's
 recorded outputs and the CPU oracle: softmax to the softmax bars (1e-5 float32, 1e-12 float64), loss to 1e-5 / 1e-12
-(relative, plus the same absolute term for losses near zero)."""
+(relative, plus the same absolute term for losses near zero); float16 / bfloat16: the loss is computed in float from the
+logits and the row statistics and rounded once — one unit in the last place of the 16-bit result."""
 import os
 
 import numpy as np
@@ -8,7 +9,7 @@ import pytest
 import torch
 
 import oracle_lib as O
-from gpu_util import to_dev, to_np
+from gpu_util import assert_half_close, to_dev, to_np
 
 pytestmark = pytest.mark.gpu
 
@@ -60,6 +61,17 @@ def test_cross_entropy_routes(port, shape, axis):
     xd = x.astype(np.float64)
     loss = F.softmax_with_cross_entropy(to_dev(xd), to_dev(hard).reshape(lshape), ignore_index=-1, axis=axis)
     np.testing.assert_allclose(to_np(loss), lh64, rtol=1e-12, atol=1e-12)
+    for half, conv, back in (("fp16", port.f32_to_fp16, port.fp16_to_f32), ("bf16", port.f32_to_bf16, port.bf16_to_f32)):
+        xh = conv(x)
+        xr = back(xh).astype(np.float64)  # the values the kernel sees
+        _, want_h = port.cross_entropy_with_softmax(xr, hard, False, True, -1, axis)
+        _, want_s = port.cross_entropy_with_softmax(xr, soft.astype(np.float64), True, True, -1, axis)
+        got_h = F.softmax_with_cross_entropy(to_dev(xh, half), to_dev(hard).reshape(lshape), ignore_index=-1, axis=axis)
+        assert_half_close(to_np(got_h), conv(want_h.astype(np.float32)), 1, f"ce hard {half}", half, atol=1e-5)
+        sl = conv(soft)
+        _, want_s = port.cross_entropy_with_softmax(xr, back(sl).astype(np.float64), True, True, -1, axis)
+        got_s = F.softmax_with_cross_entropy(to_dev(xh, half), to_dev(sl, half), soft_label=True, axis=axis)
+        assert_half_close(to_np(got_s), conv(want_s.astype(np.float32)), 1, f"ce soft {half}", half, atol=1e-4)
 
 
 def test_cross_entropy_input_is_softmax_and_errors(port):
@@ -80,4 +92,18 @@ def test_cross_entropy_input_is_softmax_and_errors(port):
     with pytest.raises(TypeError):
         F.softmax_with_cross_entropy(to_dev(x), to_dev(hard.astype(np.float32)).reshape(50, 1))
     with pytest.raises(NotImplementedError):
-        F.softmax_with_cross_entropy(to_dev(x).to(torch.float16), to_dev(hard).reshape(50, 1))
+        F.softmax_with_cross_entropy(to_dev(x).to(torch.int32), to_dev(hard).reshape(50, 1))
+    # in place (softmax written over the logits): the loss falls back to -log(softmax) and still meets the float32 bar
+    from paddlepaddle_b200 import _lib as L
+    import ctypes
+    lib = L.load()
+    tx = to_dev(x)
+    tl = to_dev(hard).reshape(50, 1)
+    loss = torch.empty(50, 1, device="cuda")
+    d, r = L.dims_array(tx.shape)
+    rc = lib.pdb200_cross_entropy_with_softmax(tx.data_ptr(), d, r, tl.data_ptr(), L.INT64, 0, 1, -100, -1, L.FLOAT32, tx.data_ptr(),
+                                               loss.data_ptr(), None, 0, None)
+    assert rc == 0, lib.pdb200_last_error()
+    want_sm, want_loss = port.cross_entropy_with_softmax(x, hard, False, True, -100, -1)
+    np.testing.assert_allclose(to_np(tx), want_sm, rtol=1e-5, atol=1e-9)
+    np.testing.assert_allclose(to_np(loss), want_loss, rtol=1e-5, atol=1e-5)
