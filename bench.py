@@ -38,7 +38,7 @@ C2_COLS = C2_SHAPE[2]
 C2_BYTES_BF16 = 2 * (C2_ROWS * C2_COLS * 2) + C2_COLS * 2  # 2,147,491,840
 
 
-def measured_traffic(name="r1_add_bf16.txt"):
+def measured_traffic(name="r1h_add_bf16.txt"):
     """DRAM bytes per launch of the headline kernel from the committed ncu --set full capture
     (profiles/<name>: dram__bytes_read.sum + dram__bytes_write.sum); None if the file is missing."""
     p = os.path.join(ROOT, "profiles", name)
@@ -506,7 +506,7 @@ def run_gpu_arm(args):
                        "frac_of_8TBps_per_gpu": round(value / world / 8000.0, 4)},
             "roofline": {"bound": "hbm", "kernel": "ew_inner_kernel<bf16,AddOp>", "achieved": round(achieved, 1), "peak": peak,
                          "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": measured_traffic(),
-                         "traffic_source": "profiles/r1_add_bf16.txt (ncu --set full, one launch)", "peak_source": peak_src,
+                         "traffic_source": "profiles/r1h_add_bf16.txt (ncu --set full, one launch)", "peak_source": peak_src,
                          "kernel_ms": round(kern_ms, 4)},
             "e2e": {"value": round(e2e_val, 2), "unit": "GB/s", "h2d_bytes_per_step": C2_ROWS * C2_COLS * 2 + C2_COLS * 2,
                     "d2h_bytes_per_step": C2_ROWS * C2_COLS * 2, "ms_per_step": round(float(e2e_ms.item()), 3),
