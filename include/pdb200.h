@@ -359,6 +359,20 @@ PDB200_API int pdb200_layer_norm_grad(const void* x, const int64_t* dims, int ra
                            void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------
+ * rms_norm forward with the optional fused bias + residual add.  Replaces phi::RmsNormKernel<T,
+ * GPUContext> without quantisation (paddle/phi/kernels/gpu/rms_norm_kernel.cu:1080-1260; python:
+ * paddle.incubate.nn.functional.fused_rms_norm):
+ *   v = x (+ residual + bias); residual_out = v (rounded to the dtype) when a residual is given;
+ *   inv_var[row] = rsqrt(mean(v^2) + epsilon) (float, optional); out = (v * inv_var) * norm_weight (+ norm_bias).
+ * rows = prod(dims[:begin_norm_axis]), D = prod(dims[begin_norm_axis:]); bias, norm_weight, norm_bias have D elements of
+ * the tensor dtype; bias, residual, norm_bias, inv_var may be NULL (bias only together with residual).  residual_out may
+ * be the residual buffer.  dtypes FLOAT32, FLOAT16, BFLOAT16 (computed in float).  The int8 / fp8 quantised outputs of
+ * the reference stay with the in-tree kernel. */
+PDB200_API int pdb200_rms_norm(const void* x, const int64_t* dims, int rank, const void* bias, const void* residual,
+                    const void* norm_weight, const void* norm_bias, float epsilon, int begin_norm_axis, int dtype,
+                    void* out, void* residual_out, void* inv_var, void* stream);
+
+/* ---------------------------------------------------------------------------
  * The exchange step of sharded reductions over NVLink peer memory — one process per GPU.
  * Replaces paddle.distributed.all_reduce -> ProcessGroupNCCL::AllReduce -> ncclAllReduce
  * (paddle/fluid/distributed/collective/process_group_nccl.cc:267-297) for the small results this path exchanges.
