@@ -326,6 +326,14 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
     rec("next: softmax_with_cross_entropy fp32 [65536,8192] hard labels (softmax + loss)", 2 * 65536 * 8192 * 4 + 65536 * 12,
         lambda: F.softmax_with_cross_entropy(xl32, lbl, return_softmax=True), 65536 * 8192)
     del xl32, lbl
+    xr_ = torch.randn((65536, 8192), device="cuda", generator=g).to(torch.bfloat16)
+    rr_ = torch.randn((65536, 8192), device="cuda", generator=g).to(torch.bfloat16)
+    wr_ = (torch.rand(8192, device="cuda", generator=g) + 0.5).to(torch.bfloat16)
+    rec("next: rms_norm bf16 [65536,8192]", 2 * 65536 * 8192 * 2 + 8192 * 2 + 65536 * 4,
+        lambda: F.fused_rms_norm(xr_, wr_, None, 1e-6, 1), 65536 * 8192)
+    rec("next: rms_norm bf16 [65536,8192] with fused residual add (out + residual_out)", 4 * 65536 * 8192 * 2 + 8192 * 2 + 65536 * 4,
+        lambda: F.fused_rms_norm(xr_, wr_, None, 1e-6, 1, residual=rr_), 65536 * 8192)
+    del xr_, rr_, wr_
     rec("next: softmax_grad bf16 [8,32,2048,2048] axis=-1", 3 * n * 2, lambda: F.softmax_grad(yy, dyy, axis=-1), n)
     del yy, dyy
     rows, D = 65536, 8192

@@ -607,3 +607,31 @@ int oracle_bitwise_shift(int right, int is_arithmetic, int dtype, const void* x,
   }
   return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * rms_norm.  PARITY UNPINNED for this function: the reference has no CPU kernel for rms_norm
+ * (GPU only, paddle/phi/kernels/gpu/rms_norm_kernel.cu), so it cannot be compiled into oracle/_ref.  This restates the
+ * formula the reference's own test checks its kernel against (test/legacy_test/test_rms_norm_op.py:37-47,74-79):
+ *     v = x + residual + bias;  variance = mean(v^2, last dims);  out = rsqrt(variance + eps) * v * gamma + beta
+ * in double precision; callers round to the tensor dtype.  residual / bias / beta may be NULL.
+ * ---------------------------------------------------------------------------------------- */
+int oracle_rms_norm(const double* x, int64_t rows, int64_t D, const double* bias, const double* residual, const double* gamma,
+                    const double* beta, double eps, double* out, double* residual_out, double* inv_var) {
+  for (int64_t r = 0; r < rows; ++r) {
+    double ss = 0.0;
+    for (int64_t i = 0; i < D; ++i) {
+      double v = x[r * D + i];
+      if (residual) { v += residual[r * D + i]; if (bias) v += bias[i]; }
+      if (residual_out) residual_out[r * D + i] = v;
+      ss += v * v;
+    }
+    const double inv = 1.0 / sqrt(ss / (double)D + eps);
+    if (inv_var) inv_var[r] = inv;
+    for (int64_t i = 0; i < D; ++i) {
+      double v = x[r * D + i];
+      if (residual) { v += residual[r * D + i]; if (bias) v += bias[i]; }
+      out[r * D + i] = inv * v * gamma[i] + (beta ? beta[i] : 0.0);
+    }
+  }
+  return 0;
+}

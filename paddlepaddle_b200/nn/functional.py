@@ -82,6 +82,45 @@ def _cross_entropy(logits, label, soft_label, use_softmax, ignore_index, axis, r
     return (loss, sm) if return_softmax else loss
 
 
+def fused_rms_norm(x, norm_weight, norm_bias=None, epsilon=1e-6, begin_norm_axis=1, bias=None, residual=None,
+                   quant_scale=-1, quant_round_type=0, quant_max_bound=0, quant_min_bound=0):
+    """paddle.incubate.nn.functional.fused_rms_norm (python/paddle/incubate/nn/functional/fused_rms_norm.py):
+    returns (out, inv_var) or, with a residual, (out, residual_out, inv_var); v = x + residual + bias is normalised by
+    its root mean square over the trailing dims from begin_norm_axis.  Quantised outputs are not on this path."""
+    _require_cuda(x, norm_weight, norm_bias, bias, residual)
+    if quant_scale > 0:
+        raise NotImplementedError("(Unimplemented) quantised rms_norm outputs stay with the reference kernel")
+    for t in (norm_weight, norm_bias, bias, residual):
+        if t is not None and t.dtype != x.dtype:
+            raise TypeError("(InvalidType) every operand of rms_norm must have the dtype of x")
+    if bias is not None and residual is None:
+        raise ValueError("(InvalidArgument) bias is only added together with a residual")
+    if residual is not None and residual.shape != x.shape:
+        raise ValueError("(InvalidArgument) residual must have the shape of x")
+    rank = x.dim()
+    if not 0 <= begin_norm_axis <= rank:
+        raise ValueError(f"(InvalidArgument) begin_norm_axis must be in [0, {rank}]")
+    D = 1
+    for d_ in x.shape[begin_norm_axis:]:
+        D *= d_
+    rows = x.numel() // D if D else 0
+    for name_, t in (("norm_weight", norm_weight), ("norm_bias", norm_bias), ("bias", bias)):
+        if t is not None and t.numel() != D:
+            raise ValueError(f"(InvalidArgument) {name_} must have {D} elements, got {t.numel()}")
+    lib = L.load()
+    x = x.contiguous()
+    cont = lambda t: t.contiguous() if t is not None else None
+    norm_weight, norm_bias, bias, residual = cont(norm_weight), cont(norm_bias), cont(bias), cont(residual)
+    out = torch.empty_like(x)
+    res_out = torch.empty_like(x) if residual is not None else None
+    inv_var = torch.empty(tuple(x.shape[:begin_norm_axis]), dtype=torch.float32, device=x.device)
+    d, r = L.dims_array(x.shape)
+    L.check(lib.pdb200_rms_norm(_ptr(x), d, r, _ptr(bias), _ptr(residual), _ptr(norm_weight), _ptr(norm_bias),
+                                ctypes.c_float(epsilon), int(begin_norm_axis), _dtype_code(x.dtype), _ptr(out), _ptr(res_out),
+                                _ptr(inv_var), _stream()), lib)
+    return (out, res_out, inv_var) if residual is not None else (out, inv_var)
+
+
 def softmax_(x, axis=-1, dtype=None, name=None):
     _require_cuda(x)
     lib = L.load()

@@ -314,6 +314,24 @@ void CrossEntropyWithSoftmaxKernel(const Context& ctx, const DenseTensor& logits
                                           Code(label.dtype()), soft_label, use_softmax, ignore_index, axis,
                                           Code(logits.dtype()), sm, lo, ws, bytes, ctx.stream()));
 }
+// rms_norm without quantisation (gpu/rms_norm_kernel.cu:1080-1260); a quantised output dtype stays with the in-tree kernel
+template <typename T, typename Context>
+void RmsNormKernel(const Context& ctx, const DenseTensor& x, const paddle::optional<DenseTensor>& bias,
+                   const paddle::optional<DenseTensor>& residual, const DenseTensor& norm_weight,
+                   const paddle::optional<DenseTensor>& norm_bias, const float epsilon, const int begin_norm_axis,
+                   const float quant_scale, const int quant_round_type, const float quant_max_bound,
+                   const float quant_min_bound, DenseTensor* out, DenseTensor* residual_out, DenseTensor* inv_var) {
+  if (out->dtype() == DataType::INT8 || out->dtype() == DataType::FLOAT8_E4M3FN)
+    PADDLE_THROW(common::errors::Unimplemented("pdb200: quantised rms_norm outputs are not on this path"));
+  T* o = ctx.template Alloc<T>(out);
+  T* ro = residual ? ctx.template Alloc<T>(residual_out) : nullptr;
+  float* iv = inv_var ? ctx.template Alloc<float>(inv_var) : nullptr;
+  auto d = Dims(x);
+  Check(pdb200_rms_norm(x.data<T>(), d.data(), static_cast<int>(d.size()), bias ? bias.get().data<T>() : nullptr,
+                        residual ? residual.get().data<T>() : nullptr, norm_weight.data<T>(),
+                        norm_bias ? norm_bias.get().data<T>() : nullptr, epsilon, begin_norm_axis, Code(x.dtype()), o, ro, iv,
+                        ctx.stream()));
+}
 template <typename T, typename Context>
 void LogSoftmaxKernel(const Context& ctx, const DenseTensor& x, int axis, DenseTensor* out) {
   T* o = ctx.template Alloc<T>(out);
@@ -467,6 +485,8 @@ PD_REGISTER_KERNEL(mean_grad, GPU, ALL_LAYOUT, pdb200_phi::ReduceMeanGradKernel,
 // gpu/cross_entropy_kernel.cu:1460-1466
 PD_REGISTER_KERNEL(cross_entropy_with_softmax, GPU, ALL_LAYOUT, pdb200_phi::CrossEntropyWithSoftmaxKernel, float, double,
                    phi::dtype::float16) {}
+PD_REGISTER_KERNEL(rms_norm, GPU, ALL_LAYOUT, pdb200_phi::RmsNormKernel, float, phi::dtype::float16,
+                   phi::dtype::bfloat16) {}  // gpu/rms_norm_kernel.cu:1333-1339
 PD_REGISTER_KERNEL(log_softmax, GPU, ALL_LAYOUT, pdb200_phi::LogSoftmaxKernel, float, double, phi::dtype::float16,
                    phi::dtype::bfloat16) {}  // gpu/log_softmax_kernel.cu registration
 PD_REGISTER_KERNEL(sum_raw, GPU, ALL_LAYOUT, pdb200_phi::SumRawKernel, bool, float, double, phi::dtype::float16,

@@ -356,6 +356,24 @@ class Oracle:
         self._check(rc)
         return sm, loss
 
+    def rms_norm(self, x, gamma, beta=None, eps=1e-6, begin_norm_axis=1, bias=None, residual=None):
+        """float64 restatement of the reference test's formula (port only: the reference has no CPU rms_norm).
+        -> (out, residual_out or None, inv_var), all float64."""
+        assert self.kind == "port", "rms_norm has no compiled-reference oracle"
+        x = np.ascontiguousarray(x, np.float64)
+        D = int(np.prod(x.shape[begin_norm_axis:], dtype=np.int64))
+        rows = x.size // D
+        f = lambda a: None if a is None else np.ascontiguousarray(a, np.float64)
+        gamma, beta, bias, residual = f(gamma), f(beta), f(bias), f(residual)
+        out = np.empty_like(x)
+        res_out = np.empty_like(x) if residual is not None else None
+        inv = np.empty(x.shape[:begin_norm_axis], np.float64)
+        p = lambda a: _vp(a) if a is not None else None
+        rc = self.lib.oracle_rms_norm(_vp(x), ctypes.c_int64(rows), ctypes.c_int64(D), p(bias), p(residual), _vp(gamma), p(beta),
+                                      ctypes.c_double(eps), _vp(out), p(res_out), _vp(inv))
+        self._check(rc)
+        return out, res_out, inv
+
     def _check(self, rc):
         if rc != 0:
             msg = ""

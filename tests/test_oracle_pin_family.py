@@ -187,3 +187,21 @@ def test_bitwise_shift_golden(port, gold):
             for right in (0, 1):
                 for ar in (0, 1):
                     assert np.array_equal(port.bitwise_shift(right, x, y, bool(ar)), gold[f"sh_{name}_{dt}_{right}{ar}__out"]), (name, dt, right, ar)
+
+
+def test_rms_norm_restatement_matches_the_reference_tests_formula(port):
+    """rms_norm has no CPU kernel in the reference (parity unpinned against oracle/_ref); the restatement is held to the
+    formula the reference's own test uses, test/legacy_test/test_rms_norm_op.py:37-47,74-79, written out in numpy."""
+    rng = np.random.default_rng(5)
+    x, res = rng.standard_normal((6, 7, 40)), rng.standard_normal((6, 7, 40))
+    g, b, bias = rng.standard_normal(40), rng.standard_normal(40), rng.standard_normal(40)
+    out, _, inv = port.rms_norm(x, g, b, 1e-5, 2)
+    var = (x ** 2).mean(-1, keepdims=True)
+    np.testing.assert_allclose(out, 1.0 / np.sqrt(var + 1e-5) * x * g + b, rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(inv, 1.0 / np.sqrt(var[..., 0] + 1e-5), rtol=1e-12, atol=1e-14)
+    out, ro, _ = port.rms_norm(x, g, b, 1e-5, 2, bias=bias, residual=res)
+    v = x + res + bias
+    np.testing.assert_allclose(ro, v, rtol=1e-15)
+    np.testing.assert_allclose(out, 1.0 / np.sqrt((v ** 2).mean(-1, keepdims=True) + 1e-5) * v * g + b, rtol=1e-12, atol=1e-14)
+    out2, _, _ = port.rms_norm(x.reshape(6, 280), np.tile(g, 7), None, 1e-5, 1)
+    assert out2.shape == (6, 280)
