@@ -142,12 +142,21 @@ template <typename T, typename Op>
 struct OpOut {
   using type = decltype(Op::apply(T(), T()));
 };
+// One 16-byte vector of each operand -> one pack of results.  The default applies the functor element by element;
+// an operator may specialise VecApply for a dtype where a packed instruction does several elements at once
+// (elementwise_pred.cu: 16-bit less_than / less_equal through the packed half compare).
+template <typename T, typename Op>
+struct VecApply {
+  static __device__ __forceinline__ Pack<typename OpOut<T, Op>::type, Vec<T>::N> run(const Vec<T>& a, const Vec<T>& b) {
+    Pack<typename OpOut<T, Op>::type, Vec<T>::N> r;
+#pragma unroll
+    for (int i = 0; i < Vec<T>::N; ++i) r.v[i] = Op::apply(a.v[i], b.v[i]);
+    return r;
+  }
+};
 template <typename T, typename Op>
 __device__ __forceinline__ Pack<typename OpOut<T, Op>::type, Vec<T>::N> apply_vec(const Vec<T>& a, const Vec<T>& b) {
-  Pack<typename OpOut<T, Op>::type, Vec<T>::N> r;
-#pragma unroll
-  for (int i = 0; i < Vec<T>::N; ++i) r.v[i] = Op::apply(a.v[i], b.v[i]);
-  return r;
+  return VecApply<T, Op>::run(a, b);
 }
 
 constexpr int kThreads = 256;
@@ -156,7 +165,7 @@ constexpr int kUnroll = 4;
 // ---- Same shape ------------------------------------------------------------------------
 // One CTA = one tile of kThreads*kUnroll vectors.  `nvec` full vectors, then a scalar tail.
 template <typename T, typename Op>
-__global__ void __launch_bounds__(kThreads) ew_same_kernel(const T* __restrict__ x,
+__global__ void __launch_bounds__(kThreads, sizeof(T) >= 2 ? 4 : 1) ew_same_kernel(const T* __restrict__ x,
                                                            const T* __restrict__ y,
                                                            typename OpOut<T, Op>::type* __restrict__ out,
                                                            int64_t nvec, int64_t numel) {
@@ -199,7 +208,7 @@ __global__ void __launch_bounds__(kThreads) ew_same_scalar_kernel(const T* x, co
 // the row advances by (kThreads mod P) per step, so the modular index is carried with
 // one add and one conditional subtract.  SWAP: the row operand is x (the left argument).
 template <typename T, typename Op, bool SWAP>
-__global__ void __launch_bounds__(kThreads) ew_inner_kernel(const T* __restrict__ big,
+__global__ void __launch_bounds__(kThreads, sizeof(T) >= 2 ? 4 : 1) ew_inner_kernel(const T* __restrict__ big,
                                                             const T* __restrict__ row,
                                                             typename OpOut<T, Op>::type* __restrict__ out,
                                                             int64_t nvec, uint32_t P, uint32_t step_mod) {

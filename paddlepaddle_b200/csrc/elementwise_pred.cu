@@ -70,6 +70,44 @@ PDB_HALF_CMP(__nv_bfloat16)
 PDB_HALF_CMP(__half)
 #undef PDB_HALF_CMP
 
+// 16-bit less_than / less_equal, eight elements at a time: four packed compares (HSETP2 — ordered, so a NaN operand gives
+// false exactly like the float comparison of the scalar functor) whose 0xFFFF / 0 lane masks are squeezed into one
+// byte per element.  The scalar route costs ~10 instructions per element (unpack both operands, compare, select, pack).
+template <typename T2>
+__device__ __forceinline__ uint32_t lt2_mask(T2 a, T2 b) { return __hlt2_mask(a, b); }
+template <typename T2>
+__device__ __forceinline__ uint32_t le2_mask(T2 a, T2 b) { return __hle2_mask(a, b); }
+template <typename T> struct Half2Of;
+template <> struct Half2Of<__nv_bfloat16> { using type = __nv_bfloat162; };
+template <> struct Half2Of<__half> { using type = __half2; };
+template <typename T, bool LE>
+__device__ __forceinline__ Pack<bool, 8> cmp8_packed(const Vec<T>& a, const Vec<T>& b) {
+  using T2 = typename Half2Of<T>::type;
+  const T2* pa = reinterpret_cast<const T2*>(&a);
+  const T2* pb = reinterpret_cast<const T2*>(&b);
+  uint32_t w[2];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const uint32_t m0 = (LE ? le2_mask(pa[2 * h], pb[2 * h]) : lt2_mask(pa[2 * h], pb[2 * h])) & 0x00010001u;
+    const uint32_t m1 = (LE ? le2_mask(pa[2 * h + 1], pb[2 * h + 1]) : lt2_mask(pa[2 * h + 1], pb[2 * h + 1])) & 0x00010001u;
+    // m0 = elements (4h, 4h+1) in bits 0 and 16; m1 = elements (4h+2, 4h+3): bytes b0 b1 b2 b3 of the output word
+    w[h] = (m0 & 0x1u) | ((m0 >> 8) & 0x100u) | ((m1 & 0x1u) << 16) | ((m1 << 8) & 0x01000000u);
+  }
+  Pack<bool, 8> r;
+  *reinterpret_cast<uint2*>(&r) = make_uint2(w[0], w[1]);
+  return r;
+}
+#define PDB_PACKED_CMP(T)                                                                                     \
+  template <> struct VecApply<T, LessThanOp<T>> {                                                             \
+    static __device__ __forceinline__ Pack<bool, 8> run(const Vec<T>& a, const Vec<T>& b) { return cmp8_packed<T, false>(a, b); } \
+  };                                                                                                          \
+  template <> struct VecApply<T, LessEqualOp<T>> {                                                            \
+    static __device__ __forceinline__ Pack<bool, 8> run(const Vec<T>& a, const Vec<T>& b) { return cmp8_packed<T, true>(a, b); } \
+  };
+PDB_PACKED_CMP(__nv_bfloat16)
+PDB_PACKED_CMP(__half)
+#undef PDB_PACKED_CMP
+
 // ---- logical: static_cast<bool>(a) op static_cast<bool>(b) ------------------------------------------------
 template <typename T> __device__ __forceinline__ bool truthy(T v) { return static_cast<bool>(v); }
 template <> __device__ __forceinline__ bool truthy<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v) != 0.0f; }
