@@ -52,6 +52,36 @@ __global__ void __launch_bounds__(kGThreads) expand_inner_kernel(const T* __rest
   for (int64_t r = r0; r < r1; ++r, dst += cols) st_stream(dst, v);
 }
 
+// the same for rows of up to K * kGThreads vectors: a thread keeps its K pieces of the row and a CTA writes WHOLE rows,
+// so every store instruction of a CTA covers a contiguous run of a row
+template <typename T, typename F, int K>
+__global__ void __launch_bounds__(kGThreads) expand_inner_rows_kernel(const T* __restrict__ g, T* __restrict__ out, int64_t rows,
+                                                                      int64_t cols, int64_t rows_per_cta, F f) {
+  constexpr int V = Vec<T>::N;
+  const int64_t nv = cols / V;
+  Vec<T> v[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const int64_t c = threadIdx.x + (int64_t)k * kGThreads;
+    if (c < nv) {
+      v[k] = ld_cached(g + c * V);
+#pragma unroll
+      for (int i = 0; i < V; ++i) v[k].v[i] = f(v[k].v[i]);
+    }
+  }
+  // rows are dealt round-robin (CTA b writes rows b, b + grid, ...): all CTAs move through x_grad together, one window of
+  // grid rows at a time — one slab per CTA means ~1200 write streams spread over the whole tensor (the same locality
+  // effect as in the split reductions, profiles/r1e_notes.txt)
+  (void)rows_per_cta;
+  const int64_t step = (int64_t)gridDim.x * cols;
+  T* dst = out + (int64_t)blockIdx.x * cols + (int64_t)threadIdx.x * V;
+  for (int64_t r = blockIdx.x; r < rows; r += gridDim.x, dst += step) {
+#pragma unroll
+    for (int k = 0; k < K; ++k)
+      if (threadIdx.x + (int64_t)k * kGThreads < nv) st_stream(dst + (int64_t)k * kGThreads * V, v[k]);
+  }
+}
+
 // x_grad[m][n] = f(g[m]); one CTA per (row, tile of kGThreads*kGUnroll vectors)
 template <typename T, typename F, bool VECTOR>
 __global__ void __launch_bounds__(kGThreads) expand_outer_kernel(const T* __restrict__ g, T* __restrict__ out, int64_t cols,
@@ -144,6 +174,16 @@ int launch_expand(const BroadcastPlan& p, const T* g, T* out, F f, cudaStream_t 
     case kBcastInner: {
       if (!(p.cols % V == 0 && is_aligned16(g) && is_aligned16(out))) break;
       const int64_t col_tiles = (p.cols / V + kGThreads - 1) / kGThreads;
+      if (col_tiles <= 8) {  // whole rows per CTA
+        int64_t slabs = std::min<int64_t>(p.rows, (int64_t)sm_count() * 8);
+        const int64_t rpc = (p.rows + slabs - 1) / slabs;
+        slabs = (p.rows + rpc - 1) / rpc;
+        if (col_tiles == 1) expand_inner_rows_kernel<T, F, 1><<<(unsigned)slabs, kGThreads, 0, st>>>(g, out, p.rows, p.cols, rpc, f);
+        else if (col_tiles == 2) expand_inner_rows_kernel<T, F, 2><<<(unsigned)slabs, kGThreads, 0, st>>>(g, out, p.rows, p.cols, rpc, f);
+        else if (col_tiles <= 4) expand_inner_rows_kernel<T, F, 4><<<(unsigned)slabs, kGThreads, 0, st>>>(g, out, p.rows, p.cols, rpc, f);
+        else expand_inner_rows_kernel<T, F, 8><<<(unsigned)slabs, kGThreads, 0, st>>>(g, out, p.rows, p.cols, rpc, f);
+        return after_launch("expand_inner_rows");
+      }
       // enough CTAs to fill the machine, but rows_per_cta large so that the one load per thread is amortised
       int64_t slabs = std::max<int64_t>(1, ((int64_t)sm_count() * 8 + col_tiles - 1) / col_tiles);
       slabs = std::min<int64_t>(std::min<int64_t>(slabs, p.rows), 65535);
