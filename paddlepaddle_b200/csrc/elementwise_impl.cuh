@@ -96,9 +96,6 @@ template <typename T> struct MinimumOp {
   template <> struct SubOp<T> {                                                                        \
     static __device__ __forceinline__ T apply(T a, T b) { return FROMF(__fsub_rn(TOF(a), TOF(b))); }   \
   };                                                                                                   \
-  template <> struct DivOp<T> {                                                                        \
-    static __device__ __forceinline__ T apply(T a, T b) { return FROMF(__fdiv_rn(TOF(a), TOF(b))); }   \
-  };                                                                                                   \
   template <> struct MaximumOp<T> {                                                                    \
     static __device__ __forceinline__ T apply(T a, T b) { return TOF(a) > TOF(b) ? a : b; }            \
   };                                                                                                   \
@@ -108,6 +105,29 @@ template <typename T> struct MinimumOp {
 PDB_HALF_OPS(__nv_bfloat16, __bfloat162float, __float2bfloat16_rn)
 PDB_HALF_OPS(__half, __half2float, __float2half_rn)
 #undef PDB_HALF_OPS
+template <> struct DivOp<__half> {  // 11-bit significands leave no such margin: the exact division
+  static __device__ __forceinline__ __half apply(__half a, __half b) {
+    return __float2half_rn(__fdiv_rn(__half2float(a), __half2float(b)));
+  }
+};
+// bf16 divide without the IEEE division sequence, still bit-identical to round_bf16(a / b):
+// the operands have 8-bit significands, a rounding boundary of the result (a midpoint between two bf16 values) has a
+// 9-bit odd significand m, and a / b = m would need a = m * b, which has at least 9 significant bits — so the exact
+// quotient is never a tie and sits at least 2^-17 (relative) from every boundary, while fa * rcp.approx(fb) is within ~2 ulp of
+// fp32 (2^-22): the approximate quotient always rounds to the same bf16 as the exact one.  That holds for normal
+// magnitudes; anything near the ends of the exponent range (and 0, inf, NaN) takes the exact division.
+template <> struct DivOp<__nv_bfloat16> {
+  static __device__ __forceinline__ __nv_bfloat16 apply(__nv_bfloat16 a, __nv_bfloat16 b) {
+    const float fa = __bfloat162float(a), fb = __bfloat162float(b);
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fb));  // 1 ulp; times fa: within ~2 ulp of fa / fb
+    const float q = fa * r;
+    const float ab = fabsf(fb), aq = fabsf(q);
+    const bool safe = ab > 7.9e-31f && ab < 1.2e30f && aq > 7.9e-31f && aq < 1.2e30f;  // 2^-100 .. 2^100
+    if (__builtin_expect(safe, 1)) return __float2bfloat16_rn(q);
+    return __float2bfloat16_rn(__fdiv_rn(fa, fb));  // a real branch: the exact sequence must not run for every element
+  }
+};
 // Integers: subtraction wraps; division truncates toward zero.  The reference's integer DivideFunctor
 // raises on a zero divisor (PADDLE_ENFORCE, a device-side assert on GPU); a kernel cannot throw, so a zero
 // divisor yields 0 here, and INT_MIN / -1 (undefined in C++) yields INT_MIN as two's-complement hardware does.
@@ -158,6 +178,37 @@ template <typename T, typename Op>
 __device__ __forceinline__ Pack<typename OpOut<T, Op>::type, Vec<T>::N> apply_vec(const Vec<T>& a, const Vec<T>& b) {
   return VecApply<T, Op>::run(a, b);
 }
+static __device__ __noinline__ float exact_div_f32(float a, float b) { return __fdiv_rn(a, b); }  // rare path, kept out of line
+
+// bf16 divide, a vector at a time: eight approximate quotients and ONE branch (all eight in the safe range, or the whole
+// vector through the exact division) instead of a divergent region per element
+template <>
+struct VecApply<__nv_bfloat16, DivOp<__nv_bfloat16>> {
+  static __device__ __forceinline__ Pack<__nv_bfloat16, 8> run(const Vec<__nv_bfloat16>& a, const Vec<__nv_bfloat16>& b) {
+    float fa[8], fb[8], q[8];
+    unpack_to_float<__nv_bfloat16>(a, fa);
+    unpack_to_float<__nv_bfloat16>(b, fb);
+    bool safe = true;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float r;
+      asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fb[i]));
+      q[i] = fa[i] * r;
+      const float ab = fabsf(fb[i]), aq = fabsf(q[i]);
+      safe = safe && ab > 7.9e-31f && ab < 1.2e30f && aq > 7.9e-31f && aq < 1.2e30f;
+    }
+    if (__builtin_expect(!safe, 0)) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) q[i] = exact_div_f32(fa[i], fb[i]);  // unrolled: the arrays must stay in registers
+    }
+    Vec<__nv_bfloat16> o;
+    pack_from_float<__nv_bfloat16>(q, o);
+    Pack<__nv_bfloat16, 8> r;
+    *reinterpret_cast<uint4*>(&r) = *reinterpret_cast<const uint4*>(&o);
+    return r;
+  }
+};
+
 
 constexpr int kThreads = 256;
 constexpr int kUnroll = 4;

@@ -247,3 +247,20 @@ def test_config2_sized_properties():
     assert int(paddle.sum(paddle.not_equal(m, paddle.minimum(x, y))).item()) == 0
     back = paddle.cast(paddle.cast(x, "float32"), "bfloat16")
     assert int(paddle.sum(paddle.not_equal(back, x)).item()) == 0
+
+
+def test_bf16_divide_is_exact_for_every_pair_of_operands():
+    """The bf16 divide skips the IEEE division sequence (approximate quotient, then one rounding — see DivOp<bf16>).
+    Checked here against round_bf16(float(a) / float(b)) with the exact fp32 division, for ALL 2^32 operand pairs,
+    bit for bit (NaN payloads included), using this library's own fp32 divide, cast and integer compare."""
+    allbits = torch.arange(65536, device="cuda", dtype=torch.int32).to(torch.int16)  # every bf16 bit pattern
+    y = allbits.view(torch.bfloat16)
+    yf = paddle.cast(y, "float32")
+    bad = 0
+    for lo in range(0, 65536, 8192):
+        x = allbits[lo:lo + 8192].view(torch.bfloat16).reshape(8192, 1)
+        fast = paddle.divide(x, y)
+        exact = paddle.cast(paddle.divide(paddle.cast(x, "float32"), yf), "bfloat16")
+        bad += int(paddle.sum(paddle.not_equal(fast.view(torch.int16), exact.view(torch.int16))).item())
+        del fast, exact
+    assert bad == 0, f"{bad} of 2^32 bf16 quotients differ from the correctly rounded result"
