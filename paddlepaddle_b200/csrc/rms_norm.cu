@@ -24,8 +24,8 @@ namespace pdb200 {
 
 struct AddRms { __device__ __forceinline__ float operator()(float a, float b) const { return a + b; } };
 
-template <typename T, int C, bool EXACT, bool RESID>
-__global__ void __launch_bounds__(512) rms_pipe_kernel(const T* __restrict__ x, const T* __restrict__ residual,
+template <typename T, int C, bool EXACT, bool RESID, int MAXT>
+__global__ void __launch_bounds__(MAXT, MAXT <= 256 ? 2 : 1) rms_pipe_kernel(const T* __restrict__ x, const T* __restrict__ residual,
                                                        const T* __restrict__ bias, const T* __restrict__ weight,
                                                        const T* __restrict__ nbias, T* __restrict__ out,
                                                        T* __restrict__ residual_out, float* __restrict__ inv_var,
@@ -64,11 +64,20 @@ __global__ void __launch_bounds__(512) rms_pipe_kernel(const T* __restrict__ x, 
     const T* sx = ring + (size_t)s * RS * D;
     float v[C * V];
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    Vec<T> raw[C], wv[C];  // the staged row first (all loads in flight), and the weights: their L1 latency hides behind
+#pragma unroll             // the CTA reduction instead of stalling the output loop
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + tid) * V;
+      if (EXACT || off < D) {
+        raw[c] = lds_vec(sx + off);
+        wv[c] = ld_cached(weight + off);
+      }
+    }
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       const int off = (c * nt + tid) * V;
       if (EXACT || off < D) {
-        unpack_to_float<T>(lds_vec(sx + off), &v[c * V]);
+        unpack_to_float<T>(raw[c], &v[c * V]);
         if constexpr (RESID) {
           float r[V];
           unpack_to_float<T>(lds_vec(sx + D + off), r);
@@ -110,7 +119,7 @@ __global__ void __launch_bounds__(512) rms_pipe_kernel(const T* __restrict__ x, 
       const int off = (c * nt + tid) * V;
       if (EXACT || off < D) {
         float w[V], o[V];
-        unpack_to_float<T>(ld_cached(weight + off), w);
+        unpack_to_float<T>(wv[c], w);
         if (nbias != nullptr) {
           float b[V];
           unpack_to_float<T>(ld_cached(nbias + off), b);
@@ -176,6 +185,7 @@ int rms_typed(const T* x, const T* residual, const T* bias, const T* weight, con
   const int64_t nchunk = D / VN;
   if (vec && nchunk >= 64 && nchunk <= 512 * 4 && rows >= 4 * (int64_t)sm_count()) {
     int C = nchunk >= 512 ? 4 : (nchunk >= (sizeof(T) == 2 ? 128 : 256) ? 2 : 1);
+    if (const int o = pipe_c_override("PDB200_RMS_PIPE_C")) C = o;  // tuning knob
     while (C < 4 && (nchunk + C - 1) / C > 512) C <<= 1;
     int threads = (int)((nchunk + C - 1) / C);
     threads = (threads + 31) / 32 * 32;
@@ -194,12 +204,14 @@ int rms_typed(const T* x, const T* residual, const T* bias, const T* weight, con
       return after_launch("rms_pipe");
     };
     int rc = -1;
-#define PDB_RMS(CC)                                                                                         \
-  if (residual) rc = exact ? launch(rms_pipe_kernel<T, CC, true, true>) : launch(rms_pipe_kernel<T, CC, false, true>); \
-  else rc = exact ? launch(rms_pipe_kernel<T, CC, true, false>) : launch(rms_pipe_kernel<T, CC, false, false>);
+#define PDB_RMS2(CC, MT)                                                                                               \
+  if (residual) rc = exact ? launch(rms_pipe_kernel<T, CC, true, true, MT>) : launch(rms_pipe_kernel<T, CC, false, true, MT>); \
+  else rc = exact ? launch(rms_pipe_kernel<T, CC, true, false, MT>) : launch(rms_pipe_kernel<T, CC, false, false, MT>);
+#define PDB_RMS(CC) if (threads <= 256) { PDB_RMS2(CC, 256) } else { PDB_RMS2(CC, 512) }
     if (threads <= 512) {
       if (C == 4) { PDB_RMS(4) } else if (C == 2) { PDB_RMS(2) } else { PDB_RMS(1) }
     }
+#undef PDB_RMS2
 #undef PDB_RMS
     if (rc >= 0) return rc;  // < 0: the pipeline does not fit, use the fallback
   }

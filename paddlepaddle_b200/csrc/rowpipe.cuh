@@ -150,6 +150,19 @@ inline bool pipe_geometry(Kern kern, int threads, size_t row_bytes, int want_cta
   for (; occ >= 1; --occ) {
     int st = static_cast<int>((sm_smem / occ - 2048) / row_bytes);  // 1 KB reserved + static barriers per CTA
     if (st > want_stages) st = want_stages;
+    // Keep about 64 KB of rows in flight per SM and no more: 2 stages instead of 3 gained 3 % (layer_norm, 16 KB rows,
+    // 2 CTAs), 10 % (layer_norm_grad), 8 % (rms_norm) and 8 % (softmax fp32, 8 KB rows, 3 CTAs); 4 stages were worse still
+    // (profiles/r1e_notes.txt).
+    // Never fewer than two stages: a CTA must be able to compute on one row while the next arrives.
+    {
+      int kb = 64;
+      if (const char* v = getenv("PDB200_PIPE_INFLIGHT_KB")) {
+        if (atoi(v) >= 8) kb = atoi(v);
+      }
+      int cap = static_cast<int>(((size_t)kb * 1024) / ((size_t)occ * row_bytes));
+      if (cap < 2) cap = 2;
+      if (st > cap) st = cap;
+    }
     for (; st >= 2; --st) {
       const size_t smem = (size_t)st * row_bytes;
       int pct = static_cast<int>((occ * (smem + 2048) * 100 + sm_smem - 1) / sm_smem);
