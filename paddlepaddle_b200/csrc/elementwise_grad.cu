@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(kTmaThreads) mulgrad_inner_tma_kernel(const __
                                                                         const T* __restrict__ rowv, T* __restrict__ dbig,
                                                                         typename AccType<T>::type* __restrict__ part,
                                                                         int64_t rows, int64_t cols, int64_t seg,
-                                                                        int splits, int64_t col_tiles) {
+                                                                        int splits, int64_t col_tiles, int nstages) {
   using A = typename AccType<T>::type;
   using Sum = SumOp<A>;
   constexpr int V = Vec<T>::N;
@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(kTmaThreads) mulgrad_inner_tma_kernel(const __
     tma_load_2d(dst + (size_t)kTmaTileRows * TI, &map_big, c0, (int32_t)(begin + t * kTmaTileRows), &full[s]);
   };
   if (tid == 0)
-    for (int s = 0; s < kMgStages && s < ntiles; ++s) issue(s, s);
+    for (int s = 0; s < nstages && s < ntiles; ++s) issue(s, s);
   Vec<T> yv;
   if (WANT_DBIG && col_ok) yv = ld_cached(rowv + col);
   A acc[V];
@@ -213,11 +213,11 @@ __global__ void __launch_bounds__(kTmaThreads) mulgrad_inner_tma_kernel(const __
       }
     }
     __syncthreads();
-    if (tid == 0 && t + kMgStages < ntiles) {
+    if (tid == 0 && t + nstages < ntiles) {
       fence_proxy_async_smem();
-      issue(s, t + kMgStages);
+      issue(s, t + nstages);
     }
-    if (++s == kMgStages) {
+    if (++s == nstages) {
       s = 0;
       phase ^= 1;
     }
@@ -281,14 +281,19 @@ struct MulGradInner {
     const size_t smem = (size_t)kMgStages * 2 * kTmaTileRows * TI * sizeof(T) + (size_t)8 * TI * sizeof(A);
     A* part = static_cast<A*>(ws);
     const int64_t blocks = g.col_tiles * g.splits;
+    static const int nstages = [] {  // tuning knob; the ring is allocated for kMgStages
+      const char* v = getenv("PDB200_MULGRAD_STAGES");
+      const int n = v ? atoi(v) : kMgStages;
+      return n >= 2 && n <= kMgStages ? n : kMgStages;
+    }();
     if (dbig) {
       auto kern = mulgrad_inner_tma_kernel<T, true>;
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      kern<<<(unsigned)blocks, kTmaThreads, smem, st>>>(md, mb, rowv, dbig, part, rows, cols, g.seg, g.splits, g.col_tiles);
+      kern<<<(unsigned)blocks, kTmaThreads, smem, st>>>(md, mb, rowv, dbig, part, rows, cols, g.seg, g.splits, g.col_tiles, nstages);
     } else {
       auto kern = mulgrad_inner_tma_kernel<T, false>;
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      kern<<<(unsigned)blocks, kTmaThreads, smem, st>>>(md, mb, rowv, dbig, part, rows, cols, g.seg, g.splits, g.col_tiles);
+      kern<<<(unsigned)blocks, kTmaThreads, smem, st>>>(md, mb, rowv, dbig, part, rows, cols, g.seg, g.splits, g.col_tiles, nstages);
     }
     const int rc = after_launch("mulgrad_inner_tma");
     if (rc != PDB200_OK) return rc;

@@ -37,7 +37,7 @@ template <typename T, typename O, typename Op, typename Fin>
 __global__ void __launch_bounds__(kTmaThreads) reduce_cols_tma_kernel(const __grid_constant__ CUtensorMap map,
                                                                       O* __restrict__ out, int64_t red, int64_t inner,
                                                                       int64_t seg, int splits, int64_t col_tiles,
-                                                                      Fin fin) {
+                                                                      Fin fin, int nstages) {
   using A = typename Op::Acc;
   constexpr int V = Vec<T>::N;
   constexpr int TI = 32 * V;  // tile width in elements (512 bytes)
@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(kTmaThreads) reduce_cols_tma_kernel(const __gr
   }
   __syncthreads();
   if (tid == 0) {
-    for (int s = 0; s < kTmaStages && s < ntiles; ++s) {
+    for (int s = 0; s < nstages && s < ntiles; ++s) {
       mbar_expect_tx(&full[s], kTileBytes);
       tma_load_2d(ring + (size_t)s * kTmaTileRows * TI, &map, c0, (int32_t)(row_base + begin + (int64_t)s * kTmaTileRows),
                   &full[s]);
@@ -90,13 +90,13 @@ __global__ void __launch_bounds__(kTmaThreads) reduce_cols_tma_kernel(const __gr
       }
     }
     __syncthreads();  // every thread is done with stage s
-    if (tid == 0 && t + kTmaStages < ntiles) {
+    if (tid == 0 && t + nstages < ntiles) {
       fence_proxy_async_smem();
       mbar_expect_tx(&full[s], kTileBytes);
       tma_load_2d(ring + (size_t)s * kTmaTileRows * TI, &map, c0,
-                  (int32_t)(row_base + begin + (t + kTmaStages) * kTmaTileRows), &full[s]);
+                  (int32_t)(row_base + begin + (t + nstages) * kTmaTileRows), &full[s]);
     }
-    if (++s == kTmaStages) {
+    if (++s == nstages) {
       s = 0;
       phase ^= 1;
     }

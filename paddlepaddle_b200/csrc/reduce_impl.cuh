@@ -561,7 +561,12 @@ int launch_pass(const ReducePass& ps, const PassGeom& g, bool vec, const T* x, O
           cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tma);
           if (dev >= 0 && dev < 64) attr_set[dev] = true;
         }
-        kern<<<(unsigned)blocks, kTmaThreads, smem_tma, st>>>(map, out, ps.red, ps.inner, g.seg, g.splits, g.col_tiles, fin);
+        static const int nstages = [] {  // tuning knob; the ring is allocated for kTmaStages
+          const char* v = getenv("PDB200_TMA_COLS_STAGES");
+          const int n = v ? atoi(v) : kTmaStages;
+          return n >= 2 && n <= kTmaStages ? n : kTmaStages;
+        }();
+        kern<<<(unsigned)blocks, kTmaThreads, smem_tma, st>>>(map, out, ps.red, ps.inner, g.seg, g.splits, g.col_tiles, fin, nstages);
         return after_launch("reduce_cols_tma");
       }
     }
