@@ -514,8 +514,9 @@ int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, typename AccT
   auto launch = [&](auto kern) -> int {
     int per_sm = 0, stages = 0;
     size_t smem = 0;
-    int want = 768 / threads;  // ~768 threads per SM, 2..6 CTAs, 3 rows in flight each
-    want = want < 2 ? 2 : (want > 6 ? 6 : want);
+    int want = 768 / threads;  // ~768 threads per SM, 2..6 CTAs; a 512-thread CTA (rows of 16-32 KB) runs alone:
+    const int lo = threads >= 512 ? 1 : 2;  // two of them put 128 KB of rows in flight, fp32 [65536,8192] 0.726 vs 0.634 ms
+    want = want < lo ? lo : (want > 6 ? 6 : want);
     if (!pipe_geometry(kern, threads, row_bytes, want, 3, &per_sm, &stages, &smem)) return -1;
     int64_t grid = (int64_t)per_sm * sm_count();
     if (grid > outer) grid = outer;
