@@ -153,6 +153,9 @@ int try_softmax_grad_pipe(const T* y, const T* dy, T* dx, int64_t outer, int64_t
     size_t smem = 0;
     int want = 768 / threads;
     want = want < 2 ? 2 : (want > 6 ? 6 : want);
+    // ~64 KB of rows in flight per SM at two stages (profiles/r1e_notes.txt): bf16 [.,2048] 6 -> 4 CTAs 1.01 -> 0.93 ms
+    const int by_bytes = (int)((64 * 1024) / (2 * stage_bytes));
+    if (want > by_bytes) want = by_bytes < 1 ? 1 : by_bytes;
     if (!pipe_geometry(kern, threads, stage_bytes, want, 3, &per_sm, &stages, &smem)) return -1;
     int64_t grid = (int64_t)per_sm * sm_count();
     if (grid > outer) grid = outer;
