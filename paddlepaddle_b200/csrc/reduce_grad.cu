@@ -175,7 +175,13 @@ int launch_expand(const BroadcastPlan& p, const T* g, T* out, F f, cudaStream_t 
       if (!(p.cols % V == 0 && is_aligned16(g) && is_aligned16(out))) break;
       const int64_t col_tiles = (p.cols / V + kGThreads - 1) / kGThreads;
       if (col_tiles <= 8) {  // whole rows per CTA
-        int64_t slabs = std::min<int64_t>(p.rows, (int64_t)sm_count() * 8);
+        // many short-lived CTAs of ~4 rows each, not a persistent grid: bf16 [131072,4096] 0.182 ms with 1184
+        // persistent CTAs, 0.151 ms (7.1 TB/s) with 4 rows per CTA, 0.158 with 16, 0.173 with 64 (profiles/r1e_notes.txt)
+        int rows_each = 4;
+        if (const char* v = getenv("PDB200_EXPAND_ROWS_PER_CTA")) {  // tuning knob
+          if (atoi(v) >= 1) rows_each = atoi(v);
+        }
+        int64_t slabs = std::min<int64_t>(std::max<int64_t>(1, p.rows / rows_each), 0x7fffffffLL);
         const int64_t rpc = (p.rows + slabs - 1) / slabs;
         slabs = (p.rows + rpc - 1) / rpc;
         if (col_tiles == 1) expand_inner_rows_kernel<T, F, 1><<<(unsigned)slabs, kGThreads, 0, st>>>(g, out, p.rows, p.cols, rpc, f);
