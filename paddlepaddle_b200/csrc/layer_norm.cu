@@ -533,6 +533,9 @@ int layer_norm_typed(const T* x, const P* scale, const P* bias, T* y, void* mean
       want = want < 2 ? 2 : (want > 4 ? 4 : want);
       if (!pipe_geometry(kern, threads, row_bytes, want, 3, &per_sm, &stages, &smem)) return -1;
       int64_t grid = (int64_t)per_sm * sm_count();
+      if (const char* v = getenv("PDB200_PIPE_ROWS_PER_CTA")) {  // tuning knob: short-lived CTAs instead of a persistent grid
+        if (atoi(v) >= 1) grid = std::max<int64_t>(grid, rows / atoi(v));
+      }
       if (grid > rows) grid = rows;
       kern<<<(unsigned)grid, threads, smem, st>>>(x, scale, bias, y, m, v, rows, (int)D, stages, eps, inv_d, pipe_contiguous());
       return after_launch("ln_pipe");

@@ -519,6 +519,13 @@ int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, typename AccT
     want = want < lo ? lo : (want > 6 ? 6 : want);
     if (!pipe_geometry(kern, threads, row_bytes, want, 3, &per_sm, &stages, &smem)) return -1;
     int64_t grid = (int64_t)per_sm * sm_count();
+    // 64-thread CTAs (16-bit rows of 2048): many short-lived CTAs of 4 rows beat the persistent grid, 0.660 -> 0.620 ms on
+    // bf16 [8,32,2048,2048]; 256-thread CTAs lose (fp32: 1.305 -> 1.49 ms), so they stay persistent (profiles/r1e_notes.txt)
+    if (threads <= 64) grid = std::max<int64_t>(grid, outer / 4);
+    if (const char* v = getenv("PDB200_PIPE_ROWS_PER_CTA")) {  // tuning knob
+      if (atoi(v) >= 1) grid = std::max<int64_t>((int64_t)per_sm * sm_count(), outer / atoi(v));
+    }
+    if (grid > 0x7fffffffLL) grid = 0x7fffffffLL;
     if (grid > outer) grid = outer;
     kern<<<(unsigned)grid, threads, smem, st>>>(x, y, outer, (int)dim, stages, pipe_contiguous(), stats);
     return after_launch("softmax_pipe");
