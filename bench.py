@@ -16,8 +16,13 @@ Headline workload (config.workload): BASELINE.json configs[1], `paddle.add` bf16
   cpu_baseline: the reference's own CPU kernel (oracle/_ref, compiled from Paddle's sources) on a
             bounded sample of the same workload, 1 thread (how Paddle runs it).
   ops     : the other BASELINE configs (C1, C2 int32, C3, C4, C5 shard) timed the same way —
-            context for the metric "reduce/broadcast/layer_norm HBM GB/s", not the headline.
-`--impl reference` times the reference CPU implementation (all host threads, bounded sample).
+            context for the metric "reduce/broadcast/layer_norm HBM GB/s", not the headline.  Every
+            row is the MAX over ranks (barrier, then all_reduce(MAX) of the device time).
+  config.per_config : the same rows in compact form {C1..C5: GB/s, fraction of 8 TB/s}; with N > 1
+            C3 and C4 are ALSO run batch-sharded (65536/N and 2^21/N rows per rank: strong scaling of
+            the fixed tensor, aggregate GB/s = whole-tensor bytes / max-over-ranks time) next to the
+            full-config-per-rank rows (weak scaling).
+`--impl reference` times the reference CPU implementation on the SAME workload (all host threads).
 Inputs are far larger than the 126 MB L2 (>= 1 GiB per operand), so no L2 flush is needed.
 """
 import argparse
@@ -36,6 +41,8 @@ C2_SHAPE = (64, 2048, 4096)
 C2_ROWS = C2_SHAPE[0] * C2_SHAPE[1]
 C2_COLS = C2_SHAPE[2]
 C2_BYTES_BF16 = 2 * (C2_ROWS * C2_COLS * 2) + C2_COLS * 2  # 2,147,491,840
+METRIC = "broadcast add HBM GB/s (algorithmic bytes / time)"
+WORKLOAD = "paddle.add bf16 [64,2048,4096] + [4096] (BASELINE configs[1])"
 
 
 def measured_traffic(name="r1h_add_bf16.txt"):
@@ -133,11 +140,14 @@ def _ref_lib():
 
 def _cpu_add_sample(oracle, rows, threads):
     """Time add bf16 [rows,4096] + [4096] on the host with `threads` threads (disjoint row slabs;
-    ctypes releases the GIL, each call is the reference's single-threaded kernel).  Returns seconds."""
+    ctypes releases the GIL, each call is the reference's single-threaded kernel).  Returns a closure whose call runs
+    one pass and returns seconds.  x is a seeded 4096-row block of N(0,1) repeated to `rows` rows (drawing 2^29 normals
+    on the host would take longer than the measurement; the add's speed does not depend on the values)."""
     import numpy as np
     import oracle_lib as O
     rng = np.random.default_rng(2)
-    x = oracle.f32_to_bf16(rng.standard_normal((rows, C2_COLS)).astype(np.float32))
+    blk = oracle.f32_to_bf16(rng.standard_normal((min(rows, 4096), C2_COLS)).astype(np.float32))
+    x = np.ascontiguousarray(np.tile(blk, ((rows + blk.shape[0] - 1) // blk.shape[0], 1))[:rows])
     y = oracle.f32_to_bf16(rng.standard_normal((C2_COLS,)).astype(np.float32))
     slabs = np.array_split(np.arange(rows), threads)
 
@@ -157,22 +167,21 @@ def _cpu_add_sample(oracle, rows, threads):
 
 
 def cpu_baseline_obj(budget_s=12.0):
-    """1-thread reference CPU kernel on a bounded sample of the headline workload."""
+    """1-thread reference CPU kernel (how Paddle runs it) on the WHOLE headline workload, best of the passes that fit
+    the budget (one pass is ~1.2 s)."""
     oracle, kind = _ref_lib()
-    rows = 8192  # 1/16 of the workload: 64 MiB in, 64 MiB out
+    rows = C2_ROWS
     run = _cpu_add_sample(oracle, rows, 1)
-    run()  # warm-up
+    run()  # warm-up (first touch of the 1 GiB output)
     best, t_used = None, 0.0
     while t_used < budget_s and (best is None or t_used < 3 * best + 1):
         dt = run()
         t_used += dt
         best = dt if best is None else min(best, dt)
-        if t_used > budget_s:
-            break
     nbytes = 2 * rows * C2_COLS * 2 + C2_COLS * 2
     return {"value": round(nbytes / best / 1e9, 3), "unit": "GB/s", "cores": 1, "kind": kind,
-            "sample": f"add bf16 [{rows},{C2_COLS}]+[{C2_COLS}] = 1/16 of the workload, best of repeats within "
-                      f"{budget_s:.0f} s, phi::funcs::ElementwiseCompute<AddFunctor<bfloat16>> on 1 thread"}
+            "sample": f"add bf16 [{rows},{C2_COLS}]+[{C2_COLS}] = the whole workload, best pass within {budget_s:.0f} s, "
+                      "phi::funcs::ElementwiseCompute<AddFunctor<bfloat16>> on 1 thread"}
 
 
 def run_reference_arm(args):
@@ -181,8 +190,11 @@ def run_reference_arm(args):
         return 0
     oracle, kind = _ref_lib()
     cores = os.cpu_count() or 1
-    rows = 1024 * cores if cores <= 32 else 32768  # bounded sample per step
-    rows = min(rows, C2_ROWS)
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except Exception:
+        pass
+    rows = C2_ROWS  # the same rows the GPU arm processes per step (one pass is ~0.1-0.2 s on 16 threads)
     run = _cpu_add_sample(oracle, rows, cores)
     for _ in range(args.warmup):
         run()
@@ -190,17 +202,17 @@ def run_reference_arm(args):
     for _ in range(args.steps):
         t += run()
     ms = t / args.steps * 1e3
-    nbytes = 2 * rows * C2_COLS * 2 + C2_COLS * 2
+    nbytes = C2_BYTES_BF16
     val = round(nbytes / (ms / 1e3) / 1e9, 3)
     line = {
-        "impl": "reference", "metric": "broadcast add HBM GB/s (algorithmic bytes / time)", "value": val, "unit": "GB/s",
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "GB/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": "paddle.add bf16 [64,2048,4096] + [4096] (BASELINE configs[1])",
-                   "sample": f"each step = add bf16 [{rows},{C2_COLS}]+[{C2_COLS}] on the host"},
+        "config": {"workload": WORKLOAD,
+                   "sample": f"each step = the whole workload, add bf16 [{rows},{C2_COLS}]+[{C2_COLS}], on the host"},
         "cpu_baseline": {"value": val, "unit": "GB/s", "cores": cores, "kind": kind,
                          "sample": f"[{rows},{C2_COLS}] rows split over {cores} threads, each running the reference's "
-                                   "single-threaded CPU kernel"},
+                                   "single-threaded CPU kernel on its slab"},
         "e2e": {"value": val, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -248,25 +260,46 @@ def time_op(torch, fn, steps, warmup, graph_reps=0):
 
 
 def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
-    """BASELINE configs other than the headline, each: algorithmic bytes, ms, GB/s, fraction."""
+    """BASELINE configs other than the headline, each: algorithmic bytes, ms (MAX over ranks), GB/s, fraction.
+    Returns (rows, per_config): the full table and its compact form for `config.per_config`."""
     F = paddle.nn.functional
     out = []
+    per_config = {}
 
-    def rec(name, nbytes, fn, elems, graph_reps=0):
-        ms = time_op(torch, fn, steps, warmup, graph_reps)
-        gbs = nbytes / (ms / 1e3) / 1e9
-        out.append({"op": name, "algorithmic_bytes": nbytes, "ms": round(ms, 4), "GB/s": round(gbs, 1),
-                    "elements/s": round(elems / (ms / 1e3), 1), "frac_of_measured_peak": round(gbs / peak, 4),
-                    "frac_of_8TBps": round(gbs / 8000.0, 4)})
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def rec(name, nbytes, fn, elems, graph_reps=0, key=None, ranks_share=False):
+        """nbytes / elems: what ONE rank processes — or, with ranks_share, what all ranks process together (a tensor
+        sharded over the ranks: strong scaling).  Aggregate GB/s = bytes of all ranks / max-over-ranks time."""
+        if world > 1:
+            dist.barrier()
+        ms = max_over_ranks(time_op(torch, fn, steps, warmup, graph_reps))
+        total_bytes = nbytes if ranks_share else nbytes * world
+        gbs = total_bytes / (ms / 1e3) / 1e9
+        row = {"op": name, "algorithmic_bytes": total_bytes, "ms": round(ms, 4), "GB/s": round(gbs, 1),
+               "elements/s": round((elems if ranks_share else elems * world) / (ms / 1e3), 1),
+               "frac_of_measured_peak_per_gpu": round(gbs / world / peak, 4), "frac_of_8TBps_per_gpu": round(gbs / world / 8000.0, 4)}
+        out.append(row)
+        if key:
+            per_config[key] = {"GB/s": row["GB/s"], "ms": row["ms"], "frac_8TBps_per_gpu": row["frac_of_8TBps_per_gpu"]}
         torch.cuda.empty_cache()
+        return row
 
+    from paddlepaddle_b200 import distributed as pdist
     g = torch.Generator(device="cuda")
     g.manual_seed(100 + rank)
     peer = None  # NVLink peer-memory exchange group, created on first use when world > 1
     # C1 sum fp32 [4096,4096] axis=-1 (67 MB: fits L2 — reported, not a steady-state number)
     x = torch.rand((4096, 4096), device="cuda", generator=g)
     rec("C1 sum fp32 [4096,4096] axis=-1 (67 MB: L2-resident between launches; 20 launches per CUDA graph replay)",
-        4096 * 4096 * 4 + 4096 * 4, lambda: paddle.sum(x, axis=-1), 4096 * 4096, graph_reps=20)
+        4096 * 4096 * 4 + 4096 * 4, lambda: paddle.sum(x, axis=-1), 4096 * 4096, graph_reps=20, key="C1_sum_fp32_graph")
+    rec("C1 sum fp32 [4096,4096] axis=-1, eager calls through the Python mirror (host cost per call included)",
+        4096 * 4096 * 4 + 4096 * 4, lambda: paddle.sum(x, axis=-1), 4096 * 4096, key="C1_sum_fp32_eager")
     del x
     # C2 int32
     xi = torch.randint(-2**30, 2**30, C2_SHAPE, device="cuda", dtype=torch.int32, generator=g)
@@ -274,24 +307,40 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
     oi = torch.empty_like(xi)
     from paddlepaddle_b200.ops import _elementwise
     rec("C2 add int32 [64,2048,4096]+[4096]", 2 * C2_ROWS * C2_COLS * 4 + C2_COLS * 4,
-        lambda: _elementwise("pdb200_add", xi, yi, out=oi), C2_ROWS * C2_COLS)
+        lambda: _elementwise("pdb200_add", xi, yi, out=oi), C2_ROWS * C2_COLS, key="C2_add_int32")
     del xi, yi, oi
-    # C3 layer_norm bf16 [65536,8192] (per rank: 65536/world rows when sharded — here the full config per GPU)
+    # C3 layer_norm bf16 [65536,8192]: the full config on every rank (weak) and, with N > 1, batch-sharded (strong)
     rows, D = 65536, 8192
     xl = torch.randn((rows, D), device="cuda", generator=g).to(torch.bfloat16)
     w = (torch.rand(D, device="cuda", generator=g) + 0.5).to(torch.bfloat16)
     b = (torch.rand(D, device="cuda", generator=g) - 0.5).to(torch.bfloat16)
-    rec("C3 layer_norm bf16 [65536,8192]", 2 * rows * D * 2 + 2 * rows * 4 + 2 * D * 2, lambda: F.layer_norm(xl, [D], w, b), rows * D)
+    c3_bytes = 2 * rows * D * 2 + 2 * rows * 4 + 2 * D * 2
+    rec("C3 layer_norm bf16 [65536,8192] (whole config per rank)", c3_bytes, lambda: F.layer_norm(xl, [D], w, b), rows * D,
+        key="C3_layer_norm_bf16")
+    if world > 1:
+        r0, r1 = pdist.shard_rows(rows, rank, world)
+        xs_ = xl[r0:r1]
+        rec(f"C3 layer_norm bf16 [65536,8192] batch-sharded: {r1 - r0} rows per rank, eager calls", c3_bytes,
+            lambda: F.layer_norm(xs_, [D], w, b), rows * D, key="C3_layer_norm_bf16_sharded", ranks_share=True)
+        rec(f"C3 layer_norm bf16 [65536,8192] batch-sharded: {r1 - r0} rows per rank, 10 launches per CUDA graph replay", c3_bytes,
+            lambda: F.layer_norm(xs_, [D], w, b), rows * D, graph_reps=10, key="C3_layer_norm_bf16_sharded_graph", ranks_share=True)
+        del xs_
     del xl
     # C4 softmax [32,32,2048,2048] last axis, bf16 and fp32
     for dt, nm, eb in ((torch.bfloat16, "bf16", 2), (torch.float32, "fp32", 4)):
         n = 32 * 32 * 2048 * 2048
         xs = torch.empty((32, 32, 2048, 2048), device="cuda", dtype=dt)
-        xs.view(-1)[:] = 0
         chunk = 1 << 28
         for i in range(0, n, chunk):
             xs.view(-1)[i:i + chunk] = (torch.randn(chunk, device="cuda", generator=g) * 2).to(dt)
-        rec(f"C4 softmax {nm} [32,32,2048,2048] axis=-1", 2 * n * eb, lambda: F.softmax(xs, axis=-1), n)
+        rec(f"C4 softmax {nm} [32,32,2048,2048] axis=-1 (whole config per rank)", 2 * n * eb, lambda: F.softmax(xs, axis=-1), n,
+            key=f"C4_softmax_{nm}")
+        if world > 1:
+            r0, r1 = pdist.shard_rows(32 * 32 * 2048, rank, world)
+            sh = xs.view(-1, 2048)[r0:r1]
+            rec(f"C4 softmax {nm} [32,32,2048,2048] batch-sharded: {r1 - r0} rows per rank", 2 * n * eb,
+                lambda: F.softmax(sh, axis=-1), n, key=f"C4_softmax_{nm}_sharded", ranks_share=True)
+            del sh
         del xs
     # Widened rows, at the shapes of the configs they sit next to
     xa = torch.randn(C2_SHAPE, device="cuda", generator=g).to(torch.bfloat16)
@@ -304,9 +353,24 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
     n2 = C2_ROWS * C2_COLS
     rec("next: less_than bf16 [64,2048,4096] vs [4096] -> bool", n2 * 2 + n2 + C2_COLS * 2,
         lambda: _elementwise("pdb200_compare", xa, ya, out=ob, op=0, out_dtype=torch.bool), n2)
+    rec("next: equal bf16 [64,2048,4096] vs [4096] -> bool", n2 * 2 + n2 + C2_COLS * 2,
+        lambda: _elementwise("pdb200_compare", xa, ya, out=ob, op=4, out_dtype=torch.bool), n2)
     rec("next: scale bf16 [64,2048,4096] (2.5*x + 1)", 2 * n2 * 2, lambda: paddle.scale(xa, 2.5, 1.0), n2)
     rec("next: cast bf16 -> fp32 [64,2048,4096]", n2 * 2 + n2 * 4, lambda: paddle.cast(xa, "float32"), n2)
     rec("next: where bf16 [64,2048,4096] (bool, x, y)", n2 + 3 * n2 * 2, lambda: paddle.where(ob, xa, oa), n2)
+    # the routes no BASELINE config takes: general N-D broadcast, column (outer) broadcast, softmax along a middle axis
+    xg = xa.view(64, 2048, 1, 4096)[:, :, :, :2048].contiguous().view(64, 2048, 1, 2048)
+    yg = torch.randn((64, 1, 2, 2048), device="cuda", generator=g).to(torch.bfloat16)
+    ng = 64 * 2048 * 2 * 2048
+    rec("route: add bf16 [64,2048,1,2048]+[64,1,2,2048] (general N-D walk)", ng * 2 + xg.numel() * 2 + yg.numel() * 2,
+        lambda: paddle.add(xg, yg), ng)
+    del xg, yg
+    yc = torch.randn((C2_ROWS, 1), device="cuda", generator=g).to(torch.bfloat16)
+    rec("route: add bf16 [131072,4096]+[131072,1] (column operand)", C2_BYTES_BF16 - C2_COLS * 2 + C2_ROWS * 2,
+        lambda: _elementwise("pdb200_add", xa.view(C2_ROWS, C2_COLS), yc, out=oa.view(C2_ROWS, C2_COLS)), n2)
+    del yc
+    xm_ = xa.view(64, 2048, 4096)
+    rec("route: softmax bf16 [64,2048,4096] axis=1 (strided axis)", 2 * n2 * 2, lambda: F.softmax(xm_, axis=1), n2)
     # backward of config 2: multiply_grad reads dout and x once, writes dx and the 4096 column sums (one pass);
     # add_grad = column sums of dout only (dx aliases dout in the reference's in-place pass, so it is not asked for)
     rec("next: multiply_grad bf16 [64,2048,4096]*[4096] (dx, dy)", 3 * n2 * 2 + 2 * C2_COLS * 2,
@@ -316,11 +380,21 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
     # mean_grad: a write-only stream (out_grad is one row)
     rec("next: mean_grad bf16 -> [64,2048,4096] (axis 0,1)", n2 * 2 + C2_COLS * 2,
         lambda: paddle.mean_grad(xa, ya, axis=[0, 1]), n2)
-    del xa, ya, oa, ob
+    del xa, ya, oa, ob, xm_
     n = 8 * 32 * 2048 * 2048
     yy = torch.rand((8, 32, 2048, 2048), device="cuda", generator=g).to(torch.bfloat16)
     dyy = torch.randn((8, 32, 2048, 2048), device="cuda", generator=g).to(torch.bfloat16)
     rec("next: log_softmax bf16 [8,32,2048,2048] axis=-1", 2 * n * 2, lambda: F.log_softmax(yy, axis=-1), n)
+    if hasattr(F, "softmax_mask_fuse"):
+        mk = torch.randn((8, 1, 2048, 2048), device="cuda", generator=g).to(torch.bfloat16)
+        rec("next: softmax_mask_fuse bf16 x[8,32,2048,2048] + mask[8,1,2048,2048]", 2 * n * 2 + mk.numel() * 2,
+            lambda: F.softmax_mask_fuse(yy, mk), n, key="fused_softmax_mask_bf16")
+        # the causal form reads and computes only col <= row: (S+1)/2S of the input; the output is written whole
+        S = 2048
+        tri_bytes = n * 2 * (S + 1) // (2 * S) + n * 2
+        rec("next: softmax_mask_fuse_upper_triangle bf16 [8,32,2048,2048] (reads col <= row only)", tri_bytes,
+            lambda: F.softmax_mask_fuse_upper_triangle(yy), n, key="fused_softmax_mask_upper_triangle_bf16")
+        del mk
     xl32 = torch.randn((65536, 8192), device="cuda", generator=g)
     lbl = torch.randint(0, 8192, (65536, 1), device="cuda", generator=g)
     rec("next: softmax_with_cross_entropy fp32 [65536,8192] hard labels (softmax + loss)", 2 * 65536 * 8192 * 4 + 65536 * 12,
@@ -333,9 +407,28 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
         lambda: F.fused_rms_norm(xr_, wr_, None, 1e-6, 1), 65536 * 8192)
     rec("next: rms_norm bf16 [65536,8192] with fused residual add (out + residual_out)", 4 * 65536 * 8192 * 2 + 8192 * 2 + 65536 * 4,
         lambda: F.fused_rms_norm(xr_, wr_, None, 1e-6, 1, residual=rr_), 65536 * 8192)
+    if hasattr(F, "fused_bias_dropout_residual_layer_norm"):
+        br_ = (torch.rand(8192, device="cuda", generator=g) - 0.5).to(torch.bfloat16)
+        rec("next: fused_bias_dropout_residual_layer_norm bf16 [65536,8192] (dropout off: y + bias_dropout_residual_out)",
+            4 * 65536 * 8192 * 2 + 3 * 8192 * 2 + 2 * 65536 * 4,
+            lambda: F.fused_bias_dropout_residual_layer_norm(xr_, rr_, br_, wr_, br_, dropout_rate=0.0), 65536 * 8192,
+            key="fused_bias_dropout_residual_layer_norm_bf16")
+        del br_
     del xr_, rr_, wr_
     rec("next: softmax_grad bf16 [8,32,2048,2048] axis=-1", 3 * n * 2, lambda: F.softmax_grad(yy, dyy, axis=-1), n)
     del yy, dyy
+    # vocabulary-sized rows: the thread-block-cluster route
+    xv = torch.randn((4096, 128256), device="cuda", generator=g).to(torch.bfloat16)
+    rec("route: softmax bf16 [4096,128256] (cluster route, 250 KB rows)", 2 * xv.numel() * 2, lambda: F.softmax(xv, axis=-1),
+        xv.numel(), key="softmax_bf16_vocab_128256")
+    wv = (torch.rand(128256, device="cuda", generator=g) + 0.5).to(torch.bfloat16)
+    rec("route: layer_norm bf16 [4096,128256] (cluster route)", 2 * xv.numel() * 2 + 2 * 128256 * 2 + 2 * 4096 * 4,
+        lambda: F.layer_norm(xv, [128256], wv, wv), xv.numel(), key="layer_norm_bf16_vocab_128256")
+    del xv, wv
+    xv = torch.randn((64, 1048576), device="cuda", generator=g).to(torch.bfloat16)
+    rec("route: softmax bf16 [64,1048576] (cluster route, 2 MB rows)", 2 * xv.numel() * 2, lambda: F.softmax(xv, axis=-1),
+        xv.numel(), key="softmax_bf16_row_1M")
+    del xv
     rows, D = 65536, 8192
     xl = torch.randn((rows, D), device="cuda", generator=g).to(torch.bfloat16)
     dl = torch.randn((rows, D), device="cuda", generator=g).to(torch.bfloat16)
@@ -345,18 +438,21 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
     rec("next: layer_norm_grad bf16 [65536,8192] (dx, dscale, dbias)", 3 * rows * D * 2 + 2 * rows * 4 + 3 * D * 2,
         lambda: F.layer_norm_grad(xl, [D], w, m_, v_, dl), rows * D)
     del xl, dl
+    xq = torch.randn((rows, D), device="cuda", generator=g)
+    rec("route: argmax fp32 [65536,8192] axis=-1", rows * D * 4 + rows * 8, lambda: paddle.argmax(xq, axis=-1), rows * D)
+    del xq
     # C5: one rank's shard of the 2^34-element full reduce (2^31 elements), int64 and fp32, sum and max;
     # with world > 1 the scalar partials are finished by an NCCL AllReduce timed separately.
     n = 1 << 31
+    allreduce_us = {}
     for dt, nm, eb in ((torch.int64, "int64", 8), (torch.float32, "fp32", 4)):
         if dt == torch.int64:
             xr = torch.randint(-2**40, 2**40, (n,), device="cuda", dtype=dt, generator=g)
         else:
             xr = torch.rand((n,), device="cuda", generator=g) * 2 - 1
         for opn, fn in (("sum", paddle.sum), ("max", paddle.max)):
-            rec(f"C5 {opn} {nm} 2^31-element shard (1/8 of 2^34)", n * eb + eb, lambda: fn(xr), n)
+            rec(f"C5 {opn} {nm} 2^31-element shard per rank (1/8 of 2^34)", n * eb + eb, lambda: fn(xr), n, key=f"C5_{opn}_{nm}")
             if world > 1:
-                from paddlepaddle_b200 import distributed as pdist
                 part = fn(xr).reshape(1)
                 op = dist.ReduceOp.SUM if opn == "sum" else dist.ReduceOp.MAX
                 # the global result, exactly as a user gets it (shard kernel + one NCCL AllReduce) ...
@@ -374,7 +470,8 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
                 if not ok:
                     raise SystemExit(f"C5 {opn} {nm}: AllReduce result {glob.item()} != gathered {want.item()}")
                 scratch = part.clone()
-                ms = time_op(torch, lambda: dist.all_reduce(scratch, op=op), 20, 5)
+                dist.barrier()
+                ms = max_over_ranks(time_op(torch, lambda: dist.all_reduce(scratch, op=op), 20, 5))
                 out[-1]["allreduce_us"] = round(ms * 1e3, 2)
                 # the same exchange without NCCL: the reduction writes into this rank's NVLink-visible slot and one
                 # kernel combines all ranks' slots (csrc/peer.cu); must give the same global result
@@ -386,32 +483,123 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
                 out[-1]["peer_exchange_matches_nccl"] = same
                 if not same or peer.error() != 0:
                     raise SystemExit(f"C5 {opn} {nm}: peer exchange {glob_p.item()} != NCCL {glob.item()} (error word {peer.error()})")
-                ms = time_op(torch, lambda: peer.all_reduce(1, part.dtype, opn), 20, 5)
+                dist.barrier()
+                ms = max_over_ranks(time_op(torch, lambda: peer.all_reduce(1, part.dtype, opn), 20, 5))
                 out[-1]["peer_exchange_us"] = round(ms * 1e3, 2)
+                allreduce_us[f"C5_{opn}_{nm}"] = {"nccl": out[-1]["allreduce_us"], "peer_kernel": out[-1]["peer_exchange_us"]}
         del xr
     if world > 1:
-        # row-sharded sum(axis=0): local column sums + exchange of the [8192] vector (SURVEY §8e last row, §8f rank 4)
-        from paddlepaddle_b200 import distributed as pdist
+        # row-sharded sum(axis=0): local column sums (float32 partials) + exchange of the [8192] vector, rounded once
+        # after the cross-rank sum (SURVEY §8e last row, §8f rank 4); checked against the float64 sum of the gathered
+        # float32 partials and against the NCCL path
         xm = torch.randn((65536, 8192), device="cuda", generator=g).to(torch.bfloat16)
         a = pdist.global_sum_axis0(xm)
         b = pdist.global_sum_axis0(xm, peer=peer)
-        ms_n = time_op(torch, lambda: pdist.global_sum_axis0(xm), steps, warmup)
-        ms_p = time_op(torch, lambda: pdist.global_sum_axis0(xm, peer=peer), steps, warmup)
+        part = paddle.sum(xm, axis=0, dtype="float32")
+        parts = [torch.empty_like(part) for _ in range(world)]
+        dist.all_gather(parts, part)
+        ref64 = torch.stack(parts).double().sum(0)
+        ulp = ref64.abs().clamp_min(1e-30) * 2.0 ** -8  # one bf16 ulp of the result (8 significand bits)
+        err_p = float(((b.double() - ref64).abs() / ulp).max())
+        err_n = float(((a.double() - ref64).abs() / ulp).max())
+        if err_p > 1.0 or err_n > 1.0:
+            raise SystemExit(f"row-sharded sum(axis=0): off by {err_p:.2f} (peer) / {err_n:.2f} (NCCL) bf16 ulp from the float64 sum")
+        dist.barrier()
+        ms_n = max_over_ranks(time_op(torch, lambda: pdist.global_sum_axis0(xm), steps, warmup))
+        dist.barrier()
+        ms_p = max_over_ranks(time_op(torch, lambda: pdist.global_sum_axis0(xm, peer=peer), steps, warmup))
         out.append({"op": f"next: sum(axis=0) of a row-sharded bf16 [{world}x65536, 8192] (local column sums + exchange)",
-                    "algorithmic_bytes": 65536 * 8192 * 2, "ms_with_nccl_allreduce": round(ms_n, 4),
-                    "ms_with_peer_exchange": round(ms_p, 4), "GB/s_per_gpu_with_peer_exchange": round(65536 * 8192 * 2 / ms_p / 1e6, 1),
-                    "max_abs_diff_peer_vs_nccl": float((a.float() - b.float()).abs().max())})
+                    "algorithmic_bytes": 65536 * 8192 * 2 * world, "ms_with_nccl_allreduce": round(ms_n, 4),
+                    "ms_with_peer_exchange": round(ms_p, 4), "GB/s_with_peer_exchange": round(65536 * 8192 * 2 * world / ms_p / 1e6, 1),
+                    "max_err_in_bf16_ulp_vs_float64_sum": {"peer": round(err_p, 3), "nccl": round(err_n, 3)},
+                    "peer_equals_nccl": bool(torch.equal(a, b))})
+        per_config["sum_axis0_row_sharded_bf16"] = {"GB/s": out[-1]["GB/s_with_peer_exchange"], "ms": out[-1]["ms_with_peer_exchange"],
+                                                   "ms_nccl": out[-1]["ms_with_nccl_allreduce"]}
         del xm
+        # bandwidth-sized exchange: a 64 MiB float32 vector per rank, two-shot kernel (reduce-scatter + all-gather over
+        # peer memory) vs ncclAllReduce.  "bus GB/s" = 2 (N-1)/N x vector bytes / time, NCCL's convention.
+        big_n = 16 << 20
+        pb = pdist.PeerGroup(slot_bytes=big_n * 4)
+        vec = torch.randn(big_n, device="cuda", generator=g)
+        outb = torch.empty_like(vec)
+        slot_t = [pb.slot(torch.float32, big_n)]
+
+        def peer_big():
+            pb.all_reduce(big_n, torch.float32, "sum", out=outb)
+
+        for _ in range(2):  # both slots hold the vector: the timed loop is the exchange kernel alone
+            pb.slot(torch.float32, big_n).copy_(vec)
+            peer_big()
+        refb = vec.clone()
+        dist.all_reduce(refb)
+        okb = bool(torch.allclose(outb, refb, rtol=1e-5, atol=1e-4))
+        if not okb:
+            raise SystemExit("64 MiB two-shot exchange differs from ncclAllReduce")
+        scratch = vec.clone()
+        dist.barrier()
+        ms_nb = max_over_ranks(time_op(torch, lambda: dist.all_reduce(scratch), 10, 3))
+        dist.barrier()
+        ms_pb = max_over_ranks(time_op(torch, peer_big, 10, 3))
+        bus = 2 * (world - 1) / world * big_n * 4
+        out.append({"op": "exchange: all-reduce of a 64 MiB float32 vector per rank", "ms_nccl": round(ms_nb, 4),
+                    "ms_peer_two_shot": round(ms_pb, 4), "bus_GB/s_nccl": round(bus / ms_nb / 1e6, 1),
+                    "bus_GB/s_peer_two_shot": round(bus / ms_pb / 1e6, 1)})
+        per_config["allreduce_64MiB_fp32"] = {"bus_GB/s_peer": out[-1]["bus_GB/s_peer_two_shot"], "bus_GB/s_nccl": out[-1]["bus_GB/s_nccl"]}
+        if pb.error() != 0:
+            raise SystemExit("64 MiB exchange raised the peer error word")
+        pb.close()
+        del vec, outb, refb, scratch, slot_t
         if peer is not None:
             peer.close()
-    return out
+    return out, per_config, allreduce_us
+
+
+def pcie_ceiling(torch, nbytes=1 << 30, reps=3):
+    """Plain pinned-memory cudaMemcpyAsync rates of THIS rank (GB/s): H2D alone, D2H alone, both at once on two
+    streams — what the e2e path can reach at best."""
+    h = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    h2 = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    h.fill_(1)
+    h2.fill_(2)
+    d = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    d2 = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+
+    def timed(fn):
+        fn()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            fn()
+        torch.cuda.synchronize()
+        return (time.perf_counter() - t0) / reps
+
+    def up():
+        with torch.cuda.stream(s1):
+            d.copy_(h, non_blocking=True)
+
+    def down():
+        with torch.cuda.stream(s2):
+            h2.copy_(d2, non_blocking=True)
+
+    def both():
+        up()
+        down()
+
+    t_up, t_down, t_both = timed(up), timed(down), timed(both)
+    return {"h2d_GB/s": round(nbytes / t_up / 1e9, 1), "d2h_GB/s": round(nbytes / t_down / 1e9, 1),
+            "both_GB/s_each_way": round(nbytes / t_both / 1e9, 1)}
 
 
 def run_gpu_arm(args):
-    import torch
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    # before torch allocates anything: run this rank on the CPUs next to its GPU, so that pinned staging memory is
+    # first-touched on that NUMA node (paddlepaddle_b200.host.bind_to_gpu_numa; a no-op when the box does not say)
+    from paddlepaddle_b200 import numa
+    numa_info = numa.bind_to_gpu_numa(local)
+    import torch
     if not torch.cuda.is_available():
         print(json.dumps({"error": "no CUDA device: paddlepaddle_b200 has no CPU path"}))
         return 2
@@ -438,6 +626,12 @@ def run_gpu_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def max_over_ranks(v):
+        t = torch.tensor([v], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
@@ -452,11 +646,8 @@ def run_gpu_arm(args):
     e.record()
     barrier()
     launches = lib.pdb200_launch_count() - launches0
-    ms_total = torch.tensor([s.elapsed_time(e)], device="cuda", dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
+    ms_step = max_over_ranks(s.elapsed_time(e)) / args.steps
     clocks = sampler.stop() if rank == 0 else None
-    ms_step = float(ms_total.item()) / args.steps
     value = C2_BYTES_BF16 * world / (ms_step / 1e3) / 1e9
 
     # dominant kernel, timed launch by launch (events on the launching stream)
@@ -470,6 +661,7 @@ def run_gpu_arm(args):
         per.append(a.elapsed_time(b_))
     kern_ms = sum(per) / len(per)
     achieved = C2_BYTES_BF16 / (kern_ms / 1e3) / 1e9
+    achieved_b2b = C2_BYTES_BF16 / (ms_step / 1e3) / 1e9
 
     # end to end through the public API with HOST buffers
     hx = torch.empty(C2_SHAPE, dtype=torch.bfloat16, pin_memory=True)
@@ -477,6 +669,7 @@ def run_gpu_arm(args):
     ho = torch.empty(C2_SHAPE, dtype=torch.bfloat16, pin_memory=True)
     hx.copy_(x)
     hy.copy_(y)
+    ho.zero_()  # first touch of the output pages on this rank's NUMA node, outside the timed region
     from paddlepaddle_b200 import host as phost
 
     def e2e_step():
@@ -489,36 +682,54 @@ def run_gpu_arm(args):
     for _ in range(e2e_steps):
         e2e_step()
     torch.cuda.synchronize()
-    e2e_ms = torch.tensor([(time.perf_counter() - t0) * 1e3 / e2e_steps], device="cuda", dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
-    e2e_val = C2_BYTES_BF16 * world / (float(e2e_ms.item()) / 1e3) / 1e9
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / e2e_steps)
+    e2e_val = C2_BYTES_BF16 * world / (e2e_ms / 1e3) / 1e9
     del hx, ho
+    # what plain pinned copies reach on this rank, all ranks copying at the same time (the e2e ceiling)
+    barrier()
+    pc = pcie_ceiling(torch)
+    pcs = [None] * world
+    if world > 1:
+        dist.all_gather_object(pcs, pc)
+    else:
+        pcs = [pc]
+    both = [p["both_GB/s_each_way"] for p in pcs]
+    # e2e moves 1 GiB up and 1 GiB down per step per rank: at `both` GB/s each way that takes 1 GiB / both
+    e2e_ceiling = sum(C2_BYTES_BF16 / ((C2_ROWS * C2_COLS * 2) / (b_ * 1e9)) for b_ in both) / 1e9
 
-    ops = None
+    ops = per_config = None
+    allreduce_us = {}
     if not args.no_ops:
         del x, out
         torch.cuda.empty_cache()
-        ops = other_configs(torch, paddle, peak, max(3, min(args.steps, 10)), 3, world, rank, dist)
+        ops, per_config, allreduce_us = other_configs(torch, paddle, peak, max(3, min(args.steps, 10)), 3, world, rank, dist)
 
     if rank == 0:
         cpu = cpu_baseline_obj() if world == 1 else None
         line = {
-            "metric": "broadcast add HBM GB/s (algorithmic bytes / time)", "value": round(value, 1), "unit": "GB/s",
+            "metric": METRIC, "value": round(value, 1), "unit": "GB/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms_step, 4),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": "paddle.add bf16 [64,2048,4096] + [4096] (BASELINE configs[1]); per-GPU shard of "
-                                   f"a [{64 * world},2048,4096] tensor", "parallelism": f"rows sharded over {world} GPU(s), no collective",
+            "config": {"workload": WORKLOAD + f"; per-GPU shard of a [{64 * world},2048,4096] tensor",
+                       "parallelism": f"rows sharded over {world} GPU(s), no collective",
                        "l2": "operands 1 GiB each >> 126 MB L2, no flush needed", "algorithmic_bytes_per_step_per_gpu": C2_BYTES_BF16,
                        "elements_per_s": round(C2_ROWS * C2_COLS * world / (ms_step / 1e3), 1),
-                       "frac_of_8TBps_per_gpu": round(value / world / 8000.0, 4)},
+                       "frac_of_8TBps_per_gpu": round(value / world / 8000.0, 4),
+                       "per_config": per_config, "allreduce_us": allreduce_us,
+                       "timing": "every per_config row: barrier, CUDA events on the launching stream, MAX over ranks"},
             "roofline": {"bound": "hbm", "kernel": "ew_inner_kernel<bf16,AddOp>", "achieved": round(achieved, 1), "peak": peak,
                          "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": measured_traffic(),
                          "traffic_source": "profiles/r1h_add_bf16.txt (ncu --set full, one launch)", "peak_source": peak_src,
-                         "kernel_ms": round(kern_ms, 4)},
+                         "kernel_ms": round(kern_ms, 4),
+                         "note": "achieved/frac: per-launch event time (one launch, synchronised each side: includes the launch gap); "
+                                 "achieved_back_to_back/frac_back_to_back: bytes / ms_per_step of the timed region",
+                         "achieved_back_to_back": round(achieved_b2b, 1), "frac_back_to_back": round(achieved_b2b / peak, 4),
+                         "frac_of_8TBps": round(achieved_b2b / 8000.0, 4)},
             "e2e": {"value": round(e2e_val, 2), "unit": "GB/s", "h2d_bytes_per_step": C2_ROWS * C2_COLS * 2 + C2_COLS * 2,
-                    "d2h_bytes_per_step": C2_ROWS * C2_COLS * 2, "ms_per_step": round(float(e2e_ms.item()), 3),
-                    "path": "paddlepaddle_b200.host.add: pinned host -> H2D -> pdb200_add -> D2H, chunk-pipelined"},
+                    "d2h_bytes_per_step": C2_ROWS * C2_COLS * 2, "ms_per_step": round(e2e_ms, 3),
+                    "path": "paddlepaddle_b200.host.add: pinned host -> H2D -> pdb200_add -> D2H, chunk-pipelined",
+                    "pinned_copy_ceiling_per_rank": pcs, "ceiling_GB/s": round(e2e_ceiling, 1),
+                    "frac_of_ceiling": round(e2e_val / e2e_ceiling, 3) if e2e_ceiling else None, "numa": numa_info},
             "gpu_launches": int(launches), "clocks": clocks,
         }
         if cpu is not None:

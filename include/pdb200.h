@@ -375,14 +375,26 @@ PDB200_API int pdb200_rms_norm(const void* x, const int64_t* dims, int rank, con
 /* ---------------------------------------------------------------------------
  * The exchange step of sharded reductions over NVLink peer memory — one process per GPU.
  * Replaces paddle.distributed.all_reduce -> ProcessGroupNCCL::AllReduce -> ncclAllReduce
- * (paddle/fluid/distributed/collective/process_group_nccl.cc:267-297) for the small results this path exchanges.
- * Each rank creates a window (device memory: flags + two slots of `slot_bytes`), sends its 64-byte IPC handle to the
- * other ranks (any transport; the Python layer uses torch.distributed.all_gather once, at set-up) and opens theirs.
+ * (paddle/fluid/distributed/collective/process_group_nccl.cc:267-297; ReduceScatter :467-500; the bucketed gradient
+ * reduce of paddle/fluid/distributed/collective/reducer.cc:1089-1111) for what this path exchanges: one scalar per rank
+ * for a full reduce, a vector of column sums for a row-sharded sum(axis=0).
+ * Each rank creates a window (device memory: control block + two slots + two result regions of `slot_bytes` each),
+ * sends its 64-byte IPC handle to the other ranks (any transport; the Python layer uses torch.distributed.all_gather
+ * once, at set-up) and opens theirs.
  * Per call: write the local partial result into pdb200_peer_slot(window, slot_bytes, epoch) — e.g. pass it as the `out`
- * of a reduction — then pdb200_peer_all_reduce with the same epoch on every rank (1, 2, 3, ... per window).  One kernel
- * publishes the epoch to all peers, waits for theirs and combines all slots in rank order (bit-identical on every rank);
- * op codes: 0 sum, 1 max, 2 min, 3 prod; accumulation in float for bf16/fp16.  The wait is bounded (~1 s): a peer that
- * never arrives sets the error word (pdb200_peer_error != 0) instead of hanging the GPU.
+ * of a reduction, in `slot_dtype` (FLOAT32 partials for a BFLOAT16 / FLOAT16 sum: the cross-rank sum is rounded once) —
+ * then pdb200_peer_all_reduce with the same epoch on every rank (1, 2, 3, ... per window).  ONE kernel publishes the
+ * epoch to all peers, waits for theirs and combines all slots in rank order (bit-identical on every rank): up to 64 KB
+ * every rank reads every slot (one NVLink round trip); beyond that rank r reduces only its 1/world of the columns and
+ * stores the result chunk into every rank's result region (reduce-scatter + all-gather: each byte crosses NVLink once
+ * per direction), and `out` is filled from the local result region.  op codes: 0 sum, 1 max, 2 min, 3 prod.
+ * (slot_dtype, out_dtype): equal, or FLOAT32 -> BFLOAT16 / FLOAT16.  `out` must be aligned to its element size
+ * (16 bytes for the fast paths).
+ * The wait is bounded in time (30 s; PDB200_PEER_TIMEOUT_MS): a peer that never arrives makes the kernel fill `out`
+ * with NaN (all-ones for integers) and raise the error word; every later call on that window then fails with
+ * PDB200_CUDA_ERROR without touching the GPU — the group must be rebuilt (pdb200_peer_error reads the word at once,
+ * synchronising).  Launch-order contract: every rank enqueues its exchanges in the same order, one process per GPU,
+ * and nothing enqueued before rank B's exchange may depend on work rank A enqueues after its own.
  * windows[r] = this process's mapping of rank r's window (its own window for r == rank).
  * These entry points allocate (window_create) and synchronise (window_create, peer_error): set-up and checks only. */
 PDB200_API size_t pdb200_peer_window_bytes(size_t slot_bytes);
@@ -393,7 +405,7 @@ PDB200_API int pdb200_peer_window_destroy(void* window);
 PDB200_API void* pdb200_peer_slot(void* window, size_t slot_bytes, unsigned long long epoch);
 PDB200_API int pdb200_peer_error(void* window);
 PDB200_API int pdb200_peer_all_reduce(int op, void* const* windows, int world, int rank, size_t slot_bytes,
-                           unsigned long long epoch, int64_t n, int dtype, void* out, void* stream);
+                           unsigned long long epoch, int64_t n, int slot_dtype, int out_dtype, void* out, void* stream);
 
 #ifdef __cplusplus
 }

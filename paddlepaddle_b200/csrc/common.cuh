@@ -9,7 +9,10 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <stdlib.h>
+
 #include <atomic>
+#include <mutex>
 #include <string>
 
 #include "../../include/pdb200.h"
@@ -48,6 +51,66 @@ inline int sm_count() {
   }
   return n;
 }
+
+// ----------------------------------------------------------------------------
+// Tuning knobs (PDB200_* environment variables, profiles/sweep.py).  Read ONCE, at the first launch that asks:
+// a launch costs no getenv() afterwards, and the values cannot change between two host threads' launches.
+// 0 / false means "use the built-in choice".
+// ----------------------------------------------------------------------------
+struct Knobs {
+  int pipe_contig, pipe_max_ctas, pipe_max_stages, pipe_inflight_kb, pipe_rows_per_cta;
+  int softmax_pipe_c, ln_pipe_c, rms_pipe_c, cluster_slice_kb, cluster_rows_per_cluster;
+  int tma_cols_stages, expand_rows_per_cta, mulgrad_stages;
+  long long mulgrad_splits;
+  bool no_tma_cols, no_interleave, no_fused_mulgrad, no_cluster_pipe;
+  long long peer_timeout_ms;
+};
+inline const Knobs& knobs() {
+  static const Knobs k = [] {
+    auto num = [](const char* name) -> long long {
+      const char* v = getenv(name);
+      return v ? atoll(v) : 0;
+    };
+    auto set = [](const char* name) { return getenv(name) != nullptr; };
+    Knobs r{};
+    r.pipe_contig = (int)num("PDB200_PIPE_CONTIG");
+    r.pipe_max_ctas = (int)num("PDB200_PIPE_MAX_CTAS");
+    r.pipe_max_stages = (int)num("PDB200_PIPE_MAX_STAGES");
+    r.pipe_inflight_kb = (int)num("PDB200_PIPE_INFLIGHT_KB");
+    r.pipe_rows_per_cta = (int)num("PDB200_PIPE_ROWS_PER_CTA");
+    r.softmax_pipe_c = (int)num("PDB200_SOFTMAX_PIPE_C");
+    r.ln_pipe_c = (int)num("PDB200_LN_PIPE_C");
+    r.rms_pipe_c = (int)num("PDB200_RMS_PIPE_C");
+    r.cluster_slice_kb = (int)num("PDB200_CLUSTER_SLICE_KB");
+    r.cluster_rows_per_cluster = (int)num("PDB200_CLUSTER_ROWS");
+    r.tma_cols_stages = (int)num("PDB200_TMA_COLS_STAGES");
+    r.expand_rows_per_cta = (int)num("PDB200_EXPAND_ROWS_PER_CTA");
+    r.mulgrad_stages = (int)num("PDB200_MULGRAD_STAGES");
+    r.mulgrad_splits = num("PDB200_MULGRAD_SPLITS");
+    r.no_tma_cols = set("PDB200_NO_TMA_COLS");
+    r.no_interleave = set("PDB200_NO_INTERLEAVE");
+    r.no_fused_mulgrad = set("PDB200_NO_FUSED_MULGRAD");
+    r.no_cluster_pipe = set("PDB200_NO_CLUSTER_PIPE");
+    r.peer_timeout_ms = num("PDB200_PEER_TIMEOUT_MS");
+    return r;
+  }();
+  return k;
+}
+
+// ----------------------------------------------------------------------------
+// Per-function launch attributes (max dynamic shared memory, shared-memory carve-out) are state of the
+// (kernel, device) pair inside the driver, not of a launch.  Every launch that depends on them takes this lock,
+// applies its pair only if it differs from what the pair was last set to, and releases the lock AFTER the launch
+// call has returned — two host threads launching different shapes of one instantiation cannot interleave a
+// set-attribute of one with the launch of the other.
+// ----------------------------------------------------------------------------
+struct FuncAttrHold {
+  std::unique_lock<std::mutex> lock;
+};
+std::mutex& func_attr_mutex();
+// Apply (max dynamic smem, carve-out pct or -1) to `kern` on the current device; `hold` keeps the lock until it dies.
+bool func_attr_apply(const void* kern, int smem_bytes, int carveout_pct, FuncAttrHold* hold);
+bool func_attr_apply_locked(const void* kern, int smem_bytes, int carveout_pct);  // caller holds func_attr_mutex()
 
 inline size_t dtype_size(int dt) {
   switch (dt) {
@@ -99,9 +162,16 @@ template <typename T>
 __device__ __forceinline__ Vec<T> ld_stream(const T* p) {
   Vec<T> r;
   uint4 u;
+#ifdef PDB200_COHERENT_STREAM
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
+               : "l"(p)
+               : "memory");
+#else
   asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
                : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
                : "l"(p));
+#endif
   *reinterpret_cast<uint4*>(&r) = u;
   return r;
 }

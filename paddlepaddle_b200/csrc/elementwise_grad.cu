@@ -247,7 +247,7 @@ struct MulGradInner {
     if (cols % V != 0 || cols / V < 32 || rows < 64) return false;
     if (rows >= (int64_t(1) << 31) || cols >= (int64_t(1) << 31)) return false;
     if (!is_aligned16(dout) || !is_aligned16(big) || !is_aligned16(rowv) || (dbig && !is_aligned16(dbig))) return false;
-    return getenv("PDB200_NO_FUSED_MULGRAD") == nullptr && tma_encode_fn() != nullptr;
+    return !knobs().no_fused_mulgrad && tma_encode_fn() != nullptr;
   }
   static PassGeom geometry(int64_t rows, int64_t cols) {
     PassGeom g = plan_pass(ReducePass{1, rows, cols}, sizeof(T), Vec<T>::N);
@@ -255,7 +255,7 @@ struct MulGradInner {
     // short-lived CTAs — 128 rows (4 boxes) per CTA, at most 1024 splits: bf16 [131072,4096] 0.503 -> 0.479 ms
     // (74 -> 1024 splits; 4096 splits of one box each: 0.673 ms).  PDB200_MULGRAD_SPLITS overrides.
     int64_t sp = std::min<int64_t>(1024, rows / 128);
-    if (const char* v = getenv("PDB200_MULGRAD_SPLITS")) sp = atoll(v);
+    if (knobs().mulgrad_splits > 0) sp = knobs().mulgrad_splits;
     {
       if (sp > g.splits) {
         sp = std::min<int64_t>(sp, std::max<int64_t>(1, rows / kTmaTileRows));
@@ -294,18 +294,17 @@ struct MulGradInner {
     const size_t smem = (size_t)kMgStages * 2 * kTmaTileRows * TI * sizeof(T) + (size_t)8 * TI * sizeof(A);
     A* part = static_cast<A*>(ws);
     const int64_t blocks = g.col_tiles * g.splits;
-    static const int nstages = [] {  // tuning knob; the ring is allocated for kMgStages
-      const char* v = getenv("PDB200_MULGRAD_STAGES");
-      const int n = v ? atoi(v) : kMgStages;
-      return n >= 2 && n <= kMgStages ? n : kMgStages;
-    }();
+    const int nstages = knobs().mulgrad_stages >= 2 && knobs().mulgrad_stages <= kMgStages ? knobs().mulgrad_stages
+                                                                                          : kMgStages;  // tuning knob
     if (dbig) {
       auto kern = mulgrad_inner_tma_kernel<T, true>;
-      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      FuncAttrHold hold;  // one size per instantiation: set once per device, a map lookup afterwards
+      func_attr_apply(reinterpret_cast<const void*>(kern), (int)smem, -1, &hold);
       kern<<<(unsigned)blocks, kTmaThreads, smem, st>>>(md, mb, rowv, dbig, part, rows, cols, g.seg, g.splits, g.col_tiles, nstages);
     } else {
       auto kern = mulgrad_inner_tma_kernel<T, false>;
-      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      FuncAttrHold hold;
+      func_attr_apply(reinterpret_cast<const void*>(kern), (int)smem, -1, &hold);
       kern<<<(unsigned)blocks, kTmaThreads, smem, st>>>(md, mb, rowv, dbig, part, rows, cols, g.seg, g.splits, g.col_tiles, nstages);
     }
     const int rc = after_launch("mulgrad_inner_tma");

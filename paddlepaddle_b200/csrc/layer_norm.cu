@@ -522,7 +522,7 @@ int layer_norm_typed(const T* x, const P* scale, const P* bias, T* y, void* mean
   // Fast path: many rows, 16-byte-multiple rows that fit <= 512 threads x 4 chunks -> TMA row pipeline.
   if (vec && sizeof(T) <= 4 && nchunk >= 64 && nchunk <= 512 * 4 && rows >= 4 * (int64_t)sm_count()) {
     int C = nchunk >= 512 ? 4 : (nchunk >= 256 ? 2 : 1);  // CTAs stay >= 128 threads wide
-    if (const int o = pipe_c_override("PDB200_LN_PIPE_C")) C = o;
+    if (const int o = knobs().ln_pipe_c) C = o;
     int threads = (int)((nchunk + C - 1) / C);
     threads = (threads + 31) / 32 * 32;
     const size_t row_bytes = (size_t)D * sizeof(T);
@@ -531,11 +531,11 @@ int layer_norm_typed(const T* x, const P* scale, const P* bias, T* y, void* mean
       size_t smem = 0;
       int want = 512 / threads;  // ~512 threads per SM, 2..4 CTAs, 3 rows in flight each
       want = want < 2 ? 2 : (want > 4 ? 4 : want);
-      if (!pipe_geometry(kern, threads, row_bytes, want, 3, &per_sm, &stages, &smem)) return -1;
+      FuncAttrHold hold;  // released when this lambda returns, i.e. after the launch
+      if (!pipe_geometry(kern, threads, row_bytes, want, 3, &per_sm, &stages, &smem, &hold)) return -1;
       int64_t grid = (int64_t)per_sm * sm_count();
-      if (const char* v = getenv("PDB200_PIPE_ROWS_PER_CTA")) {  // tuning knob: short-lived CTAs instead of a persistent grid
-        if (atoi(v) >= 1) grid = std::max<int64_t>(grid, rows / atoi(v));
-      }
+      if (const int rpc = knobs().pipe_rows_per_cta; rpc >= 1)  // tuning knob: short-lived CTAs instead of a persistent grid
+        grid = std::max<int64_t>(grid, rows / rpc);
       if (grid > rows) grid = rows;
       kern<<<(unsigned)grid, threads, smem, st>>>(x, scale, bias, y, m, v, rows, (int)D, stages, eps, inv_d, pipe_contiguous());
       return after_launch("ln_pipe");

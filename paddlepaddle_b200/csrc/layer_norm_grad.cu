@@ -299,7 +299,8 @@ int layer_norm_grad_typed(const T* x, const P* scale, const void* mean_v, const 
       auto launch = [&](auto kern) -> int {
         int per_sm = 0, stages = 0;
         size_t smem = 0;
-        if (!pipe_geometry(kern, threads, stage_bytes, 2, 3, &per_sm, &stages, &smem)) return -1;
+        FuncAttrHold hold;  // released when this lambda returns, i.e. after the launch
+        if (!pipe_geometry(kern, threads, stage_bytes, 2, 3, &per_sm, &stages, &smem, &hold)) return -1;
         int64_t grid = (int64_t)per_sm * sm_count();
         if (grid > rows) grid = rows;
         if (grid > kLnGradMaxParts) grid = kLnGradMaxParts;

@@ -178,9 +178,7 @@ int launch_expand(const BroadcastPlan& p, const T* g, T* out, F f, cudaStream_t 
         // many short-lived CTAs of ~4 rows each, not a persistent grid: bf16 [131072,4096] 0.182 ms with 1184
         // persistent CTAs, 0.151 ms (7.1 TB/s) with 4 rows per CTA, 0.158 with 16, 0.173 with 64 (profiles/r1e_notes.txt)
         int rows_each = 4;
-        if (const char* v = getenv("PDB200_EXPAND_ROWS_PER_CTA")) {  // tuning knob
-          if (atoi(v) >= 1) rows_each = atoi(v);
-        }
+        if (knobs().expand_rows_per_cta >= 1) rows_each = knobs().expand_rows_per_cta;  // tuning knob
         int64_t slabs = std::min<int64_t>(std::max<int64_t>(1, p.rows / rows_each), 0x7fffffffLL);
         const int64_t rpc = (p.rows + slabs - 1) / slabs;
         slabs = (p.rows + rpc - 1) / rpc;

@@ -492,7 +492,7 @@ inline PassGeom plan_pass(const ReducePass& ps, size_t elem_bytes, int V) {
   // The tile (32 vectors x 8 row-groups) is also a valid geometry for the plain kernel, which launch_pass
   // falls back to if the tensor map cannot be encoded.
   const bool tma = V > 1 && (elem_bytes == 2 || elem_bytes == 4 || elem_bytes == 8) && vec_cols >= 32 &&
-                   ps.red >= 64 && getenv("PDB200_NO_TMA_COLS") == nullptr;
+                   ps.red >= 64 && !knobs().no_tma_cols;
   if (tma) {
     g.kind = 3;
     g.TX = 32;
@@ -534,7 +534,7 @@ int launch_pass(const ReducePass& ps, const PassGeom& g, bool vec, const T* x, O
   if (g.kind == 1) {
     const int64_t blocks = ps.outer * g.splits;
     if (blocks > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "reduce: too many rows for one launch");
-    static const bool no_interleave = getenv("PDB200_NO_INTERLEAVE") != nullptr;  // tuning knob
+    const bool no_interleave = knobs().no_interleave;  // tuning knob
     if (vec && g.splits > 1 && !no_interleave)
       reduce_rows_block_kernel<T, O, Op, Fin, true, true><<<(unsigned)blocks, g.threads, 0, st>>>(x, out, ps.red, g.seg, g.splits, fin);
     else if (vec)
@@ -553,19 +553,11 @@ int launch_pass(const ReducePass& ps, const PassGeom& g, bool vec, const T* x, O
         constexpr int TI = 32 * Vec<T>::N;
         const size_t smem_tma = (size_t)kTmaStages * kTmaTileRows * TI * sizeof(T) + (size_t)8 * TI * sizeof(A);
         auto kern = reduce_cols_tma_kernel<T, O, Op, Fin>;
-        // the attribute is per (kernel, device): remember it per device, one flag array per instantiation
-        static bool attr_set[64] = {false};
-        int dev = 0;
-        cudaGetDevice(&dev);
-        if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-          cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tma);
-          if (dev >= 0 && dev < 64) attr_set[dev] = true;
-        }
-        static const int nstages = [] {  // tuning knob; the ring is allocated for kTmaStages
-          const char* v = getenv("PDB200_TMA_COLS_STAGES");
-          const int n = v ? atoi(v) : kTmaStages;
-          return n >= 2 && n <= kTmaStages ? n : kTmaStages;
-        }();
+        // one size per instantiation: set once per (kernel, device) under the attribute lock, a map lookup afterwards
+        FuncAttrHold hold;
+        func_attr_apply(reinterpret_cast<const void*>(kern), (int)smem_tma, -1, &hold);
+        const int ks = knobs().tma_cols_stages;  // tuning knob; the ring is allocated for kTmaStages
+        const int nstages = ks >= 2 && ks <= kTmaStages ? ks : kTmaStages;
         kern<<<(unsigned)blocks, kTmaThreads, smem_tma, st>>>(map, out, ps.red, ps.inner, g.seg, g.splits, g.col_tiles, fin, nstages);
         return after_launch("reduce_cols_tma");
       }
@@ -574,9 +566,15 @@ int launch_pass(const ReducePass& ps, const PassGeom& g, bool vec, const T* x, O
   dim3 block(g.TX, g.TY);
   const int V = vec ? Vec<T>::N : 1;
   const size_t smem = sizeof(typename Op::Acc) * (size_t)g.TX * g.TY * V;
-  if (vec)
+  if (vec) {
+    // argmax over 1-byte values folds 16 columns x 16-byte (value, index) pairs per thread: 64 KB, above the 48 KB a
+    // kernel gets without opting in
+    FuncAttrHold hold;
+    if (smem > 48 * 1024 &&
+        !func_attr_apply(reinterpret_cast<const void*>(reduce_cols_kernel<T, O, Op, Fin, true>), (int)smem, -1, &hold))
+      return fail(PDB200_CUDA_ERROR, "reduce_cols: cannot opt in to " + std::to_string(smem) + " bytes of shared memory");
     reduce_cols_kernel<T, O, Op, Fin, true><<<(unsigned)blocks, block, smem, st>>>(x, out, ps.red, ps.inner, g.seg, g.splits, g.col_tiles, fin);
-  else
+  } else
     reduce_cols_kernel<T, O, Op, Fin, false><<<(unsigned)blocks, block, smem, st>>>(x, out, ps.red, ps.inner, g.seg, g.splits, g.col_tiles, fin);
   return after_launch("reduce_cols");
 }

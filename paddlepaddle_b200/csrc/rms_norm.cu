@@ -185,7 +185,7 @@ int rms_typed(const T* x, const T* residual, const T* bias, const T* weight, con
   const int64_t nchunk = D / VN;
   if (vec && nchunk >= 64 && nchunk <= 512 * 4 && rows >= 4 * (int64_t)sm_count()) {
     int C = nchunk >= 512 ? 4 : (nchunk >= (sizeof(T) == 2 ? 128 : 256) ? 2 : 1);
-    if (const int o = pipe_c_override("PDB200_RMS_PIPE_C")) C = o;  // tuning knob
+    if (const int o = knobs().rms_pipe_c) C = o;  // tuning knob
     while (C < 4 && (nchunk + C - 1) / C > 512) C <<= 1;
     int threads = (int)((nchunk + C - 1) / C);
     threads = (threads + 31) / 32 * 32;
@@ -200,7 +200,8 @@ int rms_typed(const T* x, const T* residual, const T* bias, const T* weight, con
       // (bf16 [65536,8192] + residual: 0.698 ms with two CTAs, 0.640 ms with one)
       const int by_bytes = (int)((64 * 1024) / (2 * stage_bytes));
       if (want > by_bytes) want = by_bytes < 1 ? 1 : by_bytes;
-      if (!pipe_geometry(kern, threads, stage_bytes, want, 3, &per_sm, &stages, &smem)) return -1;
+      FuncAttrHold hold;  // released when this lambda returns, i.e. after the launch
+      if (!pipe_geometry(kern, threads, stage_bytes, want, 3, &per_sm, &stages, &smem, &hold)) return -1;
       int64_t grid = (int64_t)per_sm * sm_count();
       if (grid > rows) grid = rows;
       kern<<<(unsigned)grid, threads, smem, st>>>(x, residual, bias, weight, nbias, out, residual_out, inv_var, rows, (int)D,

@@ -80,16 +80,7 @@ __device__ __forceinline__ Vec<T> lds_vec(const T* p) {
 constexpr int kPipeMaxStages = 32;  // mbarriers per CTA
 
 // Tuning knob: row -> CTA mapping of the pipelined kernels (1 = contiguous slab per CTA).
-inline int pipe_contiguous() {
-  const char* v = getenv("PDB200_PIPE_CONTIG");
-  return v ? atoi(v) : 0;
-}
-
-// Tuning knob: chunks per thread for the pipelined kernels (0 = use the built-in choice).
-inline int pipe_c_override(const char* name) {
-  const char* v = getenv(name);
-  return v ? atoi(v) : 0;
-}
+inline int pipe_contiguous() { return knobs().pipe_contig; }
 
 // Launch helper shared by the pipelined kernels.  `want_ctas` CTAs per SM (capped by what registers
 // and threads allow) each get `want_stages` ring stages (capped by shared memory); the result is
@@ -100,51 +91,49 @@ inline int pipe_c_override(const char* name) {
 // Geometry comes from sweeps on B200 (profiles/r1_sweep.txt): past ~512-768 threads and ~3 stages
 // per SM more concurrency does not help and often hurts.
 // Returns false when fewer than 2 stages fit (caller falls back to a non-pipelined route).
+// On success `hold` owns the function-attribute lock (common.cuh): the caller launches while it is alive, so the
+// (carve-out, max dynamic smem) pair this shape needs is the one in force at the launch, whatever other host
+// threads are doing with other shapes of the same kernel.
 template <typename Kern>
 inline bool pipe_geometry(Kern kern, int threads, size_t row_bytes, int want_ctas, int want_stages,
-                          int* grid_per_sm, int* stages, size_t* smem_bytes) {
+                          int* grid_per_sm, int* stages, size_t* smem_bytes, FuncAttrHold* hold) {
   auto ok = [](cudaError_t e) {
     if (e != cudaSuccess) cudaGetLastError();
     return e == cudaSuccess;
   };
-  if (const char* v = getenv("PDB200_PIPE_MAX_CTAS")) {  // tuning knobs (profiles/sweep.py)
-    if (atoi(v) >= 1) want_ctas = atoi(v);
-  }
-  if (const char* v = getenv("PDB200_PIPE_MAX_STAGES")) {
-    if (atoi(v) >= 2) want_stages = atoi(v);
-  }
+  const Knobs& kn = knobs();
+  if (kn.pipe_max_ctas >= 1) want_ctas = kn.pipe_max_ctas;
+  if (kn.pipe_max_stages >= 2) want_stages = kn.pipe_max_stages;
   if (want_stages > kPipeMaxStages) want_stages = kPipeMaxStages;
   // The answer depends only on (kernel, device, threads, row size, wishes): remember it, so that a launch
-  // costs one map lookup instead of a dozen attribute / occupancy calls.  The attributes set below are
-  // per-function state in the driver; every cached entry of one kernel re-applies its own pair on use.
+  // costs one map lookup instead of a dozen attribute / occupancy calls.
   struct Geo { int per_sm, stages; size_t smem; int pct; bool ok; };
-  static std::mutex mu;
-  static std::map<std::tuple<const void*, int, int, size_t, int, int>, Geo> cache;
+  static std::map<std::tuple<const void*, int, int, size_t, int, int>, Geo> cache;  // guarded by func_attr_mutex()
   int dev = 0;
   cudaGetDevice(&dev);
-  const auto key = std::make_tuple(reinterpret_cast<const void*>(kern), dev, threads, row_bytes, want_ctas, want_stages);
+  const void* fn = reinterpret_cast<const void*>(kern);
+  const auto key = std::make_tuple(fn, dev, threads, row_bytes, want_ctas, want_stages);
+  hold->lock = std::unique_lock<std::mutex>(func_attr_mutex());
+  auto give_up = [&]() {
+    hold->lock.unlock();
+    return false;
+  };
   {
-    std::lock_guard<std::mutex> lock(mu);
     auto it = cache.find(key);
     if (it != cache.end()) {
       const Geo& g = it->second;
-      if (!g.ok) return false;
-      // another shape of the same kernel may have changed the function attributes since
-      if (!ok(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, g.pct))) return false;
-      if (!ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem))) return false;
+      if (!g.ok) return give_up();
+      // another shape of the same kernel may have changed the function attributes since: re-apply if so
+      if (!func_attr_apply_locked(fn, (int)g.smem, g.pct)) return give_up();
       *grid_per_sm = g.per_sm;
       *stages = g.stages;
       *smem_bytes = g.smem;
       return true;
     }
   }
-  auto remember = [&](const Geo& g) {
-    std::lock_guard<std::mutex> lock(mu);
-    cache[key] = g;
-  };
-  if (!ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * (int)row_bytes))) return false;
+  if (!func_attr_apply_locked(fn, 2 * (int)row_bytes, -1)) return give_up();
   int occ = 0;
-  if (!ok(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, 2 * row_bytes)) || occ < 1) return false;
+  if (!ok(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, 2 * row_bytes)) || occ < 1) return give_up();
   if (occ > want_ctas) occ = want_ctas;
   const size_t sm_smem = 227 * 1024;
   for (; occ >= 1; --occ) {
@@ -155,10 +144,7 @@ inline bool pipe_geometry(Kern kern, int threads, size_t row_bytes, int want_cta
     // (profiles/r1e_notes.txt).
     // Never fewer than two stages: a CTA must be able to compute on one row while the next arrives.
     {
-      int kb = 64;
-      if (const char* v = getenv("PDB200_PIPE_INFLIGHT_KB")) {
-        if (atoi(v) >= 8) kb = atoi(v);
-      }
+      const int kb = kn.pipe_inflight_kb >= 8 ? kn.pipe_inflight_kb : 64;
       int cap = static_cast<int>(((size_t)kb * 1024) / ((size_t)occ * row_bytes));
       if (cap < 2) cap = 2;
       if (st > cap) st = cap;
@@ -167,21 +153,20 @@ inline bool pipe_geometry(Kern kern, int threads, size_t row_bytes, int want_cta
       const size_t smem = (size_t)st * row_bytes;
       int pct = static_cast<int>((occ * (smem + 2048) * 100 + sm_smem - 1) / sm_smem);
       if (pct > 100) pct = 100;
-      if (!ok(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, pct))) continue;
-      if (!ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))) continue;
+      if (!func_attr_apply_locked(fn, (int)smem, pct)) continue;
       int real = 0;
       if (!ok(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&real, kern, threads, smem))) continue;
       if (real >= occ) {
         *grid_per_sm = occ;
         *stages = st;
         *smem_bytes = smem;
-        remember(Geo{occ, st, smem, pct, true});
+        cache[key] = Geo{occ, st, smem, pct, true};
         return true;
       }
     }
   }
-  remember(Geo{0, 0, 0, 0, false});
-  return false;
+  cache[key] = Geo{0, 0, 0, 0, false};
+  return give_up();
 }
 
 }  // namespace pdb200

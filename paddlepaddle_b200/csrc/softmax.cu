@@ -151,10 +151,18 @@ __global__ void __launch_bounds__(256) softmax_rows_reg_kernel(const T* __restri
 // One FFMA + FMNMX + MUFU.EX2.  The rounding of m*log2e is a common factor of the whole row and
 // cancels in the normalisation; per element the error is 0.5 ulp of the exponent argument plus
 // ex2.approx's 2^-22: <= ~2e-6 relative for |x - m| <= 64, inside the 1e-5 bar.
+// max(a, b) that returns NaN when either operand is NaN (fmaxf would drop it): one FMNMX.NAN.  A NaN logit, a +inf
+// logit (inf - inf) and a row of -inf all reach the clamp as NaN and must come out as NaN, as they do from the CPU
+// kernel's `x < -64 ? -64 : x` (softmax_impl.h:36-42) — never as a healthy-looking probability.
+__device__ __forceinline__ float max_nan(float a, float b) {
+  float r;
+  asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+}
 __device__ __forceinline__ float fast_clipped_exp(float x, float neg_m_log2e) {
   constexpr float kLog2e = 1.4426950408889634f;
   float t = fmaf(x, kLog2e, neg_m_log2e);
-  t = fmaxf(t, -64.0f * kLog2e);
+  t = max_nan(t, -64.0f * kLog2e);
   float r;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(t));
   return r;
@@ -250,7 +258,7 @@ __global__ void __launch_bounds__(512) softmax_pipe_kernel(const T* __restrict__
       for (int k = 0; k < V; ++k) {
         float p;
         if constexpr (LOG) {
-          const float d = fmaxf(e[c * V + k] - m, -64.0f);  // the exact clipped difference is the output term
+          const float d = max_nan(e[c * V + k] - m, -64.0f);  // the exact clipped difference is the output term
           e[c * V + k] = d;
           asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p) : "f"(d * 1.4426950408889634f));
         } else {
@@ -505,7 +513,7 @@ int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, typename AccT
   // chunks per thread: 16-bit rows do best with 4 (32 values a thread), fp32 rows with 2
   // (8 values): profiles/r1_sweep.txt
   int C = sizeof(T) == 2 ? (nchunk >= 256 ? 4 : (nchunk >= 128 ? 2 : 1)) : (nchunk >= 256 ? 2 : 1);
-  if (const int o = pipe_c_override("PDB200_SOFTMAX_PIPE_C")) C = o;
+  if (const int o = knobs().softmax_pipe_c) C = o;
   while (C < 8 && (nchunk + C - 1) / C > 512) C <<= 1;  // the kernel is built for <= 512 threads
   int threads = (int)((nchunk + C - 1) / C);
   if (threads > 512) return -1;
@@ -517,14 +525,14 @@ int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, typename AccT
     int want = 768 / threads;  // ~768 threads per SM, 2..6 CTAs; a 512-thread CTA (rows of 16-32 KB) runs alone:
     const int lo = threads >= 512 ? 1 : 2;  // two of them put 128 KB of rows in flight, fp32 [65536,8192] 0.726 vs 0.634 ms
     want = want < lo ? lo : (want > 6 ? 6 : want);
-    if (!pipe_geometry(kern, threads, row_bytes, want, 3, &per_sm, &stages, &smem)) return -1;
+    FuncAttrHold hold;  // released when this lambda returns, i.e. after the launch
+    if (!pipe_geometry(kern, threads, row_bytes, want, 3, &per_sm, &stages, &smem, &hold)) return -1;
     int64_t grid = (int64_t)per_sm * sm_count();
     // 64-thread CTAs (16-bit rows of 2048): many short-lived CTAs of 4 rows beat the persistent grid, 0.660 -> 0.620 ms on
     // bf16 [8,32,2048,2048]; 256-thread CTAs lose (fp32: 1.305 -> 1.49 ms), so they stay persistent (profiles/r1e_notes.txt)
     if (threads <= 64) grid = std::max<int64_t>(grid, outer / 4);
-    if (const char* v = getenv("PDB200_PIPE_ROWS_PER_CTA")) {  // tuning knob
-      if (atoi(v) >= 1) grid = std::max<int64_t>((int64_t)per_sm * sm_count(), outer / atoi(v));
-    }
+    if (const int rpc = knobs().pipe_rows_per_cta; rpc >= 1)  // tuning knob
+      grid = std::max<int64_t>((int64_t)per_sm * sm_count(), outer / rpc);
     if (grid > 0x7fffffffLL) grid = 0x7fffffffLL;
     if (grid > outer) grid = outer;
     kern<<<(unsigned)grid, threads, smem, st>>>(x, y, outer, (int)dim, stages, pipe_contiguous(), stats);

@@ -156,14 +156,14 @@ int try_softmax_grad_pipe(const T* y, const T* dy, T* dx, int64_t outer, int64_t
     // ~64 KB of rows in flight per SM at two stages (profiles/r1e_notes.txt): bf16 [.,2048] 6 -> 4 CTAs 1.01 -> 0.93 ms
     const int by_bytes = (int)((64 * 1024) / (2 * stage_bytes));
     if (want > by_bytes) want = by_bytes < 1 ? 1 : by_bytes;
-    if (!pipe_geometry(kern, threads, stage_bytes, want, 3, &per_sm, &stages, &smem)) return -1;
+    FuncAttrHold hold;  // released when this lambda returns, i.e. after the launch
+    if (!pipe_geometry(kern, threads, stage_bytes, want, 3, &per_sm, &stages, &smem, &hold)) return -1;
     int64_t grid = (int64_t)per_sm * sm_count();
     // 64-thread CTAs: short-lived CTAs of 4 rows instead of the persistent grid (bf16 [.,2048]: 0.935 -> 0.906 ms; the
     // 256-thread fp32 CTAs lose, 1.906 -> 2.05 ms, and stay persistent) — as in softmax.cu
     if (threads <= 64) grid = std::max<int64_t>(grid, outer / 4);
-    if (const char* v = getenv("PDB200_PIPE_ROWS_PER_CTA")) {  // tuning knob
-      if (atoi(v) >= 1) grid = std::max<int64_t>((int64_t)per_sm * sm_count(), outer / atoi(v));
-    }
+    if (const int rpc = knobs().pipe_rows_per_cta; rpc >= 1)  // tuning knob
+      grid = std::max<int64_t>((int64_t)per_sm * sm_count(), outer / rpc);
     if (grid > outer) grid = outer;
     if (grid > 0x7fffffffLL) grid = 0x7fffffffLL;
     kern<<<(unsigned)grid, threads, smem, st>>>(y, dy, dx, outer, (int)dim, stages);

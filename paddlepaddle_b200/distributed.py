@@ -101,13 +101,17 @@ class PeerGroup:
         ptr = self.lib.pdb200_peer_slot(self._window, self.slot_bytes, self.epoch + 1)
         return _tensor_from_ptr(ptr, numel, dtype)
 
-    def all_reduce(self, numel, dtype, op="sum", out=None):
-        """Combine the `numel` elements every rank wrote into its slot; returns a new tensor (or fills `out`)."""
+    def all_reduce(self, numel, dtype, op="sum", out=None, slot_dtype=None):
+        """Combine the `numel` elements every rank wrote into its slot; returns a new tensor (or fills `out`).
+        `slot_dtype`: what the slots hold when it is not `dtype` (float32 partials of a bfloat16 / float16 sum — the
+        cross-rank sum is then rounded once).  Raises if an EARLIER exchange of this group timed out (checked without
+        synchronising: the kernel raises a host-visible word); a timed-out exchange leaves NaN / all-ones in its output."""
         self.epoch += 1
         if out is None:
             out = torch.empty(numel, dtype=dtype, device="cuda")
         L.check(self.lib.pdb200_peer_all_reduce(self._OPS[op], self._mapped, self.world, self.rank, self.slot_bytes, self.epoch,
-                                                numel, ops._dtype_code(dtype), ctypes.c_void_p(out.data_ptr()),
+                                                numel, ops._dtype_code(slot_dtype or dtype), ops._dtype_code(dtype),
+                                                ctypes.c_void_p(out.data_ptr()),
                                                 ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)), self.lib)
         return out
 
@@ -166,18 +170,24 @@ _LOCAL = {"sum": (L.REDUCE_SUM, ReduceOp.SUM), "max": (L.REDUCE_MAX, ReduceOp.MA
 def _global(op_name, x_shard, peer, axis=None, out_dtype=None):
     """Local reduction, then the exchange: through `peer` (a PeerGroup — the reduction kernel writes its result straight
     into this rank's peer-visible slot and ONE kernel combines all ranks' slots over NVLink) or, without one, an NCCL
-    AllReduce on the native dtype."""
+    AllReduce.  Sums and products of bfloat16 / float16 travel as the float32 partials the kernels accumulate in and
+    are rounded ONCE, after the cross-rank combine ("1 ulp of the output type, accumulated in fp32" holds for the
+    global result, not per rank)."""
     code, nccl_op = _LOCAL[op_name]
     dt = out_dtype or x_shard.dtype
     if op_name == "sum" and out_dtype is None and x_shard.dtype in (torch.bool, torch.int32):
         dt = torch.int64  # SumRawInferMeta
-    if peer is not None and get_world_size() > 1:
+    # the dtype that crosses GPUs: float32 for 16-bit float sums (sum_raw has the bf16/fp16 -> fp32 kernel)
+    wire = torch.float32 if (op_name == "sum" and dt in (torch.bfloat16, torch.float16)) else dt
+    if get_world_size() == 1:
+        return ops._reduce(code, x_shard, axis, False, dt).reshape(-1)
+    if peer is not None:
         n = 1 if axis is None else x_shard.shape[-1]
-        ops._reduce(code, x_shard, axis, False, dt, out=peer.slot(dt, n))
-        return peer.all_reduce(n, dt, op_name)
-    part = ops._reduce(code, x_shard, axis, False, dt).reshape(-1)
+        ops._reduce(code, x_shard, axis, False, wire, out=peer.slot(wire, n))
+        return peer.all_reduce(n, dt, op_name, slot_dtype=wire)
+    part = ops._reduce(code, x_shard, axis, False, wire).reshape(-1)
     all_reduce(part, nccl_op)
-    return part
+    return part if wire == dt else ops.cast(part, dt)
 
 
 def global_sum(x_shard, dtype=None, peer=None):

@@ -131,30 +131,37 @@ def softmax_(x, axis=-1, dtype=None, name=None):
     return x
 
 
-def layer_norm(x, normalized_shape, weight=None, bias=None, epsilon=1e-05, name=None, return_stats=False):
-    """layer_norm over the trailing `normalized_shape` dims (norm.py:320-396).
-    return_stats=True also returns the intermediate outputs `mean` and `variance`
-    (ops.yaml:2839-2851) that Paddle keeps for the backward pass."""
-    _require_cuda(x, weight, bias)
+_ln_cache = {}
+
+
+def _ln_plan(ishape, normalized_shape, x_dtype, w, b):
+    """Shape / dtype checks of LayerNormInferMeta and of gpu/layer_norm_kernel.cu:516-538, done once per
+    (input shape, normalized_shape, dtypes) and remembered: -> (begin_norm_axis, rows, D, dims array, rank, param code)."""
     if isinstance(normalized_shape, numbers.Integral):
-        normalized_shape = [normalized_shape]
+        normalized_shape = (normalized_shape,)
+    key = (ishape, tuple(normalized_shape), x_dtype, None if w is None else (w.dtype, w.numel()),
+           None if b is None else (b.dtype, b.numel()))
+    plan = _ln_cache.get(key)
+    if plan is not None:
+        return plan
     normalized_shape = list(normalized_shape)
-    ishape = list(x.shape)
+    ish = list(ishape)
     n = len(normalized_shape)
-    if n == 0 or n > len(ishape) or ishape[len(ishape) - n:] != normalized_shape:
+    if n == 0 or n > len(ish) or ish[len(ish) - n:] != normalized_shape:
         # norm.py:380-390
         raise ValueError(
             "Given normalized_shape is " + str(normalized_shape) + ", expected input with shape [*, " +
-            str(normalized_shape)[1:] + ", but got input shape " + str(ishape))
-    begin_norm_axis = len(ishape) - n
-    lib = L.load()
-    x = x.contiguous()
+            str(normalized_shape)[1:] + ", but got input shape " + str(ish))
+    begin_norm_axis = len(ish) - n
     D = 1
     for d in normalized_shape:
         D *= d
-    rows = x.numel() // D if D else 0
+    numel = 1
+    for d in ish:
+        numel *= d
+    rows = numel // D if D else 0
     pdt = None
-    for p, nm in ((weight, "Scale"), (bias, "Bias")):
+    for p, nm in ((w, "Scale"), (b, "Bias")):
         if p is None:
             continue
         if p.numel() != D:
@@ -163,19 +170,35 @@ def layer_norm(x, normalized_shape, weight=None, bias=None, epsilon=1e-05, name=
             pdt = p.dtype
         elif p.dtype != pdt:
             raise ValueError("(InvalidArgument) Scale and Bias must share one dtype")
-    if pdt is not None and pdt != x.dtype and pdt != torch.float32:
+    if pdt is not None and pdt != x_dtype and pdt != torch.float32:
         raise ValueError("(InvalidArgument) Unsupported data type of Scale and Bias")
-    weight = weight.contiguous() if weight is not None else None
-    bias = bias.contiguous() if bias is not None else None
+    d, r = L.dims_array(ishape)
+    pcode = _dtype_code(pdt) if pdt is not None else _dtype_code(x_dtype)
+    plan = (begin_norm_axis, rows, D, d, r, pcode, _dtype_code(x_dtype))
+    if len(_ln_cache) < 4096:
+        _ln_cache[key] = plan
+    return plan
+
+
+def layer_norm(x, normalized_shape, weight=None, bias=None, epsilon=1e-05, name=None, return_stats=False):
+    """layer_norm over the trailing `normalized_shape` dims (norm.py:320-396).
+    return_stats=True also returns the intermediate outputs `mean` and `variance`
+    (ops.yaml:2839-2851) that Paddle keeps for the backward pass."""
+    _require_cuda(x, weight, bias)
+    begin_norm_axis, rows, D, d, r, pcode, xcode = _ln_plan(tuple(x.shape), normalized_shape, x.dtype, weight, bias)
+    lib = L.load()
+    if not x.is_contiguous():
+        x = x.contiguous()
+    if weight is not None and not weight.is_contiguous():
+        weight = weight.contiguous()
+    if bias is not None and not bias.is_contiguous():
+        bias = bias.contiguous()
     stat_dt = torch.float64 if x.dtype == torch.float64 else torch.float32
     y = torch.empty_like(x)
-    mean = torch.empty((rows,), dtype=stat_dt, device=x.device)
-    var = torch.empty((rows,), dtype=stat_dt, device=x.device)
-    d, r = L.dims_array(x.shape)
-    pcode = _dtype_code(pdt) if pdt is not None else _dtype_code(x.dtype)
+    stats = torch.empty((2, rows), dtype=stat_dt, device=x.device)  # mean and variance: one allocation
+    mean, var = stats[0], stats[1]
     L.check(lib.pdb200_layer_norm(_ptr(x), d, r, _ptr(weight), _ptr(bias), pcode, ctypes.c_float(float(epsilon)),
-                                  begin_norm_axis, _dtype_code(x.dtype), _ptr(y), _ptr(mean), _ptr(var),
-                                  _stream()), lib)
+                                  begin_norm_axis, xcode, _ptr(y), _ptr(mean), _ptr(var), _stream()), lib)
     if return_stats:
         return y, mean, var
     return y

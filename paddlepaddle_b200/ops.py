@@ -84,6 +84,26 @@ def _workspace(nbytes, device):
 # ---------------------------------------------------------------------------------------
 # elementwise
 # ---------------------------------------------------------------------------------------
+_bcast_cache = {}
+
+
+def _bcast_plan(xs, ys, lib):
+    """(x dims array, rank, y dims array, rank, output shape) for a pair of shapes — InferMeta's broadcast rule, asked of
+    the library once per shape pair and remembered (a call then costs one dict lookup instead of three ctypes trips)."""
+    key = (xs, ys)
+    plan = _bcast_cache.get(key)
+    if plan is None:
+        xd, xr = L.dims_array(xs)
+        yd, yr = L.dims_array(ys)
+        od = (ctypes.c_int64 * L.MAX_RANK)()
+        orank = ctypes.c_int(0)
+        L.check(lib.pdb200_broadcast_shape(xd, xr, yd, yr, od, ctypes.byref(orank)), lib)
+        plan = (xd, xr, yd, yr, tuple(od[i] for i in range(orank.value)))
+        if len(_bcast_cache) < 4096:
+            _bcast_cache[key] = plan
+    return plan
+
+
 def _elementwise(fn_name, x, y, out=None, op=None, out_dtype=None):
     """One binary broadcast call.  `op`: leading op-code argument of the coded entry points (compare /
     logical / bitwise); `out_dtype`: dtype of the result when it is not x's (bool for compare / logical)."""
@@ -92,14 +112,11 @@ def _elementwise(fn_name, x, y, out=None, op=None, out_dtype=None):
         raise TypeError(f"(InvalidType) the dtypes of X ({x.dtype}) and Y ({y.dtype}) must match "
                         "(type promotion is done by the caller in Paddle's eager layer)")
     lib = L.load()
-    x = x.contiguous()
-    y = y.contiguous()
-    xd, xr = L.dims_array(x.shape)
-    yd, yr = L.dims_array(y.shape)
-    od = (ctypes.c_int64 * L.MAX_RANK)()
-    orank = ctypes.c_int(0)
-    L.check(lib.pdb200_broadcast_shape(xd, xr, yd, yr, od, ctypes.byref(orank)), lib)
-    oshape = tuple(od[i] for i in range(orank.value))
+    if not x.is_contiguous():
+        x = x.contiguous()
+    if not y.is_contiguous():
+        y = y.contiguous()
+    xd, xr, yd, yr, oshape = _bcast_plan(tuple(x.shape), tuple(y.shape), lib)
     if out is None:
         out = torch.empty(oshape, dtype=out_dtype or x.dtype, device=x.device)
     elif tuple(out.shape) != oshape:
@@ -348,32 +365,50 @@ _REDUCE_FN = {
 }
 
 
+_reduce_cache = {}
+
+
+def _reduce_plan(op, shape, axis, keepdim, x_dtype, out_dtype, lib):
+    """Everything about a reduction that depends only on (op, shape, axes, dtypes): normalised axes, output shape, the
+    dims arrays handed to the C-ABI and the workspace size.  Remembered per key, so a repeated call does no ctypes query."""
+    akey = tuple(axis) if isinstance(axis, (list, tuple)) else axis
+    key = (op, shape, akey, keepdim, x_dtype, out_dtype)
+    plan = _reduce_cache.get(key)
+    if plan is None:
+        axes = _norm_axes(axis, len(shape))
+        oshape = _reduced_shape(shape, axes, keepdim)
+        n_out = 1
+        for d_ in oshape:
+            n_out *= d_
+        xd, xr = L.dims_array(shape)
+        ad, an = L.dims_array(axes)
+        reduce_all = 1 if not axes else 0
+        xc, oc = _dtype_code(x_dtype), _dtype_code(out_dtype)
+        nbytes = lib.pdb200_reduce_workspace_bytes(op, xd, xr, ad, an, reduce_all, xc, oc)
+        plan = (oshape, n_out, xd, xr, ad, an, reduce_all, xc, oc, nbytes, getattr(lib, _REDUCE_FN[op]))
+        if len(_reduce_cache) < 4096:
+            _reduce_cache[key] = plan
+    return plan
+
+
 def _reduce(op, x, axis, keepdim, out_dtype, out=None):
     """`out`: write the result into this buffer (right element count and dtype) instead of a new tensor — used by the
     distributed layer to let the kernel write straight into a peer-visible slot."""
     _require_cuda(x)
     lib = L.load()
-    x = x.contiguous()
-    axes = _norm_axes(axis, x.dim())
+    if not x.is_contiguous():
+        x = x.contiguous()
     if x.numel() == 0:
+        _norm_axes(axis, x.dim())
         raise ValueError("(InvalidArgument) Tensor need be reduced must not empty.")
-    oshape = _reduced_shape(tuple(x.shape), axes, keepdim)
+    oshape, n_out, xd, xr, ad, an, reduce_all, xc, oc, nbytes, fn = _reduce_plan(op, tuple(x.shape), axis, bool(keepdim),
+                                                                                 x.dtype, out_dtype, lib)
     if out is None:
         out = torch.empty(oshape, dtype=out_dtype, device=x.device)
-    else:
-        n_out = 1
-        for d_ in oshape:
-            n_out *= d_
-        if out.numel() != n_out or out.dtype != out_dtype or not out.is_contiguous():
-            raise ValueError("(InvalidArgument) out must be a contiguous tensor of the result's element count and dtype")
-    xd, xr = L.dims_array(x.shape)
-    ad, an = L.dims_array(axes)
-    reduce_all = 1 if not axes else 0
-    xc, oc = _dtype_code(x.dtype), _dtype_code(out_dtype)
-    nbytes = lib.pdb200_reduce_workspace_bytes(op, xd, xr, ad, an, reduce_all, xc, oc)
+    elif out.numel() != n_out or out.dtype != out_dtype or not out.is_contiguous():
+        raise ValueError("(InvalidArgument) out must be a contiguous tensor of the result's element count and dtype")
     ws = _workspace(nbytes, x.device)
-    L.check(getattr(lib, _REDUCE_FN[op])(_ptr(x), xd, xr, ad, an, reduce_all, xc, oc, _ptr(out), _ptr(ws),
-                                         nbytes, _stream()), lib)
+    L.check(fn(_ptr(x), xd, xr, ad, an, reduce_all, xc, oc, _ptr(out), _ptr(ws), nbytes, _stream()), lib)
     return out
 
 
