@@ -6,7 +6,7 @@ NVFLAGS   := -std=c++17 -O3 -gencode arch=compute_100a,code=sm_100a -lineinfo --
              -Xcompiler -fPIC -Xcompiler -fvisibility=hidden
 CSRC      := paddlepaddle_b200/csrc
 OBJDIR    := build
-SRCS      := runtime elementwise elementwise_more elementwise_pred unary elementwise_grad reduce_grad cross_entropy rms_norm peer softmax_grad layer_norm_grad reduce_sum reduce_minmax reduce_prod argmax softmax layer_norm no_alloc
+SRCS      := runtime elementwise elementwise_more elementwise_pred unary elementwise_grad reduce_grad cross_entropy rms_norm peer softmax_grad layer_norm_grad reduce_sum reduce_minmax reduce_prod argmax softmax softmax_mask layer_norm fused_ln no_alloc
 OBJS      := $(addprefix $(OBJDIR)/,$(addsuffix .o,$(SRCS)))
 LIB       := paddlepaddle_b200/libpdb200.so
 HDRS      := $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.h) include/pdb200.h

@@ -373,6 +373,46 @@ PDB200_API int pdb200_rms_norm(const void* x, const int64_t* dims, int rank, con
                     void* out, void* residual_out, void* inv_var, void* stream);
 
 /* ---------------------------------------------------------------------------
+ * Masked softmax of attention scores.
+ * pdb200_fused_softmax_mask replaces phi::fusion::FusedSoftmaxMaskKernel
+ * (paddle/phi/kernels/fusion/gpu/fused_softmax_mask_kernel.cu:149-316; python paddle.incubate.softmax_mask_fuse):
+ *   out[b,h,q,:] = softmax(float(x[b,h,q,:]) + float(mask[b,0,q,:]))   x_dims = [B,H,Sq,Sk], mask_dims = [B,1,Sq,Sk]
+ * computed in float with plain exp(d - max) (no clip, as the reference kernel), rounded once.  dtype FLOAT32 / FLOAT16 /
+ * BFLOAT16 (the reference registers float and float16); mask_dtype = dtype or FLOAT32.  Checks reproduced: mask's
+ * second dim is 1, the other dims equal x's (:177-202).  The reference's 32 <= Sk < 8192 and Sq-divisibility limits
+ * belong to its warp-per-row layout and are not imposed.
+ * pdb200_fused_softmax_mask_upper_triangle replaces phi::fusion::FusedSoftmaxMaskFuseUpperTriangleKernel
+ * (fusion/gpu/fused_softmax_mask_upper_triangle_kernel.cu:255-400; python paddle.incubate.softmax_mask_fuse_upper_triangle):
+ *   out[b,h,q,k] = softmax over k <= q of x[b,h,q,k], 0 for k > q      x_dims = [B,H,S,S] (Sq == Sk is checked, :271-277)
+ * Only the part of x on and below the diagonal is read.  out must not alias x. */
+PDB200_API int pdb200_fused_softmax_mask(const void* x, const int64_t* x_dims, const void* mask, const int64_t* mask_dims,
+                              int dtype, int mask_dtype, void* out, void* stream);
+PDB200_API int pdb200_fused_softmax_mask_upper_triangle(const void* x, const int64_t* x_dims, int dtype, void* out,
+                                             void* stream);
+
+/* ---------------------------------------------------------------------------
+ * layer_norm(residual + dropout(x + bias)) in one pass.
+ * Replaces phi::fusion::FusedBiasDropoutResidualLnKernel<T, GPUContext>
+ * (paddle/phi/kernels/fusion/gpu/fused_bias_dropout_residual_layer_norm_kernel.cu:24-98; element rule
+ * fusion/gpu/fused_residual_dropout_bias.h:40-156, statistics and output fused_layernorm_residual_dropout_bias.h:117-221;
+ * python paddle.incubate.nn.functional.fused_bias_dropout_residual_layer_norm):
+ *   d = (T(x) + T(bias)) * factor + residual, each step rounded to T;  bias_dropout_residual_out = d;
+ *   ln_mean / ln_variance = mean and biased variance of float(d) over the last axis (float; double for FLOAT64);
+ *   y = T(ln_scale * (d - mean) * rsqrt(variance + ln_epsilon) + ln_bias).
+ * dims / rank describe x (and residual, y, bias_dropout_residual_out); D = dims[rank-1]; bias, ln_scale, ln_bias have D
+ * elements and may be NULL; param_dtype = dtype of ln_scale / ln_bias: the tensor dtype or FLOAT32 (the reference uses
+ * LayerNormParamType<T> = float for float16).  The deterministic cases run here: dropout_rate == 0, or is_test != 0
+ * (factor = 1 resp. 1 - dropout_rate for downscale_in_infer, fused_dropout_common.h:171-181); no dropout mask is written
+ * in those cases (neither does the reference).  Training with dropout_rate > 0 returns PDB200_UNSUPPORTED: the random
+ * mask comes from the framework's Philox generator state (the PHI binding forwards that case to the in-tree kernel).
+ * dtypes FLOAT32, FLOAT64, FLOAT16 (the reference's list) and BFLOAT16.  Outputs must not alias inputs or each other. */
+PDB200_API int pdb200_fused_bias_dropout_residual_layer_norm(const void* x, const void* residual, const int64_t* dims, int rank,
+                                                  const void* bias, const void* ln_scale, const void* ln_bias,
+                                                  int param_dtype, float dropout_rate, int is_test, int upscale_in_train,
+                                                  float ln_epsilon, int dtype, void* y, void* bias_dropout_residual_out,
+                                                  void* ln_mean, void* ln_variance, void* stream);
+
+/* ---------------------------------------------------------------------------
  * The exchange step of sharded reductions over NVLink peer memory — one process per GPU.
  * Replaces paddle.distributed.all_reduce -> ProcessGroupNCCL::AllReduce -> ncclAllReduce
  * (paddle/fluid/distributed/collective/process_group_nccl.cc:267-297; ReduceScatter :467-500; the bucketed gradient

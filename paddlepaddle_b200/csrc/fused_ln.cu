@@ -1,0 +1,326 @@
+// fused_ln.cu — layer_norm(residual + dropout(x + bias)) in one pass, hand-written for sm_100a.
+//
+// Replaces (fresh design): phi::fusion::FusedBiasDropoutResidualLnKernel<T, GPUContext>
+//   paddle/phi/kernels/fusion/gpu/fused_bias_dropout_residual_layer_norm_kernel.cu:24-98 ->
+//   FusedDropoutLayerNormHelper::LayernormResidualDropoutBias (fusion/gpu/fused_dropout_helper.h:428-489) ->
+//   FusedLayernormResidualDropoutBias / fused_fast_ln_fwd_kernel (fusion/gpu/fused_layernorm_residual_dropout_bias.h:117-221,
+//   850-1100), element rule FusedResidualDropoutBiasOneThread (fusion/gpu/fused_residual_dropout_bias.h:40-156),
+//   python: paddle.incubate.nn.functional.fused_bias_dropout_residual_layer_norm.
+//     d = (T(x) + T(bias)) * keep * factor + residual        every operation rounded to T, as the reference's T arithmetic
+//     bias_dropout_residual_out = d
+//     mean, variance = statistics of float(d) over the last axis (biased variance)
+//     y = T(scale * (float(d) - mean) * rsqrt(variance + eps) + ln_bias)
+// `factor` (fused_dropout_common.h:171-181): training 1/(1-p) (upscale_in_train) or 1; inference 1 or (1-p).
+// The deterministic cases are on this path: dropout_rate == 0, or is_test (keep = 1 everywhere; the reference writes no
+// mask then either).  Random masks (training with p > 0) draw from Paddle's Philox generator state, which lives in the
+// framework: that case stays with the in-tree kernel (the PHI binding forwards it).
+// Statistics are two-pass on the register-resident row (mean, then sum of squared deviations) as in layer_norm.cu —
+// the reference's E[d^2] - mean^2 agrees to rounding and is the less accurate of the two.
+//
+// Routes ([rows][D] view):
+//   pipe : many rows, D = 64..2048 16-byte chunks — persistent CTAs on the TMA row pipeline (rowpipe.cuh); one ring
+//          stage holds the x row AND the residual row (two cp.async.bulk on one mbarrier): every input byte is read
+//          from HBM once, both outputs are streamed out of registers.
+//   rows : any other shape or float64 — one CTA per row, sweeps over global memory.
+#include <string>
+
+#include "common.cuh"
+#include "rowpipe.cuh"
+#include "shape.h"
+
+namespace pdb200 {
+
+struct AddFln { __device__ __forceinline__ float operator()(float a, float b) const { return a + b; } };
+template <typename U> struct AddFlnU { __device__ __forceinline__ U operator()(U a, U b) const { return a + b; } };
+
+// round a float to T and back (identity for float): the reference computes this chain in T arithmetic
+template <typename T>
+__device__ __forceinline__ float round_to(float v) { return cvt<float>(cvt<T>(v)); }
+template <> __device__ __forceinline__ float round_to<float>(float v) { return v; }
+
+template <typename T, typename P, int C, bool EXACT, bool HAS_BIAS, bool SCALED, int MAXT>
+__global__ void __launch_bounds__(MAXT, MAXT <= 256 ? 2 : 1)
+fln_pipe_kernel(const T* __restrict__ x, const T* __restrict__ residual, const T* __restrict__ bias,
+                const P* __restrict__ scale, const P* __restrict__ ln_bias, T* __restrict__ y, T* __restrict__ dro,
+                float* __restrict__ mean_out, float* __restrict__ var_out, int64_t rows, int D, int stages, float factor,
+                float eps, float inv_d) {
+  constexpr int V = Vec<T>::N;
+  constexpr int PV = Vec<P>::N;
+  extern __shared__ __align__(128) unsigned char ring_raw[];
+  T* ring = reinterpret_cast<T*>(ring_raw);
+  __shared__ uint64_t full[kPipeMaxStages];
+  __shared__ float red[2][32];
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const uint32_t row_bytes = (uint32_t)D * sizeof(T);
+  const int64_t row_step = gridDim.x;
+  factor = round_to<T>(factor);  // the reference multiplies by T(factor)
+  if (tid == 0) {
+    for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
+    mbar_fence_init();
+  }
+  block_reduce_1sync_init(red[0], 0.f);
+  block_reduce_1sync_init(red[1], 0.f);
+  __syncthreads();
+  auto fill = [&](int s, int64_t r) {
+    mbar_expect_tx(&full[s], 2 * row_bytes);
+    bulk_load_row(ring + (size_t)s * 2 * D, x + r * D, row_bytes, &full[s]);
+    bulk_load_row(ring + (size_t)s * 2 * D + D, residual + r * D, row_bytes, &full[s]);
+  };
+  if (tid == 0) {
+    for (int s = 0; s < stages; ++s) {
+      const int64_t r = blockIdx.x + s * row_step;
+      if (r < rows) fill(s, r);
+    }
+  }
+  int s = 0;
+  uint32_t phase = 0;
+  for (int64_t row = blockIdx.x; row < rows; row += row_step) {
+    mbar_wait(&full[s], phase);
+    const T* sx = ring + (size_t)s * 2 * D;
+    float e[C * V];
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + tid) * V;
+      if (EXACT || off < D) {
+        float r[V];
+        unpack_to_float<T>(lds_vec(sx + off), &e[c * V]);
+        unpack_to_float<T>(lds_vec(sx + D + off), r);
+        if constexpr (HAS_BIAS) {
+          float b[V];
+          unpack_to_float<T>(ld_cached(bias + off), b);
+#pragma unroll
+          for (int k = 0; k < V; ++k) e[c * V + k] = round_to<T>(e[c * V + k] + b[k]);
+        }
+        if constexpr (SCALED) {
+#pragma unroll
+          for (int k = 0; k < V; ++k) e[c * V + k] = round_to<T>(e[c * V + k] * factor);
+        }
+        Vec<T> dv;
+#pragma unroll
+        for (int k = 0; k < V; ++k) e[c * V + k] += r[k];
+        pack_from_float<T>(&e[c * V], dv);
+        st_stream(dro + row * D + off, dv);
+        unpack_to_float<T>(dv, &e[c * V]);  // the statistics see the rounded value, like the reference
+      } else {
+#pragma unroll
+        for (int k = 0; k < V; ++k) e[c * V + k] = 0.f;
+      }
+#pragma unroll
+      for (int k = 0; k < V; ++k) acc[k & 3] += e[c * V + k];
+    }
+    float sum = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+    sum = block_reduce_1sync(sum, AddFln(), red[0]);  // its barrier also means: stage s fully read
+    if (tid == 0) {
+      const int64_t nrow = row + (int64_t)stages * row_step;
+      if (nrow < rows) {
+        fence_proxy_async_smem();
+        fill(s, nrow);
+      }
+    }
+    const float mean = sum * inv_d;
+    acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + tid) * V;
+      if (EXACT || off < D) {
+#pragma unroll
+        for (int k = 0; k < V; ++k) {
+          const float d = e[c * V + k] - mean;
+          e[c * V + k] = d;
+          acc[k & 3] = fmaf(d, d, acc[k & 3]);
+        }
+      }
+    }
+    float sq = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+    sq = block_reduce_1sync(sq, AddFln(), red[1]);
+    const float var = sq * inv_d;
+    const float rstd = rsqrtf(var + eps);
+    if (tid == 0) {
+      if (mean_out) mean_out[row] = mean;
+      if (var_out) var_out[row] = var;
+    }
+    T* dst = y + row * D;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + tid) * V;
+      if (EXACT || off < D) {
+        float w[V], b[V], o[V];
+#pragma unroll
+        for (int k = 0; k < V; ++k) { w[k] = 1.f; b[k] = 0.f; }
+        if (scale != nullptr) {
+#pragma unroll
+          for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(scale + off + j * PV), &w[j * PV]);
+        }
+        if (ln_bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(ln_bias + off + j * PV), &b[j * PV]);
+        }
+#pragma unroll
+        for (int k = 0; k < V; ++k) o[k] = fmaf(w[k] * e[c * V + k], rstd, b[k]);  // scale * (d - mean) * invvar + bias
+        Vec<T> ov;
+        pack_from_float<T>(o, ov);
+        st_stream(dst + off, ov);
+      }
+    }
+    if (++s == stages) {
+      s = 0;
+      phase ^= 1;
+    }
+  }
+}
+
+// any shape / float64: one CTA per row.  U = float (double for double input).
+template <typename T, typename P, typename U>
+__global__ void __launch_bounds__(1024) fln_rows_kernel(const T* x, const T* residual, const T* bias, const P* scale,
+                                                        const P* ln_bias, T* y, T* dro, U* mean_out, U* var_out, int64_t D,
+                                                        float factor, U eps, double inv_d) {
+  __shared__ U red[33];
+  const int64_t base = (int64_t)blockIdx.x * D;
+  using AddU_ = AddFlnU<U>;
+  const bool scaled = factor != 1.0f;
+  U sum = U(0);
+  for (int64_t i = threadIdx.x; i < D; i += blockDim.x) {
+    T t = x[base + i];
+    if (bias != nullptr) t = cvt<T>(cvt<U>(t) + cvt<U>(bias[i]));
+    if (scaled) t = cvt<T>(cvt<U>(t) * cvt<U>(cvt<T>((U)factor)));
+    const T d = cvt<T>(cvt<U>(t) + cvt<U>(residual[base + i]));
+    dro[base + i] = d;  // written after the last read of x / residual at i by this thread: in-place safe
+    sum += cvt<U>(d);
+  }
+  sum = block_reduce(sum, AddU_(), U(0), red);
+  const U mean = (U)((double)sum * inv_d);
+  U sq = U(0);
+  for (int64_t i = threadIdx.x; i < D; i += blockDim.x) {
+    const U dv = cvt<U>(dro[base + i]) - mean;  // this thread's own writes
+    sq += dv * dv;
+  }
+  sq = block_reduce(sq, AddU_(), U(0), red);
+  const U var = (U)((double)sq * inv_d);
+  const U rstd = U(1) / sqrt(var + eps);
+  if (threadIdx.x == 0) {
+    if (mean_out) mean_out[blockIdx.x] = mean;
+    if (var_out) var_out[blockIdx.x] = var;
+  }
+  for (int64_t i = threadIdx.x; i < D; i += blockDim.x) {
+    const U w = scale ? cvt<U>(scale[i]) : U(1);
+    const U b = ln_bias ? cvt<U>(ln_bias[i]) : U(0);
+    y[base + i] = cvt<T>(w * (cvt<U>(dro[base + i]) - mean) * rstd + b);
+  }
+}
+
+template <typename T, typename P>
+int fln_typed(const T* x, const T* residual, const T* bias, const P* scale, const P* ln_bias, T* y, T* dro, void* mean,
+              void* var, int64_t rows, int64_t D, float factor, float epsilon, cudaStream_t st) {
+  using U = typename AccType<T>::type;
+  constexpr int VN = Vec<T>::N;
+  if constexpr (!std::is_same<T, double>::value) {
+    bool vec = (D % VN == 0) && is_aligned16(x) && is_aligned16(residual) && is_aligned16(y) && is_aligned16(dro) &&
+               (!bias || is_aligned16(bias)) && (!scale || is_aligned16(scale)) && (!ln_bias || is_aligned16(ln_bias)) &&
+               dro != y && y != x && y != residual;
+    const int64_t nchunk = D / VN;
+    if (vec && nchunk >= 64 && nchunk <= 512 * 4 && rows >= 4 * (int64_t)sm_count()) {
+      int C = nchunk >= 512 ? 4 : (nchunk >= (sizeof(T) == 2 ? 128 : 256) ? 2 : 1);
+      while (C < 4 && (nchunk + C - 1) / C > 512) C <<= 1;
+      int threads = (int)((nchunk + C - 1) / C);
+      threads = (threads + 31) / 32 * 32;
+      const bool exact = (int64_t)threads * C == nchunk;
+      const size_t stage_bytes = 2 * (size_t)D * sizeof(T);
+      auto launch = [&](auto kern) -> int {
+        int per_sm = 0, stages = 0;
+        size_t smem = 0;
+        int want = 768 / threads;
+        want = want < 2 ? 2 : (want > 4 ? 4 : want);
+        const int by_bytes = (int)((64 * 1024) / (2 * stage_bytes));  // ~64 KB of rows in flight per SM at two stages
+        if (want > by_bytes) want = by_bytes < 1 ? 1 : by_bytes;
+        FuncAttrHold hold;  // released when this lambda returns, i.e. after the launch
+        if (!pipe_geometry(kern, threads, stage_bytes, want, 3, &per_sm, &stages, &smem, &hold)) return -1;
+        int64_t grid = (int64_t)per_sm * sm_count();
+        if (grid > rows) grid = rows;
+        kern<<<(unsigned)grid, threads, smem, st>>>(x, residual, bias, scale, ln_bias, y, dro, static_cast<float*>(mean),
+                                                    static_cast<float*>(var), rows, (int)D, stages, factor, epsilon,
+                                                    (float)(1.0 / (double)D));
+        return after_launch("fln_pipe");
+      };
+      const bool scaled = factor != 1.0f;
+      int rc = -1;
+#define PDB_FLN3(CC, MT, HB, SC) rc = exact ? launch(fln_pipe_kernel<T, P, CC, true, HB, SC, MT>) : launch(fln_pipe_kernel<T, P, CC, false, HB, SC, MT>);
+#define PDB_FLN2(CC, MT)                                           \
+  if (bias && scaled) { PDB_FLN3(CC, MT, true, true) }             \
+  else if (bias) { PDB_FLN3(CC, MT, true, false) }                 \
+  else if (scaled) { PDB_FLN3(CC, MT, false, true) }               \
+  else { PDB_FLN3(CC, MT, false, false) }
+#define PDB_FLN(CC) if (threads <= 256) { PDB_FLN2(CC, 256) } else { PDB_FLN2(CC, 512) }
+      if (threads <= 512) {
+        if (C == 4) { PDB_FLN(4) } else if (C == 2) { PDB_FLN(2) } else { PDB_FLN(1) }
+      }
+#undef PDB_FLN
+#undef PDB_FLN2
+#undef PDB_FLN3
+      if (rc >= 0) return rc;
+    }
+  }
+  if (rows > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "fused_bias_dropout_residual_layer_norm: too many rows for one launch");
+  int threads = 128;
+  while (threads < 1024 && threads * 8 < D) threads <<= 1;
+  fln_rows_kernel<T, P, U><<<(unsigned)rows, threads, 0, st>>>(x, residual, bias, scale, ln_bias, y, dro, static_cast<U*>(mean),
+                                                               static_cast<U*>(var), D, factor, (U)epsilon, 1.0 / (double)D);
+  return after_launch("fln_rows");
+}
+
+}  // namespace pdb200
+
+extern "C" int pdb200_fused_bias_dropout_residual_layer_norm(const void* x, const void* residual, const int64_t* dims, int rank,
+                                                             const void* bias, const void* ln_scale, const void* ln_bias,
+                                                             int param_dtype, float dropout_rate, int is_test,
+                                                             int upscale_in_train, float ln_epsilon, int dtype, void* y,
+                                                             void* bias_dropout_residual_out, void* ln_mean, void* ln_variance,
+                                                             void* stream) {
+  using namespace pdb200;
+  PDB_CHECK_ARG(rank >= 1 && rank <= PDB200_MAX_RANK && dims != nullptr, "fused_bias_dropout_residual_layer_norm: rank must be in [1, 9]");
+  // FusedBiasDropoutResidualLnInferMeta (infermeta/fusion.cc): 0 <= dropout_rate <= 1
+  PDB_CHECK_ARG(dropout_rate >= 0.0f && dropout_rate <= 1.0f, "'dropout_rate' must be between 0.0 and 1.0.");
+  int64_t rows = 1;
+  for (int i = 0; i < rank; ++i) {
+    PDB_CHECK_ARG(dims[i] >= 0, "fused_bias_dropout_residual_layer_norm: negative dimension");
+    if (i + 1 < rank) rows *= dims[i];
+  }
+  const int64_t D = dims[rank - 1];
+  if (rows * D == 0) return PDB200_OK;
+  PDB_CHECK_ARG(x && residual && y && bias_dropout_residual_out, "fused_bias_dropout_residual_layer_norm: NULL tensor pointer");
+  if (!is_test && dropout_rate != 0.0f)
+    return fail(PDB200_UNSUPPORTED, "fused_bias_dropout_residual_layer_norm: random dropout masks (training with dropout_rate > 0) "
+                                    "draw from the framework's Philox state and are not on this path");
+  const float factor = is_test ? (upscale_in_train ? 1.0f : 1.0f - dropout_rate) : 1.0f;  // training here means p == 0
+  const bool has_param = ln_scale != nullptr || ln_bias != nullptr;
+  const bool same = !has_param || param_dtype == dtype;
+  if (has_param && !same && param_dtype != PDB200_FLOAT32)
+    return fail(PDB200_INVALID_ARGUMENT, "fused_bias_dropout_residual_layer_norm: ln_scale / ln_bias must have x's dtype or float32");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+#define PDB_FLN_CASE(DT)                                                                                                   \
+  case DT: {                                                                                                               \
+    using T = typename CType<DT>::type;                                                                                    \
+    if (same)                                                                                                              \
+      return fln_typed<T, T>(static_cast<const T*>(x), static_cast<const T*>(residual), static_cast<const T*>(bias),       \
+                             static_cast<const T*>(ln_scale), static_cast<const T*>(ln_bias), static_cast<T*>(y),          \
+                             static_cast<T*>(bias_dropout_residual_out), ln_mean, ln_variance, rows, D, factor, ln_epsilon, st); \
+    return fln_typed<T, float>(static_cast<const T*>(x), static_cast<const T*>(residual), static_cast<const T*>(bias),     \
+                               static_cast<const float*>(ln_scale), static_cast<const float*>(ln_bias), static_cast<T*>(y), \
+                               static_cast<T*>(bias_dropout_residual_out), ln_mean, ln_variance, rows, D, factor, ln_epsilon, st); \
+  }
+  switch (dtype) {
+    PDB_FLN_CASE(PDB200_FLOAT32)
+    PDB_FLN_CASE(PDB200_FLOAT16)
+    PDB_FLN_CASE(PDB200_BFLOAT16)
+    case PDB200_FLOAT64:
+      if (!same) return fail(PDB200_INVALID_ARGUMENT, "fused_bias_dropout_residual_layer_norm: float64 input needs float64 parameters");
+      return fln_typed<double, double>(static_cast<const double*>(x), static_cast<const double*>(residual),
+                                       static_cast<const double*>(bias), static_cast<const double*>(ln_scale),
+                                       static_cast<const double*>(ln_bias), static_cast<double*>(y),
+                                       static_cast<double*>(bias_dropout_residual_out), ln_mean, ln_variance, rows, D, factor,
+                                       ln_epsilon, st);
+  }
+#undef PDB_FLN_CASE
+  return fail(PDB200_UNSUPPORTED, "fused_bias_dropout_residual_layer_norm: dtype must be float32/float64/float16/bfloat16, got code " +
+                                      std::to_string(dtype));
+}

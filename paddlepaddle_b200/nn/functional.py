@@ -43,6 +43,40 @@ def log_softmax(x, axis=-1, dtype=None, name=None):
     return out
 
 
+def softmax_mask_fuse(x, mask, name=None):
+    """paddle.incubate.softmax_mask_fuse (python/paddle/incubate/operators/softmax_mask_fuse.py:26): softmax(x + mask)
+    along the last axis for attention scores x [batch, heads, q_len, k_len] and a mask [batch, 1, q_len, k_len] shared by
+    the heads, in one pass (the sum is never written)."""
+    _require_cuda(x, mask)
+    if x.dim() != 4 or mask.dim() != 4:
+        raise ValueError("(InvalidArgument) softmax_mask_fuse expects 4-D x [batch, heads, q_len, k_len] and 4-D mask")
+    if mask.dtype != x.dtype and mask.dtype != torch.float32:
+        raise TypeError("(InvalidType) the mask must have the dtype of x or float32")
+    lib = L.load()
+    x, mask = x.contiguous(), mask.contiguous()
+    out = torch.empty_like(x)
+    xd, _ = L.dims_array(x.shape)
+    md, _ = L.dims_array(mask.shape)
+    L.check(lib.pdb200_fused_softmax_mask(_ptr(x), xd, _ptr(mask), md, _dtype_code(x.dtype), _dtype_code(mask.dtype), _ptr(out),
+                                          _stream()), lib)
+    return out
+
+
+def softmax_mask_fuse_upper_triangle(x):
+    """paddle.incubate.softmax_mask_fuse_upper_triangle (python/paddle/incubate/operators/softmax_mask_fuse_upper_triangle.py:26):
+    causal softmax of square attention scores x [batch, heads, seq, seq] — row q is normalised over columns <= q, the rest
+    of the row is zero."""
+    _require_cuda(x)
+    if x.dim() != 4:
+        raise ValueError("(InvalidArgument) softmax_mask_fuse_upper_triangle expects a 4-D x [batch, heads, seq, seq]")
+    lib = L.load()
+    x = x.contiguous()
+    out = torch.empty_like(x)
+    xd, _ = L.dims_array(x.shape)
+    L.check(lib.pdb200_fused_softmax_mask_upper_triangle(_ptr(x), xd, _dtype_code(x.dtype), _ptr(out), _stream()), lib)
+    return out
+
+
 def softmax_with_cross_entropy(logits, label, soft_label=False, ignore_index=-100, numeric_stable_mode=True,
                                return_softmax=False, axis=-1):
     """paddle.nn.functional.softmax_with_cross_entropy (python/paddle/nn/functional/loss.py): loss, or (loss, softmax).
@@ -119,6 +153,57 @@ def fused_rms_norm(x, norm_weight, norm_bias=None, epsilon=1e-6, begin_norm_axis
                                 ctypes.c_float(epsilon), int(begin_norm_axis), _dtype_code(x.dtype), _ptr(out), _ptr(res_out),
                                 _ptr(inv_var), _stream()), lib)
     return (out, res_out, inv_var) if residual is not None else (out, inv_var)
+
+
+def fused_bias_dropout_residual_layer_norm(x, residual, bias=None, ln_scale=None, ln_bias=None, dropout_rate=0.5,
+                                           ln_epsilon=1e-5, training=True, mode="upscale_in_train", name=None,
+                                           return_all=False):
+    """paddle.incubate.nn.functional.fused_bias_dropout_residual_layer_norm
+    (python/paddle/incubate/nn/functional/fused_transformer.py:334): y = layer_norm(residual + dropout(bias + x)) over the
+    last axis, in one pass.  return_all=True also returns the op's other outputs (bias_dropout_residual_out, ln_mean,
+    ln_variance) that Paddle keeps for the backward pass.  Deterministic cases only (dropout_rate == 0 or training=False):
+    a random dropout mask comes from the framework's generator, which is outside this path."""
+    _require_cuda(x, residual, bias, ln_scale, ln_bias)
+    if mode not in ("upscale_in_train", "downscale_in_infer"):
+        raise ValueError("mode argument should be 'downscale_in_infer' or 'upscale_in_train'")  # fused_transformer.py:425-428
+    if tuple(residual.shape) != tuple(x.shape) or residual.dtype != x.dtype:
+        raise ValueError("(InvalidArgument) residual must have the shape and dtype of x")
+    if x.dim() < 1:
+        raise ValueError("(InvalidArgument) x needs at least one dimension")
+    D = x.shape[-1]
+    if bias is not None and (bias.numel() != D or bias.dtype != x.dtype):
+        raise ValueError(f"(InvalidArgument) bias must have {D} elements of x's dtype")
+    pdt = None
+    for p in (ln_scale, ln_bias):
+        if p is None:
+            continue
+        if p.numel() != D:
+            raise ValueError(f"(InvalidArgument) ln_scale / ln_bias must have {D} elements, got {p.numel()}")
+        if pdt is not None and p.dtype != pdt:
+            raise ValueError("(InvalidArgument) ln_scale and ln_bias must share one dtype")
+        pdt = p.dtype
+    if pdt is not None and pdt != x.dtype and pdt != torch.float32:
+        raise ValueError("(InvalidArgument) ln_scale / ln_bias must have x's dtype or float32")
+    if training and dropout_rate != 0.0:
+        raise NotImplementedError("(Unimplemented) training with dropout_rate > 0 draws its mask from the framework's generator; "
+                                  "this path runs dropout_rate == 0 and training=False")
+    lib = L.load()
+    cont = lambda t: t.contiguous() if t is not None else None
+    x, residual, bias, ln_scale, ln_bias = cont(x), cont(residual), cont(bias), cont(ln_scale), cont(ln_bias)
+    rows = x.numel() // D if D else 0
+    stat_dt = torch.float64 if x.dtype == torch.float64 else torch.float32
+    y = torch.empty_like(x)
+    dro = torch.empty_like(x)
+    stats = torch.empty((2, rows), dtype=stat_dt, device=x.device)
+    d, r = L.dims_array(x.shape)
+    pcode = _dtype_code(pdt) if pdt is not None else _dtype_code(x.dtype)
+    L.check(lib.pdb200_fused_bias_dropout_residual_layer_norm(
+        _ptr(x), _ptr(residual), d, r, _ptr(bias), _ptr(ln_scale), _ptr(ln_bias), pcode, ctypes.c_float(float(dropout_rate)),
+        int(not training), int(mode == "upscale_in_train"), ctypes.c_float(float(ln_epsilon)), _dtype_code(x.dtype), _ptr(y),
+        _ptr(dro), _ptr(stats[0]), _ptr(stats[1]), _stream()), lib)
+    if return_all:
+        return y, dro, stats[0], stats[1]
+    return y
 
 
 def softmax_(x, axis=-1, dtype=None, name=None):

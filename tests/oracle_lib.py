@@ -374,6 +374,49 @@ class Oracle:
         self._check(rc)
         return out, res_out, inv
 
+    # ---- fused neighbours whose reference kernels are GPU-only: pinned THROUGH the reference CPU kernels on
+    # pre-combined inputs --------------------------------------------------------------------
+    def softmax_mask_fuse(self, x, mask):
+        """softmax(float(x) + float(mask)) along the last axis; x [B,H,Sq,Sk], mask [B,1,Sq,Sk], float32 arrays.  The
+        sum is formed here (one float addition per element, as the GPU kernel does); the softmax is the CPU kernel,
+        whose -64 clip differs from the reference GPU kernel's plain exp only below exp(-64) = 1.6e-28."""
+        z = (np.asarray(x, np.float32) + np.asarray(mask, np.float32)).astype(np.float32)
+        return self.softmax(z, -1)
+
+    def softmax_mask_fuse_upper_triangle(self, x):
+        """Causal softmax of float32 x [B,H,S,S]: row q = CPU softmax of its first q+1 elements, exact zeros after."""
+        x = np.asarray(x, np.float32)
+        B, H, S, S2 = x.shape
+        assert S == S2
+        out = np.zeros_like(x)
+        for q in range(S):
+            out[:, :, q, :q + 1] = self.softmax(np.ascontiguousarray(x[:, :, q, :q + 1]).reshape(B * H, q + 1), -1).reshape(B, H, q + 1)
+        return out
+
+    def fused_bias_dropout_residual_layer_norm(self, x, residual, bias, ln_scale, ln_bias, eps=1e-5, factor=1.0, half=None):
+        """Deterministic cases of layer_norm(residual + dropout(x + bias)) (keep = 1): d is formed here with the
+        reference's T arithmetic — every step rounded to T (half = 'bf16' | 'fp16' | None for float32; x / residual /
+        bias then arrive as uint16 bit patterns) — and the layer_norm is the reference CPU kernel on float(d).
+        -> (y float32, d as T, mean, variance)."""
+        if half is None:
+            up = lambda a: np.asarray(a, np.float32)
+            rt = lambda a: a.astype(np.float32)
+            down = lambda a: a
+        else:
+            to_h, to_f = (self.f32_to_bf16, self.bf16_to_f32) if half == "bf16" else (self.f32_to_fp16, self.fp16_to_f32)
+            up = to_f
+            rt = lambda a: to_f(to_h(a.astype(np.float32)))
+            down = lambda a: to_h(a.astype(np.float32))
+        t = up(x)
+        if bias is not None:
+            t = rt(t + up(bias))
+        if factor != 1.0:
+            t = rt(t * rt(np.float32(factor).reshape(1))[0])
+        d = rt(t + up(residual))
+        D = d.shape[-1]
+        y, mean, var = self.layer_norm(d.reshape(-1, D), 1, ln_scale, ln_bias, eps)
+        return y.reshape(d.shape), down(d), mean, var
+
     def _check(self, rc):
         if rc != 0:
             msg = ""

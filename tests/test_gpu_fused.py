@@ -1,0 +1,139 @@
+"""GPU parity of the fused neighbours of softmax / layer_norm: masked softmax (additive mask
+shared by the heads; causal upper triangle) and layer_norm(residual + dropout(x + bias)).  The reference kernels are
+GPU-only; the oracle pins the math THROUGH the reference CPU softmax / layer_norm kernels on pre-combined inputs
+(tests/oracle_lib.py).  Bars: fp32 rtol 1e-5 (atol 2e-28 covers the CPU kernel's exp(-64) clip, which the GPU kernels
+of the reference do not have); 1 ulp of the output type for 16-bit outputs; zeros above the diagonal exact."""
+import numpy as np
+import pytest
+import torch
+
+import oracle_lib as O
+from gpu_util import assert_half_close, to_dev, to_np
+
+pytestmark = pytest.mark.gpu
+
+import paddlepaddle_b200 as paddle  # noqa: E402
+
+F = paddle.nn.functional
+
+
+@pytest.fixture(scope="module")
+def cpu(port):
+    return O.Oracle("ref") if O.have_ref() else port
+
+
+def _half(port, a, dt):
+    if dt == "bfloat16":
+        return port.f32_to_bf16(a), "bf16", port.bf16_to_f32, port.f32_to_bf16
+    if dt == "float16":
+        return port.f32_to_fp16(a), "fp16", port.fp16_to_f32, port.f32_to_fp16
+    return a, None, (lambda v: v), (lambda v: v)
+
+
+@pytest.mark.parametrize("shape", [(2, 4, 128, 128), (1, 3, 512, 2048), (2, 2, 300, 1024), (1, 3, 40, 100), (1, 2, 8, 8192)])
+@pytest.mark.parametrize("dt,mask_dt", [("float32", "float32"), ("bfloat16", "bfloat16"), ("float16", "float32"),
+                                        ("float16", "float16")])
+def test_softmax_mask_fuse(port, cpu, shape, dt, mask_dt):
+    rng = np.random.default_rng(hash((shape, dt, mask_dt)) & 0xffff)
+    B, H, Sq, Sk = shape
+    x = (rng.standard_normal(shape) * 2).astype(np.float32)
+    mask = np.where(rng.random((B, 1, Sq, Sk)) < 0.3, np.float32(-10000.0), np.float32(0.0)).astype(np.float32)
+    mask[:, :, :, 0] = 0.0  # no row fully masked
+    mask[0, 0, 1, 1:3] = -np.inf
+    mask += (rng.standard_normal(mask.shape) * 0.1).astype(np.float32) * (mask == 0)
+    xb, xh, up, down = _half(port, x, dt)
+    mb, mh, mup, _ = _half(port, mask, mask_dt)
+    want = cpu.softmax_mask_fuse(up(xb), mup(mb))
+    got = F.softmax_mask_fuse(to_dev(xb, xh), to_dev(mb, mh))
+    assert tuple(got.shape) == shape
+    if xh is None:
+        np.testing.assert_allclose(to_np(got), want, rtol=1e-5, atol=2e-28)
+    else:
+        assert_half_close(to_np(got), down(want), 1, f"softmax_mask_fuse {shape} {dt}", kind=xh, atol=1e-30)
+
+
+def test_softmax_mask_fuse_errors():
+    x = torch.zeros((2, 2, 4, 64), device="cuda")
+    with pytest.raises(ValueError, match="second dim must be 1"):
+        F.softmax_mask_fuse(x, torch.zeros((2, 2, 4, 64), device="cuda"))
+    with pytest.raises(ValueError, match="should be equal"):
+        F.softmax_mask_fuse(x, torch.zeros((2, 1, 4, 32), device="cuda"))
+    with pytest.raises(TypeError):
+        F.softmax_mask_fuse(x, torch.zeros((2, 1, 4, 64), device="cuda", dtype=torch.float16))
+
+
+@pytest.mark.parametrize("shape", [(2, 4, 128, 128), (1, 2, 2048, 2048), (3, 2, 304, 304), (1, 2, 100, 100), (2, 150, 32, 32)])
+@pytest.mark.parametrize("dt", ["float32", "bfloat16", "float16"])
+def test_softmax_mask_fuse_upper_triangle(port, cpu, shape, dt):
+    rng = np.random.default_rng(hash((shape, dt, "tri")) & 0xffff)
+    x = (rng.standard_normal(shape) * 2).astype(np.float32)
+    x[0, 0, 5, 2] = -np.inf      # a masked-out score below the diagonal
+    x[0, 1, 3, 20:] = np.nan     # garbage ABOVE the diagonal must never be read into the result
+    xb, xh, up, down = _half(port, x, dt)
+    want = cpu.softmax_mask_fuse_upper_triangle(up(xb))  # the oracle reads row prefixes only
+    got = to_np(F.softmax_mask_fuse_upper_triangle(to_dev(xb, xh)))
+    S = shape[-1]
+    upper = np.triu(np.ones((S, S), bool), 1)
+    gz = got[..., upper]
+    assert not gz.any(), "entries above the diagonal must be exactly zero"
+    if xh is None:
+        np.testing.assert_allclose(got, want, rtol=1e-5, atol=2e-28)
+    else:
+        assert_half_close(got, down(want), 1, f"upper_triangle {shape} {dt}", kind=xh, atol=1e-30)
+
+
+def test_softmax_mask_fuse_upper_triangle_errors():
+    with pytest.raises(ValueError, match="Key seq len must be equal"):
+        F.softmax_mask_fuse_upper_triangle(torch.zeros((1, 1, 32, 64), device="cuda"))
+
+
+@pytest.mark.parametrize("rows,D,dt,pdt,has_bias,training,mode,p", [
+    (4096, 8192, "bfloat16", "bfloat16", True, True, "upscale_in_train", 0.0),
+    (2048, 1024, "float32", "float32", False, True, "upscale_in_train", 0.0),
+    (1024, 4096, "float16", "float32", True, False, "downscale_in_infer", 0.3),
+    (1000, 2048, "bfloat16", "float32", True, False, "upscale_in_train", 0.5),
+    (700, 768, "float32", "float32", True, False, "downscale_in_infer", 0.25),
+    (7, 100, "float32", "float32", True, True, "upscale_in_train", 0.0),
+    (33, 1000, "float16", "float16", False, False, "downscale_in_infer", 0.1),
+])
+def test_fused_bias_dropout_residual_layer_norm(port, cpu, rows, D, dt, pdt, has_bias, training, mode, p):
+    rng = np.random.default_rng(hash((rows, D, dt, pdt)) & 0xffff)
+    x = (rng.standard_normal((rows, D)) * 2).astype(np.float32)
+    res = (rng.standard_normal((rows, D)) * 2 + 0.5).astype(np.float32)
+    bias = rng.uniform(-1, 1, D).astype(np.float32) if has_bias else None
+    w = rng.uniform(0.5, 1.5, D).astype(np.float32)
+    b = rng.uniform(-0.5, 0.5, D).astype(np.float32)
+    xb, xh, up, down = _half(port, x, dt)
+    rb = _half(port, res, dt)[0]
+    bb = _half(port, bias, dt)[0] if has_bias else None
+    wb, wh, wup, _ = _half(port, w, pdt)
+    lb = _half(port, b, pdt)[0]
+    factor = 1.0 if training or mode == "upscale_in_train" else 1.0 - p
+    wy, wd, wm, wv = cpu.fused_bias_dropout_residual_layer_norm(xb, rb, bb, wup(wb), wup(lb), 1e-5, factor, half=xh)
+    y, d, m, v = F.fused_bias_dropout_residual_layer_norm(
+        to_dev(xb, xh), to_dev(rb, xh), to_dev(bb, xh) if has_bias else None, to_dev(wb, wh), to_dev(lb, wh),
+        dropout_rate=p, ln_epsilon=1e-5, training=training, mode=mode, return_all=True)
+    if xh is None:
+        assert np.array_equal(to_np(d), wd), "bias_dropout_residual_out must be bit-exact"
+        np.testing.assert_allclose(to_np(y), wy, rtol=1e-5, atol=2e-5)
+    else:
+        assert np.array_equal(to_np(d), wd), "bias_dropout_residual_out must be bit-exact (T arithmetic, step by step)"
+        assert_half_close(to_np(y), down(wy), 1, f"fused ln y [{rows},{D}] {dt}", kind=xh, atol=2e-5)
+    np.testing.assert_allclose(to_np(m), wm, rtol=1e-5, atol=1e-5 * float(np.abs(up(wd)).max()))
+    np.testing.assert_allclose(to_np(v), wv, rtol=2e-5)
+
+
+def test_fused_bias_dropout_residual_layer_norm_float64_and_errors(cpu):
+    rng = np.random.default_rng(11)
+    x, res = rng.standard_normal((16, 64)), rng.standard_normal((16, 64))
+    w, b = rng.uniform(0.5, 1.5, 64), rng.uniform(-0.5, 0.5, 64)
+    wy, wm, wv = cpu.layer_norm(x + res, 1, w, b, 1e-5)
+    y, d, m, v = F.fused_bias_dropout_residual_layer_norm(to_dev(x), to_dev(res), None, to_dev(w), to_dev(b), dropout_rate=0.0,
+                                                          return_all=True)
+    np.testing.assert_allclose(to_np(y), wy, rtol=1e-12, atol=1e-12)
+    np.testing.assert_allclose(to_np(m), wm, rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(to_np(v), wv, rtol=1e-12)
+    with pytest.raises(NotImplementedError):
+        F.fused_bias_dropout_residual_layer_norm(to_dev(x), to_dev(res), dropout_rate=0.5, training=True)
+    with pytest.raises(ValueError):
+        F.fused_bias_dropout_residual_layer_norm(to_dev(x), to_dev(res), mode="nope", dropout_rate=0.0)
