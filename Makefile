@@ -31,11 +31,3 @@ clean:
 
 .PHONY: all oracle clean
 
-# A/B build for measurements only: every streaming load coherent (ld.global instead of ld.global.nc)
-ALTDIR := build_alt
-ALTOBJS := $(addprefix $(ALTDIR)/,$(addsuffix .o,$(SRCS)))
-$(ALTDIR)/%.o: $(CSRC)/%.cu $(HDRS)
-	@mkdir -p $(ALTDIR)
-	$(NVCC) $(NVFLAGS) -DPDB200_COHERENT_STREAM -c $< -o $@
-alt: $(ALTOBJS)
-	$(NVCC) -shared -o $(ALTDIR)/libpdb200_coh.so $(ALTOBJS) -lcudart_static -lpthread -ldl -lrt

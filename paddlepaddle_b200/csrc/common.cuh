@@ -157,21 +157,18 @@ struct alignas(16) Vec {
   T v[N];
 };
 
-// Streaming 16-byte load: read-only path, do not allocate in L1 (each byte is used once).
+// Streaming 16-byte load: do not allocate in L1 (each byte is used once).  A COHERENT load (ld.global, not
+// ld.global.nc): several entry points are called in place (add_, softmax_, scale_: out == x), where the non-coherent
+// path is outside the PTX rules even though every chunk is read and written by the same thread.  The two forms run at
+// the same speed on B200 (profiles/r2_notes.txt: config 2 6914.1 vs 6914.8 GB/s, the whole table within noise).
 template <typename T>
 __device__ __forceinline__ Vec<T> ld_stream(const T* p) {
   Vec<T> r;
   uint4 u;
-#ifdef PDB200_COHERENT_STREAM
   asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
                : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
                : "l"(p)
                : "memory");
-#else
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
-               : "l"(p));
-#endif
   *reinterpret_cast<uint4*>(&r) = u;
   return r;
 }

@@ -98,6 +98,52 @@ __device__ __forceinline__ Pack<bool, 8> cmp8_packed(const Vec<T>& a, const Vec<
   *reinterpret_cast<uint2*>(&r) = make_uint2(w[0], w[1]);
   return r;
 }
+// 16-bit equal / not_equal, packed the same way.
+//   float16 : the smallest positive value (2^-24) is above the 1e-8 tolerance and the difference of two float16 is a
+//             multiple of 2^-24, so round16(a - b) is within the tolerance exactly when a == b: ONE ordered packed
+//             compare (NaN equals nothing, inf == inf, +0 == -0 — what the scalar functor gives).
+//   bfloat16: tiny values can differ by less than 1e-8, so equal = (a == b) | (|a - b| <= tol) with the difference in
+//             packed bf16 arithmetic (one rounding) and tol = 0x322B, the largest bfloat16 not above 1e-8.  Same bits as
+//             the reference's round_bf16(float(a) - float(b)): when the float subtraction is inexact the operands lie
+//             more than 2^16 apart and both roundings return the larger one; a == b covers equal infinities, whose
+//             difference is NaN.
+__device__ __forceinline__ uint32_t eq2_mask(__half2 a, __half2 b) { return __heq2_mask(a, b); }
+__device__ __forceinline__ uint32_t eq2_mask(__nv_bfloat162 a, __nv_bfloat162 b) {
+  const unsigned int tol_bits = 0x322B322Bu;
+  const __nv_bfloat162 tol = *reinterpret_cast<const __nv_bfloat162*>(&tol_bits);
+  return __heq2_mask(a, b) | __hle2_mask(__habs2(__hsub2(a, b)), tol);
+}
+template <typename T, bool NEGATE>
+__device__ __forceinline__ Pack<bool, 8> eq8_packed(const Vec<T>& a, const Vec<T>& b) {
+  using T2 = typename Half2Of<T>::type;
+  const T2* pa = reinterpret_cast<const T2*>(&a);
+  const T2* pb = reinterpret_cast<const T2*>(&b);
+  uint32_t w[2];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    uint32_t m0 = eq2_mask(pa[2 * h], pb[2 * h]), m1 = eq2_mask(pa[2 * h + 1], pb[2 * h + 1]);
+    if (NEGATE) {
+      m0 = ~m0;
+      m1 = ~m1;
+    }
+    m0 &= 0x00010001u;
+    m1 &= 0x00010001u;
+    w[h] = (m0 & 0x1u) | ((m0 >> 8) & 0x100u) | ((m1 & 0x1u) << 16) | ((m1 << 8) & 0x01000000u);
+  }
+  Pack<bool, 8> r;
+  *reinterpret_cast<uint2*>(&r) = make_uint2(w[0], w[1]);
+  return r;
+}
+#define PDB_PACKED_EQ(T)                                                                                      \
+  template <> struct VecApply<T, EqualOp<T>> {                                                                \
+    static __device__ __forceinline__ Pack<bool, 8> run(const Vec<T>& a, const Vec<T>& b) { return eq8_packed<T, false>(a, b); } \
+  };                                                                                                          \
+  template <> struct VecApply<T, NotEqualOp<T>> {                                                             \
+    static __device__ __forceinline__ Pack<bool, 8> run(const Vec<T>& a, const Vec<T>& b) { return eq8_packed<T, true>(a, b); } \
+  };
+PDB_PACKED_EQ(__nv_bfloat16)
+PDB_PACKED_EQ(__half)
+#undef PDB_PACKED_EQ
 #define PDB_PACKED_CMP(T)                                                                                     \
   template <> struct VecApply<T, LessThanOp<T>> {                                                             \
     static __device__ __forceinline__ Pack<bool, 8> run(const Vec<T>& a, const Vec<T>& b) { return cmp8_packed<T, false>(a, b); } \

@@ -33,6 +33,12 @@ namespace pdb200 {
 struct AddFln { __device__ __forceinline__ float operator()(float a, float b) const { return a + b; } };
 template <typename U> struct AddFlnU { __device__ __forceinline__ U operator()(U a, U b) const { return a + b; } };
 
+// separately rounded multiply / add (the compiler must not contract them into an fma: the reference rounds each step)
+__device__ __forceinline__ float mul_sep(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double mul_sep(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float add_sep(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ double add_sep(double a, double b) { return __dadd_rn(a, b); }
+
 // round a float to T and back (identity for float): the reference computes this chain in T arithmetic
 template <typename T>
 __device__ __forceinline__ float round_to(float v) { return cvt<float>(cvt<T>(v)); }
@@ -90,15 +96,15 @@ fln_pipe_kernel(const T* __restrict__ x, const T* __restrict__ residual, const T
           float b[V];
           unpack_to_float<T>(ld_cached(bias + off), b);
 #pragma unroll
-          for (int k = 0; k < V; ++k) e[c * V + k] = round_to<T>(e[c * V + k] + b[k]);
+          for (int k = 0; k < V; ++k) e[c * V + k] = round_to<T>(__fadd_rn(e[c * V + k], b[k]));
         }
         if constexpr (SCALED) {
 #pragma unroll
-          for (int k = 0; k < V; ++k) e[c * V + k] = round_to<T>(e[c * V + k] * factor);
+          for (int k = 0; k < V; ++k) e[c * V + k] = round_to<T>(__fmul_rn(e[c * V + k], factor));  // never fused with the add below
         }
         Vec<T> dv;
 #pragma unroll
-        for (int k = 0; k < V; ++k) e[c * V + k] += r[k];
+        for (int k = 0; k < V; ++k) e[c * V + k] = __fadd_rn(e[c * V + k], r[k]);
         pack_from_float<T>(&e[c * V], dv);
         st_stream(dro + row * D + off, dv);
         unpack_to_float<T>(dv, &e[c * V]);  // the statistics see the rounded value, like the reference
@@ -182,9 +188,9 @@ __global__ void __launch_bounds__(1024) fln_rows_kernel(const T* x, const T* res
   U sum = U(0);
   for (int64_t i = threadIdx.x; i < D; i += blockDim.x) {
     T t = x[base + i];
-    if (bias != nullptr) t = cvt<T>(cvt<U>(t) + cvt<U>(bias[i]));
-    if (scaled) t = cvt<T>(cvt<U>(t) * cvt<U>(cvt<T>((U)factor)));
-    const T d = cvt<T>(cvt<U>(t) + cvt<U>(residual[base + i]));
+    if (bias != nullptr) t = cvt<T>(add_sep(cvt<U>(t), cvt<U>(bias[i])));
+    if (scaled) t = cvt<T>(mul_sep(cvt<U>(t), cvt<U>(cvt<T>((U)factor))));  // rounded on its own: never fused with the add
+    const T d = cvt<T>(add_sep(cvt<U>(t), cvt<U>(residual[base + i])));
     dro[base + i] = d;  // written after the last read of x / residual at i by this thread: in-place safe
     sum += cvt<U>(d);
   }

@@ -14,10 +14,18 @@ namespace pdb200 {
 
 enum FinKind { kFinCast = 0, kFinMean = 1 };
 
+// Accumulator of a reduction that produces O: MPTypeTrait, except that 1- and 2-byte integers are summed in int32
+// (shuffles move 4-byte words); the final cast back wraps, and modular sums do not depend on the width they were
+// carried in, so the result equals the reference's sum in T.
+template <typename O> struct RedAcc { using type = typename AccType<O>::type; };
+template <> struct RedAcc<int8_t> { using type = int32_t; };
+template <> struct RedAcc<uint8_t> { using type = int32_t; };
+template <> struct RedAcc<int16_t> { using type = int32_t; };
+
 // One (input T, output O) pair of one operator family.
 template <typename T, typename O, template <typename> class OpT, int FIN>
 struct ReduceRunner {
-  using A = typename AccType<O>::type;  // MPTypeTrait of the dtype the reduction runs in
+  using A = typename RedAcc<O>::type;  // MPTypeTrait of the dtype the reduction runs in
   using Op = OpT<A>;
   static size_t workspace(const ReducePlan& plan) { return reduce_scratch_bytes<T, A>(plan); }
   static int run(const ReducePlan& plan, const void* x, void* out, void* ws, size_t ws_bytes,

@@ -18,6 +18,10 @@ int sum_mean_dispatch(bool mean, bool query, size_t* ws_out, const ReducePlan& p
     PDB_REDUCE_PAIR(PDB200_INT32, PDB200_INT64, SumOp, kFinCast)
     PDB_REDUCE_PAIR(PDB200_INT32, PDB200_INT32, SumOp, kFinCast)
     PDB_REDUCE_PAIR(PDB200_BOOL, PDB200_INT64, SumOp, kFinCast)
+    // the small integers keep their dtype and wrap (kps/reduce_kernel.cu:382-400 registers int8 / uint8 / int16 too)
+    PDB_REDUCE_PAIR(PDB200_INT8, PDB200_INT8, SumOp, kFinCast)
+    PDB_REDUCE_PAIR(PDB200_UINT8, PDB200_UINT8, SumOp, kFinCast)
+    PDB_REDUCE_PAIR(PDB200_INT16, PDB200_INT16, SumOp, kFinCast)
     return fail(PDB200_UNSUPPORTED, "sum: unsupported dtype pair x=" + std::to_string(x_dtype) +
                                         " out=" + std::to_string(out_dtype));
   }

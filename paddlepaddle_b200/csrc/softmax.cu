@@ -29,6 +29,9 @@
 //        exp through ex2.approx on the pre-scaled difference.
 #include <cooperative_groups.h>
 
+#include <map>
+#include <tuple>
+
 #include "common.cuh"
 #include "rowpipe.cuh"
 #include "shape.h"
@@ -432,6 +435,192 @@ __global__ void __launch_bounds__(1024) softmax_rows_cluster_kernel(const T* __r
   cluster.sync();  // nobody leaves while a peer may still be reading its xchg[]
 }
 
+// ---- cluster_pipe: persistent clusters, the row in registers ACROSS the cluster, one DSMEM exchange per row ---------
+// The single-shot kernel above exposes everything: one bulk copy, then waiting; three sweeps over shared memory; three
+// cluster barriers; one row per cluster, then exit (3.8-4.3 TB/s on vocabulary-sized rows).  Here a cluster of `cs`
+// CTAs is PERSISTENT over rows r = cluster, cluster + n_clusters, ...; CTA `rank` owns elements [rank*slice, +slice)
+// of every row and receives them through a 2-stage ring (cp.async.bulk of this CTA's slice of row k+1 is issued as soon
+// as row k's slice has been read into registers, i.e. it overlaps everything below).  Per row and CTA:
+//   registers <- slice; local max (one CTA barrier); e = exp(x - local max) kept in registers, local sum (one CTA
+//   barrier); (local max, local sum) published in shared memory; ONE cluster barrier (arrive.release / wait.acquire);
+//   lane r of every warp reads CTA r's pair through DSMEM, a shuffle tree folds them with the online rescale
+//   sum = sum_r s_r * exp(m_r - m), m = max_r m_r, identically in every warp of every CTA; y = e * exp(m_loc - m) / sum.
+// One exp per element, one read of HBM, no sweep over shared memory after the first.  The published pairs are double
+// buffered by row parity: a CTA writes pair (k+2) only after the cluster barrier of row k+1, which every peer reaches
+// after it has read pair k.
+// Special values follow the scalar rule of the CPU kernel (softmax_impl.h:36-42): NaN / +inf / a row of -inf poison the
+// whole row through the sum; a slice that is all -inf contributes its clipped exp(-64) terms without an inf - inf.
+__device__ __forceinline__ unsigned cluster_ctarank() {
+  unsigned r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ unsigned cluster_nctarank() {
+  unsigned r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+// load a float from the same shared-memory variable of CTA `rank` of this cluster
+__device__ __forceinline__ float ld_dsmem_f32(const float* local_ptr, unsigned rank) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local_ptr)), "r"(rank));
+  float v;
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
+  return v;
+}
+
+template <typename T, int C, bool LOG>
+__global__ void __launch_bounds__(512, 1) softmax_cluster_pipe_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t rows,
+                                                                      int64_t dim, int slice, int stages,
+                                                                      float* __restrict__ stats) {
+  constexpr int V = Vec<T>::N;
+  constexpr float kLog2e = 1.4426950408889634f;
+  extern __shared__ __align__(128) unsigned char ring_raw[];
+  T* ring = reinterpret_cast<T*>(ring_raw);
+  __shared__ uint64_t full[4];
+  __shared__ float red[2][32];
+  __shared__ float xchg[2][2];  // [row parity][0] local max, [1] local sum — read by the peers through DSMEM
+  const unsigned rank = cluster_ctarank(), cs = cluster_nctarank();
+  const int64_t cluster_id = blockIdx.x / cs, n_clusters = gridDim.x / cs;
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31;
+  const int64_t begin = (int64_t)rank * slice;
+  int n = (int)(dim - begin < 0 ? 0 : (dim - begin > slice ? slice : dim - begin));
+  const uint32_t bytes = (uint32_t)n * sizeof(T);
+  if (tid == 0) {
+    for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
+    mbar_fence_init();
+  }
+  block_reduce_1sync_init(red[0], -INFINITY);
+  block_reduce_1sync_init(red[1], 0.f);
+  __syncthreads();
+  cluster_arrive_release();  // every CTA of the cluster is running before anyone touches a peer's shared memory
+  cluster_wait_acquire();
+  if (tid == 0 && n > 0) {
+    for (int s = 0; s < stages; ++s) {
+      const int64_t r = cluster_id + s * n_clusters;
+      if (r < rows) {
+        mbar_expect_tx(&full[s], bytes);
+        bulk_load_row(ring + (size_t)s * slice, x + r * dim + begin, bytes, &full[s]);
+      }
+    }
+  }
+  int s = 0, par = 0;
+  uint32_t phase = 0;
+  for (int64_t row = cluster_id; row < rows; row += n_clusters) {
+    if (n > 0) mbar_wait(&full[s], phase);
+    const T* st = ring + (size_t)s * slice;
+    float e[C * V];
+    float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + tid) * V;
+      if (off < n) {
+        unpack_to_float<T>(lds_vec(st + off), &e[c * V]);
+      } else {
+#pragma unroll
+        for (int k = 0; k < V; ++k) e[c * V + k] = -INFINITY;
+      }
+#pragma unroll
+      for (int k = 0; k < V; ++k) mx[k & 3] = fmaxf(mx[k & 3], e[c * V + k]);
+    }
+    float m_loc = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+    m_loc = block_reduce_1sync(m_loc, MaxF<float>(), red[0]);  // its barrier also means: stage s fully read
+    if (tid == 0 && n > 0) {
+      const int64_t nrow = row + (int64_t)stages * n_clusters;
+      if (nrow < rows) {
+        fence_proxy_async_smem();
+        mbar_expect_tx(&full[s], bytes);
+        bulk_load_row(ring + (size_t)s * slice, x + nrow * dim + begin, bytes, &full[s]);
+      }
+    }
+    // a slice of -inf only: shift by 0, so that -inf clips to exp(-64) instead of turning into inf - inf
+    const bool dead = m_loc == -INFINITY;
+    const float shift = dead ? 0.f : -m_loc * kLog2e;
+    float sm[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int off = (c * nt + tid) * V;
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        float p;
+        const float t = max_nan(fmaf(e[c * V + k], kLog2e, shift), -64.0f * kLog2e);
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p) : "f"(t));
+        if constexpr (!LOG) e[c * V + k] = p;  // LOG keeps x: its output term is the clipped difference itself
+        if (off < n) sm[k & 3] += p;
+      }
+    }
+    float s_loc = (sm[0] + sm[1]) + (sm[2] + sm[3]);
+    s_loc = block_reduce_1sync(s_loc, AddF<float>(), red[1]);
+    // Only the thread that publishes needs release semantics.  A release arrive by every thread made each of them
+    // wait for its own streaming stores of the previous row to drain (stall_membar 2.4 of 14 cycles per instruction,
+    // profiles/r2c_softmax_vocab_bf16.txt); the others arrive relaxed.
+    if (tid == 0) {
+      xchg[par][0] = m_loc;
+      xchg[par][1] = s_loc;
+      asm volatile("barrier.cluster.arrive.release;" ::: "memory");
+    } else {
+      asm volatile("barrier.cluster.arrive.relaxed;" ::: "memory");
+    }
+    cluster_wait_acquire();
+    float pm = -INFINITY, ps = 0.f;
+    if (lane < (int)cs) {
+      pm = ld_dsmem_f32(&xchg[par][0], lane);
+      ps = ld_dsmem_f32(&xchg[par][1], lane);
+    }
+    const float gm = group_reduce<32>(pm, MaxF<float>());
+    float contrib = ps;
+    if (pm != -INFINITY) {
+      float f;
+      asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(f) : "f"((pm - gm) * kLog2e));
+      contrib = ps * f;
+    }
+    float gs = group_reduce<32>(contrib, AddF<float>());
+    if (gm == -INFINITY) gs = __int_as_float(0x7fc00000);  // a row of -inf: inf - inf in the CPU kernel, NaN everywhere
+    if (stats != nullptr && rank == 0 && tid == 0) { stats[2 * row] = gm; stats[2 * row + 1] = logf(gs); }
+    T* dst = y + row * dim + begin;
+    if constexpr (LOG) {
+      const float lg = logf(gs);
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        const int off = (c * nt + tid) * V;
+        if (off < n) {
+          float r[V];
+#pragma unroll
+          for (int k = 0; k < V; ++k) r[k] = max_nan(e[c * V + k] - gm, -64.0f) - lg;
+          Vec<T> o;
+          pack_from_float<T>(r, o);
+          st_stream(dst + off, o);
+        }
+      }
+    } else {
+      float f = 1.0f;
+      if (!dead) asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(f) : "f"((m_loc - gm) * kLog2e));
+      const float kk = f / gs;
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        const int off = (c * nt + tid) * V;
+        if (off < n) {
+          float r[V];
+#pragma unroll
+          for (int k = 0; k < V; ++k) r[k] = e[c * V + k] * kk;
+          Vec<T> o;
+          pack_from_float<T>(r, o);
+          st_stream(dst + off, o);
+        }
+      }
+    }
+    par ^= 1;
+    if (++s == stages) {
+      s = 0;
+      phase ^= 1;
+    }
+  }
+  cluster_arrive_release();  // nobody leaves while a peer may still be reading its xchg[]
+  cluster_wait_acquire();
+}
+
 // ---- rows_stream -----------------------------------------------------------------------
 template <typename T, bool LOG>
 __global__ void __launch_bounds__(1024) softmax_rows_stream_kernel(const T* x, T* y, int64_t dim,
@@ -479,6 +668,113 @@ __global__ void __launch_bounds__(256) softmax_cols_kernel(const T* x, T* y, int
   if (stats != nullptr) { stats[2 * (o * inner + col)] = m; stats[2 * (o * inner + col) + 1] = log_acc<A>(sum); }
   for (int64_t r = 0; r < dim; ++r)
     dst[r * inner] = cvt<T>(LOG ? clipped_diff<A>(cvt<A>(src[r * inner]), m) - inv : clipped_exp<A>(cvt<A>(src[r * inner]), m) * inv);
+}
+
+// ---- cols_tile: softmax along the middle axis, vectorised along `inner` ------------------------------------------
+// blockDim = (32, TY).  Thread (tx, ty) owns V adjacent columns (one 16-byte load per row: a warp reads 512
+// contiguous bytes) and rows ty, ty + TY, ... of the reduced axis.  Sweep 1 keeps a running (max, sum) per column —
+// four rows at a time, one rescale per batch, 1.25 exp per element — the TY partial pairs of a column are folded
+// through shared memory; sweep 2 re-reads x (partly from L2), normalises and writes.  Two reads + one write of HBM at
+// worst, against three sweeps of scalar, one-thread-per-column loads in softmax_cols_kernel (1.3 TB/s on bf16
+// [64,2048,4096] axis 1, profiles/r2_notes.txt).  Elements seen while a column's running max is still -inf contribute
+// their clipped exp(-64) to a separate, never rescaled sum (the CPU kernel's max(x - max, -64) does not depend on the
+// max for them); NaN and +inf poison the column through the sum, a column of -inf only comes out NaN.
+template <typename T, bool LOG>
+__global__ void __launch_bounds__(256) softmax_cols_tile_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t dim,
+                                                                int64_t inner, int64_t col_tiles, float* __restrict__ stats) {
+  constexpr int V = Vec<T>::N;
+  constexpr int U = 4;
+  constexpr float kLog2e = 1.4426950408889634f;
+  extern __shared__ __align__(16) float cols_smem[];  // [TY][32 * V][2]
+  const int tx = threadIdx.x, ty = threadIdx.y, TY = blockDim.y;
+  const int64_t o = (int64_t)blockIdx.x / col_tiles;
+  const int64_t ct = (int64_t)blockIdx.x - o * col_tiles;
+  const int64_t col = (ct * 32 + tx) * V;
+  const bool active = col < inner;
+  const T* src = x + o * dim * inner + col;
+  T* dst = y + o * dim * inner + col;
+  float m[V], sacc[V], sabs[V];
+#pragma unroll
+  for (int k = 0; k < V; ++k) { m[k] = -INFINITY; sacc[k] = 0.f; sabs[k] = 0.f; }
+  const float kClip = 1.603810890548638e-28f;  // exp(-64)
+  if (active) {
+    int64_t r = ty;
+    for (; r + (int64_t)(U - 1) * TY < dim; r += (int64_t)U * TY) {
+      float v[U][V];
+#pragma unroll
+      for (int u = 0; u < U; ++u) unpack_to_float<T>(ld_stream(src + (r + (int64_t)u * TY) * inner), v[u]);
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        float nm = m[k];
+#pragma unroll
+        for (int u = 0; u < U; ++u) nm = fmaxf(nm, v[u][k]);
+        if (nm == -INFINITY) {  // nothing finite yet: -inf clips to exp(-64) whatever the max turns out to be; NaN propagates
+#pragma unroll
+          for (int u = 0; u < U; ++u) sabs[k] += (v[u][k] != v[u][k]) ? v[u][k] : kClip;
+        } else {
+          float resc;
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(resc) : "f"((m[k] - nm) * kLog2e));  // 0 when m was -inf
+          float add = 0.f;
+#pragma unroll
+          for (int u = 0; u < U; ++u) add += fast_clipped_exp(v[u][k], -nm * kLog2e);
+          sacc[k] = fmaf(sacc[k], resc, add);
+          m[k] = nm;
+        }
+      }
+    }
+    for (; r < dim; r += TY) {
+      float v[V];
+      unpack_to_float<T>(ld_stream(src + r * inner), v);
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        const float nm = fmaxf(m[k], v[k]);
+        if (nm == -INFINITY) {
+          sabs[k] += (v[k] != v[k]) ? v[k] : kClip;
+        } else {
+          float resc;
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(resc) : "f"((m[k] - nm) * kLog2e));
+          sacc[k] = fmaf(sacc[k], resc, fast_clipped_exp(v[k], -nm * kLog2e));
+          m[k] = nm;
+        }
+      }
+    }
+  }
+  // fold the TY partials of every column (rank order, identical in every thread that needs them)
+  float* mine = cols_smem + ((size_t)ty * 32 + tx) * V * 3;
+#pragma unroll
+  for (int k = 0; k < V; ++k) { mine[3 * k] = m[k]; mine[3 * k + 1] = sacc[k]; mine[3 * k + 2] = sabs[k]; }
+  __syncthreads();
+  float M[V], inv[V];
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    float gm = -INFINITY;
+    for (int t = 0; t < TY; ++t) gm = fmaxf(gm, cols_smem[(((size_t)t * 32 + tx) * V + k) * 3]);
+    float gs = 0.f;
+    for (int t = 0; t < TY; ++t) {
+      const float* p = cols_smem + (((size_t)t * 32 + tx) * V + k) * 3;
+      float f = 0.f;
+      if (p[0] != -INFINITY) asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(f) : "f"((p[0] - gm) * kLog2e));
+      gs += fmaf(p[1], f, p[2]);
+    }
+    if (gm == -INFINITY) gs = __int_as_float(0x7fc00000);  // a column of -inf: NaN, as inf - inf gives in the CPU kernel
+    M[k] = gm;
+    inv[k] = row_constant<LOG, float>(gs);
+    if (stats != nullptr && ty == 0 && active && col + k < inner) {
+      stats[2 * (o * inner + col + k)] = gm;
+      stats[2 * (o * inner + col + k) + 1] = logf(gs);
+    }
+  }
+  if (!active) return;
+  for (int64_t r = ty; r < dim; r += TY) {
+    float v[V];
+    unpack_to_float<T>(ld_stream(src + r * inner), v);
+#pragma unroll
+    for (int k = 0; k < V; ++k)
+      v[k] = LOG ? max_nan(v[k] - M[k], -64.0f) - inv[k] : fast_clipped_exp(v[k], -M[k] * kLog2e) * inv[k];
+    Vec<T> ov;
+    pack_from_float<T>(v, ov);
+    st_stream(dst + r * inner, ov);
+  }
 }
 
 template <typename T>
@@ -549,6 +845,81 @@ int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, typename AccT
   }
 }
 
+// Persistent cluster pipeline (softmax_cluster_pipe_kernel): rows of up to 8 x 512 x 32 values.  < 0: does not apply.
+template <typename T, bool LOG>
+int try_softmax_cluster_pipe(const T* x, T* y, int64_t outer, int64_t dim, typename AccType<T>::type* stats, cudaStream_t st) {
+  if constexpr (std::is_same<T, double>::value) {
+    return -1;  // computes in float
+  } else {
+    constexpr int VN = Vec<T>::N;
+    constexpr int kThreads = 512, kMaxVals = 32;  // values a thread keeps in registers
+    if (knobs().no_cluster_pipe) return -1;
+    const int64_t cap = (int64_t)kThreads * kMaxVals;  // elements per CTA
+    int cs = 2;
+    while (cs < 8 && (dim + cs - 1) / cs > cap) cs <<= 1;
+    // few rows: more, smaller slices put more SMs to work on each row
+    while (cs < 8 && outer * cs < (int64_t)sm_count()) cs <<= 1;
+    int64_t slice = (dim + cs - 1) / cs;
+    slice = (slice + VN - 1) / VN * VN;
+    if (slice > cap) return -1;
+    const int64_t nchunk = slice / VN;
+    int C = 1;
+    while (C < kMaxVals / VN && (nchunk + C - 1) / C > kThreads) C <<= 1;
+    int threads = (int)((nchunk + C - 1) / C);
+    threads = (threads + 31) / 32 * 32;
+    if (threads > kThreads || threads * C < nchunk) return -1;
+    const int stages = 2;
+    const size_t smem = (size_t)stages * slice * sizeof(T);
+    auto launch = [&](auto kern) -> int {
+      FuncAttrHold hold;  // the dynamic shared-memory size follows the slice: held until the launch call has returned
+      if (!func_attr_apply(reinterpret_cast<const void*>(kern), (int)smem, -1, &hold)) return -1;
+      cudaLaunchConfig_t cfg{};
+      cfg.blockDim = dim3(threads);
+      cfg.dynamicSmemBytes = smem;
+      cfg.stream = st;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = cs;
+      attr[0].val.clusterDim.y = 1;
+      attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      // how many clusters the device holds at once: asked once per (kernel, device, geometry)
+      static std::map<std::tuple<const void*, int, int, size_t, int>, int> resident;  // guarded by the attribute lock
+      int dev = 0;
+      cudaGetDevice(&dev);
+      const auto key = std::make_tuple(reinterpret_cast<const void*>(kern), dev, threads, smem, cs);
+      auto it = resident.find(key);
+      if (it == resident.end()) {
+        int ncl = 0;
+        cfg.gridDim = dim3((unsigned)(cs * sm_count()));
+        if (cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg) != cudaSuccess) {
+          cudaGetLastError();
+          ncl = 0;
+        }
+        it = resident.emplace(key, ncl).first;
+      }
+      int64_t ncl = it->second;
+      if (ncl < 1) return -1;
+      if (ncl > outer) ncl = outer;
+      cfg.gridDim = dim3((unsigned)(ncl * cs));
+      if (cudaLaunchKernelEx(&cfg, kern, x, y, outer, dim, (int)slice, stages, stats) != cudaSuccess) {
+        cudaGetLastError();
+        return -1;
+      }
+      return after_launch("softmax_cluster_pipe");
+    };
+    switch (C) {
+      case 1: return launch(softmax_cluster_pipe_kernel<T, 1, LOG>);
+      case 2: return launch(softmax_cluster_pipe_kernel<T, 2, LOG>);
+      case 4: return launch(softmax_cluster_pipe_kernel<T, 4, LOG>);
+      case 8:
+        if constexpr (kMaxVals / VN >= 8) return launch(softmax_cluster_pipe_kernel<T, 8, LOG>);
+    }
+    return -1;
+  }
+}
+
 // Cluster route: returns < 0 when the row does not fit 8 CTAs' shared memory.
 template <typename T, bool LOG>
 int try_softmax_cluster(const T* x, T* y, int64_t outer, int64_t dim, typename AccType<T>::type* stats, cudaStream_t st) {
@@ -559,9 +930,7 @@ int try_softmax_cluster(const T* x, T* y, int64_t outer, int64_t dim, typename A
   // split until a slice is <= 32 KB (several CTAs then share an SM and overlap their phases), and
   // further while there are too few rows to fill the SMs
   size_t slice_target = 64 * 1024;  // 64 KB slices: bf16 [4096,128256] 0.562 -> 0.517 ms vs 32 KB (fewer cluster barriers per byte)
-  if (const char* v = getenv("PDB200_CLUSTER_SLICE_KB")) {  // tuning knob (profiles/sweep notes)
-    if (atoi(v) >= 4) slice_target = (size_t)atoi(v) * 1024;
-  }
+  if (knobs().cluster_slice_kb >= 4) slice_target = (size_t)knobs().cluster_slice_kb * 1024;  // tuning knob
   while (cs < 8 && (row_bytes / cs > slice_target || outer * cs < 2 * (int64_t)sm_count())) cs <<= 1;
   int64_t slice = (dim + cs - 1) / cs;
   slice = (slice + VN - 1) / VN * VN;
@@ -617,7 +986,9 @@ int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, t
                  : launch_rows_reg<T, false, LOG>(x, y, outer, (int)dim, G, C, stats, st);
     }
     if (vec) {
-      const int rc = try_softmax_cluster<T, LOG>(x, y, outer, dim, stats, st);
+      int rc = try_softmax_cluster_pipe<T, LOG>(x, y, outer, dim, stats, st);
+      if (rc >= 0) return rc;
+      rc = try_softmax_cluster<T, LOG>(x, y, outer, dim, stats, st);
       if (rc >= 0) return rc;
     }
     if (outer > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "softmax: too many rows for one launch");
@@ -636,6 +1007,23 @@ int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, t
     }
     softmax_rows_stream_kernel<T, LOG><<<(unsigned)outer, 1024, 0, st>>>(x, y, dim, stats);
     return after_launch("softmax_rows_stream");
+  }
+  if constexpr (!std::is_same<T, double>::value) {
+    // vector route: 16-byte loads along `inner`; in place is fine (sweep 2 reads and writes each chunk in one thread, after
+    // sweep 1 of the whole CTA tile is done)
+    if (inner % VN == 0 && is_aligned16(x) && is_aligned16(y) && dim >= 2) {
+      const int64_t ctiles = (inner / VN + 31) / 32;
+      const int64_t nblk = ctiles * outer;
+      if (nblk <= 0x7fffffffLL) {
+        // more thread-rows when there are few column tiles to fill the machine with
+        int TY = 8;
+        while (TY > 1 && TY * 2 > dim) TY >>= 1;
+        const size_t smem = (size_t)TY * 32 * VN * 3 * sizeof(float);
+        dim3 block(32, TY);
+        softmax_cols_tile_kernel<T, LOG><<<(unsigned)nblk, block, smem, st>>>(x, y, dim, inner, ctiles, stats);
+        return after_launch("softmax_cols_tile");
+      }
+    }
   }
   int threads = 32;
   while (threads < 256 && threads < inner) threads <<= 1;

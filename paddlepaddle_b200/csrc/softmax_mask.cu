@@ -43,7 +43,7 @@ __device__ __forceinline__ float exp_shifted(float x, float neg_m_log2e) {
 template <typename T, typename MT, int C, bool EXACT, bool TRI>
 __global__ void __launch_bounds__(512) softmax_mask_pipe_kernel(const T* __restrict__ x, const MT* __restrict__ mask,
                                                                 T* __restrict__ y, int64_t rows, int dim, int sq, int heads,
-                                                                int stages) {
+                                                                int stages, int contiguous) {
   constexpr int V = Vec<T>::N;
   constexpr int MV = Vec<MT>::N;  // mask elements per 16-byte load (V, or V/2 for a float mask of a 16-bit x)
   extern __shared__ __align__(128) unsigned char ring_raw[];
@@ -53,7 +53,18 @@ __global__ void __launch_bounds__(512) softmax_mask_pipe_kernel(const T* __restr
   const uint32_t x_bytes = (uint32_t)dim * sizeof(T);
   const uint32_t m_bytes = TRI ? 0u : (uint32_t)dim * sizeof(MT);
   const size_t stage_bytes = (size_t)x_bytes + m_bytes;
-  const int64_t row_step = gridDim.x;
+  // Row -> CTA mapping: strided (row = cta + k*grid: a persistent grid then sweeps the rows in order) or, for short-lived
+  // CTAs, one contiguous slab per CTA.  Either way rows are visited in roughly increasing order machine-wide, so the
+  // mask rows of head h are re-read by head h+1 about 2*Sq*Sk*sizeof(T) bytes of traffic later — out of L2.  (Strided
+  // short-lived CTAs touch four batches at once and push that distance past the L2 size: 1.24 ms instead of 0.66 ms
+  // on bf16 [8,32,2048,2048].)
+  int64_t row_first = blockIdx.x, row_step = gridDim.x, row_end = rows;
+  if (contiguous) {
+    const int64_t slab = (rows + gridDim.x - 1) / gridDim.x;
+    row_first = (int64_t)blockIdx.x * slab;
+    row_step = 1;
+    row_end = row_first + slab < rows ? row_first + slab : rows;
+  }
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
     mbar_fence_init();
@@ -78,13 +89,13 @@ __global__ void __launch_bounds__(512) softmax_mask_pipe_kernel(const T* __restr
   };
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) {
-      const int64_t r = blockIdx.x + s * row_step;
-      if (r < rows) fill(s, r);
+      const int64_t r = row_first + s * row_step;
+      if (r < row_end) fill(s, r);
     }
   }
   int s = 0;
   uint32_t phase = 0;
-  for (int64_t row = blockIdx.x; row < rows; row += row_step) {
+  for (int64_t row = row_first; row < row_end; row += row_step) {
     const int valid = TRI ? (int)(row % sq) + 1 : dim;  // elements of this row that take part
     mbar_wait(&full[s], phase);
     const T* sx = reinterpret_cast<const T*>(ring_raw + (size_t)s * stage_bytes);
@@ -102,7 +113,7 @@ __global__ void __launch_bounds__(512) softmax_mask_pipe_kernel(const T* __restr
           for (int j = 0; j < V / MV; ++j) unpack_to_float<MT>(lds_vec(sm + off + j * MV), &mk[j * MV]);
 #pragma unroll
           for (int k = 0; k < V; ++k) e[c * V + k] += mk[k];
-        } else {
+        } else if (off + V > valid) {  // only the vector the diagonal cuts pays for per-element selects
 #pragma unroll
           for (int k = 0; k < V; ++k)
             if (off + k >= valid) e[c * V + k] = -INFINITY;  // the tail of the diagonal's vector (stale bytes of the stage)
@@ -118,7 +129,7 @@ __global__ void __launch_bounds__(512) softmax_mask_pipe_kernel(const T* __restr
     m = block_reduce_1sync(m, MaxSm(), red[0]);  // its barrier also means: stage s fully read
     if (tid == 0) {
       const int64_t nrow = row + (int64_t)stages * row_step;
-      if (nrow < rows) {
+      if (nrow < row_end) {
         fence_proxy_async_smem();
         fill(s, nrow);
       }
@@ -151,9 +162,11 @@ __global__ void __launch_bounds__(512) softmax_mask_pipe_kernel(const T* __restr
 #pragma unroll
         for (int k = 0; k < V; ++k) r[k] = e[c * V + k] * inv;
         if constexpr (TRI) {
+          if (off + V > valid) {  // the diagonal's vector and everything after it
 #pragma unroll
-          for (int k = 0; k < V; ++k)
-            if (off + k >= valid) r[k] = 0.f;  // exact zeros above the diagonal (0 * (1/sum) is NaN for a NaN / inf sum)
+            for (int k = 0; k < V; ++k)
+              if (off + k >= valid) r[k] = 0.f;  // exact zeros above the diagonal (0 * (1/sum) is NaN for a NaN / inf sum)
+          }
         }
         Vec<T> o;
         pack_from_float<T>(r, o);
@@ -203,6 +216,10 @@ int softmax_mask_typed(const T* x, const MT* mask, T* y, int64_t batch, int64_t 
       heads < (int64_t(1) << 31)) {
     // chunks per thread as in softmax.cu: 16-bit rows 4 (32 values a thread), fp32 rows 2
     int C = sizeof(T) == 2 ? (nchunk >= 256 ? 4 : (nchunk >= 128 ? 2 : 1)) : (nchunk >= 256 ? 2 : 1);
+    // The additive-mask form unpacks two operands per value: with 64-thread CTAs (2 warps) and the 4 CTAs per SM that
+    // 16 KB stages allow, 8 warps per SM cannot cover their own dependent chains (warps active 15 %, issue 43 %,
+    // DRAM 40 %: profiles/r2c_softmax_mask_bf16.txt).  Half the values per thread = twice the warps for the same rows.
+    if (!TRI && C > 1) C >>= 1;
     while (C < 8 && (nchunk + C - 1) / C > 512) C <<= 1;
     int threads = (int)((nchunk + C - 1) / C);
     threads = (threads + 31) / 32 * 32;
@@ -213,15 +230,20 @@ int softmax_mask_typed(const T* x, const MT* mask, T* y, int64_t batch, int64_t 
       size_t smem = 0;
       int want = 768 / threads;
       want = want < 2 ? 2 : (want > 6 ? 6 : want);
-      const int by_bytes = (int)((64 * 1024) / (2 * stage_bytes));  // ~64 KB of rows in flight per SM at two stages
+      const int by_bytes = (int)(((TRI ? 64 : 96) * 1024) / (2 * stage_bytes));  // ~64 KB (x only) / ~96 KB (x + mask) in flight per SM
       if (want > by_bytes) want = by_bytes < 1 ? 1 : by_bytes;
       FuncAttrHold hold;  // released when this lambda returns, i.e. after the launch
       if (!pipe_geometry(kern, threads, stage_bytes, want, 3, &per_sm, &stages, &smem, &hold)) return -1;
       int64_t grid = (int64_t)per_sm * sm_count();
-      if (threads <= 64) grid = std::max<int64_t>(grid, rows / 4);  // short-lived CTAs for narrow rows (softmax.cu)
+      int contiguous = 0;
+      int rows_each = knobs().pipe_rows_per_cta >= 1 ? knobs().pipe_rows_per_cta : 4;
+      if (threads <= 64 || knobs().pipe_rows_per_cta >= 1) {  // short-lived CTAs for narrow rows (softmax.cu), each a contiguous slab
+        grid = std::max<int64_t>(grid, rows / rows_each);
+        contiguous = 1;
+      }
       if (grid > rows) grid = rows;
       if (grid > 0x7fffffffLL) grid = 0x7fffffffLL;
-      kern<<<(unsigned)grid, threads, smem, st>>>(x, mask, y, rows, (int)sk, (int)sq, (int)heads, stages);
+      kern<<<(unsigned)grid, threads, smem, st>>>(x, mask, y, rows, (int)sk, (int)sq, (int)heads, stages, contiguous);
       return after_launch("softmax_mask_pipe");
     };
     int rc = -1;

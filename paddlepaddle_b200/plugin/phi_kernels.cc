@@ -21,12 +21,14 @@
 // reference headers (see __graft_entry__.build) and exercised for real once a wheel is present
 // (INTEGRATION.md).
 #include <cstdint>
+#include <string>
 #include <vector>
 
 #include "paddle/phi/backends/gpu/gpu_context.h"
 #include "paddle/phi/common/int_array.h"
 #include "paddle/phi/common/scalar.h"
 #include "paddle/phi/core/dense_tensor.h"
+#include "paddle/phi/core/kernel_factory.h"
 #include "paddle/phi/core/kernel_registry.h"
 #include "paddle/utils/optional.h"
 
@@ -61,6 +63,39 @@ inline void Check(int rc) {
 }
 
 inline std::vector<int64_t> Dims(const DenseTensor& t) { return common::vectorize<int64_t>(t.dims()); }
+
+// ---- what was registered BEFORE this library replaced it ---------------------------------------------------------
+// PD_REGISTER_KERNEL overwrites the whole (name, backend, layout, dtype) key.  A few attribute / dtype combinations of
+// those keys are not on the B200 path (quantised rms_norm outputs, the legacy `axis` form of the elementwise grads,
+// sum with an out_dtype pair outside the built set, random dropout masks).  Loading this library must not take them
+// away from user code that worked: the object below is defined before every registrar of this translation unit, so
+// its constructor runs first (static initialisation order inside one TU is definition order) and copies the kernels
+// that are in the factory at that moment.  A body that meets such a case calls the saved kernel's variadic function
+// with its own arguments; only when nothing was registered before does it raise Unimplemented.
+struct InTreeKernels {
+  phi::KernelNameMap saved;
+  InTreeKernels() { saved = phi::KernelFactory::Instance().kernels(); }
+  template <typename Fn>
+  Fn Find(const char* name, phi::Backend backend, DataType dtype) const {
+    auto it = saved.find(name);
+    if (it == saved.end()) return nullptr;
+    auto kt = it->second.find(phi::KernelKey(backend, phi::DataLayout::ALL_LAYOUT, dtype));
+    if (kt == it->second.end()) return nullptr;
+    return kt->second.template GetVariadicKernelFn<Fn>();
+  }
+};
+static const InTreeKernels g_in_tree;
+
+// Forward a call to the kernel this library replaced; false when there was none (or it has no variadic entry).
+// Fn is the in-tree variadic signature, spelled out by the caller (attribute types are passed by value: deducing
+// them from the arguments would turn an `int` into an `int&` and break the call).
+template <typename Fn, typename... Args>
+bool ForwardInTree(const char* name, phi::Backend backend, DataType dtype, Args&&... args) {
+  Fn fn = g_in_tree.Find<Fn>(name, backend, dtype);
+  if (fn == nullptr) return false;
+  (*fn)(std::forward<Args>(args)...);
+  return true;
+}
 
 // Scratch from Paddle's stream-safe allocator, as reduce_function.h:287-295 does with phi::Empty.
 template <typename Context>
@@ -181,8 +216,15 @@ void WhereKernel(const Context& ctx, const DenseTensor& condition, const DenseTe
 template <typename T, typename Context>
 void BinaryGrad(const Context& ctx, int op, const DenseTensor& x, const DenseTensor& y, const DenseTensor& dout, int axis,
                 DenseTensor* dx, DenseTensor* dy) {
-  if (axis != -1 && axis != std::abs(x.dims().size() - y.dims().size()))
-    PADDLE_THROW(common::errors::Unimplemented("pdb200: elementwise grad supports axis = -1 only"));
+  if (axis != -1 && axis != std::abs(x.dims().size() - y.dims().size())) {
+    // the legacy mid-axis alignment of static programs: not on this path — hand the call to the kernel we replaced
+    using Fn = void (*)(const phi::DeviceContext&, const DenseTensor&, const DenseTensor&, const DenseTensor&, int, DenseTensor*,
+                        DenseTensor*);
+    if (ForwardInTree<Fn>(op == PDB200_GRAD_ADD ? "add_grad" : "multiply_grad", phi::Backend::GPU, x.dtype(), ctx, x, y, dout, axis,
+                          dx, dy))
+      return;
+    PADDLE_THROW(common::errors::Unimplemented("pdb200: elementwise grad supports axis = -1 only and no in-tree kernel was registered"));
+  }
   T* px = dx ? ctx.template Alloc<T>(dx) : nullptr;
   T* py = dy ? ctx.template Alloc<T>(dy) : nullptr;
   auto xd = Dims(x), yd = Dims(y);
@@ -234,18 +276,40 @@ void ReduceMeanGradKernel(const Context& ctx, const DenseTensor& x, const DenseT
 typedef int (*ReduceFn)(const void*, const int64_t*, int, const int64_t*, int, int, int, int, void*, void*,
                         size_t, void*);
 
+// (input, output) dtype pairs csrc/reduce_sum.cu builds for sum
+inline bool SumPairBuilt(int xc, int oc) {
+  if (xc == oc)
+    return xc == PDB200_FLOAT32 || xc == PDB200_FLOAT64 || xc == PDB200_BFLOAT16 || xc == PDB200_FLOAT16 || xc == PDB200_INT64 ||
+           xc == PDB200_INT32 || xc == PDB200_INT8 || xc == PDB200_UINT8 || xc == PDB200_INT16;
+  return (oc == PDB200_FLOAT32 && (xc == PDB200_BFLOAT16 || xc == PDB200_FLOAT16)) ||
+         (oc == PDB200_INT64 && (xc == PDB200_INT32 || xc == PDB200_BOOL));
+}
+
 template <typename Context>
 void RunReduce(const Context& ctx, int op, ReduceFn fn, const DenseTensor& x, const std::vector<int64_t>& axes,
                bool reduce_all, DataType out_dtype, DenseTensor* out) {
   if (out_dtype == DataType::UNDEFINED) out_dtype = out->dtype();
   void* o = ctx.Alloc(out, out_dtype);
   auto xd = Dims(x);
-  const int xc = Code(x.dtype()), oc = Code(out_dtype);
+  int xc = Code(x.dtype());
+  const int oc = Code(out_dtype);
+  const void* xp = x.data();
+  DenseTensor casted;
+  if (op == PDB200_REDUCE_SUM && xc != oc && !SumPairBuilt(xc, oc)) {
+    // phi::Reduce's rule for out_dtype != x.dtype (kernels/gpu/reduce.h:49-66): cast first, then reduce in out_dtype
+    if (oc < 0 || !SumPairBuilt(oc, oc))
+      PADDLE_THROW(common::errors::Unimplemented("pdb200: sum to this out_dtype is not built"));
+    casted.Resize(x.dims());
+    void* cp = ctx.Alloc(&casted, out_dtype);
+    Check(pdb200_cast(x.data(), x.numel(), xc, oc, cp, ctx.stream()));
+    xp = cp;
+    xc = oc;
+  }
   const size_t bytes = pdb200_reduce_workspace_bytes(op, xd.data(), static_cast<int>(xd.size()), axes.data(),
                                                      static_cast<int>(axes.size()), reduce_all, xc, oc);
   DenseTensor holder;
   void* ws = Scratch(ctx, bytes, &holder);
-  Check(fn(x.data(), xd.data(), static_cast<int>(xd.size()), axes.data(), static_cast<int>(axes.size()),
+  Check(fn(xp, xd.data(), static_cast<int>(xd.size()), axes.data(), static_cast<int>(axes.size()),
            reduce_all, xc, oc, o, ws, bytes, ctx.stream()));
 }
 
@@ -314,15 +378,23 @@ void CrossEntropyWithSoftmaxKernel(const Context& ctx, const DenseTensor& logits
                                           Code(label.dtype()), soft_label, use_softmax, ignore_index, axis,
                                           Code(logits.dtype()), sm, lo, ws, bytes, ctx.stream()));
 }
-// rms_norm without quantisation (gpu/rms_norm_kernel.cu:1080-1260); a quantised output dtype stays with the in-tree kernel
+// rms_norm without quantisation (gpu/rms_norm_kernel.cu:1080-1260); a quantised output is forwarded to the in-tree kernel
 template <typename T, typename Context>
 void RmsNormKernel(const Context& ctx, const DenseTensor& x, const paddle::optional<DenseTensor>& bias,
                    const paddle::optional<DenseTensor>& residual, const DenseTensor& norm_weight,
                    const paddle::optional<DenseTensor>& norm_bias, const float epsilon, const int begin_norm_axis,
                    const float quant_scale, const int quant_round_type, const float quant_max_bound,
                    const float quant_min_bound, DenseTensor* out, DenseTensor* residual_out, DenseTensor* inv_var) {
-  if (out->dtype() == DataType::INT8 || out->dtype() == DataType::FLOAT8_E4M3FN)
-    PADDLE_THROW(common::errors::Unimplemented("pdb200: quantised rms_norm outputs are not on this path"));
+  if (quant_scale > 0.0f || out->dtype() == DataType::INT8 || out->dtype() == DataType::FLOAT8_E4M3FN) {
+    // quantised outputs: forwarded to the kernel this library replaced
+    using Fn = void (*)(const phi::DeviceContext&, const DenseTensor&, const paddle::optional<DenseTensor>&,
+                        const paddle::optional<DenseTensor>&, const DenseTensor&, const paddle::optional<DenseTensor>&, const float,
+                        const int, const float, const int, const float, const float, DenseTensor*, DenseTensor*, DenseTensor*);
+    if (ForwardInTree<Fn>("rms_norm", phi::Backend::GPU, x.dtype(), ctx, x, bias, residual, norm_weight, norm_bias, epsilon,
+                          begin_norm_axis, quant_scale, quant_round_type, quant_max_bound, quant_min_bound, out, residual_out, inv_var))
+      return;
+    PADDLE_THROW(common::errors::Unimplemented("pdb200: quantised rms_norm outputs are not on this path and no in-tree kernel was registered"));
+  }
   T* o = ctx.template Alloc<T>(out);
   T* ro = residual ? ctx.template Alloc<T>(residual_out) : nullptr;
   float* iv = inv_var ? ctx.template Alloc<float>(inv_var) : nullptr;
@@ -351,6 +423,63 @@ void SoftmaxKernel(const Context& ctx, const DenseTensor& x, int axis, DenseTens
 template <typename T, typename Context>
 void SoftmaxGPUDNNKernel(const Context& ctx, const DenseTensor& x, int axis, DenseTensor* out) {
   SoftmaxKernel<T, Context>(ctx, x, axis, out);
+}
+
+// ---- masked softmax (fusion/gpu/fused_softmax_mask_kernel.cu:149-316, fused_softmax_mask_upper_triangle_kernel.cu:255-400)
+template <typename T, typename Context>
+void FusedSoftmaxMaskKernel(const Context& ctx, const DenseTensor& x, const DenseTensor& mask, DenseTensor* out) {
+  T* o = ctx.template Alloc<T>(out);
+  PADDLE_ENFORCE_EQ(x.dims().size(), 4, common::errors::InvalidArgument("Input x must be 4-D [batch, heads, q_len, k_len]."));
+  PADDLE_ENFORCE_EQ(mask.dims().size(), 4, common::errors::InvalidArgument("Input mask must be 4-D [batch, 1, q_len, k_len]."));
+  auto xd = Dims(x), md = Dims(mask);
+  Check(pdb200_fused_softmax_mask(x.data<T>(), xd.data(), mask.data(), md.data(), Code(x.dtype()), Code(mask.dtype()), o,
+                                  ctx.stream()));
+}
+template <typename T, typename Context>
+void FusedSoftmaxMaskFuseUpperTriangleKernel(const Context& ctx, const DenseTensor& x, DenseTensor* out) {
+  T* o = ctx.template Alloc<T>(out);
+  PADDLE_ENFORCE_EQ(x.dims().size(), 4, common::errors::InvalidArgument("Input x must be 4-D [batch, heads, seq, seq]."));
+  auto xd = Dims(x);
+  Check(pdb200_fused_softmax_mask_upper_triangle(x.data<T>(), xd.data(), Code(x.dtype()), o, ctx.stream()));
+}
+
+// ---- layer_norm(residual + dropout(x + bias)) (fusion/gpu/fused_bias_dropout_residual_layer_norm_kernel.cu:24-98) ----
+template <typename T, typename Context>
+void FusedBiasDropoutResidualLnKernel(const Context& ctx, const DenseTensor& x, const DenseTensor& residual,
+                                      const paddle::optional<DenseTensor>& bias, const paddle::optional<DenseTensor>& ln_scale,
+                                      const paddle::optional<DenseTensor>& ln_bias, const float dropout_rate, const bool is_test,
+                                      const bool dropout_fix_seed, const int dropout_seed, const std::string& dropout_implementation,
+                                      const float ln_epsilon, DenseTensor* y, DenseTensor* bias_dropout_residual_out,
+                                      DenseTensor* dropout_mask_out, DenseTensor* ln_mean, DenseTensor* ln_variance) {
+  if (!is_test && dropout_rate != 0.0f) {
+    // a random mask draws from the framework's Philox generator state: forwarded to the kernel this library replaced
+    using Fn = void (*)(const phi::DeviceContext&, const DenseTensor&, const DenseTensor&, const paddle::optional<DenseTensor>&,
+                        const paddle::optional<DenseTensor>&, const paddle::optional<DenseTensor>&, const float, const bool, const bool,
+                        const int, const std::string&, const float, DenseTensor*, DenseTensor*, DenseTensor*, DenseTensor*,
+                        DenseTensor*);
+    if (ForwardInTree<Fn>("fused_bias_dropout_residual_layer_norm", phi::Backend::GPU, x.dtype(), ctx, x, residual, bias, ln_scale,
+                          ln_bias, dropout_rate, is_test, dropout_fix_seed, dropout_seed, dropout_implementation, ln_epsilon, y,
+                          bias_dropout_residual_out, dropout_mask_out, ln_mean, ln_variance))
+      return;
+    PADDLE_THROW(common::errors::Unimplemented(
+        "pdb200: training with dropout_rate > 0 needs the framework's generator and no in-tree kernel was registered"));
+  }
+  using U = typename std::conditional<std::is_same<T, double>::value, double, float>::type;
+  T* yo = ctx.template Alloc<T>(y);
+  T* dro = ctx.template Alloc<T>(bias_dropout_residual_out);
+  U* mo = ctx.template Alloc<U>(ln_mean);
+  U* vo = ctx.template Alloc<U>(ln_variance);
+  // the mask output exists in the op's signature; the reference allocates it and, like this kernel, writes nothing into it
+  // when there is no random dropout
+  if (dropout_mask_out != nullptr) ctx.template Alloc<uint8_t>(dropout_mask_out);
+  auto* sc = ln_scale.get_ptr();
+  auto* lb = ln_bias.get_ptr();
+  DataType pdt = sc ? sc->dtype() : (lb ? lb->dtype() : x.dtype());
+  auto d = Dims(x);
+  Check(pdb200_fused_bias_dropout_residual_layer_norm(
+      x.data<T>(), residual.data<T>(), d.data(), static_cast<int>(d.size()), bias ? bias.get().data<T>() : nullptr,
+      sc ? sc->data() : nullptr, lb ? lb->data() : nullptr, Code(pdt), dropout_rate, is_test ? 1 : 0,
+      dropout_implementation == "upscale_in_train" ? 1 : 0, ln_epsilon, Code(x.dtype()), yo, dro, mo, vo, ctx.stream()));
 }
 
 // ---- layer_norm --------------------------------------------------------------------------
@@ -490,11 +619,11 @@ PD_REGISTER_KERNEL(rms_norm, GPU, ALL_LAYOUT, pdb200_phi::RmsNormKernel, float, 
 PD_REGISTER_KERNEL(log_softmax, GPU, ALL_LAYOUT, pdb200_phi::LogSoftmaxKernel, float, double, phi::dtype::float16,
                    phi::dtype::bfloat16) {}  // gpu/log_softmax_kernel.cu registration
 PD_REGISTER_KERNEL(sum_raw, GPU, ALL_LAYOUT, pdb200_phi::SumRawKernel, bool, float, double, phi::dtype::float16,
-                   phi::dtype::bfloat16, int, int64_t) {
+                   phi::dtype::bfloat16, int8_t, uint8_t, int16_t, int, int64_t) {
   kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);  // reduce_sum_kernel.cc:75-77
 }
 PD_REGISTER_KERNEL(sum, GPU, ALL_LAYOUT, pdb200_phi::SumKernel, bool, float, double, phi::dtype::float16,
-                   phi::dtype::bfloat16, int, int64_t) {
+                   phi::dtype::bfloat16, int8_t, uint8_t, int16_t, int, int64_t) {
   kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);
 }
 PD_REGISTER_KERNEL(mean_raw, GPU, ALL_LAYOUT, pdb200_phi::MeanRawKernel, float, double, phi::dtype::float16,
@@ -536,4 +665,13 @@ PD_REGISTER_KERNEL(layer_norm_grad, GPU, ALL_LAYOUT, pdb200_phi::LayerNormGradKe
     kernel->OutputAt(1).SetDataType(phi::DataType::UNDEFINED);  // follows the scale dtype (x's or float32)
     kernel->OutputAt(2).SetDataType(phi::DataType::UNDEFINED);
   }
+}
+// fused neighbours; dtype lists of the in-tree registrations plus bfloat16
+PD_REGISTER_KERNEL(fused_softmax_mask, GPU, ALL_LAYOUT, pdb200_phi::FusedSoftmaxMaskKernel, float, phi::dtype::float16,
+                   phi::dtype::bfloat16) {}
+PD_REGISTER_KERNEL(fused_softmax_mask_upper_triangle, GPU, ALL_LAYOUT, pdb200_phi::FusedSoftmaxMaskFuseUpperTriangleKernel, float,
+                   phi::dtype::float16, phi::dtype::bfloat16) {}
+PD_REGISTER_KERNEL(fused_bias_dropout_residual_layer_norm, GPU, ALL_LAYOUT, pdb200_phi::FusedBiasDropoutResidualLnKernel, float,
+                   double, phi::dtype::float16, phi::dtype::bfloat16) {
+  kernel->OutputAt(1).SetDataType(phi::DataType::UINT8);  // as written in the reference registration
 }

@@ -36,6 +36,14 @@ elif case in ("softmax_vocab_bf16", "softmax_vocab_fp32"):
     dt = torch.float32 if case.endswith("fp32") else torch.bfloat16
     x = (torch.randn((4096, 128256), device="cuda", generator=g) * 2).to(dt)  # LLM-vocabulary rows
     fn = lambda: F.softmax(x, axis=-1)
+elif case in ("softmax_mask_bf16", "softmax_tri_bf16"):
+    x = (torch.randn((4, 32, 2048, 2048), device="cuda", generator=g) * 2).to(torch.bfloat16)
+    mk = torch.randn((4, 1, 2048, 2048), device="cuda", generator=g).to(torch.bfloat16)
+    fn = (lambda: F.softmax_mask_fuse(x, mk)) if case == "softmax_mask_bf16" else (lambda: F.softmax_mask_fuse_upper_triangle(x))
+elif case == "ln_vocab_bf16":
+    x = torch.randn((4096, 128256), device="cuda", generator=g).to(torch.bfloat16)
+    w = torch.rand(128256, device="cuda", generator=g).to(torch.bfloat16)
+    fn = lambda: F.layer_norm(x, [128256], w, w)
 elif case == "ln_long_bf16":
     x = torch.randn((8192, 65536), device="cuda", generator=g).to(torch.bfloat16)
     w = torch.rand(65536, device="cuda", generator=g).to(torch.bfloat16)

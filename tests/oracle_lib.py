@@ -393,17 +393,22 @@ class Oracle:
             out[:, :, q, :q + 1] = self.softmax(np.ascontiguousarray(x[:, :, q, :q + 1]).reshape(B * H, q + 1), -1).reshape(B, H, q + 1)
         return out
 
-    def fused_bias_dropout_residual_layer_norm(self, x, residual, bias, ln_scale, ln_bias, eps=1e-5, factor=1.0, half=None):
+    def fused_bias_dropout_residual_layer_norm(self, x, residual, bias, ln_scale, ln_bias, eps=1e-5, factor=1.0, half=None,
+                                               conv=None):
         """Deterministic cases of layer_norm(residual + dropout(x + bias)) (keep = 1): d is formed here with the
         reference's T arithmetic — every step rounded to T (half = 'bf16' | 'fp16' | None for float32; x / residual /
         bias then arrive as uint16 bit patterns) — and the layer_norm is the reference CPU kernel on float(d).
+        `conv`: the Oracle whose float <-> 16-bit conversions are used (default: this one).  Pass the restatement when this
+        is the compiled reference and half == 'fp16': the reference's CPU float -> float16 TRUNCATES on builds without
+        F16C (phi/common/float16.h:121-138) while the GPU rounds to nearest even.
         -> (y float32, d as T, mean, variance)."""
+        conv = conv or self
         if half is None:
             up = lambda a: np.asarray(a, np.float32)
             rt = lambda a: a.astype(np.float32)
             down = lambda a: a
         else:
-            to_h, to_f = (self.f32_to_bf16, self.bf16_to_f32) if half == "bf16" else (self.f32_to_fp16, self.fp16_to_f32)
+            to_h, to_f = (conv.f32_to_bf16, conv.bf16_to_f32) if half == "bf16" else (conv.f32_to_fp16, conv.fp16_to_f32)
             up = to_f
             rt = lambda a: to_f(to_h(a.astype(np.float32)))
             down = lambda a: to_h(a.astype(np.float32))

@@ -114,7 +114,11 @@ def test_c3_layer_norm_bf16_every_row(cpu, port):
             # 1 bf16 ulp; atol: outputs near zero are small differences of O(1) terms (see test_gpu_parity.py::test_layer_norm_routes)
             assert_half_close(to_np(y[r0:r0 + slab]), port.f32_to_bf16(oy), 1, f"config 3 rows {r0}..", atol=2e-5)
             np.testing.assert_allclose(to_np(m[r0:r0 + slab]), om, rtol=1e-5, atol=1e-5 * float(np.abs(xs).max()))
-            np.testing.assert_allclose(to_np(v[r0:r0 + slab]), ov, rtol=2e-5)
+            # variance: 1e-5 against the float64 value; the CPU kernel itself adds 8192 squares one after the other in
+            # float32 (RowwiseMean2D, funcs/math_function_impl.h:158-191) and sits up to ~4e-5 from it on some rows
+            v64 = x[r0:r0 + slab].double().var(dim=1, unbiased=False).cpu().numpy()
+            np.testing.assert_allclose(to_np(v[r0:r0 + slab]), v64, rtol=1e-5)
+            np.testing.assert_allclose(to_np(v[r0:r0 + slab]), ov, rtol=1e-4)
             return slab
 
         assert sum(_pmap(check, range(0, rows, slab))) == rows

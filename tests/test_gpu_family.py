@@ -264,3 +264,35 @@ def test_bf16_divide_is_exact_for_every_pair_of_operands():
         bad += int(paddle.sum(paddle.not_equal(fast.view(torch.int16), exact.view(torch.int16))).item())
         del fast, exact
     assert bad == 0, f"{bad} of 2^32 bf16 quotients differ from the correctly rounded result"
+
+
+@pytest.mark.parametrize("half,code", [("bf16", O.BFLOAT16), ("fp16", O.FLOAT16)])
+def test_half_equal_not_equal_every_value_against_special_operands(port, half, code):
+    """The packed 16-bit equal / not_equal (csrc/elementwise_pred.cu: eq8_packed) against the scalar rule of the CPU functor
+    (|round16(a - b)| < 1e-8, infinities exact, NaN equals nothing): EVERY 16-bit pattern as `a`, against operands chosen
+    where the rule has corners — zeros of both signs, infinities, NaNs, subnormals, values around the 1e-8 tolerance,
+    neighbours of `a` itself — on the same-shape (vector) route and, for one operand, the row-broadcast route."""
+    a = np.arange(65536, dtype=np.uint16)
+    conv = port.f32_to_bf16 if half == "bf16" else port.f32_to_fp16
+    special = np.array([0x0000, 0x8000, 0x7C00, 0xFC00, 0x7F80, 0xFF80, 0x7FC0, 0xFFC0, 0x7E00, 0x0001, 0x8001, 0x0002, 0x007F, 0x0080,
+                        0x03FF, 0x0400, 0x3C00, 0x3F80, 0xBF80, 0x7BFF, 0x7F7F], dtype=np.uint16)
+    tiny = conv(np.array([1e-8, 9.9e-9, 1.01e-8, 5e-9, 2e-9, 1e-9, -1e-9, -5e-9, 1.5e-8, 2e-8, 6e-8, 1e-7, 1e-10, 3e-39],
+                         dtype=np.float32))
+    bs = np.concatenate([special, tiny])
+    A = np.tile(a, (len(bs) + 3, 1))
+    B = np.empty_like(A)
+    for i, b in enumerate(bs):
+        B[i] = b
+    B[len(bs)] = a                      # a == a (NaN patterns must still be unequal)
+    B[len(bs) + 1] = np.roll(a, 1)      # the neighbouring bit pattern
+    B[len(bs) + 2] = a ^ np.uint16(0x8000)  # the same magnitude, other sign
+    ta, tb = to_dev(A, half), to_dev(B, half)
+    for op, fn in (("equal", paddle.equal), ("not_equal", paddle.not_equal)):
+        want = port.compare(op, A, B, code=code)
+        got = to_np(fn(ta, tb))
+        bad = np.argwhere(got != want)
+        assert bad.size == 0, (op, half, [(hex(A[i, j]), hex(B[i, j]), bool(got[i, j])) for i, j in bad[:5]])
+    # row-broadcast route: every `a` row against one row of operands
+    row = np.resize(bs, 65536).astype(np.uint16)
+    want = port.compare("equal", A[:4], row, code=code)
+    assert np.array_equal(to_np(paddle.equal(to_dev(A[:4], half), to_dev(row, half))), want)

@@ -198,3 +198,35 @@ def test_ref_family(ref):
     gl, gs = F.softmax_with_cross_entropy(to_dev(logits), to_dev(lbl), return_softmax=True)
     np.testing.assert_allclose(to_np(gs), sm, rtol=1e-5, atol=1e-30)
     np.testing.assert_allclose(to_np(gl), loss, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("shape", [(4, 300, 64), (2, 2051, 128), (3, 7, 24), (2, 48, 33)])
+@pytest.mark.parametrize("dt", ["float32", "bfloat16"])
+def test_softmax_strided_axis_special_values(port, shape, dt):
+    """softmax along a middle axis (the vectorised column kernel and, for inner % V != 0, the scalar one): columns holding
+    NaN, +inf, only -inf, a -1e4 outlier, or -inf in the rows visited first must follow the scalar rule of the CPU kernel."""
+    r = _rng(12)
+    x = (r.standard_normal(shape) * 2).astype(np.float32)
+    x[0, 3, 1] = np.nan
+    x[0, 5, 2] = np.inf
+    x[0, :, 3] = -np.inf
+    x[0, 2, 4] = -1e4
+    x[0, : shape[1] // 2, 5] = -np.inf   # the running max stays -inf for the first half of the column
+    x[1, 0, 6] = -np.inf
+    if dt == "bfloat16":
+        xb = port.f32_to_bf16(x)
+        want = port.softmax(port.bf16_to_f32(xb), 1)
+        got = port.bf16_to_f32(to_np(F.softmax(to_dev(xb, "bf16"), axis=1)))
+        tol = dict(rtol=2 ** -7, atol=2e-28)
+    else:
+        want = port.softmax(x, 1)
+        got = to_np(F.softmax(to_dev(x), axis=1))
+        tol = dict(rtol=1e-5, atol=2e-28)
+    for c in (1, 2, 3):
+        assert np.isnan(want[0, :, c]).all() and np.isnan(got[0, :, c]).all(), f"column {c} must be NaN"
+    mask = np.ones(shape, bool)
+    mask[0, :, 1:4] = False
+    np.testing.assert_allclose(got[mask], want[mask], **tol)
+    if dt == "float32":
+        lg = to_np(F.log_softmax(to_dev(x), axis=1))
+        np.testing.assert_allclose(lg[mask], port.log_softmax(x, 1)[mask], rtol=1e-5, atol=1e-5)

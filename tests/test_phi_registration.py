@@ -53,7 +53,10 @@ EXPECT = {  # the registrations of plugin/phi_kernels.cc
     "subtract": "float32 float64 int16 int32 int64 float16 bfloat16",
     "divide": "float32 float64 int8 uint8 int16 int32 int64 float16 bfloat16",
     "maximum": "float32 float64 int32 int64 float16 bfloat16", "minimum": "float32 float64 int32 int64 float16 bfloat16",
-    "sum": "bool float32 float64 float16 bfloat16 int32 int64", "sum_raw": "bool float32 float64 float16 bfloat16 int32 int64",
+    "sum": "bool float32 float64 float16 bfloat16 int8 uint8 int16 int32 int64",
+    "sum_raw": "bool float32 float64 float16 bfloat16 int8 uint8 int16 int32 int64",
+    "fused_softmax_mask": "float32 float16 bfloat16", "fused_softmax_mask_upper_triangle": "float32 float16 bfloat16",
+    "fused_bias_dropout_residual_layer_norm": "float32 float64 float16 bfloat16",
     "mean": "float32 float64 float16 bfloat16 int32 int64", "mean_raw": "float32 float64 float16 bfloat16 int32 int64",
     "max": "float32 float64 int32 int64 float16 bfloat16", "max_raw": "float32 float64 int32 int64 float16 bfloat16",
     "min": "float32 float64 int32 int64 float16 bfloat16", "min_raw": "float32 float64 int32 int64 float16 bfloat16",
