@@ -422,6 +422,10 @@ __global__ void __launch_bounds__(1024) ln_rows_cluster_kernel(const T* __restri
     }
     mbar_wait(&bar, 0);
   }
+  // Mean and sum of squared deviations OF THIS SLICE (two sweeps over shared memory, CTA reductions only), published as
+  // a pair; after ONE cluster barrier every CTA folds the cs pairs with the pairwise-variance rule
+  //     mean = sum_r n_r mean_r / D,     M2 = sum_r (M2_r + n_r (mean_r - mean)^2),     var = M2 / D
+  // (as accurate as two passes over the whole row; the first version needed two cluster barriers).
   U sum = U(0);
   for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
     const Vec<T> v = lds_vec(srow + i);
@@ -429,31 +433,45 @@ __global__ void __launch_bounds__(1024) ln_rows_cluster_kernel(const T* __restri
     for (int k = 0; k < V; ++k) sum += cvt<U>(v.v[k]);
   }
   sum = block_reduce(sum, AddU<U>(), U(0), red);
-  if (threadIdx.x == 0) xchg[0] = sum;
-  cluster.sync();
-  U total = U(0);
-  for (unsigned r = 0; r < cs; ++r) total += *cluster.map_shared_rank(&xchg[0], r);
-  const U mean = mean_of<U>(total, inv_d);
+  const U mean_loc = n > 0 ? sum / (U)n : U(0);
   U sq = U(0);
   for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
     const Vec<T> v = lds_vec(srow + i);
 #pragma unroll
     for (int k = 0; k < V; ++k) {
-      const U d = cvt<U>(v.v[k]) - mean;
+      const U d = cvt<U>(v.v[k]) - mean_loc;
       sq += d * d;
     }
   }
   sq = block_reduce(sq, AddU<U>(), U(0), red);
-  if (threadIdx.x == 0) xchg[1] = sq;
+  if (threadIdx.x == 0) {
+    xchg[0] = mean_loc;
+    xchg[1] = sq;
+  }
   cluster.sync();
+  U total = U(0);
+  for (unsigned r = 0; r < cs; ++r) {
+    int64_t nr = D - (int64_t)r * slice;
+    nr = nr < 0 ? 0 : (nr > slice ? slice : nr);
+    total += (U)nr * *cluster.map_shared_rank(&xchg[0], r);
+  }
+  const U mean = mean_of<U>(total, inv_d);
   U total_sq = U(0);
-  for (unsigned r = 0; r < cs; ++r) total_sq += *cluster.map_shared_rank(&xchg[1], r);
+  for (unsigned r = 0; r < cs; ++r) {
+    int64_t nr = D - (int64_t)r * slice;
+    nr = nr < 0 ? 0 : (nr > slice ? slice : nr);
+    const U dm = *cluster.map_shared_rank(&xchg[0], r) - mean;
+    total_sq += *cluster.map_shared_rank(&xchg[1], r) + (U)nr * dm * dm;
+  }
   const U var = mean_of<U>(total_sq, inv_d);
   const U rstd = rsqrt_exact<U>(var + eps);
   if (rank == 0 && threadIdx.x == 0) {
     if (mean_out) mean_out[row] = mean;
     if (var_out) var_out[row] = var;
   }
+  // every peer's pair has been read: arrive for the exit barrier now (relaxed — a release arrive after the stores would
+  // make every thread wait for its stores to drain), wait for it at the very end
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
   const P* sc = scale ? scale + begin : nullptr;
   const P* bi = bias ? bias + begin : nullptr;
   for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
@@ -463,178 +481,7 @@ __global__ void __launch_bounds__(1024) ln_rows_cluster_kernel(const T* __restri
     for (int k = 0; k < V; ++k) e[k] = cvt<U>(v.v[k]);
     ln_store_chunk<T, P, U, V, true>(e, mean, rstd, sc, bi, dst, i);
   }
-  cluster.sync();  // nobody leaves while a peer may still be reading its xchg[]
-}
-
-// ---- cluster_pipe: persistent clusters, the row in registers across the cluster, one DSMEM exchange per row -------
-// Same structure as softmax_cluster_pipe_kernel (softmax.cu): a cluster of `cs` CTAs is persistent over rows, CTA `rank`
-// receives its slice of every row through a 2-stage cp.async.bulk ring and keeps it in registers.  Each CTA forms the
-// mean and the sum of squared deviations OF ITS SLICE (two passes over registers, two CTA barriers), publishes the pair,
-// and after ONE cluster barrier every warp folds the cs pairs with the pairwise-variance rule
-//     mean = sum_r n_r mean_r / D,     M2 = sum_r (M2_r + n_r (mean_r - mean)^2),     var = M2 / D
-// (as accurate as two passes over the whole row: nothing is ever a difference of large sums).
-__device__ __forceinline__ unsigned ln_cluster_ctarank() {
-  unsigned r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ unsigned ln_cluster_nctarank() {
-  unsigned r;
-  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ void ln_cluster_barrier() {
-  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ float ln_ld_dsmem_f32(const float* local_ptr, unsigned rank) {
-  uint32_t remote;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local_ptr)), "r"(rank));
-  float v;
-  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
-  return v;
-}
-
-template <typename T, typename P, int C>
-__global__ void __launch_bounds__(512, 1) ln_cluster_pipe_kernel(const T* __restrict__ x, const P* __restrict__ scale,
-                                                                 const P* __restrict__ bias, T* __restrict__ y,
-                                                                 float* mean_out, float* var_out, int64_t rows, int64_t D,
-                                                                 int slice, int stages, float eps, float inv_d) {
-  constexpr int V = Vec<T>::N;
-  constexpr int PV = Vec<P>::N;
-  extern __shared__ __align__(128) unsigned char ring_raw[];
-  T* ring = reinterpret_cast<T*>(ring_raw);
-  __shared__ uint64_t full[4];
-  __shared__ float red[2][32];
-  __shared__ float xchg[2][2];  // [row parity][0] mean of this slice, [1] its sum of squared deviations
-  const unsigned rank = ln_cluster_ctarank(), cs = ln_cluster_nctarank();
-  const int64_t cluster_id = blockIdx.x / cs, n_clusters = gridDim.x / cs;
-  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31;
-  const int64_t begin = (int64_t)rank * slice;
-  const int n = (int)(D - begin < 0 ? 0 : (D - begin > slice ? slice : D - begin));
-  const uint32_t bytes = (uint32_t)n * sizeof(T);
-  // element count of lane r's CTA (lanes >= cs: 0)
-  float n_peer = 0.f;
-  if (lane < (int)cs) {
-    const int64_t b = (int64_t)lane * slice;
-    n_peer = (float)(D - b < 0 ? 0 : (D - b > slice ? slice : D - b));
-  }
-  const float inv_n = n > 0 ? 1.0f / (float)n : 0.f;
-  if (tid == 0) {
-    for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
-    mbar_fence_init();
-  }
-  block_reduce_1sync_init(red[0], 0.f);
-  block_reduce_1sync_init(red[1], 0.f);
-  __syncthreads();
-  ln_cluster_barrier();  // every CTA of the cluster is running before anyone touches a peer's shared memory
-  if (tid == 0 && n > 0) {
-    for (int s = 0; s < stages; ++s) {
-      const int64_t r = cluster_id + s * n_clusters;
-      if (r < rows) {
-        mbar_expect_tx(&full[s], bytes);
-        bulk_load_row(ring + (size_t)s * slice, x + r * D + begin, bytes, &full[s]);
-      }
-    }
-  }
-  int s = 0, par = 0;
-  uint32_t phase = 0;
-  for (int64_t row = cluster_id; row < rows; row += n_clusters) {
-    if (n > 0) mbar_wait(&full[s], phase);
-    const T* st = ring + (size_t)s * slice;
-    float e[C * V];
-    float acc[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-    for (int c = 0; c < C; ++c) {
-      const int off = (c * nt + tid) * V;
-      if (off < n) {
-        unpack_to_float<T>(lds_vec(st + off), &e[c * V]);
-      } else {
-#pragma unroll
-        for (int k = 0; k < V; ++k) e[c * V + k] = 0.f;
-      }
-#pragma unroll
-      for (int k = 0; k < V; ++k) acc[k & 3] += e[c * V + k];
-    }
-    float sum = (acc[0] + acc[1]) + (acc[2] + acc[3]);
-    sum = block_reduce_1sync(sum, AddU<float>(), red[0]);  // its barrier also means: stage s fully read
-    if (tid == 0 && n > 0) {
-      const int64_t nrow = row + (int64_t)stages * n_clusters;
-      if (nrow < rows) {
-        fence_proxy_async_smem();
-        mbar_expect_tx(&full[s], bytes);
-        bulk_load_row(ring + (size_t)s * slice, x + nrow * D + begin, bytes, &full[s]);
-      }
-    }
-    const float mean_loc = sum * inv_n;
-    acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
-#pragma unroll
-    for (int c = 0; c < C; ++c) {
-      const int off = (c * nt + tid) * V;
-      if (off < n) {
-#pragma unroll
-        for (int k = 0; k < V; ++k) {
-          const float d = e[c * V + k] - mean_loc;
-          acc[k & 3] = fmaf(d, d, acc[k & 3]);
-        }
-      }
-    }
-    float m2 = (acc[0] + acc[1]) + (acc[2] + acc[3]);
-    m2 = block_reduce_1sync(m2, AddU<float>(), red[1]);
-    // only the publishing thread arrives with release semantics (see softmax_cluster_pipe_kernel)
-    if (tid == 0) {
-      xchg[par][0] = mean_loc;
-      xchg[par][1] = m2;
-      asm volatile("barrier.cluster.arrive.release;" ::: "memory");
-    } else {
-      asm volatile("barrier.cluster.arrive.relaxed;" ::: "memory");
-    }
-    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-    float pm = 0.f, p2 = 0.f;
-    if (lane < (int)cs) {
-      pm = ln_ld_dsmem_f32(&xchg[par][0], lane);
-      p2 = ln_ld_dsmem_f32(&xchg[par][1], lane);
-    }
-    const float mean = group_reduce<32>(n_peer * pm, AddU<float>()) * inv_d;
-    const float dm = pm - mean;
-    const float var = group_reduce<32>(fmaf(n_peer * dm, dm, p2), AddU<float>()) * inv_d;
-    const float rstd = rsqrt_exact<float>(var + eps);
-    if (rank == 0 && tid == 0) {
-      if (mean_out) mean_out[row] = mean;
-      if (var_out) var_out[row] = var;
-    }
-    T* dst = y + row * D + begin;
-    const P* sc = scale ? scale + begin : nullptr;
-    const P* bi = bias ? bias + begin : nullptr;
-#pragma unroll
-    for (int c = 0; c < C; ++c) {
-      const int off = (c * nt + tid) * V;
-      if (off < n) {
-        float w[V], b[V], o[V];
-#pragma unroll
-        for (int k = 0; k < V; ++k) { w[k] = 1.f; b[k] = 0.f; }
-        if (sc != nullptr) {
-#pragma unroll
-          for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(sc + off + j * PV), &w[j * PV]);
-        }
-        if (bi != nullptr) {
-#pragma unroll
-          for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(bi + off + j * PV), &b[j * PV]);
-        }
-#pragma unroll
-        for (int k = 0; k < V; ++k) o[k] = fmaf(__fmul_rn(e[c * V + k] - mean, rstd), w[k], b[k]);
-        Vec<T> ov;
-        pack_from_float<T>(o, ov);
-        st_stream(dst + off, ov);
-      }
-    }
-    par ^= 1;
-    if (++s == stages) {
-      s = 0;
-      phase ^= 1;
-    }
-  }
-  ln_cluster_barrier();  // nobody leaves while a peer may still be reading its xchg[]
+  asm volatile("barrier.cluster.wait.aligned;" ::: "memory");  // nobody leaves while a peer may still be reading its xchg[]
 }
 
 // ---- block_strm: rows too long for registers ------------------------------------------------
@@ -759,73 +606,6 @@ int layer_norm_typed(const T* x, const P* scale, const P* bias, T* y, void* mean
     return after_launch("ln_block_reg");
   }
 #undef PDB_LN_C
-  // Long rows, first choice: persistent clusters with the row in registers across the cluster (ln_cluster_pipe_kernel).
-  if constexpr (!std::is_same<T, double>::value) {
-    constexpr int kThreads = 512, kMaxVals = 32;
-    const int64_t cap = (int64_t)kThreads * kMaxVals;
-    if (vec && nchunk > 512 * 4 && D <= 8 * cap && !knobs().no_cluster_pipe && (!scale || is_aligned16(scale)) &&
-        (!bias || is_aligned16(bias))) {
-      int cs = 2;
-      while (cs < 8 && (D + cs - 1) / cs > cap) cs <<= 1;
-      while (cs < 8 && rows * cs < (int64_t)sm_count()) cs <<= 1;
-      int64_t slice = (D + cs - 1) / cs;
-      slice = (slice + VN - 1) / VN * VN;
-      const int64_t sl_chunks = slice / VN;
-      int C = 1;
-      while (C < kMaxVals / VN && (sl_chunks + C - 1) / C > kThreads) C <<= 1;
-      int threads = (int)((sl_chunks + C - 1) / C);
-      threads = (threads + 31) / 32 * 32;
-      const int stages = 2;
-      const size_t smem = (size_t)stages * slice * sizeof(T);
-      auto launch = [&](auto kern) -> int {
-        FuncAttrHold hold;  // the dynamic shared-memory size follows the slice: held until the launch call has returned
-        if (!func_attr_apply(reinterpret_cast<const void*>(kern), (int)smem, -1, &hold)) return -1;
-        cudaLaunchConfig_t cfg{};
-        cfg.blockDim = dim3(threads);
-        cfg.dynamicSmemBytes = smem;
-        cfg.stream = st;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = cs;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        static std::map<std::tuple<const void*, int, int, size_t, int>, int> resident;  // guarded by the attribute lock
-        int dev = 0;
-        cudaGetDevice(&dev);
-        const auto key = std::make_tuple(reinterpret_cast<const void*>(kern), dev, threads, smem, cs);
-        auto it = resident.find(key);
-        if (it == resident.end()) {
-          int ncl = 0;
-          cfg.gridDim = dim3((unsigned)(cs * sm_count()));
-          if (cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg) != cudaSuccess) {
-            cudaGetLastError();
-            ncl = 0;
-          }
-          it = resident.emplace(key, ncl).first;
-        }
-        int64_t ncl = it->second;
-        if (ncl < 1) return -1;
-        if (ncl > rows) ncl = rows;
-        cfg.gridDim = dim3((unsigned)(ncl * cs));
-        if (cudaLaunchKernelEx(&cfg, kern, x, scale, bias, y, reinterpret_cast<float*>(m), reinterpret_cast<float*>(v), rows, D,
-                               (int)slice, stages, (float)eps, (float)inv_d) != cudaSuccess) {
-          cudaGetLastError();
-          return -1;
-        }
-        return after_launch("ln_cluster_pipe");
-      };
-      int rc = -1;
-      if (slice <= cap && threads <= kThreads && (int64_t)threads * C >= sl_chunks) {
-        if (C == 1) rc = launch(ln_cluster_pipe_kernel<T, P, 1>);
-        else if (C == 2) rc = launch(ln_cluster_pipe_kernel<T, P, 2>);
-        else if (C == 4) rc = launch(ln_cluster_pipe_kernel<T, P, 4>);
-        else if constexpr (kMaxVals / VN >= 8) { if (C == 8) rc = launch(ln_cluster_pipe_kernel<T, P, 8>); }
-      }
-      if (rc >= 0) return rc;
-    }
-  }
   // Long rows (beyond the register routes): thread-block cluster per row, slices in shared memory.
   if (vec && nchunk > 1024 * 4) {
     const size_t row_bytes = (size_t)D * sizeof(T);

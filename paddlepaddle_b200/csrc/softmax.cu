@@ -350,6 +350,47 @@ __global__ void __launch_bounds__(1024) softmax_rows_smem_kernel(const T* __rest
   }
 }
 
+// Online (max, sum) bookkeeping shared by the long-row kernels.
+struct MaxSum {
+  float m, s, a;  // running max; sum of exp relative to it; clipped exp(-64) terms seen while the max was still -inf
+};
+__device__ __forceinline__ MaxSum ms_combine(MaxSum x, MaxSum y) {
+  constexpr float kLog2e = 1.4426950408889634f;
+  const float M = fmaxf(x.m, y.m);
+  float fx = 0.f, fy = 0.f;  // a side whose max is -inf has s == 0: factor 0 avoids inf - inf
+  if (x.m != -INFINITY) asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(fx) : "f"((x.m - M) * kLog2e));
+  if (y.m != -INFINITY) asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(fy) : "f"((y.m - M) * kLog2e));
+  return MaxSum{M, fmaf(x.s, fx, y.s * fy), x.a + y.a};
+}
+__device__ __forceinline__ MaxSum ms_warp_reduce(MaxSum v) {
+#pragma unroll
+  for (int k = 16; k >= 1; k >>= 1)
+    v = ms_combine(v, MaxSum{__shfl_xor_sync(0xffffffffu, v.m, k), __shfl_xor_sync(0xffffffffu, v.s, k),
+                             __shfl_xor_sync(0xffffffffu, v.a, k)});
+  return v;
+}
+// fold V new values into a running (max, sum)
+template <int N>
+__device__ __forceinline__ void ms_accumulate(MaxSum& t, const float* v) {
+  constexpr float kLog2e = 1.4426950408889634f;
+  constexpr float kClip = 1.603810890548638e-28f;  // exp(-64)
+  float nm = t.m;
+#pragma unroll
+  for (int i = 0; i < N; ++i) nm = fmaxf(nm, v[i]);
+  if (nm == -INFINITY) {  // nothing finite yet: -inf clips to exp(-64) whatever the max turns out to be; NaN propagates
+#pragma unroll
+    for (int i = 0; i < N; ++i) t.a += (v[i] != v[i]) ? v[i] : kClip;
+  } else {
+    float resc;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(resc) : "f"((t.m - nm) * kLog2e));  // 0 when the old max was -inf (t.s is 0 then)
+    float add[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int i = 0; i < N; ++i) add[i & 3] += fast_clipped_exp(v[i], -nm * kLog2e);
+    t.s = fmaf(t.s, resc, (add[0] + add[1]) + (add[2] + add[3]));
+    t.m = nm;
+  }
+}
+
 // ---- rows_cluster: one thread-block cluster per row, DSMEM combine ------------------------------
 // CTA `rank` of the cluster owns elements [rank*slice, rank*slice + slice) of the row and keeps them in
 // shared memory in their storage type.  The two row-wide quantities (max, sum of exp) are produced
@@ -391,234 +432,188 @@ __global__ void __launch_bounds__(1024) softmax_rows_cluster_kernel(const T* __r
     }
     mbar_wait(&bar, 0);
   }
-  A m = neg_inf<A>();
-  for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
-    const Vec<T> v = lds_vec(srow + i);
-#pragma unroll
-    for (int k = 0; k < V; ++k) {
-      const A a = cvt<A>(v.v[k]);
-      m = a > m ? a : m;
+  // sweep 1 (shared memory): running (max, sum of exp) per thread — one pass, one rescale per vector — folded over the
+  // CTA and, after ONE cluster barrier, over the cluster through DSMEM.  (The first version made a max sweep, a cluster
+  // barrier, a sum sweep and a second cluster barrier.)
+  A gm, gs;
+  if constexpr (std::is_same<A, float>::value) {
+    MaxSum t{-INFINITY, 0.f, 0.f};
+    for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
+      float v[V];
+      unpack_to_float<T>(lds_vec(srow + i), v);
+      ms_accumulate<V>(t, v);
     }
-  }
-  m = block_reduce(m, MaxF<A>(), neg_inf<A>(), red);
-  if (threadIdx.x == 0) xchg[0] = m;
-  cluster.sync();
-  A gm = neg_inf<A>();
-  for (unsigned r = 0; r < cs; ++r) {
-    const A o = *cluster.map_shared_rank(&xchg[0], r);
-    gm = o > gm ? o : gm;
-  }
-  // sweep 2 (shared memory): local sum of exp
-  const A nml = -gm * A(1.4426950408889634);
-  A sum = A(0);
-  for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
-    const Vec<T> v = lds_vec(srow + i);
-#pragma unroll
-    for (int k = 0; k < V; ++k) sum += row_exp<A>(cvt<A>(v.v[k]), gm, nml);
-  }
-  sum = block_reduce(sum, AddF<A>(), A(0), red);
-  if (threadIdx.x == 0) xchg[1] = sum;
-  cluster.sync();
-  A gs = A(0);
-  for (unsigned r = 0; r < cs; ++r) gs += *cluster.map_shared_rank(&xchg[1], r);
-  const A inv = row_constant<LOG, A>(gs);
-  if (stats != nullptr && rank == 0 && threadIdx.x == 0) { stats[2 * row] = gm; stats[2 * row + 1] = log_acc<A>(gs); }
-  // sweep 3: normalise and store
-  for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
-    const Vec<T> v = lds_vec(srow + i);
-    Vec<T> o;
-#pragma unroll
-    for (int k = 0; k < V; ++k)
-      o.v[k] = cvt<T>(LOG ? clipped_diff<A>(cvt<A>(v.v[k]), gm) - inv : row_exp<A>(cvt<A>(v.v[k]), gm, nml) * inv);
-    st_stream(dst + i, o);
-  }
-  cluster.sync();  // nobody leaves while a peer may still be reading its xchg[]
-}
-
-// ---- cluster_pipe: persistent clusters, the row in registers ACROSS the cluster, one DSMEM exchange per row ---------
-// The single-shot kernel above exposes everything: one bulk copy, then waiting; three sweeps over shared memory; three
-// cluster barriers; one row per cluster, then exit (3.8-4.3 TB/s on vocabulary-sized rows).  Here a cluster of `cs`
-// CTAs is PERSISTENT over rows r = cluster, cluster + n_clusters, ...; CTA `rank` owns elements [rank*slice, +slice)
-// of every row and receives them through a 2-stage ring (cp.async.bulk of this CTA's slice of row k+1 is issued as soon
-// as row k's slice has been read into registers, i.e. it overlaps everything below).  Per row and CTA:
-//   registers <- slice; local max (one CTA barrier); e = exp(x - local max) kept in registers, local sum (one CTA
-//   barrier); (local max, local sum) published in shared memory; ONE cluster barrier (arrive.release / wait.acquire);
-//   lane r of every warp reads CTA r's pair through DSMEM, a shuffle tree folds them with the online rescale
-//   sum = sum_r s_r * exp(m_r - m), m = max_r m_r, identically in every warp of every CTA; y = e * exp(m_loc - m) / sum.
-// One exp per element, one read of HBM, no sweep over shared memory after the first.  The published pairs are double
-// buffered by row parity: a CTA writes pair (k+2) only after the cluster barrier of row k+1, which every peer reaches
-// after it has read pair k.
-// Special values follow the scalar rule of the CPU kernel (softmax_impl.h:36-42): NaN / +inf / a row of -inf poison the
-// whole row through the sum; a slice that is all -inf contributes its clipped exp(-64) terms without an inf - inf.
-__device__ __forceinline__ unsigned cluster_ctarank() {
-  unsigned r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ unsigned cluster_nctarank() {
-  unsigned r;
-  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ void cluster_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
-__device__ __forceinline__ void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
-// load a float from the same shared-memory variable of CTA `rank` of this cluster
-__device__ __forceinline__ float ld_dsmem_f32(const float* local_ptr, unsigned rank) {
-  uint32_t remote;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local_ptr)), "r"(rank));
-  float v;
-  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
-  return v;
-}
-
-template <typename T, int C, bool LOG>
-__global__ void __launch_bounds__(512, 1) softmax_cluster_pipe_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t rows,
-                                                                      int64_t dim, int slice, int stages,
-                                                                      float* __restrict__ stats) {
-  constexpr int V = Vec<T>::N;
-  constexpr float kLog2e = 1.4426950408889634f;
-  extern __shared__ __align__(128) unsigned char ring_raw[];
-  T* ring = reinterpret_cast<T*>(ring_raw);
-  __shared__ uint64_t full[4];
-  __shared__ float red[2][32];
-  __shared__ float xchg[2][2];  // [row parity][0] local max, [1] local sum — read by the peers through DSMEM
-  const unsigned rank = cluster_ctarank(), cs = cluster_nctarank();
-  const int64_t cluster_id = blockIdx.x / cs, n_clusters = gridDim.x / cs;
-  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31;
-  const int64_t begin = (int64_t)rank * slice;
-  int n = (int)(dim - begin < 0 ? 0 : (dim - begin > slice ? slice : dim - begin));
-  const uint32_t bytes = (uint32_t)n * sizeof(T);
-  if (tid == 0) {
-    for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
-    mbar_fence_init();
-  }
-  block_reduce_1sync_init(red[0], -INFINITY);
-  block_reduce_1sync_init(red[1], 0.f);
-  __syncthreads();
-  cluster_arrive_release();  // every CTA of the cluster is running before anyone touches a peer's shared memory
-  cluster_wait_acquire();
-  if (tid == 0 && n > 0) {
-    for (int s = 0; s < stages; ++s) {
-      const int64_t r = cluster_id + s * n_clusters;
-      if (r < rows) {
-        mbar_expect_tx(&full[s], bytes);
-        bulk_load_row(ring + (size_t)s * slice, x + r * dim + begin, bytes, &full[s]);
-      }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    __shared__ float red3[32][3];
+    __shared__ float xchg3[3];
+    t = ms_warp_reduce(t);
+    if (lane == 0) { red3[warp][0] = t.m; red3[warp][1] = t.s; red3[warp][2] = t.a; }
+    __syncthreads();
+    MaxSum g{-INFINITY, 0.f, 0.f};
+    if (lane < nwarps) g = MaxSum{red3[lane][0], red3[lane][1], red3[lane][2]};
+    g = ms_warp_reduce(g);
+    if (threadIdx.x == 0) { xchg3[0] = g.m; xchg3[1] = g.s; xchg3[2] = g.a; }
+    cluster.sync();
+    MaxSum p{-INFINITY, 0.f, 0.f};
+    if (lane < (int)cs) {
+      const float* r = cluster.map_shared_rank(xchg3, lane);
+      p = MaxSum{r[0], r[1], r[2]};
     }
-  }
-  int s = 0, par = 0;
-  uint32_t phase = 0;
-  for (int64_t row = cluster_id; row < rows; row += n_clusters) {
-    if (n > 0) mbar_wait(&full[s], phase);
-    const T* st = ring + (size_t)s * slice;
-    float e[C * V];
-    float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-    for (int c = 0; c < C; ++c) {
-      const int off = (c * nt + tid) * V;
-      if (off < n) {
-        unpack_to_float<T>(lds_vec(st + off), &e[c * V]);
-      } else {
-#pragma unroll
-        for (int k = 0; k < V; ++k) e[c * V + k] = -INFINITY;
-      }
-#pragma unroll
-      for (int k = 0; k < V; ++k) mx[k & 3] = fmaxf(mx[k & 3], e[c * V + k]);
-    }
-    float m_loc = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
-    m_loc = block_reduce_1sync(m_loc, MaxF<float>(), red[0]);  // its barrier also means: stage s fully read
-    if (tid == 0 && n > 0) {
-      const int64_t nrow = row + (int64_t)stages * n_clusters;
-      if (nrow < rows) {
-        fence_proxy_async_smem();
-        mbar_expect_tx(&full[s], bytes);
-        bulk_load_row(ring + (size_t)s * slice, x + nrow * dim + begin, bytes, &full[s]);
-      }
-    }
-    // a slice of -inf only: shift by 0, so that -inf clips to exp(-64) instead of turning into inf - inf
-    const bool dead = m_loc == -INFINITY;
-    const float shift = dead ? 0.f : -m_loc * kLog2e;
-    float sm[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-    for (int c = 0; c < C; ++c) {
-      const int off = (c * nt + tid) * V;
+    g = ms_warp_reduce(p);
+    gm = g.m;
+    gs = g.s + g.a;
+    if (g.m == -INFINITY) gs = __int_as_float(0x7fc00000);  // a row of -inf: NaN, as inf - inf gives in the CPU kernel
+  } else {
+    // double rows: exact exp, two sweeps and two barriers
+    A m = neg_inf<A>();
+    for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
+      const Vec<T> v = lds_vec(srow + i);
 #pragma unroll
       for (int k = 0; k < V; ++k) {
-        float p;
-        const float t = max_nan(fmaf(e[c * V + k], kLog2e, shift), -64.0f * kLog2e);
-        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p) : "f"(t));
-        if constexpr (!LOG) e[c * V + k] = p;  // LOG keeps x: its output term is the clipped difference itself
-        if (off < n) sm[k & 3] += p;
+        const A a = cvt<A>(v.v[k]);
+        m = a > m ? a : m;
       }
     }
-    float s_loc = (sm[0] + sm[1]) + (sm[2] + sm[3]);
-    s_loc = block_reduce_1sync(s_loc, AddF<float>(), red[1]);
-    // Only the thread that publishes needs release semantics.  A release arrive by every thread made each of them
-    // wait for its own streaming stores of the previous row to drain (stall_membar 2.4 of 14 cycles per instruction,
-    // profiles/r2c_softmax_vocab_bf16.txt); the others arrive relaxed.
-    if (tid == 0) {
-      xchg[par][0] = m_loc;
-      xchg[par][1] = s_loc;
-      asm volatile("barrier.cluster.arrive.release;" ::: "memory");
+    m = block_reduce(m, MaxF<A>(), neg_inf<A>(), red);
+    if (threadIdx.x == 0) xchg[0] = m;
+    cluster.sync();
+    gm = neg_inf<A>();
+    for (unsigned r = 0; r < cs; ++r) {
+      const A o = *cluster.map_shared_rank(&xchg[0], r);
+      gm = o > gm ? o : gm;
+    }
+    A sum = A(0);
+    for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
+      const Vec<T> v = lds_vec(srow + i);
+#pragma unroll
+      for (int k = 0; k < V; ++k) sum += row_exp<A>(cvt<A>(v.v[k]), gm, A(0));
+    }
+    sum = block_reduce(sum, AddF<A>(), A(0), red);
+    if (threadIdx.x == 0) xchg[1] = sum;
+    cluster.sync();
+    gs = A(0);
+    for (unsigned r = 0; r < cs; ++r) gs += *cluster.map_shared_rank(&xchg[1], r);
+  }
+  const A nml = -gm * A(1.4426950408889634);
+  const A inv = row_constant<LOG, A>(gs);
+  if (stats != nullptr && rank == 0 && threadIdx.x == 0) { stats[2 * row] = gm; stats[2 * row + 1] = log_acc<A>(gs); }
+  // Every CTA has read its peers' pairs by now: arrive for the exit barrier here (relaxed: nothing published after this
+  // point needs ordering, and a release arrive AFTER the stores made every thread wait for its stores to drain before
+  // the CTA could leave — stall_membar 1.0, profiles/r2e_softmax_vocab_bf16.txt), wait for it at the very end.
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+  // sweep 3: normalise and store
+  for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
+    if constexpr (std::is_same<A, float>::value) {
+      float v[V];
+      unpack_to_float<T>(lds_vec(srow + i), v);
+#pragma unroll
+      for (int k = 0; k < V; ++k) v[k] = LOG ? max_nan(v[k] - gm, -64.0f) - inv : fast_clipped_exp(v[k], nml) * inv;
+      Vec<T> o;
+      pack_from_float<T>(v, o);
+      st_stream(dst + i, o);
     } else {
-      asm volatile("barrier.cluster.arrive.relaxed;" ::: "memory");
-    }
-    cluster_wait_acquire();
-    float pm = -INFINITY, ps = 0.f;
-    if (lane < (int)cs) {
-      pm = ld_dsmem_f32(&xchg[par][0], lane);
-      ps = ld_dsmem_f32(&xchg[par][1], lane);
-    }
-    const float gm = group_reduce<32>(pm, MaxF<float>());
-    float contrib = ps;
-    if (pm != -INFINITY) {
-      float f;
-      asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(f) : "f"((pm - gm) * kLog2e));
-      contrib = ps * f;
-    }
-    float gs = group_reduce<32>(contrib, AddF<float>());
-    if (gm == -INFINITY) gs = __int_as_float(0x7fc00000);  // a row of -inf: inf - inf in the CPU kernel, NaN everywhere
-    if (stats != nullptr && rank == 0 && tid == 0) { stats[2 * row] = gm; stats[2 * row + 1] = logf(gs); }
-    T* dst = y + row * dim + begin;
-    if constexpr (LOG) {
-      const float lg = logf(gs);
+      const Vec<T> v = lds_vec(srow + i);
+      Vec<T> o;
 #pragma unroll
-      for (int c = 0; c < C; ++c) {
-        const int off = (c * nt + tid) * V;
-        if (off < n) {
-          float r[V];
-#pragma unroll
-          for (int k = 0; k < V; ++k) r[k] = max_nan(e[c * V + k] - gm, -64.0f) - lg;
-          Vec<T> o;
-          pack_from_float<T>(r, o);
-          st_stream(dst + off, o);
-        }
-      }
-    } else {
-      float f = 1.0f;
-      if (!dead) asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(f) : "f"((m_loc - gm) * kLog2e));
-      const float kk = f / gs;
-#pragma unroll
-      for (int c = 0; c < C; ++c) {
-        const int off = (c * nt + tid) * V;
-        if (off < n) {
-          float r[V];
-#pragma unroll
-          for (int k = 0; k < V; ++k) r[k] = e[c * V + k] * kk;
-          Vec<T> o;
-          pack_from_float<T>(r, o);
-          st_stream(dst + off, o);
-        }
-      }
-    }
-    par ^= 1;
-    if (++s == stages) {
-      s = 0;
-      phase ^= 1;
+      for (int k = 0; k < V; ++k)
+        o.v[k] = cvt<T>(LOG ? clipped_diff<A>(cvt<A>(v.v[k]), gm) - inv : row_exp<A>(cvt<A>(v.v[k]), gm, nml) * inv);
+      st_stream(dst + i, o);
     }
   }
-  cluster_arrive_release();  // nobody leaves while a peer may still be reading its xchg[]
-  cluster_wait_acquire();
+  asm volatile("barrier.cluster.wait.aligned;" ::: "memory");  // nobody leaves while a peer may still be reading its xchg[]
+}
+
+// ---- rows_sweep2: long rows streamed twice, the second time out of L2 ------------------------------------------------
+// For rows that do not fit the register / shared-memory routes (and as an alternative to them for vocabulary-sized rows):
+// CTA `rank` of a cluster of cs (1..8) owns slice [rank*slice, +slice) of one row.  Sweep 1 streams the slice from HBM with
+// 16-byte loads and keeps a per-thread running (max, sum) — four vectors at a time, one rescale per batch, 1.25 exp per
+// element — folded over the CTA and, through DSMEM after ONE cluster barrier, over the cluster.  Sweep 2 re-reads the
+// slice, normalises and stores; the launch keeps the slices of all resident CTAs within ~64 MB so that this second
+// read comes out of the 126 MB L2: HBM sees one read and one write.  No shared-memory staging, no limit on the row
+// length, cs x as many CTAs as rows when there are few rows.
+template <typename T, bool LOG>
+__global__ void __launch_bounds__(512) softmax_rows_sweep2_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t dim,
+                                                                  int64_t slice, float* __restrict__ stats) {
+  namespace cg = cooperative_groups;
+  constexpr int V = Vec<T>::N;
+  constexpr int U = 4;
+  constexpr float kLog2e = 1.4426950408889634f;
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned rank = cluster.block_rank(), cs = cluster.num_blocks();
+  __shared__ float red[32][3];
+  __shared__ float xchg[3];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+  const int64_t row = (int64_t)blockIdx.x / cs;
+  const int64_t begin = (int64_t)rank * slice;
+  int64_t n = dim - begin;
+  n = n < 0 ? 0 : (n > slice ? slice : n);
+  const T* src = x + row * dim + begin;
+  T* dst = y + row * dim + begin;
+  const int64_t step = (int64_t)blockDim.x * V;
+  MaxSum t{-INFINITY, 0.f, 0.f};
+  int64_t i = (int64_t)tid * V;
+  for (; i + (U - 1) * step < n; i += U * step) {
+    Vec<T> raw[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) raw[u] = ld_stream(src + i + u * step);
+    float v[U * V];
+#pragma unroll
+    for (int u = 0; u < U; ++u) unpack_to_float<T>(raw[u], &v[u * V]);
+    ms_accumulate<U * V>(t, v);
+  }
+  for (; i < n; i += step) {
+    float v[V];
+    unpack_to_float<T>(ld_stream(src + i), v);
+    ms_accumulate<V>(t, v);
+  }
+  t = ms_warp_reduce(t);
+  if (lane == 0) { red[warp][0] = t.m; red[warp][1] = t.s; red[warp][2] = t.a; }
+  __syncthreads();
+  MaxSum g{-INFINITY, 0.f, 0.f};
+  if (lane < nwarps) g = MaxSum{red[lane][0], red[lane][1], red[lane][2]};
+  g = ms_warp_reduce(g);
+  if (cs > 1) {
+    if (tid == 0) { xchg[0] = g.m; xchg[1] = g.s; xchg[2] = g.a; }
+    cluster.sync();
+    MaxSum p{-INFINITY, 0.f, 0.f};
+    if (lane < (int)cs) {
+      const float* r = cluster.map_shared_rank(xchg, lane);
+      p = MaxSum{r[0], r[1], r[2]};
+    }
+    g = ms_warp_reduce(p);
+  }
+  float gs = g.s + g.a;
+  if (g.m == -INFINITY) gs = __int_as_float(0x7fc00000);  // a row of -inf: NaN, as inf - inf gives in the CPU kernel
+  if (stats != nullptr && rank == 0 && tid == 0) { stats[2 * row] = g.m; stats[2 * row + 1] = logf(gs); }
+  const float k = LOG ? logf(gs) : 1.0f / gs;
+  const float nml = -g.m * kLog2e;
+  // sweep 2: each chunk is read and written by the same thread (in place is fine)
+  i = (int64_t)tid * V;
+  for (; i + (U - 1) * step < n; i += U * step) {
+    Vec<T> raw[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) raw[u] = ld_stream(src + i + u * step);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float v[V];
+      unpack_to_float<T>(raw[u], v);
+#pragma unroll
+      for (int q = 0; q < V; ++q) v[q] = LOG ? max_nan(v[q] - g.m, -64.0f) - k : fast_clipped_exp(v[q], nml) * k;
+      Vec<T> o;
+      pack_from_float<T>(v, o);
+      st_stream(dst + i + u * step, o);
+    }
+  }
+  for (; i < n; i += step) {
+    float v[V];
+    unpack_to_float<T>(ld_stream(src + i), v);
+#pragma unroll
+    for (int q = 0; q < V; ++q) v[q] = LOG ? max_nan(v[q] - g.m, -64.0f) - k : fast_clipped_exp(v[q], nml) * k;
+    Vec<T> o;
+    pack_from_float<T>(v, o);
+    st_stream(dst + i, o);
+  }
+  if (cs > 1) cluster.sync();  // nobody leaves while a peer may still be reading its xchg[]
 }
 
 // ---- rows_stream -----------------------------------------------------------------------
@@ -845,78 +840,49 @@ int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, typename AccT
   }
 }
 
-// Persistent cluster pipeline (softmax_cluster_pipe_kernel): rows of up to 8 x 512 x 32 values.  < 0: does not apply.
+// Two-sweep route (softmax_rows_sweep2_kernel): any row length.  < 0: could not launch.
 template <typename T, bool LOG>
-int try_softmax_cluster_pipe(const T* x, T* y, int64_t outer, int64_t dim, typename AccType<T>::type* stats, cudaStream_t st) {
+int try_softmax_sweep2(const T* x, T* y, int64_t outer, int64_t dim, typename AccType<T>::type* stats, cudaStream_t st) {
   if constexpr (std::is_same<T, double>::value) {
     return -1;  // computes in float
   } else {
     constexpr int VN = Vec<T>::N;
-    constexpr int kThreads = 512, kMaxVals = 32;  // values a thread keeps in registers
-    if (knobs().no_cluster_pipe) return -1;
-    const int64_t cap = (int64_t)kThreads * kMaxVals;  // elements per CTA
-    int cs = 2;
-    while (cs < 8 && (dim + cs - 1) / cs > cap) cs <<= 1;
-    // few rows: more, smaller slices put more SMs to work on each row
-    while (cs < 8 && outer * cs < (int64_t)sm_count()) cs <<= 1;
+    int cs = 1;
+    while (cs < 8 && outer * cs < 2 * (int64_t)sm_count()) cs <<= 1;
     int64_t slice = (dim + cs - 1) / cs;
     slice = (slice + VN - 1) / VN * VN;
-    if (slice > cap) return -1;
-    const int64_t nchunk = slice / VN;
-    int C = 1;
-    while (C < kMaxVals / VN && (nchunk + C - 1) / C > kThreads) C <<= 1;
-    int threads = (int)((nchunk + C - 1) / C);
-    threads = (threads + 31) / 32 * 32;
-    if (threads > kThreads || threads * C < nchunk) return -1;
-    const int stages = 2;
-    const size_t smem = (size_t)stages * slice * sizeof(T);
-    auto launch = [&](auto kern) -> int {
-      FuncAttrHold hold;  // the dynamic shared-memory size follows the slice: held until the launch call has returned
-      if (!func_attr_apply(reinterpret_cast<const void*>(kern), (int)smem, -1, &hold)) return -1;
-      cudaLaunchConfig_t cfg{};
-      cfg.blockDim = dim3(threads);
-      cfg.dynamicSmemBytes = smem;
-      cfg.stream = st;
-      cudaLaunchAttribute attr[1];
-      attr[0].id = cudaLaunchAttributeClusterDimension;
-      attr[0].val.clusterDim.x = cs;
-      attr[0].val.clusterDim.y = 1;
-      attr[0].val.clusterDim.z = 1;
-      cfg.attrs = attr;
-      cfg.numAttrs = 1;
-      // how many clusters the device holds at once: asked once per (kernel, device, geometry)
-      static std::map<std::tuple<const void*, int, int, size_t, int>, int> resident;  // guarded by the attribute lock
-      int dev = 0;
-      cudaGetDevice(&dev);
-      const auto key = std::make_tuple(reinterpret_cast<const void*>(kern), dev, threads, smem, cs);
-      auto it = resident.find(key);
-      if (it == resident.end()) {
-        int ncl = 0;
-        cfg.gridDim = dim3((unsigned)(cs * sm_count()));
-        if (cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg) != cudaSuccess) {
-          cudaGetLastError();
-          ncl = 0;
-        }
-        it = resident.emplace(key, ncl).first;
-      }
-      int64_t ncl = it->second;
-      if (ncl < 1) return -1;
-      if (ncl > outer) ncl = outer;
-      cfg.gridDim = dim3((unsigned)(ncl * cs));
-      if (cudaLaunchKernelEx(&cfg, kern, x, y, outer, dim, (int)slice, stages, stats) != cudaSuccess) {
-        cudaGetLastError();
-        return -1;
-      }
-      return after_launch("softmax_cluster_pipe");
-    };
-    switch (C) {
-      case 1: return launch(softmax_cluster_pipe_kernel<T, 1, LOG>);
-      case 2: return launch(softmax_cluster_pipe_kernel<T, 2, LOG>);
-      case 4: return launch(softmax_cluster_pipe_kernel<T, 4, LOG>);
-      case 8:
-        if constexpr (kMaxVals / VN >= 8) return launch(softmax_cluster_pipe_kernel<T, 8, LOG>);
+    if (outer * cs > 0x7fffffffLL) return -1;
+    const int threads = 512;
+    // keep the slices of all resident CTAs within ~64 MB, so that sweep 2 is served by L2: cap the CTAs per SM with
+    // dynamic shared memory the kernel never touches
+    const size_t slice_bytes = (size_t)slice * sizeof(T);
+    int per_sm = (int)((64u << 20) / ((size_t)sm_count() * std::max<size_t>(slice_bytes, 1)));
+    per_sm = per_sm < 1 ? 1 : (per_sm > 4 ? 4 : per_sm);
+    const size_t smem = per_sm >= 4 ? 0 : (size_t)(227 * 1024) / per_sm - 4096;
+    auto kern = softmax_rows_sweep2_kernel<T, LOG>;
+    FuncAttrHold hold;
+    if (!func_attr_apply(reinterpret_cast<const void*>(kern), (int)smem, smem ? 100 : -1, &hold)) return -1;
+    if (cs == 1) {
+      kern<<<(unsigned)outer, threads, smem, st>>>(x, y, dim, slice, stats);
+      return after_launch("softmax_rows_sweep2");
     }
-    return -1;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)(outer * cs));
+    cfg.blockDim = dim3(threads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cs;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if (cudaLaunchKernelEx(&cfg, kern, x, y, dim, slice, stats) != cudaSuccess) {
+      cudaGetLastError();
+      return -1;
+    }
+    return after_launch("softmax_rows_sweep2");
   }
 }
 
@@ -986,9 +952,12 @@ int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, t
                  : launch_rows_reg<T, false, LOG>(x, y, outer, (int)dim, G, C, stats, st);
     }
     if (vec) {
-      int rc = try_softmax_cluster_pipe<T, LOG>(x, y, outer, dim, stats, st);
-      if (rc >= 0) return rc;
-      rc = try_softmax_cluster<T, LOG>(x, y, outer, dim, stats, st);
+      // long rows: shared-memory-resident slices across a cluster (one read, rows up to 8 x 200 KB) or two sweeps with
+      // the second out of L2 (any length); PDB200_SOFTMAX_LONG = 1 / 2 forces the first / second
+      const int pick = knobs().softmax_long;
+      int rc = -1;
+      if (pick != 2) rc = try_softmax_cluster<T, LOG>(x, y, outer, dim, stats, st);
+      if (rc < 0 && pick != 1) rc = try_softmax_sweep2<T, LOG>(x, y, outer, dim, stats, st);
       if (rc >= 0) return rc;
     }
     if (outer > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "softmax: too many rows for one launch");
