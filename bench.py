@@ -499,7 +499,7 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
         parts = [torch.empty_like(part) for _ in range(world)]
         dist.all_gather(parts, part)
         ref64 = torch.stack(parts).double().sum(0)
-        ulp = ref64.abs().clamp_min(1e-30) * 2.0 ** -8  # one bf16 ulp of the result (8 significand bits)
+        ulp = torch.exp2(torch.floor(torch.log2(ref64.abs().clamp_min(1e-30))) - 7)  # one bf16 ulp at the result's binade
         err_p = float(((b.double() - ref64).abs() / ulp).max())
         err_n = float(((a.double() - ref64).abs() / ulp).max())
         if err_p > 1.0 or err_n > 1.0:

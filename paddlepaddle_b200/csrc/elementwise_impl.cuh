@@ -342,7 +342,10 @@ struct GeneralParams {
 // adding the grid stride digit by digit with carry (`inc`, computed on the host) — adds and compares, no division in
 // the loop.  (The first version ran a 64-bit div/mod chain per run: ~300 instructions per 16 bytes, 2.4 TB/s on a
 // 4-D bf16 broadcast, profiles/r2_notes.txt.)
-template <typename T, typename Op, bool VECTOR>
+// RMAX: compile-time bound on the merged rank (4 covers almost every broadcast; 9 = DDim::kMaxRank).  IDX: type of the
+// per-dim digits — uint32_t when every merged dim is below 2^31 (half the instructions of the 64-bit carry chain: the walk
+// was issue-bound, 77 % issue slots at 45 % DRAM, profiles/r2_ew_general_bf16.txt), int64_t otherwise.
+template <typename T, typename Op, bool VECTOR, int RMAX, typename IDX>
 __global__ void __launch_bounds__(kThreads) ew_general_kernel(const T* __restrict__ x,
                                                               const T* __restrict__ y,
                                                               typename OpOut<T, Op>::type* __restrict__ out,
@@ -352,26 +355,26 @@ __global__ void __launch_bounds__(kThreads) ew_general_kernel(const T* __restric
   const int64_t stride = (int64_t)gridDim.x * kThreads;
   if (run >= nruns) return;
   // digits of the first run
-  int64_t idx[PDB200_MAX_RANK];
+  IDX idx[RMAX];
   {
     int64_t rest = run;
 #pragma unroll
-    for (int d = 0; d < PDB200_MAX_RANK; ++d) {
+    for (int d = 0; d < RMAX; ++d) {
       idx[d] = 0;
       if (d < p.rank) {
         const int64_t q = rest / p.dims[d];
-        idx[d] = rest - q * p.dims[d];
+        idx[d] = (IDX)(rest - q * p.dims[d]);
         rest = q;
       }
     }
   }
   for (; run < nruns; run += stride) {
-    int64_t xo = idx[0] * V * p.xs[0], yo = idx[0] * V * p.ys[0];
+    int64_t xo = (int64_t)idx[0] * V * p.xs[0], yo = (int64_t)idx[0] * V * p.ys[0];
 #pragma unroll
-    for (int d = 1; d < PDB200_MAX_RANK; ++d) {
+    for (int d = 1; d < RMAX; ++d) {
       if (d < p.rank) {
-        xo += idx[d] * p.xs[d];
-        yo += idx[d] * p.ys[d];
+        xo += (int64_t)idx[d] * p.xs[d];
+        yo += (int64_t)idx[d] * p.ys[d];
       }
     }
     const int64_t oo = run * V;
@@ -396,14 +399,14 @@ __global__ void __launch_bounds__(kThreads) ew_general_kernel(const T* __restric
       out[oo] = Op::apply(x[xo], y[yo]);
     }
     // advance by the grid stride: digit-wise add with carry
-    int64_t carry = 0;
+    IDX carry = 0;
 #pragma unroll
-    for (int d = 0; d < PDB200_MAX_RANK; ++d) {
+    for (int d = 0; d < RMAX; ++d) {
       if (d < p.rank) {
-        int64_t v = idx[d] + p.inc[d] + carry;
+        IDX v = idx[d] + (IDX)p.inc[d] + carry;  // < 2 * dims[d]: no overflow below 2^31
         carry = 0;
-        if (v >= p.dims[d]) {
-          v -= p.dims[d];
+        if (v >= (IDX)p.dims[d]) {
+          v -= (IDX)p.dims[d];
           carry = 1;
         }
         idx[d] = v;
@@ -499,10 +502,19 @@ int launch_elementwise(const BroadcastPlan& p, const T* x, const T* y, typename 
       rest /= gp.dims[d];
     }
   }
-  if (vec_ok)
-    ew_general_kernel<T, Op, true><<<(unsigned)blocks, kThreads, 0, st>>>(x, y, out, nruns, gp);
-  else
-    ew_general_kernel<T, Op, false><<<(unsigned)blocks, kThreads, 0, st>>>(x, y, out, nruns, gp);
+  bool small = gp.rank <= 4;
+  for (int d = 0; d < gp.rank; ++d) small = small && gp.dims[d] < (int64_t(1) << 31);
+  if (small) {
+    if (vec_ok)
+      ew_general_kernel<T, Op, true, 4, uint32_t><<<(unsigned)blocks, kThreads, 0, st>>>(x, y, out, nruns, gp);
+    else
+      ew_general_kernel<T, Op, false, 4, uint32_t><<<(unsigned)blocks, kThreads, 0, st>>>(x, y, out, nruns, gp);
+  } else {
+    if (vec_ok)
+      ew_general_kernel<T, Op, true, PDB200_MAX_RANK, int64_t><<<(unsigned)blocks, kThreads, 0, st>>>(x, y, out, nruns, gp);
+    else
+      ew_general_kernel<T, Op, false, PDB200_MAX_RANK, int64_t><<<(unsigned)blocks, kThreads, 0, st>>>(x, y, out, nruns, gp);
+  }
   return after_launch("ew_general");
 }
 

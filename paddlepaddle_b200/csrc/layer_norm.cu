@@ -426,23 +426,41 @@ __global__ void __launch_bounds__(1024) ln_rows_cluster_kernel(const T* __restri
   // a pair; after ONE cluster barrier every CTA folds the cs pairs with the pairwise-variance rule
   //     mean = sum_r n_r mean_r / D,     M2 = sum_r (M2_r + n_r (mean_r - mean)^2),     var = M2 / D
   // (as accurate as two passes over the whole row; the first version needed two cluster barriers).
-  U sum = U(0);
+  // (whole-vector unpack, four independent chains: the sweeps were issue-bound — 87 % issue slots at 44 % DRAM,
+  // profiles/r2_ln_vocab_bf16.txt)
+  U acc4[4] = {U(0), U(0), U(0), U(0)};
   for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
-    const Vec<T> v = lds_vec(srow + i);
+    U e[V];
+    if constexpr (std::is_same<U, float>::value) {
+      unpack_to_float<T>(lds_vec(srow + i), e);
+    } else {
+      const Vec<T> v = lds_vec(srow + i);
 #pragma unroll
-    for (int k = 0; k < V; ++k) sum += cvt<U>(v.v[k]);
+      for (int k = 0; k < V; ++k) e[k] = cvt<U>(v.v[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < V; ++k) acc4[k & 3] += e[k];
   }
+  U sum = (acc4[0] + acc4[1]) + (acc4[2] + acc4[3]);
   sum = block_reduce(sum, AddU<U>(), U(0), red);
   const U mean_loc = n > 0 ? sum / (U)n : U(0);
-  U sq = U(0);
+  acc4[0] = acc4[1] = acc4[2] = acc4[3] = U(0);
   for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
-    const Vec<T> v = lds_vec(srow + i);
+    U e[V];
+    if constexpr (std::is_same<U, float>::value) {
+      unpack_to_float<T>(lds_vec(srow + i), e);
+    } else {
+      const Vec<T> v = lds_vec(srow + i);
+#pragma unroll
+      for (int k = 0; k < V; ++k) e[k] = cvt<U>(v.v[k]);
+    }
 #pragma unroll
     for (int k = 0; k < V; ++k) {
-      const U d = cvt<U>(v.v[k]) - mean_loc;
-      sq += d * d;
+      const U d = e[k] - mean_loc;
+      acc4[k & 3] += d * d;
     }
   }
+  U sq = (acc4[0] + acc4[1]) + (acc4[2] + acc4[3]);
   sq = block_reduce(sq, AddU<U>(), U(0), red);
   if (threadIdx.x == 0) {
     xchg[0] = mean_loc;
@@ -475,11 +493,32 @@ __global__ void __launch_bounds__(1024) ln_rows_cluster_kernel(const T* __restri
   const P* sc = scale ? scale + begin : nullptr;
   const P* bi = bias ? bias + begin : nullptr;
   for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
-    const Vec<T> v = lds_vec(srow + i);
-    U e[V];
+    if constexpr (std::is_same<U, float>::value) {
+      constexpr int PV = Vec<P>::N;
+      float e[V], w[V], b[V], o[V];
+      unpack_to_float<T>(lds_vec(srow + i), e);
 #pragma unroll
-    for (int k = 0; k < V; ++k) e[k] = cvt<U>(v.v[k]);
-    ln_store_chunk<T, P, U, V, true>(e, mean, rstd, sc, bi, dst, i);
+      for (int k = 0; k < V; ++k) { w[k] = 1.f; b[k] = 0.f; }
+      if (sc != nullptr) {
+#pragma unroll
+        for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(sc + i + j * PV), &w[j * PV]);
+      }
+      if (bi != nullptr) {
+#pragma unroll
+        for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(bi + i + j * PV), &b[j * PV]);
+      }
+#pragma unroll
+      for (int k = 0; k < V; ++k) o[k] = fmaf(__fmul_rn(e[k] - mean, rstd), w[k], b[k]);  // as ln_pipe_kernel
+      Vec<T> ov;
+      pack_from_float<T>(o, ov);
+      st_stream(dst + i, ov);
+    } else {
+      const Vec<T> v = lds_vec(srow + i);
+      U e[V];
+#pragma unroll
+      for (int k = 0; k < V; ++k) e[k] = cvt<U>(v.v[k]);
+      ln_store_chunk<T, P, U, V, true>(e, mean, rstd, sc, bi, dst, i);
+    }
   }
   asm volatile("barrier.cluster.wait.aligned;" ::: "memory");  // nobody leaves while a peer may still be reading its xchg[]
 }
@@ -607,7 +646,7 @@ int layer_norm_typed(const T* x, const P* scale, const P* bias, T* y, void* mean
   }
 #undef PDB_LN_C
   // Long rows (beyond the register routes): thread-block cluster per row, slices in shared memory.
-  if (vec && nchunk > 1024 * 4) {
+  if (vec && nchunk > 1024 * 4 && (!scale || is_aligned16(scale)) && (!bias || is_aligned16(bias))) {
     const size_t row_bytes = (size_t)D * sizeof(T);
     const size_t kMaxSlice = 200 * 1024;
     int cs = 1;

@@ -189,7 +189,7 @@ __global__ void __launch_bounds__(256) peer_allreduce_kernel(PeerPtrs ptrs, int 
 // Requires n % Vec<S>::N == 0 handled by the caller through a ragged tail done one-shot style by CTA 0; `out` 16-byte
 // aligned.  Grid <= SM count (every CTA must be resident: CTAs wait for the grid's last CTA to publish).
 template <typename S, typename T, int OP>
-__global__ void __launch_bounds__(256) peer_allreduce2_kernel(PeerPtrs ptrs, int world, int rank, size_t slot_bytes,
+__global__ void __launch_bounds__(256, 2) peer_allreduce2_kernel(PeerPtrs ptrs, int world, int rank, size_t slot_bytes,
                                                               unsigned long long epoch, int64_t n, T* out,
                                                               unsigned long long timeout_ns, int* host_err) {
   __shared__ int timed_out;
@@ -214,23 +214,49 @@ __global__ void __launch_bounds__(256) peer_allreduce2_kernel(PeerPtrs ptrs, int
   const int64_t v0 = (int64_t)rank * chunk;
   const int64_t v1 = v0 + chunk < nvec ? v0 + chunk : nvec;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = v0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < v1; i += stride) {
-    S acc[VS];
+  // kPeerUnroll vectors per thread and trip: world x kPeerUnroll 16-byte peer loads in flight per thread — a peer load
+  // takes microseconds, and the link is only full with a few KB outstanding per SM
+  constexpr int kPeerUnroll = 2;
+  constexpr int kGroup = 4;  // ranks whose loads are issued together
+  for (int64_t i0 = v0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < v1; i0 += kPeerUnroll * stride) {
+    Vec<S> in[kPeerUnroll][kGroup];
+    S acc[kPeerUnroll][VS];
+    // ranks in groups of kGroup: the loads of a group are all issued before any is used
 #pragma unroll
-    for (int r = 0; r < kPeerMaxWorld; ++r) {
-      if (r < world) {
-        const Vec<S> v = ld_peer(reinterpret_cast<const S*>(ptrs.win[r] + slot_off) + i * VS);
+    for (int half = 0; half < kPeerMaxWorld / kGroup; ++half) {
+      if (half * kGroup >= world) break;
 #pragma unroll
-        for (int k = 0; k < VS; ++k) acc[k] = r == 0 ? v.v[k] : peer_combine<S, OP>(acc[k], v.v[k]);
+      for (int u = 0; u < kPeerUnroll; ++u) {
+        const int64_t i = i0 + u * stride;
+#pragma unroll
+        for (int r = 0; r < kGroup; ++r)
+          if (half * kGroup + r < world && i < v1) in[u][r] = ld_peer(reinterpret_cast<const S*>(ptrs.win[half * kGroup + r] + slot_off) + i * VS);
+      }
+#pragma unroll
+      for (int u = 0; u < kPeerUnroll; ++u) {
+#pragma unroll
+        for (int r = 0; r < kGroup; ++r) {
+          if (half * kGroup + r < world) {
+#pragma unroll
+            for (int k = 0; k < VS; ++k)
+              acc[u][k] = (half == 0 && r == 0) ? in[u][r].v[k] : peer_combine<S, OP>(acc[u][k], in[u][r].v[k]);
+          }
+        }
       }
     }
-    Pack<T, VS> o;
 #pragma unroll
-    for (int k = 0; k < VS; ++k) o.v[k] = cvt<T>(acc[k]);
-    // the chunk goes to every rank's result region (own included): sizeof(T) * VS bytes per store
+    for (int u = 0; u < kPeerUnroll; ++u) {
+      const int64_t i = i0 + u * stride;
+      if (i < v1) {
+        Pack<T, VS> o;
 #pragma unroll
-    for (int r = 0; r < kPeerMaxWorld; ++r) {
-      if (r < world) *reinterpret_cast<Pack<T, VS>*>(reinterpret_cast<T*>(ptrs.win[r] + res_off) + i * VS) = o;
+        for (int k = 0; k < VS; ++k) o.v[k] = cvt<T>(acc[u][k]);
+        // the chunk goes to every rank's result region (own included): sizeof(T) * VS bytes per store
+#pragma unroll
+        for (int r = 0; r < kPeerMaxWorld; ++r) {
+          if (r < world) *reinterpret_cast<Pack<T, VS>*>(reinterpret_cast<T*>(ptrs.win[r] + res_off) + i * VS) = o;
+        }
+      }
     }
   }
   if (blockIdx.x == 0) {  // ragged tail (< VS elements): rank 0 reduces it for everyone
@@ -265,9 +291,14 @@ __global__ void __launch_bounds__(256) peer_allreduce2_kernel(PeerPtrs ptrs, int
   const T* res = reinterpret_cast<const T*>(mine + res_off);
   constexpr int VT = Vec<T>::N;
   const int64_t nv_out = n / VT;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nv_out; i += stride) {
-    const Vec<T> v = ld_peer(res + i * VT);
-    *reinterpret_cast<uint4*>(out + i * VT) = *reinterpret_cast<const uint4*>(&v);
+  for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < nv_out; i0 += kPeerUnroll * stride) {
+    Vec<T> v[kPeerUnroll];
+#pragma unroll
+    for (int u = 0; u < kPeerUnroll; ++u)
+      if (i0 + u * stride < nv_out) v[u] = ld_peer(res + (i0 + u * stride) * VT);
+#pragma unroll
+    for (int u = 0; u < kPeerUnroll; ++u)
+      if (i0 + u * stride < nv_out) *reinterpret_cast<uint4*>(out + (i0 + u * stride) * VT) = *reinterpret_cast<const uint4*>(&v[u]);
   }
   if (blockIdx.x == 0)
     for (int64_t i = nv_out * VT + threadIdx.x; i < n; i += blockDim.x) out[i] = reinterpret_cast<const volatile T*>(res)[i];
@@ -283,7 +314,8 @@ int peer_launch(int op, const PeerPtrs& p, int world, int rank, size_t slot_byte
   if (two_shot) {
     const int64_t chunk = (nvec + world - 1) / world;
     // the grid must be co-resident (its CTAs wait for its last CTA): never more CTAs than SMs
-    const int64_t blocks = std::max<int64_t>(1, std::min<int64_t>((chunk + 255) / 256, (int64_t)sm_count()));
+    // two CTAs per SM (256 threads, < 128 registers: both always fit) — twice the loads in flight
+    const int64_t blocks = std::max<int64_t>(1, std::min<int64_t>((chunk + 255) / 256, 2 * (int64_t)sm_count()));
 #define PDB_PEER2(OP) peer_allreduce2_kernel<S, T, OP><<<(unsigned)blocks, 256, 0, st>>>(p, world, rank, slot_bytes, epoch, n, out, timeout_ns, host_err)
     switch (op) {
       case kPeerSum: PDB_PEER2(kPeerSum); break;

@@ -760,12 +760,30 @@ __global__ void __launch_bounds__(256) softmax_cols_tile_kernel(const T* __restr
     }
   }
   if (!active) return;
-  for (int64_t r = ty; r < dim; r += TY) {
+  float nml[V];
+#pragma unroll
+  for (int k = 0; k < V; ++k) nml[k] = -M[k] * kLog2e;
+  int64_t r = ty;
+  for (; r + (int64_t)(U - 1) * TY < dim; r += (int64_t)U * TY) {  // U loads in flight per thread, as in sweep 1
+    Vec<T> raw[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) raw[u] = ld_stream(src + (r + (int64_t)u * TY) * inner);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float v[V];
+      unpack_to_float<T>(raw[u], v);
+#pragma unroll
+      for (int k = 0; k < V; ++k) v[k] = LOG ? max_nan(v[k] - M[k], -64.0f) - inv[k] : fast_clipped_exp(v[k], nml[k]) * inv[k];
+      Vec<T> ov;
+      pack_from_float<T>(v, ov);
+      st_stream(dst + (r + (int64_t)u * TY) * inner, ov);
+    }
+  }
+  for (; r < dim; r += TY) {
     float v[V];
     unpack_to_float<T>(ld_stream(src + r * inner), v);
 #pragma unroll
-    for (int k = 0; k < V; ++k)
-      v[k] = LOG ? max_nan(v[k] - M[k], -64.0f) - inv[k] : fast_clipped_exp(v[k], -M[k] * kLog2e) * inv[k];
+    for (int k = 0; k < V; ++k) v[k] = LOG ? max_nan(v[k] - M[k], -64.0f) - inv[k] : fast_clipped_exp(v[k], nml[k]) * inv[k];
     Vec<T> ov;
     pack_from_float<T>(v, ov);
     st_stream(dst + r * inner, ov);

@@ -75,13 +75,18 @@ __global__ void __launch_bounds__(512) softmax_mask_pipe_kernel(const T* __restr
   auto fill = [&](int s, int64_t r) {
     unsigned char* st = ring_raw + (size_t)s * stage_bytes;
     if constexpr (TRI) {
-      const int q = (int)(r % sq);
+      const int q = rows <= 0xffffffffLL ? (int)((uint32_t)r % (uint32_t)sq) : (int)(r % sq);  // 32-bit when it fits
       const uint32_t bytes = (((uint32_t)(q + 1) * sizeof(T)) + 15u) & ~15u;  // <= x_bytes: dim * sizeof(T) is a multiple of 16
       mbar_expect_tx(&full[s], bytes);
       bulk_load_row(st, x + r * dim, bytes, &full[s]);
     } else {
-      const int64_t b = r / ((int64_t)heads * sq);
-      const int64_t mrow = b * sq + r % sq;
+      int64_t mrow;
+      if (rows <= 0xffffffffLL) {  // 32-bit index math when it fits (a 64-bit div / mod pair costs ~100 instructions)
+        const uint32_t b = (uint32_t)r / ((uint32_t)heads * (uint32_t)sq);
+        mrow = (int64_t)b * sq + (uint32_t)r % (uint32_t)sq;
+      } else {
+        mrow = (r / ((int64_t)heads * sq)) * sq + r % sq;
+      }
       mbar_expect_tx(&full[s], x_bytes + m_bytes);
       bulk_load_row(st, x + r * dim, x_bytes, &full[s]);
       bulk_load_row(st + x_bytes, mask + mrow * dim, m_bytes, &full[s]);
@@ -96,7 +101,7 @@ __global__ void __launch_bounds__(512) softmax_mask_pipe_kernel(const T* __restr
   int s = 0;
   uint32_t phase = 0;
   for (int64_t row = row_first; row < row_end; row += row_step) {
-    const int valid = TRI ? (int)(row % sq) + 1 : dim;  // elements of this row that take part
+    const int valid = TRI ? (rows <= 0xffffffffLL ? (int)((uint32_t)row % (uint32_t)sq) : (int)(row % sq)) + 1 : dim;  // elements that take part
     mbar_wait(&full[s], phase);
     const T* sx = reinterpret_cast<const T*>(ring_raw + (size_t)s * stage_bytes);
     const MT* sm = reinterpret_cast<const MT*>(ring_raw + (size_t)s * stage_bytes + x_bytes);
@@ -216,10 +221,9 @@ int softmax_mask_typed(const T* x, const MT* mask, T* y, int64_t batch, int64_t 
       heads < (int64_t(1) << 31)) {
     // chunks per thread as in softmax.cu: 16-bit rows 4 (32 values a thread), fp32 rows 2
     int C = sizeof(T) == 2 ? (nchunk >= 256 ? 4 : (nchunk >= 128 ? 2 : 1)) : (nchunk >= 256 ? 2 : 1);
-    // The additive-mask form unpacks two operands per value: with 64-thread CTAs (2 warps) and the 4 CTAs per SM that
-    // 16 KB stages allow, 8 warps per SM cannot cover their own dependent chains (warps active 15 %, issue 43 %,
-    // DRAM 40 %: profiles/r2c_softmax_mask_bf16.txt).  Half the values per thread = twice the warps for the same rows.
-    if (!TRI && C > 1) C >>= 1;
+    // (profiles/r2_notes.txt: bf16 [4,32,2048,2048] + mask, C x KB of rows in flight per SM -> ms: 1 x 64 0.78, 2 x 64 0.58,
+    //  2 x 128 0.46, 4 x 64 0.65, 4 x 128 0.447: the x + mask stages want twice the bytes in flight of the plain softmax)
+    if (const int o = knobs().softmax_pipe_c) C = o;  // tuning knob
     while (C < 8 && (nchunk + C - 1) / C > 512) C <<= 1;
     int threads = (int)((nchunk + C - 1) / C);
     threads = (threads + 31) / 32 * 32;
@@ -229,14 +233,16 @@ int softmax_mask_typed(const T* x, const MT* mask, T* y, int64_t batch, int64_t 
       int per_sm = 0, stages = 0;
       size_t smem = 0;
       int want = 768 / threads;
-      want = want < 2 ? 2 : (want > 6 ? 6 : want);
-      const int by_bytes = (int)(((TRI ? 64 : 96) * 1024) / (2 * stage_bytes));  // ~64 KB (x only) / ~96 KB (x + mask) in flight per SM
+      want = want < 2 ? 2 : (want > 8 ? 8 : want);
+      const int kb = knobs().pipe_inflight_kb >= 8 ? knobs().pipe_inflight_kb : (TRI ? 64 : 128);
+      const int by_bytes = (int)(((size_t)kb * 1024) / (2 * stage_bytes));  // ~64 KB (x only) / ~128 KB (x + mask) in flight per SM
       if (want > by_bytes) want = by_bytes < 1 ? 1 : by_bytes;
       FuncAttrHold hold;  // released when this lambda returns, i.e. after the launch
       if (!pipe_geometry(kern, threads, stage_bytes, want, 3, &per_sm, &stages, &smem, &hold)) return -1;
       int64_t grid = (int64_t)per_sm * sm_count();
       int contiguous = 0;
-      int rows_each = knobs().pipe_rows_per_cta >= 1 ? knobs().pipe_rows_per_cta : 4;
+      // rows per short-lived CTA: 4 (mask) / 16 (triangle: 0.379 -> 0.355 ms on bf16 [4,32,2048,2048]; 2 rows 0.408)
+      int rows_each = knobs().pipe_rows_per_cta >= 1 ? knobs().pipe_rows_per_cta : (TRI ? 16 : 4);
       if (threads <= 64 || knobs().pipe_rows_per_cta >= 1) {  // short-lived CTAs for narrow rows (softmax.cu), each a contiguous slab
         grid = std::max<int64_t>(grid, rows / rows_each);
         contiguous = 1;

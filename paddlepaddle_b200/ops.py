@@ -58,7 +58,13 @@ def _require_cuda(*tensors):
             raise RuntimeError("paddlepaddle_b200 has no CPU kernels: tensors must live on a CUDA device")
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def _stream():
+    """The current CUDA stream of the current device as a void* (dev_ctx.stream() in the reference)."""
+    if _raw_stream is not None:  # one C call instead of building a torch.cuda.Stream object per launch
+        return ctypes.c_void_p(_raw_stream(torch.cuda.current_device()))
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 

@@ -40,6 +40,22 @@ elif case in ("softmax_mask_bf16", "softmax_tri_bf16"):
     x = (torch.randn((4, 32, 2048, 2048), device="cuda", generator=g) * 2).to(torch.bfloat16)
     mk = torch.randn((4, 1, 2048, 2048), device="cuda", generator=g).to(torch.bfloat16)
     fn = (lambda: F.softmax_mask_fuse(x, mk)) if case == "softmax_mask_bf16" else (lambda: F.softmax_mask_fuse_upper_triangle(x))
+elif case == "mulgrad_bf16":
+    x = torch.randn((64, 2048, 4096), device="cuda", generator=g).to(torch.bfloat16)
+    y = torch.randn((4096,), device="cuda", generator=g).to(torch.bfloat16)
+    d = torch.randn((64, 2048, 4096), device="cuda", generator=g).to(torch.bfloat16)
+    fn = lambda: paddle.multiply_grad(x, y, d)
+elif case == "ew_general_bf16":
+    x = torch.randn((64, 2048, 1, 2048), device="cuda", generator=g).to(torch.bfloat16)
+    y = torch.randn((64, 1, 2, 2048), device="cuda", generator=g).to(torch.bfloat16)
+    fn = lambda: paddle.add(x, y)
+elif case == "ew_outer_bf16":
+    x = torch.randn((131072, 4096), device="cuda", generator=g).to(torch.bfloat16)
+    y = torch.randn((131072, 1), device="cuda", generator=g).to(torch.bfloat16)
+    fn = lambda: paddle.add(x, y)
+elif case == "softmax_cols_bf16":
+    x = (torch.randn((64, 2048, 4096), device="cuda", generator=g) * 2).to(torch.bfloat16)
+    fn = lambda: F.softmax(x, axis=1)
 elif case == "softmax_long_bf16":
     x = (torch.randn((64, 1048576), device="cuda", generator=g) * 2).to(torch.bfloat16)  # 2 MB rows, few of them
     fn = lambda: F.softmax(x, axis=-1)

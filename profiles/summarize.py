@@ -1,5 +1,6 @@
-"""Turn gpurun_out/*.ncu-rep (ncu --set full captures) into the text summaries committed here.
-usage: python profiles/summarize.py gpurun_out/r1_add_bf16.ncu-rep [...]   -> profiles/<name>.txt"""
+"""Turn gpurun_out/*.ncu-rep (ncu --set full captures) — or the raw metric page already exported on the GPU box as
+<name>.raw.csv (`ncu -i x.ncu-rep --page raw --csv`) — into the text summaries committed here.
+usage: python profiles/summarize.py gpurun_out/r1_add_bf16.ncu-rep gpurun_out/r2_x.raw.csv [...]   -> profiles/<name>.txt"""
 import csv
 import io
 import os
@@ -37,10 +38,14 @@ WANT = [
 
 here = os.path.dirname(os.path.abspath(__file__))
 for rep in sys.argv[1:]:
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    if rep.endswith(".csv"):
+        raw = open(rep).read()
+        name = os.path.basename(rep)[:-len(".raw.csv")] if rep.endswith(".raw.csv") else os.path.splitext(os.path.basename(rep))[0]
+    else:
+        raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+        name = os.path.splitext(os.path.basename(rep))[0]
     rows = list(csv.reader(io.StringIO(raw)))
     hdr, units = rows[0], rows[1]
-    name = os.path.splitext(os.path.basename(rep))[0]
     with open(os.path.join(here, name + ".txt"), "w") as f:
         f.write(f"# ncu --set full --clock-control none, from {os.path.basename(rep)} (one launch per block below)\n")
         for vals in rows[2:]:
