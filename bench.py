@@ -45,7 +45,7 @@ METRIC = "broadcast add HBM GB/s (algorithmic bytes / time)"
 WORKLOAD = "paddle.add bf16 [64,2048,4096] + [4096] (BASELINE configs[1])"
 
 
-def measured_traffic(name="r1h_add_bf16.txt"):
+def measured_traffic(name="r2_add_bf16.txt"):
     """DRAM bytes per launch of the headline kernel from the committed ncu --set full capture
     (profiles/<name>: dram__bytes_read.sum + dram__bytes_write.sum); None if the file is missing."""
     p = os.path.join(ROOT, "profiles", name)
@@ -719,7 +719,7 @@ def run_gpu_arm(args):
                        "timing": "every per_config row: barrier, CUDA events on the launching stream, MAX over ranks"},
             "roofline": {"bound": "hbm", "kernel": "ew_inner_kernel<bf16,AddOp>", "achieved": round(achieved, 1), "peak": peak,
                          "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": measured_traffic(),
-                         "traffic_source": "profiles/r1h_add_bf16.txt (ncu --set full, one launch)", "peak_source": peak_src,
+                         "traffic_source": "profiles/r2_add_bf16.txt (ncu --set full, one launch)", "peak_source": peak_src,
                          "kernel_ms": round(kern_ms, 4),
                          "note": "achieved/frac: per-launch event time (one launch, synchronised each side: includes the launch gap); "
                                  "achieved_back_to_back/frac_back_to_back: bytes / ms_per_step of the timed region",

@@ -285,6 +285,11 @@ PDB200_API size_t pdb200_argmax_workspace_bytes(const int64_t* x_dims, int x_ran
 PDB200_API int pdb200_argmax(const void* x, const int64_t* x_dims, int x_rank, int64_t axis, int flatten,
                   int x_dtype, int out_dtype, void* out, void* workspace, size_t workspace_bytes,
                   void* stream);
+/* argmin.  Replaces phi::ArgMinKernel<T, GPUContext> (paddle/phi/kernels/gpu/arg_min_max_kernel.cu:233-246, the same
+ * ArgCUDAKernel with cub::ArgMin).  Same arguments, rules and workspace query as pdb200_argmax; lowest index wins ties. */
+PDB200_API int pdb200_argmin(const void* x, const int64_t* x_dims, int x_rank, int64_t axis, int flatten,
+                  int x_dtype, int out_dtype, void* out, void* workspace, size_t workspace_bytes,
+                  void* stream);
 
 /* ---------------------------------------------------------------------------
  * softmax forward along `axis`.  Replaces phi::SoftmaxGPUDNNKernel / SoftmaxKernel<T, GPUContext>

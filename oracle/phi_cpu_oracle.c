@@ -417,6 +417,38 @@ int oracle_argmax(int dtype, const void* x, const int64_t* dims, int rank, int64
   return 0;
 }
 
+/* argmin.  phi::ArgMinKernel<T,CPUContext> -> ArgMinMaxFunctor<..., kArgMin> -> Eigen argmin(axis)
+ *   paddle/phi/kernels/cpu/arg_min_max_kernel.cc:68-98,175-196.  Eigen's ArgMinTupleReducer keeps the accumulator
+ *   unless t.second < accum.second (strict) and starts at (index 0, highest()): the FIRST minimal index wins, NaN
+ *   never wins, a row that never goes below highest() answers 0 (TensorFunctors.h:383-394). */
+int oracle_argmin(int dtype, const void* x, const int64_t* dims, int rank, int64_t axis, int flatten,
+                  int out_dtype, void* out) {
+  int64_t pre = 1, n = 1, post = 1, numel = 1;
+  for (int i = 0; i < rank; ++i) numel *= dims[i];
+  if (numel <= 0) return 1;
+  if (flatten || rank == 0) { n = numel; }
+  else {
+    if (axis < -rank || axis >= rank) return 1;
+    if (axis < 0) axis += rank;
+    for (int i = 0; i < rank; ++i) { if (i < axis) pre *= dims[i]; else if (i == axis) n = dims[i]; else post *= dims[i]; }
+  }
+  for (int64_t p = 0; p < pre; ++p)
+    for (int64_t q = 0; q < post; ++q) {
+      int64_t best = 0;
+      if (dtype == DT_INT64) {
+        const int64_t* X = (const int64_t*)x;
+        int64_t bv = INT64_MAX;
+        for (int64_t k = 0; k < n; ++k) { int64_t v = X[(p * n + k) * post + q]; if (v < bv) { bv = v; best = k; } }
+      } else {
+        double bv = dtype == DT_FLOAT64 ? 1.7976931348623157e308 : (dtype == DT_INT32 ? 2147483647.0 : (dtype == DT_INT16 ? 32767.0 : (dtype == DT_UINT8 ? 255.0 : (double)3.40282346638528859812e38f)));
+        for (int64_t k = 0; k < n; ++k) { double v = load_as_double(x, dtype, (p * n + k) * post + q); if (v < bv) { bv = v; best = k; } }
+      }
+      if (out_dtype == DT_INT32) ((int32_t*)out)[p * post + q] = (int32_t)best;
+      else ((int64_t*)out)[p * post + q] = best;
+    }
+  return 0;
+}
+
 /* ------------------------------------------------------------------------------------------
  * softmax.  phi::SoftmaxKernel<T,CPUContext> (paddle/phi/kernels/impl/softmax_kernel_impl.h:25-53):
  *   0-size -> no-op; 0-D -> 1; else x viewed as [n][d] with d = prod(dims[axis:]), axis_dim = dims[axis],

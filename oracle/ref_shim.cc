@@ -247,6 +247,26 @@ int phi_ref_argmax(int dtype, const void* x, const int64_t* dims, int rank, int6
   });
 }
 
+int phi_ref_argmin(int dtype, const void* x, const int64_t* dims, int rank, int64_t axis,
+                   int keepdims, int flatten, int out_dtype, const int64_t* out_dims,
+                   int out_rank, void* out) {
+  return Guard([&] {
+    auto xt = Wrap(x, dims, rank, dtype);
+    auto ot = Wrap(out, out_dims, out_rank, out_dtype);
+    phi::Scalar ax(axis);
+    auto& ctx = GetCtx().ctx;
+    switch (dtype) {
+      case kFloat32: phi::ArgMinKernel<float, phi::CPUContext>(ctx, xt, ax, keepdims, flatten, ToPhi(out_dtype), &ot); break;
+      case kFloat64: phi::ArgMinKernel<double, phi::CPUContext>(ctx, xt, ax, keepdims, flatten, ToPhi(out_dtype), &ot); break;
+      case kInt32: phi::ArgMinKernel<int32_t, phi::CPUContext>(ctx, xt, ax, keepdims, flatten, ToPhi(out_dtype), &ot); break;
+      case kInt64: phi::ArgMinKernel<int64_t, phi::CPUContext>(ctx, xt, ax, keepdims, flatten, ToPhi(out_dtype), &ot); break;
+      case kInt16: phi::ArgMinKernel<int16_t, phi::CPUContext>(ctx, xt, ax, keepdims, flatten, ToPhi(out_dtype), &ot); break;
+      case kUInt8: phi::ArgMinKernel<uint8_t, phi::CPUContext>(ctx, xt, ax, keepdims, flatten, ToPhi(out_dtype), &ot); break;
+      default: throw std::runtime_error("phi_ref_argmin: dtype not registered on CPU");
+    }
+  });
+}
+
 // op: 0 add, 1 multiply, 2 subtract, 3 divide, 4 maximum, 5 minimum.
 int phi_ref_elementwise(int op, int dtype, const void* x, const int64_t* xdims, int xrank,
                         const void* y, const int64_t* ydims, int yrank, const int64_t* odims,

@@ -68,6 +68,7 @@ SIGNATURES = {
     "pdb200_sum_axis0_static": (_int, [_vp, ctypes.c_int64, ctypes.c_int64, _int, _int, _vp, _vp]),
     "pdb200_argmax_workspace_bytes": (_sz, [_c_i64p, _int, ctypes.c_int64, _int, _int]),
     "pdb200_argmax": (_int, [_vp, _c_i64p, _int, ctypes.c_int64, _int, _int, _int, _vp, _vp, _sz, _vp]),
+    "pdb200_argmin": (_int, [_vp, _c_i64p, _int, ctypes.c_int64, _int, _int, _int, _vp, _vp, _sz, _vp]),
     "pdb200_softmax": (_int, [_vp, _c_i64p, _int, _int, _int, _vp, _vp]),
     "pdb200_log_softmax": (_int, [_vp, _c_i64p, _int, _int, _int, _vp, _vp]),
     "pdb200_fused_softmax_mask": (_int, [_vp, _c_i64p, _vp, _c_i64p, _int, _int, _vp, _vp]),

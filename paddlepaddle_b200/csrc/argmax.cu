@@ -10,11 +10,11 @@
 
 namespace pdb200 {
 
-template <typename T, typename O>
+template <typename T, typename O, bool MIN>
 int argmax_run(const ReducePlan& plan, const void* x, void* out, void* ws, size_t ws_bytes,
                cudaStream_t st) {
   using V = typename AccType<T>::type;  // compare bf16/fp16 as float: exact and order-preserving
-  using Op = ArgMaxOp<V>;
+  using Op = ArgMaxOp<V, MIN>;
   return run_reduce<T, O, Op>(plan, static_cast<const T*>(x), static_cast<O*>(out), IndexFin<V, O>(), ws,
                               ws_bytes, st);
 }
@@ -59,11 +59,40 @@ inline int argmax_plan(const int64_t* dims, int rank, int64_t axis, int flatten,
 
 }  // namespace pdb200
 
-extern "C" {
-
 #define PDB_ARG_TYPES(M) \
   M(PDB200_FLOAT32) M(PDB200_FLOAT64) M(PDB200_INT32) M(PDB200_INT64) M(PDB200_INT16) M(PDB200_UINT8) \
   M(PDB200_BFLOAT16) M(PDB200_FLOAT16)
+
+namespace {
+template <bool MIN>
+int arg_entry(const void* x, const int64_t* x_dims, int x_rank, int64_t axis, int flatten, int x_dtype, int out_dtype,
+              void* out, void* workspace, size_t workspace_bytes, void* stream) {
+  using namespace pdb200;
+  ReducePlan plan;
+  int rc = argmax_plan(x_dims, x_rank, axis, flatten, &plan);
+  if (rc != PDB200_OK) return rc;
+  PDB_CHECK_ARG(x && out, "argmax: NULL tensor pointer");
+  // arg_min_max_kernel.cu:221-230: the index dtype is int64 (default) or int32
+  PDB_CHECK_ARG(out_dtype == PDB200_INT64 || out_dtype == PDB200_INT32,
+                "The attribute of dtype in argmin/argmax must be [int32] or [int64], but received code " +
+                    std::to_string(out_dtype));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+#define PDB_RUN(DT)                                                                              \
+  case DT: {                                                                                     \
+    using T = typename CType<DT>::type;                                                          \
+    if (out_dtype == PDB200_INT64) return argmax_run<T, int64_t, MIN>(plan, x, out, workspace, workspace_bytes, st); \
+    return argmax_run<T, int32_t, MIN>(plan, x, out, workspace, workspace_bytes, st);            \
+  }
+  switch (x_dtype) {
+    PDB_ARG_TYPES(PDB_RUN)
+    default:
+      return fail(PDB200_UNSUPPORTED, std::string(MIN ? "argmin" : "argmax") + ": unsupported dtype code " + std::to_string(x_dtype));
+  }
+#undef PDB_RUN
+}
+}  // namespace
+
+extern "C" {
 
 size_t pdb200_argmax_workspace_bytes(const int64_t* x_dims, int x_rank, int64_t axis, int flatten,
                                      int x_dtype) {
@@ -81,28 +110,13 @@ size_t pdb200_argmax_workspace_bytes(const int64_t* x_dims, int x_rank, int64_t 
 int pdb200_argmax(const void* x, const int64_t* x_dims, int x_rank, int64_t axis, int flatten,
                   int x_dtype, int out_dtype, void* out, void* workspace, size_t workspace_bytes,
                   void* stream) {
-  using namespace pdb200;
-  ReducePlan plan;
-  int rc = argmax_plan(x_dims, x_rank, axis, flatten, &plan);
-  if (rc != PDB200_OK) return rc;
-  PDB_CHECK_ARG(x && out, "argmax: NULL tensor pointer");
-  // arg_min_max_kernel.cu:221-230: the index dtype is int64 (default) or int32
-  PDB_CHECK_ARG(out_dtype == PDB200_INT64 || out_dtype == PDB200_INT32,
-                "The attribute of dtype in argmin/argmax must be [int32] or [int64], but received code " +
-                    std::to_string(out_dtype));
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-#define PDB_RUN(DT)                                                                              \
-  case DT: {                                                                                     \
-    using T = typename CType<DT>::type;                                                          \
-    if (out_dtype == PDB200_INT64) return argmax_run<T, int64_t>(plan, x, out, workspace, workspace_bytes, st); \
-    return argmax_run<T, int32_t>(plan, x, out, workspace, workspace_bytes, st);                 \
-  }
-  switch (x_dtype) {
-    PDB_ARG_TYPES(PDB_RUN)
-    default:
-      return fail(PDB200_UNSUPPORTED, "argmax: unsupported dtype code " + std::to_string(x_dtype));
-  }
-#undef PDB_RUN
+  return arg_entry<false>(x, x_dims, x_rank, axis, flatten, x_dtype, out_dtype, out, workspace, workspace_bytes, stream);
+}
+
+int pdb200_argmin(const void* x, const int64_t* x_dims, int x_rank, int64_t axis, int flatten,
+                  int x_dtype, int out_dtype, void* out, void* workspace, size_t workspace_bytes,
+                  void* stream) {
+  return arg_entry<true>(x, x_dims, x_rank, axis, flatten, x_dtype, out_dtype, out, workspace, workspace_bytes, stream);
 }
 
 }  // extern "C"

@@ -64,6 +64,7 @@ struct Knobs {
   long long mulgrad_splits;
   bool no_tma_cols, no_interleave, no_fused_mulgrad, no_cluster_pipe;
   long long peer_timeout_ms;
+  long long rows_warp_max_bytes;
 };
 inline const Knobs& knobs() {
   static const Knobs k = [] {
@@ -93,6 +94,7 @@ inline const Knobs& knobs() {
     r.no_fused_mulgrad = set("PDB200_NO_FUSED_MULGRAD");
     r.no_cluster_pipe = set("PDB200_NO_CLUSTER_PIPE");
     r.peer_timeout_ms = num("PDB200_PEER_TIMEOUT_MS");
+    r.rows_warp_max_bytes = num("PDB200_ROWS_WARP_MAX_BYTES");
     return r;
   }();
   return k;

@@ -101,14 +101,25 @@ struct alignas(16) KV {
 };
 // Lowest index wins ties — Eigen's ArgMaxTupleReducer uses strict '>' (TensorFunctors.h:370-381)
 // and so does CUB's ArgMax; combine() is order-independent because it compares indices too.
-template <typename V>
+// MIN = true turns the same machinery into argmin: every value is mapped through an exactly order-REVERSING bijection
+// first (floating point: negation; integers: bitwise NOT, which has no overflow corner) and the maximum of the mapped
+// values is sought.  Ties, NaN (never wins a strict comparison) and rows on which nothing beats the start value
+// (index 0) then behave as Eigen's ArgMinTupleReducer does (strict '<', TensorFunctors.h:383-394).
+template <bool MIN, typename V>
+__device__ __forceinline__ V arg_xform(V v) {
+  if constexpr (!MIN) return v;
+  else if constexpr (std::is_floating_point<V>::value) return -v;
+  else return (V)~v;
+}
+template <typename V, bool MIN = false>
 struct ArgMaxOp {
   using Acc = KV<V>;
+  static constexpr bool kMin = MIN;
   static __host__ __device__ __forceinline__ Acc identity() {
     return Acc{std::numeric_limits<V>::lowest(), std::numeric_limits<int64_t>::max()};
   }
   template <typename T>
-  static __device__ __forceinline__ Acc lift(T v, int64_t r) { return Acc{cvt<V>(v), r}; }
+  static __device__ __forceinline__ Acc lift(T v, int64_t r) { return Acc{arg_xform<MIN>(cvt<V>(v)), r}; }
   static __device__ __forceinline__ Acc lift(Acc v, int64_t) { return v; }
   static __device__ __forceinline__ Acc combine(Acc a, Acc b) {
     return (b.val > a.val || (b.val == a.val && b.idx < a.idx)) ? b : a;
@@ -122,11 +133,9 @@ template <typename Op, typename T>
 __device__ __forceinline__ void accumulate(typename Op::Acc& a, T v, int64_t idx) {
   a = Op::combine(a, Op::template lift<T>(v, idx));
 }
-template <typename V>
-struct ArgMaxOp;
-template <typename V, typename T>
+template <bool MIN, typename V, typename T>
 __device__ __forceinline__ void accumulate_argmax(KV<V>& a, T v, int64_t idx) {
-  const V x = cvt<V>(v);
+  const V x = arg_xform<MIN>(cvt<V>(v));
   if (x > a.val) {
     a.val = x;
     a.idx = idx;
@@ -153,7 +162,7 @@ struct IndexFin {
 };
 
 template <typename V> struct IsArgMax { static constexpr bool value = false; };
-template <typename V> struct IsArgMax<ArgMaxOp<V>> { static constexpr bool value = true; };
+template <typename V, bool MIN> struct IsArgMax<ArgMaxOp<V, MIN>> { static constexpr bool value = true; };
 
 template <typename Op, typename T>
 __device__ __forceinline__ void acc_step(typename Op::Acc& a, T v, int64_t idx) {
@@ -161,7 +170,7 @@ __device__ __forceinline__ void acc_step(typename Op::Acc& a, T v, int64_t idx) 
     if constexpr (std::is_same<T, typename Op::Acc>::value) {
       a = Op::combine(a, v);  // folding partial (value, index) pairs: indices are not ordered
     } else {
-      accumulate_argmax(a, v, idx);
+      accumulate_argmax<Op::kMin>(a, v, idx);
     }
   } else {
     accumulate<Op, T>(a, v, idx);
@@ -204,8 +213,9 @@ __device__ __forceinline__ typename Op::Acc fold_span_argmax16(const T* __restri
   }
   auto visit = [&](int u, const Vec<T>& v, int64_t i) {
     const T2* p = reinterpret_cast<const T2*>(&v);
-    const T2 m = __hmax2(__hmax2(p[0], p[1]), __hmax2(p[2], p[3]));
-    const float f = fmaxf(cvt<float>(m.x), cvt<float>(m.y));
+    // argmin: packed minimum, then negated — the running value lives in the mapped (negated) domain
+    const T2 m = Op::kMin ? __hmin2(__hmin2(p[0], p[1]), __hmin2(p[2], p[3])) : __hmax2(__hmax2(p[0], p[1]), __hmax2(p[2], p[3]));
+    const float f = Op::kMin ? -fminf(cvt<float>(m.x), cvt<float>(m.y)) : fmaxf(cvt<float>(m.x), cvt<float>(m.y));
     if (f > run[u]) {
       run[u] = f;
       best[u] = v;
@@ -231,7 +241,7 @@ __device__ __forceinline__ typename Op::Acc fold_span_argmax16(const T* __restri
       int k_first = 0;
 #pragma unroll
       for (int k = V - 1; k >= 0; --k)
-        if (cvt<float>(best[u].v[k]) == run[u]) k_first = k;
+        if (arg_xform<Op::kMin>(cvt<float>(best[u].v[k])) == run[u]) k_first = k;
       acc[u] = A{run[u], at[u] + k_first};
     }
   }
@@ -453,14 +463,19 @@ inline int pow2_ceil(int64_t v, int cap) {
 }
 
 // elem_bytes: sizeof(T) of the pass input; V: vector width in elements (1 when unaligned).
-inline PassGeom plan_pass(const ReducePass& ps, size_t elem_bytes, int V) {
+// acc_bytes: sizeof the accumulator (16 for argmax's (value, index) pairs).
+inline PassGeom plan_pass(const ReducePass& ps, size_t elem_bytes, int V, size_t acc_bytes = 8) {
   PassGeom g{};
   const int sms = sm_count();
   const int64_t target_ctas = (int64_t)sms * 4;
   if (ps.inner == 1) {
     const int64_t row_bytes = ps.red * (int64_t)elem_bytes;
     const bool many_rows = ps.outer >= target_ctas;
-    if (row_bytes <= 16384 && (many_rows || row_bytes <= 2048)) {
+    // rows up to 16 KB go to the warp kernel; (value, index) accumulators up to 64 KB: folding 16-byte pairs across a CTA
+    // through shared memory costs more than the longer per-lane loop (argmax fp32 [65536,8192]: 0.357 -> 0.295 ms, 7.3 TB/s;
+    // sum / max of the same rows are equal or slightly better in the block kernel: profiles/r2_notes.txt)
+    const int64_t warp_max = knobs().rows_warp_max_bytes > 0 ? knobs().rows_warp_max_bytes : (acc_bytes >= 16 ? 65536 : 16384);
+    if (row_bytes <= warp_max && (many_rows || row_bytes <= 2048)) {
       g.kind = 0;
       // aim for >= 4 vectors per lane so kRedUnroll loads are in flight
       g.G = pow2_ceil((ps.red / V + 3) / 4, 32);
@@ -602,7 +617,7 @@ inline std::vector<Stage> build_stages(const ReducePlan& plan, bool in_aligned) 
     const size_t eb = first ? sizeof(T) : sizeof(A);
     const int Vfull = (int)(16 / eb);
     bool vec = (first ? in_aligned : true) && ((ps.inner == 1 ? ps.red : ps.inner) % Vfull == 0);
-    Stage s{ps, plan_pass(ps, eb, vec ? Vfull : 1), vec};
+    Stage s{ps, plan_pass(ps, eb, vec ? Vfull : 1, sizeof(A)), vec};
     st.push_back(s);
     if (s.g.splits > 1) {
       ReducePass fold{ps.outer, s.g.splits, ps.inner};

@@ -281,11 +281,12 @@ def layer_norm(x, normalized_shape, weight=None, bias=None, epsilon=1e-05, name=
     stat_dt = torch.float64 if x.dtype == torch.float64 else torch.float32
     y = torch.empty_like(x)
     stats = torch.empty((2, rows), dtype=stat_dt, device=x.device)  # mean and variance: one allocation
-    mean, var = stats[0], stats[1]
+    p_mean = stats.data_ptr()
+    p_var = p_mean + rows * stats.element_size()  # views are only built when the caller wants them (2 us each)
     L.check(lib.pdb200_layer_norm(_ptr(x), d, r, _ptr(weight), _ptr(bias), pcode, ctypes.c_float(float(epsilon)),
-                                  begin_norm_axis, xcode, _ptr(y), _ptr(mean), _ptr(var), _stream()), lib)
+                                  begin_norm_axis, xcode, _ptr(y), ctypes.c_void_p(p_mean), ctypes.c_void_p(p_var), _stream()), lib)
     if return_stats:
-        return y, mean, var
+        return y, stats[0], stats[1]
     return y
 
 

@@ -475,9 +475,7 @@ def prod(x, axis=None, keepdim=False, dtype=None, name=None):
     return _reduce(L.REDUCE_PROD, x, axis, keepdim, x.dtype)
 
 
-def argmax(x, axis=None, keepdim=False, dtype="int64", name=None):
-    """paddle.argmax: axis=None flattens; lowest index wins ties; dtype int64 or int32
-    (ArgMinMaxInferMeta, infermeta/unary.cc:257)."""
+def _arg(fn_name, x, axis, keepdim, dtype):
     _require_cuda(x)
     lib = L.load()
     x = x.contiguous()
@@ -502,6 +500,17 @@ def argmax(x, axis=None, keepdim=False, dtype="int64", name=None):
     xc = _dtype_code(x.dtype)
     nbytes = lib.pdb200_argmax_workspace_bytes(xd, xr, ax, int(flatten), xc)
     ws = _workspace(nbytes, x.device)
-    L.check(lib.pdb200_argmax(_ptr(x), xd, xr, ax, int(flatten), xc, _dtype_code(odt), _ptr(out), _ptr(ws),
-                              nbytes, _stream()), lib)
+    L.check(getattr(lib, fn_name)(_ptr(x), xd, xr, ax, int(flatten), xc, _dtype_code(odt), _ptr(out), _ptr(ws),
+                                  nbytes, _stream()), lib)
     return out
+
+
+def argmax(x, axis=None, keepdim=False, dtype="int64", name=None):
+    """paddle.argmax: axis=None flattens; lowest index wins ties; dtype int64 or int32
+    (ArgMinMaxInferMeta, infermeta/unary.cc:257)."""
+    return _arg("pdb200_argmax", x, axis, keepdim, dtype)
+
+
+def argmin(x, axis=None, keepdim=False, dtype="int64", name=None):
+    """paddle.argmin (python/paddle/tensor/search.py:283): the same rules with the minimum."""
+    return _arg("pdb200_argmin", x, axis, keepdim, dtype)

@@ -361,6 +361,21 @@ void ArgMaxKernel(const Context& ctx, const DenseTensor& x, const phi::Scalar& a
                       Code(dtype), o, ws, bytes, ctx.stream()));
 }
 
+// argmin: the same signature and engine (gpu/arg_min_max_kernel.cu:233-246)
+template <typename T, typename Context>
+void ArgMinKernel(const Context& ctx, const DenseTensor& x, const phi::Scalar& axis, bool keepdims, bool flatten,
+                  DataType dtype, DenseTensor* out) {
+  if (dtype == DataType::UNDEFINED) dtype = DataType::INT64;
+  void* o = ctx.Alloc(out, dtype);
+  auto xd = Dims(x);
+  const int64_t ax = axis.to<int64_t>();
+  const size_t bytes = pdb200_argmax_workspace_bytes(xd.data(), static_cast<int>(xd.size()), ax, flatten, Code(x.dtype()));
+  DenseTensor holder;
+  void* ws = Scratch(ctx, bytes, &holder);
+  Check(pdb200_argmin(x.data(), xd.data(), static_cast<int>(xd.size()), ax, flatten, Code(x.dtype()), Code(dtype), o, ws, bytes,
+                      ctx.stream()));
+}
+
 // ---- softmax -----------------------------------------------------------------------------
 template <typename T, typename Context>
 void CrossEntropyWithSoftmaxKernel(const Context& ctx, const DenseTensor& logits, const DenseTensor& label, bool soft_label,
@@ -643,6 +658,10 @@ PD_REGISTER_KERNEL(prod, GPU, ALL_LAYOUT, pdb200_phi::ProdKernel, float, double,
 PD_REGISTER_KERNEL(argmax, GPU, ALL_LAYOUT, pdb200_phi::ArgMaxKernel, phi::dtype::float16, phi::dtype::bfloat16,
                    float, double, int32_t, int64_t, int16_t, uint8_t) {
   kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);  // gpu/arg_min_max_kernel.cu:286-288
+}
+PD_REGISTER_KERNEL(argmin, GPU, ALL_LAYOUT, pdb200_phi::ArgMinKernel, phi::dtype::float16, phi::dtype::bfloat16,
+                   float, double, int32_t, int64_t, int16_t, uint8_t) {
+  kernel->OutputAt(0).SetDataType(phi::DataType::UNDEFINED);  // gpu/arg_min_max_kernel.cu:272-284
 }
 // softmax is selected under the GPUDNN key first (kernel_factory.cc:304-314): own both keys.
 PD_REGISTER_KERNEL(softmax, GPUDNN, ALL_LAYOUT, pdb200_phi::SoftmaxGPUDNNKernel, float, double, phi::dtype::float16,

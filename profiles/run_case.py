@@ -56,6 +56,11 @@ elif case == "ew_outer_bf16":
 elif case == "softmax_cols_bf16":
     x = (torch.randn((64, 2048, 4096), device="cuda", generator=g) * 2).to(torch.bfloat16)
     fn = lambda: F.softmax(x, axis=1)
+elif case in ("argmax_fp32", "sum_rows_fp32", "max_rows_bf16"):
+    dt = torch.bfloat16 if case.endswith("bf16") else torch.float32
+    x = torch.randn((65536, 8192), device="cuda", generator=g).to(dt)
+    fn = {"argmax_fp32": lambda: paddle.argmax(x, axis=-1), "sum_rows_fp32": lambda: paddle.sum(x, axis=-1),
+          "max_rows_bf16": lambda: paddle.max(x, axis=-1)}[case]
 elif case == "softmax_long_bf16":
     x = (torch.randn((64, 1048576), device="cuda", generator=g) * 2).to(torch.bfloat16)  # 2 MB rows, few of them
     fn = lambda: F.softmax(x, axis=-1)

@@ -127,7 +127,10 @@ class Oracle:
         self._check(rc)
         return out
 
-    def argmax(self, x, axis=None, keepdim=False, dtype=np.int64, code=None):
+    def argmin(self, x, axis=None, keepdim=False, dtype=np.int64, code=None):
+        return self.argmax(x, axis, keepdim, dtype, code, _fn="argmin")
+
+    def argmax(self, x, axis=None, keepdim=False, dtype=np.int64, code=None, _fn="argmax"):
         x = np.ascontiguousarray(x)
         code = NP2CODE[x.dtype] if code is None else code
         flatten = axis is None
@@ -143,11 +146,11 @@ class Oracle:
         ocode = NP2CODE[np.dtype(dtype)]
         ax = 0 if flatten else int(axis)
         if self.kind == "port":
-            rc = self.lib.oracle_argmax(code, _vp(x), xd, xr, ctypes.c_int64(ax), int(flatten), ocode, _vp(out))
+            rc = getattr(self.lib, "oracle_" + _fn)(code, _vp(x), xd, xr, ctypes.c_int64(ax), int(flatten), ocode, _vp(out))
         else:
             od, orank = _dims(oshape)
-            rc = self.lib.phi_ref_argmax(code, _vp(x), xd, xr, ctypes.c_int64(ax), int(keepdim), int(flatten),
-                                         ocode, od, orank, _vp(out))
+            rc = getattr(self.lib, "phi_ref_" + _fn)(code, _vp(x), xd, xr, ctypes.c_int64(ax), int(keepdim), int(flatten),
+                                                     ocode, od, orank, _vp(out))
         self._check(rc)
         return out
 

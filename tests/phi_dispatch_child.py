@@ -204,6 +204,8 @@ def case_reductions():
     for x, axis, flatten in ((xf, 1, 0), (xb, 0, 0), (xi, 0, 1)):
         want = paddle.argmax(x, axis=None if flatten else axis)
         check(f"argmax/{x.dtype}", run("argmax", "argmax", [x], [want], iv=[axis, 0, flatten, PHI[torch.int64]]), want)
+    want = paddle.argmin(xf, axis=1)
+    check("argmin", run("argmin", "argmax", [xf], [want], iv=[1, 0, 0, PHI[torch.int64]]), want)
     want = paddle.argmax(xf, axis=1, dtype="int32")
     check("argmax int32 out", run("argmax", "argmax", [xf], [want], iv=[1, 0, 0, PHI[torch.int32]]), want)
 
@@ -273,7 +275,7 @@ NAMES = ["add", "multiply", "subtract", "divide", "maximum", "minimum", "less_th
          "equal", "not_equal", "logical_and", "logical_or", "logical_xor", "logical_not", "bitwise_and", "bitwise_or", "bitwise_xor",
          "bitwise_not", "bitwise_left_shift", "bitwise_right_shift", "scale", "cast", "where", "add_grad", "multiply_grad", "sum_grad",
          "mean_grad", "cross_entropy_with_softmax", "rms_norm", "log_softmax", "sum_raw", "sum", "mean_raw", "mean", "max_raw", "max",
-         "min_raw", "min", "prod", "argmax", "softmax", "layer_norm", "softmax_grad", "layer_norm_grad", "fused_softmax_mask",
+         "min_raw", "min", "prod", "argmax", "argmin", "softmax", "layer_norm", "softmax_grad", "layer_norm_grad", "fused_softmax_mask",
          "fused_softmax_mask_upper_triangle", "fused_bias_dropout_residual_layer_norm"]
 print(json.dumps({"calls": n_calls, "alloc_calls": reg.phi_min_alloc_calls(), "failed": failed,
                   "names_not_called": sorted(set(NAMES) - called)}))

@@ -230,3 +230,34 @@ def test_softmax_strided_axis_special_values(port, shape, dt):
     if dt == "float32":
         lg = to_np(F.log_softmax(to_dev(x), axis=1))
         np.testing.assert_allclose(lg[mask], port.log_softmax(x, 1)[mask], rtol=1e-5, atol=1e-5)
+
+
+def test_ref_argmin(ref, port):
+    """argmin on the argmax engine (values mapped through an order-reversing bijection): every route, ties, special values."""
+    r = _rng(13)
+    x = r.integers(0, 50, (257, 4096), dtype=np.int64)  # many ties: lowest index must win
+    for axis in (None, 0, 1, -1):
+        assert np.array_equal(to_np(paddle.argmin(to_dev(x), axis=axis)), ref.argmin(x, axis)), axis
+    xi = r.integers(-2**31, 2**31, (300, 5000), dtype=np.int32)
+    xi[5, 7] = -2**31  # the value whose negation overflows: the mapping is bitwise NOT, not negation
+    for axis in (0, 1):
+        assert np.array_equal(to_np(paddle.argmin(to_dev(xi), axis=axis)), ref.argmin(xi, axis)), ("int32", axis)
+    xf = r.standard_normal((64, 70000)).astype(np.float32)
+    xf[1, 5] = np.nan
+    xf[2, :] = np.inf
+    xf[3, 100] = -np.inf
+    xf[4, :] = np.nan
+    assert np.array_equal(to_np(paddle.argmin(to_dev(xf), axis=1)), ref.argmin(xf, 1))
+    assert np.array_equal(to_np(paddle.argmin(to_dev(xf), axis=1, dtype="int32")), ref.argmin(xf, 1, dtype=np.int32))
+    for dt in (np.uint8, np.int16):
+        info = np.iinfo(dt)
+        big = r.integers(info.min, info.max, (3, 300, 4096), dtype=dt, endpoint=True)
+        for axis in (0, 1, 2):
+            assert np.array_equal(to_np(paddle.argmin(to_dev(big), axis=axis)), ref.argmin(big, axis)), (dt, axis)
+    # 16-bit floats: the CPU kernel is not registered; the restatement applies the same rule to their float values
+    for half, code, conv in (("bf16", O.BFLOAT16, port.f32_to_bf16), ("fp16", O.FLOAT16, port.f32_to_fp16)):
+        xh = conv(r.standard_normal((33, 40000)).astype(np.float32))
+        xh[0, :8] = conv(np.array([0.0, -0.0, 0.0, -0.0, 1, 1, 1, 1], np.float32))
+        for axis in (None, 0, 1):
+            assert np.array_equal(to_np(paddle.argmin(to_dev(xh, half), axis=axis)), port.argmin(xh, axis, code=code)), (half, axis)
+        assert np.array_equal(to_np(paddle.argmax(to_dev(xh, half), axis=1)), port.argmax(xh, 1, code=code))

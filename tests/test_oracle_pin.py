@@ -211,3 +211,21 @@ def test_live_argmax_nan_and_infinities(port, ref):
         x[6, 0] = np.nan
         for ax in (0, 1, None):
             assert np.array_equal(port.argmax(x, ax), ref.argmax(x, ax))
+
+
+def test_argmin_restatement_equals_compiled_reference(port, ref):
+    """argmin (added in round 2) has no golden file: the restatement is pinned to the compiled reference live, over the
+    dtypes the CPU kernel registers, every axis and the flattened form, with ties, NaN, +-inf and all-equal rows."""
+    rng = np.random.default_rng(21)
+    for dt in (np.float32, np.float64, np.int32, np.int64, np.int16, np.uint8):
+        x = rng.integers(0, 12, (6, 31, 5)).astype(dt)
+        if np.issubdtype(dt, np.floating):
+            x[0, 3, 1] = np.nan
+            x[1, :, 2] = np.inf
+            x[2, 0, 0] = -np.inf
+            x[3, :, 3] = np.nan
+        for axis in (None, 0, 1, 2, -1):
+            for keep in (False, True):
+                a, b = port.argmin(x, axis, keep), ref.argmin(x, axis, keep)
+                assert a.shape == b.shape and np.array_equal(a, b), (dt, axis, keep)
+        assert np.array_equal(port.argmin(x, 1, dtype=np.int32), ref.argmin(x, 1, dtype=np.int32))

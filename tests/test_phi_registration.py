@@ -62,6 +62,7 @@ EXPECT = {  # the registrations of plugin/phi_kernels.cc
     "min": "float32 float64 int32 int64 float16 bfloat16", "min_raw": "float32 float64 int32 int64 float16 bfloat16",
     "prod": "float32 float64 int32 int64 float16 bfloat16",
     "argmax": "float16 bfloat16 float32 float64 int32 int64 int16 uint8",
+    "argmin": "float16 bfloat16 float32 float64 int32 int64 int16 uint8",
     "rms_norm": "float32 float16 bfloat16",
     "log_softmax": "float32 float64 float16 bfloat16", "cross_entropy_with_softmax": "float32 float64 float16",
     "softmax": "float32 float64 float16 bfloat16", "layer_norm": "float32 float64 float16 bfloat16",
