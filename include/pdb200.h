@@ -451,6 +451,13 @@ PDB200_API void* pdb200_peer_slot(void* window, size_t slot_bytes, unsigned long
 PDB200_API int pdb200_peer_error(void* window);
 PDB200_API int pdb200_peer_all_reduce(int op, void* const* windows, int world, int rank, size_t slot_bytes,
                            unsigned long long epoch, int64_t n, int slot_dtype, int out_dtype, void* out, void* stream);
+/* Self-test of the exchange on ONE GPU: all `world` windows were created by this process on the current device; the same
+ * device code runs for every rank in one cooperative grid (blockIdx.y = rank), rank r's result goes to outs[r].  No
+ * counterpart in the reference; it exists because ranks that wait for one another must never be separate launches on
+ * one GPU.  op 0 (sum) / 1 (max); (slot, out) dtypes (FLOAT32, FLOAT32), (FLOAT32, BFLOAT16), (INT64, INT64). */
+PDB200_API int pdb200_peer_all_reduce_emulated(int op, void* const* windows, int world, size_t slot_bytes,
+                                    unsigned long long epoch, int64_t n, int slot_dtype, int out_dtype,
+                                    void* const* outs, void* stream);
 
 #ifdef __cplusplus
 }

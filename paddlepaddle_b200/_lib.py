@@ -59,6 +59,8 @@ SIGNATURES = {
     "pdb200_peer_error": (_int, [_vp]),
     "pdb200_peer_all_reduce": (_int, [_int, ctypes.POINTER(_vp), _int, _int, _sz, ctypes.c_uint64, ctypes.c_int64, _int, _int, _vp,
                                _vp]),
+    "pdb200_peer_all_reduce_emulated": (_int, [_int, ctypes.POINTER(_vp), _int, _sz, ctypes.c_uint64, ctypes.c_int64, _int, _int,
+                                        ctypes.POINTER(_vp), _vp]),
     "pdb200_reduce_workspace_bytes": (_sz, [_int, _c_i64p, _int, _c_i64p, _int, _int, _int, _int]),
     "pdb200_sum_raw": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _int, _vp, _vp, _sz, _vp]),
     "pdb200_mean_raw": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _int, _vp, _vp, _sz, _vp]),

@@ -141,9 +141,9 @@ __device__ __forceinline__ void peer_poison_out(T* out, int64_t n) {
 // n elements of S (the slot type) per rank in slot (epoch & 1); out[i] = T(op over ranks in rank order).
 // VEC: out is 16-byte aligned (the slots always are); otherwise every element goes through the scalar loop.
 template <typename S, typename T, int OP, bool VEC>
-__global__ void __launch_bounds__(256) peer_allreduce_kernel(PeerPtrs ptrs, int world, int rank, size_t slot_bytes,
-                                                             unsigned long long epoch, int64_t n, T* out,
-                                                             unsigned long long timeout_ns, int* host_err) {
+__device__ __forceinline__ void peer_allreduce_body(const PeerPtrs& ptrs, int world, int rank, size_t slot_bytes,
+                                                    unsigned long long epoch, int64_t n, T* out,
+                                                    unsigned long long timeout_ns, int* host_err) {
   __shared__ int timed_out;
   unsigned char* mine = ptrs.win[rank];
   if (threadIdx.x == 0) timed_out = 0;
@@ -189,9 +189,9 @@ __global__ void __launch_bounds__(256) peer_allreduce_kernel(PeerPtrs ptrs, int 
 // Requires n % Vec<S>::N == 0 handled by the caller through a ragged tail done one-shot style by CTA 0; `out` 16-byte
 // aligned.  Grid <= SM count (every CTA must be resident: CTAs wait for the grid's last CTA to publish).
 template <typename S, typename T, int OP>
-__global__ void __launch_bounds__(256, 2) peer_allreduce2_kernel(PeerPtrs ptrs, int world, int rank, size_t slot_bytes,
-                                                              unsigned long long epoch, int64_t n, T* out,
-                                                              unsigned long long timeout_ns, int* host_err) {
+__device__ __forceinline__ void peer_allreduce2_body(const PeerPtrs& ptrs, int world, int rank, size_t slot_bytes,
+                                                     unsigned long long epoch, int64_t n, T* out,
+                                                     unsigned long long timeout_ns, int* host_err) {
   __shared__ int timed_out;
   __shared__ int last_cta;
   unsigned char* mine = ptrs.win[rank];
@@ -302,6 +302,61 @@ __global__ void __launch_bounds__(256, 2) peer_allreduce2_kernel(PeerPtrs ptrs, 
   }
   if (blockIdx.x == 0)
     for (int64_t i = nv_out * VT + threadIdx.x; i < n; i += blockDim.x) out[i] = reinterpret_cast<const volatile T*>(res)[i];
+}
+
+template <typename S, typename T, int OP, bool VEC>
+__global__ void __launch_bounds__(256) peer_allreduce_kernel(PeerPtrs ptrs, int world, int rank, size_t slot_bytes,
+                                                             unsigned long long epoch, int64_t n, T* out,
+                                                             unsigned long long timeout_ns, int* host_err) {
+  peer_allreduce_body<S, T, OP, VEC>(ptrs, world, rank, slot_bytes, epoch, n, out, timeout_ns, host_err);
+}
+template <typename S, typename T, int OP>
+__global__ void __launch_bounds__(256, 2) peer_allreduce2_kernel(PeerPtrs ptrs, int world, int rank, size_t slot_bytes,
+                                                              unsigned long long epoch, int64_t n, T* out,
+                                                              unsigned long long timeout_ns, int* host_err) {
+  peer_allreduce2_body<S, T, OP>(ptrs, world, rank, slot_bytes, epoch, n, out, timeout_ns, host_err);
+}
+
+// ---- every rank of a group in ONE grid (self-test on a single GPU) --------------------------------------------
+// The exchange kernels of different ranks wait for one another, so they may only run as separate launches when every
+// rank has a GPU of its own.  For a box with fewer GPUs than ranks the same device code runs as ONE cooperative grid:
+// blockIdx.y is the rank, its window is ptrs.win[rank] (all windows live on this GPU), its output outs.p[rank].  A
+// cooperative launch guarantees that all ranks' CTAs are resident together, which is what the waits need.
+struct PeerOuts {
+  void* p[kPeerMaxWorld];
+};
+template <typename S, typename T, int OP, bool TWO_SHOT>
+__global__ void __launch_bounds__(256, 2) peer_allreduce_all_ranks_kernel(PeerPtrs ptrs, PeerOuts outs, int world,
+                                                                          size_t slot_bytes, unsigned long long epoch,
+                                                                          int64_t n, unsigned long long timeout_ns) {
+  const int rank = blockIdx.y;
+  T* out = static_cast<T*>(outs.p[rank]);
+  if constexpr (TWO_SHOT) peer_allreduce2_body<S, T, OP>(ptrs, world, rank, slot_bytes, epoch, n, out, timeout_ns, nullptr);
+  else peer_allreduce_body<S, T, OP, true>(ptrs, world, rank, slot_bytes, epoch, n, out, timeout_ns, nullptr);
+}
+
+template <typename S, typename T>
+int peer_launch_all_ranks(int op, const PeerPtrs& p, const PeerOuts& o, int world, size_t slot_bytes, unsigned long long epoch,
+                          int64_t n, unsigned long long timeout_ns, cudaStream_t st) {
+  if (op != kPeerSum && op != kPeerMax) return fail(PDB200_UNSUPPORTED, "peer_all_reduce_emulated: op must be sum (0) or max (1)");
+  const bool two_shot = world > 1 && (size_t)n * sizeof(S) > kPeerOneShotBytes;
+  const int64_t nvec = n / Vec<S>::N;
+  const int64_t chunk = (nvec + world - 1) / world;
+  int64_t blocks = two_shot ? (chunk + 255) / 256 : (nvec + 255) / 256;
+  // all ranks' CTAs must be resident together: at most 2 CTAs per SM in total
+  const int64_t cap = std::max<int64_t>(1, 2 * (int64_t)sm_count() / world);
+  blocks = std::max<int64_t>(1, std::min<int64_t>(blocks, cap));
+  PeerPtrs pp = p;
+  PeerOuts oo = o;
+  void* args[] = {&pp, &oo, &world, &slot_bytes, &epoch, &n, &timeout_ns};
+  const void* kern = nullptr;
+  if (op == kPeerSum) kern = two_shot ? (const void*)peer_allreduce_all_ranks_kernel<S, T, kPeerSum, true>
+                                      : (const void*)peer_allreduce_all_ranks_kernel<S, T, kPeerSum, false>;
+  else kern = two_shot ? (const void*)peer_allreduce_all_ranks_kernel<S, T, kPeerMax, true>
+                       : (const void*)peer_allreduce_all_ranks_kernel<S, T, kPeerMax, false>;
+  if (cudaLaunchCooperativeKernel(kern, dim3((unsigned)blocks, (unsigned)world), dim3(256), args, 0, st) != cudaSuccess)
+    return fail(PDB200_CUDA_ERROR, std::string("peer_all_reduce_emulated: ") + cudaGetErrorString(cudaGetLastError()));
+  return after_launch("peer_allreduce_all_ranks");
 }
 
 template <typename S, typename T>
@@ -476,6 +531,32 @@ int pdb200_peer_all_reduce(int op, void* const* windows, int world, int rank, si
 #undef M
   return fail(PDB200_UNSUPPORTED, "peer_all_reduce: (slot dtype " + std::to_string(slot_dtype) + ", out dtype " +
                                       std::to_string(out_dtype) + ") is not built");
+}
+
+int pdb200_peer_all_reduce_emulated(int op, void* const* windows, int world, size_t slot_bytes, unsigned long long epoch,
+                                    int64_t n, int slot_dtype, int out_dtype, void* const* outs, void* stream) {
+  using namespace pdb200;
+  PDB_CHECK_ARG(windows && outs, "peer_all_reduce_emulated: NULL argument");
+  PDB_CHECK_ARG(world >= 1 && world <= kPeerMaxWorld, "peer_all_reduce_emulated: bad world");
+  PDB_CHECK_ARG(epoch >= 1, "peer_all_reduce_emulated: epochs start at 1");
+  const size_t es = dtype_size(slot_dtype);
+  if (es == 0) return fail(PDB200_UNSUPPORTED, "peer_all_reduce_emulated: bad dtype code");
+  const size_t slot = (slot_bytes + 255) / 256 * 256;
+  if (n < 0 || (size_t)n * es > slot) return fail(PDB200_INVALID_ARGUMENT, "peer_all_reduce_emulated: n does not fit the slot");
+  PeerPtrs p;
+  PeerOuts o;
+  for (int r = 0; r < kPeerMaxWorld; ++r) {
+    p.win[r] = r < world ? static_cast<unsigned char*>(windows[r]) : nullptr;
+    o.p[r] = r < world ? outs[r] : nullptr;
+    if (r < world) PDB_CHECK_ARG(is_aligned16(outs[r]), "peer_all_reduce_emulated: outputs must be 16-byte aligned");
+  }
+  const long long ms = knobs().peer_timeout_ms > 0 ? knobs().peer_timeout_ms : 30000;
+  const unsigned long long timeout_ns = (unsigned long long)ms * 1000000ull;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (slot_dtype == PDB200_FLOAT32 && out_dtype == PDB200_FLOAT32) return peer_launch_all_ranks<float, float>(op, p, o, world, slot, epoch, n, timeout_ns, st);
+  if (slot_dtype == PDB200_FLOAT32 && out_dtype == PDB200_BFLOAT16) return peer_launch_all_ranks<float, __nv_bfloat16>(op, p, o, world, slot, epoch, n, timeout_ns, st);
+  if (slot_dtype == PDB200_INT64 && out_dtype == PDB200_INT64) return peer_launch_all_ranks<int64_t, int64_t>(op, p, o, world, slot, epoch, n, timeout_ns, st);
+  return fail(PDB200_UNSUPPORTED, "peer_all_reduce_emulated: built for (float32, float32), (float32, bfloat16) and (int64, int64)");
 }
 
 }  // extern "C"
