@@ -275,6 +275,24 @@ PDB200_API int pdb200_sum_grad(const void* out_grad, const int64_t* x_dims, int 
 PDB200_API int pdb200_mean_grad(const void* out_grad, const int64_t* x_dims, int x_rank, const int64_t* axes, int n_axes,
                      int reduce_all, int dtype, void* x_grad, void* stream);
 
+/* Backward of max / min / prod.  x is the forward input, out the forward result and out_grad its gradient (one element
+ * per kept position each, as above); x_grad has x's shape.
+ *   max_grad, min_grad: x_grad = out_grad * (x equals out ? 1 : 0) — "equals" is the reference's EqualFunctor
+ *     (compare_functors.h:35-48: |a - b| < 1e-8 for floating types, infinities exact, NaN equals nothing), every tied
+ *     position receives the whole out_grad, and out_grad * 0 keeps inf * 0 = NaN.  Replaces
+ *     phi::ReduceMaxGradKernel / ReduceMinGradKernel, paddle/phi/kernels/gpu/reduce_kernel.cu:76-120,159-203 (two
+ *     broadcast kernels and an x-sized temporary there, one pass here).  The two entry points run the same kernel.
+ *   prod_grad: x_grad = (out_grad * out) * (1 / x), each step rounded to the tensor type (integers: 1 / x truncates to
+ *     1, -1 or 0; x == 0, a division by zero in the reference, gives 0).  Replaces phi::ProdGradKernel,
+ *     paddle/phi/kernels/gpu/prod_grad_kernel.cu:21-30 -> funcs::ProdGradFunctor (funcs/reduce_functor.h:143-159).
+ * dtypes: float32, float64, float16, bfloat16, int32, int64.  No workspace. */
+PDB200_API int pdb200_max_grad(const void* x, const int64_t* x_dims, int x_rank, const void* out, const void* out_grad,
+                    const int64_t* axes, int n_axes, int reduce_all, int dtype, void* x_grad, void* stream);
+PDB200_API int pdb200_min_grad(const void* x, const int64_t* x_dims, int x_rank, const void* out, const void* out_grad,
+                    const int64_t* axes, int n_axes, int reduce_all, int dtype, void* x_grad, void* stream);
+PDB200_API int pdb200_prod_grad(const void* x, const int64_t* x_dims, int x_rank, const void* out, const void* out_grad,
+                     const int64_t* axes, int n_axes, int reduce_all, int dtype, void* x_grad, void* stream);
+
 /* ---------------------------------------------------------------------------
  * argmax.  Replaces phi::ArgMaxKernel<T, GPUContext> (paddle/phi/kernels/gpu/arg_min_max_kernel.cu:59-204).
  * Lowest index wins ties; out_dtype is PDB200_INT64 or PDB200_INT32; flatten != 0 reduces over the

@@ -472,6 +472,80 @@ int oracle_reduce_grad(int op, int dtype, const int64_t* xd, int xr, const int* 
 }
 
 /* ------------------------------------------------------------------------------------------
+ * max_grad / min_grad / prod_grad, as the GPU kernels compute them.
+ *   max_grad, min_grad: phi::ReduceMaxGradKernel / ReduceMinGradKernel<T,GPUContext> (gpu/reduce_kernel.cu:76-120,159-203):
+ *       equal_out = Equal(out, x) with funcs::EqualFunctor<T> (funcs/compare_functors.h:35-48), stored as T;
+ *       x_grad = out_grad * equal_out.
+ *     (The CPU kernel, funcs::MaxOrMinGradFunctor reduce_functor.h:161-186, uses an exact ==; the two agree unless two
+ *     different values lie within 1e-8 of each other.  tol != 0 selects the GPU rule, tol == 0 the CPU rule.)
+ *   prod_grad: funcs::ProdGradFunctor (reduce_functor.h:143-159): dx = dy.broadcast * y.broadcast * x.inverse(), every
+ *     step in T (16-bit types: float arithmetic rounded back after each step); integer 1 / 0 -> 0 here (undefined there).
+ * op: 0 max/min, 1 prod.  red[i] != 0 marks a reduced dimension of x.
+ * ---------------------------------------------------------------------------------------- */
+static int eq_tol_f(float a, float b, float d, int tol) {  /* d = a - b rounded to T, widened */
+  if (!tol) return a == b;
+  if (isinf(a) || isinf(b)) return a == b;
+  if (isnan(a) || isnan(b)) return 0;
+  return fabs((double)d) < 1e-8;
+}
+int oracle_select_grad(int op, int tol, int dtype, const int64_t* xd, int xr, const int* red, const void* x, const void* out,
+                       const void* out_grad, void* x_grad) {
+  int64_t gs[MAXR], idx[MAXR] = {0}, numel = 1, s = 1;
+  for (int i = xr - 1; i >= 0; --i) {
+    gs[i] = red[i] ? 0 : s;
+    if (!red[i]) s *= xd[i];
+    numel *= xd[i];
+  }
+  for (int64_t i = 0; i < numel; ++i) {
+    int64_t go = 0;
+    for (int d = 0; d < xr; ++d) go += idx[d] * gs[d];
+    switch (dtype) {
+      case DT_FLOAT32: {
+        const float xv = ((const float*)x)[i], y = ((const float*)out)[go], dy = ((const float*)out_grad)[go];
+        volatile float t;
+        if (op == 0) { t = y - xv; t = dy * (eq_tol_f(y, xv, t, tol) ? 1.f : 0.f); }
+        else { volatile float inv = 1.f / xv; t = dy * y; t = t * inv; }
+        ((float*)x_grad)[i] = t; break; }
+      case DT_FLOAT64: {
+        const double xv = ((const double*)x)[i], y = ((const double*)out)[go], dy = ((const double*)out_grad)[go];
+        volatile double t;
+        if (op == 0) {
+          int e;
+          if (!tol) e = (y == xv);
+          else if (isinf((float)y) || isinf((float)xv)) e = (y == xv);
+          else if (isnan((float)y) || isnan((float)xv)) e = 0;
+          else { t = y - xv; e = fabs(t) < 1e-8; }
+          t = dy * (e ? 1.0 : 0.0);
+        } else { volatile double inv = 1.0 / xv; t = dy * y; t = t * inv; }
+        ((double*)x_grad)[i] = t; break; }
+      case DT_INT32: {
+        const int32_t xv = ((const int32_t*)x)[i], y = ((const int32_t*)out)[go], dy = ((const int32_t*)out_grad)[go];
+        if (op == 0) ((int32_t*)x_grad)[i] = y == xv ? dy : 0;
+        else ((int32_t*)x_grad)[i] = (int32_t)((uint32_t)dy * (uint32_t)y * (uint32_t)(xv == 1 ? 1 : xv == -1 ? -1 : 0));
+        break; }
+      case DT_INT64: {
+        const int64_t xv = ((const int64_t*)x)[i], y = ((const int64_t*)out)[go], dy = ((const int64_t*)out_grad)[go];
+        if (op == 0) ((int64_t*)x_grad)[i] = y == xv ? dy : 0;
+        else ((int64_t*)x_grad)[i] = (int64_t)((uint64_t)dy * (uint64_t)y * (uint64_t)(xv == 1 ? 1 : xv == -1 ? -1 : 0));
+        break; }
+      case DT_BFLOAT16: case DT_FLOAT16: {
+        const int b = dtype == DT_BFLOAT16;
+        const uint16_t xb = ((const uint16_t*)x)[i], yb = ((const uint16_t*)out)[go], gb = ((const uint16_t*)out_grad)[go];
+        const float xv = b ? bf2f(xb) : h2f(xb), y = b ? bf2f(yb) : h2f(yb), dy = b ? bf2f(gb) : h2f(gb);
+#define RT(v) (b ? bf2f(f2bf(v)) : h2f(f2h(v)))
+        float t;
+        if (op == 0) { const float d = RT(y - xv); t = RT(dy * (eq_tol_f(y, xv, d, tol) ? 1.f : 0.f)); }
+        else { const float inv = RT(1.f / xv); t = RT(dy * y); t = RT(t * inv); }
+#undef RT
+        ((uint16_t*)x_grad)[i] = b ? f2bf(t) : f2h(t); break; }
+      default: return 2;
+    }
+    for (int d = xr - 1; d >= 0; --d) { if (++idx[d] < xd[d]) break; idx[d] = 0; }
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
  * log_softmax.  phi::LogSoftmaxKernel<T,CPUContext> -> LogSoftmaxFunctor
  * (cpu/log_softmax_kernel.cc:40-127): x viewed as [n][axis_dim][remain];
  *     d = max(x - max_along_axis, -64)   (ValueClip :32-38)

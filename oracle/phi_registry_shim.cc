@@ -291,6 +291,10 @@ int phi_min_run(const char* name, const char* backend, int key_dtype, const char
       auto* fn = kernel.GetVariadicKernelFn<void (*)(const Ctx&, const DT&, const DT&, const phi::IntArray&, bool, bool, DT*)>();
       std::vector<int64_t> axes(iv + 2, iv + ni);
       (*fn)(ctx, WrapIn(in[0]), WrapIn(in[1]), phi::IntArray(axes), iv[0] != 0, iv[1] != 0, op(0));
+    } else if (fam == "select_grad") {  // max/min/prod grad: (ctx, x, out, out_grad, IntArray dims, bool keep_dim, bool reduce_all, x_grad)
+      auto* fn = kernel.GetVariadicKernelFn<void (*)(const Ctx&, const DT&, const DT&, const DT&, const phi::IntArray&, bool, bool, DT*)>();
+      std::vector<int64_t> axes(iv + 2, iv + ni);
+      (*fn)(ctx, WrapIn(in[0]), WrapIn(in[1]), WrapIn(in[2]), phi::IntArray(axes), iv[0] != 0, iv[1] != 0, op(0));
     } else if (fam == "sum_raw") {  // (ctx, x, IntArray, bool keep_dim, bool reduce_all, DataType out_dtype, out)
       auto* fn = kernel.GetVariadicKernelFn<void (*)(const Ctx&, const DT&, const phi::IntArray&, bool, bool, phi::DataType, DT*)>();
       std::vector<int64_t> axes(iv + 3, iv + ni);

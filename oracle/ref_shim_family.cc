@@ -16,6 +16,8 @@
 //   log_softmax  phi::LogSoftmaxKernel<T,CPUContext>             paddle/phi/kernels/cpu/log_softmax_kernel.cc:40-127
 //   sum_grad / mean_grad  phi::ReduceSumGradKernel / ReduceMeanGradKernel<T,CPUContext>
 //                paddle/phi/kernels/cpu/reduce_sum_grad_kernel.cc:26-43, cpu/reduce_mean_grad_kernel.cc
+//   max_grad / min_grad / prod_grad  phi::ReduceMaxGradKernel / ReduceMinGradKernel / ProdGradKernel<T,CPUContext>
+//                paddle/phi/kernels/cpu/reduce_max_grad_kernel.cc, reduce_min_grad_kernel.cc, prod_grad_kernel.cc
 //   multiply_grad phi::MultiplyGradKernel<T,CPUContext>          paddle/phi/kernels/cpu/elementwise_multiply_grad_kernel.cc:26-39
 #include "paddle/common/flags.h"
 #include "paddle/phi/common/bfloat16.h"
@@ -37,7 +39,10 @@
 #include "paddle/phi/kernels/cpu/elementwise_multiply_grad_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/log_softmax_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/logical_kernel.cc"  // NOLINT
+#include "paddle/phi/kernels/cpu/prod_grad_kernel.cc"         // NOLINT
+#include "paddle/phi/kernels/cpu/reduce_max_grad_kernel.cc"   // NOLINT
 #include "paddle/phi/kernels/cpu/reduce_mean_grad_kernel.cc"  // NOLINT
+#include "paddle/phi/kernels/cpu/reduce_min_grad_kernel.cc"   // NOLINT
 #include "paddle/phi/kernels/cpu/reduce_sum_grad_kernel.cc"   // NOLINT
 #include "paddle/phi/kernels/cpu/scale_kernel.cc"    // NOLINT
 #include "paddle/phi/kernels/cpu/where_kernel.cc"    // NOLINT
@@ -371,6 +376,35 @@ int phi_ref_reduce_grad(int op, int dtype, const void* x, const int64_t* xdims, 
     }
 #undef RG_SUM
 #undef RG_BOTH
+    if (dxt.data() != x_grad) std::memcpy(x_grad, dxt.data(), static_cast<size_t>(dxt.numel()) * phi::SizeOf(dxt.dtype()));
+  });
+}
+
+// op: 0 max_grad, 1 min_grad, 2 prod_grad (CPU registrations: float, double, int, int64_t).  out / out_grad carry the
+// shape the forward produced.
+int phi_ref_select_grad(int op, int dtype, const void* x, const int64_t* xdims, int xrank, const void* out,
+                        const void* out_grad, const int64_t* gdims, int grank, const int64_t* axes, int n_axes,
+                        int keep_dim, int reduce_all, void* x_grad) {
+  return Guard([&] {
+    auto& ctx = GetCtx().ctx;
+    auto xt = Wrap(x, xdims, xrank, dtype);
+    auto yt = Wrap(out, gdims, grank, dtype);
+    auto gt = Wrap(out_grad, gdims, grank, dtype);
+    auto dxt = Wrap(x_grad, xdims, xrank, dtype);
+    phi::IntArray ax(std::vector<int64_t>(axes, axes + n_axes));
+#define SG(T)                                                                                                        \
+  if (op == 0) phi::ReduceMaxGradKernel<T, CPUContext>(ctx, xt, yt, gt, ax, keep_dim != 0, reduce_all != 0, &dxt);      \
+  else if (op == 1) phi::ReduceMinGradKernel<T, CPUContext>(ctx, xt, yt, gt, ax, keep_dim != 0, reduce_all != 0, &dxt); \
+  else phi::ProdGradKernel<T, CPUContext>(ctx, xt, yt, gt, ax, keep_dim != 0, reduce_all != 0, &dxt);                   \
+  break;
+    switch (dtype) {
+      case kFloat32: SG(float)
+      case kFloat64: SG(double)
+      case kInt32: SG(int32_t)
+      case kInt64: SG(int64_t)
+      default: throw std::runtime_error("phi_ref_select_grad: dtype not registered on CPU");
+    }
+#undef SG
     if (dxt.data() != x_grad) std::memcpy(x_grad, dxt.data(), static_cast<size_t>(dxt.numel()) * phi::SizeOf(dxt.dtype()));
   });
 }

@@ -50,6 +50,9 @@ SIGNATURES = {
     "pdb200_multiply_grad": (_int, [_vp, _c_i64p, _int, _vp, _c_i64p, _int, _vp, _int, _vp, _vp, _vp, _sz, _vp]),
     "pdb200_sum_grad": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _vp, _vp]),
     "pdb200_mean_grad": (_int, [_vp, _c_i64p, _int, _c_i64p, _int, _int, _int, _vp, _vp]),
+    "pdb200_max_grad": (_int, [_vp, _c_i64p, _int, _vp, _vp, _c_i64p, _int, _int, _int, _vp, _vp]),
+    "pdb200_min_grad": (_int, [_vp, _c_i64p, _int, _vp, _vp, _c_i64p, _int, _int, _int, _vp, _vp]),
+    "pdb200_prod_grad": (_int, [_vp, _c_i64p, _int, _vp, _vp, _c_i64p, _int, _int, _int, _vp, _vp]),
     "pdb200_peer_window_bytes": (_sz, [_sz]),
     "pdb200_peer_window_create": (_int, [_sz, ctypes.POINTER(_vp), _vp]),
     "pdb200_peer_window_open": (_int, [_vp, ctypes.POINTER(_vp)]),

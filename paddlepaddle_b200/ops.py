@@ -456,6 +456,41 @@ def mean_grad(x, out_grad, axis=None, keepdim=False, reduce_all=False):
     return _reduce_grad("pdb200_mean_grad", x, out_grad, axis, keepdim, reduce_all)
 
 
+def _select_grad(fn_name, x, out, out_grad, axis, keepdim, reduce_all):
+    """max_grad / min_grad / prod_grad(x, out, out_grad, axis, keepdim, reduce_all) -> x_grad (backward.yaml)."""
+    _require_cuda(x, out, out_grad)
+    if not (x.dtype == out.dtype == out_grad.dtype):
+        raise TypeError("(InvalidType) x, out and out_grad must share one dtype")
+    axes = _norm_axes(axis, x.dim())
+    want = _reduced_shape(tuple(x.shape), [] if reduce_all else axes, keepdim)
+    for name, t in (("out", out), ("out_grad", out_grad)):
+        if tuple(t.shape) != tuple(want):
+            raise ValueError(f"(InvalidArgument) {name} has shape {tuple(t.shape)}, the forward output has {tuple(want)}")
+    lib = L.load()
+    x, out, out_grad = x.contiguous(), out.contiguous(), out_grad.contiguous()
+    x_grad = torch.empty(x.shape, dtype=x.dtype, device=x.device)
+    xd, xr = L.dims_array(x.shape)
+    ad, an = L.dims_array(axes)
+    L.check(getattr(lib, fn_name)(_ptr(x), xd, xr, _ptr(out), _ptr(out_grad), ad, an, int(bool(reduce_all) or not axes),
+                                  _dtype_code(x.dtype), _ptr(x_grad), _stream()), lib)
+    return x_grad
+
+
+def max_grad(x, out, out_grad, axis=None, keepdim=False, reduce_all=False):
+    """Backward of paddle.max: out_grad at every position that holds the maximum (ties all receive it), 0 elsewhere."""
+    return _select_grad("pdb200_max_grad", x, out, out_grad, axis, keepdim, reduce_all)
+
+
+def min_grad(x, out, out_grad, axis=None, keepdim=False, reduce_all=False):
+    """Backward of paddle.min."""
+    return _select_grad("pdb200_min_grad", x, out, out_grad, axis, keepdim, reduce_all)
+
+
+def prod_grad(x, out, out_grad, axis=None, keepdim=False, reduce_all=False):
+    """Backward of paddle.prod: out_grad * out / x."""
+    return _select_grad("pdb200_prod_grad", x, out, out_grad, axis, keepdim, reduce_all)
+
+
 def mean(x, axis=None, keepdim=False, name=None):
     return _reduce(L.REDUCE_MEAN, x, axis, keepdim, x.dtype)
 

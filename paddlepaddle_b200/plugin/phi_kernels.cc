@@ -272,6 +272,33 @@ void ReduceMeanGradKernel(const Context& ctx, const DenseTensor& x, const DenseT
                          reduce_all, Code(x.dtype()), o, ctx.stream()));
 }
 
+// ---- max_grad / min_grad / prod_grad (gpu/reduce_kernel.cu:76-120,159-203; gpu/prod_grad_kernel.cu -> impl/prod_grad_kernel_impl.h)
+typedef int (*SelectGradFn)(const void*, const int64_t*, int, const void*, const void*, const int64_t*, int, int, int, void*, void*);
+template <typename Context>
+void SelectGrad(SelectGradFn fn, const Context& ctx, const DenseTensor& x, const DenseTensor& out, const DenseTensor& out_grad,
+                const phi::IntArray& dims, bool reduce_all, DenseTensor* x_grad) {
+  void* o = ctx.Alloc(x_grad, x.dtype());
+  auto xd = Dims(x);
+  const auto& ax = dims.GetData();
+  Check(fn(x.data(), xd.data(), static_cast<int>(xd.size()), out.data(), out_grad.data(), ax.data(), static_cast<int>(ax.size()),
+           reduce_all, Code(x.dtype()), o, ctx.stream()));
+}
+template <typename T, typename Context>
+void ReduceMaxGradKernel(const Context& ctx, const DenseTensor& x, const DenseTensor& out, const DenseTensor& out_grad,
+                         const phi::IntArray& dims, bool keep_dim, bool reduce_all, DenseTensor* x_grad) {
+  SelectGrad(pdb200_max_grad, ctx, x, out, out_grad, dims, reduce_all, x_grad);
+}
+template <typename T, typename Context>
+void ReduceMinGradKernel(const Context& ctx, const DenseTensor& x, const DenseTensor& out, const DenseTensor& out_grad,
+                         const phi::IntArray& dims, bool keep_dim, bool reduce_all, DenseTensor* x_grad) {
+  SelectGrad(pdb200_min_grad, ctx, x, out, out_grad, dims, reduce_all, x_grad);
+}
+template <typename T, typename Context>
+void ProdGradKernel(const Context& ctx, const DenseTensor& x, const DenseTensor& out, const DenseTensor& out_grad,
+                    const phi::IntArray& dims, bool keep_dim, bool reduce_all, DenseTensor* x_grad) {
+  SelectGrad(pdb200_prod_grad, ctx, x, out, out_grad, dims, reduce_all, x_grad);
+}
+
 // ---- reductions --------------------------------------------------------------------------
 typedef int (*ReduceFn)(const void*, const int64_t*, int, const int64_t*, int, int, int, int, void*, void*,
                         size_t, void*);
@@ -626,6 +653,13 @@ PD_REGISTER_KERNEL(sum_grad, GPU, ALL_LAYOUT, pdb200_phi::ReduceSumGradKernel, f
 }
 PD_REGISTER_KERNEL(mean_grad, GPU, ALL_LAYOUT, pdb200_phi::ReduceMeanGradKernel, float, double, phi::dtype::float16,
                    phi::dtype::bfloat16, int, int64_t) {}
+// gpu/reduce_kernel.cu:335-344,360-369; gpu/prod_grad_kernel.cu:21-30
+PD_REGISTER_KERNEL(max_grad, GPU, ALL_LAYOUT, pdb200_phi::ReduceMaxGradKernel, float, double, int, int64_t, phi::dtype::float16,
+                   phi::dtype::bfloat16) {}
+PD_REGISTER_KERNEL(min_grad, GPU, ALL_LAYOUT, pdb200_phi::ReduceMinGradKernel, float, double, int, int64_t, phi::dtype::float16,
+                   phi::dtype::bfloat16) {}
+PD_REGISTER_KERNEL(prod_grad, GPU, ALL_LAYOUT, pdb200_phi::ProdGradKernel, float, double, int, int64_t, phi::dtype::float16,
+                   phi::dtype::bfloat16) {}
 // gpu/cross_entropy_kernel.cu:1460-1466
 PD_REGISTER_KERNEL(cross_entropy_with_softmax, GPU, ALL_LAYOUT, pdb200_phi::CrossEntropyWithSoftmaxKernel, float, double,
                    phi::dtype::float16) {}

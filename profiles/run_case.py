@@ -88,6 +88,18 @@ elif case in ("ln_grad_bf16", "ln_grad_bf16_dx"):
         fn = lambda: F.layer_norm_grad(x, [8192], w, m, v, dy, need_weight_grad=False, need_bias_grad=False)
     else:
         fn = lambda: F.layer_norm_grad(x, [8192], w, m, v, dy)
+elif case in ("max_grad_rows_bf16", "max_grad_cols_fp32", "prod_grad_rows_bf16", "max_grad_mid_bf16"):
+    dt = torch.float32 if case.endswith("fp32") else torch.bfloat16
+    shape = (256, 64, 16384) if "mid" in case else (65536, 8192)
+    axis = 1 if "mid" in case else (0 if "cols" in case else -1)
+    x = torch.randn(shape, device="cuda", generator=g).to(dt)
+    out = paddle.max(x, axis=axis)
+    og = torch.randn(out.shape, device="cuda", generator=g).to(dt)
+    fn = (lambda: paddle.prod_grad(x, out, og, axis=axis)) if case.startswith("prod") else (lambda: paddle.max_grad(x, out, og, axis=axis))
+elif case == "sum_grad_mid_bf16":
+    x = torch.empty((256, 64, 16384), device="cuda", dtype=torch.bfloat16)
+    og = torch.randn((256, 16384), device="cuda", generator=g).to(torch.bfloat16)
+    fn = lambda: paddle.sum_grad(x, og, axis=1)
 elif case == "sum_c1":
     x = torch.rand((4096, 4096), device="cuda", generator=g)
     fn = lambda: paddle.sum(x, axis=-1)

@@ -331,6 +331,27 @@ class Oracle:
         self._check(rc)
         return x_grad
 
+    def select_grad(self, op, x, out, out_grad, axis=None, keepdim=False, code=None, tol=True):
+        """op 'max'|'min'|'prod' -> x_grad.  port: tol=True is the GPU kernel's EqualFunctor (|a - b| < 1e-8), tol=False the
+        CPU kernel's exact ==; ref: the compiled CPU kernel (exact ==; float32 / float64 / int32 / int64)."""
+        x, out, out_grad = (np.ascontiguousarray(t) for t in (x, out, out_grad))
+        code = NP2CODE[x.dtype] if code is None else code
+        rank = x.ndim
+        axes = [] if axis is None else ([int(a) for a in axis] if isinstance(axis, (list, tuple)) else [int(axis)])
+        x_grad = np.empty(x.shape, x.dtype)
+        xd, xr = _dims(x.shape)
+        if self.kind == "port":
+            red = [1] * rank if not axes else [int(i in {a % rank for a in axes}) for i in range(rank)]
+            rc = self.lib.oracle_select_grad(int(op == "prod"), int(tol), code, xd, xr, (ctypes.c_int * max(rank, 1))(*red),
+                                             _vp(x), _vp(out), _vp(out_grad), _vp(x_grad))
+        else:
+            gd, gr = _dims(reduced_shape(x.shape, axes, keepdim))
+            ad, an = _dims(axes)
+            rc = self.lib.phi_ref_select_grad({"max": 0, "min": 1, "prod": 2}[op], code, _vp(x), xd, xr, _vp(out), _vp(out_grad),
+                                              gd, gr, ad, an, int(keepdim), int(not axes), _vp(x_grad))
+        self._check(rc)
+        return x_grad
+
     def log_softmax(self, x, axis=-1, code=None):
         x = np.ascontiguousarray(x)
         code = NP2CODE[x.dtype] if code is None else code

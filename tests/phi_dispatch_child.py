@@ -173,6 +173,17 @@ def case_grads():
     for name, fn in (("sum_grad", paddle.sum_grad), ("mean_grad", paddle.mean_grad)):
         want = fn(x, og, axis=1)
         check(name, run(name, "reduce_grad", [x, og], [want], iv=[0, 0, 1]), want)
+    for dt in (torch.float32, torch.bfloat16):
+        xs = torch.randint(-4, 5, (64, 96, 32), device="cuda", generator=g).to(dt)
+        ogs = rnd((64, 32), dt)
+        for name, fwd, fn in (("max_grad", paddle.max, paddle.max_grad), ("min_grad", paddle.min, paddle.min_grad)):
+            out = fwd(xs, axis=1)
+            want = fn(xs, out, ogs, axis=1)
+            check(f"{name}/{dt}", run(name, "select_grad", [xs, out, ogs], [want], iv=[0, 0, 1]), want)
+        xp = rnd((64, 96, 32), dt) + 3
+        out = rnd((64, 32), dt)
+        want = paddle.prod_grad(xp, out, ogs, axis=1)
+        check(f"prod_grad/{dt}", run("prod_grad", "select_grad", [xp, out, ogs], [want], iv=[0, 0, 1]), want)
 
 
 # ---- reductions -------------------------------------------------------------------------------------------------------
@@ -274,7 +285,7 @@ reg.phi_min_has_kernel.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_in
 NAMES = ["add", "multiply", "subtract", "divide", "maximum", "minimum", "less_than", "less_equal", "greater_than", "greater_equal",
          "equal", "not_equal", "logical_and", "logical_or", "logical_xor", "logical_not", "bitwise_and", "bitwise_or", "bitwise_xor",
          "bitwise_not", "bitwise_left_shift", "bitwise_right_shift", "scale", "cast", "where", "add_grad", "multiply_grad", "sum_grad",
-         "mean_grad", "cross_entropy_with_softmax", "rms_norm", "log_softmax", "sum_raw", "sum", "mean_raw", "mean", "max_raw", "max",
+         "mean_grad", "max_grad", "min_grad", "prod_grad", "cross_entropy_with_softmax", "rms_norm", "log_softmax", "sum_raw", "sum", "mean_raw", "mean", "max_raw", "max",
          "min_raw", "min", "prod", "argmax", "argmin", "softmax", "layer_norm", "softmax_grad", "layer_norm_grad", "fused_softmax_mask",
          "fused_softmax_mask_upper_triangle", "fused_bias_dropout_residual_layer_norm"]
 print(json.dumps({"calls": n_calls, "alloc_calls": reg.phi_min_alloc_calls(), "failed": failed,

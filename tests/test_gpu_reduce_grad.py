@@ -40,7 +40,7 @@ def test_reduce_grad_golden(gold):
 
 ROUTES = [((4096, 512), 0), ((4096, 512), 1), ((4096, 512), None), ((1000, 264), 0), ((257, 1031), 0), ((257, 1031), 1),
           ((64, 8, 128), 1), ((64, 8, 128), (0, 2)), ((7, 33, 5, 16), (1, 3)), ((1 << 20,), 0), ((3, 70000), 1), ((65, 1, 9), 1),
-          ((2, 3, 4, 5, 6), (0, 2, 4))]
+          ((2, 3, 4, 5, 6), (0, 2, 4)), ((16, 13, 2048), 1), ((3, 70, 1024), 1)]  # the last two: the batched inner route
 
 
 @pytest.mark.parametrize("shape,axis", ROUTES)

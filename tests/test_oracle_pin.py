@@ -229,3 +229,40 @@ def test_argmin_restatement_equals_compiled_reference(port, ref):
                 a, b = port.argmin(x, axis, keep), ref.argmin(x, axis, keep)
                 assert a.shape == b.shape and np.array_equal(a, b), (dt, axis, keep)
         assert np.array_equal(port.argmin(x, 1, dtype=np.int32), ref.argmin(x, 1, dtype=np.int32))
+
+
+def test_select_grad_restatement_equals_compiled_reference(port, ref):
+    """max_grad / min_grad / prod_grad (round 2) have no golden file: the restatement is pinned to the compiled reference
+    live.  max / min: the CPU kernel compares exactly, so the restatement runs with tol=False here and, on inputs whose
+    distinct values are further than 1e-8 apart, with the GPU rule (tol=True) as well — the same bits.  prod: bit-exact for
+    float32 / float64 (three correctly rounded steps), integers away from x == 0."""
+    rng = np.random.default_rng(33)
+    for dt in (np.float32, np.float64, np.int32, np.int64):
+        for shape, axis in (((6, 31, 5), None), ((6, 31, 5), 1), ((6, 31, 5), (0, 2)), ((6, 31, 5), -1), ((17,), 0), ((4, 1, 9), 1)):
+            x = rng.integers(-3, 4, shape).astype(dt)  # many ties
+            for keep in (False, True):
+                axes = None if axis is None else (list(axis) if isinstance(axis, tuple) else [axis])
+                for op, fwd in (("max", np.max), ("min", np.min)):
+                    out = fwd(x, axis=axis, keepdims=keep)
+                    g = rng.integers(-5, 6, np.shape(out)).astype(dt)
+                    if np.issubdtype(dt, np.floating) and g.size:
+                        g.flat[0] = np.inf  # inf * 0 = NaN at the non-maximal positions
+                    want = ref.select_grad(op, x, out, g, axes, keep)
+                    assert np.array_equal(port.select_grad(op, x, out, g, axes, keep, tol=False), want, equal_nan=True), (dt, shape, axis, op)
+                    assert np.array_equal(port.select_grad(op, x, out, g, axes, keep, tol=True), want, equal_nan=True), (dt, shape, axis, op)
+                xp = x.copy()
+                xp[xp == 0] = 2
+                if np.issubdtype(dt, np.floating):
+                    xp = (xp * rng.uniform(0.5, 1.5, shape)).astype(dt)
+                out = np.prod(xp, axis=axis, keepdims=keep).astype(dt)
+                g = rng.standard_normal(np.shape(out)).astype(dt) if np.issubdtype(dt, np.floating) else rng.integers(-5, 6, np.shape(out)).astype(dt)
+                want = ref.select_grad("prod", xp, out, g, axes, keep)
+                assert np.array_equal(port.select_grad("prod", xp, out, g, axes, keep), want), (dt, shape, axis, "prod")
+    # NaN and infinities in x: NaN equals nothing, inf == inf
+    x = np.array([[1.0, np.inf, np.nan, np.inf], [np.nan, -np.inf, 2.0, 2.0]], np.float32)
+    out = np.array([np.inf, 2.0], np.float32)
+    g = np.array([3.0, -1.0], np.float32)
+    want = ref.select_grad("max", x, out, g, [1], False)
+    assert np.array_equal(want, np.array([[0, 3, 0, 3], [0, 0, -1, -1]], np.float32))
+    for tol in (False, True):
+        assert np.array_equal(port.select_grad("max", x, out, g, [1], False, tol=tol), want)

@@ -36,7 +36,7 @@ out["has"] = {f"{n}/{b}/{d}": reg.phi_min_has_kernel(n.encode(), b.encode(), d) 
 ar = {}
 a, b_, c = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
 for n in ["add", "divide", "sum", "sum_raw", "mean", "max_raw", "prod", "argmax", "softmax", "layer_norm", "softmax_grad",
-          "layer_norm_grad", "less_than", "logical_not", "logical_xor", "scale", "cast", "where", "add_grad", "multiply_grad", "sum_grad", "mean_grad", "cross_entropy_with_softmax"]:
+          "layer_norm_grad", "less_than", "logical_not", "logical_xor", "scale", "cast", "where", "add_grad", "multiply_grad", "sum_grad", "mean_grad", "max_grad", "prod_grad", "cross_entropy_with_softmax"]:
     reg.phi_min_arity(n.encode(), b"GPU", 10, ctypes.byref(a), ctypes.byref(b_), ctypes.byref(c))
     ar[n] = [a.value, b_.value, c.value]
 out["arity"] = ar
@@ -77,6 +77,8 @@ EXPECT = {  # the registrations of plugin/phi_kernels.cc
     "cast": "float32 float64 int32 int64 int16 bool int8 uint8 float16 bfloat16",
     "where": "float32 float64 int32 int64 float16 bfloat16",
     "sum_grad": "float32 float64 float16 bfloat16 int32 int64", "mean_grad": "float32 float64 float16 bfloat16 int32 int64",
+    "max_grad": "float32 float64 int32 int64 float16 bfloat16", "min_grad": "float32 float64 int32 int64 float16 bfloat16",
+    "prod_grad": "float32 float64 int32 int64 float16 bfloat16",
     "add_grad": "float32 float64 int32 int64 float16 bfloat16", "multiply_grad": "float32 float16 float64 int32 int64 bfloat16",
 }
 
@@ -102,7 +104,8 @@ def test_pd_register_kernel_overwrites_paddles_keys():
                             "layer_norm": [3, 2, 3], "softmax_grad": [2, 1, 1], "layer_norm_grad": [6, 2, 3],
                             "less_than": [2, 0, 1], "logical_not": [1, 0, 1], "logical_xor": [2, 0, 1], "scale": [1, 3, 1],
                             "cast": [1, 1, 1], "where": [3, 0, 1], "add_grad": [3, 1, 2], "multiply_grad": [3, 1, 2], "sum_grad": [2, 3, 1],
-                            "mean_grad": [2, 3, 1], "cross_entropy_with_softmax": [2, 5, 2]}
+                            "mean_grad": [2, 3, 1], "max_grad": [3, 3, 1], "prod_grad": [3, 3, 1],
+                            "cross_entropy_with_softmax": [2, 5, 2]}
     # output dtypes left UNDEFINED where the in-tree registration bodies do so
     assert out["ln_out_dtypes"] == [DT["bfloat16"], 0, 0] and out["sum_out_dtype"] == 0 and out["argmax_out_dtype"] == 0
     # compare / logical outputs are BOOL, cast's is left to InferMeta, scale keeps the input dtype
