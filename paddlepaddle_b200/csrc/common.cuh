@@ -59,7 +59,7 @@ inline int sm_count() {
 // ----------------------------------------------------------------------------
 struct Knobs {
   int pipe_contig, pipe_max_ctas, pipe_max_stages, pipe_inflight_kb, pipe_rows_per_cta;
-  int softmax_pipe_c, ln_pipe_c, rms_pipe_c, cluster_slice_kb, cluster_rows_per_cluster, softmax_long;
+  int softmax_pipe_c, ln_pipe_c, rms_pipe_c, cluster_slice_kb, cluster_rows_per_cluster, softmax_long, cluster_threads, relay_stages, relay_cfg;
   int tma_cols_stages, expand_rows_per_cta, mulgrad_stages;
   long long mulgrad_splits;
   bool no_tma_cols, no_interleave, no_fused_mulgrad, no_cluster_pipe;
@@ -83,6 +83,9 @@ inline const Knobs& knobs() {
     r.ln_pipe_c = (int)num("PDB200_LN_PIPE_C");
     r.rms_pipe_c = (int)num("PDB200_RMS_PIPE_C");
     r.cluster_slice_kb = (int)num("PDB200_CLUSTER_SLICE_KB");
+    r.cluster_threads = (int)num("PDB200_CLUSTER_THREADS");
+    r.relay_stages = (int)num("PDB200_RELAY_STAGES");
+    r.relay_cfg = (int)num("PDB200_RELAY_CFG");
     r.cluster_rows_per_cluster = (int)num("PDB200_CLUSTER_ROWS");
     r.softmax_long = (int)num("PDB200_SOFTMAX_LONG");
     r.tma_cols_stages = (int)num("PDB200_TMA_COLS_STAGES");

@@ -523,6 +523,419 @@ __global__ void __launch_bounds__(1024) softmax_rows_cluster_kernel(const T* __r
   asm volatile("barrier.cluster.wait.aligned;" ::: "memory");  // nobody leaves while a peer may still be reading its xchg[]
 }
 
+// ---- rows_cluster_lean: the shared-memory cluster kernel for float accumulators, with cheap sweeps ----------------------
+// Same data movement as softmax_rows_cluster_kernel (one bulk copy of the slice into shared memory, one cluster barrier),
+// different arithmetic.  That kernel ran 20 instructions and 2.25 ex2 per element on [4096,128256] bf16 (issue 63 % busy,
+// XU 63 %: profiles/r2e_softmax_vocab_bf16.txt) — its 1024 threads owned only 32 elements each, so the per-row reductions
+// of (max, sum, clipped) triples (three shuffles and two ex2 per combine) cost as much as the sweeps.  Here:
+//   sweep A  the slice maximum m_c alone: packed 16-bit max, half an instruction per element;
+//   sweep B  s_c = sum exp(x - m_c) relative to the CTA's OWN maximum (no exchange needed before it), fp32 pairs;
+//   one cluster barrier: (m_c, s_c) of every CTA through DSMEM -> M, S = sum s_c exp(m_c - M);
+//   sweep C  y = max(exp(x - M), exp(-64)) / S, the clip applied to the packed 16-bit result.
+// 256 or 512 threads own 64+ elements each; plain float reductions.  S ignores the clip (a clipped term adds at most
+// 1.6e-28 to a sum >= 1).
+template <typename T> struct PackedMax;  // running maximum of the raw vectors
+template <> struct PackedMax<float> {
+  float m = -INFINITY;
+  __device__ __forceinline__ void add(const Vec<float>& v) { m = fmaxf(fmaxf(m, fmaxf(v.v[0], v.v[1])), fmaxf(v.v[2], v.v[3])); }
+  __device__ __forceinline__ float get() const { return m; }
+};
+template <> struct PackedMax<__nv_bfloat16> {
+  __nv_bfloat162 m = __nv_bfloat162(__ushort_as_bfloat16(0xFF80), __ushort_as_bfloat16(0xFF80));
+  __device__ __forceinline__ void add(const Vec<__nv_bfloat16>& v) {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+    m = __hmax2(m, __hmax2(__hmax2(h[0], h[1]), __hmax2(h[2], h[3])));
+  }
+  __device__ __forceinline__ float get() const { return fmaxf(__bfloat162float(m.x), __bfloat162float(m.y)); }
+};
+template <> struct PackedMax<__half> {
+  __half2 m = __half2(__ushort_as_half(0xFC00), __ushort_as_half(0xFC00));
+  __device__ __forceinline__ void add(const Vec<__half>& v) {
+    const __half2* h = reinterpret_cast<const __half2*>(&v);
+    m = __hmax2(m, __hmax2(__hmax2(h[0], h[1]), __hmax2(h[2], h[3])));
+  }
+  __device__ __forceinline__ float get() const { return fmaxf(__half2float(m.x), __half2float(m.y)); }
+};
+// the packed result never below `floor2` (NaN kept): the -64 clip on the rounded output
+__device__ __forceinline__ void clip_packed(Vec<__nv_bfloat16>& o, float floor_v) {
+  const __nv_bfloat162 f = __float2bfloat162_rn(floor_v);
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __hmax2_nan(h[i], f);
+}
+__device__ __forceinline__ void clip_packed(Vec<__half>& o, float floor_v) {
+  const __half2 f = __float2half2_rn(floor_v);
+  __half2* h = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __hmax2_nan(h[i], f);
+}
+__device__ __forceinline__ void clip_packed(Vec<float>& o, float floor_v) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) o.v[i] = max_nan(o.v[i], floor_v);
+}
+__device__ __forceinline__ float ex2_fast(float t) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(t));
+  return r;
+}
+
+template <typename T, bool LOG>
+__global__ void __launch_bounds__(512) softmax_rows_cluster_lean_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t dim,
+                                                                        int64_t slice, float* __restrict__ stats) {
+  namespace cg = cooperative_groups;
+  constexpr int V = Vec<T>::N;
+  constexpr int P = V / 2;
+  constexpr float kLog2e = 1.4426950408889634f;
+  constexpr float kClip = 1.603810890548638e-28f;  // exp(-64)
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned rank = cluster.block_rank(), cs = cluster.num_blocks();
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* srow = reinterpret_cast<T*>(smem_raw);  // [slice]
+  __shared__ float red[2][32];
+  __shared__ float xchg[2];
+  __shared__ uint64_t bar;
+  const int tid = threadIdx.x;
+  const int64_t row = (int64_t)blockIdx.x / cs;
+  const int64_t begin = (int64_t)rank * slice;
+  int64_t n64 = dim - begin;
+  const int n = (int)(n64 < 0 ? 0 : (n64 > slice ? slice : n64));
+  const T* src = x + row * dim + begin;
+  T* dst = y + row * dim + begin;
+  const int step = blockDim.x * V;
+  if (tid == 0) {
+    mbar_init(&bar, 1);
+    mbar_fence_init();
+  }
+  if (tid < 32) { red[0][tid] = -INFINITY; red[1][tid] = 0.f; }
+  __syncthreads();
+  if (n > 0) {
+    if (tid == 0) {
+      mbar_expect_tx(&bar, (uint32_t)(n * sizeof(T)));
+      bulk_load_row(srow, src, (uint32_t)(n * sizeof(T)), &bar);
+    }
+    mbar_wait(&bar, 0);
+  }
+  // sweep A
+  PackedMax<T> pmx;
+  int i = tid * V;
+  for (; i + step < n; i += 2 * step) {
+    const Vec<T> a = lds_vec(srow + i), b = lds_vec(srow + i + step);
+    pmx.add(a);
+    pmx.add(b);
+  }
+  if (i < n) pmx.add(lds_vec(srow + i));
+  const float mc = block_reduce_1sync(pmx.get(), MaxF<float>(), red[0]);
+  // sweep B
+  const F2 l2e = f2_splat(kLog2e), nmc = f2_splat(mc == -INFINITY ? 0.f : -mc * kLog2e);  // a slice of -inf only: every term 0
+  F2 acc[2] = {f2_splat(0.f), f2_splat(0.f)};
+#pragma unroll 2
+  for (i = tid * V; i < n; i += step) {
+    float v[V];
+    unpack_to_float<T>(lds_vec(srow + i), v);
+#pragma unroll
+    for (int j = 0; j < P; ++j) {
+      const F2 t = f2_fma(f2_make(v[2 * j], v[2 * j + 1]), l2e, nmc);
+      acc[j & 1] = f2_add(acc[j & 1], f2_make(ex2_fast(f2_lo(t)), ex2_fast(f2_hi(t))));
+    }
+  }
+  const F2 a2 = f2_add(acc[0], acc[1]);
+  const float sc = block_reduce_1sync(f2_lo(a2) + f2_hi(a2), AddF<float>(), red[1]);
+  if (tid == 0) { xchg[0] = mc; xchg[1] = sc; }
+  cluster.sync();
+  float pm = -INFINITY, ps = 0.f;
+  const int lane = tid & 31;
+  if (lane < (int)cs) {
+    const float* r = cluster.map_shared_rank(xchg, lane);
+    pm = r[0];
+    ps = r[1];
+  }
+  const float M = __shfl_sync(0xffffffffu, group_reduce<8>(pm, MaxF<float>()), 0);  // cs <= 8: lanes 0..7 hold the pairs
+  float f = 0.f;
+  if (pm != -INFINITY) f = ex2_fast((pm - M) * kLog2e);
+  float S = __shfl_sync(0xffffffffu, group_reduce<8>(ps * f, AddF<float>()), 0);
+  if (M == -INFINITY) S = __int_as_float(0x7fc00000);  // a row of -inf: NaN, as inf - inf gives in the CPU kernel
+  if (stats != nullptr && rank == 0 && tid == 0) { stats[2 * row] = M; stats[2 * row + 1] = logf(S); }
+  // every CTA has read its peers' pairs: arrive for the exit barrier now (relaxed), wait for it after the stores
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+  const float inv = row_constant<LOG, float>(S);
+  // sweep C
+  const F2 nM = f2_splat(LOG ? -M : -M * kLog2e), k2 = f2_splat(LOG ? -inv : inv);
+#pragma unroll 2
+  for (i = tid * V; i < n; i += step) {
+    float v[V];
+    unpack_to_float<T>(lds_vec(srow + i), v);
+    Vec<T> o;
+    if constexpr (LOG) {
+#pragma unroll
+      for (int j = 0; j < P; ++j) {
+        const F2 d = f2_add(f2_make(v[2 * j], v[2 * j + 1]), nM);
+        const F2 r = f2_add(f2_make(max_nan(f2_lo(d), -64.0f), max_nan(f2_hi(d), -64.0f)), k2);
+        v[2 * j] = f2_lo(r);
+        v[2 * j + 1] = f2_hi(r);
+      }
+      pack_from_float<T>(v, o);
+    } else {
+#pragma unroll
+      for (int j = 0; j < P; ++j) {
+        const F2 t = f2_fma(f2_make(v[2 * j], v[2 * j + 1]), l2e, nM);
+        const F2 r = f2_mul(f2_make(ex2_fast(f2_lo(t)), ex2_fast(f2_hi(t))), k2);
+        v[2 * j] = f2_lo(r);
+        v[2 * j + 1] = f2_hi(r);
+      }
+      pack_from_float<T>(v, o);
+      clip_packed(o, kClip * inv);
+    }
+    st_stream(dst + i, o);
+  }
+  asm volatile("barrier.cluster.wait.aligned;" ::: "memory");  // nobody leaves while a peer may still be reading its xchg[]
+}
+
+// ---- rows_relay: long rows as a stream of chunks through persistent CTAs, one read, one write, one exp ----------------
+// The cluster kernels above stop near 4.5-4.9 TB/s on vocabulary-sized rows whatever their instruction count (the lean
+// kernel halves the instructions of the first one and gains 7 %): a CTA loads its slice, waits, computes, waits for
+// the cluster, stores and leaves — the bytes in flight per SM follow that duty cycle.  This kernel keeps the copies
+// running: a row is cut into chunks of THREADS x EPT elements, chunk g of the whole tensor goes to CTA g mod G of a
+// persistent co-resident grid (several small CTAs per SM: independent chains whose phases overlap), and every CTA
+// prefetches its next chunks into a ring of shared-memory stages with bulk copies.  Per chunk:
+//   P1  stage -> registers (EPT floats per thread); every WARP works relative to its own maximum m_w: e = exp(x - m_w)
+//       ONCE per element, kept in registers, s_w = sum e; one CTA barrier (which also frees the stage for its refill)
+//       and every warp folds the warps' pairs into the chunk's (m_c, s_c), published as one 8-byte word in a global
+//       record array (zeroed by the launcher; a published word is never all-zero);
+//   P2  one iteration LATER (after P1 of the CTA's next chunk, so the CTAs working on the same row have had a whole
+//       chunk's time to publish; the record loads are issued in the middle of that P1): M = max m_c,
+//       S = sum s_c exp(m_c - M), and the chunk is finished from registers: y = max(e * exp(m_w - M), exp(-64)) / S.
+// No cluster, no barrier between CTAs; the only cross-CTA wait is the poll, bounded by a timer (trap on expiry).  It cannot
+// deadlock: P2 of chunk h needs P1 of chunks < h + chunks_per_row, whose CTAs need P2 of chunks 2 G earlier — strictly
+// decreasing, and the cooperative launch guarantees every CTA is resident.
+constexpr int kRelayMaxStages = 8;
+
+__device__ __forceinline__ unsigned long long relay_peek(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long relay_poll(const unsigned long long* p, unsigned long long timeout_ns) {
+  unsigned long long v = relay_peek(p);
+  if (v != 0ull) return v;
+  unsigned long long t0, t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+  for (;;) {
+#pragma unroll 1
+    for (int spin = 0; spin < 64; ++spin) {
+      v = relay_peek(p);
+      if (v != 0ull) return v;
+    }
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    if (t - t0 > timeout_ns) __trap();  // a record that never arrives: fail loudly rather than hang
+  }
+}
+
+template <typename T>
+struct RelayCtx {
+  const T* x;
+  T* y;
+  int64_t dim, total;
+  int cpr, stages;
+  unsigned long long* rec;
+  float* stats;
+  unsigned long long timeout_ns;
+  T* ring;
+  uint64_t* full;
+  float2 (*wp)[32];  // [2][32]: the warps' (m_w, s_w), double-buffered by iteration parity
+};
+
+// Position of a chunk: g = row * cpr + ci.  Stepped by the grid size without a division (64-bit divisions cost ~100
+// instructions each, three per chunk in the first version of this kernel: half of its instruction count).
+struct RelayPos {
+  int64_t g, row;
+  int ci;
+  __device__ __forceinline__ void step(int64_t dg, int64_t drow, int dci, int cpr) {
+    g += dg;
+    row += drow;
+    ci += dci;
+    if (ci >= cpr) {
+      ci -= cpr;
+      ++row;
+    }
+  }
+};
+// fold (m, s) pairs held one per lane (lanes without a pair: m = -inf, s = 0) over the warp
+__device__ __forceinline__ void relay_fold(float m, float s, float& M, float& S) {
+  constexpr float kLog2e = 1.4426950408889634f;
+  M = group_reduce<32>(m, MaxF<float>());
+  S = group_reduce<32>(m == -INFINITY ? 0.f : s * ex2_fast((m - M) * kLog2e), AddF<float>());
+}
+
+// `pend_rec` / `pre`: the records of the row whose P2 follows this P1 (or nullptr), and where the first 32 are prefetched to.
+// FULL: the chunk fills the stage (every chunk of a row but its last): no bounds checks.
+template <typename T, bool LOG, int THREADS, int EPT, bool FULL>
+__device__ __forceinline__ void relay_p1(const RelayCtx<T>& c, const RelayPos& pos, const RelayPos& nxt, int n, int s, uint32_t phase,
+                                         int par, float (&e)[EPT], float& mw_out, const unsigned long long* pend_rec,
+                                         unsigned long long& pre) {
+  constexpr int V = Vec<T>::N;
+  constexpr int K = EPT / V;
+  constexpr int NW = THREADS / 32;
+  constexpr float kLog2e = 1.4426950408889634f;
+  constexpr int kCap = THREADS * EPT;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  mbar_wait(&c.full[s], phase);
+  const T* st = c.ring + (size_t)s * kCap + tid * V;
+  PackedMax<T> pmx;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    if (FULL || (k * THREADS + tid) * V < n) {
+      const Vec<T> raw = lds_vec(st + k * THREADS * V);
+      pmx.add(raw);
+      unpack_to_float<T>(raw, &e[k * V]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < V; ++i) e[k * V + i] = -INFINITY;  // exp -> 0, never stored
+    }
+  }
+  pre = 0ull;
+  if (pend_rec != nullptr && lane < c.cpr) pre = relay_peek(pend_rec + lane);  // back by the time P2 runs
+  const float mw = group_reduce<32>(pmx.get(), MaxF<float>());
+  const float nmw = mw == -INFINITY ? 0.f : -mw * kLog2e;  // -inf only: every term 0
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int j = 0; j < EPT; ++j) {
+    const float pq = ex2_fast(fmaf(e[j], kLog2e, nmw));
+    acc[j & 3] += pq;
+    if (!LOG) e[j] = pq;
+  }
+  const float sw = group_reduce<32>((acc[0] + acc[1]) + (acc[2] + acc[3]), AddF<float>());
+  if (lane == 0) c.wp[par][warp] = make_float2(mw, sw);
+  __syncthreads();  // the warps' pairs are visible; stage s is fully read
+  if (tid == 0 && nxt.g < c.total) {
+    const int64_t nstart = (int64_t)nxt.ci * kCap;
+    const int64_t nleft = c.dim - nstart;
+    const uint32_t nbytes = (uint32_t)((nleft < kCap ? nleft : kCap) * sizeof(T));
+    fence_proxy_async_smem();
+    mbar_expect_tx(&c.full[s], nbytes);
+    bulk_load_row(c.ring + (size_t)s * kCap, c.x + nxt.row * c.dim + nstart, nbytes, &c.full[s]);
+  }
+  if (warp == 0) {
+    const float2 q = lane < NW ? c.wp[par][lane] : make_float2(-INFINITY, 0.f);
+    float mc, sc;
+    relay_fold(q.x, q.y, mc, sc);
+    if (lane == 0) {
+      const unsigned long long w = (unsigned long long)__float_as_uint(mc) | ((unsigned long long)__float_as_uint(sc) << 32);
+      asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(c.rec + pos.g), "l"(w) : "memory");
+    }
+  }
+  mw_out = mw;
+}
+
+template <typename T, bool LOG, int THREADS, int EPT, bool FULL>
+__device__ __forceinline__ void relay_p2(const RelayCtx<T>& c, const RelayPos& ch, int n, const float (&e)[EPT], float mw,
+                                         unsigned long long pre) {
+  constexpr int V = Vec<T>::N;
+  constexpr int K = EPT / V;
+  constexpr int kCap = THREADS * EPT;
+  constexpr float kLog2e = 1.4426950408889634f;
+  constexpr float kClip = 1.603810890548638e-28f;  // exp(-64)
+  const int tid = threadIdx.x, lane = tid & 31;
+  // every warp gathers the row's records itself (no CTA barrier in P2)
+  const unsigned long long* rrec = c.rec + (ch.g - ch.ci);
+  float ml = -INFINITY, sl = 0.f;
+  for (int j = lane; j < c.cpr; j += 32) {
+    unsigned long long w;
+    w = (j < 32 && pre != 0ull) ? pre : relay_poll(rrec + j, c.timeout_ns);
+    const float pm = __uint_as_float((unsigned)(w & 0xffffffffull)), ps = __uint_as_float((unsigned)(w >> 32));
+    const float nm = fmaxf(ml, pm);
+    const float fa = ml == -INFINITY ? 0.f : ex2_fast((ml - nm) * kLog2e);
+    const float fb = pm == -INFINITY ? 0.f : ex2_fast((pm - nm) * kLog2e);
+    sl = fmaf(sl, fa, ps * fb);
+    ml = nm;
+  }
+  float M, S;
+  relay_fold(ml, sl, M, S);
+  if (M == -INFINITY) S = __int_as_float(0x7fc00000);  // a row of -inf: NaN, as inf - inf gives in the CPU kernel
+  if (c.stats != nullptr && ch.ci == 0 && tid == 0) { c.stats[2 * ch.row] = M; c.stats[2 * ch.row + 1] = logf(S); }
+  const float inv = row_constant<LOG, float>(S);
+  T* dst = c.y + ch.row * c.dim + (int64_t)ch.ci * kCap + tid * V;
+  const float gf = (mw == -INFINITY ? 0.f : ex2_fast((mw - M) * kLog2e)) * inv;
+  const float floor_v = kClip * inv;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    if (FULL || (k * THREADS + tid) * V < n) {
+      float r[V];
+#pragma unroll
+      for (int j = 0; j < V; ++j) r[j] = LOG ? max_nan(e[k * V + j] - M, -64.0f) - inv : e[k * V + j] * gf;
+      Vec<T> o;
+      pack_from_float<T>(r, o);
+      if constexpr (!LOG) clip_packed(o, floor_v);
+      st_stream(dst + k * THREADS * V, o);
+    }
+  }
+}
+
+template <typename T, bool LOG, int THREADS, int EPT>
+__global__ void __launch_bounds__(THREADS) softmax_rows_relay_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t dim,
+                                                                     int64_t total, int cpr, int stages,
+                                                                     unsigned long long* __restrict__ rec,
+                                                                     float* __restrict__ stats, unsigned long long timeout_ns) {
+  extern __shared__ __align__(128) unsigned char ring_raw[];
+  __shared__ uint64_t full[kRelayMaxStages];
+  __shared__ float2 wp[2][32];
+  constexpr int kCap = THREADS * EPT;
+  const int tid = threadIdx.x;
+  RelayCtx<T> c{x, y, dim, total, cpr, stages, rec, stats, timeout_ns, reinterpret_cast<T*>(ring_raw), full, wp};
+  // the grid step in (row, chunk-in-row) form, and this CTA's first chunk
+  const int64_t G = gridDim.x;
+  const int64_t drow = G / cpr;
+  const int dci = (int)(G - drow * cpr);
+  const int tail = (int)(dim - (int64_t)(cpr - 1) * kCap);  // elements of a row's last chunk
+  RelayPos pos{(int64_t)blockIdx.x, (int64_t)blockIdx.x / cpr, (int)(blockIdx.x % cpr)};
+  RelayPos nxt = pos;  // the chunk `stages` iterations ahead: what a refill loads
+  if (tid == 0) {
+    for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  for (int s = 0; s < stages; ++s) {
+    if (tid == 0 && nxt.g < total) {
+      const int64_t start = (int64_t)nxt.ci * kCap;
+      const uint32_t bytes = (uint32_t)((nxt.ci == cpr - 1 ? tail : kCap) * sizeof(T));
+      mbar_expect_tx(&full[s], bytes);
+      bulk_load_row(c.ring + (size_t)s * kCap, x + nxt.row * dim + start, bytes, &full[s]);
+    }
+    nxt.step(G, drow, dci, cpr);
+  }
+  float eA[EPT], eB[EPT];
+  float mwA = 0.f, mwB = 0.f;
+  unsigned long long preA = 0ull, preB = 0ull;
+  RelayPos chA{-1, 0, 0}, chB{-1, 0, 0};
+  int s = 0;
+  uint32_t phase = 0;
+  // one P1 (chunk `pos` into e / mw, remembering it in `ch`) followed by the P2 of the chunk before it
+#define RELAY_STEP(E1, MW1, CH1, PAR, E2, MW2, CH2, PRE2)                                                              \
+  if (pos.g < total) {                                                                                                 \
+    const unsigned long long* pend = CH2.g >= 0 ? rec + (CH2.g - CH2.ci) : nullptr;                                    \
+    if (pos.ci != cpr - 1 || tail == kCap)                                                                             \
+      relay_p1<T, LOG, THREADS, EPT, true>(c, pos, nxt, kCap, s, phase, PAR, E1, MW1, pend, PRE2);                     \
+    else                                                                                                               \
+      relay_p1<T, LOG, THREADS, EPT, false>(c, pos, nxt, tail, s, phase, PAR, E1, MW1, pend, PRE2);                    \
+    CH1 = pos;                                                                                                         \
+  } else {                                                                                                             \
+    CH1.g = -1;                                                                                                        \
+    PRE2 = 0ull;                                                                                                       \
+  }                                                                                                                    \
+  if (CH2.g >= 0) {                                                                                                    \
+    if (CH2.ci != cpr - 1 || tail == kCap) relay_p2<T, LOG, THREADS, EPT, true>(c, CH2, kCap, E2, MW2, PRE2);          \
+    else relay_p2<T, LOG, THREADS, EPT, false>(c, CH2, tail, E2, MW2, PRE2);                                           \
+  }                                                                                                                    \
+  if (CH1.g < 0) break;                                                                                                \
+  pos.step(G, drow, dci, cpr);                                                                                         \
+  nxt.step(G, drow, dci, cpr);                                                                                         \
+  if (++s == stages) { s = 0; phase ^= 1; }
+  for (;;) {
+    RELAY_STEP(eA, mwA, chA, 0, eB, mwB, chB, preB)
+    RELAY_STEP(eB, mwB, chB, 1, eA, mwA, chA, preA)
+  }
+#undef RELAY_STEP
+}
+
 // ---- rows_sweep2: long rows streamed twice, the second time out of L2 ------------------------------------------------
 // For rows that do not fit the register / shared-memory routes (and as an alternative to them for vocabulary-sized rows):
 // CTA `rank` of a cluster of cs (1..8) owns slice [rank*slice, +slice) of one row.  Sweep 1 streams the slice from HBM with
@@ -904,6 +1317,78 @@ int try_softmax_sweep2(const T* x, T* y, int64_t outer, int64_t dim, typename Ac
   }
 }
 
+// Relay route: returns < 0 when it cannot run (no cooperative launch, no stream-ordered allocator, launch failure).
+template <typename T, bool LOG, int THREADS, int EPT>
+int launch_softmax_relay(const T* x, T* y, int64_t outer, int64_t dim, float* stats, cudaStream_t st) {
+  constexpr int VN = Vec<T>::N;
+  constexpr int kCap = THREADS * EPT;
+  const int64_t cpr64 = (dim + kCap - 1) / kCap;
+  if (cpr64 > 16384 || outer <= 0) return -1;
+  const int cpr = (int)cpr64;  // kCap elements per chunk, the row's last chunk takes what is left
+  (void)VN;
+  const int64_t total = outer * cpr;
+  const size_t stage_bytes = (size_t)kCap * sizeof(T);
+  auto kern = softmax_rows_relay_kernel<T, LOG, THREADS, EPT>;
+  // CTAs per SM by registers / threads (no dynamic shared memory in the query), then the ring sized to share ~200 KB
+  int occ = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, THREADS, 0) != cudaSuccess || occ < 1) {
+    cudaGetLastError();
+    return -1;
+  }
+  occ = std::min(occ, 8);
+  int stages = 0;
+  for (; occ >= 1; --occ) {
+    stages = (int)std::min<size_t>(kRelayMaxStages, (200 * 1024 / occ - 1024) / stage_bytes);
+    if (stages >= 3) break;
+  }
+  if (occ < 1) return -1;
+  if (knobs().relay_stages >= 2 && knobs().relay_stages <= stages) stages = knobs().relay_stages;  // tuning knob
+  const int64_t grid = std::min<int64_t>(total, (int64_t)sm_count() * occ);
+  const size_t smem = stage_bytes * stages;
+  FuncAttrHold hold;  // the attribute and the launch under one lock (another thread may launch this kernel with other sizes)
+  if (!func_attr_apply(reinterpret_cast<const void*>(kern), (int)smem, 100, &hold)) {
+    cudaGetLastError();
+    return -1;
+  }
+  unsigned long long* rec = nullptr;
+  if (cudaMallocAsync(&rec, (size_t)total * sizeof(unsigned long long), st) != cudaSuccess) {
+    cudaGetLastError();
+    return -1;
+  }
+  int rc = -1;
+  if (cudaMemsetAsync(rec, 0, (size_t)total * sizeof(unsigned long long), st) == cudaSuccess) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;  // every CTA resident: the polls cannot wait for a CTA that never starts
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    const unsigned long long timeout_ns = 10ull * 1000 * 1000 * 1000;
+    if (cudaLaunchKernelEx(&cfg, kern, x, y, dim, total, cpr, stages, rec, stats, timeout_ns) == cudaSuccess)
+      rc = after_launch("softmax_rows_relay");
+  }
+  if (rc < 0) cudaGetLastError();
+  cudaFreeAsync(rec, st);
+  return rc;
+}
+template <typename T, bool LOG>
+int try_softmax_relay(const T* x, T* y, int64_t outer, int64_t dim, float* stats, cudaStream_t st) {
+  switch (knobs().relay_cfg) {  // tuning knob: threads x elements per thread
+    case 1: return launch_softmax_relay<T, LOG, 256, 32>(x, y, outer, dim, stats, st);
+    case 3: return launch_softmax_relay<T, LOG, 512, 32>(x, y, outer, dim, stats, st);
+    case 6: return launch_softmax_relay<T, LOG, 128, 32>(x, y, outer, dim, stats, st);
+    default: break;
+  }
+  // chunks that a row fills: 512 x 32 for long rows, smaller CTAs (more of them per SM) below that
+  if (dim >= 4 * 512 * 32) return launch_softmax_relay<T, LOG, 512, 32>(x, y, outer, dim, stats, st);
+  if (dim >= 4 * 256 * 32) return launch_softmax_relay<T, LOG, 256, 32>(x, y, outer, dim, stats, st);
+  return launch_softmax_relay<T, LOG, 128, 32>(x, y, outer, dim, stats, st);
+}
+
 // Cluster route: returns < 0 when the row does not fit 8 CTAs' shared memory.
 template <typename T, bool LOG>
 int try_softmax_cluster(const T* x, T* y, int64_t outer, int64_t dim, typename AccType<T>::type* stats, cudaStream_t st) {
@@ -923,7 +1408,16 @@ int try_softmax_cluster(const T* x, T* y, int64_t outer, int64_t dim, typename A
   int threads = 256;
   while (threads < 1024 && (int64_t)threads * VN * 16 < slice) threads <<= 1;
   const size_t smem = (size_t)slice * sizeof(T);
+  using A = typename AccType<T>::type;
   auto kern = softmax_rows_cluster_kernel<T, LOG>;
+  if constexpr (std::is_same<A, float>::value) {
+    if (knobs().softmax_long != 5) {  // 5: the first (online-rescale) kernel, kept for A/B runs and for double rows
+      kern = softmax_rows_cluster_lean_kernel<T, LOG>;
+      threads = 128;
+      while (threads < 256 && (int64_t)threads * VN * 8 < slice) threads <<= 1;  // 64+ elements per thread; 256 beat 512 and 128
+      if (knobs().cluster_threads >= 64) threads = knobs().cluster_threads;
+    }
+  }
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxSlice) != cudaSuccess) {
     cudaGetLastError();
     return -1;
@@ -971,11 +1465,18 @@ int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, t
     }
     if (vec) {
       // long rows: shared-memory-resident slices across a cluster (one read, rows up to 8 x 200 KB) or two sweeps with
-      // the second out of L2 (any length); PDB200_SOFTMAX_LONG = 1 / 2 forces the first / second
+      // the second out of L2 (any length); PDB200_SOFTMAX_LONG = 1 / 2 forces the first / second (3: both, without the one-exp kernel)
+      // PDB200_SOFTMAX_LONG forces a route: 1 cluster (lean kernel), 2 two-sweep, 5 cluster (first kernel), 6 relay
       const int pick = knobs().softmax_long;
       int rc = -1;
-      if (pick != 2) rc = try_softmax_cluster<T, LOG>(x, y, outer, dim, stats, st);
-      if (rc < 0 && pick != 1) rc = try_softmax_sweep2<T, LOG>(x, y, outer, dim, stats, st);
+      if constexpr (std::is_same<A, float>::value) {
+        // the relay kernel first for 4-byte elements and for rows beyond the clusters' shared memory (measured:
+        // profiles/r2_notes.txt section 5b); 16-bit rows that fit a cluster take the lean cluster kernel
+        const bool fits_cluster = (size_t)dim * sizeof(T) <= 8 * (size_t)200 * 1024;
+        if (pick == 6 || (pick == 0 && (sizeof(T) == 4 || !fits_cluster))) rc = try_softmax_relay<T, LOG>(x, y, outer, dim, stats, st);
+      }
+      if (rc < 0 && pick != 2 && pick != 6) rc = try_softmax_cluster<T, LOG>(x, y, outer, dim, stats, st);
+      if (rc < 0 && pick != 1 && pick != 5 && pick != 6) rc = try_softmax_sweep2<T, LOG>(x, y, outer, dim, stats, st);
       if (rc >= 0) return rc;
     }
     if (outer > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "softmax: too many rows for one launch");
