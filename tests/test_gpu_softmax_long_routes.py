@@ -34,3 +34,30 @@ def test_relay_geometries(cfg):
     assert r.returncode == 0, r.stderr[-3000:]
     out = json.loads(r.stdout.strip().splitlines()[-1])
     assert out["ok"], out["fails"]
+
+
+def test_relay_inside_a_cuda_graph():
+    """The default long-row route for float32 (cooperative launch, stream-ordered record array) captured into a CUDA
+    graph and replayed on new data: same bits as the eager call."""
+    import torch
+
+    import paddlepaddle_b200 as paddle
+    F = paddle.nn.functional
+    x = torch.randn(64, 40000, device="cuda")
+    y = torch.empty_like(x)
+    eager = F.softmax(x, axis=-1)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        F.softmax(x, axis=-1)  # warm-up on the capture stream
+    torch.cuda.current_stream().wait_stream(s)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        y.copy_(F.softmax(x, axis=-1))
+    g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(y, eager)
+    x.copy_(torch.randn(64, 40000, device="cuda") * 3)
+    g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(y, F.softmax(x, axis=-1))
