@@ -435,6 +435,24 @@ PDB200_API int pdb200_fused_bias_dropout_residual_layer_norm(const void* x, cons
                                                   float ln_epsilon, int dtype, void* y, void* bias_dropout_residual_out,
                                                   void* ln_mean, void* ln_variance, void* stream);
 
+/* layer_norm(x + bias + residual_alpha * residual) in one pass — paddle.incubate.nn.functional.fused_layer_norm.
+ * Replaces phi::fusion::FusedLayerNormKernel<T, GPUContext> (paddle/phi/kernels/fusion/gpu/fused_layernorm_kernel.cu:996-1216,
+ * registered as fused_bias_residual_layernorm :1222-1260), its three unquantised forms:
+ *   residual != NULL, norm_weight == norm_bias == NULL:  out = (x + bias) + residual * T(residual_alpha), every step rounded
+ *       to T (ResidualDropoutBias, fused_residual_dropout_bias.h:40-156, dropout off); no other output is written;
+ *   residual != NULL, a norm parameter given:  residual_out = the same sum; mean / variance (float, one per row) = mean and
+ *       biased variance of float(residual_out); out = T(norm_weight * (residual_out - mean) * rsqrt(variance + epsilon) +
+ *       norm_bias)  (LayernormResidualDropoutBias, fused_dropout_helper.h:428-489);
+ *   residual == NULL:  out, mean, variance = layer_norm(x) with the float parameters; bias is not read (:1204-1213).
+ * dims / rank describe x; rows = prod(dims[:begin_norm_axis]), the rest is normalised.  bias has the row length and x's
+ * dtype; norm_weight / norm_bias are FLOAT32 (LayerNormParamType<T>) and may each be NULL.  dtypes FLOAT32, FLOAT16,
+ * BFLOAT16.  The quantised outputs (int8 / float8 out with quant_scale > 0) are not on this path: the PHI binding forwards
+ * them to the in-tree kernel.  Outputs must not alias inputs or each other. */
+PDB200_API int pdb200_fused_bias_residual_layernorm(const void* x, const int64_t* dims, int rank, const void* bias,
+                                         const void* residual, const void* norm_weight, const void* norm_bias,
+                                         float epsilon, float residual_alpha, int begin_norm_axis, int dtype, void* out,
+                                         void* residual_out, void* mean, void* variance, void* stream);
+
 /* ---------------------------------------------------------------------------
  * The exchange step of sharded reductions over NVLink peer memory — one process per GPU.
  * Replaces paddle.distributed.all_reduce -> ProcessGroupNCCL::AllReduce -> ncclAllReduce

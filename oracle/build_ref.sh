@@ -57,6 +57,9 @@ for f in $TUS; do
 done
 build_one "$HERE/ref_shim.cc" "$OUT/ref_shim.o" &
 build_one "$HERE/ref_shim_family.cc" "$OUT/ref_shim_family.o" &
+# the reference's AVX-512 kernel (fused_bias_residual_layernorm on CPU): its own TU with the instruction set enabled; the
+# shim checks the CPU before entering it
+FLAGS="$FLAGS -mavx512f -mavx512dq -mavx512bw -mavx512vl" build_one "$HERE/ref_shim_avx512.cc" "$OUT/ref_shim_avx512.o" &
 wait
 g++ -shared -o "$OUT/libphi_cpu_ref.so" "$OUT"/*.o -Wl,--no-undefined -lpthread -ldl
 echo "built $OUT/libphi_cpu_ref.so"

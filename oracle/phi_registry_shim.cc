@@ -347,6 +347,12 @@ int phi_min_run(const char* name, const char* backend, int key_dtype, const char
       const std::string impl = iv[1] != 0 ? "upscale_in_train" : "downscale_in_infer";
       (*fn)(ctx, WrapIn(in[0]), WrapIn(in[1]), WrapOpt(in[2]), WrapOpt(in[3]), WrapOpt(in[4]), static_cast<float>(f[0]), iv[0] != 0, false,
             0, impl, static_cast<float>(f[1]), op(0), op(1), op(2), op(3), op(4));
+    } else if (fam == "fused_layernorm") {  // (ctx, x, bias?, residual?, norm_weight?, norm_bias?, eps, alpha, bna, qscale, qround, qmax, qmin, out, residual_out, mean, var)
+      auto* fn = kernel.GetVariadicKernelFn<void (*)(const Ctx&, const DT&, const OptT&, const OptT&, const OptT&, const OptT&, const float,
+                                                     const float, const int, const float, const int, const float, const float, DT*, DT*,
+                                                     DT*, DT*)>();
+      (*fn)(ctx, WrapIn(in[0]), WrapOpt(in[1]), WrapOpt(in[2]), WrapOpt(in[3]), WrapOpt(in[4]), static_cast<float>(f[0]),
+            static_cast<float>(f[1]), static_cast<int>(iv[0]), -1.0f, 0, 0.0f, 0.0f, op(0), op(1), op(2), op(3));
     } else {
       throw std::runtime_error("phi_min: unknown signature family '" + fam + "'");
     }

@@ -80,6 +80,8 @@ SIGNATURES = {
     "pdb200_fused_softmax_mask_upper_triangle": (_int, [_vp, _c_i64p, _int, _vp, _vp]),
     "pdb200_fused_bias_dropout_residual_layer_norm": (_int, [_vp, _vp, _c_i64p, _int, _vp, _vp, _vp, _int, ctypes.c_float, _int, _int,
                                                       ctypes.c_float, _int, _vp, _vp, _vp, _vp, _vp]),
+    "pdb200_fused_bias_residual_layernorm": (_int, [_vp, _c_i64p, _int, _vp, _vp, _vp, _vp, ctypes.c_float, ctypes.c_float, _int, _int,
+                                             _vp, _vp, _vp, _vp, _vp]),
     "pdb200_cross_entropy_workspace_bytes": (_sz, [_c_i64p, _int, _int, _int]),
     "pdb200_cross_entropy_with_softmax": (_int, [_vp, _c_i64p, _int, _vp, _int, _int, _int, _int, _int, _int, _vp, _vp, _vp, _sz,
                                                  _vp]),

@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(MAXT, MAXT <= 256 ? 2 : 1)
 fln_pipe_kernel(const T* __restrict__ x, const T* __restrict__ residual, const T* __restrict__ bias,
                 const P* __restrict__ scale, const P* __restrict__ ln_bias, T* __restrict__ y, T* __restrict__ dro,
                 float* __restrict__ mean_out, float* __restrict__ var_out, int64_t rows, int D, int stages, float factor,
-                float eps, float inv_d) {
+                float alpha, float eps, float inv_d) {
   constexpr int V = Vec<T>::N;
   constexpr int PV = Vec<P>::N;
   extern __shared__ __align__(128) unsigned char ring_raw[];
@@ -60,6 +60,7 @@ fln_pipe_kernel(const T* __restrict__ x, const T* __restrict__ residual, const T
   const uint32_t row_bytes = (uint32_t)D * sizeof(T);
   const int64_t row_step = gridDim.x;
   factor = round_to<T>(factor);  // the reference multiplies by T(factor)
+  alpha = round_to<T>(alpha);    // ... and the residual by T(residual_alpha)
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
     mbar_fence_init();
@@ -101,6 +102,10 @@ fln_pipe_kernel(const T* __restrict__ x, const T* __restrict__ residual, const T
         if constexpr (SCALED) {
 #pragma unroll
           for (int k = 0; k < V; ++k) e[c * V + k] = round_to<T>(__fmul_rn(e[c * V + k], factor));  // never fused with the add below
+        }
+        if (alpha != 1.0f) {  // fused_bias_residual_layernorm's residual_alpha (uniform branch; a product with T(1) is exact)
+#pragma unroll
+          for (int k = 0; k < V; ++k) r[k] = round_to<T>(__fmul_rn(r[k], alpha));
         }
         Vec<T> dv;
 #pragma unroll
@@ -180,7 +185,7 @@ fln_pipe_kernel(const T* __restrict__ x, const T* __restrict__ residual, const T
 template <typename T, typename P, typename U>
 __global__ void __launch_bounds__(1024) fln_rows_kernel(const T* x, const T* residual, const T* bias, const P* scale,
                                                         const P* ln_bias, T* y, T* dro, U* mean_out, U* var_out, int64_t D,
-                                                        float factor, U eps, double inv_d) {
+                                                        float factor, float alpha, U eps, double inv_d) {
   __shared__ U red[33];
   const int64_t base = (int64_t)blockIdx.x * D;
   using AddU_ = AddFlnU<U>;
@@ -190,7 +195,9 @@ __global__ void __launch_bounds__(1024) fln_rows_kernel(const T* x, const T* res
     T t = x[base + i];
     if (bias != nullptr) t = cvt<T>(add_sep(cvt<U>(t), cvt<U>(bias[i])));
     if (scaled) t = cvt<T>(mul_sep(cvt<U>(t), cvt<U>(cvt<T>((U)factor))));  // rounded on its own: never fused with the add
-    const T d = cvt<T>(add_sep(cvt<U>(t), cvt<U>(residual[base + i])));
+    T rv = residual[base + i];
+    if (alpha != 1.0f) rv = cvt<T>(mul_sep(cvt<U>(rv), cvt<U>(cvt<T>((U)alpha))));
+    const T d = cvt<T>(add_sep(cvt<U>(t), cvt<U>(rv)));
     dro[base + i] = d;  // written after the last read of x / residual at i by this thread: in-place safe
     sum += cvt<U>(d);
   }
@@ -217,7 +224,7 @@ __global__ void __launch_bounds__(1024) fln_rows_kernel(const T* x, const T* res
 
 template <typename T, typename P>
 int fln_typed(const T* x, const T* residual, const T* bias, const P* scale, const P* ln_bias, T* y, T* dro, void* mean,
-              void* var, int64_t rows, int64_t D, float factor, float epsilon, cudaStream_t st) {
+              void* var, int64_t rows, int64_t D, float factor, float alpha, float epsilon, cudaStream_t st) {
   using U = typename AccType<T>::type;
   constexpr int VN = Vec<T>::N;
   if constexpr (!std::is_same<T, double>::value) {
@@ -244,7 +251,7 @@ int fln_typed(const T* x, const T* residual, const T* bias, const P* scale, cons
         int64_t grid = (int64_t)per_sm * sm_count();
         if (grid > rows) grid = rows;
         kern<<<(unsigned)grid, threads, smem, st>>>(x, residual, bias, scale, ln_bias, y, dro, static_cast<float*>(mean),
-                                                    static_cast<float*>(var), rows, (int)D, stages, factor, epsilon,
+                                                    static_cast<float*>(var), rows, (int)D, stages, factor, alpha, epsilon,
                                                     (float)(1.0 / (double)D));
         return after_launch("fln_pipe");
       };
@@ -270,8 +277,57 @@ int fln_typed(const T* x, const T* residual, const T* bias, const P* scale, cons
   int threads = 128;
   while (threads < 1024 && threads * 8 < D) threads <<= 1;
   fln_rows_kernel<T, P, U><<<(unsigned)rows, threads, 0, st>>>(x, residual, bias, scale, ln_bias, y, dro, static_cast<U*>(mean),
-                                                               static_cast<U*>(var), D, factor, (U)epsilon, 1.0 / (double)D);
+                                                               static_cast<U*>(var), D, factor, alpha, (U)epsilon, 1.0 / (double)D);
   return after_launch("fln_rows");
+}
+
+// fused_bias_residual_layernorm without norm parameters: out = (x + bias) + residual * alpha, every step rounded to T
+// (FusedDropoutLayerNormHelper::ResidualDropoutBias with dropout off, fused_residual_dropout_bias.h:40-156).
+template <typename T, bool VECTOR>
+__global__ void __launch_bounds__(256) bias_residual_sum_kernel(const T* __restrict__ x, const T* __restrict__ residual,
+                                                                const T* __restrict__ bias, T* __restrict__ out, int64_t n_items,
+                                                                int64_t items_per_row, float alpha) {
+  using U = typename AccType<T>::type;
+  constexpr int V = VECTOR ? Vec<T>::N : 1;
+  const T alpha_t = cvt<T>((U)alpha);
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n_items; i += stride) {
+    const int64_t col = (i % items_per_row) * V;
+    if constexpr (VECTOR) {
+      Vec<T> xv = ld_stream(x + i * V);
+      const Vec<T> rv = ld_stream(residual + i * V);
+      Vec<T> bv;
+      if (bias != nullptr) bv = ld_cached(bias + col);
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        T t = xv.v[k];
+        if (bias != nullptr) t = cvt<T>(add_sep(cvt<U>(t), cvt<U>(bv.v[k])));
+        T r = rv.v[k];
+        if (alpha != 1.0f) r = cvt<T>(mul_sep(cvt<U>(r), cvt<U>(alpha_t)));
+        xv.v[k] = cvt<T>(add_sep(cvt<U>(t), cvt<U>(r)));
+      }
+      st_stream(out + i * V, xv);
+    } else {
+      T t = x[i];
+      if (bias != nullptr) t = cvt<T>(add_sep(cvt<U>(t), cvt<U>(bias[col])));
+      T r = residual[i];
+      if (alpha != 1.0f) r = cvt<T>(mul_sep(cvt<U>(r), cvt<U>(alpha_t)));
+      out[i] = cvt<T>(add_sep(cvt<U>(t), cvt<U>(r)));
+    }
+  }
+}
+
+template <typename T>
+int bias_residual_sum(const T* x, const T* residual, const T* bias, T* out, int64_t rows, int64_t D, float alpha, cudaStream_t st) {
+  constexpr int VN = Vec<T>::N;
+  const bool vec = (D % VN == 0) && is_aligned16(x) && is_aligned16(residual) && is_aligned16(out) && (!bias || is_aligned16(bias));
+  const int64_t per_row = vec ? D / VN : D;
+  const int64_t n = rows * per_row;
+  const int64_t blocks = std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, (int64_t)sm_count() * 32));
+  if (vec) bias_residual_sum_kernel<T, true><<<(unsigned)blocks, 256, 0, st>>>(x, residual, bias, out, n, per_row, alpha);
+  else bias_residual_sum_kernel<T, false><<<(unsigned)blocks, 256, 0, st>>>(x, residual, bias, out, n, per_row, alpha);
+  return after_launch("bias_residual_sum");
 }
 
 }  // namespace pdb200
@@ -309,10 +365,10 @@ extern "C" int pdb200_fused_bias_dropout_residual_layer_norm(const void* x, cons
     if (same)                                                                                                              \
       return fln_typed<T, T>(static_cast<const T*>(x), static_cast<const T*>(residual), static_cast<const T*>(bias),       \
                              static_cast<const T*>(ln_scale), static_cast<const T*>(ln_bias), static_cast<T*>(y),          \
-                             static_cast<T*>(bias_dropout_residual_out), ln_mean, ln_variance, rows, D, factor, ln_epsilon, st); \
+                             static_cast<T*>(bias_dropout_residual_out), ln_mean, ln_variance, rows, D, factor, 1.0f, ln_epsilon, st); \
     return fln_typed<T, float>(static_cast<const T*>(x), static_cast<const T*>(residual), static_cast<const T*>(bias),     \
                                static_cast<const float*>(ln_scale), static_cast<const float*>(ln_bias), static_cast<T*>(y), \
-                               static_cast<T*>(bias_dropout_residual_out), ln_mean, ln_variance, rows, D, factor, ln_epsilon, st); \
+                               static_cast<T*>(bias_dropout_residual_out), ln_mean, ln_variance, rows, D, factor, 1.0f, ln_epsilon, st); \
   }
   switch (dtype) {
     PDB_FLN_CASE(PDB200_FLOAT32)
@@ -324,9 +380,55 @@ extern "C" int pdb200_fused_bias_dropout_residual_layer_norm(const void* x, cons
                                        static_cast<const double*>(bias), static_cast<const double*>(ln_scale),
                                        static_cast<const double*>(ln_bias), static_cast<double*>(y),
                                        static_cast<double*>(bias_dropout_residual_out), ln_mean, ln_variance, rows, D, factor,
-                                       ln_epsilon, st);
+                                       1.0f, ln_epsilon, st);
   }
 #undef PDB_FLN_CASE
   return fail(PDB200_UNSUPPORTED, "fused_bias_dropout_residual_layer_norm: dtype must be float32/float64/float16/bfloat16, got code " +
                                       std::to_string(dtype));
+}
+
+
+extern "C" int pdb200_layer_norm(const void* x, const int64_t* dims, int rank, const void* scale, const void* bias, int param_dtype,
+                                 float epsilon, int begin_norm_axis, int dtype, void* y, void* mean, void* variance, void* stream);
+
+extern "C" int pdb200_fused_bias_residual_layernorm(const void* x, const int64_t* dims, int rank, const void* bias,
+                                                    const void* residual, const void* norm_weight, const void* norm_bias,
+                                                    float epsilon, float residual_alpha, int begin_norm_axis, int dtype, void* out,
+                                                    void* residual_out, void* mean, void* variance, void* stream) {
+  using namespace pdb200;
+  PDB_CHECK_ARG(rank >= 1 && rank <= PDB200_MAX_RANK && dims != nullptr, "fused_bias_residual_layernorm: rank must be in [1, 9]");
+  PDB_CHECK_ARG(begin_norm_axis >= 0 && begin_norm_axis <= rank, "fused_bias_residual_layernorm: begin_norm_axis out of range");
+  int64_t rows = 1, D = 1;
+  for (int i = 0; i < rank; ++i) {
+    PDB_CHECK_ARG(dims[i] >= 0, "fused_bias_residual_layernorm: negative dimension");
+    (i < begin_norm_axis ? rows : D) *= dims[i];
+  }
+  if (rows * D == 0) return PDB200_OK;
+  PDB_CHECK_ARG(x && out, "fused_bias_residual_layernorm: NULL tensor pointer");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const bool has_param = norm_weight != nullptr || norm_bias != nullptr;
+  if (residual == nullptr) {
+    // plain layer_norm of x with float32 parameters; `bias` is not used on this branch (fused_layernorm_kernel.cu:1204-1213)
+    PDB_CHECK_ARG(mean && variance, "fused_bias_residual_layernorm: mean / variance are outputs of the layer_norm forms");
+    return pdb200_layer_norm(x, dims, rank, norm_weight, norm_bias, PDB200_FLOAT32, epsilon, begin_norm_axis, dtype, out, mean,
+                             variance, stream);
+  }
+  switch (dtype) {
+#define PDB_FBRL_CASE(DT)                                                                                                          \
+  case DT: {                                                                                                                       \
+    using T = typename CType<DT>::type;                                                                                            \
+    if (!has_param)                                                                                                                \
+      return bias_residual_sum<T>(static_cast<const T*>(x), static_cast<const T*>(residual), static_cast<const T*>(bias),          \
+                                  static_cast<T*>(out), rows, D, residual_alpha, st);                                              \
+    PDB_CHECK_ARG(residual_out && mean && variance, "fused_bias_residual_layernorm: residual_out / mean / variance are outputs of this form"); \
+    return fln_typed<T, float>(static_cast<const T*>(x), static_cast<const T*>(residual), static_cast<const T*>(bias),             \
+                               static_cast<const float*>(norm_weight), static_cast<const float*>(norm_bias), static_cast<T*>(out), \
+                               static_cast<T*>(residual_out), mean, variance, rows, D, 1.0f, residual_alpha, epsilon, st);         \
+  }
+    PDB_FBRL_CASE(PDB200_FLOAT32)
+    PDB_FBRL_CASE(PDB200_FLOAT16)
+    PDB_FBRL_CASE(PDB200_BFLOAT16)
+#undef PDB_FBRL_CASE
+  }
+  return fail(PDB200_UNSUPPORTED, "fused_bias_residual_layernorm: dtype must be float32/float16/bfloat16, got code " + std::to_string(dtype));
 }

@@ -206,6 +206,48 @@ def fused_bias_dropout_residual_layer_norm(x, residual, bias=None, ln_scale=None
     return y
 
 
+def fused_layer_norm(x, norm_weight, norm_bias, epsilon, residual_alpha=1.0, begin_norm_axis=1, bias=None, residual=None,
+                     quant_scale=-1, quant_round_type=0, quant_max_bound=0, quant_min_bound=0, return_all=False):
+    """paddle.incubate.nn.functional.fused_layer_norm (python/paddle/incubate/nn/functional/fused_layer_norm.py:65) =
+    the op fused_bias_residual_layernorm: layer_norm(bias + residual_alpha * residual + x) in one pass; with
+    norm_weight = norm_bias = None it returns the fused sum alone.  Returns what the eager op returns: (out, residual_out,
+    mean, variance) — residual_out / mean / variance are None where the kernel does not write them.  float32 parameters
+    (LayerNormParamType); the quantised outputs (quant_scale > 0) are outside this path."""
+    _require_cuda(x, norm_weight, norm_bias, bias, residual)
+    if quant_scale > 0:
+        raise NotImplementedError("(Unimplemented) quantised fused_layer_norm outputs (quant_scale > 0) are not on this path")
+    nd = x.dim()
+    if not (0 <= begin_norm_axis <= nd) or nd < 1:
+        raise ValueError(f"(InvalidArgument) begin_norm_axis must be in [0, {nd}]")
+    D = 1
+    for s in x.shape[begin_norm_axis:]:
+        D *= int(s)
+    rows = x.numel() // D if D else 0
+    for name_, p in (("norm_weight", norm_weight), ("norm_bias", norm_bias)):
+        if p is not None and (p.numel() != D or p.dtype != torch.float32):
+            raise ValueError(f"(InvalidArgument) {name_} must be float32 with {D} elements")
+    if bias is not None and (bias.numel() != D or bias.dtype != x.dtype):
+        raise ValueError(f"(InvalidArgument) bias must have {D} elements of x's dtype")
+    if residual is not None and (tuple(residual.shape) != tuple(x.shape) or residual.dtype != x.dtype):
+        raise ValueError("(InvalidArgument) residual must have the shape and dtype of x")
+    lib = L.load()
+    cont = lambda t: t.contiguous() if t is not None else None
+    x, residual, bias, norm_weight, norm_bias = cont(x), cont(residual), cont(bias), cont(norm_weight), cont(norm_bias)
+    has_param = norm_weight is not None or norm_bias is not None
+    out = torch.empty_like(x)
+    sum_only = residual is not None and not has_param
+    res_out = torch.empty_like(x) if (residual is not None and has_param) else None
+    stats = None if sum_only else torch.empty((2, rows), dtype=torch.float32, device=x.device)
+    d, r = L.dims_array(x.shape)
+    L.check(lib.pdb200_fused_bias_residual_layernorm(
+        _ptr(x), d, r, _ptr(bias), _ptr(residual), _ptr(norm_weight), _ptr(norm_bias), ctypes.c_float(float(epsilon)),
+        ctypes.c_float(float(residual_alpha)), int(begin_norm_axis), _dtype_code(x.dtype), _ptr(out), _ptr(res_out),
+        _ptr(stats[0]) if stats is not None else None, _ptr(stats[1]) if stats is not None else None, _stream()), lib)
+    if return_all:
+        return out, res_out, (stats[0] if stats is not None else None), (stats[1] if stats is not None else None)
+    return (out, res_out) if residual is not None and has_param else out
+
+
 def softmax_(x, axis=-1, dtype=None, name=None):
     _require_cuda(x)
     lib = L.load()

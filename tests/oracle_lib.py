@@ -418,13 +418,15 @@ class Oracle:
         return out
 
     def fused_bias_dropout_residual_layer_norm(self, x, residual, bias, ln_scale, ln_bias, eps=1e-5, factor=1.0, half=None,
-                                               conv=None):
+                                               conv=None, alpha=1.0, sum_only=False):
         """Deterministic cases of layer_norm(residual + dropout(x + bias)) (keep = 1): d is formed here with the
         reference's T arithmetic — every step rounded to T (half = 'bf16' | 'fp16' | None for float32; x / residual /
         bias then arrive as uint16 bit patterns) — and the layer_norm is the reference CPU kernel on float(d).
         `conv`: the Oracle whose float <-> 16-bit conversions are used (default: this one).  Pass the restatement when this
         is the compiled reference and half == 'fp16': the reference's CPU float -> float16 TRUNCATES on builds without
         F16C (phi/common/float16.h:121-138) while the GPU rounds to nearest even.
+        alpha / sum_only: the op fused_bias_residual_layernorm (fused_layernorm_kernel.cu) built on the same helper —
+        the residual is multiplied by T(alpha) first; sum_only returns d alone (the form without norm parameters).
         -> (y float32, d as T, mean, variance)."""
         conv = conv or self
         if half is None:
@@ -441,10 +443,43 @@ class Oracle:
             t = rt(t + up(bias))
         if factor != 1.0:
             t = rt(t * rt(np.float32(factor).reshape(1))[0])
-        d = rt(t + up(residual))
+        r = up(residual)
+        if alpha != 1.0:  # fused_bias_residual_layernorm: residual * T(residual_alpha), rounded to T before the sum
+            r = rt(r * rt(np.float32(alpha).reshape(1))[0])
+        d = rt(t + r)
+        if sum_only:
+            return down(d)
         D = d.shape[-1]
         y, mean, var = self.layer_norm(d.reshape(-1, D), 1, ln_scale, ln_bias, eps)
         return y.reshape(d.shape), down(d), mean, var
+
+    def have_avx512(self):
+        return self.kind == "ref" and hasattr(self.lib, "phi_ref_have_avx512") and bool(self.lib.phi_ref_have_avx512())
+
+    def fused_layer_norm_cpu(self, x, bias, residual, norm_weight, norm_bias, eps=1e-5, alpha=1.0):
+        """The reference's own CPU kernel of fused_bias_residual_layernorm (fusion/cpu/fused_layer_norm_avx_kernel.cc, float32,
+        AVX-512 hosts only; kind == 'ref').  It forms x + alpha * residual + bias — the GPU kernel (x + bias) + alpha * residual —
+        and returns 1 / sqrt(var + eps) where the GPU kernel returns the variance: comparisons against the GPU path are
+        to rounding, not to the bit.  -> (out, residual_out | None, mean | None, rstd | None)."""
+        assert self.kind == "ref"
+        x = np.ascontiguousarray(x, np.float32)
+        rows, cols = x.shape
+        f = lambda a: None if a is None else np.ascontiguousarray(a, np.float32)
+        bias, residual, norm_weight, norm_bias = f(bias), f(residual), f(norm_weight), f(norm_bias)
+        has_param = norm_weight is not None or norm_bias is not None
+        out = np.empty_like(x)
+        ro = np.empty_like(x) if residual is not None else None
+        m = np.empty(rows, np.float32) if has_param else None
+        rs = np.empty(rows, np.float32) if has_param else None
+        P = lambda a: ctypes.c_void_p(0) if a is None else _vp(a)
+        fn = self.lib.phi_ref_fused_layer_norm
+        fn.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64] + [ctypes.c_void_p] * 4 + [ctypes.c_float, ctypes.c_float] + \
+                      [ctypes.c_void_p] * 4
+        self._check(fn(_vp(x), rows, cols, P(bias), P(residual), P(norm_weight), P(norm_bias), float(eps), float(alpha), P(out), P(ro),
+                       P(m), P(rs)))
+        if residual is not None and not has_param:
+            ro = None  # the sum-only form writes `out` alone
+        return out, ro, m, rs
 
     def _check(self, rc):
         if rc != 0:

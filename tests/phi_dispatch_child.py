@@ -275,6 +275,18 @@ def case_rows():
     got = run("fused_bias_dropout_residual_layer_norm", "fused_ln", [xf, rf, bf, ws, wb], [y, dro, mask_like, m, v], f=[0.3, 1e-5],
               iv=[1, 0])
     check("fused_bias_dropout_residual_layer_norm", [got[0], got[1], got[3], got[4]], [y, dro, m, v])
+    # fused_bias_residual_layernorm (paddle.incubate.nn.functional.fused_layer_norm): the layer_norm form with a residual,
+    # the sum-only form (no norm parameters: only `out` is allocated) and the plain form (no residual)
+    nw, nb = rnd((4096,), torch.float32) * 0.1 + 1, rnd((4096,), torch.float32) * 0.1
+    o, ro, m, v = F.fused_layer_norm(xf, nw, nb, 1e-5, residual_alpha=0.5, begin_norm_axis=1, bias=bf, residual=rf, return_all=True)
+    got = run("fused_bias_residual_layernorm", "fused_layernorm", [xf, bf, rf, nw, nb], [o, ro, m, v], f=[1e-5, 0.5], iv=[1])
+    check("fused_bias_residual_layernorm/ln+residual", got, [o, ro, m, v])
+    o = F.fused_layer_norm(xf, None, None, 1e-5, residual_alpha=0.5, begin_norm_axis=1, bias=bf, residual=rf)
+    got = run("fused_bias_residual_layernorm", "fused_layernorm", [xf, bf, rf, ABSENT, ABSENT], [o, ABSENT, ABSENT, ABSENT], f=[1e-5, 0.5], iv=[1])
+    check("fused_bias_residual_layernorm/sum only", [got[0]], [o])
+    o, _, m, v = F.fused_layer_norm(xf, nw, nb, 1e-5, begin_norm_axis=1, return_all=True)
+    got = run("fused_bias_residual_layernorm", "fused_layernorm", [xf, ABSENT, ABSENT, nw, nb], [o, ABSENT, m, v], f=[1e-5, 1.0], iv=[1])
+    check("fused_bias_residual_layernorm/plain", [got[0], got[2], got[3]], [o, m, v])
 
 
 for label, fn in (("elementwise", case_binary), ("grads", case_grads), ("reductions", case_reductions), ("rows", case_rows)):
@@ -287,6 +299,6 @@ NAMES = ["add", "multiply", "subtract", "divide", "maximum", "minimum", "less_th
          "bitwise_not", "bitwise_left_shift", "bitwise_right_shift", "scale", "cast", "where", "add_grad", "multiply_grad", "sum_grad",
          "mean_grad", "max_grad", "min_grad", "prod_grad", "cross_entropy_with_softmax", "rms_norm", "log_softmax", "sum_raw", "sum", "mean_raw", "mean", "max_raw", "max",
          "min_raw", "min", "prod", "argmax", "argmin", "softmax", "layer_norm", "softmax_grad", "layer_norm_grad", "fused_softmax_mask",
-         "fused_softmax_mask_upper_triangle", "fused_bias_dropout_residual_layer_norm"]
+         "fused_softmax_mask_upper_triangle", "fused_bias_dropout_residual_layer_norm", "fused_bias_residual_layernorm"]
 print(json.dumps({"calls": n_calls, "alloc_calls": reg.phi_min_alloc_calls(), "failed": failed,
                   "names_not_called": sorted(set(NAMES) - called)}))

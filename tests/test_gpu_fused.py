@@ -137,3 +137,87 @@ def test_fused_bias_dropout_residual_layer_norm_float64_and_errors(cpu):
         F.fused_bias_dropout_residual_layer_norm(to_dev(x), to_dev(res), dropout_rate=0.5, training=True)
     with pytest.raises(ValueError):
         F.fused_bias_dropout_residual_layer_norm(to_dev(x), to_dev(res), mode="nope", dropout_rate=0.0)
+
+
+@pytest.mark.parametrize("rows,D,dt,has_bias,alpha", [
+    (4096, 8192, "bfloat16", True, 1.0), (2048, 1024, "float32", False, 0.5), (1024, 4096, "float16", True, 0.7071),
+    (1000, 2048, "bfloat16", True, 2.0), (700, 768, "float32", True, 1.5), (7, 100, "float32", True, 0.3),
+    (33, 1000, "float16", False, 1.0),
+])
+def test_fused_layer_norm_with_residual(port, cpu, rows, D, dt, has_bias, alpha):
+    """fused_bias_residual_layernorm, the forms with a residual: layer_norm(x + bias + alpha * residual) with float32
+    parameters, and the sum alone when no norm parameter is given.  The sum is bit-exact (T arithmetic step by step, as
+    the reference's helper), the normalisation goes through the reference CPU layer_norm on float(sum)."""
+    rng = np.random.default_rng(hash((rows, D, dt, alpha)) & 0xffff)
+    x = (rng.standard_normal((rows, D)) * 2).astype(np.float32)
+    res = (rng.standard_normal((rows, D)) * 2 + 0.5).astype(np.float32)
+    bias = rng.uniform(-1, 1, D).astype(np.float32) if has_bias else None
+    w = rng.uniform(0.5, 1.5, D).astype(np.float32)
+    b = rng.uniform(-0.5, 0.5, D).astype(np.float32)
+    xb, xh, up, down = _half(port, x, dt)
+    rb = _half(port, res, dt)[0]
+    bb = _half(port, bias, dt)[0] if has_bias else None
+    wy, wd, wm, wv = cpu.fused_bias_dropout_residual_layer_norm(xb, rb, bb, w, b, 1e-5, 1.0, half=xh, conv=port, alpha=alpha)
+    dx, dr, db = to_dev(xb, xh), to_dev(rb, xh), (to_dev(bb, xh) if has_bias else None)
+    y, d, m, v = F.fused_layer_norm(dx, to_dev(w), to_dev(b), 1e-5, residual_alpha=alpha, begin_norm_axis=1, bias=db, residual=dr,
+                                    return_all=True)
+    assert np.array_equal(to_np(d), wd), "residual_out must be bit-exact"
+    if xh is None:
+        np.testing.assert_allclose(to_np(y), wy, rtol=1e-5, atol=2e-5)
+    else:
+        assert_half_close(to_np(y), down(wy), 1, f"fused_layer_norm y [{rows},{D}] {dt}", kind=xh, atol=2e-5)
+    np.testing.assert_allclose(to_np(m), wm, rtol=1e-5, atol=1e-5 * float(np.abs(up(wd)).max()))
+    np.testing.assert_allclose(to_np(v), wv, rtol=2e-5)
+    if xh is None and cpu.kind == "ref" and cpu.have_avx512():
+        # the reference's own CPU kernel of this op (AVX-512; it adds the residual before the bias and uses E[d^2] - mean^2)
+        co, cro, cm, crstd = cpu.fused_layer_norm_cpu(x, bias, res, w, b, 1e-5, alpha)
+        np.testing.assert_allclose(to_np(d), cro, rtol=1e-6, atol=1e-6)
+        np.testing.assert_allclose(to_np(y), co, rtol=1e-4, atol=1e-4)
+        np.testing.assert_allclose(1.0 / np.sqrt(to_np(v) + 1e-5), crstd, rtol=5e-5)
+    # the two-output form the Python API returns, and only one norm parameter
+    y2, d2 = F.fused_layer_norm(dx, to_dev(w), None, 1e-5, residual_alpha=alpha, bias=db, residual=dr)
+    assert np.array_equal(to_np(d2), wd)
+    wy2 = cpu.fused_bias_dropout_residual_layer_norm(xb, rb, bb, w, None, 1e-5, 1.0, half=xh, conv=port, alpha=alpha)[0]
+    if xh is None:
+        np.testing.assert_allclose(to_np(y2), wy2, rtol=1e-5, atol=2e-5)
+    else:
+        assert_half_close(to_np(y2), down(wy2), 1, "fused_layer_norm, weight only", kind=xh, atol=2e-5)
+    # no norm parameters: the fused sum alone
+    s = F.fused_layer_norm(dx, None, None, 1e-5, residual_alpha=alpha, bias=db, residual=dr)
+    assert np.array_equal(to_np(s), cpu.fused_bias_dropout_residual_layer_norm(xb, rb, bb, None, None, 1e-5, 1.0, half=xh, conv=port,
+                                                                             alpha=alpha, sum_only=True))
+
+
+def test_fused_layer_norm_plain_axes_and_errors(port, cpu):
+    """Without a residual the op is layer_norm(x) with float32 parameters (bias is not read); begin_norm_axis folds the
+    trailing dimensions; an unaligned / ragged row takes the one-CTA-per-row route."""
+    rng = np.random.default_rng(5)
+    x = (rng.standard_normal((6, 50, 40)) * 3 + 1).astype(np.float32)
+    w, b = rng.uniform(0.5, 1.5, 2000).astype(np.float32), rng.uniform(-0.5, 0.5, 2000).astype(np.float32)
+    wy, wm, wv = cpu.layer_norm(x.reshape(6, 2000), 1, w, b, 1e-6)
+    y, r, m, v = F.fused_layer_norm(to_dev(x), to_dev(w), to_dev(b), 1e-6, begin_norm_axis=1, return_all=True)
+    assert r is None
+    np.testing.assert_allclose(to_np(y).reshape(6, 2000), wy, rtol=1e-5, atol=2e-5)
+    np.testing.assert_allclose(to_np(m), wm, rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(to_np(v), wv, rtol=2e-5)
+    bits = port.f32_to_bf16(x)
+    yb = F.fused_layer_norm(to_dev(bits, "bf16"), to_dev(w), to_dev(b), 1e-6, begin_norm_axis=1,
+                            bias=to_dev(port.f32_to_bf16(b), "bf16"))  # bias ignored on this branch, as in the reference
+    wyb = cpu.layer_norm(port.bf16_to_f32(bits).reshape(6, 2000), 1, w, b, 1e-6)[0]
+    assert_half_close(to_np(yb).reshape(6, 2000), port.f32_to_bf16(wyb), 1, "fused_layer_norm plain bf16", kind="bf16", atol=2e-5)
+    # residual + begin_norm_axis = 2 + a ragged row length
+    xr = (rng.standard_normal((5, 7, 33)) * 2).astype(np.float32)
+    rr = (rng.standard_normal((5, 7, 33)) * 2).astype(np.float32)
+    w3, b3 = rng.uniform(0.5, 1.5, 33).astype(np.float32), rng.uniform(-0.5, 0.5, 33).astype(np.float32)
+    wy, wd, wm, wv = cpu.fused_bias_dropout_residual_layer_norm(xr.reshape(35, 33), rr.reshape(35, 33), None, w3, b3, 1e-5, 1.0, alpha=0.25)
+    y, d, m, v = F.fused_layer_norm(to_dev(xr), to_dev(w3), to_dev(b3), 1e-5, residual_alpha=0.25, begin_norm_axis=2,
+                                    residual=to_dev(rr), return_all=True)
+    assert np.array_equal(to_np(d).reshape(35, 33), wd)
+    np.testing.assert_allclose(to_np(y).reshape(35, 33), wy, rtol=1e-5, atol=2e-5)
+    np.testing.assert_allclose(to_np(v), wv, rtol=2e-5)
+    with pytest.raises(NotImplementedError):
+        F.fused_layer_norm(to_dev(xr), to_dev(w3), to_dev(b3), 1e-5, begin_norm_axis=2, quant_scale=0.5)
+    with pytest.raises(ValueError):
+        F.fused_layer_norm(to_dev(xr), to_dev(w3.astype(np.float64)), None, 1e-5, begin_norm_axis=2)
+    with pytest.raises(ValueError):
+        F.fused_layer_norm(to_dev(xr), to_dev(w3), None, 1e-5, begin_norm_axis=2, residual=to_dev(rr[:2]))

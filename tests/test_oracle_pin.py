@@ -266,3 +266,35 @@ def test_select_grad_restatement_equals_compiled_reference(port, ref):
     assert np.array_equal(want, np.array([[0, 3, 0, 3], [0, 0, -1, -1]], np.float32))
     for tol in (False, True):
         assert np.array_equal(port.select_grad("max", x, out, g, [1], False, tol=tol), want)
+
+
+def test_fused_layer_norm_helper_agrees_with_the_reference_avx512_kernel(port, ref):
+    """fused_bias_residual_layernorm: the test oracle is the reference's layer_norm CPU kernel applied to a sum formed the way
+    the GPU helper forms it (oracle_lib.fused_bias_dropout_residual_layer_norm, alpha=...).  The reference also ships a CPU
+    kernel of this very op (AVX-512, float32): the two must agree to rounding — it adds the residual before the bias and
+    uses E[d^2] - mean^2 — which pins the formula (what is summed, what alpha multiplies, biased variance, where epsilon
+    goes, rsqrt) to the reference's own code."""
+    if not ref.have_avx512():
+        pytest.skip("the reference's CPU kernel of this op needs AVX-512")
+    rng = np.random.default_rng(44)
+    for rows, cols, alpha, has_bias in ((37, 1000, 0.5, True), (8, 4096, 1.0, False), (64, 70, 2.0, True), (3, 16, 0.25, True)):
+        x = (rng.standard_normal((rows, cols)) * 2).astype(np.float32)
+        res = (rng.standard_normal((rows, cols)) * 2 + 0.5).astype(np.float32)
+        bias = rng.uniform(-1, 1, cols).astype(np.float32) if has_bias else None
+        w = rng.uniform(0.5, 1.5, cols).astype(np.float32)
+        b = rng.uniform(-0.5, 0.5, cols).astype(np.float32)
+        wy, wd, wm, wv = ref.fused_bias_dropout_residual_layer_norm(x, res, bias, w, b, 1e-5, 1.0, alpha=alpha)
+        out, ro, m, rstd = ref.fused_layer_norm_cpu(x, bias, res, w, b, 1e-5, alpha)
+        np.testing.assert_allclose(ro, wd, rtol=1e-6, atol=1e-6)
+        np.testing.assert_allclose(m, wm, rtol=1e-5, atol=1e-5)
+        np.testing.assert_allclose(rstd, 1.0 / np.sqrt(wv + 1e-5), rtol=2e-5)
+        np.testing.assert_allclose(out, wy, rtol=1e-4, atol=1e-4)
+        # the sum-only form and the form without a residual
+        s, ro2, _, _ = ref.fused_layer_norm_cpu(x, bias, res, None, None, 1e-5, alpha)
+        assert ro2 is None
+        np.testing.assert_allclose(s, ref.fused_bias_dropout_residual_layer_norm(x, res, bias, None, None, 1e-5, 1.0, alpha=alpha,
+                                                                                  sum_only=True), rtol=1e-6, atol=1e-6)
+        out0, _, m0, r0 = ref.fused_layer_norm_cpu(x, None, None, w, b, 1e-5, 1.0)
+        y0, mm0, vv0 = ref.layer_norm(x, 1, w, b, 1e-5)
+        np.testing.assert_allclose(out0, y0, rtol=1e-4, atol=1e-4)
+        np.testing.assert_allclose(r0, 1.0 / np.sqrt(vv0 + 1e-5), rtol=2e-5)

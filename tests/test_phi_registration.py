@@ -79,6 +79,7 @@ EXPECT = {  # the registrations of plugin/phi_kernels.cc
     "sum_grad": "float32 float64 float16 bfloat16 int32 int64", "mean_grad": "float32 float64 float16 bfloat16 int32 int64",
     "max_grad": "float32 float64 int32 int64 float16 bfloat16", "min_grad": "float32 float64 int32 int64 float16 bfloat16",
     "prod_grad": "float32 float64 int32 int64 float16 bfloat16",
+    "fused_bias_residual_layernorm": "float32 float16 bfloat16",
     "add_grad": "float32 float64 int32 int64 float16 bfloat16", "multiply_grad": "float32 float16 float64 int32 int64 bfloat16",
 }
 
