@@ -345,6 +345,17 @@ __device__ __forceinline__ A shfl_xor_any(A v, int mask) {
   return out.a;
 }
 
+template <typename A>
+__device__ __forceinline__ A shfl_idx_any(A v, int src_lane) {
+  static_assert(sizeof(A) % 4 == 0, "shuffle payload must be a multiple of 4 bytes");
+  constexpr int W = sizeof(A) / 4;
+  union { A a; uint32_t w[W]; } in, out;
+  in.a = v;
+#pragma unroll
+  for (int i = 0; i < W; ++i) out.w[i] = __shfl_sync(0xffffffffu, in.w[i], src_lane);
+  return out.a;
+}
+
 // Reduce across the G (power of two, <= 32) consecutive lanes that share a row.
 template <int G, typename A, typename Combine>
 __device__ __forceinline__ A group_reduce(A v, Combine comb) {

@@ -399,7 +399,7 @@ __global__ void __launch_bounds__(1024) ln_rows_cluster_kernel(const T* __restri
   const unsigned rank = cluster.block_rank(), cs = cluster.num_blocks();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* srow = reinterpret_cast<T*>(smem_raw);
-  __shared__ U red[33];
+  __shared__ U red[2][32];
   __shared__ U xchg[2];
   const int64_t row = (int64_t)blockIdx.x / cs;
   const int64_t begin = (int64_t)rank * slice;
@@ -414,6 +414,8 @@ __global__ void __launch_bounds__(1024) ln_rows_cluster_kernel(const T* __restri
     mbar_init(&bar, 1);
     mbar_fence_init();
   }
+  block_reduce_1sync_init(red[0], U(0));
+  block_reduce_1sync_init(red[1], U(0));
   __syncthreads();
   if (n > 0) {
     if (threadIdx.x == 0) {
@@ -428,7 +430,11 @@ __global__ void __launch_bounds__(1024) ln_rows_cluster_kernel(const T* __restri
   // (as accurate as two passes over the whole row; the first version needed two cluster barriers).
   // (whole-vector unpack, four independent chains: the sweeps were issue-bound — 87 % issue slots at 44 % DRAM,
   // profiles/r2_ln_vocab_bf16.txt)
+  // (one-barrier CTA reductions, the cluster's pairs read one per lane and folded with shuffles: the first version walked
+  // the ranks in a loop of dependent DSMEM loads in every thread and used three-barrier reductions — with 2 to 8 vectors per
+  // thread those fixed costs were most of the kernel: 1024 threads per CTA ran 3x slower than 128.)
   U acc4[4] = {U(0), U(0), U(0), U(0)};
+#pragma unroll 2
   for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
     U e[V];
     if constexpr (std::is_same<U, float>::value) {
@@ -442,9 +448,10 @@ __global__ void __launch_bounds__(1024) ln_rows_cluster_kernel(const T* __restri
     for (int k = 0; k < V; ++k) acc4[k & 3] += e[k];
   }
   U sum = (acc4[0] + acc4[1]) + (acc4[2] + acc4[3]);
-  sum = block_reduce(sum, AddU<U>(), U(0), red);
+  sum = block_reduce_1sync(sum, AddU<U>(), red[0]);
   const U mean_loc = n > 0 ? sum / (U)n : U(0);
   acc4[0] = acc4[1] = acc4[2] = acc4[3] = U(0);
+#pragma unroll 2
   for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
     U e[V];
     if constexpr (std::is_same<U, float>::value) {
@@ -461,27 +468,28 @@ __global__ void __launch_bounds__(1024) ln_rows_cluster_kernel(const T* __restri
     }
   }
   U sq = (acc4[0] + acc4[1]) + (acc4[2] + acc4[3]);
-  sq = block_reduce(sq, AddU<U>(), U(0), red);
+  sq = block_reduce_1sync(sq, AddU<U>(), red[1]);
   if (threadIdx.x == 0) {
     xchg[0] = mean_loc;
     xchg[1] = sq;
   }
   cluster.sync();
-  U total = U(0);
-  for (unsigned r = 0; r < cs; ++r) {
-    int64_t nr = D - (int64_t)r * slice;
+  // lane r < cs of every warp reads rank r's (mean, M2): one DSMEM round trip, then two shuffle folds
+  const unsigned lane = threadIdx.x & 31;
+  U mean_r = U(0), sq_r = U(0), n_r = U(0);
+  if (lane < cs) {
+    const U* q = cluster.map_shared_rank(xchg, lane);
+    mean_r = q[0];
+    sq_r = q[1];
+    int64_t nr = D - (int64_t)lane * slice;
     nr = nr < 0 ? 0 : (nr > slice ? slice : nr);
-    total += (U)nr * *cluster.map_shared_rank(&xchg[0], r);
+    n_r = (U)nr;
   }
-  const U mean = mean_of<U>(total, inv_d);
-  U total_sq = U(0);
-  for (unsigned r = 0; r < cs; ++r) {
-    int64_t nr = D - (int64_t)r * slice;
-    nr = nr < 0 ? 0 : (nr > slice ? slice : nr);
-    const U dm = *cluster.map_shared_rank(&xchg[0], r) - mean;
-    total_sq += *cluster.map_shared_rank(&xchg[1], r) + (U)nr * dm * dm;
-  }
-  const U var = mean_of<U>(total_sq, inv_d);
+  const U total = group_reduce<8>(n_r * mean_r, AddU<U>());  // cs <= 8: lanes 0..7 hold the pairs; every lane of that group gets the sum
+  const U mean = mean_of<U>(shfl_idx_any(total, 0), inv_d);
+  const U dm = mean_r - mean;
+  const U total_sq = group_reduce<8>(sq_r + n_r * dm * dm, AddU<U>());
+  const U var = mean_of<U>(shfl_idx_any(total_sq, 0), inv_d);
   const U rstd = rsqrt_exact<U>(var + eps);
   if (rank == 0 && threadIdx.x == 0) {
     if (mean_out) mean_out[row] = mean;
@@ -492,6 +500,7 @@ __global__ void __launch_bounds__(1024) ln_rows_cluster_kernel(const T* __restri
   asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
   const P* sc = scale ? scale + begin : nullptr;
   const P* bi = bias ? bias + begin : nullptr;
+#pragma unroll 2
   for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
     if constexpr (std::is_same<U, float>::value) {
       constexpr int PV = Vec<P>::N;
@@ -650,7 +659,9 @@ int layer_norm_typed(const T* x, const P* scale, const P* bias, T* y, void* mean
     const size_t row_bytes = (size_t)D * sizeof(T);
     const size_t kMaxSlice = 200 * 1024;
     int cs = 1;
-    while (cs < 8 && (row_bytes / cs > 32 * 1024 || rows * cs < 2 * (int64_t)sm_count())) cs <<= 1;
+    size_t slice_target = 32 * 1024;
+    if (knobs().cluster_slice_kb >= 4) slice_target = (size_t)knobs().cluster_slice_kb * 1024;  // tuning knob
+    while (cs < 8 && (row_bytes / cs > slice_target || rows * cs < 2 * (int64_t)sm_count())) cs <<= 1;
     int64_t slice = (D + cs - 1) / cs;
     slice = (slice + VN - 1) / VN * VN;
     auto kern = ln_rows_cluster_kernel<T, P>;
@@ -658,6 +669,7 @@ int layer_norm_typed(const T* x, const P* scale, const P* bias, T* y, void* mean
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxSlice) == cudaSuccess) {
       int threads = 256;
       while (threads < 1024 && (int64_t)threads * VN * 16 < slice) threads <<= 1;
+      if (knobs().cluster_threads >= 64) threads = knobs().cluster_threads;  // tuning knob
       cudaLaunchConfig_t cfg{};
       cfg.gridDim = dim3((unsigned)(rows * cs));
       cfg.blockDim = dim3(threads);
