@@ -44,7 +44,7 @@ template <typename T>
 __device__ __forceinline__ float round_to(float v) { return cvt<float>(cvt<T>(v)); }
 template <> __device__ __forceinline__ float round_to<float>(float v) { return v; }
 
-template <typename T, typename P, int C, bool EXACT, bool HAS_BIAS, bool SCALED, int MAXT>
+template <typename T, typename P, int C, bool EXACT, bool HAS_BIAS, int SC, int MAXT>
 __global__ void __launch_bounds__(MAXT, MAXT <= 256 ? 2 : 1)
 fln_pipe_kernel(const T* __restrict__ x, const T* __restrict__ residual, const T* __restrict__ bias,
                 const P* __restrict__ scale, const P* __restrict__ ln_bias, T* __restrict__ y, T* __restrict__ dro,
@@ -99,11 +99,11 @@ fln_pipe_kernel(const T* __restrict__ x, const T* __restrict__ residual, const T
 #pragma unroll
           for (int k = 0; k < V; ++k) e[c * V + k] = round_to<T>(__fadd_rn(e[c * V + k], b[k]));
         }
-        if constexpr (SCALED) {
+        if constexpr (SC == 1) {
 #pragma unroll
           for (int k = 0; k < V; ++k) e[c * V + k] = round_to<T>(__fmul_rn(e[c * V + k], factor));  // never fused with the add below
         }
-        if (alpha != 1.0f) {  // fused_bias_residual_layernorm's residual_alpha (uniform branch; a product with T(1) is exact)
+        if constexpr (SC == 2) {  // fused_bias_residual_layernorm's residual_alpha
 #pragma unroll
           for (int k = 0; k < V; ++k) r[k] = round_to<T>(__fmul_rn(r[k], alpha));
         }
@@ -255,16 +255,20 @@ int fln_typed(const T* x, const T* residual, const T* bias, const P* scale, cons
                                                     (float)(1.0 / (double)D));
         return after_launch("fln_pipe");
       };
-      const bool scaled = factor != 1.0f;
+      // SC: 1 a dropout factor on (x + bias), 2 a residual_alpha on the residual; the two ops that reach this kernel never
+      // need both (the one-CTA-per-row kernel below handles any combination)
+      const int sc_mode = factor != 1.0f ? 1 : (alpha != 1.0f ? 2 : 0);
       int rc = -1;
 #define PDB_FLN3(CC, MT, HB, SC) rc = exact ? launch(fln_pipe_kernel<T, P, CC, true, HB, SC, MT>) : launch(fln_pipe_kernel<T, P, CC, false, HB, SC, MT>);
 #define PDB_FLN2(CC, MT)                                           \
-  if (bias && scaled) { PDB_FLN3(CC, MT, true, true) }             \
-  else if (bias) { PDB_FLN3(CC, MT, true, false) }                 \
-  else if (scaled) { PDB_FLN3(CC, MT, false, true) }               \
-  else { PDB_FLN3(CC, MT, false, false) }
+  if (bias && sc_mode == 1) { PDB_FLN3(CC, MT, true, 1) }          \
+  else if (bias && sc_mode == 2) { PDB_FLN3(CC, MT, true, 2) }     \
+  else if (bias) { PDB_FLN3(CC, MT, true, 0) }                     \
+  else if (sc_mode == 1) { PDB_FLN3(CC, MT, false, 1) }            \
+  else if (sc_mode == 2) { PDB_FLN3(CC, MT, false, 2) }            \
+  else { PDB_FLN3(CC, MT, false, 0) }
 #define PDB_FLN(CC) if (threads <= 256) { PDB_FLN2(CC, 256) } else { PDB_FLN2(CC, 512) }
-      if (threads <= 512) {
+      if (threads <= 512 && !(factor != 1.0f && alpha != 1.0f)) {
         if (C == 4) { PDB_FLN(4) } else if (C == 2) { PDB_FLN(2) } else { PDB_FLN(1) }
       }
 #undef PDB_FLN

@@ -1383,8 +1383,8 @@ int try_softmax_relay(const T* x, T* y, int64_t outer, int64_t dim, float* stats
     case 6: return launch_softmax_relay<T, LOG, 128, 32>(x, y, outer, dim, stats, st);
     default: break;
   }
-  // chunks that a row fills: 512 x 32 for long rows, smaller CTAs (more of them per SM) below that
-  if (dim >= 4 * 512 * 32) return launch_softmax_relay<T, LOG, 512, 32>(x, y, outer, dim, stats, st);
+  // chunks that a row fills several times over: 256 x 32 elements (two CTAs per SM; 512 x 32 is no faster on vocabulary
+  // rows and slower on 1M-element rows, 0.138 vs 0.119 ms), 128 x 32 for shorter rows
   if (dim >= 4 * 256 * 32) return launch_softmax_relay<T, LOG, 256, 32>(x, y, outer, dim, stats, st);
   return launch_softmax_relay<T, LOG, 128, 32>(x, y, outer, dim, stats, st);
 }
@@ -1470,10 +1470,11 @@ int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, t
       const int pick = knobs().softmax_long;
       int rc = -1;
       if constexpr (std::is_same<A, float>::value) {
-        // the relay kernel first for 4-byte elements and for rows beyond the clusters' shared memory (measured:
-        // profiles/r2_notes.txt section 5b); 16-bit rows that fit a cluster take the lean cluster kernel
-        const bool fits_cluster = (size_t)dim * sizeof(T) <= 8 * (size_t)200 * 1024;
-        if (pick == 6 || (pick == 0 && (sizeof(T) == 4 || !fits_cluster))) rc = try_softmax_relay<T, LOG>(x, y, outer, dim, stats, st);
+        // the relay kernel first for large tensors of 4-byte elements (measured: profiles/r2_notes.txt section 5b; its
+        // record array, memset and cooperative launch cost ~15 us per call, so small tensors stay with the routes below);
+        // 16-bit rows that fit a cluster take the lean cluster kernel, longer ones the two-sweep kernel
+        const bool big = (size_t)outer * (size_t)dim * sizeof(T) >= ((size_t)128 << 20);
+        if (pick == 6 || (pick == 0 && sizeof(T) == 4 && big)) rc = try_softmax_relay<T, LOG>(x, y, outer, dim, stats, st);
       }
       if (rc < 0 && pick != 2 && pick != 6) rc = try_softmax_cluster<T, LOG>(x, y, outer, dim, stats, st);
       if (rc < 0 && pick != 1 && pick != 5 && pick != 6) rc = try_softmax_sweep2<T, LOG>(x, y, outer, dim, stats, st);
