@@ -433,42 +433,58 @@ __global__ void __launch_bounds__(1024) ln_rows_cluster_kernel(const T* __restri
   // (one-barrier CTA reductions, the cluster's pairs read one per lane and folded with shuffles: the first version walked
   // the ranks in a loop of dependent DSMEM loads in every thread and used three-barrier reductions — with 2 to 8 vectors per
   // thread those fixed costs were most of the kernel: 1024 threads per CTA ran 3x slower than 128.)
-  U acc4[4] = {U(0), U(0), U(0), U(0)};
+  // float accumulators: the sweeps run on packed fp32 pairs (FADD2 / FFMA2: the same roundings, half the issue slots — this
+  // kernel was issue-bound, 27 instructions per element at 82 % issue, profiles/r2g_ln_vocab_bf16.txt) with 32-bit indices
+  U mean_loc, sq;
+  const int ni = (int)n, stepi = (int)step, i0 = (int)threadIdx.x * V;
+  if constexpr (std::is_same<U, float>::value) {
+    F2 a2[2] = {f2_splat(0.f), f2_splat(0.f)};
 #pragma unroll 2
-  for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
-    U e[V];
-    if constexpr (std::is_same<U, float>::value) {
+    for (int i = i0; i < ni; i += stepi) {
+      float e[V];
       unpack_to_float<T>(lds_vec(srow + i), e);
-    } else {
+#pragma unroll
+      for (int j = 0; j < V / 2; ++j) a2[j & 1] = f2_add(a2[j & 1], f2_make(e[2 * j], e[2 * j + 1]));
+    }
+    const F2 s2 = f2_add(a2[0], a2[1]);
+    const float sum = block_reduce_1sync(f2_lo(s2) + f2_hi(s2), AddU<U>(), red[0]);
+    mean_loc = n > 0 ? sum / (U)n : U(0);
+    const F2 nm2 = f2_splat(-mean_loc);
+    a2[0] = a2[1] = f2_splat(0.f);
+#pragma unroll 2
+    for (int i = i0; i < ni; i += stepi) {
+      float e[V];
+      unpack_to_float<T>(lds_vec(srow + i), e);
+#pragma unroll
+      for (int j = 0; j < V / 2; ++j) {
+        const F2 d = f2_add(f2_make(e[2 * j], e[2 * j + 1]), nm2);
+        a2[j & 1] = f2_fma(d, d, a2[j & 1]);
+      }
+    }
+    const F2 q2 = f2_add(a2[0], a2[1]);
+    sq = block_reduce_1sync(f2_lo(q2) + f2_hi(q2), AddU<U>(), red[1]);
+  } else {
+    U acc4[4] = {U(0), U(0), U(0), U(0)};
+    for (int i = i0; i < ni; i += stepi) {
       const Vec<T> v = lds_vec(srow + i);
 #pragma unroll
-      for (int k = 0; k < V; ++k) e[k] = cvt<U>(v.v[k]);
+      for (int k = 0; k < V; ++k) acc4[k & 3] += cvt<U>(v.v[k]);
     }
-#pragma unroll
-    for (int k = 0; k < V; ++k) acc4[k & 3] += e[k];
-  }
-  U sum = (acc4[0] + acc4[1]) + (acc4[2] + acc4[3]);
-  sum = block_reduce_1sync(sum, AddU<U>(), red[0]);
-  const U mean_loc = n > 0 ? sum / (U)n : U(0);
-  acc4[0] = acc4[1] = acc4[2] = acc4[3] = U(0);
-#pragma unroll 2
-  for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
-    U e[V];
-    if constexpr (std::is_same<U, float>::value) {
-      unpack_to_float<T>(lds_vec(srow + i), e);
-    } else {
+    U sum = (acc4[0] + acc4[1]) + (acc4[2] + acc4[3]);
+    sum = block_reduce_1sync(sum, AddU<U>(), red[0]);
+    mean_loc = n > 0 ? sum / (U)n : U(0);
+    acc4[0] = acc4[1] = acc4[2] = acc4[3] = U(0);
+    for (int i = i0; i < ni; i += stepi) {
       const Vec<T> v = lds_vec(srow + i);
 #pragma unroll
-      for (int k = 0; k < V; ++k) e[k] = cvt<U>(v.v[k]);
+      for (int k = 0; k < V; ++k) {
+        const U d = cvt<U>(v.v[k]) - mean_loc;
+        acc4[k & 3] += d * d;
+      }
     }
-#pragma unroll
-    for (int k = 0; k < V; ++k) {
-      const U d = e[k] - mean_loc;
-      acc4[k & 3] += d * d;
-    }
+    sq = (acc4[0] + acc4[1]) + (acc4[2] + acc4[3]);
+    sq = block_reduce_1sync(sq, AddU<U>(), red[1]);
   }
-  U sq = (acc4[0] + acc4[1]) + (acc4[2] + acc4[3]);
-  sq = block_reduce_1sync(sq, AddU<U>(), red[1]);
   if (threadIdx.x == 0) {
     xchg[0] = mean_loc;
     xchg[1] = sq;
@@ -500,28 +516,44 @@ __global__ void __launch_bounds__(1024) ln_rows_cluster_kernel(const T* __restri
   asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
   const P* sc = scale ? scale + begin : nullptr;
   const P* bi = bias ? bias + begin : nullptr;
-#pragma unroll 2
-  for (int64_t i = (int64_t)threadIdx.x * V; i < n; i += step) {
-    if constexpr (std::is_same<U, float>::value) {
+  if constexpr (std::is_same<U, float>::value) {
+    // o = fma((e - mean) * rstd, w, b) with the product rounded on its own, as ln_pipe_kernel: FADD2, FMUL2, FFMA2
+    const F2 nm2 = f2_splat(-mean), r2 = f2_splat(rstd);
+    auto sweep = [&](auto has_w, auto has_b) {
       constexpr int PV = Vec<P>::N;
-      float e[V], w[V], b[V], o[V];
-      unpack_to_float<T>(lds_vec(srow + i), e);
+#pragma unroll 2
+      for (int i = i0; i < ni; i += stepi) {
+        float e[V], w[V], b[V];
+        unpack_to_float<T>(lds_vec(srow + i), e);
+        if constexpr (decltype(has_w)::value) {
 #pragma unroll
-      for (int k = 0; k < V; ++k) { w[k] = 1.f; b[k] = 0.f; }
-      if (sc != nullptr) {
+          for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(sc + i + j * PV), &w[j * PV]);
+        }
+        if constexpr (decltype(has_b)::value) {
 #pragma unroll
-        for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(sc + i + j * PV), &w[j * PV]);
+          for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(bi + i + j * PV), &b[j * PV]);
+        }
+#pragma unroll
+        for (int j = 0; j < V / 2; ++j) {
+          F2 t = f2_mul(f2_add(f2_make(e[2 * j], e[2 * j + 1]), nm2), r2);
+          if constexpr (decltype(has_w)::value && decltype(has_b)::value) t = f2_fma(t, f2_make(w[2 * j], w[2 * j + 1]), f2_make(b[2 * j], b[2 * j + 1]));
+          else if constexpr (decltype(has_w)::value) t = f2_fma(t, f2_make(w[2 * j], w[2 * j + 1]), f2_splat(0.f));
+          else if constexpr (decltype(has_b)::value) t = f2_fma(t, f2_splat(1.f), f2_make(b[2 * j], b[2 * j + 1]));
+          else t = f2_fma(t, f2_splat(1.f), f2_splat(0.f));
+          e[2 * j] = f2_lo(t);
+          e[2 * j + 1] = f2_hi(t);
+        }
+        Vec<T> ov;
+        pack_from_float<T>(e, ov);
+        st_stream(dst + i, ov);
       }
-      if (bi != nullptr) {
-#pragma unroll
-        for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(bi + i + j * PV), &b[j * PV]);
-      }
-#pragma unroll
-      for (int k = 0; k < V; ++k) o[k] = fmaf(__fmul_rn(e[k] - mean, rstd), w[k], b[k]);  // as ln_pipe_kernel
-      Vec<T> ov;
-      pack_from_float<T>(o, ov);
-      st_stream(dst + i, ov);
-    } else {
+    };
+    if (sc != nullptr && bi != nullptr) sweep(std::true_type{}, std::true_type{});
+    else if (sc != nullptr) sweep(std::true_type{}, std::false_type{});
+    else if (bi != nullptr) sweep(std::false_type{}, std::true_type{});
+    else sweep(std::false_type{}, std::false_type{});
+  } else {
+    for (int i = i0; i < ni; i += stepi) {
       const Vec<T> v = lds_vec(srow + i);
       U e[V];
 #pragma unroll
