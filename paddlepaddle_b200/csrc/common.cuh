@@ -356,6 +356,16 @@ __device__ __forceinline__ A shfl_idx_any(A v, int src_lane) {
   return out.a;
 }
 
+// Cluster barrier whose only published data was written by ONE thread (which calls this with publisher = true right after
+// its shared-memory stores): that thread fences at cluster scope, every thread arrives relaxed and waits with acquire.
+// cg::cluster_group::sync() makes EVERY thread run MEMBAR.ALL.GPU before its arrive (stall_membar ~1.2 cycles per issue in
+// the long-row kernels, profiles/r2g_softmax_vocab_bf16.txt).  All threads of a warp execute the same .aligned instructions.
+__device__ __forceinline__ void cluster_sync_published_by(bool publisher) {
+  if (publisher) asm volatile("fence.acq_rel.cluster;" ::: "memory");
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 // Reduce across the G (power of two, <= 32) consecutive lanes that share a row.
 template <int G, typename A, typename Combine>
 __device__ __forceinline__ A group_reduce(A v, Combine comb) {

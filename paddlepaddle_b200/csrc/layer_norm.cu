@@ -489,7 +489,7 @@ __global__ void __launch_bounds__(1024) ln_rows_cluster_kernel(const T* __restri
     xchg[0] = mean_loc;
     xchg[1] = sq;
   }
-  cluster.sync();
+  cluster_sync_published_by(threadIdx.x == 0);
   // lane r < cs of every warp reads rank r's (mean, M2): one DSMEM round trip, then two shuffle folds
   const unsigned lane = threadIdx.x & 31;
   U mean_r = U(0), sq_r = U(0), n_r = U(0);

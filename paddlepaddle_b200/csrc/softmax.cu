@@ -641,7 +641,7 @@ __global__ void __launch_bounds__(512) softmax_rows_cluster_lean_kernel(const T*
   const F2 a2 = f2_add(acc[0], acc[1]);
   const float sc = block_reduce_1sync(f2_lo(a2) + f2_hi(a2), AddF<float>(), red[1]);
   if (tid == 0) { xchg[0] = mc; xchg[1] = sc; }
-  cluster.sync();
+  cluster_sync_published_by(tid == 0);
   float pm = -INFINITY, ps = 0.f;
   const int lane = tid & 31;
   if (lane < (int)cs) {
