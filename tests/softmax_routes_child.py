@@ -1,5 +1,6 @@
 """Child of tests/test_gpu_softmax_long_routes.py: the long-row softmax kernels, one forced route per process
 (PDB200_SOFTMAX_LONG is read once per process).  Prints one JSON line {"ok": bool, "fails": [...]}."""
+import ctypes
 import json
 import os
 import sys
@@ -13,6 +14,7 @@ import oracle_lib as O  # noqa: E402
 from gpu_util import to_dev, to_np, ulp_diff_16  # noqa: E402
 
 import paddlepaddle_b200 as paddle  # noqa: E402
+from paddlepaddle_b200 import _lib as L  # noqa: E402
 
 F = paddle.nn.functional
 port = O.Oracle("port")
@@ -58,6 +60,21 @@ for shape in shapes:
         d = ulp_diff_16(got_h, want_h)
         if d.max() > 1:
             fails.append(f"softmax {half} {shape}: {int((d > 1).sum())} elements beyond 1 ulp, max {int(d.max())}")
+    # the forced route writes inside its output and nowhere else (compute-sanitizer is closed on this pool: canaries)
+    for tdt in (torch.float32, torch.bfloat16):
+        xt = to_dev(x).to(tdt)
+        n_el, guard = xt.numel(), 4096
+        buf = torch.empty(n_el + 2 * guard, dtype=tdt, device="cuda")
+        buf.view(torch.uint8).fill_(0xA5)
+        out = buf[guard:guard + n_el]
+        lib = L.load()
+        dd, rr = L.dims_array(shape)
+        L.check(lib.pdb200_softmax(ctypes.c_void_p(xt.data_ptr()), dd, rr, -1, L.FLOAT32 if tdt == torch.float32 else L.BFLOAT16,
+                                   ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)), lib)
+        torch.cuda.synchronize()
+        raw, es = buf.view(torch.uint8), buf.element_size()
+        if not (bool((raw[:guard * es] == 0xA5).all()) and bool((raw[(guard + n_el) * es:] == 0xA5).all())):
+            fails.append(f"softmax {tdt} {shape}: wrote outside its output")
     # in place
     t = to_dev(x)
     F.softmax_(t, axis=-1)

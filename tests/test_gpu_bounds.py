@@ -120,3 +120,57 @@ def test_softmax_and_layer_norm_stay_in_bounds(rows, D, dtype):
     L.check(lib.pdb200_softmax(_p(x3), d3, r3, 1, code, _p(out), _st()), lib)
     torch.cuda.synchronize()
     _check(buf, x3.numel(), "softmax axis=1")
+
+
+@pytest.mark.parametrize("shape,axes", [((4096, 512), (1,)), ((4096, 512), (0,)), ((257, 1031), (0,)), ((37, 96, 40), (1,)),
+                                        ((16, 13, 2048), (1,)), ((7, 33, 5, 16), (1, 3)), ((3, 70000), (1,)), ((1000003,), (0,))])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.int64])
+def test_reduction_backward_stays_in_bounds(shape, axes, dtype):
+    """max_grad / prod_grad / sum_grad on every route (outer, inner, batched inner, general; ragged and unaligned)."""
+    lib = L.load()
+    x = torch.ones(shape, device="cuda").to(dtype)
+    oshape = [s for i, s in enumerate(shape) if i not in axes]
+    out = torch.ones(oshape, device="cuda").to(dtype)
+    og = torch.full(oshape, 3, device="cuda").to(dtype)
+    n = x.numel()
+    xd, xr = L.dims_array(shape)
+    ad, an = L.dims_array(axes)
+    code = CODES[dtype]
+    for name in ("pdb200_max_grad", "pdb200_prod_grad"):
+        buf, dx = _guarded(n, dtype)
+        L.check(getattr(lib, name)(_p(x), xd, xr, _p(out), _p(og), ad, an, 0, code, _p(dx), _st()), lib)
+        torch.cuda.synchronize()
+        _check(buf, n, f"{name} {shape} {axes} {dtype}")
+        assert bool((dx == 3).all()), f"{name}: every element written (x == out == 1 everywhere)"
+    buf, dx = _guarded(n, dtype)
+    L.check(lib.pdb200_sum_grad(_p(og), xd, xr, ad, an, 0, code, _p(dx), _st()), lib)
+    torch.cuda.synchronize()
+    _check(buf, n, f"sum_grad {shape} {axes} {dtype}")
+    assert bool((dx == 3).all())
+
+
+@pytest.mark.parametrize("rows,D", [(700, 1024), (33, 1000), (7, 100), (600, 8192), (5, 20000)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_fused_layer_norm_stays_in_bounds(rows, D, dtype):
+    lib = L.load()
+    x = torch.randn((rows, D), device="cuda").to(dtype)
+    res = torch.randn((rows, D), device="cuda").to(dtype)
+    bias = torch.randn(D, device="cuda").to(dtype)
+    w = torch.ones(D, device="cuda")
+    b = torch.zeros(D, device="cuda")
+    d, r = L.dims_array((rows, D))
+    code = CODES[dtype]
+    obuf, out = _guarded(rows * D, dtype)
+    rbuf, ro = _guarded(rows * D, dtype)
+    mbuf, m = _guarded(rows, torch.float32)
+    vbuf, v = _guarded(rows, torch.float32)
+    L.check(lib.pdb200_fused_bias_residual_layernorm(_p(x), d, r, _p(bias), _p(res), _p(w), _p(b), ctypes.c_float(1e-5),
+                                                     ctypes.c_float(0.5), 1, code, _p(out), _p(ro), _p(m), _p(v), _st()), lib)
+    torch.cuda.synchronize()
+    for bb, nn, what in ((obuf, rows * D, "out"), (rbuf, rows * D, "residual_out"), (mbuf, rows, "mean"), (vbuf, rows, "variance")):
+        _check(bb, nn, f"fused_layer_norm {what} {rows}x{D} {dtype}")
+    obuf, out = _guarded(rows * D, dtype)  # the sum-only form
+    L.check(lib.pdb200_fused_bias_residual_layernorm(_p(x), d, r, _p(bias), _p(res), None, None, ctypes.c_float(1e-5),
+                                                     ctypes.c_float(0.5), 1, code, _p(out), None, None, None, _st()), lib)
+    torch.cuda.synchronize()
+    _check(obuf, rows * D, f"fused_layer_norm sum-only {rows}x{D} {dtype}")
