@@ -188,15 +188,18 @@ struct VecApply<__nv_bfloat16, DivOp<__nv_bfloat16>> {
     float fa[8], fb[8], q[8];
     unpack_to_float<__nv_bfloat16>(a, fa);
     unpack_to_float<__nv_bfloat16>(b, fb);
-    bool safe = true;
+    // the range test on the smallest and the largest magnitude of the vector (two FMNMX with |.| operands per value instead
+    // of four compares); a NaN slips through min / max, and may: the approximate quotient of a NaN is the same NaN
+    float lo = INFINITY, hi = 0.f;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       float r;
       asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fb[i]));
       q[i] = fa[i] * r;
-      const float ab = fabsf(fb[i]), aq = fabsf(q[i]);
-      safe = safe && ab > 7.9e-31f && ab < 1.2e30f && aq > 7.9e-31f && aq < 1.2e30f;
+      lo = fminf(lo, fminf(fabsf(fb[i]), fabsf(q[i])));
+      hi = fmaxf(hi, fmaxf(fabsf(fb[i]), fabsf(q[i])));
     }
+    const bool safe = lo > 7.9e-31f && hi < 1.2e30f;
     if (__builtin_expect(!safe, 0)) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) q[i] = exact_div_f32(fa[i], fb[i]);  // unrolled: the arrays must stay in registers

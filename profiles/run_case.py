@@ -100,6 +100,10 @@ elif case == "sum_grad_mid_bf16":
     x = torch.empty((256, 64, 16384), device="cuda", dtype=torch.bfloat16)
     og = torch.randn((256, 16384), device="cuda", generator=g).to(torch.bfloat16)
     fn = lambda: paddle.sum_grad(x, og, axis=1)
+elif case == "divide_bf16":
+    x = torch.randn((64, 2048, 4096), device="cuda", generator=g).to(torch.bfloat16)
+    y = (torch.rand((4096,), device="cuda", generator=g) + 0.5).to(torch.bfloat16)
+    fn = lambda: paddle.divide(x, y)
 elif case == "sum_c1":
     x = torch.rand((4096, 4096), device="cuda", generator=g)
     fn = lambda: paddle.sum(x, axis=-1)
