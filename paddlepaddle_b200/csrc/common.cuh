@@ -62,7 +62,7 @@ struct Knobs {
   int softmax_pipe_c, ln_pipe_c, rms_pipe_c, cluster_slice_kb, cluster_rows_per_cluster, softmax_long, cluster_threads, relay_stages, relay_cfg;
   int tma_cols_stages, expand_rows_per_cta, mulgrad_stages;
   long long mulgrad_splits;
-  bool no_tma_cols, no_interleave, no_fused_mulgrad, no_cluster_pipe;
+  bool no_tma_cols, no_interleave, no_fused_mulgrad, no_cluster_pipe, no_cols_cluster;
   long long peer_timeout_ms;
   long long rows_warp_max_bytes;
 };
@@ -96,6 +96,7 @@ inline const Knobs& knobs() {
     r.no_interleave = set("PDB200_NO_INTERLEAVE");
     r.no_fused_mulgrad = set("PDB200_NO_FUSED_MULGRAD");
     r.no_cluster_pipe = set("PDB200_NO_CLUSTER_PIPE");
+    r.no_cols_cluster = set("PDB200_NO_COLS_CLUSTER");
     r.peer_timeout_ms = num("PDB200_PEER_TIMEOUT_MS");
     r.rows_warp_max_bytes = num("PDB200_ROWS_WARP_MAX_BYTES");
     return r;

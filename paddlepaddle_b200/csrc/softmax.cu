@@ -573,6 +573,39 @@ __device__ __forceinline__ void clip_packed(Vec<float>& o, float floor_v) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) o.v[i] = max_nan(o.v[i], floor_v);
 }
+// elementwise maximum of two raw vectors (NaN operands ignored, like fmaxf) and the same with NaN kept
+__device__ __forceinline__ void vmax_raw(Vec<__nv_bfloat16>& a, const Vec<__nv_bfloat16>& b) {
+  __nv_bfloat162* pa = reinterpret_cast<__nv_bfloat162*>(&a);
+  const __nv_bfloat162* pb = reinterpret_cast<const __nv_bfloat162*>(&b);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) pa[i] = __hmax2(pa[i], pb[i]);
+}
+__device__ __forceinline__ void vmax_raw(Vec<__half>& a, const Vec<__half>& b) {
+  __half2* pa = reinterpret_cast<__half2*>(&a);
+  const __half2* pb = reinterpret_cast<const __half2*>(&b);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) pa[i] = __hmax2(pa[i], pb[i]);
+}
+__device__ __forceinline__ void vmax_raw(Vec<float>& a, const Vec<float>& b) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) a.v[i] = fmaxf(a.v[i], b.v[i]);
+}
+__device__ __forceinline__ void vclip_raw(Vec<__nv_bfloat16>& a, const Vec<__nv_bfloat16>& floor_v) {
+  __nv_bfloat162* pa = reinterpret_cast<__nv_bfloat162*>(&a);
+  const __nv_bfloat162* pb = reinterpret_cast<const __nv_bfloat162*>(&floor_v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) pa[i] = __hmax2_nan(pa[i], pb[i]);
+}
+__device__ __forceinline__ void vclip_raw(Vec<__half>& a, const Vec<__half>& floor_v) {
+  __half2* pa = reinterpret_cast<__half2*>(&a);
+  const __half2* pb = reinterpret_cast<const __half2*>(&floor_v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) pa[i] = __hmax2_nan(pa[i], pb[i]);
+}
+__device__ __forceinline__ void vclip_raw(Vec<float>& a, const Vec<float>& floor_v) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) a.v[i] = max_nan(a.v[i], floor_v.v[i]);
+}
 __device__ __forceinline__ float ex2_fast(float t) {
   float r;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(t));
@@ -1442,6 +1475,243 @@ int try_softmax_cluster(const T* x, T* y, int64_t outer, int64_t dim, typename A
   return after_launch("softmax_rows_cluster");
 }
 
+// ---- cols_cluster: softmax along a middle axis, one read: a column tile held in the shared memory of a cluster ---------
+// softmax_cols_tile_kernel reads x twice, and on a tensor larger than L2 both reads come from HBM (DRAM read = 2 x input,
+// profiles/r2_softmax_cols_bf16.txt).  (Tried first: the same two sweeps with narrow tiles and a capped number of resident
+// CTAs so that the second sweep would hit L2 — 0.76-1.18 ms against 0.65: one or two CTAs per SM cannot overlap one tile's
+// reads with another's writes.)  Here a cluster of cs <= 8 CTAs owns a tile of 16 vectors (256 bytes) x all `dim` rows; CTA
+// `rank` keeps rows [rank*TR, +TR) of it in shared memory (<= 64 KB), forms the column maxima and the sums relative to ITS
+// OWN maxima, publishes the two 16*V-float arrays, and after ONE cluster barrier every CTA folds the cs pairs per column
+// through DSMEM and writes its rows: x is read once.  256 threads = 16 vector lanes x 16 row lanes.
+template <typename T, bool LOG>
+__global__ void __launch_bounds__(256) softmax_cols_cluster_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t dim,
+                                                                   int64_t inner, int64_t col_tiles, int tr,
+                                                                   float* __restrict__ stats) {
+  namespace cg = cooperative_groups;
+  constexpr int V = Vec<T>::N;
+  constexpr int TCV = 16;            // vectors per row segment
+  constexpr int RL = 16;             // row lanes
+  constexpr float kLog2e = 1.4426950408889634f;
+  constexpr float kClip = 1.603810890548638e-28f;  // exp(-64)
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned rank = cluster.block_rank(), cs = cluster.num_blocks();
+  extern __shared__ __align__(16) unsigned char cc_raw[];
+  T* tile = reinterpret_cast<T*>(cc_raw);                     // [tr][TCV * V]
+  __shared__ __align__(16) float part[8][TCV * V];            // per-warp column partials; later [0]: the columns' maxima
+  __shared__ __align__(16) float part2[1][TCV * V];           // the columns' sums
+  __shared__ __align__(16) float xm[TCV * V], xs[TCV * V];    // this CTA's column (max, sum): read by the peers
+  const int tid = threadIdx.x, vx = tid & 15, ry = tid >> 4, warp = tid >> 5;
+  const int64_t cl = (int64_t)blockIdx.x / cs;
+  const int64_t o = cl / col_tiles, ct = cl - o * col_tiles;
+  const int64_t col = (ct * TCV + vx) * V;
+  const bool active = col < inner;
+  const int row0 = (int)rank * tr;
+  int nrows = (int)dim - row0;
+  nrows = nrows < 0 ? 0 : (nrows > tr ? tr : nrows);
+  const T* src = x + (o * dim + row0) * inner + col;
+  T* dst = y + (o * dim + row0) * inner + col;
+  // phase 1: HBM -> shared (U loads in flight per thread), column maxima on the way (elementwise on the raw vectors)
+  float m[V];
+  {
+    Vec<T> rmax;
+    float ninf[V];
+#pragma unroll
+    for (int k = 0; k < V; ++k) ninf[k] = -INFINITY;
+    pack_from_float<T>(ninf, rmax);
+    if (active) {
+      // every row segment of this thread as a 16-byte asynchronous copy straight into the tile (no registers: all of the
+      // CTA's 64 KB are in flight at once; with 8 register-staged loads per thread the kernel ran 0.59 ms, not faster than
+      // the two-sweep kernel), then the maxima from shared memory
+      for (int r = ry; r < nrows; r += RL) {
+        const unsigned dsts = smem_u32(tile + ((size_t)r * TCV + vx) * V);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dsts), "l"(src + (int64_t)r * inner) : "memory");
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+#pragma unroll 4
+      for (int r = ry; r < nrows; r += RL) vmax_raw(rmax, lds_vec(tile + ((size_t)r * TCV + vx) * V));
+    }
+    unpack_to_float<T>(rmax, m);
+  }
+  // column maxima of this CTA: the two row lanes of a warp by shuffle, the 8 warps through shared memory
+#pragma unroll
+  for (int k = 0; k < V; ++k) m[k] = fmaxf(m[k], __shfl_xor_sync(0xffffffffu, m[k], 16));
+  if ((tid & 31) < 16) {
+#pragma unroll
+    for (int k = 0; k < V; ++k) part[warp][vx * V + k] = m[k];
+  }
+  __syncthreads();  // also: the tile is complete
+  float nml[V];
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    float g = part[0][vx * V + k];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) g = fmaxf(g, part[w][vx * V + k]);
+    m[k] = g;
+    nml[k] = g == -INFINITY ? 0.f : -g * kLog2e;  // a column slice of -inf only: every term 0
+  }
+  __syncthreads();  // part[] is reused for the sums
+  // phase 2: sums relative to this CTA's own maxima
+  float s[V];
+  {
+    const F2 l2e = f2_splat(kLog2e);
+    F2 n2[V / 2], s2[V / 2];
+#pragma unroll
+    for (int j = 0; j < V / 2; ++j) {
+      n2[j] = f2_make(nml[2 * j], nml[2 * j + 1]);
+      s2[j] = f2_splat(0.f);
+    }
+    if (active) {
+#pragma unroll 2
+      for (int r = ry; r < nrows; r += RL) {
+        float v[V];
+        unpack_to_float<T>(lds_vec(tile + ((size_t)r * TCV + vx) * V), v);
+#pragma unroll
+        for (int j = 0; j < V / 2; ++j) {
+          const F2 t = f2_fma(f2_make(v[2 * j], v[2 * j + 1]), l2e, n2[j]);
+          s2[j] = f2_add(s2[j], f2_make(ex2_fast(f2_lo(t)), ex2_fast(f2_hi(t))));
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < V / 2; ++j) {
+      s[2 * j] = f2_lo(s2[j]);
+      s[2 * j + 1] = f2_hi(s2[j]);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < V; ++k) s[k] += __shfl_xor_sync(0xffffffffu, s[k], 16);
+  if ((tid & 31) < 16) {
+#pragma unroll
+    for (int k = 0; k < V; ++k) part[warp][vx * V + k] = s[k];
+  }
+  __syncthreads();
+  if (ry == 0) {
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+      float g = part[0][vx * V + k];
+#pragma unroll
+      for (int w = 1; w < 8; ++w) g += part[w][vx * V + k];
+      xm[vx * V + k] = m[k];
+      xs[vx * V + k] = g;
+    }
+  }
+  cluster.sync();
+  // the cluster's pairs, folded ONCE per column: thread c < 16 * V reads column c's (max, sum) of every rank through DSMEM
+  // and leaves the column's (M, S) in local shared memory for the threads that own it.  (Earlier versions: every thread
+  // read all ranks with scalar loads — 32768 remote words per CTA, 5.1 ms; then every thread folded its 8 columns x 8 ranks
+  // itself — 6 instructions and one extra ex2 per ELEMENT of its 128-element share, 0.72 ms.)
+  if (tid < TCV * V) {
+    float Mc = -INFINITY, Sc = 0.f;
+    for (unsigned r = 0; r < cs; ++r) {
+      const float a = cluster.map_shared_rank(xm, r)[tid], b = cluster.map_shared_rank(xs, r)[tid];
+      const float nm = fmaxf(Mc, a);
+      const float f1 = Mc == -INFINITY ? 0.f : ex2_fast((Mc - nm) * kLog2e);
+      const float f2 = a == -INFINITY ? 0.f : ex2_fast((a - nm) * kLog2e);
+      Sc = fmaf(Sc, f1, b * f2);
+      Mc = nm;
+    }
+    part[0][tid] = Mc;
+    part2[0][tid] = Sc;
+  }
+  __syncthreads();
+  float M[V], S[V];
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    M[k] = part[0][vx * V + k];
+    S[k] = part2[0][vx * V + k];
+  }
+  // every peer array has been read: arrive for the exit barrier (relaxed), wait for it after the stores
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+  float inv[V], floor_v[V];
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    if (M[k] == -INFINITY) S[k] = __int_as_float(0x7fc00000);  // a column of -inf: NaN, as inf - inf gives in the CPU kernel
+    inv[k] = row_constant<LOG, float>(S[k]);
+    floor_v[k] = kClip * inv[k];
+    nml[k] = -M[k] * kLog2e;
+    if (stats != nullptr && rank == 0 && ry == 0 && active) {
+      stats[2 * (o * inner + col + k)] = M[k];
+      stats[2 * (o * inner + col + k) + 1] = logf(S[k]);
+    }
+  }
+  if (active) {
+    const F2 l2e = f2_splat(kLog2e);
+    F2 n2[V / 2], i2[V / 2];
+#pragma unroll
+    for (int j = 0; j < V / 2; ++j) {
+      n2[j] = LOG ? f2_make(-M[2 * j], -M[2 * j + 1]) : f2_make(nml[2 * j], nml[2 * j + 1]);
+      i2[j] = LOG ? f2_make(-inv[2 * j], -inv[2 * j + 1]) : f2_make(inv[2 * j], inv[2 * j + 1]);
+    }
+    Vec<T> floor_raw;
+    pack_from_float<T>(floor_v, floor_raw);  // the -64 clip on the rounded output (rounding is monotone)
+#pragma unroll 2
+    for (int r = ry; r < nrows; r += RL) {
+      float v[V];
+      unpack_to_float<T>(lds_vec(tile + ((size_t)r * TCV + vx) * V), v);
+#pragma unroll
+      for (int j = 0; j < V / 2; ++j) {
+        F2 q;
+        if constexpr (LOG) {
+          const F2 d = f2_add(f2_make(v[2 * j], v[2 * j + 1]), n2[j]);
+          q = f2_add(f2_make(max_nan(f2_lo(d), -64.0f), max_nan(f2_hi(d), -64.0f)), i2[j]);
+        } else {
+          const F2 t = f2_fma(f2_make(v[2 * j], v[2 * j + 1]), l2e, n2[j]);
+          q = f2_mul(f2_make(ex2_fast(f2_lo(t)), ex2_fast(f2_hi(t))), i2[j]);
+        }
+        v[2 * j] = f2_lo(q);
+        v[2 * j + 1] = f2_hi(q);
+      }
+      Vec<T> ov;
+      pack_from_float<T>(v, ov);
+      if constexpr (!LOG) vclip_raw(ov, floor_raw);
+      st_stream(dst + (int64_t)r * inner, ov);
+    }
+  }
+  asm volatile("barrier.cluster.wait.aligned;" ::: "memory");  // nobody leaves while a peer may still be reading its arrays
+}
+
+// Returns < 0 when the shape does not suit the kernel (the caller falls back to softmax_cols_tile_kernel).
+template <typename T, bool LOG>
+int try_softmax_cols_cluster(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, float* stats, cudaStream_t st) {
+  constexpr int VN = Vec<T>::N;
+  constexpr int TCV = 16;
+  const size_t total = (size_t)outer * dim * inner * sizeof(T);
+  // small tensors are served out of L2 by the two-sweep kernel; short axes leave the CTAs too little to do
+  if (total <= ((size_t)96 << 20) || dim < 256 || dim > 8 * 256 || inner / VN < TCV) return -1;
+  int cs = 1;
+  while (cs < 8 && (dim + cs - 1) / cs > 256) cs <<= 1;
+  const int tr = (int)((dim + cs - 1) / cs);
+  if (tr > 256) return -1;
+  const int64_t ctiles = (inner / VN + TCV - 1) / TCV;
+  const int64_t nblk = ctiles * outer * cs;
+  if (nblk > 0x7fffffffLL) return -1;
+  const size_t smem = (size_t)tr * TCV * 16;
+  auto kern = softmax_cols_cluster_kernel<T, LOG>;
+  FuncAttrHold hold;
+  if (!func_attr_apply(reinterpret_cast<const void*>(kern), (int)(256 * TCV * 16), 100, &hold)) {
+    cudaGetLastError();
+    return -1;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)nblk);
+  cfg.blockDim = dim3(256);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cs;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if (cudaLaunchKernelEx(&cfg, kern, x, y, dim, inner, ctiles, tr, stats) != cudaSuccess) {
+    cudaGetLastError();
+    return -1;
+  }
+  return after_launch("softmax_cols_cluster");
+}
+
 template <typename T, bool LOG>
 int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, typename AccType<T>::type* stats,
                   cudaStream_t st) {
@@ -1501,6 +1771,10 @@ int softmax_typed(const T* x, T* y, int64_t outer, int64_t dim, int64_t inner, t
     // vector route: 16-byte loads along `inner`; in place is fine (sweep 2 reads and writes each chunk in one thread, after
     // sweep 1 of the whole CTA tile is done)
     if (inner % VN == 0 && is_aligned16(x) && is_aligned16(y) && dim >= 2) {
+      if (!knobs().no_cols_cluster) {
+        const int rc = try_softmax_cols_cluster<T, LOG>(x, y, outer, dim, inner, stats, st);
+        if (rc >= 0) return rc;
+      }
       const int64_t ctiles = (inner / VN + 31) / 32;
       const int64_t nblk = ctiles * outer;
       if (nblk <= 0x7fffffffLL) {

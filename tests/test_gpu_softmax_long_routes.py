@@ -61,3 +61,49 @@ def test_relay_inside_a_cuda_graph():
     g.replay()
     torch.cuda.synchronize()
     assert torch.equal(y, F.softmax(x, axis=-1))
+
+
+@pytest.mark.parametrize("shape,dt", [((8, 2048, 4096), "bfloat16"), ((24, 1000, 2056), "float32"), ((40, 300, 4104), "float16")])
+def test_strided_axis_cluster_route(shape, dt):
+    """softmax / log_softmax along a middle axis of a tensor larger than L2: the column tile is held in the shared memory
+    of a cluster (csrc/softmax.cu softmax_cols_cluster_kernel) and x is read once.  Against a float64 statement of the
+    reference's formula (shifted logits clipped at -64); ragged row slices (1000 = 4 x 250, 300 = 2 x 150), a partial last
+    column tile, a column of -inf, a NaN, columns far below the clip."""
+    import numpy as np
+    import torch
+
+    import paddlepaddle_b200 as paddle
+    from gpu_util import ulp_diff_16
+    F = paddle.nn.functional
+    tdt = getattr(torch, dt)
+    g = torch.Generator(device="cuda")
+    g.manual_seed(7)
+    x = (torch.randn(shape, device="cuda", generator=g) * 3).to(tdt)
+    x[0, :, 5] = float("-inf")          # a whole column of -inf -> NaN column
+    x[1, 7, 9] = float("nan")           # one NaN -> NaN column
+    x[2, : shape[1] // 2, 11] -= 100.0  # half a column far below the clip
+    x[3, 3, :] = 50.0                   # one dominant row
+    y = F.softmax(x, axis=1)
+    ly = F.log_softmax(x, axis=1)
+    for o in (0, 1, 2, 3, shape[0] - 1):  # whole [dim, inner] slabs against float64
+        xs = x[o].double().cpu().numpy()
+        with np.errstate(invalid="ignore"):
+            d = np.maximum(xs - xs.max(axis=0, keepdims=True), -64.0)
+        e = np.exp(d)
+        s = e.sum(axis=0, keepdims=True)
+        want, lwant = e / s, d - np.log(s)
+        got, lgot = y[o].float().cpu().numpy(), ly[o].float().cpu().numpy()
+        nanc = np.isnan(want).any(axis=0)
+        assert np.isnan(got[:, nanc]).all() and np.isnan(lgot[:, nanc]).all()
+        if dt == "float32":
+            np.testing.assert_allclose(got[:, ~nanc], want[:, ~nanc], rtol=1e-5, atol=1e-30)
+            np.testing.assert_allclose(lgot[:, ~nanc], lwant[:, ~nanc], rtol=1e-5, atol=2e-5)
+        else:
+            wt = torch.from_numpy(want[:, ~nanc]).to(tdt).view(torch.int16).numpy().view(np.uint16)
+            gt = y[o][:, torch.from_numpy(~nanc).cuda()].contiguous().view(torch.int16).cpu().numpy().view(np.uint16)
+            assert ulp_diff_16(gt, wt).max() <= 1
+            np.testing.assert_allclose(lgot[:, ~nanc], lwant[:, ~nanc], rtol=1e-2, atol=5e-2)
+    # in place
+    x2 = x.clone()
+    F.softmax_(x2, axis=1)
+    assert torch.equal(torch.nan_to_num(x2.float(), nan=-1.0), torch.nan_to_num(y.float(), nan=-1.0))
