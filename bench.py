@@ -414,6 +414,21 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
             lambda: F.fused_bias_dropout_residual_layer_norm(xr_, rr_, br_, wr_, br_, dropout_rate=0.0), 65536 * 8192,
             key="fused_bias_dropout_residual_layer_norm_bf16")
         del br_
+    if hasattr(F, "fused_layer_norm"):
+        nw_ = torch.rand(8192, device="cuda", generator=g) + 0.5
+        nb_ = torch.rand(8192, device="cuda", generator=g) - 0.5
+        bb_ = (torch.rand(8192, device="cuda", generator=g) - 0.5).to(torch.bfloat16)
+        rec("next: fused_layer_norm (fused_bias_residual_layernorm) bf16 [65536,8192], residual_alpha 0.5 (out + residual_out)",
+            4 * 65536 * 8192 * 2 + 8192 * 2 + 2 * 8192 * 4 + 2 * 65536 * 4,
+            lambda: F.fused_layer_norm(xr_, nw_, nb_, 1e-5, residual_alpha=0.5, bias=bb_, residual=rr_), 65536 * 8192,
+            key="fused_bias_residual_layernorm_bf16")
+        del nw_, nb_, bb_
+    if hasattr(paddle, "max_grad"):
+        mo_ = paddle.max(xr_, axis=-1)
+        mg_ = torch.randn(65536, device="cuda", generator=g).to(torch.bfloat16)
+        rec("next: max_grad bf16 [65536,8192] axis=-1 (x, out, out_grad -> x_grad in one pass)", 2 * 65536 * 8192 * 2 + 2 * 65536 * 2,
+            lambda: paddle.max_grad(xr_, mo_, mg_, axis=-1), 65536 * 8192, key="max_grad_bf16")
+        del mo_, mg_
     del xr_, rr_, wr_
     rec("next: softmax_grad bf16 [8,32,2048,2048] axis=-1", 3 * n * 2, lambda: F.softmax_grad(yy, dyy, axis=-1), n)
     del yy, dyy
@@ -421,12 +436,16 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
     xv = torch.randn((4096, 128256), device="cuda", generator=g).to(torch.bfloat16)
     rec("route: softmax bf16 [4096,128256] (cluster route, 250 KB rows)", 2 * xv.numel() * 2, lambda: F.softmax(xv, axis=-1),
         xv.numel(), key="softmax_bf16_vocab_128256")
+    xv32 = xv.float()
+    rec("route: softmax fp32 [4096,128256] (relay route: persistent CTAs, chunk records)", 2 * xv32.numel() * 4,
+        lambda: F.softmax(xv32, axis=-1), xv32.numel(), key="softmax_fp32_vocab_128256")
+    del xv32
     wv = (torch.rand(128256, device="cuda", generator=g) + 0.5).to(torch.bfloat16)
     rec("route: layer_norm bf16 [4096,128256] (cluster route)", 2 * xv.numel() * 2 + 2 * 128256 * 2 + 2 * 4096 * 4,
         lambda: F.layer_norm(xv, [128256], wv, wv), xv.numel(), key="layer_norm_bf16_vocab_128256")
     del xv, wv
     xv = torch.randn((64, 1048576), device="cuda", generator=g).to(torch.bfloat16)
-    rec("route: softmax bf16 [64,1048576] (cluster route, 2 MB rows)", 2 * xv.numel() * 2, lambda: F.softmax(xv, axis=-1),
+    rec("route: softmax bf16 [64,1048576] (two-sweep route, 2 MB rows)", 2 * xv.numel() * 2, lambda: F.softmax(xv, axis=-1),
         xv.numel(), key="softmax_bf16_row_1M")
     del xv
     rows, D = 65536, 8192
