@@ -59,10 +59,10 @@ inline int sm_count() {
 // ----------------------------------------------------------------------------
 struct Knobs {
   int pipe_contig, pipe_max_ctas, pipe_max_stages, pipe_inflight_kb, pipe_rows_per_cta;
-  int softmax_pipe_c, ln_pipe_c, rms_pipe_c, cluster_slice_kb, cluster_rows_per_cluster, softmax_long, cluster_threads, relay_stages, relay_cfg;
+  int softmax_pipe_c, ln_pipe_c, rms_pipe_c, cluster_slice_kb, cluster_rows_per_cluster, softmax_long, cluster_threads, relay_stages, relay_cfg, ln_param_smem;
   int tma_cols_stages, expand_rows_per_cta, mulgrad_stages;
   long long mulgrad_splits;
-  bool no_tma_cols, no_interleave, no_fused_mulgrad, no_cluster_pipe, no_cols_cluster;
+  bool no_tma_cols, no_interleave, no_fused_mulgrad, no_cluster_pipe, no_cols_cluster, no_fln_param_smem;
   long long peer_timeout_ms;
   long long rows_warp_max_bytes;
 };
@@ -86,6 +86,7 @@ inline const Knobs& knobs() {
     r.cluster_threads = (int)num("PDB200_CLUSTER_THREADS");
     r.relay_stages = (int)num("PDB200_RELAY_STAGES");
     r.relay_cfg = (int)num("PDB200_RELAY_CFG");
+    r.ln_param_smem = (int)num("PDB200_LN_PARAM_SMEM");
     r.cluster_rows_per_cluster = (int)num("PDB200_CLUSTER_ROWS");
     r.softmax_long = (int)num("PDB200_SOFTMAX_LONG");
     r.tma_cols_stages = (int)num("PDB200_TMA_COLS_STAGES");
@@ -97,6 +98,7 @@ inline const Knobs& knobs() {
     r.no_fused_mulgrad = set("PDB200_NO_FUSED_MULGRAD");
     r.no_cluster_pipe = set("PDB200_NO_CLUSTER_PIPE");
     r.no_cols_cluster = set("PDB200_NO_COLS_CLUSTER");
+    r.no_fln_param_smem = set("PDB200_NO_FLN_PARAM_SMEM");
     r.peer_timeout_ms = num("PDB200_PEER_TIMEOUT_MS");
     r.rows_warp_max_bytes = num("PDB200_ROWS_WARP_MAX_BYTES");
     return r;

@@ -44,7 +44,30 @@ template <typename T>
 __device__ __forceinline__ float round_to(float v) { return cvt<float>(cvt<T>(v)); }
 template <> __device__ __forceinline__ float round_to<float>(float v) { return v; }
 
-template <typename T, typename P, int C, bool EXACT, bool HAS_BIAS, int SC, int MAXT>
+// the same rounding for two values at once: one packed conversion (F2FP, ALU pipe) instead of two single ones (F2F, XU pipe —
+// with the residual_alpha step the kernel ran 0.98 ms against 0.82 without it)
+template <typename T>
+__device__ __forceinline__ void round_pair_to(float& a, float& b) {
+  a = round_to<T>(a);
+  b = round_to<T>(b);
+}
+template <>
+__device__ __forceinline__ void round_pair_to<__nv_bfloat16>(float& a, float& b) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  const uint32_t w = *reinterpret_cast<const uint32_t*>(&h);
+  a = __uint_as_float(w << 16);
+  b = __uint_as_float(w & 0xffff0000u);
+}
+template <>
+__device__ __forceinline__ void round_pair_to<__half>(float& a, float& b) {
+  const float2 f = __half22float2(__floats2half2_rn(a, b));
+  a = f.x;
+  b = f.y;
+}
+template <>
+__device__ __forceinline__ void round_pair_to<float>(float&, float&) {}
+
+template <typename T, typename P, int C, bool EXACT, bool HAS_BIAS, int SC, int MAXT, bool PSM = false>
 __global__ void __launch_bounds__(MAXT, MAXT <= 256 ? 2 : 1)
 fln_pipe_kernel(const T* __restrict__ x, const T* __restrict__ residual, const T* __restrict__ bias,
                 const P* __restrict__ scale, const P* __restrict__ ln_bias, T* __restrict__ y, T* __restrict__ dro,
@@ -67,6 +90,21 @@ fln_pipe_kernel(const T* __restrict__ x, const T* __restrict__ residual, const T
   }
   block_reduce_1sync_init(red[0], 0.f);
   block_reduce_1sync_init(red[1], 0.f);
+  // PSM: ln_scale / ln_bias copied once per persistent CTA into shared memory behind the ring, piece j of every thread's
+  // parameters stored together ([c][j][t][PV]: consecutive 16-byte reads across a warp) — see ln_pipe_kernel (layer_norm.cu):
+  // float parameters of a 16-bit row otherwise sit at a 32-byte stride per thread, two passes per read on either path.
+  P* const sw = reinterpret_cast<P*>(ring_raw + (size_t)stages * 2 * row_bytes);
+  P* const sb = sw + (size_t)C * nt * V;
+  if constexpr (PSM) {
+    constexpr int J = V / PV;
+    for (int i = tid; i < D / PV; i += nt) {
+      const int vi = i / J, j = i - vi * J;
+      const int c = vi / nt, t = vi - c * nt;
+      const int dsti = ((c * J + j) * nt + t) * PV;
+      *reinterpret_cast<uint4*>(sw + dsti) = *reinterpret_cast<const uint4*>(scale + (size_t)i * PV);
+      *reinterpret_cast<uint4*>(sb + dsti) = *reinterpret_cast<const uint4*>(ln_bias + (size_t)i * PV);
+    }
+  }
   __syncthreads();
   auto fill = [&](int s, int64_t r) {
     mbar_expect_tx(&full[s], 2 * row_bytes);
@@ -97,15 +135,27 @@ fln_pipe_kernel(const T* __restrict__ x, const T* __restrict__ residual, const T
           float b[V];
           unpack_to_float<T>(ld_cached(bias + off), b);
 #pragma unroll
-          for (int k = 0; k < V; ++k) e[c * V + k] = round_to<T>(__fadd_rn(e[c * V + k], b[k]));
+          for (int k = 0; k < V; k += 2) {
+            e[c * V + k] = __fadd_rn(e[c * V + k], b[k]);
+            e[c * V + k + 1] = __fadd_rn(e[c * V + k + 1], b[k + 1]);
+            round_pair_to<T>(e[c * V + k], e[c * V + k + 1]);
+          }
         }
         if constexpr (SC == 1) {
 #pragma unroll
-          for (int k = 0; k < V; ++k) e[c * V + k] = round_to<T>(__fmul_rn(e[c * V + k], factor));  // never fused with the add below
+          for (int k = 0; k < V; k += 2) {  // never fused with the add below
+            e[c * V + k] = __fmul_rn(e[c * V + k], factor);
+            e[c * V + k + 1] = __fmul_rn(e[c * V + k + 1], factor);
+            round_pair_to<T>(e[c * V + k], e[c * V + k + 1]);
+          }
         }
         if constexpr (SC == 2) {  // fused_bias_residual_layernorm's residual_alpha
 #pragma unroll
-          for (int k = 0; k < V; ++k) r[k] = round_to<T>(__fmul_rn(r[k], alpha));
+          for (int k = 0; k < V; k += 2) {
+            r[k] = __fmul_rn(r[k], alpha);
+            r[k + 1] = __fmul_rn(r[k + 1], alpha);
+            round_pair_to<T>(r[k], r[k + 1]);
+          }
         }
         Vec<T> dv;
 #pragma unroll
@@ -159,13 +209,21 @@ fln_pipe_kernel(const T* __restrict__ x, const T* __restrict__ residual, const T
         float w[V], b[V], o[V];
 #pragma unroll
         for (int k = 0; k < V; ++k) { w[k] = 1.f; b[k] = 0.f; }
-        if (scale != nullptr) {
+        if constexpr (PSM) {
 #pragma unroll
-          for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(scale + off + j * PV), &w[j * PV]);
-        }
-        if (ln_bias != nullptr) {
+          for (int j = 0; j < V / PV; ++j) {
+            unpack_to_float<P>(lds_vec(sw + ((c * (V / PV) + j) * nt + tid) * PV), &w[j * PV]);
+            unpack_to_float<P>(lds_vec(sb + ((c * (V / PV) + j) * nt + tid) * PV), &b[j * PV]);
+          }
+        } else {
+          if (scale != nullptr) {
 #pragma unroll
-          for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(ln_bias + off + j * PV), &b[j * PV]);
+            for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(scale + off + j * PV), &w[j * PV]);
+          }
+          if (ln_bias != nullptr) {
+#pragma unroll
+            for (int j = 0; j < V / PV; ++j) unpack_to_float<P>(ld_cached(ln_bias + off + j * PV), &b[j * PV]);
+          }
         }
 #pragma unroll
         for (int k = 0; k < V; ++k) o[k] = fmaf(w[k] * e[c * V + k], rstd, b[k]);  // scale * (d - mean) * invvar + bias
@@ -234,11 +292,17 @@ int fln_typed(const T* x, const T* residual, const T* bias, const P* scale, cons
     const int64_t nchunk = D / VN;
     if (vec && nchunk >= 64 && nchunk <= 512 * 4 && rows >= 4 * (int64_t)sm_count()) {
       int C = nchunk >= 512 ? 4 : (nchunk >= (sizeof(T) == 2 ? 128 : 256) ? 2 : 1);
+      // float parameters of a 16-bit row live in shared memory (PSM): 2 * D * 4 bytes next to the ring leave room for one CTA
+      // per SM, so that CTA is made 512 threads wide
+      const bool psm = sizeof(P) > sizeof(T) && scale != nullptr && ln_bias != nullptr && !knobs().no_fln_param_smem &&
+                       2 * (size_t)D * sizeof(P) <= 64 * 1024;
+      if (psm && nchunk >= 512) C = 2;
       while (C < 4 && (nchunk + C - 1) / C > 512) C <<= 1;
       int threads = (int)((nchunk + C - 1) / C);
       threads = (threads + 31) / 32 * 32;
       const bool exact = (int64_t)threads * C == nchunk;
       const size_t stage_bytes = 2 * (size_t)D * sizeof(T);
+      const size_t param_bytes = psm ? 2 * (size_t)C * threads * VN * sizeof(P) : 0;
       auto launch = [&](auto kern) -> int {
         int per_sm = 0, stages = 0;
         size_t smem = 0;
@@ -247,7 +311,7 @@ int fln_typed(const T* x, const T* residual, const T* bias, const P* scale, cons
         const int by_bytes = (int)((64 * 1024) / (2 * stage_bytes));  // ~64 KB of rows in flight per SM at two stages
         if (want > by_bytes) want = by_bytes < 1 ? 1 : by_bytes;
         FuncAttrHold hold;  // released when this lambda returns, i.e. after the launch
-        if (!pipe_geometry(kern, threads, stage_bytes, want, 3, &per_sm, &stages, &smem, &hold)) return -1;
+        if (!pipe_geometry(kern, threads, stage_bytes, want, 3, &per_sm, &stages, &smem, &hold, param_bytes)) return -1;
         int64_t grid = (int64_t)per_sm * sm_count();
         if (grid > rows) grid = rows;
         kern<<<(unsigned)grid, threads, smem, st>>>(x, residual, bias, scale, ln_bias, y, dro, static_cast<float*>(mean),
@@ -259,7 +323,9 @@ int fln_typed(const T* x, const T* residual, const T* bias, const P* scale, cons
       // need both (the one-CTA-per-row kernel below handles any combination)
       const int sc_mode = factor != 1.0f ? 1 : (alpha != 1.0f ? 2 : 0);
       int rc = -1;
-#define PDB_FLN3(CC, MT, HB, SC) rc = exact ? launch(fln_pipe_kernel<T, P, CC, true, HB, SC, MT>) : launch(fln_pipe_kernel<T, P, CC, false, HB, SC, MT>);
+#define PDB_FLN3(CC, MT, HB, SC)                                                                                      \
+  if (psm) rc = exact ? launch(fln_pipe_kernel<T, P, CC, true, HB, SC, MT, true>) : launch(fln_pipe_kernel<T, P, CC, false, HB, SC, MT, true>); \
+  else rc = exact ? launch(fln_pipe_kernel<T, P, CC, true, HB, SC, MT>) : launch(fln_pipe_kernel<T, P, CC, false, HB, SC, MT>);
 #define PDB_FLN2(CC, MT)                                           \
   if (bias && sc_mode == 1) { PDB_FLN3(CC, MT, true, 1) }          \
   else if (bias && sc_mode == 2) { PDB_FLN3(CC, MT, true, 2) }     \

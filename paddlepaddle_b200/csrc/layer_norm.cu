@@ -231,7 +231,7 @@ __global__ void __launch_bounds__(1024) ln_block_reg_kernel(const T* __restrict_
 // EXACT (D == C*blockDim.x*V) are compile-time so no per-element predicates remain, bf16 unpacks
 // in one instruction per element, sums run in four independent chains, the affine step is one
 // FFMA, and each CTA reduction costs one barrier.
-template <typename T, typename P, int C, bool AFFINE, bool EXACT, int MAXT>
+template <typename T, typename P, int C, bool AFFINE, bool EXACT, int MAXT, bool PSM = false>
 __global__ void __launch_bounds__(MAXT, MAXT <= 256 ? 2 : 1)
 ln_pipe_kernel(const T* __restrict__ x, const P* __restrict__ scale, const P* __restrict__ bias,
                T* __restrict__ y, float* mean_out, float* var_out, int64_t rows, int D, int stages, float eps,
@@ -258,6 +258,26 @@ ln_pipe_kernel(const T* __restrict__ x, const P* __restrict__ scale, const P* __
   }
   block_reduce_1sync_init(red[0], 0.f);
   block_reduce_1sync_init(red[1], 0.f);
+  // PSM: scale and bias copied ONCE per (persistent) CTA into shared memory behind the ring and read from there for every
+  // row.  Through L1 the parameters cost 2 * D * sizeof(P) bytes of global-load traffic per row — four times the row
+  // itself for float parameters of a bf16 row — and that path sustains about half the bytes per clock of a shared-memory
+  // read: bf16 [65536,8192] with float parameters ran 0.49 ms against 0.33 with bf16 parameters (profiles/r2_notes.txt).
+  // Layout: thread t's parameters of chunk c arrive as V / PV 16-byte pieces; piece j of all threads is stored together
+  // ([c][j][t][PV]) so that a warp's 16-byte reads are consecutive — in the tensor's own order a float parameter vector of a
+  // 16-bit row sits at a 32-byte stride per thread: two-way bank conflicts on every read (shared-memory pipe 69 % busy,
+  // profiles/r2h_ln_f32p.txt), and the same two passes on the L1 path.
+  P* const sw = reinterpret_cast<P*>(ring_raw + (size_t)stages * row_bytes);
+  P* const sb = sw + (size_t)C * nt * V;
+  if constexpr (PSM) {
+    constexpr int J = V / PV;
+    for (int i = tid; i < D / PV; i += nt) {  // i: 16-byte piece of the parameter vectors
+      const int vi = i / J, j = i - vi * J;   // vi: which 16-byte chunk of the row; j: which piece of its parameters
+      const int c = vi / nt, t = vi - c * nt;
+      const int dsti = ((c * J + j) * nt + t) * PV;
+      *reinterpret_cast<uint4*>(sw + dsti) = *reinterpret_cast<const uint4*>(scale + (size_t)i * PV);
+      *reinterpret_cast<uint4*>(sb + dsti) = *reinterpret_cast<const uint4*>(bias + (size_t)i * PV);
+    }
+  }
   __syncthreads();
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) {
@@ -353,8 +373,13 @@ ln_pipe_kernel(const T* __restrict__ x, const P* __restrict__ scale, const P* __
           } else {
 #pragma unroll
             for (int j = 0; j < V / PV; ++j) {
-              unpack_to_float<P>(ld_cached(scale + off + j * PV), &w[j * PV]);
-              unpack_to_float<P>(ld_cached(bias + off + j * PV), &b[j * PV]);
+              if constexpr (PSM) {
+                unpack_to_float<P>(lds_vec(sw + ((c * (V / PV) + j) * nt + tid) * PV), &w[j * PV]);
+                unpack_to_float<P>(lds_vec(sb + ((c * (V / PV) + j) * nt + tid) * PV), &b[j * PV]);
+              } else {
+                unpack_to_float<P>(ld_cached(scale + off + j * PV), &w[j * PV]);
+                unpack_to_float<P>(ld_cached(bias + off + j * PV), &b[j * PV]);
+              }
             }
           }
           float o[V];
@@ -627,13 +652,19 @@ int layer_norm_typed(const T* x, const P* scale, const P* bias, T* y, void* mean
     int threads = (int)((nchunk + C - 1) / C);
     threads = (threads + 31) / 32 * 32;
     const size_t row_bytes = (size_t)D * sizeof(T);
-    auto launch = [&](auto kern) -> int {
+    const bool affine = scale != nullptr && bias != nullptr;
+    // scale and bias resident in shared memory (PSM) when both are given, 16-byte aligned and small enough to leave the ring its room
+    const size_t param_bytes = 2 * (size_t)C * threads * VN * sizeof(P);  // the kernel's [C][pieces][threads] layout, D rounded up
+    int psm_mode = knobs().ln_param_smem;  // tuning knob: 1 never, 2 always (when it fits); default: float parameters of 16-bit rows
+    const bool psm = affine && is_aligned16(scale) && is_aligned16(bias) && D % (16 / (int)sizeof(P)) == 0 && param_bytes <= 64 * 1024 &&
+                     (psm_mode == 2 || (psm_mode != 1 && sizeof(P) > sizeof(T)));
+    auto launch = [&](auto kern, size_t extra) -> int {
       int per_sm = 0, stages = 0;
       size_t smem = 0;
       int want = 512 / threads;  // ~512 threads per SM, 2..4 CTAs, 3 rows in flight each
       want = want < 2 ? 2 : (want > 4 ? 4 : want);
       FuncAttrHold hold;  // released when this lambda returns, i.e. after the launch
-      if (!pipe_geometry(kern, threads, row_bytes, want, 3, &per_sm, &stages, &smem, &hold)) return -1;
+      if (!pipe_geometry(kern, threads, row_bytes, want, 3, &per_sm, &stages, &smem, &hold, extra)) return -1;
       int64_t grid = (int64_t)per_sm * sm_count();
       if (const int rpc = knobs().pipe_rows_per_cta; rpc >= 1)  // tuning knob: short-lived CTAs instead of a persistent grid
         grid = std::max<int64_t>(grid, rows / rpc);
@@ -641,13 +672,16 @@ int layer_norm_typed(const T* x, const P* scale, const P* bias, T* y, void* mean
       kern<<<(unsigned)grid, threads, smem, st>>>(x, scale, bias, y, m, v, rows, (int)D, stages, eps, inv_d, pipe_contiguous());
       return after_launch("ln_pipe");
     };
-    const bool affine = scale != nullptr && bias != nullptr;
     const bool exact = (int64_t)threads * C == nchunk;
     int rc = -1;
-#define PDB_LN_PIPE2(CC, MT)                                                             \
-  if (affine && exact) rc = launch(ln_pipe_kernel<T, P, CC, true, true, MT>);            \
-  else if (affine) rc = launch(ln_pipe_kernel<T, P, CC, true, false, MT>);               \
-  else rc = launch(ln_pipe_kernel<T, P, CC, false, false, MT>);
+#define PDB_LN_PIPE2(CC, MT)                                                                              \
+  if (psm && exact) rc = launch(ln_pipe_kernel<T, P, CC, true, true, MT, true>, param_bytes);             \
+  else if (psm) rc = launch(ln_pipe_kernel<T, P, CC, true, false, MT, true>, param_bytes);                \
+  if (rc < 0) {                                                                                           \
+    if (affine && exact) rc = launch(ln_pipe_kernel<T, P, CC, true, true, MT>, 0);                        \
+    else if (affine) rc = launch(ln_pipe_kernel<T, P, CC, true, false, MT>, 0);                           \
+    else rc = launch(ln_pipe_kernel<T, P, CC, false, false, MT>, 0);                                      \
+  }
 #define PDB_LN_PIPE(CC) if (threads <= 256) { PDB_LN_PIPE2(CC, 256) } else { PDB_LN_PIPE2(CC, 512) }
     if constexpr (!std::is_same<T, double>::value) {
       if (C == 4) { PDB_LN_PIPE(4) } else if (C == 2) { PDB_LN_PIPE(2) } else { PDB_LN_PIPE(1) }

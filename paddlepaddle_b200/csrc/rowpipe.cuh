@@ -96,7 +96,7 @@ inline int pipe_contiguous() { return knobs().pipe_contig; }
 // threads are doing with other shapes of the same kernel.
 template <typename Kern>
 inline bool pipe_geometry(Kern kern, int threads, size_t row_bytes, int want_ctas, int want_stages,
-                          int* grid_per_sm, int* stages, size_t* smem_bytes, FuncAttrHold* hold) {
+                          int* grid_per_sm, int* stages, size_t* smem_bytes, FuncAttrHold* hold, size_t extra_bytes = 0) {
   auto ok = [](cudaError_t e) {
     if (e != cudaSuccess) cudaGetLastError();
     return e == cudaSuccess;
@@ -108,11 +108,11 @@ inline bool pipe_geometry(Kern kern, int threads, size_t row_bytes, int want_cta
   // The answer depends only on (kernel, device, threads, row size, wishes): remember it, so that a launch
   // costs one map lookup instead of a dozen attribute / occupancy calls.
   struct Geo { int per_sm, stages; size_t smem; int pct; bool ok; };
-  static std::map<std::tuple<const void*, int, int, size_t, int, int>, Geo> cache;  // guarded by func_attr_mutex()
+  static std::map<std::tuple<const void*, int, int, size_t, int, int, size_t>, Geo> cache;  // guarded by func_attr_mutex()
   int dev = 0;
   cudaGetDevice(&dev);
   const void* fn = reinterpret_cast<const void*>(kern);
-  const auto key = std::make_tuple(fn, dev, threads, row_bytes, want_ctas, want_stages);
+  const auto key = std::make_tuple(fn, dev, threads, row_bytes, want_ctas, want_stages, extra_bytes);
   hold->lock = std::unique_lock<std::mutex>(func_attr_mutex());
   auto give_up = [&]() {
     hold->lock.unlock();
@@ -131,13 +131,15 @@ inline bool pipe_geometry(Kern kern, int threads, size_t row_bytes, int want_cta
       return true;
     }
   }
-  if (!func_attr_apply_locked(fn, 2 * (int)row_bytes, -1)) return give_up();
+  // extra_bytes: shared memory the kernel keeps next to its ring for the life of the CTA (layer_norm: scale and bias)
+  if (!func_attr_apply_locked(fn, (int)(2 * row_bytes + extra_bytes), -1)) return give_up();
   int occ = 0;
-  if (!ok(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, 2 * row_bytes)) || occ < 1) return give_up();
+  if (!ok(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, 2 * row_bytes + extra_bytes)) || occ < 1) return give_up();
   if (occ > want_ctas) occ = want_ctas;
   const size_t sm_smem = 227 * 1024;
   for (; occ >= 1; --occ) {
-    int st = static_cast<int>((sm_smem / occ - 2048) / row_bytes);  // 1 KB reserved + static barriers per CTA
+    if (sm_smem / occ < 2048 + extra_bytes + 2 * row_bytes) continue;
+    int st = static_cast<int>((sm_smem / occ - 2048 - extra_bytes) / row_bytes);  // 1 KB reserved + static barriers per CTA
     if (st > want_stages) st = want_stages;
     // Keep about 64 KB of rows in flight per SM and no more: 2 stages instead of 3 gained 3 % (layer_norm, 16 KB rows,
     // 2 CTAs), 10 % (layer_norm_grad), 8 % (rms_norm) and 8 % (softmax fp32, 8 KB rows, 3 CTAs); 4 stages were worse still
@@ -150,7 +152,7 @@ inline bool pipe_geometry(Kern kern, int threads, size_t row_bytes, int want_cta
       if (st > cap) st = cap;
     }
     for (; st >= 2; --st) {
-      const size_t smem = (size_t)st * row_bytes;
+      const size_t smem = (size_t)st * row_bytes + extra_bytes;
       int pct = static_cast<int>((occ * (smem + 2048) * 100 + sm_smem - 1) / sm_smem);
       if (pct > 100) pct = 100;
       if (!func_attr_apply_locked(fn, (int)smem, pct)) continue;

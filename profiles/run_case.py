@@ -104,6 +104,11 @@ elif case == "divide_bf16":
     x = torch.randn((64, 2048, 4096), device="cuda", generator=g).to(torch.bfloat16)
     y = (torch.rand((4096,), device="cuda", generator=g) + 0.5).to(torch.bfloat16)
     fn = lambda: paddle.divide(x, y)
+elif case in ("ln_bf16_f32params", "ln_bf16_f32params_l1"):
+    x = torch.randn((65536, 8192), device="cuda", generator=g).to(torch.bfloat16)
+    w = torch.rand(8192, device="cuda", generator=g)
+    b = torch.rand(8192, device="cuda", generator=g)
+    fn = lambda: F.layer_norm(x, [8192], w, b)
 elif case == "sum_c1":
     x = torch.rand((4096, 4096), device="cuda", generator=g)
     fn = lambda: paddle.sum(x, axis=-1)
