@@ -573,6 +573,46 @@ __global__ void __launch_bounds__(1024) ln_rows_cluster_kernel(const T* __restri
         st_stream(dst + i, ov);
       }
     };
+    // float parameters of a 16-bit row: a thread's 8 parameters are 32 bytes, i.e. two 16-byte loads at a 32-byte stride across
+    // the warp (two passes per request).  That case walks the slice in units of FOUR elements per thread instead: 8-byte
+    // reads of x, one 16-byte load each of scale and bias at a 16-byte stride, 8-byte stores (0.61 -> see r2_notes §11).
+    if constexpr (sizeof(P) == 4 && sizeof(T) == 2) {
+      if (sc != nullptr && bi != nullptr) {
+        const int h0 = (int)threadIdx.x * 4, hstep = (int)blockDim.x * 4;
+#pragma unroll 4
+        for (int i = h0; i < ni; i += hstep) {
+          const uint2 raw = *reinterpret_cast<const uint2*>(srow + i);
+          const float4 w4 = __ldg(reinterpret_cast<const float4*>(sc + i));
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(bi + i));
+          float e0, e1, e2, e3;
+          if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+            e0 = __uint_as_float(raw.x << 16);
+            e1 = __uint_as_float(raw.x & 0xffff0000u);
+            e2 = __uint_as_float(raw.y << 16);
+            e3 = __uint_as_float(raw.y & 0xffff0000u);
+          } else {
+            const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
+            const float2 c = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+            e0 = a.x; e1 = a.y; e2 = c.x; e3 = c.y;
+          }
+          const F2 t0 = f2_fma(f2_mul(f2_add(f2_make(e0, e1), nm2), r2), f2_make(w4.x, w4.y), f2_make(b4.x, b4.y));
+          const F2 t1 = f2_fma(f2_mul(f2_add(f2_make(e2, e3), nm2), r2), f2_make(w4.z, w4.w), f2_make(b4.z, b4.w));
+          uint2 o;
+          if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+            const __nv_bfloat162 p0 = __floats2bfloat162_rn(f2_lo(t0), f2_hi(t0)), p1 = __floats2bfloat162_rn(f2_lo(t1), f2_hi(t1));
+            o.x = *reinterpret_cast<const uint32_t*>(&p0);
+            o.y = *reinterpret_cast<const uint32_t*>(&p1);
+          } else {
+            const __half2 p0 = __floats2half2_rn(f2_lo(t0), f2_hi(t0)), p1 = __floats2half2_rn(f2_lo(t1), f2_hi(t1));
+            o.x = *reinterpret_cast<const uint32_t*>(&p0);
+            o.y = *reinterpret_cast<const uint32_t*>(&p1);
+          }
+          asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};" ::"l"(dst + i), "r"(o.x), "r"(o.y) : "memory");
+        }
+        asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
+        return;
+      }
+    }
     if (sc != nullptr && bi != nullptr) sweep(std::true_type{}, std::true_type{});
     else if (sc != nullptr) sweep(std::true_type{}, std::false_type{});
     else if (bi != nullptr) sweep(std::false_type{}, std::true_type{});
