@@ -317,6 +317,10 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
     c3_bytes = 2 * rows * D * 2 + 2 * rows * 4 + 2 * D * 2
     rec("C3 layer_norm bf16 [65536,8192] (whole config per rank)", c3_bytes, lambda: F.layer_norm(xl, [D], w, b), rows * D,
         key="C3_layer_norm_bf16")
+    wf_, bf_ = w.float(), b.float()  # Paddle's LayerNormParamType<bf16> = float: the other common way to call it
+    rec("C3 layer_norm bf16 [65536,8192] with float32 scale / bias (whole config per rank)", c3_bytes + 2 * D * 2,
+        lambda: F.layer_norm(xl, [D], wf_, bf_), rows * D, key="C3_layer_norm_bf16_f32params")
+    del wf_, bf_
     if world > 1:
         r0, r1 = pdist.shard_rows(rows, rank, world)
         xs_ = xl[r0:r1]
