@@ -117,7 +117,11 @@ __global__ void __launch_bounds__(512) softmax_mask_pipe_kernel(const T* __restr
 #pragma unroll
           for (int j = 0; j < V / MV; ++j) unpack_to_float<MT>(lds_vec(sm + off + j * MV), &mk[j * MV]);
 #pragma unroll
-          for (int k = 0; k < V; ++k) e[c * V + k] += mk[k];
+          for (int j = 0; j < V / 2; ++j) {
+            const F2 t = f2_add(f2_make(e[c * V + 2 * j], e[c * V + 2 * j + 1]), f2_make(mk[2 * j], mk[2 * j + 1]));
+            e[c * V + 2 * j] = f2_lo(t);
+            e[c * V + 2 * j + 1] = f2_hi(t);
+          }
         } else if (off + V > valid) {  // only the vector the diagonal cuts pays for per-element selects
 #pragma unroll
           for (int k = 0; k < V; ++k)
@@ -139,25 +143,33 @@ __global__ void __launch_bounds__(512) softmax_mask_pipe_kernel(const T* __restr
         fill(s, nrow);
       }
     }
-    const float nml = -m * 1.4426950408889634f;
-    float sm4[4] = {0.f, 0.f, 0.f, 0.f};
+    // exp, sum and the final scaling on packed fp32 pairs (FFMA2 / FADD2 / FMUL2: the same roundings, half the issue slots)
+    const F2 nml2 = f2_splat(-m * 1.4426950408889634f), l2e2 = f2_splat(1.4426950408889634f);
+    F2 sm2[2] = {f2_splat(0.f), f2_splat(0.f)};
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       const int off = (c * nt + tid) * V;
       if ((EXACT || off < dim) && off < valid) {  // CTA-uniform per chunk only in the mask form; warp-divergent at the diagonal
 #pragma unroll
-        for (int k = 0; k < V; ++k) {
-          e[c * V + k] = exp_shifted(e[c * V + k], nml);  // exp(-inf - m) = 0 for the masked tail
-          sm4[k & 3] += e[c * V + k];
+        for (int j = 0; j < V / 2; ++j) {
+          const F2 t = f2_fma(f2_make(e[c * V + 2 * j], e[c * V + 2 * j + 1]), l2e2, nml2);  // exp(-inf - m) = 0 for the masked tail
+          float p0, p1;
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p0) : "f"(f2_lo(t)));
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p1) : "f"(f2_hi(t)));
+          e[c * V + 2 * j] = p0;
+          e[c * V + 2 * j + 1] = p1;
+          sm2[j & 1] = f2_add(sm2[j & 1], f2_make(p0, p1));
         }
       } else {
 #pragma unroll
         for (int k = 0; k < V; ++k) e[c * V + k] = 0.f;
       }
     }
-    float sum = (sm4[0] + sm4[1]) + (sm4[2] + sm4[3]);
+    const F2 s2 = f2_add(sm2[0], sm2[1]);
+    float sum = f2_lo(s2) + f2_hi(s2);
     sum = block_reduce_1sync(sum, AddSm(), red[1]);
     const float inv = 1.0f / sum;
+    const F2 inv2 = f2_splat(inv);
     T* dst = y + row * dim;
 #pragma unroll
     for (int c = 0; c < C; ++c) {
@@ -165,7 +177,11 @@ __global__ void __launch_bounds__(512) softmax_mask_pipe_kernel(const T* __restr
       if (EXACT || off < dim) {
         float r[V];
 #pragma unroll
-        for (int k = 0; k < V; ++k) r[k] = e[c * V + k] * inv;
+        for (int j = 0; j < V / 2; ++j) {
+          const F2 q = f2_mul(f2_make(e[c * V + 2 * j], e[c * V + 2 * j + 1]), inv2);
+          r[2 * j] = f2_lo(q);
+          r[2 * j + 1] = f2_hi(q);
+        }
         if constexpr (TRI) {
           if (off + V > valid) {  // the diagonal's vector and everything after it
 #pragma unroll
