@@ -375,6 +375,12 @@ PDB200_API int pdb200_layer_norm(const void* x, const int64_t* dims, int rank, c
  * ------------------------------------------------------------------------- */
 PDB200_API int pdb200_softmax_grad(const void* out, const void* out_grad, const int64_t* dims, int rank, int axis,
                         int dtype, void* x_grad, void* stream);
+/* Backward of log_softmax on the same kernels: s = sum over `axis` of out_grad, x_grad = out_grad - exp(out) * s.
+ * Replaces phi::LogSoftmaxGradKernel<T, GPUContext> (paddle/phi/kernels/gpu/log_softmax_grad_kernel.cu:25-60; the CPU
+ * functor the oracle is built from: cpu/log_softmax_grad_kernel.cc:30-62).  Same arguments, dtypes, routes and 0-D rule
+ * (x_grad = 0) as pdb200_softmax_grad. */
+PDB200_API int pdb200_log_softmax_grad(const void* out, const void* out_grad, const int64_t* dims, int rank, int axis,
+                            int dtype, void* x_grad, void* stream);
 PDB200_API size_t pdb200_layer_norm_grad_workspace_bytes(const int64_t* dims, int rank, int begin_norm_axis, int dtype);
 PDB200_API int pdb200_layer_norm_grad(const void* x, const int64_t* dims, int rank, const void* scale, int param_dtype,
                            const void* mean, const void* variance, const void* out_grad, float epsilon,

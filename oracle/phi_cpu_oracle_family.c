@@ -472,6 +472,41 @@ int oracle_reduce_grad(int op, int dtype, const int64_t* xd, int xr, const int* 
 }
 
 /* ------------------------------------------------------------------------------------------
+ * log_softmax_grad.  phi::LogSoftmaxGradKernel<T,CPUContext> -> LogSoftmaxGradFunctor
+ * (cpu/log_softmax_grad_kernel.cc:30-62): x viewed as [n][axis_dim][remain];
+ *     dx = dy - exp(y) * sum_along_axis(dy)
+ * 0-D -> 0; 0-size -> no-op.  The sum runs along the axis in increasing index (Eigen's reducer order only moves the last
+ * bits: tests compare to 1e-5 of the row scale).  T = float or double.
+ * ---------------------------------------------------------------------------------------- */
+int oracle_log_softmax_grad(int dtype, const void* out, const void* out_grad, const int64_t* dims, int rank, int axis,
+                            void* x_grad) {
+  if (dtype != DT_FLOAT32 && dtype != DT_FLOAT64) return 2;
+  if (rank == 0) { if (dtype == DT_FLOAT32) *(float*)x_grad = 0.f; else *(double*)x_grad = 0.0; return 0; }
+  if (axis < -rank || axis >= rank) return 1;
+  if (axis < 0) axis += rank;
+  int64_t n = 1, ad = dims[axis], rem = 1;
+  for (int i = 0; i < axis; ++i) n *= dims[i];
+  for (int i = axis + 1; i < rank; ++i) rem *= dims[i];
+  if (n * ad * rem == 0) return 0;
+  for (int64_t b = 0; b < n; ++b)
+    for (int64_t r = 0; r < rem; ++r) {
+      const int64_t base = b * ad * rem + r;
+      if (dtype == DT_FLOAT32) {
+        const float* Y = (const float*)out; const float* G = (const float*)out_grad; float* DX = (float*)x_grad;
+        float s = 0.f;
+        for (int64_t k = 0; k < ad; ++k) s += G[base + k * rem];
+        for (int64_t k = 0; k < ad; ++k) DX[base + k * rem] = G[base + k * rem] - expf(Y[base + k * rem]) * s;
+      } else {
+        const double* Y = (const double*)out; const double* G = (const double*)out_grad; double* DX = (double*)x_grad;
+        double s = 0.0;
+        for (int64_t k = 0; k < ad; ++k) s += G[base + k * rem];
+        for (int64_t k = 0; k < ad; ++k) DX[base + k * rem] = G[base + k * rem] - exp(Y[base + k * rem]) * s;
+      }
+    }
+  return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
  * max_grad / min_grad / prod_grad, as the GPU kernels compute them.
  *   max_grad, min_grad: phi::ReduceMaxGradKernel / ReduceMinGradKernel<T,GPUContext> (gpu/reduce_kernel.cu:76-120,159-203):
  *       equal_out = Equal(out, x) with funcs::EqualFunctor<T> (funcs/compare_functors.h:35-48), stored as T;

@@ -14,6 +14,7 @@
 //   cross_entropy_with_softmax  phi::CrossEntropyWithSoftmaxKernel<T,CPUContext>
 //                paddle/phi/kernels/cpu/cross_entropy_kernel.cc:73-104 (+ funcs/cross_entropy.cc, compiled as its own TU)
 //   log_softmax  phi::LogSoftmaxKernel<T,CPUContext>             paddle/phi/kernels/cpu/log_softmax_kernel.cc:40-127
+//   log_softmax_grad  phi::LogSoftmaxGradKernel<T,CPUContext>    paddle/phi/kernels/cpu/log_softmax_grad_kernel.cc:30-84
 //   sum_grad / mean_grad  phi::ReduceSumGradKernel / ReduceMeanGradKernel<T,CPUContext>
 //                paddle/phi/kernels/cpu/reduce_sum_grad_kernel.cc:26-43, cpu/reduce_mean_grad_kernel.cc
 //   max_grad / min_grad / prod_grad  phi::ReduceMaxGradKernel / ReduceMinGradKernel / ProdGradKernel<T,CPUContext>
@@ -37,6 +38,7 @@
 #include "paddle/phi/kernels/cpu/cross_entropy_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/elementwise_add_grad_kernel.cc"       // NOLINT
 #include "paddle/phi/kernels/cpu/elementwise_multiply_grad_kernel.cc"  // NOLINT
+#include "paddle/phi/kernels/cpu/log_softmax_grad_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/log_softmax_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/logical_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/prod_grad_kernel.cc"         // NOLINT
@@ -408,5 +410,22 @@ int phi_ref_select_grad(int op, int dtype, const void* x, const int64_t* xdims, 
     if (dxt.data() != x_grad) std::memcpy(x_grad, dxt.data(), static_cast<size_t>(dxt.numel()) * phi::SizeOf(dxt.dtype()));
   });
 }
+
+int phi_ref_log_softmax_grad(int dtype, const void* out, const void* out_grad, const int64_t* dims, int rank, int axis,
+                             void* x_grad) {
+  return Guard([&] {
+    auto yt = Wrap(out, dims, rank, dtype);
+    auto gt = Wrap(out_grad, dims, rank, dtype);
+    auto xt = Wrap(x_grad, dims, rank, dtype);
+    auto& ctx = GetCtx().ctx;
+    switch (dtype) {
+      case kFloat32: phi::LogSoftmaxGradKernel<float, CPUContext>(ctx, yt, gt, axis, &xt); break;
+      case kFloat64: phi::LogSoftmaxGradKernel<double, CPUContext>(ctx, yt, gt, axis, &xt); break;
+      default: throw std::runtime_error("phi_ref_log_softmax_grad: dtype not registered on CPU");
+    }
+    if (xt.data() != x_grad) std::memcpy(x_grad, xt.data(), static_cast<size_t>(xt.numel()) * phi::SizeOf(xt.dtype()));
+  });
+}
+
 
 }  // extern "C"

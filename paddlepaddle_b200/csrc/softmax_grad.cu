@@ -5,6 +5,9 @@
 // Numerics follow the CPU kernel the parity oracle is built from
 // (paddle/phi/kernels/funcs/softmax_impl.h:275-308,406-445):
 //     dot = sum_j y_j * dy_j ;  dx_i = (dy_i - dot) * y_i        (fp16/bf16: in float, one rounding)
+// and, with LOG, the backward of log_softmax on the same kernels (phi::LogSoftmaxGradKernel, gpu/log_softmax_grad_kernel.cu;
+// CPU functor cpu/log_softmax_grad_kernel.cc:30-62):
+//     s = sum_j dy_j ;  dx_i = dy_i - exp(y_i) * s
 //
 // Routes (tensors viewed as [outer][dim][inner]):
 //   inner == 1, many rows -> pipe : persistent CTAs on the TMA row pipeline of rowpipe.cuh; a stage holds the
@@ -21,7 +24,7 @@ namespace pdb200 {
 template <typename A> struct AddG { __device__ __forceinline__ A operator()(A a, A b) const { return a + b; } };
 
 // ---- pipe ---------------------------------------------------------------------------------------------
-template <typename T, int C, bool EXACT>
+template <typename T, int C, bool EXACT, bool LOG>
 __global__ void __launch_bounds__(512) softmax_grad_pipe_kernel(const T* __restrict__ y, const T* __restrict__ dy,
                                                                 T* __restrict__ dx, int64_t rows, int dim,
                                                                 int stages) {
@@ -70,7 +73,7 @@ __global__ void __launch_bounds__(512) softmax_grad_pipe_kernel(const T* __restr
         for (int k = 0; k < V; ++k) yv[c * V + k] = gv[c * V + k] = 0.f;
       }
 #pragma unroll
-      for (int k = 0; k < V; ++k) acc[k & 3] = fmaf(yv[c * V + k], gv[c * V + k], acc[k & 3]);
+      for (int k = 0; k < V; ++k) acc[k & 3] = LOG ? acc[k & 3] + gv[c * V + k] : fmaf(yv[c * V + k], gv[c * V + k], acc[k & 3]);
     }
     float dot = (acc[0] + acc[1]) + (acc[2] + acc[3]);
     dot = block_reduce_1sync(dot, AddG<float>(), red[flip]);  // its barrier also means: stage s fully read
@@ -89,7 +92,15 @@ __global__ void __launch_bounds__(512) softmax_grad_pipe_kernel(const T* __restr
       if (EXACT || off < dim) {
         float r[V];
 #pragma unroll
-        for (int k = 0; k < V; ++k) r[k] = __fmul_rn(gv[c * V + k] - dot, yv[c * V + k]);
+        for (int k = 0; k < V; ++k) {
+          if constexpr (LOG) {
+            float ey;
+            asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(ey) : "f"(yv[c * V + k] * 1.4426950408889634f));
+            r[k] = fmaf(-ey, dot, gv[c * V + k]);
+          } else {
+            r[k] = __fmul_rn(gv[c * V + k] - dot, yv[c * V + k]);
+          }
+        }
         Vec<T> o;
         pack_from_float<T>(r, o);
         st_stream(dst + off, o);
@@ -103,7 +114,11 @@ __global__ void __launch_bounds__(512) softmax_grad_pipe_kernel(const T* __restr
 }
 
 // ---- rows: one CTA per row, any length / alignment --------------------------------------------------------
-template <typename T>
+template <typename A> __device__ __forceinline__ A exp_acc(A v);
+template <> __device__ __forceinline__ float exp_acc<float>(float v) { return expf(v); }
+template <> __device__ __forceinline__ double exp_acc<double>(double v) { return exp(v); }
+
+template <typename T, bool LOG>
 __global__ void __launch_bounds__(1024) softmax_grad_rows_kernel(const T* y, const T* dy, T* dx, int64_t dim) {
   using A = typename AccType<T>::type;
   __shared__ A red[33];
@@ -111,14 +126,15 @@ __global__ void __launch_bounds__(1024) softmax_grad_rows_kernel(const T* y, con
   const T* rg = dy + (int64_t)blockIdx.x * dim;
   T* rd = dx + (int64_t)blockIdx.x * dim;
   A dot = A(0);
-  for (int64_t i = threadIdx.x; i < dim; i += blockDim.x) dot += cvt<A>(ry[i]) * cvt<A>(rg[i]);
+  for (int64_t i = threadIdx.x; i < dim; i += blockDim.x) dot += LOG ? cvt<A>(rg[i]) : cvt<A>(ry[i]) * cvt<A>(rg[i]);
   dot = block_reduce(dot, AddG<A>(), A(0), red);
   // dx may alias dy (in-place grad): each element is read and written by the same thread
-  for (int64_t i = threadIdx.x; i < dim; i += blockDim.x) rd[i] = cvt<T>((cvt<A>(rg[i]) - dot) * cvt<A>(ry[i]));
+  for (int64_t i = threadIdx.x; i < dim; i += blockDim.x)
+    rd[i] = cvt<T>(LOG ? cvt<A>(rg[i]) - exp_acc<A>(cvt<A>(ry[i])) * dot : (cvt<A>(rg[i]) - dot) * cvt<A>(ry[i]));
 }
 
 // ---- cols: softmax axis is not the last one ---------------------------------------------------------------
-template <typename T>
+template <typename T, bool LOG>
 __global__ void __launch_bounds__(256) softmax_grad_cols_kernel(const T* y, const T* dy, T* dx, int64_t dim,
                                                                 int64_t inner, int64_t col_tiles) {
   using A = typename AccType<T>::type;
@@ -128,17 +144,21 @@ __global__ void __launch_bounds__(256) softmax_grad_cols_kernel(const T* y, cons
   if (col >= inner) return;
   const int64_t base = o * dim * inner + col;
   A dot = A(0);
-  for (int64_t r = 0; r < dim; ++r) dot += cvt<A>(y[base + r * inner]) * cvt<A>(dy[base + r * inner]);
+  for (int64_t r = 0; r < dim; ++r) dot += LOG ? cvt<A>(dy[base + r * inner]) : cvt<A>(y[base + r * inner]) * cvt<A>(dy[base + r * inner]);
   for (int64_t r = 0; r < dim; ++r)
-    dx[base + r * inner] = cvt<T>((cvt<A>(dy[base + r * inner]) - dot) * cvt<A>(y[base + r * inner]));
+    dx[base + r * inner] = cvt<T>(LOG ? cvt<A>(dy[base + r * inner]) - exp_acc<A>(cvt<A>(y[base + r * inner])) * dot
+                                      : (cvt<A>(dy[base + r * inner]) - dot) * cvt<A>(y[base + r * inner]));
 }
 
 template <typename T>
 __global__ void softmax_grad_zero_kernel(T* dx) { dx[0] = cvt<T>(typename AccType<T>::type(0)); }
 
 // ---- host ---------------------------------------------------------------------------------------------------
-template <typename T>
+template <typename T, bool LOG>
 int try_softmax_grad_pipe(const T* y, const T* dy, T* dx, int64_t outer, int64_t dim, cudaStream_t st) {
+  if constexpr (std::is_same<T, double>::value) {
+    return -1;
+  } else {
   constexpr int VN = Vec<T>::N;
   const int64_t nchunk = dim / VN;
   int C = sizeof(T) == 2 ? (nchunk >= 256 ? 4 : (nchunk >= 128 ? 2 : 1)) : (nchunk >= 256 ? 2 : 1);
@@ -169,29 +189,28 @@ int try_softmax_grad_pipe(const T* y, const T* dy, T* dx, int64_t outer, int64_t
     kern<<<(unsigned)grid, threads, smem, st>>>(y, dy, dx, outer, (int)dim, stages);
     return after_launch("softmax_grad_pipe");
   };
-#define PDB_SMG(CC) return exact ? launch(softmax_grad_pipe_kernel<T, CC, true>) : launch(softmax_grad_pipe_kernel<T, CC, false>);
+#define PDB_SMG(CC) return exact ? launch(softmax_grad_pipe_kernel<T, CC, true, LOG>) : launch(softmax_grad_pipe_kernel<T, CC, false, LOG>);
   if (C == 4) { PDB_SMG(4) }
   if (C == 2) { PDB_SMG(2) }
   PDB_SMG(1)
 #undef PDB_SMG
+  }
 }
-template <>
-int try_softmax_grad_pipe<double>(const double*, const double*, double*, int64_t, int64_t, cudaStream_t) { return -1; }
 
-template <typename T>
+template <typename T, bool LOG>
 int softmax_grad_typed(const T* y, const T* dy, T* dx, int64_t outer, int64_t dim, int64_t inner, cudaStream_t st) {
   constexpr int VN = Vec<T>::N;
   if (inner == 1) {
     const bool vec = (dim % VN == 0) && is_aligned16(y) && is_aligned16(dy) && is_aligned16(dx);
     const int64_t nchunk = dim / VN;
     if (vec && nchunk >= 64 && nchunk <= 512 * 4 && outer >= 4 * (int64_t)sm_count() && dx != y) {
-      const int rc = try_softmax_grad_pipe<T>(y, dy, dx, outer, dim, st);
+      const int rc = try_softmax_grad_pipe<T, LOG>(y, dy, dx, outer, dim, st);
       if (rc >= 0) return rc;
     }
     if (outer > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "softmax_grad: too many rows for one launch");
     int threads = 128;
     while (threads < 1024 && threads * 4 < dim) threads <<= 1;
-    softmax_grad_rows_kernel<T><<<(unsigned)outer, threads, 0, st>>>(y, dy, dx, dim);
+    softmax_grad_rows_kernel<T, LOG><<<(unsigned)outer, threads, 0, st>>>(y, dy, dx, dim);
     return after_launch("softmax_grad_rows");
   }
   int threads = 32;
@@ -199,15 +218,16 @@ int softmax_grad_typed(const T* y, const T* dy, T* dx, int64_t outer, int64_t di
   const int64_t col_tiles = (inner + threads - 1) / threads;
   const int64_t blocks = col_tiles * outer;
   if (blocks > 0x7fffffffLL) return fail(PDB200_UNSUPPORTED, "softmax_grad: too many tiles for one launch");
-  softmax_grad_cols_kernel<T><<<(unsigned)blocks, threads, 0, st>>>(y, dy, dx, dim, inner, col_tiles);
+  softmax_grad_cols_kernel<T, LOG><<<(unsigned)blocks, threads, 0, st>>>(y, dy, dx, dim, inner, col_tiles);
   return after_launch("softmax_grad_cols");
 }
 
 }  // namespace pdb200
 
-extern "C" int pdb200_softmax_grad(const void* out, const void* out_grad, const int64_t* dims, int rank, int axis,
-                                   int dtype, void* x_grad, void* stream) {
-  using namespace pdb200;
+namespace pdb200 {
+template <bool LOG>
+int softmax_grad_entry(const void* out, const void* out_grad, const int64_t* dims, int rank, int axis, int dtype, void* x_grad,
+                       void* stream) {
   PDB_CHECK_ARG(rank >= 0 && rank <= PDB200_MAX_RANK, "softmax_grad: rank must be in [0, 9]");
   PDB_CHECK_ARG(rank == 0 || dims != nullptr, "softmax_grad: dims is NULL");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
@@ -232,7 +252,7 @@ extern "C" int pdb200_softmax_grad(const void* out, const void* out_grad, const 
       softmax_grad_zero_kernel<T><<<1, 1, 0, st>>>(static_cast<T*>(x_grad));                               \
       return after_launch("softmax_grad_zero");                                                            \
     }                                                                                                      \
-    return softmax_grad_typed<T>(static_cast<const T*>(out), static_cast<const T*>(out_grad),              \
+    return softmax_grad_typed<T, LOG>(static_cast<const T*>(out), static_cast<const T*>(out_grad),              \
                                  static_cast<T*>(x_grad), outer, dim, inner, st);                          \
   }
   switch (dtype) {
@@ -245,4 +265,14 @@ extern "C" int pdb200_softmax_grad(const void* out, const void* out_grad, const 
                                           std::to_string(dtype));
   }
 #undef PDB_SMG_CASE
+}
+}  // namespace pdb200
+
+extern "C" int pdb200_softmax_grad(const void* out, const void* out_grad, const int64_t* dims, int rank, int axis,
+                                   int dtype, void* x_grad, void* stream) {
+  return pdb200::softmax_grad_entry<false>(out, out_grad, dims, rank, axis, dtype, x_grad, stream);
+}
+extern "C" int pdb200_log_softmax_grad(const void* out, const void* out_grad, const int64_t* dims, int rank, int axis,
+                                       int dtype, void* x_grad, void* stream) {
+  return pdb200::softmax_grad_entry<true>(out, out_grad, dims, rank, axis, dtype, x_grad, stream);
 }

@@ -350,6 +350,20 @@ def softmax_grad(out, out_grad, axis=-1):
     return x_grad
 
 
+def log_softmax_grad(out, out_grad, axis=-1):
+    """x_grad of log_softmax given its output and the output's gradient: out_grad - exp(out) * sum(out_grad, axis)."""
+    _require_cuda(out, out_grad)
+    if out.shape != out_grad.shape or out.dtype != out_grad.dtype:
+        raise ValueError("(InvalidArgument) out and out_grad must have the same shape and dtype")
+    lib = L.load()
+    out, out_grad = out.contiguous(), out_grad.contiguous()
+    x_grad = torch.empty_like(out)
+    d, r = L.dims_array(out.shape)
+    L.check(lib.pdb200_log_softmax_grad(_ptr(out), _ptr(out_grad), d, r, int(axis), _dtype_code(out.dtype), _ptr(x_grad),
+                                        _stream()), lib)
+    return x_grad
+
+
 def layer_norm_grad(x, normalized_shape, weight, mean, variance, out_grad, epsilon=1e-05, need_weight_grad=None,
                     need_bias_grad=True):
     """(x_grad, weight_grad or None, bias_grad or None) of layer_norm.  mean / variance are the forward

@@ -590,6 +590,15 @@ void SoftmaxGradKernel(const Context& ctx, const DenseTensor& out, const DenseTe
   Check(pdb200_softmax_grad(out.data<T>(), out_grad.data<T>(), d.data(), static_cast<int>(d.size()), axis,
                             Code(out.dtype()), dx, ctx.stream()));
 }
+// log_softmax_grad (gpu/log_softmax_grad_kernel.cu:25-60): the same signature
+template <typename T, typename Context>
+void LogSoftmaxGradKernel(const Context& ctx, const DenseTensor& out, const DenseTensor& out_grad, int axis,
+                          DenseTensor* x_grad) {
+  T* dx = ctx.template Alloc<T>(x_grad);
+  auto d = Dims(out);
+  Check(pdb200_log_softmax_grad(out.data<T>(), out_grad.data<T>(), d.data(), static_cast<int>(d.size()), axis,
+                                Code(out.dtype()), dx, ctx.stream()));
+}
 template <typename T, typename Context>
 void SoftmaxGradGPUDNNKernel(const Context& ctx, const DenseTensor& out, const DenseTensor& out_grad, int axis,
                              DenseTensor* x_grad) {
@@ -746,6 +755,8 @@ PD_REGISTER_KERNEL(layer_norm, GPU, ALL_LAYOUT, pdb200_phi::LayerNormKernel, flo
 PD_REGISTER_KERNEL(softmax_grad, GPUDNN, ALL_LAYOUT, pdb200_phi::SoftmaxGradGPUDNNKernel, float, double,
                    phi::dtype::float16, phi::dtype::bfloat16) {}
 PD_REGISTER_KERNEL(softmax_grad, GPU, ALL_LAYOUT, pdb200_phi::SoftmaxGradKernel, float, double, phi::dtype::float16,
+                   phi::dtype::bfloat16) {}
+PD_REGISTER_KERNEL(log_softmax_grad, GPU, ALL_LAYOUT, pdb200_phi::LogSoftmaxGradKernel, float, double, phi::dtype::float16,
                    phi::dtype::bfloat16) {}
 PD_REGISTER_KERNEL(layer_norm_grad, GPU, ALL_LAYOUT, pdb200_phi::LayerNormGradKernel, float, double,
                    phi::dtype::float16, phi::dtype::bfloat16) {

@@ -187,6 +187,15 @@ class Oracle:
         self._check(rc)
         return dx
 
+    def log_softmax_grad(self, out, out_grad, axis=-1):
+        out = np.ascontiguousarray(out)
+        out_grad = np.ascontiguousarray(out_grad, out.dtype)
+        dx = np.empty_like(out)
+        d, r = _dims(out.shape)
+        rc = getattr(self.lib, self.p + "log_softmax_grad")(NP2CODE[out.dtype], _vp(out), _vp(out_grad), d, r, int(axis), _vp(dx))
+        self._check(rc)
+        return dx
+
     def layer_norm_grad(self, x, begin_norm_axis, scale, mean, var, out_grad, epsilon=1e-5, want_bias_grad=True):
         """Returns (dx, dscale or None, dbias or None).  dscale is produced exactly when scale is given."""
         x = np.ascontiguousarray(x)

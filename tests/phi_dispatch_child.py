@@ -234,6 +234,8 @@ def case_rows():
         wg = F.softmax_grad(want, dy, axis=-1)
         for backend in ("GPUDNN", "GPU"):
             check(f"softmax_grad/{backend}/{dt}", run("softmax_grad", "axis_grad", [want, dy], [wg], iv=[-1], backend=backend), wg)
+        wlg = F.log_softmax_grad(wl, dy, axis=-1)
+        check(f"log_softmax_grad/{dt}", run("log_softmax_grad", "axis_grad", [wl, dy], [wlg], iv=[-1]), wlg)
     # layer_norm: bfloat16 key, float32 scale / bias (the mixed-dtype rule), mean / variance outputs are float32
     rows, D = 700, 8192
     x = rnd((rows, D), torch.bfloat16, 3.0)
@@ -298,7 +300,7 @@ NAMES = ["add", "multiply", "subtract", "divide", "maximum", "minimum", "less_th
          "equal", "not_equal", "logical_and", "logical_or", "logical_xor", "logical_not", "bitwise_and", "bitwise_or", "bitwise_xor",
          "bitwise_not", "bitwise_left_shift", "bitwise_right_shift", "scale", "cast", "where", "add_grad", "multiply_grad", "sum_grad",
          "mean_grad", "max_grad", "min_grad", "prod_grad", "cross_entropy_with_softmax", "rms_norm", "log_softmax", "sum_raw", "sum", "mean_raw", "mean", "max_raw", "max",
-         "min_raw", "min", "prod", "argmax", "argmin", "softmax", "layer_norm", "softmax_grad", "layer_norm_grad", "fused_softmax_mask",
+         "min_raw", "min", "prod", "argmax", "argmin", "softmax", "layer_norm", "softmax_grad", "log_softmax_grad", "layer_norm_grad", "fused_softmax_mask",
          "fused_softmax_mask_upper_triangle", "fused_bias_dropout_residual_layer_norm", "fused_bias_residual_layernorm"]
 print(json.dumps({"calls": n_calls, "alloc_calls": reg.phi_min_alloc_calls(), "failed": failed,
                   "names_not_called": sorted(set(NAMES) - called)}))

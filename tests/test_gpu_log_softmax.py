@@ -82,3 +82,43 @@ def test_log_softmax_config4_sized():
     assert int(paddle.sum(paddle.not_equal(paddle.argmax(ls, axis=-1), paddle.argmax(x, axis=-1))).item()) <= x.numel() // 2048 // 100
     sm = F.softmax(x, axis=-1)
     assert int(paddle.sum(paddle.not_equal(paddle.argmax(sm, axis=-1), paddle.argmax(ls, axis=-1))).item()) <= x.numel() // 2048 // 100
+
+
+@pytest.mark.parametrize("shape,axis", [((64, 2048), -1), ((33, 1001), -1), ((700, 4096), -1), ((1300, 512), -1), ((5, 40000), -1),
+                                        ((8, 100, 64), 1), ((4, 17, 5, 3), 1), ((50, 1), -1), ((3, 7), 0)])
+def test_log_softmax_grad_routes(port, shape, axis):
+    """Backward of log_softmax (pdb200_log_softmax_grad, the softmax_grad kernels with the log rule): against the reference
+    CPU kernel through the restatement pinned to it; 16-bit: <= 1 ulp of the rounded float result."""
+    rng = np.random.default_rng(31)
+    x = (rng.standard_normal(shape) * 2).astype(np.float32)
+    y = port.log_softmax(x, axis)
+    g = rng.standard_normal(shape).astype(np.float32)
+    want = port.log_softmax_grad(y, g, axis)
+    got = to_np(F.log_softmax_grad(to_dev(y), to_dev(g), axis=axis))
+    scale = float(np.abs(g).sum(axis=axis).max())
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-6 * (scale + 1))
+    for half, conv, back in (("bf16", port.f32_to_bf16, port.bf16_to_f32), ("fp16", port.f32_to_fp16, port.fp16_to_f32)):
+        yb, gb = conv(y), conv(g)
+        wh = port.log_softmax_grad(back(yb), back(gb), axis)
+        gh = to_np(F.log_softmax_grad(to_dev(yb, half), to_dev(gb, half), axis=axis))
+        ulp = 2.0 ** -8 if half == "bf16" else 2.0 ** -11
+        np.testing.assert_allclose(back(gh), wh, rtol=1.01 * ulp, atol=ulp * 1e-3 * (scale + 1) + 1e-6 * (scale + 1))
+    xd = rng.standard_normal(shape)
+    yd = xd - np.log(np.exp(xd).sum(axis=axis, keepdims=True))
+    gd = rng.standard_normal(shape)
+    np.testing.assert_allclose(to_np(F.log_softmax_grad(to_dev(yd), to_dev(gd), axis=axis)), port.log_softmax_grad(yd, gd, axis),
+                               rtol=1e-12, atol=1e-12)
+
+
+def test_log_softmax_grad_chain_and_edges(port):
+    """Forward then backward against torch autograd in float64 on the same data; 0-D gives 0; in place on out_grad."""
+    x = torch.randn(600, 4096, device="cuda")
+    g = torch.randn(600, 4096, device="cuda")
+    y = F.log_softmax(x, axis=-1)
+    dx = F.log_softmax_grad(y, g, axis=-1)
+    xr = x.double().requires_grad_(True)
+    torch.log_softmax(xr, dim=-1).backward(g.double())
+    np.testing.assert_allclose(to_np(dx), xr.grad.cpu().numpy(), rtol=1e-5, atol=1e-5)
+    assert float(F.log_softmax_grad(torch.tensor(0.0, device="cuda"), torch.tensor(3.0, device="cuda"), axis=-1)) == 0.0
+    with pytest.raises(ValueError):
+        F.log_softmax_grad(y, g[:5], axis=-1)

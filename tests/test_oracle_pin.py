@@ -298,3 +298,18 @@ def test_fused_layer_norm_helper_agrees_with_the_reference_avx512_kernel(port, r
         y0, mm0, vv0 = ref.layer_norm(x, 1, w, b, 1e-5)
         np.testing.assert_allclose(out0, y0, rtol=1e-4, atol=1e-4)
         np.testing.assert_allclose(r0, 1.0 / np.sqrt(vv0 + 1e-5), rtol=2e-5)
+
+
+def test_log_softmax_grad_restatement_equals_compiled_reference(port, ref):
+    """log_softmax_grad (round 2): the restatement against the compiled reference CPU kernel (Eigen expression
+    dy - exp(y) * sum(dy)); the reducer's summation order moves the last bits, so 1e-6 of the row scale."""
+    rng = np.random.default_rng(55)
+    for dt in (np.float32, np.float64):
+        for shape, axis in (((7, 33), -1), ((7, 33), 0), ((4, 9, 5), 1), ((2, 3, 4, 5), 2), ((64, 1000), 1), ((5,), 0)):
+            y = (rng.standard_normal(shape) - 2.0).astype(dt)  # any tensor is a valid "out" for the kernel
+            g = rng.standard_normal(shape).astype(dt)
+            a, b = port.log_softmax_grad(y, g, axis), ref.log_softmax_grad(y, g, axis)
+            tol = 1e-6 if dt == np.float32 else 1e-13
+            np.testing.assert_allclose(a, b, rtol=tol, atol=tol * float(np.abs(g).sum(axis=axis).max() + 1))
+    z = np.zeros((), np.float32)
+    assert port.log_softmax_grad(z, z + 3, 0) == 0 and ref.log_softmax_grad(z, z + 3, 0) == 0  # 0-D: gradient 0
