@@ -346,6 +346,17 @@ PDB200_API int pdb200_cross_entropy_with_softmax(const void* logits, const int64
                                       int label_dtype, int soft_label, int use_softmax, int ignore_index, int axis,
                                       int dtype, void* softmax, void* loss, void* workspace, size_t workspace_bytes,
                                       void* stream);
+/* Backward of cross_entropy_with_softmax with use_softmax != 0: logits_grad from the saved softmax, the labels and loss_grad
+ * (one value per position, the logits' shape with a 1 along `axis`).  Replaces phi::CrossEntropyWithSoftmaxGradKernel<T,
+ * GPUContext> (paddle/phi/kernels/gpu/cross_entropy_grad_kernel.cu:281-306); arithmetic as the CPU kernel
+ * (cpu/cross_entropy_grad_kernel.cc:143-179): soft labels g * (p - y); hard labels p * g, minus g at the label's class (two
+ * roundings), zero for a position whose label is ignore_index.  dims / rank describe softmax and logits_grad.  label:
+ * INT64 / INT32 class indices or, with soft_label, distributions of the tensor dtype.  dtypes FLOAT32, FLOAT64, FLOAT16,
+ * BFLOAT16 (16-bit: float arithmetic, one rounding).  use_softmax == 0 returns PDB200_UNSUPPORTED (the PHI binding
+ * forwards it).  logits_grad may alias softmax (the reference computes in place). */
+PDB200_API int pdb200_cross_entropy_with_softmax_grad(const void* label, int label_dtype, const void* softmax, const void* loss_grad,
+                                           const int64_t* dims, int rank, int soft_label, int use_softmax, int ignore_index,
+                                           int axis, int dtype, void* logits_grad, void* stream);
 
 /* ---------------------------------------------------------------------------
  * layer_norm forward.  Replaces phi::LayerNormKernel<T, GPUContext>

@@ -472,6 +472,46 @@ int oracle_reduce_grad(int op, int dtype, const int64_t* xd, int xr, const int* 
 }
 
 /* ------------------------------------------------------------------------------------------
+ * cross_entropy_with_softmax_grad, use_softmax = true.  phi::CrossEntropyWithSoftmaxGradKernel<T,CPUContext>
+ * (cpu/cross_entropy_grad_kernel.cc:143-179) on [n][axis_dim][remain], p = softmax, g = loss_grad[i][j]:
+ *   soft: dx = g * (p - y)
+ *   hard: dx = p * g; dx[label] -= g (a second rounding); label == ignore_index: the whole position 0.   (label: int64 here)
+ * T = float or double.
+ * ---------------------------------------------------------------------------------------- */
+int oracle_cross_entropy_with_softmax_grad(int dtype, const void* label, const void* softmax, const void* loss_grad,
+                                           const int64_t* dims, int rank, int soft_label, int ignore_index, int axis,
+                                           void* logits_grad) {
+  if (dtype != DT_FLOAT32 && dtype != DT_FLOAT64) return 2;
+  if (rank < 1 || axis < -rank || axis >= rank) return 1;
+  if (axis < 0) axis += rank;
+  int64_t n = 1, ad = dims[axis], rem = 1;
+  for (int i = 0; i < axis; ++i) n *= dims[i];
+  for (int i = axis + 1; i < rank; ++i) rem *= dims[i];
+  for (int64_t b = 0; b < n; ++b)
+    for (int64_t j = 0; j < rem; ++j) {
+      const int64_t pos = b * rem + j;
+      const int64_t lbl = soft_label ? -1 : ((const int64_t*)label)[pos];
+      for (int64_t k = 0; k < ad; ++k) {
+        const int64_t i = (b * ad + k) * rem + j;
+        if (dtype == DT_FLOAT32) {
+          const float p = ((const float*)softmax)[i], g = ((const float*)loss_grad)[pos];
+          volatile float r;
+          if (soft_label) { r = p - ((const float*)label)[i]; r = g * r; }
+          else { r = p * g; if (k == lbl) r = r - g; if (lbl == ignore_index) r = 0.f; }
+          ((float*)logits_grad)[i] = r;
+        } else {
+          const double p = ((const double*)softmax)[i], g = ((const double*)loss_grad)[pos];
+          volatile double r;
+          if (soft_label) { r = p - ((const double*)label)[i]; r = g * r; }
+          else { r = p * g; if (k == lbl) r = r - g; if (lbl == ignore_index) r = 0.0; }
+          ((double*)logits_grad)[i] = r;
+        }
+      }
+    }
+  return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
  * log_softmax_grad.  phi::LogSoftmaxGradKernel<T,CPUContext> -> LogSoftmaxGradFunctor
  * (cpu/log_softmax_grad_kernel.cc:30-62): x viewed as [n][axis_dim][remain];
  *     dx = dy - exp(y) * sum_along_axis(dy)

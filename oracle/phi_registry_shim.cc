@@ -347,6 +347,9 @@ int phi_min_run(const char* name, const char* backend, int key_dtype, const char
       const std::string impl = iv[1] != 0 ? "upscale_in_train" : "downscale_in_infer";
       (*fn)(ctx, WrapIn(in[0]), WrapIn(in[1]), WrapOpt(in[2]), WrapOpt(in[3]), WrapOpt(in[4]), static_cast<float>(f[0]), iv[0] != 0, false,
             0, impl, static_cast<float>(f[1]), op(0), op(1), op(2), op(3), op(4));
+    } else if (fam == "cross_entropy_grad") {  // (ctx, label, softmax, loss_grad, bool soft, bool use_softmax, bool stable, int ignore, int axis, logits_grad)
+      auto* fn = kernel.GetVariadicKernelFn<void (*)(const Ctx&, const DT&, const DT&, const DT&, bool, bool, bool, int, int, DT*)>();
+      (*fn)(ctx, WrapIn(in[0]), WrapIn(in[1]), WrapIn(in[2]), iv[0] != 0, iv[1] != 0, true, static_cast<int>(iv[2]), static_cast<int>(iv[3]), op(0));
     } else if (fam == "fused_layernorm") {  // (ctx, x, bias?, residual?, norm_weight?, norm_bias?, eps, alpha, bna, qscale, qround, qmax, qmin, out, residual_out, mean, var)
       auto* fn = kernel.GetVariadicKernelFn<void (*)(const Ctx&, const DT&, const OptT&, const OptT&, const OptT&, const OptT&, const float,
                                                      const float, const int, const float, const int, const float, const float, DT*, DT*,

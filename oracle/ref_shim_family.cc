@@ -13,6 +13,8 @@
 //   add_grad     phi::AddGradKernel<T,CPUContext>                paddle/phi/kernels/cpu/elementwise_add_grad_kernel.cc:25-62
 //   cross_entropy_with_softmax  phi::CrossEntropyWithSoftmaxKernel<T,CPUContext>
 //                paddle/phi/kernels/cpu/cross_entropy_kernel.cc:73-104 (+ funcs/cross_entropy.cc, compiled as its own TU)
+//   cross_entropy_with_softmax_grad  phi::CrossEntropyWithSoftmaxGradKernel<T,CPUContext>
+//                paddle/phi/kernels/cpu/cross_entropy_grad_kernel.cc:26-215
 //   log_softmax  phi::LogSoftmaxKernel<T,CPUContext>             paddle/phi/kernels/cpu/log_softmax_kernel.cc:40-127
 //   log_softmax_grad  phi::LogSoftmaxGradKernel<T,CPUContext>    paddle/phi/kernels/cpu/log_softmax_grad_kernel.cc:30-84
 //   sum_grad / mean_grad  phi::ReduceSumGradKernel / ReduceMeanGradKernel<T,CPUContext>
@@ -35,6 +37,7 @@
 #include "paddle/phi/kernels/cpu/bitwise_kernel.cc"  // NOLINT (kernel templates live in the .cc)
 #include "paddle/phi/kernels/cpu/cast_kernel.cc"     // NOLINT
 #include "paddle/phi/kernels/cpu/compare_kernel.cc"  // NOLINT
+#include "paddle/phi/kernels/cpu/cross_entropy_grad_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/cross_entropy_kernel.cc"  // NOLINT
 #include "paddle/phi/kernels/cpu/elementwise_add_grad_kernel.cc"       // NOLINT
 #include "paddle/phi/kernels/cpu/elementwise_multiply_grad_kernel.cc"  // NOLINT
@@ -427,5 +430,30 @@ int phi_ref_log_softmax_grad(int dtype, const void* out, const void* out_grad, c
   });
 }
 
+
+// label as for the forward; loss_grad has the logits shape with 1 along axis
+int phi_ref_cross_entropy_with_softmax_grad(int dtype, const void* label, const int64_t* ldims, const void* softmax, const void* loss_grad,
+                                            const int64_t* dims, int rank, int soft_label, int use_softmax, int ignore_index, int axis,
+                                            void* logits_grad) {
+  return Guard([&] {
+    auto& ctx = GetCtx().ctx;
+    auto lt = Wrap(label, ldims, rank, soft_label ? dtype : kInt64);
+    auto st = Wrap(softmax, dims, rank, dtype);
+    std::vector<int64_t> od(dims, dims + rank);
+    od[axis < 0 ? axis + rank : axis] = 1;
+    auto gt = Wrap(loss_grad, od.data(), rank, dtype);
+    auto dxt = Wrap(logits_grad, dims, rank, dtype);
+    switch (dtype) {
+      case kFloat32:
+        phi::CrossEntropyWithSoftmaxGradKernel<float, CPUContext>(ctx, lt, st, gt, soft_label != 0, use_softmax != 0, true, ignore_index, axis, &dxt);
+        break;
+      case kFloat64:
+        phi::CrossEntropyWithSoftmaxGradKernel<double, CPUContext>(ctx, lt, st, gt, soft_label != 0, use_softmax != 0, true, ignore_index, axis, &dxt);
+        break;
+      default: throw std::runtime_error("phi_ref_cross_entropy_with_softmax_grad: dtype not registered on CPU");
+    }
+    if (dxt.data() != logits_grad) std::memcpy(logits_grad, dxt.data(), static_cast<size_t>(dxt.numel()) * phi::SizeOf(dxt.dtype()));
+  });
+}
 
 }  // extern "C"

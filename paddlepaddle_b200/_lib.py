@@ -85,6 +85,7 @@ SIGNATURES = {
     "pdb200_cross_entropy_workspace_bytes": (_sz, [_c_i64p, _int, _int, _int]),
     "pdb200_cross_entropy_with_softmax": (_int, [_vp, _c_i64p, _int, _vp, _int, _int, _int, _int, _int, _int, _vp, _vp, _vp, _sz,
                                                  _vp]),
+    "pdb200_cross_entropy_with_softmax_grad": (_int, [_vp, _int, _vp, _vp, _c_i64p, _int, _int, _int, _int, _int, _int, _vp, _vp]),
     "pdb200_rms_norm": (_int, [_vp, _c_i64p, _int, _vp, _vp, _vp, _vp, ctypes.c_float, _int, _int, _vp, _vp, _vp, _vp]),
     "pdb200_softmax_grad": (_int, [_vp, _vp, _c_i64p, _int, _int, _int, _vp, _vp]),
     "pdb200_log_softmax_grad": (_int, [_vp, _vp, _c_i64p, _int, _int, _int, _vp, _vp]),

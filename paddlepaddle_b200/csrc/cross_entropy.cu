@@ -134,6 +134,144 @@ inline size_t ce_stats_bytes(int64_t n_pos, int dtype) {
   return (size_t)n_pos * 2 * (dtype == PDB200_FLOAT64 ? sizeof(double) : sizeof(float));
 }
 
+// ======================================================================================================
+// Backward: logits_grad from the saved softmax, the labels and loss_grad (use_softmax = true).
+// Replaces (fresh design): phi::CrossEntropyWithSoftmaxGradKernel<T, GPUContext>,
+//   paddle/phi/kernels/gpu/cross_entropy_grad_kernel.cu:281-306 (SoftmaxWithCrossEntropyGradHardLabel / SoftCrossEntropyGradientKernel);
+// arithmetic as the CPU kernel the oracle is built from (cpu/cross_entropy_grad_kernel.cc:143-179):
+//   soft labels: dx = g * (p - y)
+//   hard labels: dx = p * g everywhere, dx[label] = p * g - g (two roundings), a whole position zero when label == ignore_index
+// with p the softmax, g = loss_grad of the position (one value per [n][remain] position), every step in T's accumulator
+// type (16-bit types: float, one rounding at the end).  One pass: p (and y) read once, dx written once.
+// ======================================================================================================
+template <typename A> __device__ __forceinline__ A mul_rn(A a, A b);
+template <> __device__ __forceinline__ float mul_rn<float>(float a, float b) { return __fmul_rn(a, b); }
+template <> __device__ __forceinline__ double mul_rn<double>(double a, double b) { return __dmul_rn(a, b); }
+template <typename A> __device__ __forceinline__ A sub_rn(A a, A b);
+template <> __device__ __forceinline__ float sub_rn<float>(float a, float b) { return __fsub_rn(a, b); }
+template <> __device__ __forceinline__ double sub_rn<double>(double a, double b) { return __dsub_rn(a, b); }
+
+constexpr int kCeThreads = 256;
+constexpr int kCeUnroll = 4;
+
+// class axis last: one CTA per (row, tile of kCeThreads * kCeUnroll vectors)
+template <typename T, typename LT, bool SOFT, bool VECTOR>
+__global__ void __launch_bounds__(kCeThreads) ce_grad_rows_kernel(const T* __restrict__ p, const void* __restrict__ label,
+                                                                  const T* __restrict__ lg, T* __restrict__ dx, int64_t cols,
+                                                                  int64_t tiles_per_row, int64_t ignore_index) {
+  using A = typename AccType<T>::type;
+  constexpr int V = VECTOR ? Vec<T>::N : 1;
+  const int64_t row = (int64_t)blockIdx.x / tiles_per_row;
+  const int64_t tile = (int64_t)blockIdx.x - row * tiles_per_row;
+  const A g = cvt<A>(lg[row]);
+  const int64_t n = cols / V;
+  const T* src = p + row * cols;
+  T* dst = dx + row * cols;
+  const int64_t base = tile * (kCeThreads * kCeUnroll) + threadIdx.x;
+  int64_t lbl = -1;
+  bool ignored = false;
+  if constexpr (!SOFT) {
+    lbl = static_cast<int64_t>(static_cast<const LT*>(label)[row]);
+    ignored = lbl == ignore_index;
+  }
+  const T* ysrc = SOFT ? static_cast<const T*>(label) + row * cols : nullptr;
+  if constexpr (VECTOR) {
+    Vec<T> pv[kCeUnroll], yv[kCeUnroll];
+#pragma unroll
+    for (int u = 0; u < kCeUnroll; ++u) {
+      const int64_t v = base + u * kCeThreads;
+      if (v < n) {
+        pv[u] = ld_stream(src + v * V);
+        if constexpr (SOFT) yv[u] = ld_stream(ysrc + v * V);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kCeUnroll; ++u) {
+      const int64_t v = base + u * kCeThreads;
+      if (v < n) {
+#pragma unroll
+        for (int i = 0; i < V; ++i) {
+          const A pi = cvt<A>(pv[u].v[i]);
+          A r;
+          if constexpr (SOFT) {
+            r = mul_rn<A>(g, sub_rn<A>(pi, cvt<A>(yv[u].v[i])));
+          } else {
+            r = mul_rn<A>(pi, g);
+            if (v * V + i == lbl) r = sub_rn<A>(r, g);
+            if (ignored) r = A(0);
+          }
+          pv[u].v[i] = cvt<T>(r);
+        }
+        st_stream(dst + v * V, pv[u]);
+      }
+    }
+  } else {
+#pragma unroll
+    for (int u = 0; u < kCeUnroll; ++u) {
+      const int64_t v = base + u * kCeThreads;
+      if (v < n) {
+        const A pi = cvt<A>(src[v]);
+        A r;
+        if constexpr (SOFT) {
+          r = mul_rn<A>(g, sub_rn<A>(pi, cvt<A>(ysrc[v])));
+        } else {
+          r = mul_rn<A>(pi, g);
+          if (v == lbl) r = sub_rn<A>(r, g);
+          if (ignored) r = A(0);
+        }
+        dst[v] = cvt<T>(r);
+      }
+    }
+  }
+}
+
+// class axis not last: [n][dim][remain], one thread per element
+template <typename T, typename LT, bool SOFT>
+__global__ void __launch_bounds__(256) ce_grad_general_kernel(const T* __restrict__ p, const void* __restrict__ label,
+                                                              const T* __restrict__ lg, T* __restrict__ dx, int64_t numel,
+                                                              int64_t dim, int64_t remain, int64_t ignore_index) {
+  using A = typename AccType<T>::type;
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < numel; i += stride) {
+    const int64_t b = i / (dim * remain), k = (i / remain) % dim, j = i % remain;
+    const int64_t pos = b * remain + j;
+    const A g = cvt<A>(lg[pos]);
+    const A pi = cvt<A>(p[i]);
+    A r;
+    if constexpr (SOFT) {
+      r = mul_rn<A>(g, sub_rn<A>(pi, cvt<A>(static_cast<const T*>(label)[i])));
+    } else {
+      const int64_t lbl = static_cast<int64_t>(static_cast<const LT*>(label)[pos]);
+      r = mul_rn<A>(pi, g);
+      if (k == lbl) r = sub_rn<A>(r, g);
+      if (lbl == ignore_index) r = A(0);
+    }
+    dx[i] = cvt<T>(r);
+  }
+}
+
+template <typename T, typename LT, bool SOFT>
+int ce_grad_launch(const T* p, const void* label, const T* lg, T* dx, int64_t n, int64_t dim, int64_t remain, int64_t ignore_index,
+                   cudaStream_t st) {
+  constexpr int V = Vec<T>::N;
+  if (remain == 1) {
+    const bool vec = dim % V == 0 && is_aligned16(p) && is_aligned16(dx) && (!SOFT || is_aligned16(label));
+    const int64_t nv = vec ? dim / V : dim;
+    const int64_t tiles = (nv + kCeThreads * kCeUnroll - 1) / (kCeThreads * kCeUnroll);
+    const int64_t blocks = tiles * n;
+    if (blocks <= 0x7fffffffLL) {
+      if (vec) ce_grad_rows_kernel<T, LT, SOFT, true><<<(unsigned)blocks, kCeThreads, 0, st>>>(p, label, lg, dx, dim, tiles, ignore_index);
+      else ce_grad_rows_kernel<T, LT, SOFT, false><<<(unsigned)blocks, kCeThreads, 0, st>>>(p, label, lg, dx, dim, tiles, ignore_index);
+      return after_launch("ce_grad_rows");
+    }
+  }
+  const int64_t numel = n * dim * remain;
+  const int64_t blocks = std::max<int64_t>(1, std::min<int64_t>((numel + 255) / 256, (int64_t)sm_count() * 32));
+  ce_grad_general_kernel<T, LT, SOFT><<<(unsigned)blocks, 256, 0, st>>>(p, label, lg, dx, numel, dim, remain, ignore_index);
+  return after_launch("ce_grad_general");
+}
+
 }  // namespace pdb200
 
 extern "C" size_t pdb200_cross_entropy_workspace_bytes(const int64_t* dims, int rank, int axis, int dtype) {
@@ -203,4 +341,50 @@ extern "C" int pdb200_cross_entropy_with_softmax(const void* logits, const int64
 #undef M
   }
   return fail(PDB200_UNSUPPORTED, "cross_entropy_with_softmax: dtype not built");
+}
+
+
+extern "C" int pdb200_cross_entropy_with_softmax_grad(const void* label, int label_dtype, const void* softmax, const void* loss_grad,
+                                                      const int64_t* dims, int rank, int soft_label, int use_softmax,
+                                                      int ignore_index, int axis, int dtype, void* logits_grad, void* stream) {
+  using namespace pdb200;
+  PDB_CHECK_ARG(rank >= 1 && rank <= PDB200_MAX_RANK && dims != nullptr, "cross_entropy_with_softmax_grad: rank must be in [1, 9]");
+  PDB_CHECK_ARG(axis >= -rank && axis < rank, "The axis is expected to be in range of [" + std::to_string(-rank) + ", " +
+                                                  std::to_string(rank) + "), but got " + std::to_string(axis));
+  if (axis < 0) axis += rank;
+  if (!use_softmax)
+    return fail(PDB200_UNSUPPORTED, "cross_entropy_with_softmax_grad: use_softmax = false (the input already is a distribution) is not on this path");
+  int64_t n = 1, dim = dims[axis], remain = 1;
+  for (int i = 0; i < rank; ++i) {
+    PDB_CHECK_ARG(dims[i] >= 0, "cross_entropy_with_softmax_grad: negative dimension");
+    if (i < axis) n *= dims[i];
+    else if (i > axis) remain *= dims[i];
+  }
+  if (n * dim * remain == 0) return PDB200_OK;
+  PDB_CHECK_ARG(label && softmax && loss_grad && logits_grad, "cross_entropy_with_softmax_grad: NULL tensor pointer");
+  if (soft_label && label_dtype != dtype)
+    return fail(PDB200_INVALID_ARGUMENT, "The Input(Label) should be with the same data type as kernel data type.");
+  if (!soft_label && label_dtype != PDB200_INT64 && label_dtype != PDB200_INT32)
+    return fail(PDB200_UNSUPPORTED, "cross_entropy_with_softmax_grad: hard labels must be int64 or int32, got dtype code " +
+                                        std::to_string(label_dtype));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+#define PDB_CEG_CASE(DT)                                                                                                      \
+  case DT: {                                                                                                                  \
+    using T = typename CType<DT>::type;                                                                                       \
+    const T* p = static_cast<const T*>(softmax);                                                                              \
+    const T* g = static_cast<const T*>(loss_grad);                                                                            \
+    T* dx = static_cast<T*>(logits_grad);                                                                                     \
+    if (soft_label) return ce_grad_launch<T, int64_t, true>(p, label, g, dx, n, dim, remain, ignore_index, st);               \
+    if (label_dtype == PDB200_INT64) return ce_grad_launch<T, int64_t, false>(p, label, g, dx, n, dim, remain, ignore_index, st); \
+    return ce_grad_launch<T, int32_t, false>(p, label, g, dx, n, dim, remain, ignore_index, st);                              \
+  }
+  switch (dtype) {
+    PDB_CEG_CASE(PDB200_FLOAT32)
+    PDB_CEG_CASE(PDB200_FLOAT64)
+    PDB_CEG_CASE(PDB200_FLOAT16)
+    PDB_CEG_CASE(PDB200_BFLOAT16)
+  }
+#undef PDB_CEG_CASE
+  return fail(PDB200_UNSUPPORTED, "cross_entropy_with_softmax_grad: dtype must be float32/float64/float16/bfloat16, got code " +
+                                      std::to_string(dtype));
 }

@@ -116,6 +116,37 @@ def _cross_entropy(logits, label, soft_label, use_softmax, ignore_index, axis, r
     return (loss, sm) if return_softmax else loss
 
 
+def softmax_with_cross_entropy_grad(label, softmax, loss_grad, soft_label=False, ignore_index=-100, axis=-1):
+    """logits_grad of softmax_with_cross_entropy (what _C_ops.cross_entropy_with_softmax_grad computes) from the saved
+    softmax, the labels and the gradient of the loss (the logits' shape with a 1 along `axis`)."""
+    _require_cuda(label, softmax, loss_grad)
+    rank = softmax.dim()
+    if rank == 0:
+        raise ValueError("(InvalidArgument) cross_entropy needs at least one dimension")
+    if not -rank <= axis < rank:
+        raise ValueError(f"(InvalidArgument) The axis is expected to be in range of [{-rank}, {rank}), but got {axis}")
+    ax = axis % rank
+    lshape = tuple(1 if i == ax else d for i, d in enumerate(softmax.shape))
+    if tuple(loss_grad.shape) != lshape or loss_grad.dtype != softmax.dtype:
+        raise ValueError(f"(InvalidArgument) loss_grad must have shape {lshape} and the softmax's dtype")
+    if soft_label:
+        if tuple(label.shape) != tuple(softmax.shape) or label.dtype != softmax.dtype:
+            raise ValueError("(InvalidArgument) soft labels must have the shape and dtype of the logits")
+    else:
+        if label.dtype not in (torch.int64, torch.int32):
+            raise TypeError("(InvalidType) hard labels must be int64 or int32")
+        if tuple(label.shape) != lshape:
+            raise ValueError(f"(InvalidArgument) label has shape {tuple(label.shape)}, expected {lshape}")
+    lib = L.load()
+    label, softmax, loss_grad = label.contiguous(), softmax.contiguous(), loss_grad.contiguous()
+    dx = torch.empty_like(softmax)
+    d, r = L.dims_array(softmax.shape)
+    L.check(lib.pdb200_cross_entropy_with_softmax_grad(_ptr(label), _dtype_code(label.dtype), _ptr(softmax), _ptr(loss_grad), d, r,
+                                                       int(bool(soft_label)), 1, int(ignore_index), int(axis),
+                                                       _dtype_code(softmax.dtype), _ptr(dx), _stream()), lib)
+    return dx
+
+
 def fused_rms_norm(x, norm_weight, norm_bias=None, epsilon=1e-6, begin_norm_axis=1, bias=None, residual=None,
                    quant_scale=-1, quant_round_type=0, quant_max_bound=0, quant_min_bound=0):
     """paddle.incubate.nn.functional.fused_rms_norm (python/paddle/incubate/nn/functional/fused_rms_norm.py):

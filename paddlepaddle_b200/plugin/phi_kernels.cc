@@ -420,6 +420,25 @@ void CrossEntropyWithSoftmaxKernel(const Context& ctx, const DenseTensor& logits
                                           Code(label.dtype()), soft_label, use_softmax, ignore_index, axis,
                                           Code(logits.dtype()), sm, lo, ws, bytes, ctx.stream()));
 }
+// cross_entropy_with_softmax_grad (gpu/cross_entropy_grad_kernel.cu:281-306); use_softmax = false is forwarded
+template <typename T, typename Context>
+void CrossEntropyWithSoftmaxGradKernel(const Context& ctx, const DenseTensor& label, const DenseTensor& softmax,
+                                       const DenseTensor& loss_grad, bool soft_label, bool use_softmax, bool numeric_stable_mode,
+                                       int ignore_index, int axis, DenseTensor* logits_grad) {
+  if (!use_softmax) {
+    using Fn = void (*)(const phi::DeviceContext&, const DenseTensor&, const DenseTensor&, const DenseTensor&, bool, bool, bool, int, int,
+                        DenseTensor*);
+    if (ForwardInTree<Fn>("cross_entropy_with_softmax_grad", phi::Backend::GPU, softmax.dtype(), ctx, label, softmax, loss_grad,
+                          soft_label, use_softmax, numeric_stable_mode, ignore_index, axis, logits_grad))
+      return;
+    PADDLE_THROW(common::errors::Unimplemented("pdb200: cross_entropy_with_softmax_grad with use_softmax = false and no in-tree kernel was registered"));
+  }
+  T* dx = ctx.template Alloc<T>(logits_grad);
+  auto d = Dims(softmax);
+  Check(pdb200_cross_entropy_with_softmax_grad(label.data(), Code(label.dtype()), softmax.data<T>(), loss_grad.data<T>(), d.data(),
+                                               static_cast<int>(d.size()), soft_label, use_softmax, ignore_index, axis,
+                                               Code(softmax.dtype()), dx, ctx.stream()));
+}
 // rms_norm without quantisation (gpu/rms_norm_kernel.cu:1080-1260); a quantised output is forwarded to the in-tree kernel
 template <typename T, typename Context>
 void RmsNormKernel(const Context& ctx, const DenseTensor& x, const paddle::optional<DenseTensor>& bias,
@@ -707,6 +726,8 @@ PD_REGISTER_KERNEL(prod_grad, GPU, ALL_LAYOUT, pdb200_phi::ProdGradKernel, float
 // gpu/cross_entropy_kernel.cu:1460-1466
 PD_REGISTER_KERNEL(cross_entropy_with_softmax, GPU, ALL_LAYOUT, pdb200_phi::CrossEntropyWithSoftmaxKernel, float, double,
                    phi::dtype::float16) {}
+PD_REGISTER_KERNEL(cross_entropy_with_softmax_grad, GPU, ALL_LAYOUT, pdb200_phi::CrossEntropyWithSoftmaxGradKernel, float, double,
+                   phi::dtype::float16) {}  // gpu/cross_entropy_grad_kernel.cu:281-306
 PD_REGISTER_KERNEL(rms_norm, GPU, ALL_LAYOUT, pdb200_phi::RmsNormKernel, float, phi::dtype::float16,
                    phi::dtype::bfloat16) {}  // gpu/rms_norm_kernel.cu:1333-1339
 PD_REGISTER_KERNEL(log_softmax, GPU, ALL_LAYOUT, pdb200_phi::LogSoftmaxKernel, float, double, phi::dtype::float16,

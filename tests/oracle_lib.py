@@ -389,6 +389,24 @@ class Oracle:
         self._check(rc)
         return sm, loss
 
+    def cross_entropy_with_softmax_grad(self, label, softmax, loss_grad, soft_label=False, ignore_index=-100, axis=-1):
+        """-> logits_grad (use_softmax = True); hard labels are int64 with a 1 along `axis`."""
+        softmax = np.ascontiguousarray(softmax)
+        label = np.ascontiguousarray(label if soft_label else np.asarray(label, np.int64))
+        loss_grad = np.ascontiguousarray(loss_grad, softmax.dtype)
+        code = NP2CODE[softmax.dtype]
+        dx = np.empty_like(softmax)
+        d, r = _dims(softmax.shape)
+        if self.kind == "port":
+            rc = self.lib.oracle_cross_entropy_with_softmax_grad(code, _vp(label), _vp(softmax), _vp(loss_grad), d, r, int(soft_label),
+                                                                 int(ignore_index), int(axis), _vp(dx))
+        else:
+            ld, _ = _dims(label.shape)
+            rc = self.lib.phi_ref_cross_entropy_with_softmax_grad(code, _vp(label), ld, _vp(softmax), _vp(loss_grad), d, r,
+                                                                  int(soft_label), 1, int(ignore_index), int(axis), _vp(dx))
+        self._check(rc)
+        return dx
+
     def rms_norm(self, x, gamma, beta=None, eps=1e-6, begin_norm_axis=1, bias=None, residual=None):
         """float64 restatement of the reference test's formula (port only: the reference has no CPU rms_norm).
         -> (out, residual_out or None, inv_var), all float64."""

@@ -253,6 +253,10 @@ def case_rows():
     loss, sm = F.softmax_with_cross_entropy(logits, lbl, return_softmax=True)
     check("cross_entropy_with_softmax", run("cross_entropy_with_softmax", "cross_entropy", [logits, lbl], [sm, loss],
                                             iv=[0, 1, 1, -100, -1]), [sm, loss])
+    lg = rnd((512, 1), torch.float32)
+    wdx = F.softmax_with_cross_entropy_grad(lbl, sm, lg)
+    check("cross_entropy_with_softmax_grad", run("cross_entropy_with_softmax_grad", "cross_entropy_grad", [lbl, sm, lg], [wdx],
+                                                 iv=[0, 1, -100, -1], key=PHI[torch.float32]), wdx)  # key dtype: softmax's
     # rms_norm with the fused residual + bias add
     xr, rr = rnd((700, 4096), torch.bfloat16), rnd((700, 4096), torch.bfloat16)
     wr, br, nb = rnd((4096,), torch.bfloat16) * 0.1 + 1, rnd((4096,), torch.bfloat16), rnd((4096,), torch.bfloat16)
@@ -299,7 +303,7 @@ reg.phi_min_has_kernel.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_in
 NAMES = ["add", "multiply", "subtract", "divide", "maximum", "minimum", "less_than", "less_equal", "greater_than", "greater_equal",
          "equal", "not_equal", "logical_and", "logical_or", "logical_xor", "logical_not", "bitwise_and", "bitwise_or", "bitwise_xor",
          "bitwise_not", "bitwise_left_shift", "bitwise_right_shift", "scale", "cast", "where", "add_grad", "multiply_grad", "sum_grad",
-         "mean_grad", "max_grad", "min_grad", "prod_grad", "cross_entropy_with_softmax", "rms_norm", "log_softmax", "sum_raw", "sum", "mean_raw", "mean", "max_raw", "max",
+         "mean_grad", "max_grad", "min_grad", "prod_grad", "cross_entropy_with_softmax", "cross_entropy_with_softmax_grad", "rms_norm", "log_softmax", "sum_raw", "sum", "mean_raw", "mean", "max_raw", "max",
          "min_raw", "min", "prod", "argmax", "argmin", "softmax", "layer_norm", "softmax_grad", "log_softmax_grad", "layer_norm_grad", "fused_softmax_mask",
          "fused_softmax_mask_upper_triangle", "fused_bias_dropout_residual_layer_norm", "fused_bias_residual_layernorm"]
 print(json.dumps({"calls": n_calls, "alloc_calls": reg.phi_min_alloc_calls(), "failed": failed,

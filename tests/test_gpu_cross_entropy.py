@@ -107,3 +107,53 @@ def test_cross_entropy_input_is_softmax_and_errors(port):
     want_sm, want_loss = port.cross_entropy_with_softmax(x, hard, False, True, -100, -1)
     np.testing.assert_allclose(to_np(tx), want_sm, rtol=1e-5, atol=1e-9)
     np.testing.assert_allclose(to_np(loss), want_loss, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("shape,axis", [((700, 4096), -1), ((64, 1000), 1), ((33, 1001), -1), ((4, 9, 5), 1), ((3, 5, 4, 6), 2),
+                                        ((2, 50000), -1), ((5, 1), -1)])
+def test_cross_entropy_grad_against_compiled_reference(ref, port, shape, axis):
+    """logits_grad (pdb200_cross_entropy_with_softmax_grad) bit-exact against the reference CPU kernel for float32 / float64,
+    hard labels (int64 and int32, with ignored positions) and soft labels; float16 / bfloat16 within one ulp of the rounded
+    float result."""
+    rng = np.random.default_rng(9)
+    ax = axis % len(shape)
+    lshape = tuple(1 if i == ax else d for i, d in enumerate(shape))
+    for dt in (np.float32, np.float64):
+        x = (rng.standard_normal(shape) * 2).astype(dt)
+        sm = port.softmax(x, axis)
+        g = rng.standard_normal(lshape).astype(dt)
+        lbl = rng.integers(0, shape[ax], lshape).astype(np.int64)
+        lbl.reshape(-1)[::3] = -100
+        want = ref.cross_entropy_with_softmax_grad(lbl, sm, g, False, -100, axis)
+        for ldt in (np.int64, np.int32):
+            got = F.softmax_with_cross_entropy_grad(to_dev(lbl.astype(ldt)), to_dev(sm), to_dev(g), soft_label=False, ignore_index=-100, axis=axis)
+            assert np.array_equal(to_np(got), want), (dt, ldt)
+        y = rng.dirichlet(np.ones(shape[ax]), size=int(np.prod(lshape))).astype(dt)
+        y = np.moveaxis(y.reshape(tuple(d for i, d in enumerate(shape) if i != ax) + (shape[ax],)), -1, ax).copy()
+        want = ref.cross_entropy_with_softmax_grad(y, sm, g, True, -100, axis)
+        got = F.softmax_with_cross_entropy_grad(to_dev(y), to_dev(sm), to_dev(g), soft_label=True, axis=axis)
+        assert np.array_equal(to_np(got), want), (dt, "soft")
+    x = (rng.standard_normal(shape) * 2).astype(np.float32)
+    sm = port.softmax(x, axis)
+    g = rng.standard_normal(lshape).astype(np.float32)
+    lbl = rng.integers(0, shape[ax], lshape).astype(np.int64)
+    for half, conv, back in (("bf16", port.f32_to_bf16, port.bf16_to_f32), ("fp16", port.f32_to_fp16, port.fp16_to_f32)):
+        sb, gb = conv(sm), conv(g)
+        want = port.cross_entropy_with_softmax_grad(lbl, back(sb), back(gb), False, -100, axis)
+        got = to_np(F.softmax_with_cross_entropy_grad(to_dev(lbl), to_dev(sb, half), to_dev(gb, half), axis=axis))
+        assert_half_close(got, conv(want), 1, f"ce grad {half} {shape}", kind=half, atol=1e-6)
+
+
+def test_cross_entropy_forward_backward_chain():
+    """softmax_with_cross_entropy then its backward against torch autograd in float64 (mean-reduced loss), config-sized rows."""
+    n, c = 4096, 8192
+    x = torch.randn(n, c, device="cuda")
+    lbl = torch.randint(0, c, (n, 1), device="cuda")
+    loss, sm = F.softmax_with_cross_entropy(x, lbl, return_softmax=True)
+    g = torch.full((n, 1), 1.0 / n, device="cuda")
+    dx = F.softmax_with_cross_entropy_grad(lbl, sm, g)
+    xr = x.double().requires_grad_(True)
+    torch.nn.functional.cross_entropy(xr, lbl.view(-1)).backward()
+    np.testing.assert_allclose(to_np(dx), xr.grad.cpu().numpy(), rtol=1e-4, atol=1e-9)
+    with pytest.raises(ValueError):
+        F.softmax_with_cross_entropy_grad(lbl, sm, g[:5])

@@ -313,3 +313,25 @@ def test_log_softmax_grad_restatement_equals_compiled_reference(port, ref):
             np.testing.assert_allclose(a, b, rtol=tol, atol=tol * float(np.abs(g).sum(axis=axis).max() + 1))
     z = np.zeros((), np.float32)
     assert port.log_softmax_grad(z, z + 3, 0) == 0 and ref.log_softmax_grad(z, z + 3, 0) == 0  # 0-D: gradient 0
+
+
+def test_cross_entropy_grad_restatement_equals_compiled_reference(port, ref):
+    """cross_entropy_with_softmax_grad (round 2, use_softmax = True): the restatement is bit-identical to the compiled
+    reference CPU kernel — soft labels g * (p - y); hard labels p * g with g subtracted at the label's class, a position
+    whose label is ignore_index all zero; class axis last and in the middle."""
+    rng = np.random.default_rng(66)
+    for dt in (np.float32, np.float64):
+        for shape, axis in (((7, 33), -1), ((64, 1000), 1), ((4, 9, 5), 1), ((3, 5, 4, 6), 2), ((5, 1), -1)):
+            ax = axis % len(shape)
+            lshape = tuple(1 if i == ax else d for i, d in enumerate(shape))
+            x = (rng.standard_normal(shape) * 2).astype(dt)
+            sm = port.softmax(x, axis)
+            g = rng.standard_normal(lshape).astype(dt)
+            lbl = rng.integers(0, shape[ax], lshape).astype(np.int64)
+            lbl.reshape(-1)[::3] = -100  # ignored positions
+            a, b = port.cross_entropy_with_softmax_grad(lbl, sm, g, False, -100, axis), ref.cross_entropy_with_softmax_grad(lbl, sm, g, False, -100, axis)
+            assert np.array_equal(a, b), (dt, shape, axis, "hard")
+            y = rng.dirichlet(np.ones(shape[ax]), size=int(np.prod(lshape))).astype(dt)
+            y = np.moveaxis(y.reshape(tuple(d for i, d in enumerate(shape) if i != ax) + (shape[ax],)), -1, ax).copy()
+            a, b = port.cross_entropy_with_softmax_grad(y, sm, g, True, -100, axis), ref.cross_entropy_with_softmax_grad(y, sm, g, True, -100, axis)
+            assert np.array_equal(a, b), (dt, shape, axis, "soft")

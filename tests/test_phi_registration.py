@@ -67,7 +67,7 @@ EXPECT = {  # the registrations of plugin/phi_kernels.cc
     "log_softmax": "float32 float64 float16 bfloat16", "cross_entropy_with_softmax": "float32 float64 float16",
     "softmax": "float32 float64 float16 bfloat16", "layer_norm": "float32 float64 float16 bfloat16",
     "softmax_grad": "float32 float64 float16 bfloat16", "layer_norm_grad": "float32 float64 float16 bfloat16",
-    "log_softmax_grad": "float32 float64 float16 bfloat16",
+    "log_softmax_grad": "float32 float64 float16 bfloat16", "cross_entropy_with_softmax_grad": "float32 float64 float16",
     **{n: "bool int32 uint8 int8 int16 int64 float32 float64 float16 bfloat16"
        for n in ("less_than", "less_equal", "greater_than", "greater_equal", "equal", "not_equal")},
     **{n: "float32 float16 bfloat16 float64 bool int64 int32 int8 int16"
