@@ -403,6 +403,13 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
     lbl = torch.randint(0, 8192, (65536, 1), device="cuda", generator=g)
     rec("next: softmax_with_cross_entropy fp32 [65536,8192] hard labels (softmax + loss)", 2 * 65536 * 8192 * 4 + 65536 * 12,
         lambda: F.softmax_with_cross_entropy(xl32, lbl, return_softmax=True), 65536 * 8192)
+    if hasattr(F, "softmax_with_cross_entropy_grad"):
+        _, sm32 = F.softmax_with_cross_entropy(xl32, lbl, return_softmax=True)
+        lg32 = torch.full((65536, 1), 1.0 / 65536, device="cuda")
+        rec("next: cross_entropy_with_softmax_grad fp32 [65536,8192] hard labels (saved softmax -> logits_grad)",
+            2 * 65536 * 8192 * 4 + 65536 * 12, lambda: F.softmax_with_cross_entropy_grad(lbl, sm32, lg32), 65536 * 8192,
+            key="cross_entropy_with_softmax_grad_fp32")
+        del sm32, lg32
     del xl32, lbl
     xr_ = torch.randn((65536, 8192), device="cuda", generator=g).to(torch.bfloat16)
     rr_ = torch.randn((65536, 8192), device="cuda", generator=g).to(torch.bfloat16)
@@ -435,6 +442,9 @@ def other_configs(torch, paddle, peak, steps, warmup, world, rank, dist):
         del mo_, mg_
     del xr_, rr_, wr_
     rec("next: softmax_grad bf16 [8,32,2048,2048] axis=-1", 3 * n * 2, lambda: F.softmax_grad(yy, dyy, axis=-1), n)
+    if hasattr(F, "log_softmax_grad"):
+        rec("next: log_softmax_grad bf16 [8,32,2048,2048] axis=-1", 3 * n * 2, lambda: F.log_softmax_grad(yy, dyy, axis=-1), n,
+            key="log_softmax_grad_bf16")
     del yy, dyy
     # vocabulary-sized rows: the thread-block-cluster route
     xv = torch.randn((4096, 128256), device="cuda", generator=g).to(torch.bfloat16)
