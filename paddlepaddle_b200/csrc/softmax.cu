@@ -1265,9 +1265,16 @@ int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, typename AccT
   } else {
   constexpr int VN = Vec<T>::N;
   const int64_t nchunk = dim / VN;
-  // chunks per thread: 16-bit rows do best with 4 (32 values a thread), fp32 rows with 2
-  // (8 values): profiles/r1_sweep.txt
-  int C = sizeof(T) == 2 ? (nchunk >= 256 ? 4 : (nchunk >= 128 ? 2 : 1)) : (nchunk >= 256 ? 2 : 1);
+  // chunks per thread: 32 values a thread while that leaves a CTA of >= 64 threads — 4 chunks for 16-bit rows, 8 for fp32 rows
+  // of up to 4096 elements (fp32 [.,2048]: 1.310 -> 1.248 ms on a quarter of config 4, [.,4096] 0.799 -> 0.708, [.,1024]
+  // 0.656 -> 0.622; 8192-element fp32 rows stay at 4 chunks x 512 threads: 0.632 against 0.716) — profiles/r2_notes.txt
+  int C;
+  if (sizeof(T) == 2) {
+    C = nchunk >= 256 ? 4 : (nchunk >= 128 ? 2 : 1);
+  } else {
+    C = nchunk <= 1024 ? 8 : 4;
+    while (C > 1 && nchunk / C < 64) C >>= 1;
+  }
   if (const int o = knobs().softmax_pipe_c) C = o;
   while (C < 8 && (nchunk + C - 1) / C > 512) C <<= 1;  // the kernel is built for <= 512 threads
   int threads = (int)((nchunk + C - 1) / C);
@@ -1280,6 +1287,10 @@ int try_softmax_pipe(const T* x, T* y, int64_t outer, int64_t dim, typename AccT
     int want = 768 / threads;  // ~768 threads per SM, 2..6 CTAs; a 512-thread CTA (rows of 16-32 KB) runs alone:
     const int lo = threads >= 512 ? 1 : 2;  // two of them put 128 KB of rows in flight, fp32 [65536,8192] 0.726 vs 0.634 ms
     want = want < lo ? lo : (want > 6 ? 6 : want);
+    // ... and no more CTAs than keep ~64 KB of rows in flight per SM at two stages each (as in rms_norm / softmax_grad):
+    // 16 KB rows run on 2 CTAs per SM, not 3 — bf16 [.,8192] 0.374 -> 0.325 ms, fp32 [.,4096] 0.701 -> 0.674
+    const int by_bytes = (int)((64 * 1024) / (2 * row_bytes));
+    if (want > by_bytes) want = by_bytes < lo ? lo : by_bytes;
     FuncAttrHold hold;  // released when this lambda returns, i.e. after the launch
     if (!pipe_geometry(kern, threads, row_bytes, want, 3, &per_sm, &stages, &smem, &hold)) return -1;
     int64_t grid = (int64_t)per_sm * sm_count();

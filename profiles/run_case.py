@@ -109,6 +109,11 @@ elif case in ("ln_bf16_f32params", "ln_bf16_f32params_l1"):
     w = torch.rand(8192, device="cuda", generator=g)
     b = torch.rand(8192, device="cuda", generator=g)
     fn = lambda: F.layer_norm(x, [8192], w, b)
+elif case in ("softmax_fp32_8192", "softmax_fp32_1024", "softmax_fp32_4096", "softmax_bf16_8192"):
+    D = int(case.rsplit("_", 1)[1])
+    dt = torch.bfloat16 if "bf16" in case else torch.float32
+    x = (torch.randn(((1 << 29) // D, D), device="cuda", generator=g) * 2).to(dt)
+    fn = lambda: F.softmax(x, axis=-1)
 elif case == "sum_c1":
     x = torch.rand((4096, 4096), device="cuda", generator=g)
     fn = lambda: paddle.sum(x, axis=-1)
