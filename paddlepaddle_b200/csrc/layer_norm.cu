@@ -687,7 +687,10 @@ int layer_norm_typed(const T* x, const P* scale, const P* bias, T* y, void* mean
     break;
   // Fast path: many rows, 16-byte-multiple rows that fit <= 512 threads x 4 chunks -> TMA row pipeline.
   if (vec && sizeof(T) <= 4 && nchunk >= 64 && nchunk <= 512 * 4 && rows >= 4 * (int64_t)sm_count()) {
-    int C = nchunk >= 512 ? 4 : (nchunk >= 256 ? 2 : 1);  // CTAs stay >= 128 threads wide
+    // 32 values a thread (4 chunks of a 16-bit row) down to CTAs of one warp: short rows were the weak spot — bf16 [.,1024]
+    // ran 0.737 ms with 128 threads x 1 chunk on 4 persistent CTAs per SM, 0.357 with 32 threads x 4 chunks, 8 CTAs per SM,
+    // 16 rows per short-lived CTA; [.,2048] 0.445 -> 0.329 (profiles/r2_notes.txt section 13)
+    int C = nchunk >= 128 ? 4 : (nchunk >= 64 ? 2 : 1);
     if (const int o = knobs().ln_pipe_c) C = o;
     int threads = (int)((nchunk + C - 1) / C);
     threads = (threads + 31) / 32 * 32;
@@ -701,11 +704,14 @@ int layer_norm_typed(const T* x, const P* scale, const P* bias, T* y, void* mean
     auto launch = [&](auto kern, size_t extra) -> int {
       int per_sm = 0, stages = 0;
       size_t smem = 0;
-      int want = 512 / threads;  // ~512 threads per SM, 2..4 CTAs, 3 rows in flight each
-      want = want < 2 ? 2 : (want > 4 ? 4 : want);
+      int want = 768 / threads;  // 2..8 CTAs per SM, but no more than keep ~64 KB of rows in flight at two stages each
+      want = want < 2 ? 2 : (want > 8 ? 8 : want);
+      const int by_bytes = (int)((64 * 1024) / (2 * row_bytes));
+      if (want > by_bytes) want = by_bytes < 2 ? 2 : by_bytes;
       FuncAttrHold hold;  // released when this lambda returns, i.e. after the launch
       if (!pipe_geometry(kern, threads, row_bytes, want, 3, &per_sm, &stages, &smem, &hold, extra)) return -1;
       int64_t grid = (int64_t)per_sm * sm_count();
+      if (threads <= 64) grid = std::max<int64_t>(grid, rows / 16);  // short rows: short-lived CTAs of 16 rows
       if (const int rpc = knobs().pipe_rows_per_cta; rpc >= 1)  // tuning knob: short-lived CTAs instead of a persistent grid
         grid = std::max<int64_t>(grid, rows / rpc);
       if (grid > rows) grid = rows;

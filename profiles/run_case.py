@@ -114,6 +114,12 @@ elif case in ("softmax_fp32_8192", "softmax_fp32_1024", "softmax_fp32_4096", "so
     dt = torch.bfloat16 if "bf16" in case else torch.float32
     x = (torch.randn(((1 << 29) // D, D), device="cuda", generator=g) * 2).to(dt)
     fn = lambda: F.softmax(x, axis=-1)
+elif case in ("ln_bf16_1024", "ln_bf16_2048", "ln_bf16_4096", "ln_fp32_4096", "ln_fp32_8192"):
+    D = int(case.rsplit("_", 1)[1])
+    dt = torch.bfloat16 if "bf16" in case else torch.float32
+    x = torch.randn(((1 << 29) // D, D), device="cuda", generator=g).to(dt)
+    w = torch.rand(D, device="cuda", generator=g).to(dt)
+    fn = lambda: F.layer_norm(x, [D], w, w)
 elif case == "sum_c1":
     x = torch.rand((4096, 4096), device="cuda", generator=g)
     fn = lambda: paddle.sum(x, axis=-1)
