@@ -184,7 +184,8 @@ int rms_typed(const T* x, const T* residual, const T* bias, const T* weight, con
   if (residual) vec = vec && is_aligned16(residual) && is_aligned16(residual_out) && (!bias || is_aligned16(bias));
   const int64_t nchunk = D / VN;
   if (vec && nchunk >= 64 && nchunk <= 512 * 4 && rows >= 4 * (int64_t)sm_count()) {
-    int C = nchunk >= 512 ? 4 : (nchunk >= (sizeof(T) == 2 ? 128 : 256) ? 2 : 1);
+    // 32 values a thread for 16-bit rows down to one-warp CTAs, as in layer_norm.cu (short rows: profiles/r2_notes.txt section 13)
+    int C = sizeof(T) == 2 ? (nchunk >= 128 ? 4 : (nchunk >= 64 ? 2 : 1)) : (nchunk >= 512 ? 4 : (nchunk >= 256 ? 2 : 1));
     if (const int o = knobs().rms_pipe_c) C = o;  // tuning knob
     while (C < 4 && (nchunk + C - 1) / C > 512) C <<= 1;
     int threads = (int)((nchunk + C - 1) / C);
@@ -195,7 +196,7 @@ int rms_typed(const T* x, const T* residual, const T* bias, const T* weight, con
       int per_sm = 0, stages = 0;
       size_t smem = 0;
       int want = 768 / threads;
-      want = want < 2 ? 2 : (want > 4 ? 4 : want);
+      want = want < 2 ? 2 : (want > 8 ? 8 : want);
       // ~64 KB of rows in flight per SM at two stages: with a residual (32 KB stages) that is ONE CTA per SM
       // (bf16 [65536,8192] + residual: 0.698 ms with two CTAs, 0.640 ms with one)
       const int by_bytes = (int)((64 * 1024) / (2 * stage_bytes));
@@ -203,6 +204,7 @@ int rms_typed(const T* x, const T* residual, const T* bias, const T* weight, con
       FuncAttrHold hold;  // released when this lambda returns, i.e. after the launch
       if (!pipe_geometry(kern, threads, stage_bytes, want, 3, &per_sm, &stages, &smem, &hold)) return -1;
       int64_t grid = (int64_t)per_sm * sm_count();
+      if (threads <= 64) grid = std::max<int64_t>(grid, rows / 16);  // short rows: short-lived CTAs of 16 rows
       if (grid > rows) grid = rows;
       kern<<<(unsigned)grid, threads, smem, st>>>(x, residual, bias, weight, nbias, out, residual_out, inv_var, rows, (int)D,
                                                   stages, eps, (float)(1.0 / (double)D));

@@ -120,6 +120,11 @@ elif case in ("ln_bf16_1024", "ln_bf16_2048", "ln_bf16_4096", "ln_fp32_4096", "l
     x = torch.randn(((1 << 29) // D, D), device="cuda", generator=g).to(dt)
     w = torch.rand(D, device="cuda", generator=g).to(dt)
     fn = lambda: F.layer_norm(x, [D], w, w)
+elif case in ("rms_bf16_1024", "rms_bf16_2048", "rms_bf16_4096", "rms_bf16_8192"):
+    D = int(case.rsplit("_", 1)[1])
+    x = torch.randn(((1 << 29) // D, D), device="cuda", generator=g).to(torch.bfloat16)
+    w = torch.rand(D, device="cuda", generator=g).to(torch.bfloat16)
+    fn = lambda: F.fused_rms_norm(x, w, None, 1e-6, 1)
 elif case == "sum_c1":
     x = torch.rand((4096, 4096), device="cuda", generator=g)
     fn = lambda: paddle.sum(x, axis=-1)
