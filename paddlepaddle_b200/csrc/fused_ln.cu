@@ -291,7 +291,8 @@ int fln_typed(const T* x, const T* residual, const T* bias, const P* scale, cons
                dro != y && y != x && y != residual;
     const int64_t nchunk = D / VN;
     if (vec && nchunk >= 64 && nchunk <= 512 * 4 && rows >= 4 * (int64_t)sm_count()) {
-      int C = nchunk >= 512 ? 4 : (nchunk >= (sizeof(T) == 2 ? 128 : 256) ? 2 : 1);
+      // 32 values a thread for 16-bit rows, as in layer_norm.cu (short rows: profiles/r2_notes.txt section 13)
+      int C = sizeof(T) == 2 ? (nchunk >= 128 ? 4 : (nchunk >= 64 ? 2 : 1)) : (nchunk >= 512 ? 4 : (nchunk >= 256 ? 2 : 1));
       // float parameters of a 16-bit row live in shared memory (PSM): 2 * D * 4 bytes next to the ring leave room for one CTA
       // per SM, so that CTA is made 512 threads wide
       const bool psm = sizeof(P) > sizeof(T) && scale != nullptr && ln_bias != nullptr && !knobs().no_fln_param_smem &&
@@ -307,12 +308,13 @@ int fln_typed(const T* x, const T* residual, const T* bias, const P* scale, cons
         int per_sm = 0, stages = 0;
         size_t smem = 0;
         int want = 768 / threads;
-        want = want < 2 ? 2 : (want > 4 ? 4 : want);
+        want = want < 2 ? 2 : (want > 8 ? 8 : want);
         const int by_bytes = (int)((64 * 1024) / (2 * stage_bytes));  // ~64 KB of rows in flight per SM at two stages
         if (want > by_bytes) want = by_bytes < 1 ? 1 : by_bytes;
         FuncAttrHold hold;  // released when this lambda returns, i.e. after the launch
         if (!pipe_geometry(kern, threads, stage_bytes, want, 3, &per_sm, &stages, &smem, &hold, param_bytes)) return -1;
         int64_t grid = (int64_t)per_sm * sm_count();
+        if (threads <= 64) grid = std::max<int64_t>(grid, rows / 16);  // short rows: short-lived CTAs of 16 rows
         if (grid > rows) grid = rows;
         kern<<<(unsigned)grid, threads, smem, st>>>(x, residual, bias, scale, ln_bias, y, dro, static_cast<float*>(mean),
                                                     static_cast<float*>(var), rows, (int)D, stages, factor, alpha, epsilon,
