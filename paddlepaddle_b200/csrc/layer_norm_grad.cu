@@ -300,7 +300,9 @@ int layer_norm_grad_typed(const T* x, const P* scale, const void* mean_v, const 
         int per_sm = 0, stages = 0;
         size_t smem = 0;
         FuncAttrHold hold;  // released when this lambda returns, i.e. after the launch
-        if (!pipe_geometry(kern, threads, stage_bytes, 2, 3, &per_sm, &stages, &smem, &hold)) return -1;
+        // CTAs of up to 128 threads (rows of <= 4096 16-bit elements) run four to an SM, wider ones two: bf16 [.,1024]
+        // 1.58 -> 0.92 ms, [.,2048] 0.91 -> 0.60, [.,4096] 0.67 -> 0.55 on 2^29-element tensors (profiles/r2_notes.txt section 14)
+        if (!pipe_geometry(kern, threads, stage_bytes, threads <= 128 ? 4 : 2, 3, &per_sm, &stages, &smem, &hold)) return -1;
         int64_t grid = (int64_t)per_sm * sm_count();
         if (grid > rows) grid = rows;
         if (grid > kLnGradMaxParts) grid = kLnGradMaxParts;
